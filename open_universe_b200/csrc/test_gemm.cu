@@ -1,0 +1,297 @@
+// Standalone GPU unit test for gemm_tc_kernel (no torch): random planes tensors,
+// CPU fp64 reference computed from the same bf16-rounded data.
+//   ./test_gemm <case> [swap_lbo]      case = name or "perf"
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <cmath>
+#include <string>
+#include <vector>
+
+#include "gemm_tc.cuh"
+
+using namespace uv;
+
+#define CK(x)                                                                        \
+  do {                                                                               \
+    cudaError_t e_ = (x);                                                            \
+    if (e_ != cudaSuccess) {                                                         \
+      printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e_), __FILE__, __LINE__); \
+      exit(2);                                                                       \
+    }                                                                                \
+  } while (0)
+
+static uint32_t rng_state = 12345;
+static float frand() {
+  rng_state = rng_state * 1664525u + 1013904223u;
+  return ((rng_state >> 8) & 0xFFFF) / 32768.0f - 1.0f;
+}
+static uint16_t f2bf(float f) {
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  u += 0x7FFF + ((u >> 16) & 1);
+  return (uint16_t)(u >> 16);
+}
+static float bf2f(uint16_t h) {
+  uint32_t u = (uint32_t)h << 16;
+  float f;
+  memcpy(&f, &u, 4);
+  return f;
+}
+
+// Host mirror of a planes tensor.
+struct HT {
+  int C, split, L, B, Lh, P, G, esz;  // L = valid unsplit length; Lh in split rows
+  std::vector<uint8_t> data;
+  char* dev = nullptr;
+  size_t idx(int b, int l, int c) const {
+    int ph = l % split, ll = l / split;
+    size_t row = (size_t)(ph * (C / 8) + c / 8) * P + G + (size_t)b * Lh + ll;
+    return (row * 8 + c % 8);
+  }
+  float get(int b, int l, int c) const {
+    size_t i = idx(b, l, c);
+    if (esz == 2) return bf2f(((const uint16_t*)data.data())[i]);
+    return ((const float*)data.data())[i];
+  }
+  void set(int b, int l, int c, float v) {
+    size_t i = idx(b, l, c);
+    if (esz == 2) ((uint16_t*)data.data())[i] = f2bf(v);
+    else ((float*)data.data())[i] = v;
+  }
+  // raw row access in phase plane `ph` at row-space index m (may be outside [0, L/split))
+  float get_row(int ph, int b, int m, int c) const {
+    size_t row = (size_t)(ph * (C / 8) + c / 8) * P + G + (size_t)b * Lh + m;
+    size_t i = row * 8 + c % 8;
+    return bf2f(((const uint16_t*)data.data())[i]);
+  }
+};
+
+static HT make_tensor(int B, int L, int C, int split, int esz, bool randomize) {
+  HT t;
+  t.B = B; t.L = L; t.C = C; t.split = split; t.esz = esz; t.G = kGuard;
+  int rows = (L + split - 1) / split;
+  t.Lh = ((rows + 2 + 7) / 8) * 8;
+  t.P = t.G + ((B * t.Lh + 127) / 128) * 128 + t.G;
+  t.data.assign((size_t)split * (C / 8) * t.P * 8 * esz, 0);
+  if (randomize)
+    for (int b = 0; b < B; ++b)
+      for (int l = 0; l < L; ++l)
+        for (int c = 0; c < C; ++c) t.set(b, l, c, frand());
+  CK(cudaMalloc(&t.dev, t.data.size()));
+  CK(cudaMemcpy(t.dev, t.data.data(), t.data.size(), cudaMemcpyHostToDevice));
+  return t;
+}
+static TensDesc desc_of(const HT& t) {
+  TensDesc d;
+  d.base = t.dev; d.esize_log2 = t.esz == 2 ? 1 : 2; d.nchunks = t.C / 8; d.split = t.split;
+  d.Lh = t.Lh; d.P = t.P; d.G = t.G; d.pad_ = 0;
+  return d;
+}
+static void fetch(HT& t) { CK(cudaMemcpy(t.data.data(), t.dev, t.data.size(), cudaMemcpyDeviceToHost)); }
+
+struct Case {
+  const char* name;
+  int B, L_out_space;  // rows per utterance in A row space (M_valid)
+  int C_in, n_src, smin, smax, KC;
+  int C_out, up, N_TILE;
+  bool bias, film, add1, add2f32;
+  float scale;
+  int out1_split;   // 0 = no second output
+  bool rm;
+};
+
+static const Case kCases[] = {
+    {"k1", 2, 200, 64, 1, 0, 0, 64, 64, 1, 64, false, false, false, false, 1.f, 0, false},
+    {"k5", 2, 200, 64, 1, -2, 2, 64, 64, 1, 64, true, false, false, false, 1.f, 0, false},
+    {"c32", 3, 301, 32, 1, -2, 2, 32, 32, 1, 32, true, false, false, false, 1.f, 0, false},
+    {"c48", 2, 150, 48, 1, -1, 1, 48, 48, 1, 48, true, false, false, false, 1.f, 0, false},
+    {"big", 2, 401, 256, 1, -1, 1, 64, 512, 1, 256, true, false, false, false, 1.f, 0, false},
+    {"down", 2, 100, 64, 4, -1, 1, 64, 128, 1, 128, true, false, false, false, 1.f, 0, false},
+    {"up", 2, 100, 128, 1, -1, 1, 64, 64, 4, 64, true, false, true, false, 0.70710678f, 0, false},
+    {"epi", 2, 200, 64, 1, -2, 2, 64, 64, 1, 64, true, true, true, true, 0.5f, 2, true},
+    {"mel", 2, 201, 80, 1, -1, 1, 80, 512, 1, 256, true, false, false, false, 1.f, 0, false},
+};
+
+static int run_case(const Case& c, int swap_lbo, int num_sms) {
+  const int n_shift = c.smax - c.smin + 1;
+  const int N_total = c.up * c.C_out;
+  // A: split tensor with n_src phases; unsplit valid length = M_valid * n_src
+  HT A = make_tensor(c.B, c.L_out_space * c.n_src, c.C_in, c.n_src, 2, true);
+  const int L_out = c.L_out_space * c.up;
+  // weights [n][s][q][ci]
+  std::vector<float> W((size_t)N_total * c.n_src * n_shift * c.C_in);
+  for (auto& w : W) w = bf2f(f2bf(frand() * 0.1f));
+  const int n_groups = c.C_in / c.KC, n_tiles_n = N_total / c.N_TILE, kcc = c.KC / 8;
+  std::vector<uint16_t> img((size_t)N_total * c.n_src * n_shift * c.C_in);
+  for (int nt = 0; nt < n_tiles_n; ++nt)
+    for (int s = 0; s < c.n_src; ++s)
+      for (int g = 0; g < n_groups; ++g)
+        for (int q = 0; q < n_shift; ++q) {
+          size_t base = ((((size_t)nt * c.n_src + s) * n_groups + g) * n_shift + q) * (size_t)c.N_TILE * c.KC;
+          for (int j = 0; j < kcc; ++j)
+            for (int n = 0; n < c.N_TILE; ++n)
+              for (int e = 0; e < 8; ++e) {
+                int ci = g * c.KC + j * 8 + e;
+                int ng = nt * c.N_TILE + n;
+                img[base + ((size_t)j * c.N_TILE + n) * 8 + e] =
+                    f2bf(W[(((size_t)ng * c.n_src + s) * n_shift + q) * c.C_in + ci]);
+              }
+        }
+  char* d_w;
+  CK(cudaMalloc(&d_w, img.size() * 2));
+  CK(cudaMemcpy(d_w, img.data(), img.size() * 2, cudaMemcpyHostToDevice));
+  std::vector<float> bias(c.C_out), film(2 * c.C_out);
+  for (auto& v : bias) v = frand() * 0.5f;
+  for (auto& v : film) v = frand();
+  float *d_bias, *d_film;
+  CK(cudaMalloc(&d_bias, bias.size() * 4));
+  CK(cudaMalloc(&d_film, film.size() * 4));
+  CK(cudaMemcpy(d_bias, bias.data(), bias.size() * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(d_film, film.data(), film.size() * 4, cudaMemcpyHostToDevice));
+
+  HT add1 = make_tensor(c.B, L_out, c.C_out, 1, 2, true);
+  HT add2 = make_tensor(c.B, L_out, c.C_out, 1, 4, true);
+  HT out0 = make_tensor(c.B, L_out, c.C_out, 1, 2, false);
+  HT out1 = make_tensor(c.B, L_out, c.C_out, c.out1_split ? c.out1_split : 1, 2, false);
+  float* d_rm = nullptr;
+  const int m_rows = c.B * A.Lh;
+  if (c.rm) {
+    CK(cudaMalloc(&d_rm, (size_t)m_rows * N_total * 4));
+    CK(cudaMemset(d_rm, 0, (size_t)m_rows * N_total * 4));
+  }
+  int* d_err;
+  CK(cudaMalloc(&d_err, 4));
+  CK(cudaMemset(d_err, 0, 4));
+
+  GemmParams p;
+  memset(&p, 0, sizeof(p));
+  p.a_base = A.dev; p.a_nchunks = c.C_in / 8; p.a_P = A.P; p.a_G = A.G; p.n_src = c.n_src;
+  p.smin = c.smin; p.smax = c.smax; p.KC = c.KC; p.n_groups = n_groups;
+  p.w = d_w; p.N_TILE = c.N_TILE; p.n_tiles_n = n_tiles_n;
+  p.m_rows = m_rows; p.Lh_A = A.Lh; p.M_valid = c.L_out_space;
+  p.up = c.up; p.C_out = c.C_out;
+  p.bias = c.bias ? d_bias : nullptr;
+  p.film = c.film ? d_film : nullptr;
+  if (c.add1) p.add1 = desc_of(add1);
+  if (c.add2f32) p.add2 = desc_of(add2);
+  p.scale = c.scale;
+  p.n_out = c.out1_split ? 2 : 1;
+  p.out[0].t = desc_of(out0); p.out[0].act = 0;
+  p.out[1].t = desc_of(out1); p.out[1].act = 2; p.out[1].a1 = 0.25f; p.out[1].a2 = -0.5f;
+  p.rm_out = d_rm; p.rm_ld = N_total;
+  p.dbg_swap_lbo = swap_lbo;
+  p.err_flag = d_err;
+
+  CK(gemm_launch(p, num_sms, 0));
+  cudaError_t e = cudaDeviceSynchronize();
+  int err = 0;
+  if (e != cudaSuccess) {
+    printf("[%s] kernel failed: %s\n", c.name, cudaGetErrorString(e));
+    return 1;
+  }
+  CK(cudaMemcpy(&err, d_err, 4, cudaMemcpyDeviceToHost));
+  fetch(out0);
+  fetch(out1);
+  std::vector<float> rm;
+  if (c.rm) {
+    rm.resize((size_t)m_rows * N_total);
+    CK(cudaMemcpy(rm.data(), d_rm, rm.size() * 4, cudaMemcpyDeviceToHost));
+  }
+
+  double max_err = 0, max_err1 = 0, max_rm = 0, max_ref = 0;
+  for (int b = 0; b < c.B; ++b)
+    for (int m = 0; m < c.L_out_space; ++m)
+      for (int n = 0; n < N_total; ++n) {
+        double acc = 0;
+        for (int s = 0; s < c.n_src; ++s)
+          for (int q = 0; q < n_shift; ++q)
+            for (int ci = 0; ci < c.C_in; ++ci)
+              acc += (double)A.get_row(s, b, m + c.smin + q, ci) *
+                     W[(((size_t)n * c.n_src + s) * n_shift + q) * c.C_in + ci];
+        int phase = n / c.C_out, co = n % c.C_out, l = c.up * m + phase;
+        double v = acc;
+        if (c.bias) v += bias[co];
+        if (c.add1) v += add1.get(b, l, co);
+        if (c.add2f32) v += add2.get(b, l, co);
+        v *= c.scale;
+        if (c.film) v = film[co] * v + film[c.C_out + co];
+        max_ref = fmax(max_ref, fabs(v));
+        max_err = fmax(max_err, fabs(v - out0.get(b, l, co)));
+        if (c.out1_split) {
+          double w = v >= 0 ? v : 0.25 * v;
+          w = w >= 0 ? w : -0.5 * w;
+          max_err1 = fmax(max_err1, fabs(w - out1.get(b, l, co)));
+        }
+        if (c.rm) max_rm = fmax(max_rm, fabs(v - rm[(size_t)(b * A.Lh + m) * N_total + n]));
+      }
+  // gap rows must stay zero
+  double gap = 0;
+  for (int b = 0; b < c.B; ++b)
+    for (int co = 0; co < c.C_out; ++co) {
+      size_t row = (size_t)(co / 8) * out0.P + out0.G + (size_t)b * out0.Lh + L_out;
+      gap = fmax(gap, fabs(bf2f(((uint16_t*)out0.data.data())[row * 8 + co % 8])));
+    }
+  bool ok = max_err < 0.02 * fmax(1.0, max_ref) && max_err1 < 0.02 * fmax(1.0, max_ref) && max_rm < 1e-3 * fmax(1.0, max_ref) &&
+            gap == 0 && err == 0;
+  printf("[%s] swap=%d max_ref=%.4f err_out0=%.5f err_out1=%.5f err_rm=%.6f gap=%.3g flag=%d -> %s\n", c.name, swap_lbo,
+         max_ref, max_err, max_err1, max_rm, gap, err, ok ? "PASS" : "FAIL");
+  return ok ? 0 : 1;
+}
+
+// Throughput of layer-shaped problems (cfg 2 sizes: B=64, 4 s clips).
+static void run_perf(int num_sms) {
+  struct PC { const char* name; int B, Lv, C, k; } pcs[] = {
+      {"L0 C32 k5", 64, 64160, 32, 5}, {"L0 C32 k3", 64, 64160, 32, 3}, {"L1 C64 k5", 64, 32080, 64, 5},
+      {"L2 C128 k5", 64, 8020, 128, 5}, {"L3 C256 k5", 64, 2005, 256, 5}, {"L4 C512 k5", 64, 401, 512, 5},
+      {"L4 C512 k3", 64, 401, 512, 3}};
+  for (auto& pc : pcs) {
+    HT A = make_tensor(pc.B, pc.Lv, pc.C, 1, 2, false);
+    CK(cudaMemset(A.dev, 0x3c, A.data.size()));  // small finite bf16 values everywhere
+    HT O = make_tensor(pc.B, pc.Lv, pc.C, 1, 2, false);
+    HT O2 = make_tensor(pc.B, pc.Lv, pc.C, 1, 2, false);
+    const int KC = pc.C < 64 ? pc.C : 64, NT = pc.C < 256 ? pc.C : 256;
+    size_t wbytes = (size_t)pc.C * pc.C * pc.k * 2;
+    char* d_w;
+    CK(cudaMalloc(&d_w, wbytes));
+    CK(cudaMemset(d_w, 0x3c, wbytes));
+    GemmParams p;
+    memset(&p, 0, sizeof(p));
+    p.a_base = A.dev; p.a_nchunks = pc.C / 8; p.a_P = A.P; p.a_G = A.G; p.n_src = 1;
+    p.smin = -(pc.k / 2); p.smax = pc.k / 2; p.KC = KC; p.n_groups = pc.C / KC;
+    p.w = d_w; p.N_TILE = NT; p.n_tiles_n = pc.C / NT;
+    p.m_rows = pc.B * A.Lh; p.Lh_A = A.Lh; p.M_valid = pc.Lv; p.up = 1; p.C_out = pc.C;
+    p.scale = 1.f; p.n_out = 2;
+    p.out[0].t = desc_of(O); p.out[1].t = desc_of(O2); p.out[1].act = 1; p.out[1].a1 = 0.25f;
+    int* d_err; CK(cudaMalloc(&d_err, 4)); CK(cudaMemset(d_err, 0, 4));
+    p.err_flag = d_err;
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    for (int i = 0; i < 3; ++i) CK(gemm_launch(p, num_sms, 0));
+    CK(cudaDeviceSynchronize());
+    const int iters = 10;
+    CK(cudaEventRecord(e0));
+    for (int i = 0; i < iters; ++i) CK(gemm_launch(p, num_sms, 0));
+    CK(cudaEventRecord(e1));
+    CK(cudaDeviceSynchronize());
+    float ms; CK(cudaEventElapsedTime(&ms, e0, e1)); ms /= iters;
+    double flop = 2.0 * pc.B * pc.Lv * (double)pc.C * pc.C * pc.k;
+    double bytes = (double)pc.B * pc.Lv * pc.C * 2 * 3;
+    printf("[perf %s] %.3f ms  %.1f TFLOP/s  %.0f GB/s (1 read + 2 writes)\n", pc.name, ms, flop / ms * 1e-9, bytes / ms * 1e-6);
+    cudaFree(A.dev); cudaFree(O.dev); cudaFree(O2.dev); cudaFree(d_w); cudaFree(d_err);
+  }
+}
+
+int main(int argc, char** argv) {
+  if (argc < 2) { printf("usage: test_gemm <case|perf|list> [swap]\n"); return 2; }
+  int dev_sms = 0;
+  CK(cudaDeviceGetAttribute(&dev_sms, cudaDevAttrMultiProcessorCount, 0));
+  std::string name = argv[1];
+  int swap = argc > 2 ? atoi(argv[2]) : 0;
+  if (name == "list") { for (auto& c : kCases) printf("%s\n", c.name); return 0; }
+  if (name == "perf") { run_perf(dev_sms); return 0; }
+  for (auto& c : kCases)
+    if (name == c.name) return run_case(c, swap, dev_sms);
+  printf("unknown case %s\n", name.c_str());
+  return 2;
+}

@@ -1,0 +1,89 @@
+// Shared device-side definitions for the open-universe B200 kernels.
+//
+// Activation layout ("planes"): every activation tensor of C channels lives in
+// HBM as  [phase t < split][chunk j < C/8][row < P][8 channels]  (bf16 or f32),
+// where a row is  G + b*Lh + (l / split)  for utterance b, sample l (phase
+// t = l % split).  Rows G + b*Lh + [Lvalid, Lh) between utterances and the
+// guard rows [0,G) / tail are zero and are NEVER written: they are the zero
+// padding of every "same" convolution (reference: padding="same" in
+// open_universe/networks/universe/blocks.py:293-316), so a conv tap is just a
+// row shift of the A operand and needs no bounds handling.
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace uv {
+
+constexpr int kGuard = 8;        // guard rows at the start/end of each plane
+constexpr int kTileM = 128;      // rows per GEMM tile (UMMA M)
+
+struct TensDesc {
+  char* base;        // nullptr => unused
+  int esize_log2;    // 1 = bf16, 2 = f32
+  int nchunks;       // C / 8
+  int split;         // phase split r (1 = plain)
+  int Lh;            // utterance pitch in rows
+  int P;             // plane pitch in rows
+  int G;             // guard rows
+  int pad_;
+};
+
+struct OutDesc {
+  TensDesc t;
+  int act;           // 0 none, 1 prelu(a1), 2 prelu(prelu(.,a1),a2)
+  float a1, a2;
+  int pad_;
+};
+
+struct GemmParams {
+  // ---- A operand: bf16 planes tensor, sources = its phases
+  const char* a_base;
+  int a_nchunks;     // chunks per source (C_in / 8)
+  int a_P;           // plane pitch (rows)
+  int a_G;
+  int n_src;         // number of sources (phases of A)
+  int smin, smax;    // row shifts applied to every source
+  int KC;            // channels per K group (multiple of 16)
+  int n_groups;      // C_in / KC
+  // ---- B operand: packed weight images
+  //  [n_tile][src][group][shift][KC/8][N_TILE][8] bf16
+  const char* w;
+  int N_TILE;        // multiple of 16, <= 256
+  int n_tiles_n;
+  // ---- row space
+  int m_rows;        // B * Lh_A flat rows
+  int Lh_A;          // utterance pitch of the row space
+  int M_valid;       // valid rows per utterance
+  int n_tiles_m;
+  // ---- epilogue
+  int up;            // l_out = up*m + phase, phase = n_glob / C_out
+  int C_out;
+  const float* bias; // [C_out] or null
+  const float* film; // [2*C_out] gamma|beta or null
+  TensDesc add1, add2;
+  float scale;
+  int n_out;
+  OutDesc out[3];
+  float* rm_out;     // optional f32 row-major output [m_rows][rm_ld], column n_glob
+  int rm_ld;
+  // ---- pipeline (filled by host)
+  int na_stages, nb_stages;
+  int a_stage_bytes, b_stage_bytes;
+  int dbg_swap_lbo;  // test hook: swap LBO/SBO roles in the smem descriptors
+  int* err_flag;     // set on watchdog timeout
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+
+__device__ __forceinline__ float prelu1(float v, float a) { return v >= 0.f ? v : a * v; }
+
+__device__ __forceinline__ float apply_act(float v, int act, float a1, float a2) {
+  if (act >= 1) v = prelu1(v, a1);
+  if (act == 2) v = prelu1(v, a2);
+  return v;
+}
+
+}  // namespace uv
