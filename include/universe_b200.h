@@ -1,0 +1,148 @@
+/* universe_b200.h -- C ABI of the B200-native UNIVERSE / UNIVERSE++ enhance() path.
+ *
+ * The reference (kolyangg/open-universe) is 100 % Python and has no FFI of its
+ * own: its boundary for this path is
+ *     open_universe/inference_utils/model_loader.py:65-140   load_model()
+ *     open_universe/networks/universe/universe.py:231-375    Universe.enhance()
+ * which today bottom out in torch / cuDNN library calls.  This header is the
+ * native boundary that replaces those library calls: plain pointers and sizes,
+ * no torch types.  The Python drop-in (open_universe_b200/) binds it with
+ * ctypes; INTEGRATION.md shows the stub a reference maintainer would add.
+ *
+ * Model = a read-only weight blob (folded + packed by the host compiler).
+ * Plan  = an "op program" for one (batch, length, n_steps) shape: a flat array
+ *         of uv_op records, each one kernel launch of the hot path, plus the
+ *         workspace ("arena") size.  uv_plan_create() captures the whole program
+ *         (conditioner once + n_steps score evaluations + sampler updates) into
+ *         ONE CUDA graph; uv_enhance() replays it.
+ *
+ * All functions return 0 on success, a negative uv_status otherwise;
+ * uv_last_error() gives a human readable message (thread local).
+ * No exceptions cross the boundary.  Calls on one handle must be serialised by
+ * the caller.  All device work is enqueued on the cudaStream_t passed in
+ * (as void*; NULL = legacy default stream).
+ */
+#ifndef UNIVERSE_B200_H_
+#define UNIVERSE_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define UV_ABI_VERSION 3
+
+typedef enum {
+  UV_OK = 0,
+  UV_ERR_INVALID = -1,   /* bad argument / malformed program            */
+  UV_ERR_CUDA = -2,      /* CUDA runtime error (message has the detail) */
+  UV_ERR_NO_DEVICE = -3, /* no sm_100 device                            */
+  UV_ERR_KERNEL = -4     /* device-side watchdog fired                  */
+} uv_status;
+
+/* ---- tensor addressing ("planes" layout, see csrc/uv_common.cuh) ---------
+ * element (utterance b, sample l, channel c) lives at
+ *   off + (((l % split) * nch + c / 8) * P + G + b * Lh + l / split) * 8 + c % 8   [elements]
+ */
+typedef struct {
+  int64_t off;    /* byte offset into the arena; < 0 => unused            */
+  int32_t dtype;  /* 1 = bf16, 2 = f32                                    */
+  int32_t nch;    /* channels / 8                                         */
+  int32_t split;  /* phase split r (1 = plain)                            */
+  int32_t Lh;     /* utterance pitch (rows)                               */
+  int32_t P;      /* plane pitch (rows)                                   */
+  int32_t G;      /* guard rows at the start of each plane                */
+} uv_tens;
+
+typedef struct {
+  uv_tens t;
+  int32_t act;    /* 0 none, 1 prelu(a1), 2 prelu(prelu(., a1), a2)       */
+  float a1, a2;
+  int32_t pad_;
+} uv_out;
+
+typedef enum {
+  UV_OP_PREP = 1,     /* pad + per-utterance normalise   (universe.py:219-223, utils/norm.py:47-87)   */
+  UV_OP_MEL = 2,      /* framed DFT power -> mel         (condition.py:92-108)                        */
+  UV_OP_MEL_FIN = 3,  /* global mel normalisation -> bf16 planes                                      */
+  UV_OP_CONV_IN = 4,  /* 1 -> C k3 input conv on a signal (score.py:285, condition.py:360)            */
+  UV_OP_GEMM = 5,     /* multi-tap tensor-core conv GEMM (blocks.py:331-416, every dense layer)       */
+  UV_OP_GRU = 6,      /* bidirectional GRU recurrence    (score.py:117, condition.py:212)             */
+  UV_OP_CONV_OUT = 7, /* C -> 1 k3 output conv + EDM wrapper + sampler update (universe.py:197-209,334-343) */
+  UV_OP_INIT_X = 8,   /* x = sigma_0 * z_0               (universe.py:326)                            */
+  UV_OP_POST = 9,     /* crop, keep_rms, peak normalise  (universe.py:349-357)                        */
+  UV_OP_FILM = 10     /* noise-level embedding + FiLM table (sigma_block.py, score.py:109,208)        */
+} uv_op_type;
+
+/* One record per kernel launch.  Offsets named *_w index the model's weight
+ * blob, all others index the plan's arena; < 0 means "absent".            */
+typedef struct {
+  int32_t type;
+  int32_t step;          /* sampler step this op belongs to (-1 = conditioner / setup) */
+  /* ---- UV_OP_GEMM (also GRU epilogue fields: add1, scale, n_out, out) */
+  uv_tens a;             /* A operand (bf16); its phases are the K sources */
+  int32_t n_src, smin, smax, KC;
+  int64_t w_w;           /* packed weight images                           */
+  int32_t N_TILE, N_total;
+  int32_t m_rows, Lh_A, M_valid, up, C_out;
+  int64_t bias_w;        /* f32 [C_out]                                    */
+  int64_t film;          /* arena: f32 [2*C_out] gamma|beta                */
+  uv_tens add1, add2;
+  float scale;
+  int32_t n_out;
+  uv_out out[3];
+  int64_t rm_out;        /* arena: f32 row-major [m_rows][rm_ld]           */
+  int32_t rm_ld;
+  /* ---- generic fields used by the small ops (meaning per type, see csrc/ops.cu) */
+  int32_t B, T, Lp, C, H, F;
+  int32_t i0, i1, i2, i3;
+  int64_t p0, p1, p2, p3, p4, p5;
+  float f0, f1, f2, f3;
+} uv_op;
+
+typedef struct uv_model uv_model;
+typedef struct uv_plan uv_plan;
+
+/* Sampler coefficients of one step (host computed from sigma, eta, beta and the
+ * EDM weights; universe.py:175-209,301-343):  x <- a*x + b*net + c*z          */
+typedef struct {
+  float a, b, c, pad_;
+} uv_step_coef;
+
+int uv_abi_version(void);
+const char* uv_last_error(void);
+
+/* Uploads the packed weight blob to `device`. */
+int uv_model_create(uv_model** out, const void* weights, size_t nbytes, int device);
+void uv_model_destroy(uv_model* m);
+
+/* Builds a plan: allocates + zeroes the arena, copies `init` (nbytes_init bytes)
+ * to arena offset init_off, runs the ops flagged step == -2 once (plan-time
+ * setup such as the FiLM table) and captures the remaining ops in a CUDA graph. */
+int uv_plan_create(uv_plan** out, uv_model* m, const uv_op* ops, int n_ops, size_t arena_bytes,
+                   const void* init, size_t nbytes_init, size_t init_off, int n_steps, int use_graph);
+void uv_plan_destroy(uv_plan* p);
+size_t uv_plan_arena_bytes(const uv_plan* p);
+
+/* One enhance() pass.  Device pointers: mix [B][T] f32, noise [n_steps][B][Lp]
+ * f32, out [B][T] f32, dbg_net (optional) [n_steps][B][Lp] f32 per-step network
+ * outputs.  coef: host array of n_steps uv_step_coef. keep_rms as in enhance(). */
+int uv_enhance(uv_plan* p, const float* mix, const float* noise, float* out, float* dbg_net,
+               const uv_step_coef* coef, int keep_rms, void* stream);
+
+/* Debug / parity: run ops [first, last) eagerly (no graph) on `stream` with the
+ * same io pointers, and copy a byte range of the arena back / forth.       */
+int uv_run_ops(uv_plan* p, int first, int last, const float* mix, const float* noise, float* out,
+               float* dbg_net, const uv_step_coef* coef, int keep_rms, void* stream);
+int uv_arena_read(uv_plan* p, size_t off, void* host_dst, size_t nbytes);
+int uv_arena_write(uv_plan* p, size_t off, const void* host_src, size_t nbytes);
+
+/* Number of kernel launches one uv_enhance() replays (for bench accounting). */
+int uv_plan_num_launches(const uv_plan* p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* UNIVERSE_B200_H_ */

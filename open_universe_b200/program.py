@@ -1,0 +1,427 @@
+"""Op-program builder: turns a packed model + a shape (B, T, n_steps) into the flat
+list of uv_op records (one per kernel launch) that the native executor captures
+into a CUDA graph.  The topology mirrors the reference forward passes:
+
+  Universe.enhance            networks/universe/universe.py:231-375
+  ConditionerNetwork.forward  networks/universe/condition.py:346-377 (+189-220, 264-270)
+  ScoreNetwork.forward        networks/universe/score.py:278-298 (+105-128, 197-211)
+  ConvBlock.forward           networks/universe/blocks.py:331-416
+
+Every tensor consumed by a tensor-core GEMM is stored already PReLU-activated
+with the consumer's slope (the MMA reads shared memory directly, so the
+activation is applied by the producer's epilogue); raw copies are kept only
+where a residual / skip / condition needs them.
+"""
+import math
+
+import numpy as np
+import torch
+
+from . import _abi
+from ._abi import DT_BF16, DT_F32, UvTens, new_op
+
+G = 8  # guard rows (csrc/uv_common.cuh kGuard)
+SQRT1_2 = 1.0 / math.sqrt(2.0)
+
+
+def _ru(x, m):
+    return (x + m - 1) // m * m
+
+
+class Level:
+    """Row geometry of one time resolution."""
+
+    def __init__(self, B, L):
+        self.L = L
+        self.Lh = _ru(L + 2, 8)
+        self.rows = B * self.Lh
+        self.P = G + _ru(self.rows, 128) + G
+
+
+class Program:
+    def __init__(self, pm, B, T, n_steps, sigmas, log10_sigmas, in_scales):
+        self.pm = pm
+        self.ops = []
+        self.names = []
+        self.arena = 0
+        self.tensors = {}
+        self.B, self.T, self.n_steps = B, T, n_steps
+        self.sigmas, self.log10_sigmas, self.in_scales = sigmas, log10_sigmas, in_scales
+
+    # ---- arena
+    def alloc(self, nbytes, align=1024):
+        off = _ru(self.arena, align)
+        self.arena = off + nbytes
+        return off
+
+    def tens(self, name, lev, C, split=1, dtype=DT_BF16):
+        """Allocates (or returns) the planes tensor `name` whose row space is `lev`."""
+        if name in self.tensors:
+            t = self.tensors[name]
+            assert (t.nch, t.split, t.Lh, t.P, t.dtype) == (C // 8, split, lev.Lh, lev.P, dtype), name
+            return t
+        assert C % 8 == 0
+        es = 2 if dtype == DT_BF16 else 4
+        off = self.alloc(split * (C // 8) * lev.P * 8 * es)
+        t = UvTens(off, dtype, C // 8, split, lev.Lh, lev.P, G)
+        self.tensors[name] = t
+        return t
+
+    def emit(self, op, name):
+        self.ops.append(op)
+        self.names.append(name)
+        return op
+
+    # ---- op helpers
+    def gemm(self, name, layer, a, lev_rows, M_valid, outs, step=-1, add1=None, add2=None, scale=1.0,
+             film=-1, rm_out=-1, bias=True):
+        ly = self.pm.layers[layer]
+        op = new_op(_abi.OP_GEMM, step)
+        op.a = a
+        assert a.nch * 8 == ly["C_in"] and a.split == ly["n_src"], (name, a.nch * 8, ly["C_in"], a.split, ly["n_src"])
+        assert (a.Lh, a.P) == (lev_rows.Lh, lev_rows.P), name
+        op.n_src, op.smin, op.smax, op.KC = ly["n_src"], ly["smin"], ly["smax"], ly["KC"]
+        op.w_w, op.N_TILE, op.N_total = ly["w_w"], ly["N_TILE"], ly["N_total"]
+        op.m_rows, op.Lh_A, op.M_valid = lev_rows.rows, lev_rows.Lh, M_valid
+        op.up, op.C_out = ly["up"], ly["C_out"]
+        op.bias_w = ly["bias_w"] if bias else -1
+        op.film = film
+        if add1 is not None:
+            op.add1 = add1
+        if add2 is not None:
+            op.add2 = add2
+        op.scale = scale
+        op.n_out = len(outs)
+        for i, (t, act, a1, a2) in enumerate(outs):
+            op.out[i].t, op.out[i].act, op.out[i].a1, op.out[i].a2 = t, act, a1, a2
+        op.rm_out = rm_out
+        op.rm_ld = ly["N_total"]
+        return self.emit(op, name)
+
+
+def _act(t, slope):
+    return (t, 1, slope, 1.0)
+
+
+def _raw(t):
+    return (t, 0, 1.0, 1.0)
+
+
+def sampler_tables(cfg, n_steps):
+    """sigma schedule in fp32 exactly as the reference builds it (universe.py:308-311,380-386)
+    plus per-step network-input scale and embedding input (universe.py:175-209)."""
+    d = cfg["diffusion"]
+    s_min, s_max = float(d["sigma_min"]), float(d["sigma_max"])
+    time = torch.linspace(0, 1, n_steps).flip(dims=[0])
+    sigma = s_min * (s_max / s_min) ** time  # fp32 tensor
+    edm = cfg.get("edm")
+    if edm is not None:
+        level_db = float(edm.get("data_level_db", cfg.get("normalization_kwargs", {}).get("level_db", 0.0)))
+        sigma_data = 10.0 ** (level_db / 20.0)
+        sigma_norm = (sigma**2 + sigma_data**2) ** 0.5
+        w_in = 1.0 / sigma_norm
+        emb_in = float(edm["noise"]) * sigma
+    else:
+        w_in = torch.ones_like(sigma)
+        emb_in = sigma
+    return sigma, torch.log10(emb_in), w_in
+
+
+def step_coefs(cfg, n_steps, epsilon):
+    """Per-step (a, b, c) with x <- a x + b net + c z  (universe.py:301-305, 334-343, 197-209).
+    EDM: score = (w_skip x + w_out net - x) / s^2, so x + s^2 eta score = (1 - eta + eta w_skip) x + eta w_out net."""
+    d = cfg["diffusion"]
+    s_min, s_max = float(d["sigma_min"]), float(d["sigma_max"])
+    sigma, _, _ = sampler_tables(cfg, n_steps)
+    sig = [float(s) for s in sigma]
+    delta_t = 1.0 / (n_steps - 1)
+    gamma = (s_max / s_min) ** -delta_t
+    eta = 1 - gamma**epsilon
+    beta = math.sqrt(1 - gamma ** (2 * (epsilon - 1.0)))
+    edm = cfg.get("edm")
+    out = []
+    for n in range(n_steps):
+        s = sig[n]
+        last = n == n_steps - 1
+        e = 1.0 if last else eta
+        c = 0.0 if last else beta * sig[n + 1]
+        if edm is not None:
+            level_db = float(edm.get("data_level_db", cfg.get("normalization_kwargs", {}).get("level_db", 0.0)))
+            sd2 = (10.0 ** (level_db / 20.0)) ** 2
+            w_skip = sd2 / (s * s + sd2)
+            w_out = s * math.sqrt(sd2) / math.sqrt(s * s + sd2)
+            out.append((1.0 - e + e * w_skip, e * w_out, c))
+        else:
+            out.append((1.0, s * s * e, c))
+    return out
+
+
+def build_program(pm, cfg, B, T, n_steps):
+    meta = pm.meta
+    rates, chans, extra = meta["rates"], meta["chans"], meta["extra"]
+    nlev = len(rates)
+    tot_ds = math.prod(rates)
+    pad = tot_ds - T % tot_ds
+    Lp = T + pad
+    sigma, log10s, w_in = sampler_tables(cfg, n_steps)
+    pg = Program(pm, B, T, n_steps, sigma, log10s, w_in)
+    pg.Lp, pg.pad_left = Lp, pad // 2
+    lv = [Level(B, Lp // math.prod(rates[:i])) for i in range(nlev + 1)]
+    pg.levels = lv
+    Fr = lv[nlev].L  # bottleneck frames
+    Cb = chans[nlev]
+    L = pm.layers
+
+    # ---- fixed buffers
+    pg.sig = pg.alloc(B * Lp * 4)        # normalised, padded mixture (f32 [B][Lp])
+    pg.x = pg.alloc(B * Lp * 4)          # sampler state (f32 [B][Lp])
+    pg.mix_rms = pg.alloc(B * 4)
+    pg.coef = pg.alloc(n_steps * 16 + 16)  # uv_step_coef[n_steps] | keep_rms flag
+    pg.log10s = pg.alloc(n_steps * 4)
+    R = L["s.film"]["R"]
+    pg.film = pg.alloc(n_steps * R * 4)
+    pg.init_off = pg.log10s
+    pg.init_blob = np.asarray(log10s.numpy(), dtype=np.float32).tobytes()
+
+    # ---- plan-time setup: FiLM table (sigma_block.py:50-57,73-78; score.py:109,208)
+    op = new_op(_abi.OP_FILM, -2)
+    op.i0, op.i1, op.i2, op.C, op.H = n_steps, 0 if meta["simple_embed"] else 1, R, meta["noise_cond_dim"], L["s.embed"]["n_rff"]
+    op.p0, op.p1, op.p3, op.p4, op.p5 = pg.log10s, pg.film, L["s.embed"]["w_w"], L["s.film"]["w_w"], L["s.film"]["bias_w"]
+    pg.emit(op, "film_table")
+
+    # ---- PREP (universe.py:219-223,272; utils/norm.py:47-87)
+    level = 10.0 ** (float(cfg.get("normalization_kwargs", {}).get("level_db", 0.0)) / 20.0)
+    mel = L["c.mel"]
+    nft = (Fr + 7) // 8
+    pg.mel_energy = pg.alloc(B * nft * 4)
+    pg.melraw = pg.alloc(B * Fr * mel["n_mels"] * 4)
+    op = new_op(_abi.OP_PREP)
+    op.B, op.T, op.Lp, op.i0, op.f0, op.p0, op.p1 = B, T, Lp, pg.pad_left, level, pg.sig, pg.mix_rms
+    pg.emit(op, "prep")
+
+    # =========================================================== conditioner
+    lb = lv[nlev]
+    # mel front-end (condition.py:92-114)
+    op = new_op(_abi.OP_MEL)
+    op.B, op.Lp, op.F, op.C = B, Lp, Fr, mel["n_mels"]
+    op.i0, op.i1, op.i2, op.i3 = mel["n_fft"], mel["hop"], mel["n_bins"], (mel["n_fft"] - mel["hop"]) // 2
+    op.H = mel["nbp"]
+    op.p0, op.p1, op.p2, op.p3, op.p4 = pg.sig, pg.melraw, pg.mel_energy, mel["basis_w"], mel["fb_w"]
+    pg.emit(op, "c.mel")
+    t_mel = pg.tens("c.mel", lb, mel["n_mels"])
+    op = new_op(_abi.OP_MEL_FIN)
+    op.B, op.F, op.C, op.i0, op.p0, op.p1 = B, Fr, mel["n_mels"], nft, pg.melraw, pg.mel_energy
+    op.n_out = 1
+    op.out[0].t = t_mel
+    pg.emit(op, "c.mel_fin")
+
+    def conv_block(pfx, name, lev, C, h_raw, h_act, v_outs, step=-1, film=-1, cond=None, cond_out=None,
+                   v_add2=None, v_scale=SQRT1_2, only_conv1=False):
+        """conv1 -> [+cond]/sqrt2 -> [FiLM] -> conv2 -> conv3 -> (h + c)/sqrt2  (blocks.py:387-403).
+        h_act = PReLU_conv1(h), h_raw = h.  v_outs: outputs of the residual sum."""
+        c1 = pg.tens(f"{pfx}tmp.c1.{lev.L}.{C}", lev, C)
+        c2 = pg.tens(f"{pfx}tmp.c2.{lev.L}.{C}", lev, C)
+        s2, s3 = L[name + ".conv2"]["slope"], L[name + ".conv3"]["slope"]
+        outs = [] if only_conv1 else [_act(c1, s2)]
+        if cond_out is not None:
+            outs.append(_raw(cond_out))
+        pg.gemm(name + ".conv1", name + ".conv1", h_act, lev, lev.L, outs, step, add1=cond,
+                scale=SQRT1_2 if cond is not None else 1.0, film=film)
+        if only_conv1:
+            return
+        pg.gemm(name + ".conv2", name + ".conv2", c1, lev, lev.L, [_act(c2, s3)], step)
+        pg.gemm(name + ".conv3", name + ".conv3", c2, lev, lev.L, v_outs, step, add1=h_raw, add2=v_add2, scale=v_scale)
+
+    def gru_layer(name, x_raw, out_list, step=-1, add1=None, scale=1.0):
+        """in-proj GEMM -> recurrence (score.py:117 / condition.py:212)."""
+        H = L[name + ".hh"]["H"]
+        gi = pg.tensors.get("gi")
+        if gi is None:
+            gi = pg.alloc(lb.P * 6 * H * 4)
+            pg.tensors["gi"] = gi
+        pg.gemm(name + ".ih", name + ".ih", x_raw, lb, lb.L, [], step, rm_out=gi)
+        op = new_op(_abi.OP_GRU, step)
+        op.B, op.T, op.H, op.Lh_A = B, Fr, H, lb.Lh
+        op.p0, op.p3, op.p4 = gi, L[name + ".hh"]["whh_w"], L[name + ".hh"]["bhh_w"]
+        if add1 is not None:
+            op.add1 = add1
+        op.scale = scale
+        op.n_out = len(out_list)
+        for i, (t, act, a1, a2) in enumerate(out_list):
+            op.out[i].t, op.out[i].act, op.out[i].a1, op.out[i].a2 = t, act, a1, a2
+        pg.emit(op, name + ".hh")
+
+    # mel conv + ConvBlock (condition.py:112-113)
+    mb_raw, mb_act = pg.tens("c.melblk.h", lb, Cb), pg.tens("c.melblk.ha", lb, Cb)
+    pg.gemm("c.mel.conv", "c.mel.conv", t_mel, lb, lb.L, [_raw(mb_raw), _act(mb_act, L["c.melblk.conv1"]["slope"])])
+    x_mel = pg.tens("c.x_mel", lb, Cb, dtype=DT_F32)
+    conv_block("c.", "c.melblk", lb, Cb, mb_raw, mb_act, [_raw(x_mel)])
+
+    # input conv (condition.py:360) and encoder (condition.py:189-206)
+    h_raw, h_act = pg.tens("c.h0", lv[0], chans[0]), pg.tens("c.h0a", lv[0], chans[0])
+    op = new_op(_abi.OP_CONV_IN)
+    op.B, op.Lp, op.C, op.p0, op.p3, op.p4, op.f0 = B, Lp, chans[0], pg.sig, L["c.in"]["w_w"], L["c.in"]["bias_w"], 1.0
+    op.n_out = 2
+    op.out[0].t = h_raw
+    op.out[1].t, op.out[1].act, op.out[1].a1, op.out[1].a2 = h_act, 1, L["c.enc0.conv1"]["slope"], 1.0
+    pg.emit(op, "c.in")
+    st_inputs = []
+    for i in range(nlev):
+        C = chans[i]
+        vds = pg.tens(f"c.enc{i}.vds", lv[i + 1], C, split=rates[i])
+        outs = [_act(vds, L[f"c.enc{i}.rc"]["slope"])]
+        if i < nlev - 1:
+            S = math.prod(rates[i:])
+            vst = pg.tens(f"c.enc{i}.vst", lb, C, split=S)
+            outs.append(_act(vst, L[f"c.st{i}"]["slope"]))
+            st_inputs.append((i, vst))
+        conv_block("c.", f"c.enc{i}", lv[i], C, h_raw, h_act, outs)
+        h_raw, h_act = pg.tens(f"c.h{i+1}", lv[i + 1], chans[i + 1]), pg.tens(f"c.h{i+1}a", lv[i + 1], chans[i + 1])
+        nxt = f"c.enc{i+1}.conv1" if (i + 1 < nlev or extra) else "c.cb1.conv1"
+        pg.gemm(f"c.enc{i}.rc", f"c.enc{i}.rc", vds, lv[i + 1], lv[i + 1].L, [_raw(h_raw), _act(h_act, L[nxt]["slope"])])
+    # extra 512-channel block (condition.py:159-166): x = its v_out
+    if extra:
+        x_last = pg.tens("c.x_last", lb, Cb, dtype=DT_F32)
+        conv_block("c.", f"c.enc{nlev}", lb, Cb, h_raw, h_act, [_raw(x_last)])
+    else:
+        x_last = h_raw
+    # out = (x_mel + sum_i st_conv_i(res_i) + x) / sqrt(n)   (condition.py:197-206): the st GEMMs
+    # chain through add1, the last one also adds x and applies the 1/sqrt(n) scale.
+    assert st_inputs, "at least two rate factors are required"
+    acc = x_mel
+    s_raw, s_act = pg.tens("c.sum", lb, Cb), pg.tens("c.suma", lb, Cb)
+    n_sum = len(st_inputs) + 2
+    for k, (i, vst) in enumerate(st_inputs):
+        if k < len(st_inputs) - 1:
+            nacc = pg.tens(f"c.stacc{k % 2}", lb, Cb, dtype=DT_F32)
+            pg.gemm(f"c.st{i}", f"c.st{i}", vst, lb, lb.L, [_raw(nacc)], add1=acc)
+            acc = nacc
+        else:
+            pg.gemm(f"c.st{i}", f"c.st{i}", vst, lb, lb.L, [_raw(s_raw), _act(s_act, L["c.cb1.conv1"]["slope"])],
+                    add1=acc, add2=x_last, scale=1.0 / math.sqrt(n_sum))
+    # conv_block1 -> 2-layer bi-GRU (+residual) -> conv_block2   (condition.py:208-216)
+    g_in = pg.tens("c.gru_in", lb, Cb)
+    conv_block("c.", "c.cb1", lb, Cb, s_raw, s_act, [_raw(g_in)])
+    g_mid = pg.tens("c.gru_mid", lb, Cb)
+    gru_layer("c.gru0", g_in, [_raw(g_mid)])
+    b2_raw, b2_act = pg.tens("c.cb2.h", lb, Cb), pg.tens("c.cb2.ha", lb, Cb)
+    if meta["gru_residual"]:
+        gru_layer("c.gru1", g_mid, [_raw(b2_raw), _act(b2_act, L["c.cb2.conv1"]["slope"])], add1=g_in, scale=SQRT1_2)
+    else:
+        gru_layer("c.gru1", g_mid, [_raw(b2_raw), _act(b2_act, L["c.cb2.conv1"]["slope"])])
+    # conv_block2 -> decoder.input_conv_block (condition.py:216, 266)
+    d_raw, d_act = pg.tens("c.dec_in.h", lb, Cb), pg.tens("c.dec_in.ha", lb, Cb)
+    conv_block("c.", "c.cb2", lb, Cb, b2_raw, b2_act, [_raw(d_raw), _act(d_act, L["c.dec_in.conv1"]["slope"])])
+    # decoder (condition.py:264-270): conditions = conv1 outputs of every up module
+    up_rates = ([None] if extra else []) + rates[::-1]
+    n_dec = len(up_rates)
+    first = "c.dec0.conv1" if extra else "c.dec0.rc"
+    y_raw, y_act = pg.tens("c.dec.y4", lb, Cb), pg.tens("c.dec.y4a", lb, Cb)
+    conv_block("c.", "c.dec_in", lb, Cb, d_raw, d_act, [_raw(y_raw), _act(y_act, L[first]["slope"])])
+    conds = []
+    lev_i = nlev
+    for i, r in enumerate(up_rates):
+        name = f"c.dec{i}"
+        last = i == n_dec - 1
+        if r is not None:
+            lev_i -= 1
+            lev, C = lv[lev_i], chans[lev_i]
+            u_raw, u_act = pg.tens(f"{name}.u", lev, C), pg.tens(f"{name}.ua", lev, C)
+            outs = [_act(u_act, L[name + ".conv1"]["slope"])] + ([] if last else [_raw(u_raw)])
+            pg.gemm(name + ".rc", name + ".rc", y_act, lv[lev_i + 1], lv[lev_i + 1].L, outs)
+            y_raw, y_act = u_raw, u_act
+        lev, C = lv[lev_i], chans[lev_i]
+        cond = pg.tens(f"cond{i}", lev, C)
+        conds.append(cond)
+        if last:
+            # y_hat is unused by enhance() (universe.py:314-316): only conv1 (the condition) is needed
+            conv_block("c.", name, lev, C, y_raw, y_act, [], cond_out=cond, only_conv1=True)
+        else:
+            nxt = f"c.dec{i+1}.rc"
+            v_act = pg.tens(f"{name}.va", lev, C)
+            conv_block("c.", name, lev, C, y_raw, y_act, [_act(v_act, L[nxt]["slope"])], cond_out=cond)
+            y_raw, y_act = None, v_act
+    # hoisted step-invariant 1x1 condition projections (score.py:168,192,209)
+    scs = []
+    lev_i = nlev
+    for i, r in enumerate(up_rates):
+        if r is not None:
+            lev_i -= 1
+        lev, C = lv[lev_i], chans[lev_i]
+        sc = pg.tens(f"sc{i}", lev, C)
+        pg.gemm(f"s.dec{i}.sc", f"s.dec{i}.sc", conds[i], lev, lev.L, [_raw(sc)])
+        scs.append(sc)
+
+    # =========================================================== sampler / score network
+    op = new_op(_abi.OP_INIT_X)
+    op.B, op.Lp, op.p0, op.f0, op.i0 = B, Lp, pg.x, float(sigma[0]), 0
+    pg.emit(op, "init_x")
+    frows = L["s.film"]["rows"]
+    n_blocks = meta["n_blocks"]
+    for n in range(n_steps):
+        fbase = pg.film + n * R * 4
+        h_raw, h_act = pg.tens("s.h0", lv[0], chans[0]), pg.tens("s.h0a", lv[0], chans[0])
+        op = new_op(_abi.OP_CONV_IN, n)
+        op.B, op.Lp, op.C, op.p0, op.p3, op.p4 = B, Lp, chans[0], pg.x, L["s.in"]["w_w"], L["s.in"]["bias_w"]
+        op.f0 = float(w_in[n])
+        op.n_out = 2
+        op.out[0].t = h_raw
+        op.out[1].t, op.out[1].act, op.out[1].a1, op.out[1].a2 = h_act, 1, L["s.enc0.conv1"]["slope"], 1.0
+        pg.emit(op, f"s{n}.in")
+        skips = []
+        for i in range(n_blocks):
+            lev, C = lv[min(i, nlev)], chans[min(i, nlev)]
+            skip = pg.tens(f"s.skip{i}", lev, C)
+            skips.append(skip)
+            outs = [_raw(skip)]
+            if i < nlev:
+                vds = pg.tens(f"s.enc{i}.vds", lv[i + 1], C, split=rates[i])
+                outs.append(_act(vds, L[f"s.enc{i}.rc"]["slope"]))
+            conv_block("s.", f"s.enc{i}", lev, C, h_raw, h_act, outs, step=n, film=fbase + frows[f"enc{i}"] * 4)
+            if i < nlev:
+                h_raw = pg.tens(f"s.h{i+1}", lv[i + 1], chans[i + 1])
+                outs = [_raw(h_raw)]
+                if i + 1 < n_blocks:
+                    h_act = pg.tens(f"s.h{i+1}a", lv[i + 1], chans[i + 1])
+                    outs.append(_act(h_act, L[f"s.enc{i+1}.conv1"]["slope"]))
+                pg.gemm(f"s.enc{i}.rc", f"s.enc{i}.rc", vds, lv[i + 1], lv[i + 1].L, outs, n)
+        gru_in = skips[-1] if extra else h_raw
+        # decoder (score.py:197-211)
+        lev_i = nlev
+        y_act = None
+        for i, r in enumerate(up_rates):
+            name = f"s.dec{i}"
+            res = skips[n_blocks - 1 - i]
+            if i == 0:
+                # GRU (score.py:117) fused with the first decoder block's (h + res)/sqrt2 when it has no up conv
+                if r is None:
+                    u_raw, u_act = pg.tens("s.dec0.u", lb, Cb), pg.tens("s.dec0.ua", lb, Cb)
+                    gru_layer("s.gru", gru_in, [_raw(u_raw), _act(u_act, L[name + ".conv1"]["slope"])], step=n,
+                              add1=res, scale=SQRT1_2)
+                else:
+                    y_act = pg.tens("s.gru_out", lb, Cb)
+                    gru_layer("s.gru", gru_in, [_act(y_act, L[name + ".rc"]["slope"])], step=n)
+            if r is not None:
+                lev_i -= 1
+                lev, C = lv[lev_i], chans[lev_i]
+                u_raw, u_act = pg.tens(f"{name}.u", lev, C), pg.tens(f"{name}.ua", lev, C)
+                pg.gemm(name + ".rc", name + ".rc", y_act, lv[lev_i + 1], lv[lev_i + 1].L,
+                        [_raw(u_raw), _act(u_act, L[name + ".conv1"]["slope"])], n, add1=res, scale=SQRT1_2)
+            lev, C = lv[lev_i], chans[lev_i]
+            v_act = pg.tens(f"{name}.va", lev, C)
+            if i < n_dec - 1:
+                vo = _act(v_act, L[f"s.dec{i+1}.rc"]["slope"])
+            else:
+                vo = (v_act, 2, L["s.out"]["slope_a"], L["s.out"]["slope_b"])  # score.py:290 (two PReLUs)
+            conv_block("s.", name, lev, C, u_raw, u_act, [vo], step=n, film=fbase + frows[f"dec{i}"] * 4, cond=scs[i])
+            y_act = v_act
+        op = new_op(_abi.OP_CONV_OUT, n)
+        op.a = y_act
+        op.B, op.Lp, op.C, op.p0, op.p3, op.p4, op.i0 = B, Lp, chans[0], pg.x, L["s.out"]["w_w"], L["s.out"]["bias_w"], n
+        op.p1 = pg.coef
+        pg.emit(op, f"s{n}.out")
+    op = new_op(_abi.OP_POST)
+    op.B, op.T, op.Lp, op.i0, op.p0, op.p1, op.p2 = B, T, Lp, pg.pad_left, pg.x, pg.mix_rms, pg.coef + n_steps * 16
+    pg.emit(op, "post")
+    pg.arena = _ru(pg.arena, 1024)
+    return pg

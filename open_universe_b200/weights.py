@@ -1,0 +1,299 @@
+"""Weight folding and packing: reference state dict -> device weight blob.
+
+All transformations are exact algebra done once at load time in fp32:
+  * old-style weight norm  w = g * v / ||v||  (norm over all dims but 0;
+    reference networks/universe/blocks.py:40-46),
+  * the binomial anti-aliasing low-pass of PReLU_Conv (blocks.py:217-229)
+    folded into the strided / transposed rate-change convolutions,
+  * re-expression of every dense layer as a multi-tap GEMM
+        D[row, n] = sum_{src s, shift q, c}  A_s[row + q, c] * W4[n, s, q, c]
+    and packing of W4 into bf16 tile images [n_tile][s][group][q][KC/8][N_TILE][8]
+    (the no-swizzle K-major UMMA layout consumed by csrc/gemm_tc.cuh),
+  * GRU recurrent weights into mma.m16n8k16 A-fragment order (csrc/gru.cuh).
+"""
+import math
+
+import numpy as np
+import torch
+
+
+def eff_weight(sd, prefix):
+    if prefix + ".weight_g" in sd:
+        g, v = sd[prefix + ".weight_g"].float(), sd[prefix + ".weight_v"].float()
+        dims = tuple(range(1, v.ndim))
+        return g * v / v.pow(2).sum(dim=dims, keepdim=True).sqrt()
+    return sd[prefix + ".weight"].float()
+
+
+def pick_kc(c_in):
+    if c_in % 64 == 0:
+        return 64
+    if c_in % 48 == 0:
+        return 48
+    if c_in <= 96:
+        return c_in
+    if c_in % 32 == 0:
+        return 32
+    return 16
+
+
+def pick_ntile(c_out):
+    for n in range(min(256, c_out), 15, -16):
+        if c_out % n == 0:
+            return n
+    raise ValueError(f"no N tile for C_out={c_out}")
+
+
+def to_bf16_bits(x):
+    return x.contiguous().to(torch.bfloat16).view(torch.int16).numpy()
+
+
+class Blob:
+    """Append-only byte blob with 256-byte aligned entries."""
+
+    def __init__(self):
+        self.parts = []
+        self.size = 0
+
+    def add(self, arr):
+        b = arr.tobytes() if isinstance(arr, np.ndarray) else bytes(arr)
+        off = self.size
+        pad = (-len(b)) % 256
+        self.parts.append(b + b"\0" * pad)
+        self.size += len(b) + pad
+        return off
+
+    def add_f32(self, t):
+        return self.add(np.ascontiguousarray(t.detach().float().cpu().numpy(), dtype=np.float32))
+
+    def bytes(self):
+        return b"".join(self.parts)
+
+
+# ---------------------------------------------------------------- W4 builders
+def w4_plain(w):
+    """Conv1d weight [Co, Ci, k] ('same', odd k) -> W4 [Co, 1, k, Ci], smin = -(k//2)."""
+    return w.permute(0, 2, 1)[:, None].contiguous(), -(w.shape[2] // 2)
+
+
+def w4_down(w, lp=None):
+    """Strided conv (k = stride = r), optionally preceded by the 'same' low-pass lp
+    (2r+1 taps): y[m] = sum_tau W'[tau] v[r m + tau - r], W' = W (*) lp (3r taps).
+    Source t = phase plane v[r m' + t], shift q - 1:  W4[co, t, q, ci] = W'[co, ci, r q + t]."""
+    co, ci, r = w.shape
+    if lp is None:
+        return w.permute(0, 2, 1)[:, :, None].contiguous(), 0
+    wf = torch.zeros(co, ci, 3 * r)
+    for t in range(r):
+        wf[:, :, t : t + 2 * r + 1] += w[:, :, t : t + 1] * lp[None, None, :]
+    return wf.view(co, ci, 3, r).permute(0, 3, 2, 1).contiguous(), -1
+
+
+def w4_up(w, lp=None):
+    """ConvTranspose1d (k = stride = r), weight [Ci, Co, r], optionally followed by the
+    low-pass.  Output row r m + t is column n = t * Co + co of a GEMM on x[m + d]:
+    W4[t*Co + co, 0, d+1, ci] = sum_j lp[j] W[ci, co, t + j - r (d+1)]."""
+    ci, co, r = w.shape
+    if lp is None:
+        return w.permute(2, 1, 0).reshape(r * co, 1, 1, ci).contiguous(), 0
+    w4 = torch.zeros(r, co, 1, 3, ci)
+    for t in range(r):
+        for j in range(2 * r + 1):
+            dq, tt = divmod(t + j, r)
+            w4[t, :, 0, dq, :] += lp[j] * w[:, :, tt].t()
+    return w4.view(r * co, 1, 3, ci).contiguous(), -1
+
+
+def pack_w4(w4, kc, n_tile):
+    """[N, S, Q, Ci] fp32 -> bf16 images [N/n_tile][S][Ci/kc][Q][kc/8][n_tile][8]."""
+    n, s, q, ci = w4.shape
+    assert n % n_tile == 0 and ci % kc == 0 and kc % 16 == 0 and n_tile % 16 == 0
+    x = w4.view(n // n_tile, n_tile, s, q, ci // kc, kc // 8, 8)
+    x = x.permute(0, 2, 4, 3, 5, 1, 6)  # nt, s, g, q, j, n, e
+    return to_bf16_bits(x)
+
+
+def unpack_w4(bits, n, s, q, ci, kc, n_tile):
+    """Inverse of pack_w4 (used by the CPU emulator): -> fp32 [N, S, Q, Ci]."""
+    x = torch.from_numpy(np.ascontiguousarray(bits)).view(torch.bfloat16).float()
+    x = x.view(n // n_tile, s, ci // kc, q, kc // 8, n_tile, 8)
+    return x.permute(0, 5, 1, 3, 2, 4, 6).reshape(n, s, q, ci).contiguous()
+
+
+def pack_gru_whh(w_hh_f, w_hh_b):
+    """[3H, H] x 2 directions -> bf16 mma.m16n8k16 A fragments
+    [dir][3H/16][H/16][lane 32][reg 4][2]."""
+    out = []
+    for w in (w_hh_f, w_hh_b):
+        m, k = w.shape
+        t = w.float().view(m // 16, 16, k // 16, 16).permute(0, 2, 1, 3)  # mt, kt, row, col
+        lane = torch.arange(32)
+        row0, col0 = lane // 4, (lane % 4) * 2
+        frag = torch.empty(m // 16, k // 16, 32, 4, 2)
+        for reg, (dr, dc) in enumerate(((0, 0), (8, 0), (0, 8), (8, 8))):
+            for e in range(2):
+                frag[:, :, :, reg, e] = t[:, :, row0 + dr, col0 + dc + e]
+        out.append(frag)
+    return to_bf16_bits(torch.stack(out))
+
+
+def dft_basis(window, n_fft):
+    """Windowed real-DFT basis f32 [n_fft][2 * nbp]: cos | sin, nbp = bins padded to 32."""
+    nb = n_fft // 2 + 1
+    nbp = (nb + 31) // 32 * 32
+    n = torch.arange(n_fft, dtype=torch.float64)[:, None]
+    k = torch.arange(nb, dtype=torch.float64)[None, :]
+    ang = 2.0 * math.pi * ((n * k) % n_fft) / n_fft
+    basis = torch.zeros(n_fft, 2 * nbp, dtype=torch.float64)
+    w = window.double()[:, None]
+    basis[:, :nb] = torch.cos(ang) * w
+    basis[:, nbp : nbp + nb] = torch.sin(ang) * w
+    return basis.float(), nb, nbp
+
+
+class PackedModel:
+    def __init__(self):
+        self.blob = Blob()
+        self.layers = {}
+        self.meta = {}
+
+    def add_gemm(self, name, w4, smin, c_out, up=1, bias=None, slope=None):
+        n, s, q, ci = w4.shape
+        kc, n_tile = pick_kc(ci), pick_ntile(c_out)
+        self.layers[name] = dict(
+            w_w=self.blob.add(pack_w4(w4, kc, n_tile)),
+            bias_w=self.blob.add_f32(bias) if bias is not None else -1,
+            n_src=s, smin=smin, smax=smin + q - 1, KC=kc, N_TILE=n_tile, N_total=n,
+            C_out=c_out, C_in=ci, up=up, slope=slope,
+        )
+
+    def add_conv_block(self, sd, prefix, name, rate=None, direction="none"):
+        """ConvBlock parameters (blocks.py:240-329)."""
+        for cn in ("conv1", "conv2", "conv3"):
+            p = f"{prefix}.{cn}"
+            w4, smin = w4_plain(eff_weight(sd, p + ".conv"))
+            self.add_gemm(f"{name}.{cn}", w4, smin, w4.shape[0], bias=sd[p + ".conv.bias"],
+                          slope=float(sd[p + ".prelu.weight"]))
+        if direction in ("down", "up"):
+            p = f"{prefix}.rate_change_conv"
+            w = eff_weight(sd, p + ".conv")
+            lp = sd.get(p + ".low_pass_filter.weights")
+            lp = lp.float() if lp is not None else None
+            bias = sd[p + ".bias"] if p + ".bias" in sd else sd.get(p + ".conv.bias")
+            if direction == "down":
+                w4, smin = w4_down(w, lp)
+                self.add_gemm(f"{name}.rc", w4, smin, w.shape[0], bias=bias, slope=float(sd[p + ".prelu.weight"]))
+            else:
+                w4, smin = w4_up(w, lp)
+                self.add_gemm(f"{name}.rc", w4, smin, w.shape[1], up=rate, bias=bias,
+                              slope=float(sd[p + ".prelu.weight"]))
+
+    def add_gru(self, sd, prefix, name, layer):
+        sufs = ("", "_reverse")
+        w_ih = torch.cat([sd[f"{prefix}.weight_ih_l{layer}{s}"].float() for s in sufs])  # [6H, C]
+        b_ih = torch.cat([sd[f"{prefix}.bias_ih_l{layer}{s}"].float() for s in sufs])
+        self.add_gemm(f"{name}.ih", w_ih[:, None, None, :].contiguous(), 0, w_ih.shape[0], bias=b_ih)
+        whh = [sd[f"{prefix}.weight_hh_l{layer}{s}"].float() for s in sufs]
+        self.layers[f"{name}.hh"] = dict(
+            whh_w=self.blob.add(pack_gru_whh(*whh)),
+            bhh_w=self.blob.add_f32(torch.cat([sd[f"{prefix}.bias_hh_l{layer}{s}"].float() for s in sufs])),
+            H=whh[0].shape[1],
+        )
+
+    def add_conv_in(self, sd, prefix, name):
+        w = eff_weight(sd, prefix)  # [C, 1, 3]
+        self.layers[name] = dict(w_w=self.blob.add_f32(w[:, 0, :].t().contiguous()),
+                                 bias_w=self.blob.add_f32(sd[prefix + ".bias"]), C=w.shape[0])
+
+
+def pack_model(sd, cfg):
+    """sd: reference-layout state dict (tensors on CPU); cfg: resolved `model` config node."""
+    sd = {k: v.detach().cpu() for k, v in sd.items()}
+    pm = PackedModel()
+    scfg, ccfg = cfg["score_model"], cfg["condition_model"]
+    edm = cfg.get("edm") is not None
+    sp, cp = ("_edm_model" if edm else "score_model"), "condition_model"
+    rates = [int(r) for r in scfg["rate_factors"]]
+    extra = bool(scfg.get("extra_conv_block", False))
+    nlev = len(rates)
+    n_blocks = nlev + (1 if extra else 0)
+    c0 = int(scfg["n_channels"])
+    chans = [c0 * 2**i for i in range(nlev + 1)]
+    pm.meta = dict(rates=rates, extra=extra, chans=chans, edm=edm, n_blocks=n_blocks,
+                   simple_embed=scfg.get("time_embedding") == "simple",
+                   noise_cond_dim=int(scfg.get("noise_cond_dim", 512)))
+    if scfg.get("encoder_gru_conv_sandwich"):
+        raise NotImplementedError("encoder_gru_conv_sandwich is not used by the supported configs")
+    if scfg.get("seq_model", "gru") != "gru" or ccfg.get("seq_model", "gru") != "gru":
+        raise NotImplementedError("only seq_model == 'gru' is supported")
+
+    # ---------------- score network (score.py:214-298)
+    pm.add_conv_in(sd, sp + ".input_conv", "s.in")
+    film_w, film_b, film_rows = [], [], {}
+    row = 0
+
+    def add_film(prefix, key):
+        nonlocal row
+        w = eff_weight(sd, prefix)
+        film_w.append(w)
+        film_b.append(sd[prefix + ".bias"].float())
+        film_rows[key] = row
+        row += w.shape[0]
+
+    for i in range(n_blocks):
+        down = i < nlev
+        pm.add_conv_block(sd, f"{sp}.encoder.ds_modules.{i}", f"s.enc{i}", rates[i] if down else None,
+                          "down" if down else "none")
+        add_film(f"{sp}.encoder.cond_proj.{i}", f"enc{i}")
+    pm.add_gru(sd, sp + ".encoder.gru", "s.gru", 0)
+    up_rates = ([None] if extra else []) + rates[::-1]
+    for i, r in enumerate(up_rates):
+        pm.add_conv_block(sd, f"{sp}.decoder.up_modules.{i}", f"s.dec{i}", r, "up" if r else "none")
+        add_film(f"{sp}.decoder.noise_cond_proj.{i}", f"dec{i}")
+        w4, smin = w4_plain(eff_weight(sd, f"{sp}.decoder.signal_cond_proj.{i}"))
+        pm.add_gemm(f"s.dec{i}.sc", w4, smin, w4.shape[0], bias=sd[f"{sp}.decoder.signal_cond_proj.{i}.bias"])
+    pm.layers["s.film"] = dict(w_w=pm.blob.add_f32(torch.cat(film_w)), bias_w=pm.blob.add_f32(torch.cat(film_b)),
+                               rows=film_rows, R=row)
+    if pm.meta["simple_embed"]:
+        emb = torch.stack([sd[sp + ".sigma_block.weight"].reshape(()), sd[sp + ".sigma_block.bias"].reshape(())])
+        pm.layers["s.embed"] = dict(w_w=pm.blob.add_f32(emb), n_rff=0)
+    else:
+        parts = [sd[sp + ".sigma_block.freq"].float().reshape(-1)]
+        for i in (1, 2, 3):
+            parts += [sd[f"{sp}.sigma_block.layer{i}.prelu.weight"].float().reshape(-1),
+                      sd[f"{sp}.sigma_block.layer{i}.lin.weight"].float().reshape(-1),
+                      sd[f"{sp}.sigma_block.layer{i}.lin.bias"].float().reshape(-1)]
+        pm.layers["s.embed"] = dict(w_w=pm.blob.add_f32(torch.cat(parts)), n_rff=int(sd[sp + ".sigma_block.freq"].numel()))
+    wo = eff_weight(sd, sp + ".output_conv.conv")  # [1, C, 3]
+    pm.layers["s.out"] = dict(w_w=pm.blob.add_f32(wo[0].t().contiguous()), bias_w=pm.blob.add_f32(sd[sp + ".output_conv.conv.bias"]),
+                              slope_a=float(sd[sp + ".prelu.weight"]), slope_b=float(sd[sp + ".output_conv.prelu.weight"]))
+
+    # ---------------- conditioner (condition.py:273-377)
+    pm.add_conv_in(sd, cp + ".input_conv", "c.in")
+    tot_ds = math.prod(rates)
+    n_fft = int(ccfg.get("n_mel_oversample", 4)) * tot_ds
+    basis, nb, nbp = dft_basis(sd[cp + ".input_mel.mel_spec.spectrogram.window"], n_fft)
+    fb = sd[cp + ".input_mel.mel_spec.mel_scale.fb"].float()
+    pm.layers["c.mel"] = dict(basis_w=pm.blob.add_f32(basis), fb_w=pm.blob.add_f32(fb), n_fft=n_fft, hop=tot_ds,
+                              n_bins=nb, nbp=nbp, n_mels=fb.shape[1])
+    w4, smin = w4_plain(eff_weight(sd, cp + ".input_mel.conv"))
+    pm.add_gemm("c.mel.conv", w4, smin, w4.shape[0], bias=sd[cp + ".input_mel.conv.bias"])
+    pm.add_conv_block(sd, cp + ".input_mel.conv_block", "c.melblk")
+    for i in range(n_blocks):
+        down = i < nlev
+        pm.add_conv_block(sd, f"{cp}.encoder.ds_modules.{i}", f"c.enc{i}", rates[i] if down else None,
+                          "down" if down else "none")
+        if i < nlev - 1:
+            p = f"{cp}.encoder.st_convs.{i}"
+            w = eff_weight(sd, p + ".conv")
+            w4, smin = w4_down(w)
+            pm.add_gemm(f"c.st{i}", w4, smin, w.shape[0], bias=sd[p + ".conv.bias"], slope=float(sd[p + ".prelu.weight"]))
+    pm.add_conv_block(sd, cp + ".encoder.conv_block1", "c.cb1")
+    pm.add_gru(sd, cp + ".encoder.gru", "c.gru0", 0)
+    pm.add_gru(sd, cp + ".encoder.gru", "c.gru1", 1)
+    pm.add_conv_block(sd, cp + ".encoder.conv_block2", "c.cb2")
+    pm.add_conv_block(sd, cp + ".decoder.input_conv_block", "c.dec_in")
+    for i, r in enumerate(up_rates):
+        pm.add_conv_block(sd, f"{cp}.decoder.up_modules.{i}", f"c.dec{i}", r, "up" if r else "none")
+    pm.meta["gru_residual"] = bool(ccfg.get("encoder_gru_residual", False))
+    return pm

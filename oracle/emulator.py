@@ -1,0 +1,303 @@
+"""TEST INFRASTRUCTURE ONLY (CPU) -- never imported by the product path.
+
+Executes a compiled op program (open_universe_b200/program.py) on the CPU with
+the exact memory layout, packed weights and rounding points (bf16 stores) of
+the CUDA kernels, one op at a time.  It serves two purposes:
+  * on the CPU box: proves the compiler's bookkeeping (layouts, weight folding
+    and packing, epilogue flags, buffer aliasing) against the oracle without a GPU;
+  * on the GPU box: gives the expected arena contents after every op, so a
+    kernel bug is localised to one launch.
+"""
+import math
+
+import numpy as np
+import torch
+
+from open_universe_b200 import _abi
+from open_universe_b200.weights import unpack_w4
+
+
+def _dt(t):
+    return torch.bfloat16 if t.dtype == _abi.DT_BF16 else torch.float32
+
+
+class Emulator:
+    def __init__(self, pm, pg):
+        self.pm, self.pg = pm, pg
+        self.blob = np.frombuffer(pm.blob.bytes(), dtype=np.uint8)
+        self.arena = torch.zeros(pg.arena, dtype=torch.uint8)
+        init = np.frombuffer(pg.init_blob, dtype=np.uint8)
+        self.arena[pg.init_off : pg.init_off + len(init)] = torch.from_numpy(init.copy())
+        self._wcache = {}
+
+    # ---------------------------------------------------------------- views
+    def w_f32(self, off, n):
+        return torch.from_numpy(self.blob[off : off + 4 * n].copy()).view(torch.float32)
+
+    def a_f32(self, off, n):
+        return self.arena[off : off + 4 * n].view(torch.float32)
+
+    def view(self, t):
+        """[split, nch, P, 8] view of a planes tensor."""
+        es = 2 if t.dtype == _abi.DT_BF16 else 4
+        n = t.split * t.nch * t.P * 8
+        return self.arena[t.off : t.off + n * es].view(_dt(t)).view(t.split, t.nch, t.P, 8)
+
+    def read_tensor(self, t, B, L):
+        """-> [B, C, L] fp32 logical tensor."""
+        v = self.view(t).float()
+        rows = (L + t.split - 1) // t.split
+        out = torch.zeros(B, t.nch * 8, rows * t.split)
+        for b in range(B):
+            blk = v[:, :, t.G + b * t.Lh : t.G + b * t.Lh + rows, :]  # [split, nch, rows, 8]
+            out[b] = blk.permute(1, 3, 2, 0).reshape(t.nch * 8, rows * t.split)
+        return out[:, :, :L]
+
+    def _scatter(self, t, b_idx, l_idx, vals):
+        """vals [n, C] -> tensor t at (b, l)."""
+        v = self.view(t)
+        ph = l_idx % t.split
+        row = t.G + b_idx * t.Lh + l_idx // t.split
+        C = t.nch * 8
+        v[ph, :, row, :] = vals.to(v.dtype).view(-1, C // 8, 8)
+
+    def _gather(self, t, b_idx, l_idx):
+        v = self.view(t)
+        ph = l_idx % t.split
+        row = t.G + b_idx * t.Lh + l_idx // t.split
+        return v[ph, :, row, :].float().reshape(len(b_idx), -1)
+
+    @staticmethod
+    def _act(v, o):
+        if o.act >= 1:
+            v = torch.where(v >= 0, v, o.a1 * v)
+        if o.act == 2:
+            v = torch.where(v >= 0, v, o.a2 * v)
+        return v
+
+    def _write_outs(self, op, b_idx, l_idx, v):
+        for i in range(op.n_out):
+            o = op.out[i]
+            self._scatter(o.t, b_idx, l_idx, self._act(v, o))
+
+    # ---------------------------------------------------------------- ops
+    def op_gemm(self, op):
+        a = self.view(op.a).float()  # [n_src, nch, P, 8]
+        n_shift = op.smax - op.smin + 1
+        C_in = op.a.nch * 8
+        key = (op.w_w, op.N_total, op.n_src, n_shift, C_in)
+        if key not in self._wcache:
+            nb = op.N_total * op.n_src * n_shift * C_in * 2
+            bits = self.blob[op.w_w : op.w_w + nb].view(np.int16)
+            self._wcache[key] = unpack_w4(bits, op.N_total, op.n_src, n_shift, C_in, op.KC, op.N_TILE)
+        w4 = self._wcache[key]
+        M = op.m_rows
+        acc = torch.zeros(M, op.N_total)
+        for s in range(op.n_src):
+            for q in range(n_shift):
+                r0 = op.a.G + op.smin + q
+                x = a[s, :, r0 : r0 + M, :].permute(1, 0, 2).reshape(M, C_in)
+                acc += x @ w4[:, s, q, :].t()
+        g = torch.arange(M)
+        b_idx, m = g // op.Lh_A, g % op.Lh_A
+        valid = m < op.M_valid
+        b_idx, m, acc = b_idx[valid], m[valid], acc[valid]
+        if op.rm_out >= 0:
+            rm = self.a_f32(op.rm_out, M * op.rm_ld).view(M, op.rm_ld)
+        bias = self.w_f32(op.bias_w, op.C_out) if op.bias_w >= 0 else None
+        film = self.a_f32(op.film, 2 * op.C_out) if op.film >= 0 else None
+        for ph in range(op.N_total // op.C_out):
+            v = acc[:, ph * op.C_out : (ph + 1) * op.C_out].clone()
+            l = op.up * m + ph
+            if bias is not None:
+                v += bias
+            if op.add1.off >= 0:
+                v += self._gather(op.add1, b_idx, l)
+            if op.add2.off >= 0:
+                v += self._gather(op.add2, b_idx, l)
+            v *= np.float32(op.scale)
+            if film is not None:
+                v = film[: op.C_out] * v + film[op.C_out :]
+            if op.rm_out >= 0:
+                rm[g[valid], ph * op.C_out : (ph + 1) * op.C_out] = v
+            self._write_outs(op, b_idx, l, v)
+
+    def op_prep(self, op, io):
+        mix = io["mix"].float()
+        B, T, Lp = op.B, op.T, op.Lp
+        x = torch.zeros(B, Lp)
+        x[:, op.i0 : op.i0 + T] = mix
+        rms = mix.square().mean(dim=1).sqrt()
+        mean = x.mean(dim=1, keepdim=True)
+        x = x - mean
+        gain = op.f0 / x.std(dim=1, keepdim=True).clamp(min=1e-5)
+        self.a_f32(op.p0, B * Lp).copy_((x * gain).reshape(-1))
+        self.a_f32(op.p1, B).copy_(rms)
+
+    def op_mel(self, op):
+        B, Lp, F_, n_mels = op.B, op.Lp, op.F, op.C
+        n_fft, hop, nb, padl, nbp = op.i0, op.i1, op.i2, op.i3, op.H
+        sig = self.a_f32(op.p0, B * Lp).view(B, Lp)
+        xp = torch.zeros(B, (F_ - 1) * hop + n_fft)
+        n = min(Lp, xp.shape[1] - padl)
+        xp[:, padl : padl + n] = sig[:, :n]
+        frames = xp.unfold(-1, n_fft, hop)  # [B, F, n_fft]
+        basis = self.w_f32(op.p3, n_fft * 2 * nbp).view(n_fft, 2 * nbp)
+        fb = self.w_f32(op.p4, nb * n_mels).view(nb, n_mels)
+        ri = frames @ basis
+        power = ri[..., :nb] ** 2 + ri[..., nbp : nbp + nb] ** 2
+        mel = power @ fb  # [B, F, n_mels]
+        self.a_f32(op.p1, B * F_ * n_mels).copy_(mel.reshape(-1))
+        nft = (F_ + 7) // 8
+        e = torch.zeros(B, nft * 8)
+        e[:, :F_] = (mel**2).sum(-1)
+        self.a_f32(op.p2, B * nft).copy_(e.view(B, nft, 8).sum(-1).reshape(-1))
+
+    def op_mel_fin(self, op):
+        B, F_, n_mels, nft = op.B, op.F, op.C, op.i0
+        mel = self.a_f32(op.p0, B * F_ * n_mels).view(B, F_, n_mels)
+        energy = self.a_f32(op.p1, B * nft).view(B, nft).sum(-1)
+        norm = (energy / F_).sqrt().clamp(min=1e-5)
+        v = mel / norm[:, None, None]
+        b_idx = torch.arange(B).repeat_interleave(F_)
+        l_idx = torch.arange(F_).repeat(B)
+        self._write_outs(op, b_idx, l_idx, v.reshape(B * F_, n_mels))
+
+    def op_conv_in(self, op):
+        B, Lp, C = op.B, op.Lp, op.C
+        x = self.a_f32(op.p0, B * Lp).view(B, Lp) * np.float32(op.f0)
+        w = self.w_f32(op.p3, 3 * C).view(3, C)
+        bias = self.w_f32(op.p4, C)
+        xp = torch.nn.functional.pad(x, (1, 1))
+        v = xp[:, :-2, None] * w[0] + xp[:, 1:-1, None] * w[1] + xp[:, 2:, None] * w[2] + bias  # [B, Lp, C]
+        b_idx = torch.arange(B).repeat_interleave(Lp)
+        l_idx = torch.arange(Lp).repeat(B)
+        self._write_outs(op, b_idx, l_idx, v.reshape(B * Lp, C))
+
+    def op_init_x(self, op, io):
+        self.a_f32(op.p0, op.B * op.Lp).copy_((io["noise"][op.i0].float() * np.float32(op.f0)).reshape(-1))
+
+    def op_conv_out(self, op, io):
+        B, Lp, C = op.B, op.Lp, op.C
+        a = self.read_tensor(op.a, B, Lp)  # [B, C, Lp]
+        w = self.w_f32(op.p3, 3 * C).view(3, C)
+        bias = self.w_f32(op.p4, 1)
+        ap = torch.nn.functional.pad(a, (1, 1))
+        net = bias + sum((ap[:, :, k : k + Lp] * w[k][None, :, None]).sum(1) for k in range(3))  # [B, Lp]
+        ca, cb, cc = [np.float32(v) for v in io["coef"][op.i0]]
+        x = self.a_f32(op.p0, B * Lp).view(B, Lp)
+        xn = ca * x + cb * net
+        if cc != 0:
+            xn = xn + cc * io["noise"][op.i0 + 1].float().view(B, Lp)
+        x.copy_(xn)
+        if io.get("dbg") is not None:
+            io["dbg"][op.i0] = net.clone()
+
+    def op_post(self, op, io):
+        B, T, Lp = op.B, op.T, op.Lp
+        x = self.a_f32(op.p0, B * Lp).view(B, Lp)[:, op.i0 : op.i0 + T].clone()
+        if io.get("keep_rms"):
+            rms = self.a_f32(op.p1, B)
+            x_rms = x.square().mean(dim=1).sqrt().clamp(min=1e-5)
+            x = x * (rms / x_rms)[:, None]
+        scale = x.abs().max(dim=1, keepdim=True).values
+        io["out"] = torch.where(scale > 1.0, x / scale, x)
+
+    def op_film(self, op):
+        n_steps, kind, R, D, n_rff = op.i0, op.i1, op.i2, op.C, op.H
+        ls = self.a_f32(op.p0, n_steps)
+        if kind == 0:
+            wb = self.w_f32(op.p3, 2)
+            t = torch.arange(D // 2)
+            f = 0.5 * torch.sigmoid(wb[0] * ls[:, None] + wb[1])
+            p = 2.0 * math.pi * f * t
+            g = torch.cat([torch.sin(p), torch.cos(p)], dim=-1)
+        else:
+            sizes = [(2 * n_rff, 4 * n_rff), (4 * n_rff, 8 * n_rff), (8 * n_rff, D)]
+            tot = n_rff + sum(1 + i * o + o for i, o in sizes)
+            buf = self.w_f32(op.p3, tot)
+            freq, pos = buf[:n_rff], n_rff
+            p = 2.0 * math.pi * freq[None, :] * ls[:, None]
+            g = torch.cat([torch.sin(p), torch.cos(p)], dim=-1)
+            for i, o in sizes:
+                a = buf[pos]
+                W = buf[pos + 1 : pos + 1 + i * o].view(o, i)
+                bb = buf[pos + 1 + i * o : pos + 1 + i * o + o]
+                pos += 1 + i * o + o
+                g = g @ W.t() + bb
+                g = torch.where(g >= 0, g, a * g)
+        W = self.w_f32(op.p4, R * D).view(R, D)
+        b = self.w_f32(op.p5, R)
+        self.a_f32(op.p1, n_steps * R).copy_((g @ W.t() + b).reshape(-1))
+
+    def op_gru(self, op, round_h=True):
+        B, T, H, Lh = op.B, op.T, op.H, op.Lh_A
+        rows = B * Lh
+        gi = self.a_f32(op.p0, rows * 6 * H).view(rows, 6 * H)
+        # recover W_hh from the fragment packing
+        mt, kt = 3 * H // 16, H // 16
+        bits = self.blob[op.p3 : op.p3 + 2 * 3 * H * H * 2].view(np.int16)
+        frag = torch.from_numpy(bits.copy()).view(torch.bfloat16).float().view(2, mt, kt, 32, 4, 2)
+        lane = torch.arange(32)
+        row0, col0 = lane // 4, (lane % 4) * 2
+        whh = torch.zeros(2, mt, kt, 16, 16)
+        for reg, (dr, dc) in enumerate(((0, 0), (8, 0), (0, 8), (8, 8))):
+            for e in range(2):
+                whh[:, :, :, row0 + dr, col0 + dc + e] = frag[:, :, :, :, reg, e]
+        whh = whh.permute(0, 1, 3, 2, 4).reshape(2, 3 * H, H)
+        bhh = self.w_f32(op.p4, 6 * H).view(2, 3 * H)
+        ridx = (torch.arange(B) * Lh)[:, None] + torch.arange(T)[None, :]  # [B, T]
+        out = torch.zeros(B, T, 2 * H)
+        for d in range(2):
+            h = torch.zeros(B, H)
+            g_d = gi[:, d * 3 * H : (d + 1) * 3 * H]
+            for t in (range(T) if d == 0 else range(T - 1, -1, -1)):
+                hb = h.to(torch.bfloat16).float() if round_h else h
+                gh = hb @ whh[d].t() + bhh[d]
+                git = g_d[ridx[:, t]]
+                r = torch.sigmoid(git[:, :H] + gh[:, :H])
+                z = torch.sigmoid(git[:, H : 2 * H] + gh[:, H : 2 * H])
+                n = torch.tanh(git[:, 2 * H :] + r * gh[:, 2 * H :])
+                h = (1 - z) * n + z * h
+                out[:, t, d * H : (d + 1) * H] = h
+        b_idx = torch.arange(B).repeat_interleave(T)
+        l_idx = torch.arange(T).repeat(B)
+        v = out.reshape(B * T, 2 * H)
+        if op.add1.off >= 0:
+            v = v + self._gather(op.add1, b_idx, l_idx)
+        v = v * np.float32(op.scale)
+        self._write_outs(op, b_idx, l_idx, v)
+
+    # ---------------------------------------------------------------- driver
+    def run_op(self, i, io):
+        op = self.pg.ops[i]
+        t = op.type
+        if t == _abi.OP_GEMM:
+            self.op_gemm(op)
+        elif t == _abi.OP_PREP:
+            self.op_prep(op, io)
+        elif t == _abi.OP_MEL:
+            self.op_mel(op)
+        elif t == _abi.OP_MEL_FIN:
+            self.op_mel_fin(op)
+        elif t == _abi.OP_CONV_IN:
+            self.op_conv_in(op)
+        elif t == _abi.OP_INIT_X:
+            self.op_init_x(op, io)
+        elif t == _abi.OP_CONV_OUT:
+            self.op_conv_out(op, io)
+        elif t == _abi.OP_POST:
+            self.op_post(op, io)
+        elif t == _abi.OP_FILM:
+            self.op_film(op)
+        elif t == _abi.OP_GRU:
+            self.op_gru(op)
+        else:
+            raise ValueError(t)
+
+    def run(self, mix, noises, coefs, keep_rms=False, dbg=False, first=0, last=None):
+        io = dict(mix=mix, noise=noises, coef=coefs, keep_rms=keep_rms, dbg={} if dbg else None)
+        last = len(self.pg.ops) if last is None else last
+        for i in range(first, last):
+            self.run_op(i, io)
+        return io
