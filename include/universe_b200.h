@@ -112,6 +112,7 @@ typedef struct {
 } uv_step_coef;
 
 int uv_abi_version(void);
+size_t uv_sizeof_op(void); /* sizeof(uv_op), for binding self-checks */
 const char* uv_last_error(void);
 
 /* Uploads the packed weight blob to `device`. */

@@ -1,0 +1,157 @@
+"""ctypes binding of libuniverse_b200.so (include/universe_b200.h).
+
+There is NO fallback: if the shared library is missing or does not match the header,
+loading raises -- the product path never routes through PyTorch ops or the CPU oracle.
+"""
+import ctypes as C
+import os
+import subprocess
+
+from . import _abi
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libuniverse_b200.so")
+CSRC = os.path.join(_HERE, "csrc")
+
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17"]
+
+EXPORTS = [
+    "uv_abi_version", "uv_sizeof_op", "uv_last_error", "uv_model_create", "uv_model_destroy", "uv_plan_create",
+    "uv_plan_destroy", "uv_plan_arena_bytes", "uv_enhance", "uv_run_ops", "uv_arena_read", "uv_arena_write",
+    "uv_plan_num_launches",
+]
+
+
+def build_library(verbose=False):
+    """Compiles csrc/capi.cu for sm_100a into the in-tree shared library (nvcc cross-compiles without a GPU)."""
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    cmd = [nvcc] + NVCC_FLAGS + ["-shared", "-Xcompiler", "-fPIC", "-o", LIB_PATH, os.path.join(CSRC, "capi.cu")]
+    if verbose:
+        cmd.insert(1, "-Xptxas=-v")
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
+    return LIB_PATH, res.stdout + res.stderr
+
+
+def _needs_build():
+    if not os.path.exists(LIB_PATH):
+        return True
+    t = os.path.getmtime(LIB_PATH)
+    srcs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh"))]
+    srcs.append(os.path.join(_HERE, "..", "include", "universe_b200.h"))
+    return any(os.path.exists(s) and os.path.getmtime(s) > t for s in srcs)
+
+
+_lib = None
+
+
+def lib():
+    """Loads (once) and returns the native library; raises if it is absent or inconsistent."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"native library {LIB_PATH} not found. Build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(needs nvcc); open_universe_b200 has no PyTorch / CPU fallback."
+        )
+    L = C.CDLL(LIB_PATH)
+    for name in EXPORTS:
+        if not hasattr(L, name):
+            raise RuntimeError(f"{LIB_PATH} does not export {name}")
+    L.uv_abi_version.restype = C.c_int
+    L.uv_sizeof_op.restype = C.c_size_t
+    L.uv_last_error.restype = C.c_char_p
+    L.uv_model_create.argtypes = [C.POINTER(C.c_void_p), C.c_void_p, C.c_size_t, C.c_int]
+    L.uv_model_destroy.argtypes = [C.c_void_p]
+    L.uv_model_destroy.restype = None
+    L.uv_plan_create.argtypes = [C.POINTER(C.c_void_p), C.c_void_p, C.POINTER(_abi.UvOp), C.c_int, C.c_size_t,
+                                 C.c_void_p, C.c_size_t, C.c_size_t, C.c_int, C.c_int]
+    L.uv_plan_destroy.argtypes = [C.c_void_p]
+    L.uv_plan_destroy.restype = None
+    L.uv_plan_arena_bytes.argtypes = [C.c_void_p]
+    L.uv_plan_arena_bytes.restype = C.c_size_t
+    L.uv_plan_num_launches.argtypes = [C.c_void_p]
+    io = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(_abi.UvStepCoef), C.c_int, C.c_void_p]
+    L.uv_enhance.argtypes = [C.c_void_p] + io
+    L.uv_run_ops.argtypes = [C.c_void_p, C.c_int, C.c_int] + io
+    L.uv_arena_read.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
+    L.uv_arena_write.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
+    if L.uv_abi_version() != _abi.UV_ABI_VERSION:
+        raise RuntimeError(f"ABI version mismatch: library {L.uv_abi_version()}, binding {_abi.UV_ABI_VERSION}")
+    if L.uv_sizeof_op() != C.sizeof(_abi.UvOp):
+        raise RuntimeError(f"uv_op size mismatch: library {L.uv_sizeof_op()}, binding {C.sizeof(_abi.UvOp)}")
+    _lib = L
+    return L
+
+
+def _check(rc, what):
+    if rc != 0:
+        raise RuntimeError(f"{what} failed ({rc}): {lib().uv_last_error().decode()}")
+
+
+class NativeModel:
+    """Device-resident packed weights."""
+
+    def __init__(self, blob_bytes, device_index):
+        self.handle = C.c_void_p()
+        self.device_index = device_index
+        buf = C.create_string_buffer(blob_bytes, len(blob_bytes))
+        _check(lib().uv_model_create(C.byref(self.handle), buf, len(blob_bytes), device_index), "uv_model_create")
+
+    def close(self):
+        if self.handle:
+            lib().uv_model_destroy(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class NativePlan:
+    """One (B, T, n_steps) plan: arena + captured CUDA graph."""
+
+    def __init__(self, model, pg, use_graph=True):
+        self.model = model  # keep alive
+        self.pg = pg
+        self.handle = C.c_void_p()
+        n = len(pg.ops)
+        arr = (_abi.UvOp * n)(*pg.ops)
+        init = C.create_string_buffer(pg.init_blob, len(pg.init_blob))
+        _check(lib().uv_plan_create(C.byref(self.handle), model.handle, arr, n, pg.arena, init, len(pg.init_blob),
+                                    pg.init_off, pg.n_steps, 1 if use_graph else 0), "uv_plan_create")
+        self.num_launches = lib().uv_plan_num_launches(self.handle)
+
+    def _coefs(self, coefs):
+        arr = (_abi.UvStepCoef * len(coefs))()
+        for i, (a, b, c) in enumerate(coefs):
+            arr[i].a, arr[i].b, arr[i].c = a, b, c
+        return arr
+
+    def enhance(self, mix_ptr, noise_ptr, out_ptr, dbg_ptr, coefs, keep_rms, stream_ptr):
+        _check(lib().uv_enhance(self.handle, mix_ptr, noise_ptr, out_ptr, dbg_ptr, self._coefs(coefs),
+                                1 if keep_rms else 0, stream_ptr), "uv_enhance")
+
+    def run_ops(self, first, last, mix_ptr, noise_ptr, out_ptr, dbg_ptr, coefs, keep_rms, stream_ptr):
+        _check(lib().uv_run_ops(self.handle, first, last, mix_ptr, noise_ptr, out_ptr, dbg_ptr, self._coefs(coefs),
+                                1 if keep_rms else 0, stream_ptr), "uv_run_ops")
+
+    def arena_read(self, off, nbytes):
+        buf = C.create_string_buffer(nbytes)
+        _check(lib().uv_arena_read(self.handle, off, buf, nbytes), "uv_arena_read")
+        return buf.raw
+
+    def close(self):
+        if self.handle:
+            lib().uv_plan_destroy(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

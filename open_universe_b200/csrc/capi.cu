@@ -1,0 +1,356 @@
+// C ABI (include/universe_b200.h): model = device weight blob, plan = op program +
+// arena + CUDA graph.  Translates uv_op records into kernel launches.
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/universe_b200.h"
+#include "gemm_tc.cuh"
+#include "gru.cuh"
+#include "small_ops.cuh"
+
+using namespace uv;
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string& msg) {
+  g_err = msg;
+  return code;
+}
+#define CUDA_TRY(x)                                                                              \
+  do {                                                                                           \
+    cudaError_t e_ = (x);                                                                        \
+    if (e_ != cudaSuccess)                                                                       \
+      return fail(UV_ERR_CUDA, std::string(#x) + ": " + cudaGetErrorString(e_) + " (" + __FILE__ + ":" + \
+                                   std::to_string(__LINE__) + ")");                              \
+  } while (0)
+
+struct uv_model {
+  int device = 0;
+  char* blob = nullptr;
+  size_t nbytes = 0;
+  int num_sms = 0;
+};
+
+struct uv_plan {
+  uv_model* model = nullptr;
+  std::vector<uv_op> ops;
+  char* arena = nullptr;
+  size_t arena_bytes = 0;
+  IoTable* io_dev = nullptr;
+  IoTable* io_host = nullptr;     // pinned
+  char* coef_host = nullptr;      // pinned: uv_step_coef[n_steps] + int keep_rms (+pad)
+  int64_t coef_off = -1;
+  int n_steps = 0;
+  int* err_flag = nullptr;
+  cudaGraph_t graph = nullptr;
+  cudaGraphExec_t exec = nullptr;
+  cudaStream_t cap_stream = nullptr;
+  int n_launches = 0;
+  bool use_graph = false;
+};
+
+extern "C" int uv_abi_version(void) { return UV_ABI_VERSION; }
+extern "C" size_t uv_sizeof_op(void) { return sizeof(uv_op); }
+extern "C" const char* uv_last_error(void) { return g_err.c_str(); }
+
+extern "C" int uv_model_create(uv_model** out, const void* weights, size_t nbytes, int device) {
+  if (!out || !weights || nbytes == 0) return fail(UV_ERR_INVALID, "uv_model_create: null argument");
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || device >= n) return fail(UV_ERR_NO_DEVICE, "no such CUDA device");
+  cudaDeviceProp prop;
+  CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) return fail(UV_ERR_NO_DEVICE, "device is not sm_100 (B200): found sm_" + std::to_string(prop.major * 10 + prop.minor));
+  CUDA_TRY(cudaSetDevice(device));
+  uv_model* m = new uv_model();
+  m->device = device;
+  m->nbytes = nbytes;
+  m->num_sms = prop.multiProcessorCount;
+  CUDA_TRY(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  CUDA_TRY(cudaFuncSetAttribute(gru_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gru_smem_bytes(kGruMaxH)));
+  CUDA_TRY(cudaMalloc(&m->blob, nbytes));
+  CUDA_TRY(cudaMemcpy(m->blob, weights, nbytes, cudaMemcpyHostToDevice));
+  *out = m;
+  return UV_OK;
+}
+
+extern "C" void uv_model_destroy(uv_model* m) {
+  if (!m) return;
+  cudaSetDevice(m->device);
+  cudaFree(m->blob);
+  delete m;
+}
+
+// ------------------------------------------------------------------ op translation
+static TensDesc to_desc(const uv_plan* p, const uv_tens& t) {
+  TensDesc d;
+  memset(&d, 0, sizeof(d));
+  if (t.off < 0) return d;
+  d.base = p->arena + t.off;
+  d.esize_log2 = t.dtype == 1 ? 1 : 2;
+  d.nchunks = t.nch; d.split = t.split; d.Lh = t.Lh; d.P = t.P; d.G = t.G;
+  return d;
+}
+static OutDesc to_out(const uv_plan* p, const uv_out& o) {
+  OutDesc d;
+  memset(&d, 0, sizeof(d));
+  d.t = to_desc(p, o.t);
+  d.act = o.act; d.a1 = o.a1; d.a2 = o.a2;
+  return d;
+}
+template <typename T>
+static T* wptr(const uv_plan* p, int64_t off) { return off < 0 ? nullptr : reinterpret_cast<T*>(p->model->blob + off); }
+template <typename T>
+static T* aptr(const uv_plan* p, int64_t off) { return off < 0 ? nullptr : reinterpret_cast<T*>(p->arena + off); }
+
+static int check_tens(const uv_plan* p, const uv_tens& t, const char* what) {
+  if (t.off < 0) return UV_OK;
+  const size_t es = t.dtype == 1 ? 2 : 4;
+  const size_t end = (size_t)t.off + (size_t)t.split * t.nch * t.P * 8 * es;
+  if (end > p->arena_bytes || (t.off & 15)) return fail(UV_ERR_INVALID, std::string("tensor out of arena: ") + what);
+  return UV_OK;
+}
+
+static int launch_op(uv_plan* p, const uv_op& op, cudaStream_t s) {
+  switch (op.type) {
+    case UV_OP_GEMM: {
+      GemmParams g;
+      memset(&g, 0, sizeof(g));
+      g.a_base = p->arena + op.a.off;
+      g.a_nchunks = op.a.nch; g.a_P = op.a.P; g.a_G = op.a.G;
+      g.n_src = op.n_src; g.smin = op.smin; g.smax = op.smax; g.KC = op.KC;
+      g.n_groups = op.a.nch * 8 / op.KC;
+      g.w = wptr<const char>(p, op.w_w);
+      g.N_TILE = op.N_TILE; g.n_tiles_n = op.N_total / op.N_TILE;
+      g.m_rows = op.m_rows; g.Lh_A = op.Lh_A; g.M_valid = op.M_valid;
+      g.up = op.up; g.C_out = op.C_out;
+      g.bias = wptr<const float>(p, op.bias_w);
+      g.film = aptr<const float>(p, op.film);
+      g.add1 = to_desc(p, op.add1); g.add2 = to_desc(p, op.add2);
+      g.scale = op.scale; g.n_out = op.n_out;
+      for (int i = 0; i < 3; ++i) g.out[i] = to_out(p, op.out[i]);
+      g.rm_out = aptr<float>(p, op.rm_out); g.rm_ld = op.rm_ld;
+      g.err_flag = p->err_flag;
+      CUDA_TRY(gemm_launch(g, p->model->num_sms, s));
+      break;
+    }
+    case UV_OP_PREP:
+      prep_kernel<<<op.B, 1024, 0, s>>>(p->io_dev, op.T, op.Lp, op.i0, op.f0, aptr<float>(p, op.p0), aptr<float>(p, op.p1));
+      break;
+    case UV_OP_MEL: {
+      const int nft = (op.F + kMelFT - 1) / kMelFT;
+      const size_t sm = ((size_t)(kMelFT - 1) * op.i1 + op.i0 + (size_t)kMelFT * op.i2) * sizeof(float);
+      mel_kernel<<<dim3(nft, op.B), 256, sm, s>>>(aptr<const float>(p, op.p0), op.Lp, op.F, op.i0, op.i1, op.i2, op.H, op.C,
+                                                  op.i3, wptr<const float>(p, op.p3), wptr<const float>(p, op.p4),
+                                                  aptr<float>(p, op.p1), aptr<float>(p, op.p2), nft);
+      break;
+    }
+    case UV_OP_MEL_FIN: {
+      const int items = op.F * (op.C / 8);
+      mel_fin_kernel<<<dim3((items + 255) / 256, op.B), 256, 0, s>>>(aptr<const float>(p, op.p0), aptr<const float>(p, op.p1),
+                                                                     op.F, op.C, op.i0, to_out(p, op.out[0]));
+      break;
+    }
+    case UV_OP_CONV_IN: {
+      const long long n = (long long)op.B * op.Lp;
+      conv_in_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(aptr<const float>(p, op.p0), op.B, op.Lp, op.C, op.f0,
+                                                                 wptr<const float>(p, op.p3), wptr<const float>(p, op.p4),
+                                                                 op.n_out, to_out(p, op.out[0]), to_out(p, op.out[1]));
+      break;
+    }
+    case UV_OP_INIT_X: {
+      const long long n = (long long)op.B * op.Lp;
+      init_x_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(p->io_dev, n, op.i0, op.f0, aptr<float>(p, op.p0));
+      break;
+    }
+    case UV_OP_CONV_OUT: {
+      const long long n = (long long)op.B * op.Lp;
+      conv_out_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(to_desc(p, op.a), op.B, op.Lp, op.C, wptr<const float>(p, op.p3),
+                                                                  wptr<const float>(p, op.p4), aptr<float>(p, op.p0),
+                                                                  aptr<const StepCoef>(p, op.p1), op.i0, p->io_dev);
+      break;
+    }
+    case UV_OP_POST:
+      post_kernel<<<op.B, 1024, 0, s>>>(aptr<const float>(p, op.p0), op.T, op.Lp, op.i0, aptr<const float>(p, op.p1),
+                                        aptr<const int>(p, op.p2), p->io_dev);
+      break;
+    case UV_OP_FILM:
+      film_kernel<<<op.i0, 512, 2 * op.C * sizeof(float), s>>>(aptr<const float>(p, op.p0), op.i1, op.C, op.H, op.i2,
+                                                               wptr<const float>(p, op.p3), wptr<const float>(p, op.p4),
+                                                               wptr<const float>(p, op.p5), aptr<float>(p, op.p1));
+      break;
+    case UV_OP_GRU: {
+      if (op.H > kGruMaxH || op.H % 16) return fail(UV_ERR_INVALID, "GRU hidden size unsupported");
+      GruParams g;
+      memset(&g, 0, sizeof(g));
+      g.gi = aptr<const float>(p, op.p0);
+      g.whh = wptr<const uint4>(p, op.p3);
+      g.bhh = wptr<const float>(p, op.p4);
+      g.B = op.B; g.T = op.T; g.H = op.H; g.Lh = op.Lh_A;
+      g.add1 = to_desc(p, op.add1); g.scale = op.scale; g.n_out = op.n_out;
+      for (int i = 0; i < 3; ++i) g.out[i] = to_out(p, op.out[i]);
+      const size_t sm = gru_smem_bytes(op.H);
+      gru_kernel<<<dim3((op.B + kGruNB - 1) / kGruNB, 2), kGruThreads, sm, s>>>(g);
+      break;
+    }
+    default:
+      return fail(UV_ERR_INVALID, "unknown op type " + std::to_string(op.type));
+  }
+  CUDA_TRY(cudaGetLastError());
+  return UV_OK;
+}
+
+static int validate_ops(uv_plan* p) {
+  for (size_t i = 0; i < p->ops.size(); ++i) {
+    const uv_op& op = p->ops[i];
+    int rc;
+    if ((rc = check_tens(p, op.a, "a"))) return rc;
+    if ((rc = check_tens(p, op.add1, "add1"))) return rc;
+    if ((rc = check_tens(p, op.add2, "add2"))) return rc;
+    for (int k = 0; k < 3; ++k)
+      if ((rc = check_tens(p, op.out[k].t, "out"))) return rc;
+    if (op.type == UV_OP_GEMM) {
+      if (op.a.off < 0 || op.KC % 16 || op.N_TILE % 16 || op.N_TILE > 256 || op.N_total % op.N_TILE ||
+          (op.a.nch * 8) % op.KC || op.C_out % op.N_TILE || op.smin < -kGuard || op.smax > kGuard || op.a.split != op.n_src)
+        return fail(UV_ERR_INVALID, "malformed GEMM op #" + std::to_string(i));
+      if (op.a.P < op.a.G + ((op.m_rows + 127) / 128) * 128 + op.smax)
+        return fail(UV_ERR_INVALID, "GEMM A plane too short, op #" + std::to_string(i));
+    }
+  }
+  return UV_OK;
+}
+
+static int enqueue_range(uv_plan* p, int first, int last, cudaStream_t s, bool skip_setup) {
+  for (int i = first; i < last; ++i) {
+    if (skip_setup && p->ops[i].step == -2) continue;
+    int rc = launch_op(p, p->ops[i], s);
+    if (rc) return rc;
+  }
+  return UV_OK;
+}
+
+extern "C" int uv_plan_create(uv_plan** out, uv_model* m, const uv_op* ops, int n_ops, size_t arena_bytes,
+                              const void* init, size_t nbytes_init, size_t init_off, int n_steps, int use_graph) {
+  if (!out || !m || !ops || n_ops <= 0) return fail(UV_ERR_INVALID, "uv_plan_create: null argument");
+  CUDA_TRY(cudaSetDevice(m->device));
+  uv_plan* p = new uv_plan();
+  p->model = m;
+  p->ops.assign(ops, ops + n_ops);
+  p->arena_bytes = arena_bytes;
+  p->n_steps = n_steps;
+  p->use_graph = use_graph != 0;
+  CUDA_TRY(cudaMalloc(&p->arena, arena_bytes));
+  CUDA_TRY(cudaMemset(p->arena, 0, arena_bytes));
+  if (init && nbytes_init) {
+    if (init_off + nbytes_init > arena_bytes) return fail(UV_ERR_INVALID, "init blob out of arena");
+    CUDA_TRY(cudaMemcpy(p->arena + init_off, init, nbytes_init, cudaMemcpyHostToDevice));
+  }
+  CUDA_TRY(cudaMalloc(&p->io_dev, sizeof(IoTable)));
+  CUDA_TRY(cudaMallocHost(&p->io_host, sizeof(IoTable)));
+  CUDA_TRY(cudaMallocHost(&p->coef_host, (size_t)n_steps * 16 + 16));
+  CUDA_TRY(cudaMalloc(&p->err_flag, sizeof(int)));
+  CUDA_TRY(cudaMemset(p->err_flag, 0, sizeof(int)));
+  int rc = validate_ops(p);
+  if (rc) { uv_plan_destroy(p); return rc; }
+  for (const uv_op& op : p->ops) {
+    if (op.type == UV_OP_CONV_OUT) p->coef_off = op.p1;
+    if (op.step != -2) ++p->n_launches;
+  }
+  // plan-time setup ops (FiLM table)
+  for (int i = 0; i < n_ops; ++i)
+    if (p->ops[i].step == -2 && (rc = launch_op(p, p->ops[i], 0))) { uv_plan_destroy(p); return rc; }
+  CUDA_TRY(cudaDeviceSynchronize());
+  if (p->use_graph) {
+    CUDA_TRY(cudaStreamCreateWithFlags(&p->cap_stream, cudaStreamNonBlocking));
+    CUDA_TRY(cudaStreamBeginCapture(p->cap_stream, cudaStreamCaptureModeThreadLocal));
+    rc = enqueue_range(p, 0, n_ops, p->cap_stream, true);
+    cudaError_t e = cudaStreamEndCapture(p->cap_stream, &p->graph);
+    if (rc) { uv_plan_destroy(p); return rc; }
+    if (e != cudaSuccess) { uv_plan_destroy(p); return fail(UV_ERR_CUDA, std::string("graph capture: ") + cudaGetErrorString(e)); }
+    CUDA_TRY(cudaGraphInstantiate(&p->exec, p->graph, 0));
+  }
+  *out = p;
+  return UV_OK;
+}
+
+extern "C" void uv_plan_destroy(uv_plan* p) {
+  if (!p) return;
+  cudaSetDevice(p->model->device);
+  if (p->exec) cudaGraphExecDestroy(p->exec);
+  if (p->graph) cudaGraphDestroy(p->graph);
+  if (p->cap_stream) cudaStreamDestroy(p->cap_stream);
+  cudaFree(p->arena);
+  cudaFree(p->io_dev);
+  cudaFree(p->err_flag);
+  if (p->io_host) cudaFreeHost(p->io_host);
+  if (p->coef_host) cudaFreeHost(p->coef_host);
+  delete p;
+}
+
+extern "C" size_t uv_plan_arena_bytes(const uv_plan* p) { return p ? p->arena_bytes : 0; }
+extern "C" int uv_plan_num_launches(const uv_plan* p) { return p ? p->n_launches : 0; }
+
+static int stage_io(uv_plan* p, const float* mix, const float* noise, float* out, float* dbg,
+                    const uv_step_coef* coef, int keep_rms, cudaStream_t s) {
+  if (!mix || !noise || !out || !coef) return fail(UV_ERR_INVALID, "uv_enhance: null pointer");
+  // the previous call's async copies from these pinned buffers must have completed
+  CUDA_TRY(cudaStreamSynchronize(s));
+  p->io_host->mix = mix; p->io_host->noise = noise; p->io_host->out = out; p->io_host->dbg = dbg;
+  CUDA_TRY(cudaMemcpyAsync(p->io_dev, p->io_host, sizeof(IoTable), cudaMemcpyHostToDevice, s));
+  if (p->coef_off >= 0) {
+    memcpy(p->coef_host, coef, (size_t)p->n_steps * 16);
+    int kr[4] = {keep_rms, 0, 0, 0};
+    memcpy(p->coef_host + (size_t)p->n_steps * 16, kr, 16);
+    CUDA_TRY(cudaMemcpyAsync(p->arena + p->coef_off, p->coef_host, (size_t)p->n_steps * 16 + 16, cudaMemcpyHostToDevice, s));
+  }
+  return UV_OK;
+}
+
+static int check_err_flag(uv_plan* p) {
+  int flag = 0;
+  CUDA_TRY(cudaMemcpy(&flag, p->err_flag, sizeof(int), cudaMemcpyDeviceToHost));
+  if (flag) return fail(UV_ERR_KERNEL, "device watchdog fired, code " + std::to_string(flag));
+  return UV_OK;
+}
+
+extern "C" int uv_enhance(uv_plan* p, const float* mix, const float* noise, float* out, float* dbg_net,
+                          const uv_step_coef* coef, int keep_rms, void* stream) {
+  if (!p) return fail(UV_ERR_INVALID, "uv_enhance: null plan");
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  CUDA_TRY(cudaSetDevice(p->model->device));
+  int rc = stage_io(p, mix, noise, out, dbg_net, coef, keep_rms, s);
+  if (rc) return rc;
+  if (p->use_graph) {
+    CUDA_TRY(cudaGraphLaunch(p->exec, s));
+  } else if ((rc = enqueue_range(p, 0, (int)p->ops.size(), s, true))) {
+    return rc;
+  }
+  return UV_OK;
+}
+
+extern "C" int uv_run_ops(uv_plan* p, int first, int last, const float* mix, const float* noise, float* out,
+                          float* dbg_net, const uv_step_coef* coef, int keep_rms, void* stream) {
+  if (!p || first < 0 || last > (int)p->ops.size()) return fail(UV_ERR_INVALID, "uv_run_ops: bad range");
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  CUDA_TRY(cudaSetDevice(p->model->device));
+  int rc = stage_io(p, mix, noise, out, dbg_net, coef, keep_rms, s);
+  if (rc) return rc;
+  if ((rc = enqueue_range(p, first, last, s, false))) return rc;
+  CUDA_TRY(cudaStreamSynchronize(s));
+  return check_err_flag(p);
+}
+
+extern "C" int uv_arena_read(uv_plan* p, size_t off, void* host_dst, size_t nbytes) {
+  if (!p || off + nbytes > p->arena_bytes) return fail(UV_ERR_INVALID, "uv_arena_read: out of range");
+  CUDA_TRY(cudaSetDevice(p->model->device));
+  CUDA_TRY(cudaDeviceSynchronize());
+  CUDA_TRY(cudaMemcpy(host_dst, p->arena + off, nbytes, cudaMemcpyDeviceToHost));
+  return UV_OK;
+}
+
+extern "C" int uv_arena_write(uv_plan* p, size_t off, const void* host_src, size_t nbytes) {
+  if (!p || off + nbytes > p->arena_bytes) return fail(UV_ERR_INVALID, "uv_arena_write: out of range");
+  CUDA_TRY(cudaSetDevice(p->model->device));
+  CUDA_TRY(cudaMemcpy(p->arena + off, host_src, nbytes, cudaMemcpyHostToDevice));
+  return UV_OK;
+}

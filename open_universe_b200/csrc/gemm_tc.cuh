@@ -116,62 +116,6 @@ __device__ __forceinline__ uint32_t make_idesc(int M, int N) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
-struct RowAddr {
-  char* p;            // address of (row, chunk 0) in phase plane; nullptr if unused
-  long long pstride;  // bytes between chunk planes
-};
-
-__device__ __forceinline__ RowAddr row_addr(const TensDesc& t, int b, int l) {
-  RowAddr r;
-  if (t.base == nullptr) {
-    r.p = nullptr;
-    r.pstride = 0;
-    return r;
-  }
-  int ph = 0, ll = l;
-  if (t.split > 1) {
-    ll = l / t.split;
-    ph = l - ll * t.split;
-  }
-  long long row = (long long)ph * t.nchunks * t.P + t.G + (long long)b * t.Lh + ll;
-  r.p = t.base + ((row * 8) << t.esize_log2);
-  r.pstride = ((long long)t.P * 8) << t.esize_log2;
-  return r;
-}
-
-__device__ __forceinline__ void load8(const RowAddr& r, int esize_log2, int chunk, float* v) {
-  const char* p = r.p + (long long)chunk * r.pstride;
-  if (esize_log2 == 1) {
-    uint4 u = *reinterpret_cast<const uint4*>(p);
-    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      float2 f = __bfloat1622float2(h[i]);
-      v[2 * i] = f.x;
-      v[2 * i + 1] = f.y;
-    }
-  } else {
-    float4 a = *reinterpret_cast<const float4*>(p);
-    float4 c = *reinterpret_cast<const float4*>(p + 16);
-    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
-    v[4] = c.x; v[5] = c.y; v[6] = c.z; v[7] = c.w;
-  }
-}
-
-__device__ __forceinline__ void store8(const RowAddr& r, int esize_log2, int chunk, const float* v) {
-  char* p = r.p + (long long)chunk * r.pstride;
-  if (esize_log2 == 1) {
-    uint4 u;
-    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
-#pragma unroll
-    for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
-    *reinterpret_cast<uint4*>(p) = u;
-  } else {
-    *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
-    *reinterpret_cast<float4*>(p + 16) = make_float4(v[4], v[5], v[6], v[7]);
-  }
-}
-
 // ------------------------------------------------------------------ kernel
 __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_constant__ GemmParams P) {
   extern __shared__ __align__(1024) uint8_t smem[];

@@ -1,0 +1,319 @@
+// Memory-bound kernels of the enhance() path: normalise/pad, mel front-end,
+// 1->C input conv, C->1 output conv fused with the sampler update, post-processing
+// and the FiLM table.  All coalesced + vectorised; reductions by warp shuffle.
+#pragma once
+#include "uv_common.cuh"
+
+namespace uv {
+
+struct IoTable {
+  const float* mix;    // [B][T]
+  const float* noise;  // [n_steps][B][Lp]
+  float* out;          // [B][T]
+  float* dbg;          // [n_steps][B][Lp] or null
+};
+
+struct StepCoef {
+  float a, b, c, pad_;
+};
+
+template <typename T>
+__device__ __forceinline__ T warp_sum(T v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// Block-wide sum of up to 3 doubles (blockDim.x multiple of 32, <= 1024). Result valid in all threads.
+__device__ __forceinline__ void block_sum3(double& a, double& b, double& c, double* sh /* [3*32] */) {
+  a = warp_sum(a); b = warp_sum(b); c = warp_sum(c);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31, nw = blockDim.x >> 5;
+  __syncthreads();
+  if (l == 0) { sh[w] = a; sh[32 + w] = b; sh[64 + w] = c; }
+  __syncthreads();
+  a = (l < nw) ? sh[l] : 0.0; b = (l < nw) ? sh[32 + l] : 0.0; c = (l < nw) ? sh[64 + l] : 0.0;
+  a = warp_sum(a); b = warp_sum(b); c = warp_sum(c);
+}
+
+// ---------------------------------------------------------------- PREP
+// Universe.pad (universe.py:219-223) + utils.normalize_batch norm=2, zero_mean
+// (utils/norm.py:47-87): statistics over the PADDED signal, unbiased std, clamp 1e-5.
+// Also mix_rms over the unpadded input (universe.py:259).  One CTA per utterance.
+__global__ void __launch_bounds__(1024) prep_kernel(const IoTable* io, int T, int Lp, int pad_left, float level,
+                                                    float* sig, float* mix_rms) {
+  __shared__ double sh[96];
+  const int b = blockIdx.x;
+  const float* mix = io->mix + (size_t)b * T;
+  double s = 0, ss = 0, dummy = 0;
+  for (int i = threadIdx.x; i < T; i += blockDim.x) {
+    const double v = mix[i];
+    s += v; ss += v * v;
+  }
+  block_sum3(s, ss, dummy, sh);
+  const double mean = s / Lp;
+  double var = (ss - (double)Lp * mean * mean) / (double)(Lp - 1);
+  if (var < 0) var = 0;
+  const float meanf = (float)mean;
+  const float gain = level / fmaxf((float)sqrt(var), 1e-5f);
+  if (threadIdx.x == 0) mix_rms[b] = (float)sqrt(ss / T);
+  float* o = sig + (size_t)b * Lp;
+  for (int i = threadIdx.x; i < Lp; i += blockDim.x) {
+    const int j = i - pad_left;
+    const float v = (j >= 0 && j < T) ? mix[j] : 0.f;
+    o[i] = (v - meanf) * gain;
+  }
+}
+
+// ---------------------------------------------------------------- MEL
+// MelAdapter.compute_mel_spec (condition.py:92-108): explicit (n_fft-hop)/2 padding,
+// Hann-windowed power spectrum (torchaudio MelSpectrogram, center=False, power=2),
+// mel filterbank.  The windowed real-DFT basis [n_fft][2*nbp] and fb come from the
+// checkpoint buffers.  One CTA = 8 frames of one utterance; fp32 throughout.
+constexpr int kMelFT = 8;
+__global__ void __launch_bounds__(256) mel_kernel(const float* __restrict__ sig, int Lp, int F, int n_fft, int hop,
+                                                  int nb, int nbp, int n_mels, int pad_left,
+                                                  const float* __restrict__ basis, const float* __restrict__ fb,
+                                                  float* __restrict__ melraw, float* __restrict__ energy, int nft) {
+  extern __shared__ float smem_f[];
+  const int span = (kMelFT - 1) * hop + n_fft;
+  float* xs = smem_f;          // [span]
+  float* pw = smem_f + span;   // [kMelFT][nb]
+  __shared__ double sh[96];
+  const int b = blockIdx.y, f0 = blockIdx.x * kMelFT;
+  const float* x = sig + (size_t)b * Lp;
+  for (int i = threadIdx.x; i < span; i += blockDim.x) {
+    const int j = f0 * hop + i - pad_left;
+    xs[i] = (j >= 0 && j < Lp) ? x[j] : 0.f;
+  }
+  __syncthreads();
+  for (int k = threadIdx.x; k < nb; k += blockDim.x) {
+    float re[kMelFT], im[kMelFT];
+#pragma unroll
+    for (int f = 0; f < kMelFT; ++f) re[f] = im[f] = 0.f;
+    const float* bc = basis + k;
+    const float* bs = basis + nbp + k;
+    for (int n = 0; n < n_fft; ++n) {
+      const float c = bc[(size_t)n * 2 * nbp], s = bs[(size_t)n * 2 * nbp];
+#pragma unroll
+      for (int f = 0; f < kMelFT; ++f) {
+        const float v = xs[f * hop + n];
+        re[f] = fmaf(v, c, re[f]);
+        im[f] = fmaf(v, s, im[f]);
+      }
+    }
+#pragma unroll
+    for (int f = 0; f < kMelFT; ++f) pw[f * nb + k] = re[f] * re[f] + im[f] * im[f];
+  }
+  __syncthreads();
+  double e = 0, d1 = 0, d2 = 0;
+  for (int idx = threadIdx.x; idx < kMelFT * n_mels; idx += blockDim.x) {
+    const int f = idx / n_mels, m = idx - f * n_mels;
+    float acc = 0.f;
+    for (int k = 0; k < nb; ++k) acc = fmaf(pw[f * nb + k], fb[(size_t)k * n_mels + m], acc);
+    if (f0 + f < F) {
+      melraw[((size_t)b * F + f0 + f) * n_mels + m] = acc;
+      e += (double)acc * acc;
+    }
+  }
+  block_sum3(e, d1, d2, sh);
+  if (threadIdx.x == 0) energy[(size_t)b * nft + blockIdx.x] = (float)e;
+}
+
+// Global mel normalisation (condition.py:105-106): x / clamp(sqrt(mean_t sum_m x^2), 1e-5) -> bf16 planes.
+__global__ void __launch_bounds__(256) mel_fin_kernel(const float* __restrict__ melraw, const float* __restrict__ energy,
+                                                      int F, int n_mels, int nft, OutDesc out) {
+  __shared__ float s_inv;
+  const int b = blockIdx.y;
+  if (threadIdx.x == 0) {
+    float e = 0.f;
+    for (int i = 0; i < nft; ++i) e += energy[(size_t)b * nft + i];
+    s_inv = 1.f / fmaxf(sqrtf(e / (float)F), 1e-5f);
+  }
+  __syncthreads();
+  const float inv = s_inv;
+  const int nch = n_mels >> 3;
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;  // (frame, chunk), frame fastest
+  if (idx >= F * nch) return;
+  const int ch = idx / F, f = idx - ch * F;
+  const float* src = melraw + ((size_t)b * F + f) * n_mels + ch * 8;
+  float v[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] = apply_act(src[i] * inv, out.act, out.a1, out.a2);
+  RowAddr r = row_addr(out.t, b, f);
+  store8(r, out.t.esize_log2, ch, v);
+}
+
+// ---------------------------------------------------------------- CONV_IN
+// 1 -> C, k=3, "same" input convolution on an f32 signal (score.py:285 on w_in*x,
+// condition.py:360), writing the raw tensor and the PReLU-activated copy.
+__global__ void __launch_bounds__(256) conv_in_kernel(const float* __restrict__ x, int B, int Lp, int C, float in_scale,
+                                                      const float* __restrict__ w /*[3][C]*/, const float* __restrict__ bias,
+                                                      int n_out, OutDesc o0, OutDesc o1) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (long long)B * Lp) return;
+  const int b = (int)(idx / Lp), l = (int)(idx - (long long)b * Lp);
+  const float* xr = x + (size_t)b * Lp;
+  const float xm = (l > 0 ? xr[l - 1] : 0.f) * in_scale;
+  const float x0 = xr[l] * in_scale;
+  const float xp = (l + 1 < Lp ? xr[l + 1] : 0.f) * in_scale;
+  RowAddr r0 = row_addr(o0.t, b, l), r1 = row_addr(o1.t, b, l);
+  for (int ch = 0; ch < (C >> 3); ++ch) {
+    float v[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int c = ch * 8 + i;
+      v[i] = fmaf(w[c], xm, fmaf(w[C + c], x0, fmaf(w[2 * C + c], xp, bias[c])));
+    }
+    if (n_out > 0) {
+      float u[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) u[i] = apply_act(v[i], o0.act, o0.a1, o0.a2);
+      store8(r0, o0.t.esize_log2, ch, u);
+    }
+    if (n_out > 1) {
+      float u[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) u[i] = apply_act(v[i], o1.act, o1.a1, o1.a2);
+      store8(r1, o1.t.esize_log2, ch, u);
+    }
+  }
+}
+
+// ---------------------------------------------------------------- INIT_X   x = sigma_0 * z_0 (universe.py:326)
+__global__ void __launch_bounds__(256) init_x_kernel(const IoTable* io, long long n, int noise_idx, float sigma0, float* x) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) x[i] = sigma0 * io->noise[(long long)noise_idx * n + i];
+}
+
+// ---------------------------------------------------------------- CONV_OUT
+// output_conv (C -> 1, k=3; score.py:290) on the already doubly-activated planes, fused with
+// the EDM wrapper and the sampler update (universe.py:197-209, 334-343):  x <- a x + b net + c z.
+__global__ void __launch_bounds__(256) conv_out_kernel(TensDesc a, int B, int Lp, int C, const float* __restrict__ w /*[3][C]*/,
+                                                       const float* __restrict__ bias, float* __restrict__ x,
+                                                       const StepCoef* __restrict__ coef, int step, const IoTable* io) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (long long)B * Lp) return;
+  const int b = (int)(idx / Lp), l = (int)(idx - (long long)b * Lp);
+  // rows l-1, l, l+1 of the plain planes tensor; rows -1 and Lp are the zero gap
+  const RowAddr r = row_addr(a, b, l);
+  float acc = bias[0];
+  for (int ch = 0; ch < (C >> 3); ++ch) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      RowAddr rk = r;
+      rk.p += (long long)(k - 1) * 16;
+      float v[8];
+      load8(rk, 1, ch, v);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc = fmaf(v[i], w[k * C + ch * 8 + i], acc);
+    }
+  }
+  const StepCoef cf = coef[step];
+  float xn = cf.a * x[idx] + cf.b * acc;
+  if (cf.c != 0.f) xn = fmaf(cf.c, io->noise[(long long)(step + 1) * B * Lp + idx], xn);
+  x[idx] = xn;
+  if (io->dbg) io->dbg[(long long)step * B * Lp + idx] = acc;
+}
+
+// ---------------------------------------------------------------- POST
+// unpad, optional keep_rms, per-utterance peak normalisation (universe.py:349-357). One CTA per utterance.
+__global__ void __launch_bounds__(1024) post_kernel(const float* __restrict__ x, int T, int Lp, int pad_left,
+                                                    const float* __restrict__ mix_rms, const int* __restrict__ keep_rms,
+                                                    const IoTable* io) {
+  __shared__ double sh[96];
+  __shared__ float s_max[32];
+  const int b = blockIdx.x;
+  const float* xr = x + (size_t)b * Lp + pad_left;
+  double ss = 0, d1 = 0, d2 = 0;
+  float mx = 0.f;
+  for (int i = threadIdx.x; i < T; i += blockDim.x) {
+    const float v = xr[i];
+    ss += (double)v * v;
+    mx = fmaxf(mx, fabsf(v));
+  }
+  block_sum3(ss, d1, d2, sh);
+  mx = warp_max(mx);
+  if ((threadIdx.x & 31) == 0) s_max[threadIdx.x >> 5] = mx;
+  __syncthreads();
+  mx = (threadIdx.x & 31) < (blockDim.x >> 5) ? s_max[threadIdx.x & 31] : 0.f;
+  mx = warp_max(mx);
+  float g = 1.f;
+  if (*keep_rms) {
+    const float x_rms = fmaxf((float)sqrt(ss / T), 1e-5f);
+    g = mix_rms[b] / x_rms;
+  }
+  const float peak = mx * g;
+  float* o = io->out + (size_t)b * T;
+  for (int i = threadIdx.x; i < T; i += blockDim.x) {
+    float v = xr[i] * g;
+    if (peak > 1.f) v = v / peak;
+    o[i] = v;
+  }
+}
+
+// ---------------------------------------------------------------- FILM
+// Noise-level embedding (SimpleTimeEmbedding sigma_block.py:73-78 / SigmaBlock :50-57) followed by
+// every FiLM projection Linear(D -> 2C) of the score network (score.py:109,208) for one sampler step.
+__global__ void __launch_bounds__(512) film_kernel(const float* __restrict__ log10s, int kind, int D, int n_rff, int R,
+                                                   const float* __restrict__ emb, const float* __restrict__ W,
+                                                   const float* __restrict__ bias, float* __restrict__ film) {
+  extern __shared__ float smem_f[];
+  float* g = smem_f;        // [D]
+  float* tmp = smem_f + D;  // [D]
+  const int step = blockIdx.x;
+  const float ls = log10s[step];
+  const float two_pi = 6.283185307179586f;
+  if (kind == 0) {
+    const float f = 0.5f * (1.f / (1.f + expf(-(emb[0] * ls + emb[1]))));
+    for (int i = threadIdx.x; i < D / 2; i += blockDim.x) {
+      const float p = two_pi * f * (float)i;
+      g[i] = sinf(p);
+      g[D / 2 + i] = cosf(p);
+    }
+    __syncthreads();
+  } else {
+    for (int i = threadIdx.x; i < n_rff; i += blockDim.x) {
+      const float p = two_pi * emb[i] * ls;
+      g[i] = sinf(p);
+      g[n_rff + i] = cosf(p);
+    }
+    __syncthreads();
+    const float* p = emb + n_rff;
+    int in = 2 * n_rff;
+    float* src = g;
+    float* dst = tmp;
+    for (int layer = 0; layer < 3; ++layer) {
+      const int out = layer == 2 ? D : 2 * in;
+      const float slope = p[0];
+      const float* Wl = p + 1;
+      const float* bl = Wl + (size_t)in * out;
+      for (int o = threadIdx.x; o < out; o += blockDim.x) {
+        float acc = bl[o];
+        for (int k = 0; k < in; ++k) acc = fmaf(Wl[(size_t)o * in + k], src[k], acc);
+        dst[o] = prelu1(acc, slope);
+      }
+      __syncthreads();
+      p = bl + out;
+      in = out;
+      float* t = src; src = dst; dst = t;
+    }
+    if (src != g) {
+      for (int i = threadIdx.x; i < D; i += blockDim.x) g[i] = src[i];
+      __syncthreads();
+    }
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  for (int r = warp; r < R; r += nw) {
+    float acc = 0.f;
+    for (int k = lane; k < D; k += 32) acc = fmaf(W[(size_t)r * D + k], g[k], acc);
+    acc = warp_sum(acc);
+    if (lane == 0) film[(size_t)step * R + r] = acc + bias[r];
+  }
+}
+
+}  // namespace uv

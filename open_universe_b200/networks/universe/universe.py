@@ -1,0 +1,276 @@
+"""Drop-in `Universe` / `UniverseGAN` model objects (reference
+open_universe/networks/universe/universe.py:44-375, universe_gan.py:62-151).
+
+They keep the reference's constructor signature, state-dict layout, EMA handling and the
+`enhance()` keyword surface, but own no PyTorch compute: `enhance()` compiles the weights
+into a packed blob + op program (weights.py, program.py) and replays one CUDA graph of
+hand-written sm_100a kernels through the C ABI (_native.py).
+"""
+import itertools
+import logging
+import math
+from typing import Optional
+
+import torch
+
+from ... import _native, program, weights
+from ...config import AttrDict, instantiate, to_attr
+from ...ema import ExponentialMovingAverage
+from .layers import SignalDecouplingP
+
+log = logging.getLogger(__name__)
+
+
+class Universe(torch.nn.Module):
+    def __init__(self, fs, normalization_norm, score_model, condition_model, diffusion, losses=None, training=None,
+                 validation=None, optimizer=None, scheduler=None, grad_clipper=None, transform=None,
+                 normalization_kwargs={}, with_noise_target=False, detach_cond=False, edm=None):
+        super().__init__()
+        self.fs = fs
+        self.normalization_norm = normalization_norm
+        self.normalization_kwargs = to_attr(dict(normalization_kwargs or {}))
+        self.with_noise_target = with_noise_target
+        self.detach_cond = detach_cond
+        self.opt_kwargs, self.schedule_kwargs, self.grad_clip_kwargs = optimizer, scheduler, grad_clipper
+        self.diff_kwargs = to_attr(dict(diffusion))
+        self.losses_kwargs = to_attr(losses or {})
+        self.val_kwargs = to_attr(validation or {})
+        self.train_kwargs = to_attr(training or {})
+        if transform is not None:
+            raise NotImplementedError("`transform` (STFT-domain models) is outside the supported enhance() path")
+        score_model, condition_model = to_attr(dict(score_model)), to_attr(dict(condition_model))
+        self._score_cfg, self._cond_cfg = score_model, condition_model
+        if edm is not None:
+            self.edm_kwargs = to_attr(dict(edm))
+            self._edm_model = instantiate(score_model)
+            self.with_edm = True
+        else:
+            self.edm_kwargs = None
+            self.score_model = instantiate(score_model)
+            self.with_edm = False
+        self.condition_model = instantiate(condition_model)
+        self.n_channels = score_model.get("n_channels", 32)
+        rate_factors = score_model.get("rate_factors", [2, 4, 4, 5])
+        self.n_stages = len(rate_factors)
+        self.latent_n_channels = 2**self.n_stages * self.n_channels
+        self.tot_ds = math.prod(int(r) for r in rate_factors)
+        self.init_losses(score_model, condition_model, self.losses_kwargs, self.train_kwargs)
+
+        self.ema_decay = float(self.train_kwargs.get("ema_decay", 0.0) or 0.0)
+        self._error_loading_ema = False
+        self.ema = ExponentialMovingAverage(self.model_parameters(), decay=self.ema_decay) if self.ema_decay > 0.0 else None
+
+        self._packed = None      # weights.PackedModel
+        self._native_model = None
+        self._plans = {}
+        self.use_cuda_graph = True
+
+    # ------------------------------------------------------------------ reference API surface
+    def init_losses(self, score_model, condition_model, losses, training):
+        """Training losses (MDN heads, reference universe.py:138-168) are not part of inference;
+        their checkpoint keys (loss_*) are ignored by load_state_dict below."""
+
+    def get_score_model(self):
+        return self._edm_model if self.with_edm else self.score_model
+
+    def model_parameters(self):
+        return itertools.chain(self.get_score_model().parameters(), self.condition_model.parameters())
+
+    def model_config(self):
+        """The resolved `model` config node this object was built from (what the compiler needs)."""
+        cfg = dict(fs=self.fs, normalization_norm=self.normalization_norm, normalization_kwargs=dict(self.normalization_kwargs),
+                   score_model=dict(self._score_cfg), condition_model=dict(self._cond_cfg), diffusion=dict(self.diff_kwargs))
+        if self.with_edm:
+            cfg["edm"] = dict(self.edm_kwargs)
+        return cfg
+
+    def load_state_dict(self, state_dict, strict=True, assign=False):
+        # training-only sub-modules of the reference (MDN / GAN losses) are not instantiated here
+        sd = {k: v for k, v in state_dict.items() if not k.startswith("loss_")}
+        self._invalidate()
+        return super().load_state_dict(sd, strict=strict, assign=assign)
+
+    def train(self, mode=True, no_ema=False):
+        """Same EMA protocol as the reference (universe.py:841-862): eval() swaps the EMA shadow
+        parameters in, train() restores the raw ones."""
+        res = super().train(mode)
+        if getattr(self, "ema", None) is None:
+            return res
+        if not self._error_loading_ema:
+            if mode is False and not no_ema:
+                self.ema.store(self.model_parameters())
+                self.ema.copy_to(self.model_parameters())
+            elif self.ema.collected_params is not None:
+                self.ema.restore(self.model_parameters())
+        self._invalidate()
+        return res
+
+    def eval(self, no_ema=False):
+        return self.train(False, no_ema=no_ema)
+
+    def to(self, *args, **kwargs):
+        if getattr(self, "ema", None) is not None:
+            self.ema.to(*args, **kwargs)
+        self._invalidate()
+        return super().to(*args, **kwargs)
+
+    def aux_to_wav(self, y_aux):
+        return y_aux
+
+    def pad(self, x, pad=None):
+        if pad is None:
+            pad = self.tot_ds - x.shape[-1] % self.tot_ds
+        return torch.nn.functional.pad(x, (pad // 2, pad - pad // 2)), pad
+
+    def unpad(self, x, pad):
+        return x[..., pad // 2 : -(pad - pad // 2)]
+
+    def forward(self, xt, sigma, cond):
+        raise RuntimeError("Universe has no PyTorch forward in open_universe_b200: use enhance()")
+
+    # ------------------------------------------------------------------ native plumbing
+    def _invalidate(self):
+        for p in getattr(self, "_plans", {}).values():
+            p.close()
+        self._plans = {}
+        if getattr(self, "_native_model", None) is not None:
+            self._native_model.close()
+        self._native_model = None
+        self._packed = None
+
+    def _device(self):
+        return next(self.parameters()).device
+
+    def _get_plan(self, B, T, n_steps):
+        dev = self._device()
+        if dev.type != "cuda":
+            raise RuntimeError(
+                "open_universe_b200 runs only on a CUDA sm_100 (B200) device; the model is on "
+                f"'{dev}'. There is no CPU / PyTorch fallback: move it with model.to('cuda')."
+            )
+        if self._packed is None:
+            sd = {k: v.detach().float().cpu() for k, v in self.state_dict().items()}
+            self._packed = weights.pack_model(sd, self.model_config())
+            self._native_model = _native.NativeModel(self._packed.blob.bytes(), dev.index or 0)
+        key = (B, T, n_steps)
+        if key not in self._plans:
+            pg = program.build_program(self._packed, self.model_config(), B, T, n_steps)
+            self._plans[key] = _native.NativePlan(self._native_model, pg, use_graph=self.use_cuda_graph)
+        return self._plans[key]
+
+    # ------------------------------------------------------------------ enhance (reference universe.py:231-375)
+    def enhance(
+        self,
+        mix,
+        n_steps: Optional[int] = None,
+        epsilon: Optional[float] = None,
+        target: Optional[torch.Tensor] = None,
+        fake_score_snr: Optional[float] = None,
+        rng: Optional[torch.Generator] = None,
+        use_aux_signal: Optional[bool] = False,
+        keep_rms: Optional[bool] = False,
+        ensemble: Optional[int] = None,
+        ensemble_stat: Optional[str] = "median",
+        warm_start: Optional[int] = None,
+    ) -> torch.Tensor:
+        out = self._enhance_impl(mix, n_steps, epsilon, target, fake_score_snr, rng, use_aux_signal, keep_rms,
+                                 ensemble, ensemble_stat, warm_start, noise=None, return_steps=False)
+        return out
+
+    def enhance_debug(self, mix, noise, n_steps=None, epsilon=None, keep_rms=False):
+        """Parity entry point: runs enhance() with an injected noise sequence `noise`
+        ([n_steps, B, Lp] on the model device) and also returns the per-step network outputs."""
+        return self._enhance_impl(mix, n_steps, epsilon, None, None, None, False, keep_rms, None, "median", None,
+                                  noise=noise, return_steps=True)
+
+    def _enhance_impl(self, mix, n_steps, epsilon, target, fake_score_snr, rng, use_aux_signal, keep_rms, ensemble,
+                      ensemble_stat, warm_start, noise, return_steps):
+        if epsilon is None:
+            epsilon = self.diff_kwargs.epsilon
+        if n_steps is None:
+            n_steps = self.diff_kwargs.n_steps
+        n_steps, epsilon = int(n_steps), float(epsilon)
+        x_ndim = mix.ndim
+        if x_ndim == 1:
+            mix = mix[None, None, :]
+        elif x_ndim == 2:
+            mix = mix[:, None, :]
+        elif x_ndim > 3:
+            raise ValueError("The input should have at most 3 dimensions")
+        if mix.shape[1] != 1:
+            raise ValueError("open_universe_b200 supports single-channel conditioners (input_channels == 1)")
+        if ensemble_stat not in ("mean", "median", "signal_median"):
+            raise NotImplementedError()
+        if target is not None or fake_score_snr is not None:
+            raise NotImplementedError("the `target` / `fake_score_snr` sampler test hook is not implemented natively yet")
+        if use_aux_signal or warm_start is not None:
+            raise NotImplementedError("`use_aux_signal` / `warm_start` (signal decoupling layer) are not implemented natively yet")
+        if ensemble_stat == "signal_median" and ensemble is not None:
+            raise NotImplementedError("ensemble_stat='signal_median' is not implemented yet")
+        if self.normalization_norm not in (2, "2"):
+            raise NotImplementedError("only normalization_norm == 2 is supported")
+        if self.diff_kwargs.get("schedule", "geometric") != "geometric":
+            raise NotImplementedError()
+        if n_steps < 2:
+            raise ValueError("n_steps must be at least 2")
+
+        if ensemble is not None:
+            mix_shape = mix.shape
+            mix = torch.stack([mix] * ensemble, dim=0).view((-1,) + mix_shape[1:])
+
+        B, T = mix.shape[0], mix.shape[-1]
+        plan = self._get_plan(B, T, n_steps)
+        dev = self._device()
+        Lp = plan.pg.Lp
+        mix_f = mix.reshape(B, T).to(device=dev, dtype=torch.float32).contiguous()
+        if noise is None:
+            # same draws, same order as the reference (universe.py:39-41,326,338): n_steps tensors of (B,1,Lp)
+            noise = torch.empty((n_steps, B, Lp), dtype=torch.float32, device=dev)
+            for i in range(n_steps):
+                noise[i] = torch.randn((B, 1, Lp), dtype=torch.float32, device=dev, generator=rng)[:, 0, :]
+        else:
+            noise = noise.to(device=dev, dtype=torch.float32).reshape(n_steps, B, Lp).contiguous()
+        out = torch.empty((B, T), dtype=torch.float32, device=dev)
+        dbg = torch.empty((n_steps, B, Lp), dtype=torch.float32, device=dev) if return_steps else None
+        coefs = program.step_coefs(self.model_config(), n_steps, epsilon)
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        with torch.cuda.device(dev):
+            plan.enhance(mix_f.data_ptr(), noise.data_ptr(), out.data_ptr(), dbg.data_ptr() if dbg is not None else None,
+                         coefs, bool(keep_rms), stream)
+        x = out.to(mix.dtype)[:, None, :]
+
+        if ensemble is not None:
+            x = x.view((-1,) + mix_shape)
+            x = x.mean(dim=0) if ensemble_stat == "mean" else x.median(dim=0).values
+        if x_ndim == 1:
+            x = x[0, 0]
+        elif x_ndim == 2:
+            x = x[:, 0, :]
+        if return_steps:
+            return x, dbg
+        return x
+
+
+class UniverseGAN(Universe):
+    """UNIVERSE++ (reference universe_gan.py:62-151): for inference it only adds the
+    `signal_decoupling_layer` parameters (used by use_aux_signal / warm_start) to the state dict
+    and to the EMA parameter list."""
+
+    def __init__(self, fs, normalization_norm, score_model, condition_model, diffusion, losses=None, training=None,
+                 validation=None, optimizer=None, scheduler=None, grad_clipper=None, transform=None,
+                 normalization_kwargs={}, detach_cond=False, edm=None):
+        super().__init__(fs, normalization_norm, score_model, condition_model, diffusion, losses, training, validation,
+                         optimizer, scheduler, grad_clipper, transform=transform, normalization_kwargs=normalization_kwargs,
+                         detach_cond=detach_cond, edm=edm)
+
+    def init_losses(self, score_model, condition_model, losses, training):
+        if losses.get("use_signal_decoupling", False):
+            self.signal_decoupling_layer = SignalDecouplingP(self.n_channels, losses.get("signal_decoupling_act", None))
+        else:
+            self.signal_decoupling_layer = None
+
+    def model_parameters(self):
+        params = itertools.chain(self.get_score_model().parameters(), self.condition_model.parameters())
+        if getattr(self, "signal_decoupling_layer", None) is not None:
+            params = itertools.chain(params, self.signal_decoupling_layer.parameters())
+        return params

@@ -1,0 +1,90 @@
+"""Weight folding / packing algebra (open_universe_b200/weights.py) against torch.nn.functional."""
+import math
+
+import torch
+import torch.nn.functional as F
+
+from open_universe_b200 import weights
+from open_universe_b200.networks.universe.layers import LowPass
+
+
+def _apply_w4(x, w4, smin, up=1):
+    """Reference evaluation of the multi-tap GEMM on x [B, C, L] with sources = phases of x."""
+    n, s, q, ci = w4.shape
+    B, C, L = x.shape
+    M = L // s
+    xs = x.view(B, C, M, s)  # phase t = l % s
+    out = torch.zeros(B, n, M)
+    for t in range(s):
+        xp = F.pad(xs[..., t], (8, 8))
+        for j in range(q):
+            sh = smin + j
+            out += torch.einsum("nc,bcm->bnm", w4[:, t, j, :], xp[:, :, 8 + sh : 8 + sh + M])
+    if up > 1:
+        co = n // up
+        out = out.view(B, up, co, M).permute(0, 2, 3, 1).reshape(B, co, M * up)
+    return out
+
+
+def test_plain_conv():
+    torch.manual_seed(0)
+    w, x = torch.randn(24, 16, 5), torch.randn(2, 16, 50)
+    w4, smin = weights.w4_plain(w)
+    assert torch.allclose(_apply_w4(x, w4, smin), F.conv1d(x, w, padding="same"), atol=1e-4)
+
+
+def test_down_conv_with_and_without_antialias():
+    torch.manual_seed(1)
+    for r in (2, 4, 5):
+        w, x = torch.randn(32, 16, r), torch.randn(2, 16, 20 * r)
+        w4, smin = weights.w4_down(w)
+        assert torch.allclose(_apply_w4(x, w4, smin), F.conv1d(x, w, stride=r), atol=1e-4)
+        lp = LowPass(2 * r + 1).weights
+        ref = F.conv1d(F.conv1d(x, lp[None, None].expand(16, 1, -1), padding="same", groups=16), w, stride=r)
+        w4, smin = weights.w4_down(w, lp)
+        assert torch.allclose(_apply_w4(x, w4, smin), ref, atol=1e-4)
+
+
+def test_up_conv_with_and_without_antialias():
+    torch.manual_seed(2)
+    for r in (2, 3, 5, 8):
+        w, x = torch.randn(32, 16, r), torch.randn(2, 32, 20)
+        w4, smin = weights.w4_up(w)
+        assert torch.allclose(_apply_w4(x, w4, smin, up=r), F.conv_transpose1d(x, w, stride=r), atol=1e-4)
+        lp = LowPass(2 * r + 1).weights
+        y = F.conv_transpose1d(x, w, stride=r)
+        ref = F.conv1d(y, lp[None, None].expand(16, 1, -1), padding="same", groups=16)
+        w4, smin = weights.w4_up(w, lp)
+        assert torch.allclose(_apply_w4(x, w4, smin, up=r), ref, atol=1e-4)
+
+
+def test_pack_unpack_roundtrip():
+    torch.manual_seed(3)
+    w4 = torch.randn(512, 2, 3, 128).to(torch.bfloat16).float()
+    bits = weights.pack_w4(w4, 64, 256)
+    assert torch.equal(weights.unpack_w4(bits.reshape(-1), 512, 2, 3, 128, 64, 256), w4)
+
+
+def test_tile_choices():
+    for c in (32, 48, 64, 80, 96, 128, 192, 256, 384, 512, 768):
+        kc = weights.pick_kc(c)
+        assert c % kc == 0 and kc % 16 == 0
+    for c in (32, 48, 64, 96, 128, 192, 256, 384, 512, 768, 1536, 2304):
+        n = weights.pick_ntile(c)
+        assert c % n == 0 and n % 16 == 0 and n <= 256
+
+
+def test_binomial_taps_closed_form():
+    # SURVEY.md appendix A
+    assert torch.allclose(LowPass(5).weights, torch.tensor([0.267261, 1.069045, 1.603567, 1.069045, 0.267261]), atol=1e-5)
+    assert abs(LowPass(17).weights[8].item() - 2.164396) < 1e-5
+
+
+def test_dft_basis_matches_rfft():
+    torch.manual_seed(4)
+    win = torch.hann_window(64, periodic=True)
+    basis, nb, nbp = weights.dft_basis(win, 64)
+    x = torch.randn(5, 64)
+    ri = x @ basis
+    ref = torch.fft.rfft(x * win)
+    assert torch.allclose(ri[:, :nb], ref.real, atol=1e-4) and torch.allclose(ri[:, nbp : nbp + nb], -ref.imag, atol=1e-4)
