@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define UV_ABI_VERSION 3
+#define UV_ABI_VERSION 4
 
 typedef enum {
   UV_OK = 0,
@@ -139,6 +139,11 @@ int uv_run_ops(uv_plan* p, int first, int last, const float* mix, const float* n
                float* dbg_net, const uv_step_coef* coef, int keep_rms, void* stream);
 int uv_arena_read(uv_plan* p, size_t off, void* host_dst, size_t nbytes);
 int uv_arena_write(uv_plan* p, size_t off, const void* host_src, size_t nbytes);
+
+/* Measurement: runs the program eagerly with a cudaEvent pair around every launch (on `stream`)
+ * and returns the device time of each op in ms_per_op[n_ops] (0 for plan-time setup ops).  */
+int uv_profile_ops(uv_plan* p, const float* mix, const float* noise, float* out, float* dbg_net,
+                   const uv_step_coef* coef, int keep_rms, void* stream, float* ms_per_op);
 
 /* Number of kernel launches one uv_enhance() replays (for bench accounting). */
 int uv_plan_num_launches(const uv_plan* p);

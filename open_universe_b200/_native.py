@@ -18,7 +18,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 EXPORTS = [
     "uv_abi_version", "uv_sizeof_op", "uv_last_error", "uv_model_create", "uv_model_destroy", "uv_plan_create",
     "uv_plan_destroy", "uv_plan_arena_bytes", "uv_enhance", "uv_run_ops", "uv_arena_read", "uv_arena_write",
-    "uv_plan_num_launches",
+    "uv_plan_num_launches", "uv_profile_ops",
 ]
 
 
@@ -76,6 +76,7 @@ def lib():
     io = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(_abi.UvStepCoef), C.c_int, C.c_void_p]
     L.uv_enhance.argtypes = [C.c_void_p] + io
     L.uv_run_ops.argtypes = [C.c_void_p, C.c_int, C.c_int] + io
+    L.uv_profile_ops.argtypes = [C.c_void_p] + io + [C.POINTER(C.c_float)]
     L.uv_arena_read.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
     L.uv_arena_write.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
     if L.uv_abi_version() != _abi.UV_ABI_VERSION:
@@ -139,6 +140,13 @@ class NativePlan:
     def run_ops(self, first, last, mix_ptr, noise_ptr, out_ptr, dbg_ptr, coefs, keep_rms, stream_ptr):
         _check(lib().uv_run_ops(self.handle, first, last, mix_ptr, noise_ptr, out_ptr, dbg_ptr, self._coefs(coefs),
                                 1 if keep_rms else 0, stream_ptr), "uv_run_ops")
+
+    def profile_ops(self, mix_ptr, noise_ptr, out_ptr, dbg_ptr, coefs, keep_rms, stream_ptr):
+        """Per-op device times (ms) of one eager pass, measured with CUDA events."""
+        ms = (C.c_float * len(self.pg.ops))()
+        _check(lib().uv_profile_ops(self.handle, mix_ptr, noise_ptr, out_ptr, dbg_ptr, self._coefs(coefs),
+                                    1 if keep_rms else 0, stream_ptr, ms), "uv_profile_ops")
+        return list(ms)
 
     def arena_read(self, off, nbytes):
         buf = C.create_string_buffer(nbytes)

@@ -340,6 +340,31 @@ extern "C" int uv_run_ops(uv_plan* p, int first, int last, const float* mix, con
   return check_err_flag(p);
 }
 
+extern "C" int uv_profile_ops(uv_plan* p, const float* mix, const float* noise, float* out, float* dbg_net,
+                              const uv_step_coef* coef, int keep_rms, void* stream, float* ms_per_op) {
+  if (!p || !ms_per_op) return fail(UV_ERR_INVALID, "uv_profile_ops: null argument");
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  CUDA_TRY(cudaSetDevice(p->model->device));
+  int rc = stage_io(p, mix, noise, out, dbg_net, coef, keep_rms, s);
+  if (rc) return rc;
+  const int n = (int)p->ops.size();
+  std::vector<cudaEvent_t> ev(2 * n);
+  for (auto& e : ev) CUDA_TRY(cudaEventCreate(&e));
+  for (int i = 0; i < n; ++i) {
+    if (p->ops[i].step == -2) continue;
+    CUDA_TRY(cudaEventRecord(ev[2 * i], s));
+    if ((rc = launch_op(p, p->ops[i], s))) return rc;
+    CUDA_TRY(cudaEventRecord(ev[2 * i + 1], s));
+  }
+  CUDA_TRY(cudaStreamSynchronize(s));
+  for (int i = 0; i < n; ++i) {
+    ms_per_op[i] = 0.f;
+    if (p->ops[i].step != -2) CUDA_TRY(cudaEventElapsedTime(&ms_per_op[i], ev[2 * i], ev[2 * i + 1]));
+  }
+  for (auto& e : ev) cudaEventDestroy(e);
+  return check_err_flag(p);
+}
+
 extern "C" int uv_arena_read(uv_plan* p, size_t off, void* host_dst, size_t nbytes) {
   if (!p || off + nbytes > p->arena_bytes) return fail(UV_ERR_INVALID, "uv_arena_read: out of range");
   CUDA_TRY(cudaSetDevice(p->model->device));

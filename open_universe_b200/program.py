@@ -425,3 +425,51 @@ def build_program(pm, cfg, B, T, n_steps):
     pg.emit(op, "post")
     pg.arena = _ru(pg.arena, 1024)
     return pg
+
+
+def algorithmic_flops(cfg, Lp, n_steps):
+    """Dense-layer work of one utterance in the REFERENCE's formulation (2*Co*Ci*k*L_out per conv,
+    no credit for the wider anti-alias-folded kernels).  Returns a dict with the
+    conditioner total, the per-step score-network total, and the share executed by the tensor-core
+    GEMM kernel (everything except the GRU recurrence and the 1<->C edge convs)."""
+    sc, cc = cfg["score_model"], cfg["condition_model"]
+    rates = [int(r) for r in sc["rate_factors"]]
+    c0 = int(sc["n_channels"])
+    nlev = len(rates)
+    extra = bool(sc.get("extra_conv_block", False))
+    chans = [c0 * 2**i for i in range(nlev + 1)]
+    lens = [Lp // math.prod(rates[:i]) for i in range(nlev + 1)]
+    Cb, Fr, H = chans[nlev], lens[nlev], chans[nlev] // 2
+
+    def block(C, L):
+        return 2 * C * C * (5 + 3 + 3) * L
+
+    def rc(C, L):  # rate change between (C @ L) and (2C @ L/r)
+        return 4 * C * C * L
+
+    gru_ih = 2 * Cb * 3 * H * 2 * Fr
+    gru_hh = 2 * H * 3 * H * 2 * Fr
+    edge = 2 * 3 * c0 * Lp  # 1 -> C or C -> 1, k = 3
+    # score network, one evaluation
+    s_gemm = 0
+    for i in range(nlev):
+        s_gemm += 2 * (block(chans[i], lens[i]) + rc(chans[i], lens[i]))  # encoder + decoder block at this level
+        s_gemm += 2 * chans[i] * chans[i] * lens[i]                      # signal_cond_proj 1x1
+    if extra:
+        s_gemm += 2 * block(Cb, Fr) + 2 * Cb * Cb * Fr
+    s_gemm += gru_ih
+    score = s_gemm + gru_hh + 2 * edge
+    # conditioner
+    n_mels = int(cc.get("n_mels", 80))
+    c_gemm = 2 * n_mels * Cb * 3 * Fr + block(Cb, Fr)                    # mel conv + mel ConvBlock
+    for i in range(nlev):
+        c_gemm += 2 * (block(chans[i], lens[i]) + rc(chans[i], lens[i]))
+        if i < nlev - 1:
+            c_gemm += 2 * chans[i] * Cb * lens[i]                        # st_conv
+    n_bottleneck = 3 + (2 if extra else 0)                               # conv_block1/2, decoder input (+ extra enc/dec)
+    c_gemm += n_bottleneck * block(Cb, Fr)
+    c_gemm += 2 * gru_ih
+    cond = c_gemm + 2 * gru_hh + edge
+    # the hoisted 1x1 projections run once, not per step; algorithmic count keeps the reference's per-step figure
+    return dict(cond=cond, score=score, total=cond + n_steps * score, gemm=c_gemm + n_steps * s_gemm,
+                gru_hh=(2 + n_steps) * gru_hh)

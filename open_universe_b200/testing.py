@@ -41,6 +41,12 @@ def seed_weights(model, seed=0):
         for name, b in model.named_buffers():
             if name.endswith("sigma_block.freq"):
                 b.copy_((16 * torch.randn(tuple(b.shape), generator=g)).to(b.device, b.dtype))
+    # keep the EMA shadow (what eval() swaps in, reference universe.py:841-862) in sync
+    if getattr(model, "ema", None) is not None:
+        model.ema.shadow_params = [p.detach().clone() for p in model.model_parameters()]
+        model.ema.collected_params = None
+    if hasattr(model, "_invalidate"):
+        model._invalidate()
     return model
 
 
