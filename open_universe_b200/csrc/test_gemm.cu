@@ -241,10 +241,11 @@ static int run_case(const Case& c, int swap_lbo, int num_sms) {
 
 // Throughput of layer-shaped problems (cfg 2 sizes: B=64, 4 s clips).
 static void run_perf(int num_sms) {
-  struct PC { const char* name; int B, Lv, C, k; } pcs[] = {
-      {"L0 C32 k5", 64, 64160, 32, 5}, {"L0 C32 k3", 64, 64160, 32, 3}, {"L1 C64 k5", 64, 32080, 64, 5},
-      {"L2 C128 k5", 64, 8020, 128, 5}, {"L3 C256 k5", 64, 2005, 256, 5}, {"L4 C512 k5", 64, 401, 512, 5},
-      {"L4 C512 k3", 64, 401, 512, 3}};
+  struct PC { const char* name; int B, Lv, C, k, add; } pcs[] = {
+      {"L0 C32 k5", 64, 64160, 32, 5, 0}, {"L0 C32 k3", 64, 64160, 32, 3, 0}, {"L0 C32 k3 +add", 64, 64160, 32, 3, 1},
+      {"L1 C64 k5", 64, 32080, 64, 5, 0}, {"L1 C64 k3 +add", 64, 32080, 64, 3, 1},
+      {"L2 C128 k5", 64, 8020, 128, 5, 0}, {"L2 C128 k3 +add", 64, 8020, 128, 3, 1}, {"L3 C256 k5", 64, 2005, 256, 5, 0},
+      {"L4 C512 k5", 64, 401, 512, 5, 0}, {"L4 C512 k3", 64, 401, 512, 3, 0}};
   for (auto& pc : pcs) {
     HT A = make_tensor(pc.B, pc.Lv, pc.C, 1, 2, false);
     CK(cudaMemset(A.dev, 0x3c, A.data.size()));  // small finite bf16 values everywhere
@@ -263,6 +264,8 @@ static void run_perf(int num_sms) {
     p.m_rows = pc.B * A.Lh; p.Lh_A = A.Lh; p.M_valid = pc.Lv; p.up = 1; p.C_out = pc.C;
     p.scale = 1.f; p.n_out = 2;
     p.out[0].t = desc_of(O); p.out[1].t = desc_of(O2); p.out[1].act = 1; p.out[1].a1 = 0.25f;
+    HT AD = make_tensor(pc.B, pc.Lv, pc.C, 1, 2, false);
+    if (pc.add) p.add1 = desc_of(AD);
     int* d_err; CK(cudaMalloc(&d_err, 4)); CK(cudaMemset(d_err, 0, 4));
     p.err_flag = d_err;
     cudaEvent_t e0, e1;
@@ -276,9 +279,9 @@ static void run_perf(int num_sms) {
     CK(cudaDeviceSynchronize());
     float ms; CK(cudaEventElapsedTime(&ms, e0, e1)); ms /= iters;
     double flop = 2.0 * pc.B * pc.Lv * (double)pc.C * pc.C * pc.k;
-    double bytes = (double)pc.B * pc.Lv * pc.C * 2 * 3;
-    printf("[perf %s] %.3f ms  %.1f TFLOP/s  %.0f GB/s (1 read + 2 writes)\n", pc.name, ms, flop / ms * 1e-9, bytes / ms * 1e-6);
-    cudaFree(A.dev); cudaFree(O.dev); cudaFree(O2.dev); cudaFree(d_w); cudaFree(d_err);
+    double bytes = (double)pc.B * pc.Lv * pc.C * 2 * (3 + pc.add);
+    printf("[perf %s] %.3f ms  %.1f TFLOP/s  %.0f GB/s (reads + 2 writes)\n", pc.name, ms, flop / ms * 1e-9, bytes / ms * 1e-6);
+    cudaFree(AD.dev); cudaFree(A.dev); cudaFree(O.dev); cudaFree(O2.dev); cudaFree(d_w); cudaFree(d_err);
   }
 }
 

@@ -70,6 +70,8 @@ struct GemmParams {
   // ---- pipeline (filled by host)
   int na_stages, nb_stages;
   int a_stage_bytes, b_stage_bytes;
+  int b_resident;    // 1: all weight images of the (single) N tile stay in smem for the whole kernel
+  int n_acc;         // TMEM accumulator stages (2 or 4)
   int dbg_swap_lbo;  // test hook: swap LBO/SBO roles in the smem descriptors
   int* err_flag;     // set on watchdog timeout
 };
