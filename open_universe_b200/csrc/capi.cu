@@ -66,7 +66,7 @@ extern "C" int uv_model_create(uv_model** out, const void* weights, size_t nbyte
   m->device = device;
   m->nbytes = nbytes;
   m->num_sms = prop.multiProcessorCount;
-  CUDA_TRY(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  CUDA_TRY(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemBudget));
   CUDA_TRY(cudaFuncSetAttribute(gru_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gru_smem_bytes(kGruMaxH)));
   CUDA_TRY(cudaMalloc(&m->blob, nbytes));
   CUDA_TRY(cudaMemcpy(m->blob, weights, nbytes, cudaMemcpyHostToDevice));
@@ -124,7 +124,7 @@ static int launch_op(uv_plan* p, const uv_op& op, cudaStream_t s) {
       g.N_TILE = op.N_TILE; g.n_tiles_n = op.N_total / op.N_TILE;
       g.m_rows = op.m_rows; g.Lh_A = op.Lh_A; g.M_valid = op.M_valid;
       g.up = op.up; g.C_out = op.C_out;
-      g.bias = wptr<const float>(p, op.bias_w);
+      g.has_bias = op.bias_w >= 0 ? 1 : 0;
       g.film = aptr<const float>(p, op.film);
       g.add1 = to_desc(p, op.add1); g.add2 = to_desc(p, op.add2);
       g.scale = op.scale; g.n_out = op.n_out;
@@ -213,7 +213,7 @@ static int validate_ops(uv_plan* p) {
       if (op.a.off < 0 || op.KC % 16 || op.N_TILE % 16 || op.N_TILE > 256 || op.N_total % op.N_TILE ||
           (op.a.nch * 8) % op.KC || op.C_out % op.N_TILE || op.smin < -kGuard || op.smax > kGuard || op.a.split != op.n_src)
         return fail(UV_ERR_INVALID, "malformed GEMM op #" + std::to_string(i));
-      if (op.a.P < op.a.G + ((op.m_rows + 127) / 128) * 128 + op.smax)
+      if (op.a.P < op.a.G + ((op.m_rows + kTileM - 1) / kTileM) * kTileM + op.smax)
         return fail(UV_ERR_INVALID, "GEMM A plane too short, op #" + std::to_string(i));
     }
   }

@@ -1,6 +1,6 @@
 // Multi-tap implicit-GEMM conv1d on the sm_100a tensor cores (tcgen05 + TMEM).
 //
-//   D[row, n] = sum_{src s} sum_{shift q} sum_{c}  A_s[row + q, c] * W[s][q][n][c]
+//   D[row, n] = bias[n] + sum_{src s} sum_{shift q} sum_{c}  A_s[row + q, c] * W[s][q][n][c]
 //
 // covers every dense layer of the reference's ConvBlock
 // (open_universe/networks/universe/blocks.py:331-416): "same" k=3/5 convs
@@ -9,32 +9,43 @@
 // source, N = r phases x C_out; blocks.py:223-225 folded), the conditioner's
 // st_convs (condition.py:53-59) and the GRU input projection.
 //
-// A tiles are halo'd [KC/8][128 + smax - smin][8] bf16 slabs fetched with 1-D
-// bulk async copies straight out of the planes layout (uv_common.cuh); that is
-// the canonical no-swizzle K-major UMMA layout, in which a tap shift is
-// +16 bytes on the descriptor start address, so one slab serves all taps.
-// Weight tiles are pre-packed images [KC/8][N_TILE][8].
+// Tile = 256 rows x N_TILE columns, issued as two M=128 UMMAs per K step that share
+// every weight image (halves the L2->smem weight traffic per FLOP; the 8 epilogue
+// warps split into one group per 128-row half).  A tiles are halo'd
+// [KC/8][256 + smax - smin][8] bf16 slabs fetched with 1-D bulk async copies straight
+// out of the planes layout (uv_common.cuh); that is the canonical no-swizzle K-major
+// UMMA layout, in which a tap shift is +16 bytes on the descriptor start address, so
+// one slab serves all taps.  Weight tiles are pre-packed images [KC/8][N_TILE][8].
+// The bias enters through the tensor core as well: a constant "ones" A tile times a
+// [hi | lo] bf16 split of the fp32 bias initialises the accumulator, so the epilogue
+// carries no per-column bias loads.
 //
-// Warp roles (320 threads): warp0 = bulk-copy producer, warp1 = MMA issuer and
-// TMEM owner, warps 2-9 = two epilogue groups that take alternate tiles (TMEM ->
-// registers -> fused bias / add / FiLM / PReLU -> coalesced 16-byte stores into up
-// to three planes tensors; the add operands of the next 16-column group are
-// prefetched while the current one is processed).  Up to four accumulator stages
-// live in TMEM so the MMAs run ahead of the epilogues.  Small layers keep their
-// whole weight set resident in shared memory and give the rest to a deep A ring
-// (the memory latency of these HBM-bound layers needs many tiles in flight).
-// Persistent grid, static round-robin tile schedule.
+// Warp roles (320 threads): warp0 = bulk-copy producer, warp1 = MMA issuer and TMEM
+// owner, warps 2-9 = epilogue (TMEM -> registers -> fused add / scale / FiLM / PReLU ->
+// coalesced 16-byte stores into up to three planes tensors).  The epilogue is
+// specialised at compile time on (has adds, has FiLM, single plain output) and
+// software-pipelined: the TMEM load and the residual loads of column group g+1 are in
+// flight while group g is processed.  2-4 accumulator stages live in TMEM so the MMAs
+// run ahead of the epilogues.  Layers whose whole weight set fits keep it resident in
+// shared memory and give the rest to a deep A ring.  Persistent grid, static
+// round-robin tile schedule.
 #pragma once
 #include "uv_common.cuh"
 
 namespace uv {
 
-constexpr int kMaxAStages = 16;
+constexpr int kSubM = 128;          // UMMA M
+constexpr int kTileM = 256;         // rows per CTA tile (two UMMA sub-tiles)
+constexpr int kMaxAStages = 12;
 constexpr int kMaxBStages = 8;
 constexpr int kGemmThreads = 320;   // producer warp, MMA warp, 2 x 4 epilogue warps
 constexpr int kMaxAcc = 4;          // TMEM accumulator stages
+constexpr int kOnesBytes = 2 * kSubM * 16;   // [2 chunks][128 rows][8] bf16
+constexpr int kFilmMaxC = 768;
+constexpr int kFilmBytes = 2 * kFilmMaxC * 4;
+constexpr int kGemmSmemBudget = 227 * 1024;
 
-// TMEM columns per accumulator stage (power of two >= 32); two stages are allocated.
+// TMEM columns per accumulator (power of two >= 32).
 __host__ __device__ inline uint32_t accum_stride_cols(int n_tile) {
   uint32_t c = 32;
   while ((int)c < n_tile) c <<= 1;
@@ -80,6 +91,13 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
       "l"(src), "r"(bytes), "r"(bar)
       : "memory");
 }
+// One lane of the (converged) warp; lets ptxas see that the role body runs single-threaded, so
+// descriptors / addresses go through uniform registers without a per-lane serialisation loop.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.b32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
@@ -95,18 +113,17 @@ __device__ __forceinline__ void tc_mma_bf16(uint32_t d_tmem, uint64_t adesc, uin
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
-__device__ __forceinline__ void tc_ld16(uint32_t taddr, float* v) {
-  uint32_t r[16];
+// 32 lanes x 16 consecutive fp32 columns -> 16 registers; completes at tc_ld_wait().
+__device__ __forceinline__ void tc_ld16_issue(uint32_t taddr, uint32_t* r) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
       "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
       : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
         "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-      : "r"(taddr));
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+      : "r"(taddr)
+      : "memory");
 }
+__device__ __forceinline__ void tc_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // K-major, no-swizzle shared-memory matrix descriptor (sm_100 format, version 1).
 //   lbo: byte stride between the two 8x16B core matrices of one K=16 step
@@ -121,134 +138,247 @@ __device__ __forceinline__ uint32_t make_idesc(int M, int N) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
-// ------------------------------------------------------------------ kernel
-struct AddBuf {
-  uint4 a1[4];  // 16 columns of add1: 2 x uint4 (bf16) or 4 x uint4 (f32)
-  uint4 a2[4];
-};
+// ------------------------------------------------------------------ epilogue helpers
+// PReLU without a compare+select: for a <= 1 it is max(v, a v), otherwise min(v, a v).
+__device__ __forceinline__ float prelu_mm(float v, float a, bool le1) {
+  const float av = a * v;
+  return le1 ? fmaxf(v, av) : fminf(v, av);
+}
 
-__device__ __forceinline__ void add_prefetch(const GemmParams& P, bool valid, int b, int l_out, int chunk0, AddBuf& buf) {
-  if (!valid) return;
-  if (P.add1.base) {
-    const RowAddr r = row_addr(P.add1, b, l_out);
-    if (P.add1.esize_log2 == 1) {
-      buf.a1[0] = *reinterpret_cast<const uint4*>(r.p + (long long)chunk0 * r.pstride);
-      buf.a1[1] = *reinterpret_cast<const uint4*>(r.p + (long long)(chunk0 + 1) * r.pstride);
-    } else {
+struct ActSpec {
+  int act;
+  float a1, a2;
+  bool le1_1, le1_2;
+};
+__device__ __forceinline__ ActSpec act_spec(const OutDesc& o) {
+  ActSpec s;
+  s.act = o.act; s.a1 = o.a1; s.a2 = o.a2;
+  s.le1_1 = o.a1 <= 1.f; s.le1_2 = o.a2 <= 1.f;
+  return s;
+}
+__device__ __forceinline__ float act_apply(float v, const ActSpec& s) {
+  if (s.act >= 1) v = prelu_mm(v, s.a1, s.le1_1);
+  if (s.act == 2) v = prelu_mm(v, s.a2, s.le1_2);
+  return v;
+}
+
+// stores 16 consecutive channels (chunks chunk0, chunk0+1) of one row
+__device__ __forceinline__ void store16(const RowAddr& r, int esize_log2, int chunk0, const float* v) {
+  char* p = r.p + (long long)chunk0 * r.pstride;
+  if (esize_log2 == 1) {
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const char* p = r.p + (long long)(chunk0 + h) * r.pstride;
-        buf.a1[2 * h] = *reinterpret_cast<const uint4*>(p);
-        buf.a1[2 * h + 1] = *reinterpret_cast<const uint4*>(p + 16);
-      }
+    for (int h = 0; h < 2; ++h) {
+      uint4 u;
+      __nv_bfloat162* q = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) q[i] = __floats2bfloat162_rn(v[8 * h + 2 * i], v[8 * h + 2 * i + 1]);
+      *reinterpret_cast<uint4*>(p + h * r.pstride) = u;
     }
-  }
-  if (P.add2.base) {
-    const RowAddr r = row_addr(P.add2, b, l_out);
-    if (P.add2.esize_log2 == 1) {
-      buf.a2[0] = *reinterpret_cast<const uint4*>(r.p + (long long)chunk0 * r.pstride);
-      buf.a2[1] = *reinterpret_cast<const uint4*>(r.p + (long long)(chunk0 + 1) * r.pstride);
-    } else {
+  } else {
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const char* p = r.p + (long long)(chunk0 + h) * r.pstride;
-        buf.a2[2 * h] = *reinterpret_cast<const uint4*>(p);
-        buf.a2[2 * h + 1] = *reinterpret_cast<const uint4*>(p + 16);
-      }
+    for (int h = 0; h < 2; ++h) {
+      *reinterpret_cast<float4*>(p + h * r.pstride) = make_float4(v[8 * h], v[8 * h + 1], v[8 * h + 2], v[8 * h + 3]);
+      *reinterpret_cast<float4*>(p + h * r.pstride + 16) = make_float4(v[8 * h + 4], v[8 * h + 5], v[8 * h + 6], v[8 * h + 7]);
     }
   }
 }
 
-// adds the 8 channels of half `h` (0/1) of a prefetched 16-column group to v
-__device__ __forceinline__ void add_apply(const uint4* a, int esize_log2, int h, float* v) {
-  if (esize_log2 == 1) {
+struct AddRegs {
+  uint4 a1[2], a2[2];  // 16 bf16 columns of each residual operand
+};
+
+__device__ __forceinline__ void add_unpack(const uint4* a, float* v) {
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
     const __nv_bfloat162* q = reinterpret_cast<const __nv_bfloat162*>(&a[h]);
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       const float2 f = __bfloat1622float2(q[i]);
-      v[2 * i] += f.x;
-      v[2 * i + 1] += f.y;
+      v[8 * h + 2 * i] += f.x;
+      v[8 * h + 2 * i + 1] += f.y;
     }
-  } else {
-    const float* f = reinterpret_cast<const float*>(&a[2 * h]);
-#pragma unroll
-    for (int i = 0; i < 8; ++i) v[i] += f[i];
   }
 }
 
-struct TileCtx {
-  int b, l_out, g, n0, co0;
-  bool valid;
-};
+// Epilogue of one warp: lane = TMEM lane = output row of its 128-row half of every tile.
+template <bool ADD, bool FILM, bool MULTI>
+__device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem_base, uint64_t* t_full, uint64_t* t_empty,
+                                              const float* film_s, int warp, int lane) {
+  const int sub = (warp - 2) >> 2;
+  const int quarter = warp & 3;                 // a warp may only touch TMEM lanes 32*(warp%4)..+31
+  const int row_in_tile = sub * kSubM + quarter * 32 + lane;
+  const int ngroups = P.N_TILE >> 4;
+  const uint32_t acc_stride = accum_stride_cols(P.N_TILE);
+  const int n_acc = P.n_acc;
+  const int total_tiles = P.n_tiles_m * P.n_tiles_n;
+  const bool a1_bf16 = ADD && P.add1.esize_log2 == 1;
+  const bool a2_on = ADD && P.add2.base != nullptr;
+  const bool a2_bf16 = a2_on && P.add2.esize_log2 == 1;
+  const float scale = P.scale;
+  const bool do_scale = scale != 1.f;
+  ActSpec as0 = act_spec(P.out[0]), as1 = act_spec(P.out[1]), as2 = act_spec(P.out[2]);
 
-__device__ __forceinline__ TileCtx tile_ctx(const GemmParams& P, int tile, int row_in_tile) {
-  TileCtx c;
-  const int n_tile = tile % P.n_tiles_n;
-  const int m_tile = tile / P.n_tiles_n;
-  c.n0 = n_tile * P.N_TILE;
-  const int phase = c.n0 / P.C_out;
-  c.co0 = c.n0 - phase * P.C_out;
-  c.g = m_tile * kTileM + row_in_tile;
-  c.b = c.g / P.Lh_A;
-  const int m = c.g - c.b * P.Lh_A;
-  c.valid = (c.g < P.m_rows) && (m < P.M_valid);
-  c.l_out = P.up * m + phase;
-  return c;
-}
+  int it = 0;
+  for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+    const int n_tile = tile % P.n_tiles_n;
+    const int m_tile = tile / P.n_tiles_n;
+    const int n0 = n_tile * P.N_TILE;
+    const int phase = n0 / P.C_out;
+    const int co0 = n0 - phase * P.C_out;
+    const int g = m_tile * kTileM + row_in_tile;
+    const int b = g / P.Lh_A;
+    const int m = g - b * P.Lh_A;
+    const bool valid = (g < P.m_rows) && (m < P.M_valid);
+    const int l_out = P.up * m + phase;
+    const int chunk_base = co0 >> 3;
 
-// One 16-column group of the epilogue: TMEM -> registers -> fused math -> stores.
-__device__ __forceinline__ void epilogue_group(const GemmParams& P, const TileCtx& c, uint32_t t_addr, int c0,
-                                               const AddBuf& buf, const RowAddr* ro) {
-  float acc[16];
-  tc_ld16(t_addr + c0, acc);
-  if (!c.valid) return;
-#pragma unroll
-  for (int h = 0; h < 2; ++h) {
-    float* v = acc + 8 * h;
-    const int co = c.co0 + c0 + 8 * h;
-    const int chunk = co >> 3;
-    if (P.bias) {
-      const float4 b0 = __ldg(reinterpret_cast<const float4*>(P.bias + co));
-      const float4 b1 = __ldg(reinterpret_cast<const float4*>(P.bias + co + 4));
-      v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
-      v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
-    }
-    if (P.add1.base) add_apply(buf.a1, P.add1.esize_log2, h, v);
-    if (P.add2.base) add_apply(buf.a2, P.add2.esize_log2, h, v);
-#pragma unroll
-    for (int i = 0; i < 8; ++i) v[i] *= P.scale;
-    if (P.film) {
-      const float4 g0 = __ldg(reinterpret_cast<const float4*>(P.film + co));
-      const float4 g1 = __ldg(reinterpret_cast<const float4*>(P.film + co + 4));
-      const float4 e0 = __ldg(reinterpret_cast<const float4*>(P.film + P.C_out + co));
-      const float4 e1 = __ldg(reinterpret_cast<const float4*>(P.film + P.C_out + co + 4));
-      v[0] = fmaf(g0.x, v[0], e0.x); v[1] = fmaf(g0.y, v[1], e0.y); v[2] = fmaf(g0.z, v[2], e0.z); v[3] = fmaf(g0.w, v[3], e0.w);
-      v[4] = fmaf(g1.x, v[4], e1.x); v[5] = fmaf(g1.y, v[5], e1.y); v[6] = fmaf(g1.z, v[6], e1.z); v[7] = fmaf(g1.w, v[7], e1.w);
-    }
-    if (P.rm_out) {
-      float* dst = P.rm_out + (long long)c.g * P.rm_ld + c.n0 + c0 + 8 * h;
-      *reinterpret_cast<float4*>(dst) = make_float4(v[0], v[1], v[2], v[3]);
-      *reinterpret_cast<float4*>(dst + 4) = make_float4(v[4], v[5], v[6], v[7]);
-    }
+    RowAddr ro[3], ra1, ra2;
 #pragma unroll
     for (int o = 0; o < 3; ++o) {
-      if (ro[o].p) {
-        float w[8];
+      if (o < P.n_out && valid && (MULTI || o == 0)) ro[o] = row_addr(P.out[o].t, b, l_out);
+      else { ro[o].p = nullptr; ro[o].pstride = 0; }
+    }
+    if (ADD && valid) {
+      ra1 = row_addr(P.add1, b, l_out);
+      ra2 = row_addr(P.add2, b, l_out);
+    } else {
+      ra1.p = ra2.p = nullptr; ra1.pstride = ra2.pstride = 0;
+    }
+    float* rm_row = (MULTI && P.rm_out && valid) ? P.rm_out + (long long)g * P.rm_ld + n0 : nullptr;
+
+    const int stage = it % n_acc;
+    mbar_wait(smem_u32(&t_full[stage]), (it / n_acc) & 1, P.err_flag, 6);
+    tc_fence_after();
+    const uint32_t taddr = tmem_base + (uint32_t)(stage * 2 + sub) * acc_stride + ((uint32_t)(quarter * 32) << 16);
+
+    uint32_t r0[16], r1[16];
+    AddRegs ad0, ad1;
+
+    auto add_issue = [&](int cg, AddRegs& ad) {
+      if (!ADD) return;
+      const int ch = chunk_base + 2 * cg;
+      if (a1_bf16 && ra1.p) {
+        ad.a1[0] = *reinterpret_cast<const uint4*>(ra1.p + (long long)ch * ra1.pstride);
+        ad.a1[1] = *reinterpret_cast<const uint4*>(ra1.p + (long long)(ch + 1) * ra1.pstride);
+      }
+      if (a2_bf16 && ra2.p) {
+        ad.a2[0] = *reinterpret_cast<const uint4*>(ra2.p + (long long)ch * ra2.pstride);
+        ad.a2[1] = *reinterpret_cast<const uint4*>(ra2.p + (long long)(ch + 1) * ra2.pstride);
+      }
+    };
+
+    auto process = [&](int cg, const uint32_t* r, const AddRegs& ad) {
+      if (!valid) return;
+      float v[16];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) w[i] = apply_act(v[i], P.out[o].act, P.out[o].a1, P.out[o].a2);
-        store8(ro[o], P.out[o].t.esize_log2, chunk, w);
+      for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+      const int ch = chunk_base + 2 * cg;
+      if (ADD) {
+        if (a1_bf16) add_unpack(ad.a1, v);
+        else {
+          float t[8];
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            load8(ra1, 2, ch + h, t);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[8 * h + i] += t[i];
+          }
+        }
+        if (a2_on) {
+          if (a2_bf16) add_unpack(ad.a2, v);
+          else {
+            float t[8];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              load8(ra2, 2, ch + h, t);
+#pragma unroll
+              for (int i = 0; i < 8; ++i) v[8 * h + i] += t[i];
+            }
+          }
+        }
+      }
+      if (do_scale) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] *= scale;
+      }
+      if (FILM) {
+        const float4* ga = reinterpret_cast<const float4*>(film_s + co0 + 16 * cg);
+        const float4* be = reinterpret_cast<const float4*>(film_s + P.C_out + co0 + 16 * cg);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float4 gq = ga[i], bq = be[i];
+          v[4 * i] = fmaf(gq.x, v[4 * i], bq.x);
+          v[4 * i + 1] = fmaf(gq.y, v[4 * i + 1], bq.y);
+          v[4 * i + 2] = fmaf(gq.z, v[4 * i + 2], bq.z);
+          v[4 * i + 3] = fmaf(gq.w, v[4 * i + 3], bq.w);
+        }
+      }
+      if (!MULTI) {
+        float w[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) w[i] = act_apply(v[i], as0);
+        store16(ro[0], P.out[0].t.esize_log2, ch, w);
+      } else {
+        if (rm_row) {
+          float4* dst = reinterpret_cast<float4*>(rm_row + 16 * cg);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) dst[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        }
+#pragma unroll
+        for (int o = 0; o < 3; ++o) {
+          if (ro[o].p) {
+            const ActSpec& s = o == 0 ? as0 : (o == 1 ? as1 : as2);
+            float w[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) w[i] = act_apply(v[i], s);
+            store16(ro[o], P.out[o].t.esize_log2, ch, w);
+          }
+        }
+      }
+    };
+
+    // software pipeline: TMEM load + residual loads of group cg+1 fly while group cg is processed
+    tc_ld16_issue(taddr, r0);
+    add_issue(0, ad0);
+    for (int cg = 0; cg < ngroups; cg += 2) {
+      tc_ld_wait();
+      const bool more1 = cg + 1 < ngroups;
+      if (more1) {
+        tc_ld16_issue(taddr + 16 * (cg + 1), r1);
+        add_issue(cg + 1, ad1);
+      } else {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&t_empty[stage]));
+      }
+      process(cg, r0, ad0);
+      if (more1) {
+        tc_ld_wait();
+        const bool more2 = cg + 2 < ngroups;
+        if (more2) {
+          tc_ld16_issue(taddr + 16 * (cg + 2), r0);
+          add_issue(cg + 2, ad0);
+        } else {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(smem_u32(&t_empty[stage]));
+        }
+        process(cg + 1, r1, ad1);
       }
     }
   }
 }
 
+// ------------------------------------------------------------------ kernel
 __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_constant__ GemmParams P) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
-  // smem carve-up: A ring | B ring (or resident weight set) | barriers | tmem ptr
-  uint8_t* a_ring = smem;
+  // smem carve-up: ones tile | FiLM table | A ring | B ring (or resident weight set) | barriers | tmem ptr
+  uint8_t* ones = smem;
+  float* film_s = reinterpret_cast<float*>(smem + kOnesBytes);
+  uint8_t* a_ring = smem + kOnesBytes + kFilmBytes;
   uint8_t* b_ring = a_ring + (size_t)P.na_stages * P.a_stage_bytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(b_ring + (size_t)P.nb_stages * P.b_stage_bytes);
   uint64_t* a_full = bars;
@@ -261,15 +391,26 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
 
   const uint32_t acc_stride = accum_stride_cols(P.N_TILE);
   const int n_acc = P.n_acc;
+  const uint32_t tmem_cols = (uint32_t)n_acc * 2u * acc_stride;
   if (threadIdx.x == 0) {
-    for (int i = 0; i < P.na_stages; ++i) { mbar_init(smem_u32(&a_full[i]), 1); mbar_init(smem_u32(&a_empty[i]), 1); }
+    for (int i = 0; i < kMaxAStages; ++i) { mbar_init(smem_u32(&a_full[i]), 1); mbar_init(smem_u32(&a_empty[i]), 1); }
     for (int i = 0; i < kMaxBStages; ++i) { mbar_init(smem_u32(&b_full[i]), 1); mbar_init(smem_u32(&b_empty[i]), 1); }
-    for (int i = 0; i < kMaxAcc; ++i) { mbar_init(smem_u32(&t_full[i]), 1); mbar_init(smem_u32(&t_empty[i]), 128); }
+    for (int i = 0; i < kMaxAcc; ++i) { mbar_init(smem_u32(&t_full[i]), 1); mbar_init(smem_u32(&t_empty[i]), 8); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
+  // ones tile: K columns 0 and 1 are 1.0 (they meet the hi / lo halves of the bias image), the rest 0
+  if (threadIdx.x < 256) {
+    uint4 u = make_uint4(0u, 0u, 0u, 0u);
+    if (threadIdx.x < kSubM) u.x = 0x3F803F80u;
+    reinterpret_cast<uint4*>(ones)[threadIdx.x] = u;
+  }
+  if (P.film) {
+    for (int i = threadIdx.x; i < 2 * P.C_out; i += kGemmThreads) film_s[i] = P.film[i];
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   if (warp == 1) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr_smem)),
-                 "r"((uint32_t)n_acc * acc_stride)
+                 "r"(tmem_cols)
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
@@ -285,14 +426,16 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
   const uint32_t a_slab_chunk_bytes = (uint32_t)rows_a * 16u;
   const uint32_t a_bytes = a_slab_chunk_bytes * kc_chunks;
   const uint32_t b_bytes = (uint32_t)P.N_TILE * P.KC * 2u;
+  const uint32_t bias_bytes = P.has_bias ? (uint32_t)P.N_TILE * 32u : 0u;
   const int n_img = P.n_src * P.n_groups * n_shift;  // weight images per N tile
+  const long long w_ntile_stride = (long long)n_img * b_bytes + bias_bytes;
 
   if (warp == 0) {
     // ============================== producer
-    if (lane == 0) {
+    if (elect_one()) {
       if (P.b_resident) {
         const uint32_t fbb = smem_u32(&b_full[0]);
-        const uint32_t total = (uint32_t)n_img * b_bytes;
+        const uint32_t total = (uint32_t)w_ntile_stride;
         mbar_expect_tx(fbb, total);
         for (uint32_t off = 0; off < total; off += 32768u) {
           const uint32_t n = total - off < 32768u ? total - off : 32768u;
@@ -305,6 +448,14 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
         const int n_tile = tile % P.n_tiles_n;
         const int m_tile = tile / P.n_tiles_n;
         const long long row0 = (long long)P.a_G + (long long)m_tile * kTileM + P.smin;
+        const char* w_tile = P.w + (long long)n_tile * w_ntile_stride;
+        if (!P.b_resident && bias_bytes) {
+          mbar_wait(smem_u32(&b_empty[ib]), pb ^ 1, P.err_flag, 2);
+          const uint32_t fbb = smem_u32(&b_full[ib]);
+          mbar_expect_tx(fbb, bias_bytes);
+          bulk_g2s(smem_u32(b_ring + (size_t)ib * P.b_stage_bytes), w_tile + (long long)n_img * b_bytes, bias_bytes, fbb);
+          if (++ib == P.nb_stages) { ib = 0; pb ^= 1; }
+        }
         for (int s = 0; s < P.n_src; ++s) {
           for (int g = 0; g < P.n_groups; ++g) {
             mbar_wait(smem_u32(&a_empty[ia]), pa ^ 1, P.err_flag, 1);
@@ -322,8 +473,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
                 mbar_wait(smem_u32(&b_empty[ib]), pb ^ 1, P.err_flag, 2);
                 const uint32_t fbb = smem_u32(&b_full[ib]);
                 mbar_expect_tx(fbb, b_bytes);
-                const long long img = ((long long)n_tile * P.n_src + s) * P.n_groups * n_shift + (long long)g * n_shift + q;
-                bulk_g2s(smem_u32(b_ring + (size_t)ib * P.b_stage_bytes), P.w + img * b_bytes, b_bytes, fbb);
+                const long long img = ((long long)s * P.n_groups + g) * n_shift + q;
+                bulk_g2s(smem_u32(b_ring + (size_t)ib * P.b_stage_bytes), w_tile + img * b_bytes, b_bytes, fbb);
                 if (++ib == P.nb_stages) { ib = 0; pb ^= 1; }
               }
             }
@@ -333,14 +484,10 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
     }
   } else if (warp == 1) {
     // ============================== MMA issuer
-    if (lane == 0) {
-      const uint32_t idesc = make_idesc(kTileM, P.N_TILE);
-      uint32_t lbo_a = a_slab_chunk_bytes, sbo_a = 128;
-      uint32_t lbo_b = (uint32_t)P.N_TILE * 16u, sbo_b = 128;
-      if (P.dbg_swap_lbo) {
-        uint32_t t = lbo_a; lbo_a = sbo_a; sbo_a = t;
-        t = lbo_b; lbo_b = sbo_b; sbo_b = t;
-      }
+    if (elect_one()) {
+      const uint32_t idesc = make_idesc(kSubM, P.N_TILE);
+      const uint32_t lbo_a = a_slab_chunk_bytes, lbo_b = (uint32_t)P.N_TILE * 16u;
+      const uint64_t ones_desc = make_desc(smem_u32(ones), (uint32_t)kSubM * 16u, 128);
       if (P.b_resident) {
         mbar_wait(smem_u32(&b_full[0]), 0, P.err_flag, 7);
         tc_fence_after();
@@ -351,8 +498,27 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
         const int as = it % n_acc;
         mbar_wait(smem_u32(&t_empty[as]), ((it / n_acc) & 1) ^ 1, P.err_flag, 3);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + as * acc_stride;
+        const uint32_t d0 = tmem_base + (uint32_t)(as * 2) * acc_stride;
+        const uint32_t d1 = d0 + acc_stride;
         uint32_t accumulate = 0;
+        if (bias_bytes) {
+          uint32_t bias_addr;
+          if (P.b_resident) {
+            bias_addr = smem_u32(b_ring) + (uint32_t)n_img * b_bytes;
+          } else {
+            mbar_wait(smem_u32(&b_full[ib]), pb, P.err_flag, 5);
+            tc_fence_after();
+            bias_addr = smem_u32(b_ring + (size_t)ib * P.b_stage_bytes);
+          }
+          const uint64_t bd = make_desc(bias_addr, lbo_b, 128);
+          tc_mma_bf16(d0, ones_desc, bd, idesc, 0);
+          tc_mma_bf16(d1, ones_desc, bd, idesc, 0);
+          accumulate = 1;
+          if (!P.b_resident) {
+            tc_commit(smem_u32(&b_empty[ib]));
+            if (++ib == P.nb_stages) { ib = 0; pb ^= 1; }
+          }
+        }
         for (int s = 0; s < P.n_src; ++s) {
           for (int g = 0; g < P.n_groups; ++g) {
             mbar_wait(smem_u32(&a_full[ia]), pa, P.err_flag, 4);
@@ -368,9 +534,10 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
                 b_addr = smem_u32(b_ring + (size_t)ib * P.b_stage_bytes);
               }
               for (int kk = 0; kk < (P.KC >> 4); ++kk) {
-                const uint64_t ad = make_desc(a_addr + q * 16 + kk * 2 * a_slab_chunk_bytes, lbo_a, sbo_a);
-                const uint64_t bd = make_desc(b_addr + kk * 2 * (uint32_t)P.N_TILE * 16u, lbo_b, sbo_b);
-                tc_mma_bf16(d_tmem, ad, bd, idesc, accumulate);
+                const uint32_t a_k = a_addr + q * 16 + kk * 2 * a_slab_chunk_bytes;
+                const uint64_t bd = make_desc(b_addr + kk * 2 * lbo_b, lbo_b, 128);
+                tc_mma_bf16(d0, make_desc(a_k, lbo_a, 128), bd, idesc, accumulate);
+                tc_mma_bf16(d1, make_desc(a_k + kSubM * 16, lbo_a, 128), bd, idesc, accumulate);
                 accumulate = 1;
               }
               if (!P.b_resident) {
@@ -386,60 +553,20 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
       }
     }
   } else {
-    // ============================== epilogue: 2 groups x 4 warps, alternate tiles; TMEM lane quarter = warp % 4
-    const int egroup = (warp - 2) >> 2;
-    const int quarter = warp & 3;
-    const int row_in_tile = quarter * 32 + lane;
-    const int ngroups = P.N_TILE >> 4;
-    int it = egroup;
-    int tile = blockIdx.x + it * gridDim.x;
-    int cg = 0;
-    TileCtx cur;
-    RowAddr ro[3];
-    uint32_t t_addr = 0;
-    AddBuf bufA, bufB;
-    bool have = tile < total_tiles;
-    if (have) {
-      cur = tile_ctx(P, tile, row_in_tile);
-      add_prefetch(P, cur.valid, cur.b, cur.l_out, cur.co0 >> 3, bufA);
-    }
-    // processes the current (tile, column group) with `bc`, prefetching the next one into `bn`
-    auto step = [&](const AddBuf& bc, AddBuf& bn) -> bool {
-      int n_it = it, n_cg = cg + 1, n_tile = tile;
-      if (n_cg == ngroups) {
-        n_cg = 0;
-        n_it = it + 2;
-        n_tile = blockIdx.x + n_it * gridDim.x;
-      }
-      const bool n_have = n_tile < total_tiles;
-      TileCtx nxt = cur;
-      if (n_have) {
-        if (n_cg == 0) nxt = tile_ctx(P, n_tile, row_in_tile);
-        add_prefetch(P, nxt.valid, nxt.b, nxt.l_out, (nxt.co0 + 16 * n_cg) >> 3, bn);
-      }
-      const int as = it % n_acc;
-      if (cg == 0) {
-#pragma unroll
-        for (int o = 0; o < 3; ++o) {
-          if (o < P.n_out && cur.valid) ro[o] = row_addr(P.out[o].t, cur.b, cur.l_out);
-          else { ro[o].p = nullptr; ro[o].pstride = 0; }
-        }
-        mbar_wait(smem_u32(&t_full[as]), (it / n_acc) & 1, P.err_flag, 6);
-        tc_fence_after();
-        t_addr = tmem_base + as * acc_stride + ((uint32_t)(quarter * 32) << 16);
-      }
-      epilogue_group(P, cur, t_addr, cg * 16, bc, ro);
-      if (cg == ngroups - 1) {
-        tc_fence_before();
-        mbar_arrive(smem_u32(&t_empty[as]));
-      }
-      it = n_it; cg = n_cg; tile = n_tile; cur = nxt;
-      return n_have;
-    };
-    while (have) {
-      have = step(bufA, bufB);
-      if (!have) break;
-      have = step(bufB, bufA);
+    // ============================== epilogue (specialised once, outside the tile loop)
+    const bool has_add = P.add1.base != nullptr;
+    const bool has_film = P.film != nullptr;
+    const bool multi = P.n_out != 1 || P.rm_out != nullptr;
+    const int kind = (has_add ? 1 : 0) | (has_film ? 2 : 0) | (multi ? 4 : 0);
+    switch (kind) {
+      case 0: epilogue_role<false, false, false>(P, tmem_base, t_full, t_empty, film_s, warp, lane); break;
+      case 1: epilogue_role<true, false, false>(P, tmem_base, t_full, t_empty, film_s, warp, lane); break;
+      case 2: epilogue_role<false, true, false>(P, tmem_base, t_full, t_empty, film_s, warp, lane); break;
+      case 3: epilogue_role<true, true, false>(P, tmem_base, t_full, t_empty, film_s, warp, lane); break;
+      case 4: epilogue_role<false, false, true>(P, tmem_base, t_full, t_empty, film_s, warp, lane); break;
+      case 5: epilogue_role<true, false, true>(P, tmem_base, t_full, t_empty, film_s, warp, lane); break;
+      case 6: epilogue_role<false, true, true>(P, tmem_base, t_full, t_empty, film_s, warp, lane); break;
+      default: epilogue_role<true, true, true>(P, tmem_base, t_full, t_empty, film_s, warp, lane); break;
     }
   }
 
@@ -447,52 +574,64 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)n_acc * acc_stride)
-                 : "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols) : "memory");
   }
 }
 
 // ------------------------------------------------------------------ host side
 inline size_t gemm_smem_bytes(const GemmParams& p) {
-  return (size_t)p.na_stages * p.a_stage_bytes + (size_t)p.nb_stages * p.b_stage_bytes +
+  return (size_t)kOnesBytes + kFilmBytes + (size_t)p.na_stages * p.a_stage_bytes + (size_t)p.nb_stages * p.b_stage_bytes +
          (2 * kMaxAStages + 2 * kMaxBStages + 2 * kMaxAcc) * sizeof(uint64_t) + 16;
 }
 
 // Fills the pipeline fields of `p` (stage sizes / counts, resident-weight mode) for the 227 KB smem of an SM.
-inline void gemm_plan_pipeline(GemmParams& p) {
+// Returns false if the layer cannot be scheduled.
+inline bool gemm_plan_pipeline(GemmParams& p) {
   const int rows_a = kTileM + p.smax - p.smin;
   const int a_bytes = (p.KC / 8) * rows_a * 16;
   const int b_bytes = p.N_TILE * p.KC * 2;
+  const int bias_bytes = p.has_bias ? p.N_TILE * 32 : 0;
   p.a_stage_bytes = (a_bytes + 127) & ~127;
   p.n_tiles_m = (p.m_rows + kTileM - 1) / kTileM;
-  p.n_acc = accum_stride_cols(p.N_TILE) <= 128 ? 4 : 2;
-  const int budget = 216 * 1024;
+  const int stride = (int)accum_stride_cols(p.N_TILE);
+  p.n_acc = 512 / (2 * stride);
+  if (p.n_acc > kMaxAcc) p.n_acc = kMaxAcc;
+  if (p.n_acc < 1) return false;
+  const long long fixed = kOnesBytes + kFilmBytes + (2 * kMaxAStages + 2 * kMaxBStages + 2 * kMaxAcc) * 8 + 16 + 1024;
+  const long long budget = kGemmSmemBudget - fixed;
   const int n_img = p.n_src * p.n_groups * (p.smax - p.smin + 1);
-  const long long total_b = (long long)n_img * b_bytes;
-  if (p.n_tiles_n == 1 && total_b <= 112 * 1024 && (budget - total_b) / p.a_stage_bytes >= 3) {
+  const long long total_b = (((long long)n_img * b_bytes + bias_bytes) + 127) & ~127LL;
+  if (p.n_tiles_n == 1 && total_b + 3LL * p.a_stage_bytes <= budget) {
     p.b_resident = 1;
-    p.b_stage_bytes = b_bytes;
-    p.nb_stages = n_img;
+    p.b_stage_bytes = 128;
+    p.nb_stages = (int)(total_b / 128);
     int na = (int)((budget - total_b) / p.a_stage_bytes);
     p.na_stages = na > kMaxAStages ? kMaxAStages : na;
-    return;
+    return true;
   }
   p.b_resident = 0;
   p.b_stage_bytes = (b_bytes + 127) & ~127;
-  int na = 3, nb = 6;
-  while (na * p.a_stage_bytes + nb * p.b_stage_bytes > budget && nb > 2) --nb;
-  while (na * p.a_stage_bytes + nb * p.b_stage_bytes > budget && na > 2) --na;
-  while (na < 6 && (na + 1) * p.a_stage_bytes + nb * p.b_stage_bytes <= budget) ++na;
+  int na = 2, nb = 3;
+  if ((long long)na * p.a_stage_bytes + (long long)nb * p.b_stage_bytes > budget) return false;
+  // grow both rings round-robin, B (one image per tap) twice as eagerly as A (one slab per K group)
+  for (;;) {
+    bool grew = false;
+    for (int k = 0; k < 2; ++k)
+      if (nb < kMaxBStages && (long long)na * p.a_stage_bytes + (long long)(nb + 1) * p.b_stage_bytes <= budget) { ++nb; grew = true; }
+    if (na < 4 && (long long)(na + 1) * p.a_stage_bytes + (long long)nb * p.b_stage_bytes <= budget) { ++na; grew = true; }
+    if (!grew) break;
+  }
   p.na_stages = na;
   p.nb_stages = nb;
+  return true;
 }
 
 inline cudaError_t gemm_launch(GemmParams p, int num_sms, cudaStream_t stream) {
-  gemm_plan_pipeline(p);
+  if (!gemm_plan_pipeline(p)) return cudaErrorInvalidConfiguration;
   const size_t smem = gemm_smem_bytes(p);
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemBudget);
     if (e != cudaSuccess) return e;
     attr_set = true;
   }

@@ -72,7 +72,7 @@ static HT make_tensor(int B, int L, int C, int split, int esz, bool randomize) {
   t.B = B; t.L = L; t.C = C; t.split = split; t.esz = esz; t.G = kGuard;
   int rows = (L + split - 1) / split;
   t.Lh = ((rows + 2 + 7) / 8) * 8;
-  t.P = t.G + ((B * t.Lh + 127) / 128) * 128 + t.G;
+  t.P = t.G + ((B * t.Lh + kTileM - 1) / kTileM) * kTileM + t.G;
   t.data.assign((size_t)split * (C / 8) * t.P * 8 * esz, 0);
   if (randomize)
     for (int b = 0; b < B; ++b)
@@ -110,7 +110,12 @@ static const Case kCases[] = {
     {"down", 2, 100, 64, 4, -1, 1, 64, 128, 1, 128, true, false, false, false, 1.f, 0, false},
     {"up", 2, 100, 128, 1, -1, 1, 64, 64, 4, 64, true, false, true, false, 0.70710678f, 0, false},
     {"epi", 2, 200, 64, 1, -2, 2, 64, 64, 1, 64, true, true, true, true, 0.5f, 2, true},
-    {"mel", 2, 201, 80, 1, -1, 1, 80, 512, 1, 256, true, false, false, false, 1.f, 0, false},
+    {"mel", 2, 201, 80, 1, -1, 1, 80, 512, 1, 128, true, false, false, false, 1.f, 0, false},
+    {"big128", 3, 401, 256, 1, -2, 2, 64, 512, 1, 128, true, false, true, false, 0.70710678f, 0, false},
+    {"film", 2, 700, 64, 1, -2, 2, 64, 64, 1, 64, true, true, true, false, 0.70710678f, 0, false},
+    {"nobias", 2, 300, 32, 1, -1, 1, 32, 32, 1, 32, false, false, false, false, 1.f, 0, false},
+    {"c96", 2, 333, 96, 1, -1, 1, 48, 96, 1, 96, true, false, true, true, 1.f, 0, false},
+    {"rmonly", 2, 130, 64, 1, 0, 0, 64, 256, 1, 128, true, false, false, false, 1.f, -1, true},
 };
 
 static int run_case(const Case& c, int swap_lbo, int num_sms) {
@@ -123,12 +128,18 @@ static int run_case(const Case& c, int swap_lbo, int num_sms) {
   std::vector<float> W((size_t)N_total * c.n_src * n_shift * c.C_in);
   for (auto& w : W) w = bf2f(f2bf(frand() * 0.1f));
   const int n_groups = c.C_in / c.KC, n_tiles_n = N_total / c.N_TILE, kcc = c.KC / 8;
-  std::vector<uint16_t> img((size_t)N_total * c.n_src * n_shift * c.C_in);
-  for (int nt = 0; nt < n_tiles_n; ++nt)
+  std::vector<float> bias(c.C_out), film(2 * c.C_out);
+  for (auto& v : bias) v = frand() * 0.5f;
+  for (auto& v : film) v = frand();
+  const size_t n_img_elems = (size_t)c.n_src * n_groups * n_shift * c.N_TILE * c.KC;
+  const size_t bias_elems = c.bias ? (size_t)c.N_TILE * 16 : 0;
+  const size_t nt_stride = n_img_elems + bias_elems;
+  std::vector<uint16_t> img(nt_stride * n_tiles_n, 0);
+  for (int nt = 0; nt < n_tiles_n; ++nt) {
     for (int s = 0; s < c.n_src; ++s)
       for (int g = 0; g < n_groups; ++g)
         for (int q = 0; q < n_shift; ++q) {
-          size_t base = ((((size_t)nt * c.n_src + s) * n_groups + g) * n_shift + q) * (size_t)c.N_TILE * c.KC;
+          size_t base = nt * nt_stride + (((size_t)s * n_groups + g) * n_shift + q) * (size_t)c.N_TILE * c.KC;
           for (int j = 0; j < kcc; ++j)
             for (int n = 0; n < c.N_TILE; ++n)
               for (int e = 0; e < 8; ++e) {
@@ -138,12 +149,17 @@ static int run_case(const Case& c, int swap_lbo, int num_sms) {
                     f2bf(W[(((size_t)ng * c.n_src + s) * n_shift + q) * c.C_in + ci]);
               }
         }
+    if (c.bias)
+      for (int n = 0; n < c.N_TILE; ++n) {
+        const float bv = bias[(nt * c.N_TILE + n) % c.C_out];
+        const uint16_t hi = f2bf(bv);
+        img[nt * nt_stride + n_img_elems + (size_t)n * 8 + 0] = hi;
+        img[nt * nt_stride + n_img_elems + (size_t)n * 8 + 1] = f2bf(bv - bf2f(hi));
+      }
+  }
   char* d_w;
   CK(cudaMalloc(&d_w, img.size() * 2));
   CK(cudaMemcpy(d_w, img.data(), img.size() * 2, cudaMemcpyHostToDevice));
-  std::vector<float> bias(c.C_out), film(2 * c.C_out);
-  for (auto& v : bias) v = frand() * 0.5f;
-  for (auto& v : film) v = frand();
   float *d_bias, *d_film;
   CK(cudaMalloc(&d_bias, bias.size() * 4));
   CK(cudaMalloc(&d_film, film.size() * 4));
@@ -153,7 +169,7 @@ static int run_case(const Case& c, int swap_lbo, int num_sms) {
   HT add1 = make_tensor(c.B, L_out, c.C_out, 1, 2, true);
   HT add2 = make_tensor(c.B, L_out, c.C_out, 1, 4, true);
   HT out0 = make_tensor(c.B, L_out, c.C_out, 1, 2, false);
-  HT out1 = make_tensor(c.B, L_out, c.C_out, c.out1_split ? c.out1_split : 1, 2, false);
+  HT out1 = make_tensor(c.B, L_out, c.C_out, c.out1_split > 0 ? c.out1_split : 1, 2, false);
   float* d_rm = nullptr;
   const int m_rows = c.B * A.Lh;
   if (c.rm) {
@@ -171,16 +187,15 @@ static int run_case(const Case& c, int swap_lbo, int num_sms) {
   p.w = d_w; p.N_TILE = c.N_TILE; p.n_tiles_n = n_tiles_n;
   p.m_rows = m_rows; p.Lh_A = A.Lh; p.M_valid = c.L_out_space;
   p.up = c.up; p.C_out = c.C_out;
-  p.bias = c.bias ? d_bias : nullptr;
+  p.has_bias = c.bias ? 1 : 0;
   p.film = c.film ? d_film : nullptr;
   if (c.add1) p.add1 = desc_of(add1);
   if (c.add2f32) p.add2 = desc_of(add2);
   p.scale = c.scale;
-  p.n_out = c.out1_split ? 2 : 1;
+  p.n_out = c.out1_split < 0 ? 0 : (c.out1_split ? 2 : 1);
   p.out[0].t = desc_of(out0); p.out[0].act = 0;
   p.out[1].t = desc_of(out1); p.out[1].act = 2; p.out[1].a1 = 0.25f; p.out[1].a2 = -0.5f;
   p.rm_out = d_rm; p.rm_ld = N_total;
-  p.dbg_swap_lbo = swap_lbo;
   p.err_flag = d_err;
 
   CK(gemm_launch(p, num_sms, 0));
@@ -217,8 +232,8 @@ static int run_case(const Case& c, int swap_lbo, int num_sms) {
         v *= c.scale;
         if (c.film) v = film[co] * v + film[c.C_out + co];
         max_ref = fmax(max_ref, fabs(v));
-        max_err = fmax(max_err, fabs(v - out0.get(b, l, co)));
-        if (c.out1_split) {
+        if (c.out1_split >= 0) max_err = fmax(max_err, fabs(v - out0.get(b, l, co)));
+        if (c.out1_split > 0) {
           double w = v >= 0 ? v : 0.25 * v;
           w = w >= 0 ? w : -0.5 * w;
           max_err1 = fmax(max_err1, fabs(w - out1.get(b, l, co)));
@@ -241,18 +256,19 @@ static int run_case(const Case& c, int swap_lbo, int num_sms) {
 
 // Throughput of layer-shaped problems (cfg 2 sizes: B=64, 4 s clips).
 static void run_perf(int num_sms) {
-  struct PC { const char* name; int B, Lv, C, k, add; } pcs[] = {
-      {"L0 C32 k5", 64, 64160, 32, 5, 0}, {"L0 C32 k3", 64, 64160, 32, 3, 0}, {"L0 C32 k3 +add", 64, 64160, 32, 3, 1},
-      {"L1 C64 k5", 64, 32080, 64, 5, 0}, {"L1 C64 k3 +add", 64, 32080, 64, 3, 1},
-      {"L2 C128 k5", 64, 8020, 128, 5, 0}, {"L2 C128 k3 +add", 64, 8020, 128, 3, 1}, {"L3 C256 k5", 64, 2005, 256, 5, 0},
-      {"L4 C512 k5", 64, 401, 512, 5, 0}, {"L4 C512 k3", 64, 401, 512, 3, 0}};
+  struct PC { const char* name; int B, Lv, C, k, add, nout; } pcs[] = {
+      {"L0 C32 k5", 64, 64160, 32, 5, 0, 1}, {"L0 C32 k3", 64, 64160, 32, 3, 0, 1}, {"L0 C32 k3 +add 2out", 64, 64160, 32, 3, 1, 2},
+      {"L1 C64 k5", 64, 32080, 64, 5, 0, 1}, {"L1 C64 k3", 64, 32080, 64, 3, 0, 1}, {"L1 C64 k3 +add 2out", 64, 32080, 64, 3, 1, 2},
+      {"L2 C128 k5", 64, 8020, 128, 5, 0, 1}, {"L2 C128 k3", 64, 8020, 128, 3, 0, 1}, {"L2 C128 k3 +add 2out", 64, 8020, 128, 3, 1, 2},
+      {"L3 C256 k5", 64, 2005, 256, 5, 0, 1}, {"L3 C256 k3", 64, 2005, 256, 3, 0, 1},
+      {"L4 C512 k5", 64, 401, 512, 5, 0, 1}, {"L4 C512 k3", 64, 401, 512, 3, 0, 1}};
   for (auto& pc : pcs) {
     HT A = make_tensor(pc.B, pc.Lv, pc.C, 1, 2, false);
     CK(cudaMemset(A.dev, 0x3c, A.data.size()));  // small finite bf16 values everywhere
     HT O = make_tensor(pc.B, pc.Lv, pc.C, 1, 2, false);
     HT O2 = make_tensor(pc.B, pc.Lv, pc.C, 1, 2, false);
-    const int KC = pc.C < 64 ? pc.C : 64, NT = pc.C < 256 ? pc.C : 256;
-    size_t wbytes = (size_t)pc.C * pc.C * pc.k * 2;
+    const int KC = pc.C < 64 ? pc.C : 64, NT = pc.C < 128 ? pc.C : 128;
+    size_t wbytes = (size_t)pc.C * pc.C * pc.k * 2 + (size_t)pc.C * 32;
     char* d_w;
     CK(cudaMalloc(&d_w, wbytes));
     CK(cudaMemset(d_w, 0x3c, wbytes));
@@ -262,7 +278,7 @@ static void run_perf(int num_sms) {
     p.smin = -(pc.k / 2); p.smax = pc.k / 2; p.KC = KC; p.n_groups = pc.C / KC;
     p.w = d_w; p.N_TILE = NT; p.n_tiles_n = pc.C / NT;
     p.m_rows = pc.B * A.Lh; p.Lh_A = A.Lh; p.M_valid = pc.Lv; p.up = 1; p.C_out = pc.C;
-    p.scale = 1.f; p.n_out = 2;
+    p.has_bias = 1; p.scale = 1.f; p.n_out = pc.nout;
     p.out[0].t = desc_of(O); p.out[1].t = desc_of(O2); p.out[1].act = 1; p.out[1].a1 = 0.25f;
     HT AD = make_tensor(pc.B, pc.Lv, pc.C, 1, 2, false);
     if (pc.add) p.add1 = desc_of(AD);
@@ -279,8 +295,8 @@ static void run_perf(int num_sms) {
     CK(cudaDeviceSynchronize());
     float ms; CK(cudaEventElapsedTime(&ms, e0, e1)); ms /= iters;
     double flop = 2.0 * pc.B * pc.Lv * (double)pc.C * pc.C * pc.k;
-    double bytes = (double)pc.B * pc.Lv * pc.C * 2 * (3 + pc.add);
-    printf("[perf %s] %.3f ms  %.1f TFLOP/s  %.0f GB/s (reads + 2 writes)\n", pc.name, ms, flop / ms * 1e-9, bytes / ms * 1e-6);
+    double bytes = (double)pc.B * pc.Lv * pc.C * 2 * (1 + pc.nout + pc.add);
+    printf("[perf %s] %.3f ms  %.1f TFLOP/s  %.0f GB/s (algorithmic reads + writes)\n", pc.name, ms, flop / ms * 1e-9, bytes / ms * 1e-6);
     cudaFree(AD.dev); cudaFree(A.dev); cudaFree(O.dev); cudaFree(O2.dev); cudaFree(d_w); cudaFree(d_err);
   }
 }

@@ -16,7 +16,6 @@
 namespace uv {
 
 constexpr int kGuard = 8;        // guard rows at the start/end of each plane
-constexpr int kTileM = 128;      // rows per GEMM tile (UMMA M)
 
 struct TensDesc {
   char* base;        // nullptr => unused
@@ -47,8 +46,10 @@ struct GemmParams {
   int KC;            // channels per K group (multiple of 16)
   int n_groups;      // C_in / KC
   // ---- B operand: packed weight images
-  //  [n_tile][src][group][shift][KC/8][N_TILE][8] bf16
+  //  per N tile: [src][group][shift][KC/8][N_TILE][8] bf16, then (has_bias) the bias image
+  //  [2][N_TILE][8] bf16 whose K columns 0 / 1 hold the hi / lo bf16 halves of the fp32 bias
   const char* w;
+  int has_bias;
   int N_TILE;        // multiple of 16, <= 256
   int n_tiles_n;
   // ---- row space
@@ -59,7 +60,6 @@ struct GemmParams {
   // ---- epilogue
   int up;            // l_out = up*m + phase, phase = n_glob / C_out
   int C_out;
-  const float* bias; // [C_out] or null
   const float* film; // [2*C_out] gamma|beta or null
   TensDesc add1, add2;
   float scale;
@@ -71,8 +71,7 @@ struct GemmParams {
   int na_stages, nb_stages;
   int a_stage_bytes, b_stage_bytes;
   int b_resident;    // 1: all weight images of the (single) N tile stay in smem for the whole kernel
-  int n_acc;         // TMEM accumulator stages (2 or 4)
-  int dbg_swap_lbo;  // test hook: swap LBO/SBO roles in the smem descriptors
+  int n_acc;         // TMEM accumulator stages (1, 2 or 4), each holding both 128-row halves of a tile
   int* err_flag;     // set on watchdog timeout
 };
 

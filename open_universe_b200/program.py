@@ -35,7 +35,7 @@ class Level:
         self.L = L
         self.Lh = _ru(L + 2, 8)
         self.rows = B * self.Lh
-        self.P = G + _ru(self.rows, 128) + G
+        self.P = G + _ru(self.rows, 256) + G   # GEMM tiles are 256 rows (csrc/gemm_tc.cuh kTileM)
 
 
 class Program:

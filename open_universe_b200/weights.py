@@ -25,20 +25,32 @@ def eff_weight(sd, prefix):
     return sd[prefix + ".weight"].float()
 
 
-def pick_kc(c_in):
-    if c_in % 64 == 0:
-        return 64
-    if c_in % 48 == 0:
-        return 48
-    if c_in <= 96:
-        return c_in
-    if c_in % 32 == 0:
-        return 32
-    return 16
+TILE_M = 256          # csrc/gemm_tc.cuh kTileM
+SMEM_BUDGET = 227 * 1024 - (4096 + 6144 + 384 + 16 + 1024)  # gemm_plan_pipeline(): 227 KB minus the fixed regions
+
+
+def _kc_options(c_in):
+    cand = [64, 48, 32, 16] + ([c_in] if c_in <= 96 else [])
+    return sorted({k for k in cand if c_in % k == 0 and k % 16 == 0}, reverse=True)
+
+
+def pick_kc(c_in, n_total=None, n_tile=None, n_src=1, n_shift=1):
+    """Channels per K group.  Largest slab that divides C_in, except that a layer whose whole weight
+    set can stay resident in shared memory (single N tile) takes the largest KC that still leaves
+    room for three A stages next to it (mirrors gemm_plan_pipeline in csrc/gemm_tc.cuh)."""
+    opts = _kc_options(c_in)
+    if n_total is not None and n_total == n_tile:
+        total_b = n_total * n_src * n_shift * c_in * 2 + n_tile * 32
+        for kc in opts:
+            a_stage = (kc // 8) * (TILE_M + n_shift - 1) * 16
+            if total_b + 3 * a_stage + 256 <= SMEM_BUDGET:
+                return kc
+    return opts[0]
 
 
 def pick_ntile(c_out):
-    for n in range(min(256, c_out), 15, -16):
+    """Largest multiple of 16 that divides C_out and leaves two TMEM accumulator stages (<= 128)."""
+    for n in range(min(128, c_out), 15, -16):
         if c_out % n == 0:
             return n
     raise ValueError(f"no N tile for C_out={c_out}")
@@ -104,20 +116,36 @@ def w4_up(w, lp=None):
     return w4.view(r * co, 1, 3, ci).contiguous(), -1
 
 
-def pack_w4(w4, kc, n_tile):
-    """[N, S, Q, Ci] fp32 -> bf16 images [N/n_tile][S][Ci/kc][Q][kc/8][n_tile][8]."""
+def pack_w4(w4, kc, n_tile, bias_n=None):
+    """[N, S, Q, Ci] fp32 -> per N tile: bf16 images [S][Ci/kc][Q][kc/8][n_tile][8] followed (bias_n
+    given: fp32 [N]) by the bias image [2][n_tile][8] whose K columns 0 / 1 carry the hi / lo bf16
+    halves of the bias (it meets the kernel's constant ones tile, csrc/gemm_tc.cuh)."""
     n, s, q, ci = w4.shape
     assert n % n_tile == 0 and ci % kc == 0 and kc % 16 == 0 and n_tile % 16 == 0
     x = w4.view(n // n_tile, n_tile, s, q, ci // kc, kc // 8, 8)
-    x = x.permute(0, 2, 4, 3, 5, 1, 6)  # nt, s, g, q, j, n, e
+    x = x.permute(0, 2, 4, 3, 5, 1, 6).reshape(n // n_tile, -1)  # nt, (s, g, q, j, n, e)
+    if bias_n is not None:
+        b = bias_n.float().view(n // n_tile, n_tile)
+        hi = b.to(torch.bfloat16).float()
+        img = torch.zeros(n // n_tile, 2, n_tile, 8)
+        img[:, 0, :, 0] = hi
+        img[:, 0, :, 1] = b - hi
+        x = torch.cat([x, img.reshape(n // n_tile, -1)], dim=1)
     return to_bf16_bits(x)
 
 
-def unpack_w4(bits, n, s, q, ci, kc, n_tile):
-    """Inverse of pack_w4 (used by the CPU emulator): -> fp32 [N, S, Q, Ci]."""
+def unpack_w4(bits, n, s, q, ci, kc, n_tile, has_bias=False):
+    """Inverse of pack_w4 (used by the CPU emulator): -> fp32 [N, S, Q, Ci] (and the bias [N] the
+    tensor core sees, hi + lo, when has_bias)."""
     x = torch.from_numpy(np.ascontiguousarray(bits)).view(torch.bfloat16).float()
-    x = x.view(n // n_tile, s, ci // kc, q, kc // 8, n_tile, 8)
-    return x.permute(0, 5, 1, 3, 2, 4, 6).reshape(n, s, q, ci).contiguous()
+    x = x.view(n // n_tile, -1)
+    n_w = s * q * ci * n_tile
+    w = x[:, :n_w].reshape(n // n_tile, s, ci // kc, q, kc // 8, n_tile, 8)
+    w = w.permute(0, 5, 1, 3, 2, 4, 6).reshape(n, s, q, ci).contiguous()
+    if not has_bias:
+        return w
+    img = x[:, n_w:].reshape(n // n_tile, 2, n_tile, 8)
+    return w, (img[:, 0, :, 0] + img[:, 0, :, 1]).reshape(n)
 
 
 def pack_gru_whh(w_hh_f, w_hh_b):
@@ -159,9 +187,11 @@ class PackedModel:
 
     def add_gemm(self, name, w4, smin, c_out, up=1, bias=None, slope=None):
         n, s, q, ci = w4.shape
-        kc, n_tile = pick_kc(ci), pick_ntile(c_out)
+        n_tile = pick_ntile(c_out)
+        kc = pick_kc(ci, n, n_tile, s, q)
+        bias_n = bias.float().repeat(n // c_out) if bias is not None else None  # column n -> channel n % C_out
         self.layers[name] = dict(
-            w_w=self.blob.add(pack_w4(w4, kc, n_tile)),
+            w_w=self.blob.add(pack_w4(w4, kc, n_tile, bias_n)),
             bias_w=self.blob.add_f32(bias) if bias is not None else -1,
             n_src=s, smin=smin, smax=smin + q - 1, KC=kc, N_TILE=n_tile, N_total=n,
             C_out=c_out, C_in=ci, up=up, slope=slope,

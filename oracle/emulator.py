@@ -85,12 +85,14 @@ class Emulator:
         a = self.view(op.a).float()  # [n_src, nch, P, 8]
         n_shift = op.smax - op.smin + 1
         C_in = op.a.nch * 8
-        key = (op.w_w, op.N_total, op.n_src, n_shift, C_in)
+        has_bias = op.bias_w >= 0
+        key = (op.w_w, op.N_total, op.n_src, n_shift, C_in, has_bias)
         if key not in self._wcache:
-            nb = op.N_total * op.n_src * n_shift * C_in * 2
+            nb = op.N_total * op.n_src * n_shift * C_in * 2 + (op.N_total * 32 if has_bias else 0)
             bits = self.blob[op.w_w : op.w_w + nb].view(np.int16)
-            self._wcache[key] = unpack_w4(bits, op.N_total, op.n_src, n_shift, C_in, op.KC, op.N_TILE)
-        w4 = self._wcache[key]
+            res = unpack_w4(bits, op.N_total, op.n_src, n_shift, C_in, op.KC, op.N_TILE, has_bias)
+            self._wcache[key] = res if has_bias else (res, None)
+        w4, bias_n = self._wcache[key]
         M = op.m_rows
         acc = torch.zeros(M, op.N_total)
         for s in range(op.n_src):
@@ -104,7 +106,8 @@ class Emulator:
         b_idx, m, acc = b_idx[valid], m[valid], acc[valid]
         if op.rm_out >= 0:
             rm = self.a_f32(op.rm_out, M * op.rm_ld).view(M, op.rm_ld)
-        bias = self.w_f32(op.bias_w, op.C_out) if op.bias_w >= 0 else None
+        # the kernel adds the bias on the tensor core from its packed hi + lo bf16 image
+        bias = bias_n[: op.C_out] if bias_n is not None else None
         film = self.a_f32(op.film, 2 * op.C_out) if op.film >= 0 else None
         for ph in range(op.N_total // op.C_out):
             v = acc[:, ph * op.C_out : (ph + 1) * op.C_out].clone()

@@ -61,17 +61,27 @@ def test_up_conv_with_and_without_antialias():
 def test_pack_unpack_roundtrip():
     torch.manual_seed(3)
     w4 = torch.randn(512, 2, 3, 128).to(torch.bfloat16).float()
-    bits = weights.pack_w4(w4, 64, 256)
-    assert torch.equal(weights.unpack_w4(bits.reshape(-1), 512, 2, 3, 128, 64, 256), w4)
+    bits = weights.pack_w4(w4, 64, 128)
+    assert torch.equal(weights.unpack_w4(bits.reshape(-1), 512, 2, 3, 128, 64, 128), w4)
+    # with the bias image (hi + lo bf16 split of the fp32 bias, one image per N tile)
+    bias = torch.randn(512)
+    bits = weights.pack_w4(w4, 64, 128, bias)
+    assert bits.size == 512 * 2 * 3 * 128 + 512 * 16
+    w_back, b_back = weights.unpack_w4(bits.reshape(-1), 512, 2, 3, 128, 64, 128, has_bias=True)
+    assert torch.equal(w_back, w4)
+    assert torch.allclose(b_back, bias, rtol=2.0**-15, atol=1e-30)
 
 
 def test_tile_choices():
     for c in (32, 48, 64, 80, 96, 128, 192, 256, 384, 512, 768):
         kc = weights.pick_kc(c)
         assert c % kc == 0 and kc % 16 == 0
+        # single-N-tile k=5 layer: the resident-weights choice must still be a legal K group
+        kc = weights.pick_kc(c, min(c, 128), weights.pick_ntile(c), 1, 5)
+        assert c % kc == 0 and kc % 16 == 0
     for c in (32, 48, 64, 96, 128, 192, 256, 384, 512, 768, 1536, 2304):
         n = weights.pick_ntile(c)
-        assert c % n == 0 and n % 16 == 0 and n <= 256
+        assert c % n == 0 and n % 16 == 0 and n <= 128
 
 
 def test_binomial_taps_closed_form():
