@@ -44,6 +44,7 @@ constexpr int kOnesBytes = 2 * kSubM * 16;   // [2 chunks][128 rows][8] bf16
 constexpr int kFilmMaxC = 768;
 constexpr int kFilmBytes = 2 * kFilmMaxC * 4;
 constexpr int kGemmSmemBudget = 227 * 1024;
+constexpr int kAddRowsBytes = kTileM * 16;   // one 8-channel chunk of a residual slab (no halo)
 
 // TMEM columns per accumulator (power of two >= 32).
 __host__ __device__ inline uint32_t accum_stride_cols(int n_tile) {
@@ -375,10 +376,11 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
-  // smem carve-up: ones tile | FiLM table | A ring | B ring (or resident weight set) | barriers | tmem ptr
+  // smem carve-up: ones tile | FiLM table | identity images | A ring | B ring (or resident weight set) | barriers | tmem ptr
   uint8_t* ones = smem;
   float* film_s = reinterpret_cast<float*>(smem + kOnesBytes);
-  uint8_t* a_ring = smem + kOnesBytes + kFilmBytes;
+  uint8_t* ident = smem + kOnesBytes + kFilmBytes;
+  uint8_t* a_ring = ident + P.ident_bytes;
   uint8_t* b_ring = a_ring + (size_t)P.na_stages * P.a_stage_bytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(b_ring + (size_t)P.nb_stages * P.b_stage_bytes);
   uint64_t* a_full = bars;
@@ -406,6 +408,19 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
   }
   if (P.film) {
     for (int i = threadIdx.x; i < 2 * P.C_out; i += kGemmThreads) film_s[i] = P.film[i];
+  }
+  if (P.add_kc) {
+    // identity images [N_TILE / add_kc][add_kc / 8][N_TILE][8]: image j maps residual channel j*add_kc + k to column j*add_kc + k
+    const int per_img = (P.add_kc >> 3) * P.N_TILE;
+    const int n_ent = (P.N_TILE / P.add_kc) * per_img;
+    for (int i = threadIdx.x; i < n_ent; i += kGemmThreads) {
+      const int j = i / per_img, rem = i - j * per_img;
+      const int c = rem / P.N_TILE, n = rem - c * P.N_TILE;
+      const int e = n - j * P.add_kc - 8 * c;   // K element of this 16-byte entry that is 1.0
+      uint32_t w[4] = {0u, 0u, 0u, 0u};
+      if (e >= 0 && e < 8) w[e >> 1] = (e & 1) ? 0x3F800000u : 0x00003F80u;
+      reinterpret_cast<uint4*>(ident)[i] = make_uint4(w[0], w[1], w[2], w[3]);
+    }
   }
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   if (warp == 1) {
@@ -480,6 +495,26 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
             }
           }
         }
+        if (P.add_kc) {
+          // residual operand (same row space, phase plane = output phase): one un-halo'd slab per identity image
+          const int n0 = n_tile * P.N_TILE;
+          const int phase = n0 / P.C_out;
+          const int co0 = n0 - phase * P.C_out;
+          const int cpi = P.add_kc >> 3;
+          for (int j = 0; j < P.N_TILE / P.add_kc; ++j) {
+            mbar_wait(smem_u32(&a_empty[ia]), pa ^ 1, P.err_flag, 1);
+            const uint32_t fb = smem_u32(&a_full[ia]);
+            mbar_expect_tx(fb, (uint32_t)cpi * kAddRowsBytes);
+            const uint32_t dst = smem_u32(a_ring + (size_t)ia * P.a_stage_bytes);
+            const long long plane0 = (long long)phase * P.add1.nchunks + (co0 >> 3) + j * cpi;
+            const long long rowa = (long long)P.add1.G + (long long)m_tile * kTileM;
+            for (int jc = 0; jc < cpi; ++jc) {
+              const char* src = P.add1.base + (((plane0 + jc) * P.add1.P + rowa) << 4);
+              bulk_g2s(dst + jc * kAddRowsBytes, src, kAddRowsBytes, fb);
+            }
+            if (++ia == P.na_stages) { ia = 0; pa ^= 1; }
+          }
+        }
       }
     }
   } else if (warp == 1) {
@@ -549,12 +584,30 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
             if (++ia == P.na_stages) { ia = 0; pa ^= 1; }
           }
         }
+        if (P.add_kc) {
+          const uint32_t img_bytes = (uint32_t)P.N_TILE * P.add_kc * 2u;
+          for (int j = 0; j < P.N_TILE / P.add_kc; ++j) {
+            mbar_wait(smem_u32(&a_full[ia]), pa, P.err_flag, 4);
+            tc_fence_after();
+            const uint32_t a_addr = smem_u32(a_ring + (size_t)ia * P.a_stage_bytes);
+            const uint32_t i_addr = smem_u32(ident) + j * img_bytes;
+            for (int kk = 0; kk < (P.add_kc >> 4); ++kk) {
+              const uint32_t a_k = a_addr + kk * 2 * kAddRowsBytes;
+              const uint64_t bd = make_desc(i_addr + kk * 2 * lbo_b, lbo_b, 128);
+              tc_mma_bf16(d0, make_desc(a_k, kAddRowsBytes, 128), bd, idesc, accumulate);
+              tc_mma_bf16(d1, make_desc(a_k + kSubM * 16, kAddRowsBytes, 128), bd, idesc, accumulate);
+              accumulate = 1;
+            }
+            tc_commit(smem_u32(&a_empty[ia]));
+            if (++ia == P.na_stages) { ia = 0; pa ^= 1; }
+          }
+        }
         tc_commit(smem_u32(&t_full[as]));
       }
     }
   } else {
     // ============================== epilogue (specialised once, outside the tile loop)
-    const bool has_add = P.add1.base != nullptr;
+    const bool has_add = P.add1.base != nullptr && P.add_kc == 0;   // add_kc: the residual went through the tensor core
     const bool has_film = P.film != nullptr;
     const bool multi = P.n_out != 1 || P.rm_out != nullptr;
     const int kind = (has_add ? 1 : 0) | (has_film ? 2 : 0) | (multi ? 4 : 0);
@@ -580,7 +633,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
 
 // ------------------------------------------------------------------ host side
 inline size_t gemm_smem_bytes(const GemmParams& p) {
-  return (size_t)kOnesBytes + kFilmBytes + (size_t)p.na_stages * p.a_stage_bytes + (size_t)p.nb_stages * p.b_stage_bytes +
+  return (size_t)kOnesBytes + kFilmBytes + p.ident_bytes + (size_t)p.na_stages * p.a_stage_bytes + (size_t)p.nb_stages * p.b_stage_bytes +
          (2 * kMaxAStages + 2 * kMaxBStages + 2 * kMaxAcc) * sizeof(uint64_t) + 16;
 }
 
@@ -592,12 +645,26 @@ inline bool gemm_plan_pipeline(GemmParams& p) {
   const int b_bytes = p.N_TILE * p.KC * 2;
   const int bias_bytes = p.has_bias ? p.N_TILE * 32 : 0;
   p.a_stage_bytes = (a_bytes + 127) & ~127;
+  // Residual through the tensor core (identity MMA): a bf16 add1 laid out in the GEMM's own row space
+  // (phase-split like the output of an up conv), memory-bound layers only (C_out <= 128).
+  p.add_kc = 0;
+  p.ident_bytes = 0;
+  if (p.add1.base && !p.add2.base && p.add1.esize_log2 == 1 && p.add1.Lh == p.Lh_A && p.add1.split == p.up &&
+      p.add1.G == p.a_G && p.C_out <= 128 && !p.no_add_mma) {
+    for (int kc = 64; kc >= 16; kc -= 16)
+      if (p.N_TILE % kc == 0) { p.add_kc = kc; break; }
+    if (p.add_kc) {
+      p.ident_bytes = p.N_TILE * p.N_TILE * 2;
+      const int add_bytes = (p.add_kc / 8) * kAddRowsBytes;
+      if (add_bytes > p.a_stage_bytes) p.a_stage_bytes = add_bytes;
+    }
+  }
   p.n_tiles_m = (p.m_rows + kTileM - 1) / kTileM;
   const int stride = (int)accum_stride_cols(p.N_TILE);
   p.n_acc = 512 / (2 * stride);
   if (p.n_acc > kMaxAcc) p.n_acc = kMaxAcc;
   if (p.n_acc < 1) return false;
-  const long long fixed = kOnesBytes + kFilmBytes + (2 * kMaxAStages + 2 * kMaxBStages + 2 * kMaxAcc) * 8 + 16 + 1024;
+  const long long fixed = kOnesBytes + kFilmBytes + p.ident_bytes + (2 * kMaxAStages + 2 * kMaxBStages + 2 * kMaxAcc) * 8 + 16 + 1024;
   const long long budget = kGemmSmemBudget - fixed;
   const int n_img = p.n_src * p.n_groups * (p.smax - p.smin + 1);
   const long long total_b = (((long long)n_img * b_bytes + bias_bytes) + 127) & ~127LL;

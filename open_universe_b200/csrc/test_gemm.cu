@@ -115,6 +115,12 @@ static const Case kCases[] = {
     {"film", 2, 700, 64, 1, -2, 2, 64, 64, 1, 64, true, true, true, false, 0.70710678f, 0, false},
     {"nobias", 2, 300, 32, 1, -1, 1, 32, 32, 1, 32, false, false, false, false, 1.f, 0, false},
     {"c96", 2, 333, 96, 1, -1, 1, 48, 96, 1, 96, true, false, true, true, 1.f, 0, false},
+    {"add32", 3, 777, 32, 1, -1, 1, 32, 32, 1, 32, true, false, true, false, 0.70710678f, 0, false},
+    {"add64x2", 2, 500, 64, 1, -2, 2, 64, 64, 1, 64, true, true, true, false, 0.70710678f, 2, false},
+    {"add128", 2, 400, 128, 1, -1, 1, 64, 128, 1, 128, true, false, true, false, 0.70710678f, 0, false},
+    {"add96", 2, 300, 96, 1, -1, 1, 48, 96, 1, 96, true, false, true, false, 1.f, 0, false},
+    {"upsplit", 2, 300, 128, 1, -1, 1, 64, 64, 4, 64, true, false, true, false, 0.70710678f, 0, false},
+    {"add256reg", 2, 300, 256, 1, -1, 1, 64, 256, 1, 128, true, false, true, false, 0.70710678f, 0, false},
     {"rmonly", 2, 130, 64, 1, 0, 0, 64, 256, 1, 128, true, false, false, false, 1.f, -1, true},
 };
 
@@ -166,7 +172,7 @@ static int run_case(const Case& c, int swap_lbo, int num_sms) {
   CK(cudaMemcpy(d_bias, bias.data(), bias.size() * 4, cudaMemcpyHostToDevice));
   CK(cudaMemcpy(d_film, film.data(), film.size() * 4, cudaMemcpyHostToDevice));
 
-  HT add1 = make_tensor(c.B, L_out, c.C_out, 1, 2, true);
+  HT add1 = make_tensor(c.B, L_out, c.C_out, strstr(c.name, "split") ? c.up : 1, 2, true);
   HT add2 = make_tensor(c.B, L_out, c.C_out, 1, 4, true);
   HT out0 = make_tensor(c.B, L_out, c.C_out, 1, 2, false);
   HT out1 = make_tensor(c.B, L_out, c.C_out, c.out1_split > 0 ? c.out1_split : 1, 2, false);

@@ -70,6 +70,9 @@ struct GemmParams {
   // ---- pipeline (filled by host)
   int na_stages, nb_stages;
   int a_stage_bytes, b_stage_bytes;
+  int add_kc;        // > 0: add1 is accumulated by identity MMAs in K slabs of add_kc channels (host decides)
+  int ident_bytes;   // smem bytes of the identity images
+  int no_add_mma;    // test hook: keep add1 on the register path
   int b_resident;    // 1: all weight images of the (single) N tile stay in smem for the whole kernel
   int n_acc;         // TMEM accumulator stages (1, 2 or 4), each holding both 128-row halves of a tile
   int* err_flag;     // set on watchdog timeout

@@ -371,7 +371,12 @@ def build_program(pm, cfg, B, T, n_steps):
         skips = []
         for i in range(n_blocks):
             lev, C = lv[min(i, nlev)], chans[min(i, nlev)]
-            skip = pg.tens(f"s.skip{i}", lev, C)
+            if i < nlev:
+                # consumed only as the residual of the decoder's up conv: stored phase-split in the
+                # coarser row space so that conv's GEMM can stream it like an A operand (identity MMA)
+                skip = pg.tens(f"s.skip{i}", lv[i + 1], C, split=rates[i])
+            else:
+                skip = pg.tens(f"s.skip{i}", lev, C)
             skips.append(skip)
             outs = [_raw(skip)]
             if i < nlev:

@@ -34,7 +34,7 @@ def _kc_options(c_in):
     return sorted({k for k in cand if c_in % k == 0 and k % 16 == 0}, reverse=True)
 
 
-def pick_kc(c_in, n_total=None, n_tile=None, n_src=1, n_shift=1):
+def pick_kc(c_in, n_total=None, n_tile=None, n_src=1, n_shift=1, reserve=0):
     """Channels per K group.  Largest slab that divides C_in, except that a layer whose whole weight
     set can stay resident in shared memory (single N tile) takes the largest KC that still leaves
     room for three A stages next to it (mirrors gemm_plan_pipeline in csrc/gemm_tc.cuh)."""
@@ -43,7 +43,7 @@ def pick_kc(c_in, n_total=None, n_tile=None, n_src=1, n_shift=1):
         total_b = n_total * n_src * n_shift * c_in * 2 + n_tile * 32
         for kc in opts:
             a_stage = (kc // 8) * (TILE_M + n_shift - 1) * 16
-            if total_b + 3 * a_stage + 256 <= SMEM_BUDGET:
+            if total_b + 3 * a_stage + 256 + reserve <= SMEM_BUDGET:
                 return kc
     return opts[0]
 
@@ -185,10 +185,12 @@ class PackedModel:
         self.layers = {}
         self.meta = {}
 
-    def add_gemm(self, name, w4, smin, c_out, up=1, bias=None, slope=None):
+    def add_gemm(self, name, w4, smin, c_out, up=1, bias=None, slope=None, resid=False):
+        """resid: the op that uses this layer adds a residual / condition tensor; for C_out <= 128 it goes
+        through identity MMAs whose images take N_TILE^2 * 2 bytes of shared memory (csrc/gemm_tc.cuh)."""
         n, s, q, ci = w4.shape
         n_tile = pick_ntile(c_out)
-        kc = pick_kc(ci, n, n_tile, s, q)
+        kc = pick_kc(ci, n, n_tile, s, q, reserve=n_tile * n_tile * 2 if (resid and c_out <= 128) else 0)
         bias_n = bias.float().repeat(n // c_out) if bias is not None else None  # column n -> channel n % C_out
         self.layers[name] = dict(
             w_w=self.blob.add(pack_w4(w4, kc, n_tile, bias_n)),
@@ -202,8 +204,9 @@ class PackedModel:
         for cn in ("conv1", "conv2", "conv3"):
             p = f"{prefix}.{cn}"
             w4, smin = w4_plain(eff_weight(sd, p + ".conv"))
+            resid = cn == "conv3" or (cn == "conv1" and name.startswith("s.dec"))
             self.add_gemm(f"{name}.{cn}", w4, smin, w4.shape[0], bias=sd[p + ".conv.bias"],
-                          slope=float(sd[p + ".prelu.weight"]))
+                          slope=float(sd[p + ".prelu.weight"]), resid=resid)
         if direction in ("down", "up"):
             p = f"{prefix}.rate_change_conv"
             w = eff_weight(sd, p + ".conv")
@@ -216,7 +219,7 @@ class PackedModel:
             else:
                 w4, smin = w4_up(w, lp)
                 self.add_gemm(f"{name}.rc", w4, smin, w.shape[1], up=rate, bias=bias,
-                              slope=float(sd[p + ".prelu.weight"]))
+                              slope=float(sd[p + ".prelu.weight"]), resid=name.startswith("s.dec"))
 
     def add_gru(self, sd, prefix, name, layer):
         sufs = ("", "_reverse")
