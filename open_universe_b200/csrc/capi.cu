@@ -1,6 +1,7 @@
 // C ABI (include/universe_b200.h): model = device weight blob, plan = op program +
 // arena + CUDA graph.  Translates uv_op records into kernel launches.
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -67,7 +68,7 @@ extern "C" int uv_model_create(uv_model** out, const void* weights, size_t nbyte
   m->nbytes = nbytes;
   m->num_sms = prop.multiProcessorCount;
   CUDA_TRY(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemBudget));
-  CUDA_TRY(cudaFuncSetAttribute(gru_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gru_smem_bytes(kGruMaxH)));
+  CUDA_TRY(cudaFuncSetAttribute(gru_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   CUDA_TRY(cudaMalloc(&m->blob, nbytes));
   CUDA_TRY(cudaMemcpy(m->blob, weights, nbytes, cudaMemcpyHostToDevice));
   *out = m;
@@ -180,17 +181,33 @@ static int launch_op(uv_plan* p, const uv_op& op, cudaStream_t s) {
                                                                wptr<const float>(p, op.p5), aptr<float>(p, op.p1));
       break;
     case UV_OP_GRU: {
-      if (op.H > kGruMaxH || op.H % 16) return fail(UV_ERR_INVALID, "GRU hidden size unsupported");
+      if (op.H > kGruMaxH || op.H % (8 * kGruNC)) return fail(UV_ERR_INVALID, "GRU hidden size unsupported (needs H % 64 == 0, H <= 384)");
       GruParams g;
       memset(&g, 0, sizeof(g));
       g.gi = aptr<const float>(p, op.p0);
-      g.whh = wptr<const uint4>(p, op.p3);
+      g.whh = wptr<const char>(p, op.p3);
       g.bhh = wptr<const float>(p, op.p4);
       g.B = op.B; g.T = op.T; g.H = op.H; g.Lh = op.Lh_A;
       g.add1 = to_desc(p, op.add1); g.scale = op.scale; g.n_out = op.n_out;
       for (int i = 0; i < 3; ++i) g.out[i] = to_out(p, op.out[i]);
-      const size_t sm = gru_smem_bytes(op.H);
-      gru_kernel<<<dim3((op.B + kGruNB - 1) / kGruNB, 2), kGruThreads, sm, s>>>(g);
+      g.err_flag = p->err_flag;
+      static const bool clk_dbg = getenv("UV_GRU_CLK") != nullptr;   // debug: per-phase clocks of one CTA, printed to stderr
+      if (clk_dbg) {
+        long long* d = nullptr;
+        CUDA_TRY(cudaMalloc(&d, 16 * sizeof(long long)));
+        CUDA_TRY(cudaMemset(d, 0, 16 * sizeof(long long)));
+        g.clk = d;
+        CUDA_TRY(gru_launch(g, s));
+        long long h[16];
+        CUDA_TRY(cudaStreamSynchronize(s));
+        CUDA_TRY(cudaMemcpy(h, d, sizeof(h), cudaMemcpyDeviceToHost));
+        cudaFree(d);
+        fprintf(stderr, "[gru clk/step] T=%d:", op.T);
+        for (int i = 0; i < 10; ++i) fprintf(stderr, " p%d=%lld", i, h[i] / (op.T > 0 ? op.T : 1));
+        fprintf(stderr, "\n");
+        break;
+      }
+      CUDA_TRY(gru_launch(g, s));
       break;
     }
     default:

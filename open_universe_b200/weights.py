@@ -9,7 +9,7 @@ All transformations are exact algebra done once at load time in fp32:
         D[row, n] = sum_{src s, shift q, c}  A_s[row + q, c] * W4[n, s, q, c]
     and packing of W4 into bf16 tile images [n_tile][s][group][q][KC/8][N_TILE][8]
     (the no-swizzle K-major UMMA layout consumed by csrc/gemm_tc.cuh),
-  * GRU recurrent weights into mma.m16n8k16 A-fragment order (csrc/gru.cuh).
+  * GRU recurrent weights into per-CTA K-major UMMA slices (csrc/gru.cuh).
 """
 import math
 
@@ -148,21 +148,27 @@ def unpack_w4(bits, n, s, q, ci, kc, n_tile, has_bias=False):
     return w, (img[:, 0, :, 0] + img[:, 0, :, 1]).reshape(n)
 
 
+GRU_NC = 8  # csrc/gru.cuh kGruNC: CTAs per cluster, each owning H/8 hidden units
+
+
 def pack_gru_whh(w_hh_f, w_hh_b):
-    """[3H, H] x 2 directions -> bf16 mma.m16n8k16 A fragments
-    [dir][3H/16][H/16][lane 32][reg 4][2]."""
+    """[3H, H] x 2 directions -> bf16 K-major UMMA images of the per-CTA slices
+    [dir][rank 8][H/8][3U][8], U = H/8; slice row gate*U + u is W_hh row gate*H + rank*U + u."""
     out = []
     for w in (w_hh_f, w_hh_b):
-        m, k = w.shape
-        t = w.float().view(m // 16, 16, k // 16, 16).permute(0, 2, 1, 3)  # mt, kt, row, col
-        lane = torch.arange(32)
-        row0, col0 = lane // 4, (lane % 4) * 2
-        frag = torch.empty(m // 16, k // 16, 32, 4, 2)
-        for reg, (dr, dc) in enumerate(((0, 0), (8, 0), (0, 8), (8, 8))):
-            for e in range(2):
-                frag[:, :, :, reg, e] = t[:, :, row0 + dr, col0 + dc + e]
-        out.append(frag)
+        m, h = w.shape
+        u = h // GRU_NC
+        x = w.float().view(3, GRU_NC, u, h // 8, 8)          # gate, rank, u, j, e
+        out.append(x.permute(1, 3, 0, 2, 4).reshape(GRU_NC, h // 8, 3 * u, 8))
     return to_bf16_bits(torch.stack(out))
+
+
+def unpack_gru_whh(bits, h):
+    """Inverse of pack_gru_whh (CPU emulator): -> fp32 [2, 3H, H]."""
+    u = h // GRU_NC
+    x = torch.from_numpy(np.ascontiguousarray(bits)).view(torch.bfloat16).float()
+    x = x.view(2, GRU_NC, h // 8, 3, u, 8)                    # dir, rank, j, gate, u, e
+    return x.permute(0, 3, 1, 4, 2, 5).reshape(2, 3 * h, h).contiguous()
 
 
 def dft_basis(window, n_fft):

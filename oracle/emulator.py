@@ -14,7 +14,7 @@ import numpy as np
 import torch
 
 from open_universe_b200 import _abi
-from open_universe_b200.weights import unpack_w4
+from open_universe_b200.weights import unpack_gru_whh, unpack_w4
 
 
 def _dt(t):
@@ -237,17 +237,8 @@ class Emulator:
         B, T, H, Lh = op.B, op.T, op.H, op.Lh_A
         rows = B * Lh
         gi = self.a_f32(op.p0, rows * 6 * H).view(rows, 6 * H)
-        # recover W_hh from the fragment packing
-        mt, kt = 3 * H // 16, H // 16
         bits = self.blob[op.p3 : op.p3 + 2 * 3 * H * H * 2].view(np.int16)
-        frag = torch.from_numpy(bits.copy()).view(torch.bfloat16).float().view(2, mt, kt, 32, 4, 2)
-        lane = torch.arange(32)
-        row0, col0 = lane // 4, (lane % 4) * 2
-        whh = torch.zeros(2, mt, kt, 16, 16)
-        for reg, (dr, dc) in enumerate(((0, 0), (8, 0), (0, 8), (8, 8))):
-            for e in range(2):
-                whh[:, :, :, row0 + dr, col0 + dc + e] = frag[:, :, :, :, reg, e]
-        whh = whh.permute(0, 1, 3, 2, 4).reshape(2, 3 * H, H)
+        whh = unpack_gru_whh(bits.copy(), H)
         bhh = self.w_f32(op.p4, 6 * H).view(2, 3 * H)
         ridx = (torch.arange(B) * Lh)[:, None] + torch.arange(T)[None, :]  # [B, T]
         out = torch.zeros(B, T, 2 * H)
