@@ -140,46 +140,66 @@ __device__ __forceinline__ uint32_t make_idesc(int M, int N) {
 }
 
 // ------------------------------------------------------------------ epilogue helpers
-// PReLU without a compare+select: for a <= 1 it is max(v, a v), otherwise min(v, a v).
-__device__ __forceinline__ float prelu_mm(float v, float a, bool le1) {
-  const float av = a * v;
-  return le1 ? fmaxf(v, av) : fminf(v, av);
+// PReLU: slopes <= 1 (every trained / initialised slope of these networks) take the two-instruction
+// form max(v, a v); the LE1 = false instantiation is the general compare-free form.
+template <bool LE1>
+__device__ __forceinline__ float prelu_t(float v, float a) {
+  if (LE1) return fmaxf(v, a * v);
+  return fmaf(a, fminf(v, 0.f), fmaxf(v, 0.f));
 }
 
-struct ActSpec {
-  int act;
-  float a1, a2;
-  bool le1_1, le1_2;
+// floor(g / d) for 0 <= g < 2^24-ish without an integer division (per tile, per thread)
+__device__ __forceinline__ int fast_div(int g, int d, float inv_d) {
+  int q = __float2int_rz(((float)g + 0.5f) * inv_d);
+  const int r = g - q * d;
+  if (r < 0) --q;
+  else if (r >= d) ++q;
+  return q;
+}
+
+// One output tensor of the epilogue, reduced to what the column loop needs.
+struct OutPtr {
+  char* p;             // (row, first chunk of this tile); nullptr = nothing to store for this thread
+  long long pstride;   // bytes between chunk planes
 };
-__device__ __forceinline__ ActSpec act_spec(const OutDesc& o) {
-  ActSpec s;
-  s.act = o.act; s.a1 = o.a1; s.a2 = o.a2;
-  s.le1_1 = o.a1 <= 1.f; s.le1_2 = o.a2 <= 1.f;
-  return s;
-}
-__device__ __forceinline__ float act_apply(float v, const ActSpec& s) {
-  if (s.act >= 1) v = prelu_mm(v, s.a1, s.le1_1);
-  if (s.act == 2) v = prelu_mm(v, s.a2, s.le1_2);
-  return v;
+
+__device__ __forceinline__ OutPtr out_ptr(const TensDesc& t, int b, int l, int chunk0, float inv_split) {
+  OutPtr o;
+  int ph = 0, ll = l;
+  if (t.split > 1) {
+    ll = fast_div(l, t.split, inv_split);
+    ph = l - ll * t.split;
+  }
+  const long long row = (long long)ph * t.nchunks * t.P + t.G + (long long)b * t.Lh + ll;
+  o.pstride = ((long long)t.P * 8) << t.esize_log2;
+  o.p = t.base + ((row * 8) << t.esize_log2) + (long long)chunk0 * o.pstride;
+  return o;
 }
 
-// stores 16 consecutive channels (chunks chunk0, chunk0+1) of one row
-__device__ __forceinline__ void store16(const RowAddr& r, int esize_log2, int chunk0, const float* v) {
-  char* p = r.p + (long long)chunk0 * r.pstride;
-  if (esize_log2 == 1) {
+template <bool LE1>
+__device__ __forceinline__ void store16_act(char* p, long long pstride, bool f32, int act, float a1, float a2, const float* v) {
+  float w[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    float x = v[i];
+    if (act >= 1) x = prelu_t<LE1>(x, a1);
+    if (act == 2) x = prelu_t<LE1>(x, a2);
+    w[i] = x;
+  }
+  if (!f32) {
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
       uint4 u;
       __nv_bfloat162* q = reinterpret_cast<__nv_bfloat162*>(&u);
 #pragma unroll
-      for (int i = 0; i < 4; ++i) q[i] = __floats2bfloat162_rn(v[8 * h + 2 * i], v[8 * h + 2 * i + 1]);
-      *reinterpret_cast<uint4*>(p + h * r.pstride) = u;
+      for (int i = 0; i < 4; ++i) q[i] = __floats2bfloat162_rn(w[8 * h + 2 * i], w[8 * h + 2 * i + 1]);
+      *reinterpret_cast<uint4*>(p + h * pstride) = u;
     }
   } else {
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
-      *reinterpret_cast<float4*>(p + h * r.pstride) = make_float4(v[8 * h], v[8 * h + 1], v[8 * h + 2], v[8 * h + 3]);
-      *reinterpret_cast<float4*>(p + h * r.pstride + 16) = make_float4(v[8 * h + 4], v[8 * h + 5], v[8 * h + 6], v[8 * h + 7]);
+      *reinterpret_cast<float4*>(p + h * pstride) = make_float4(w[8 * h], w[8 * h + 1], w[8 * h + 2], w[8 * h + 3]);
+      *reinterpret_cast<float4*>(p + h * pstride + 16) = make_float4(w[8 * h + 4], w[8 * h + 5], w[8 * h + 6], w[8 * h + 7]);
     }
   }
 }
@@ -200,9 +220,20 @@ __device__ __forceinline__ void add_unpack(const uint4* a, float* v) {
     }
   }
 }
+__device__ __forceinline__ void add_f32(const char* p, long long pstride, float* v) {
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const float4 x = *reinterpret_cast<const float4*>(p + h * pstride);
+    const float4 y = *reinterpret_cast<const float4*>(p + h * pstride + 16);
+    v[8 * h] += x.x; v[8 * h + 1] += x.y; v[8 * h + 2] += x.z; v[8 * h + 3] += x.w;
+    v[8 * h + 4] += y.x; v[8 * h + 5] += y.y; v[8 * h + 6] += y.z; v[8 * h + 7] += y.w;
+  }
+}
 
 // Epilogue of one warp: lane = TMEM lane = output row of its 128-row half of every tile.
-template <bool ADD, bool FILM, bool MULTI>
+// All per-tile address work is done once (no integer divisions, 64-bit pointers advanced by a
+// constant per column group); the column loop is TMEM load -> math -> 16-byte stores.
+template <bool ADD, bool FILM, bool MULTI, bool LE1>
 __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem_base, uint64_t* t_full, uint64_t* t_empty,
                                               const float* film_s, int warp, int lane) {
   const int sub = (warp - 2) >> 2;
@@ -211,39 +242,56 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
   const int ngroups = P.N_TILE >> 4;
   const uint32_t acc_stride = accum_stride_cols(P.N_TILE);
   const int n_acc = P.n_acc;
-  const int total_tiles = P.n_tiles_m * P.n_tiles_n;
+  const int ntn = P.n_tiles_n;
+  const int total_tiles = P.n_tiles_m * ntn;
   const bool a1_bf16 = ADD && P.add1.esize_log2 == 1;
   const bool a2_on = ADD && P.add2.base != nullptr;
   const bool a2_bf16 = a2_on && P.add2.esize_log2 == 1;
   const float scale = P.scale;
   const bool do_scale = scale != 1.f;
-  ActSpec as0 = act_spec(P.out[0]), as1 = act_spec(P.out[1]), as2 = act_spec(P.out[2]);
+  const int n_out = P.n_out;
+  const float inv_Lh = 1.f / (float)P.Lh_A;
+  const float inv_Cout = 1.f / (float)P.C_out;
+  float inv_split[3];
+  bool o_f32[3];
+#pragma unroll
+  for (int o = 0; o < 3; ++o) {
+    inv_split[o] = 1.f / (float)(P.out[o].t.split > 0 ? P.out[o].t.split : 1);
+    o_f32[o] = P.out[o].t.esize_log2 == 2;
+  }
+  const float inv_split_a1 = 1.f / (float)(P.add1.split > 0 ? P.add1.split : 1);
+  const float inv_split_a2 = 1.f / (float)(P.add2.split > 0 ? P.add2.split : 1);
 
+  int n_tile = blockIdx.x % ntn, m_tile = blockIdx.x / ntn;
+  const int dn = gridDim.x % ntn, dm = gridDim.x / ntn;
   int it = 0;
   for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-    const int n_tile = tile % P.n_tiles_n;
-    const int m_tile = tile / P.n_tiles_n;
     const int n0 = n_tile * P.N_TILE;
-    const int phase = n0 / P.C_out;
-    const int co0 = n0 - phase * P.C_out;
+    int phase = 0, co0 = n0;
+    if (P.up > 1) {
+      phase = fast_div(n0, P.C_out, inv_Cout);
+      co0 = n0 - phase * P.C_out;
+    }
     const int g = m_tile * kTileM + row_in_tile;
-    const int b = g / P.Lh_A;
+    const int b = fast_div(g, P.Lh_A, inv_Lh);
     const int m = g - b * P.Lh_A;
     const bool valid = (g < P.m_rows) && (m < P.M_valid);
     const int l_out = P.up * m + phase;
     const int chunk_base = co0 >> 3;
+    // next tile of this CTA (static round robin)
+    n_tile += dn; m_tile += dm;
+    if (n_tile >= ntn) { n_tile -= ntn; ++m_tile; }
 
-    RowAddr ro[3], ra1, ra2;
+    OutPtr op[3], pa1, pa2;
 #pragma unroll
     for (int o = 0; o < 3; ++o) {
-      if (o < P.n_out && valid && (MULTI || o == 0)) ro[o] = row_addr(P.out[o].t, b, l_out);
-      else { ro[o].p = nullptr; ro[o].pstride = 0; }
+      if (o < n_out && valid && (MULTI || o == 0)) op[o] = out_ptr(P.out[o].t, b, l_out, chunk_base, inv_split[o]);
+      else { op[o].p = nullptr; op[o].pstride = 0; }
     }
+    pa1.p = pa2.p = nullptr; pa1.pstride = pa2.pstride = 0;
     if (ADD && valid) {
-      ra1 = row_addr(P.add1, b, l_out);
-      ra2 = row_addr(P.add2, b, l_out);
-    } else {
-      ra1.p = ra2.p = nullptr; ra1.pstride = ra2.pstride = 0;
+      pa1 = out_ptr(P.add1, b, l_out, chunk_base, inv_split_a1);
+      if (a2_on) pa2 = out_ptr(P.add2, b, l_out, chunk_base, inv_split_a2);
     }
     float* rm_row = (MULTI && P.rm_out && valid) ? P.rm_out + (long long)g * P.rm_ld + n0 : nullptr;
 
@@ -257,14 +305,15 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
 
     auto add_issue = [&](int cg, AddRegs& ad) {
       if (!ADD) return;
-      const int ch = chunk_base + 2 * cg;
-      if (a1_bf16 && ra1.p) {
-        ad.a1[0] = *reinterpret_cast<const uint4*>(ra1.p + (long long)ch * ra1.pstride);
-        ad.a1[1] = *reinterpret_cast<const uint4*>(ra1.p + (long long)(ch + 1) * ra1.pstride);
+      if (a1_bf16 && pa1.p) {
+        const char* q = pa1.p + (long long)(2 * cg) * pa1.pstride;
+        ad.a1[0] = *reinterpret_cast<const uint4*>(q);
+        ad.a1[1] = *reinterpret_cast<const uint4*>(q + pa1.pstride);
       }
-      if (a2_bf16 && ra2.p) {
-        ad.a2[0] = *reinterpret_cast<const uint4*>(ra2.p + (long long)ch * ra2.pstride);
-        ad.a2[1] = *reinterpret_cast<const uint4*>(ra2.p + (long long)(ch + 1) * ra2.pstride);
+      if (a2_bf16 && pa2.p) {
+        const char* q = pa2.p + (long long)(2 * cg) * pa2.pstride;
+        ad.a2[0] = *reinterpret_cast<const uint4*>(q);
+        ad.a2[1] = *reinterpret_cast<const uint4*>(q + pa2.pstride);
       }
     };
 
@@ -273,29 +322,12 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
       float v[16];
 #pragma unroll
       for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
-      const int ch = chunk_base + 2 * cg;
       if (ADD) {
         if (a1_bf16) add_unpack(ad.a1, v);
-        else {
-          float t[8];
-#pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            load8(ra1, 2, ch + h, t);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) v[8 * h + i] += t[i];
-          }
-        }
+        else add_f32(pa1.p + (long long)(2 * cg) * pa1.pstride, pa1.pstride, v);
         if (a2_on) {
           if (a2_bf16) add_unpack(ad.a2, v);
-          else {
-            float t[8];
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-              load8(ra2, 2, ch + h, t);
-#pragma unroll
-              for (int i = 0; i < 8; ++i) v[8 * h + i] += t[i];
-            }
-          }
+          else add_f32(pa2.p + (long long)(2 * cg) * pa2.pstride, pa2.pstride, v);
         }
       }
       if (do_scale) {
@@ -314,26 +346,16 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
           v[4 * i + 3] = fmaf(gq.w, v[4 * i + 3], bq.w);
         }
       }
-      if (!MULTI) {
-        float w[16];
+      if (MULTI && rm_row) {
+        float4* dst = reinterpret_cast<float4*>(rm_row + 16 * cg);
 #pragma unroll
-        for (int i = 0; i < 16; ++i) w[i] = act_apply(v[i], as0);
-        store16(ro[0], P.out[0].t.esize_log2, ch, w);
-      } else {
-        if (rm_row) {
-          float4* dst = reinterpret_cast<float4*>(rm_row + 16 * cg);
+        for (int i = 0; i < 4; ++i) dst[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+      }
 #pragma unroll
-          for (int i = 0; i < 4; ++i) dst[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-        }
-#pragma unroll
-        for (int o = 0; o < 3; ++o) {
-          if (ro[o].p) {
-            const ActSpec& s = o == 0 ? as0 : (o == 1 ? as1 : as2);
-            float w[16];
-#pragma unroll
-            for (int i = 0; i < 16; ++i) w[i] = act_apply(v[i], s);
-            store16(ro[o], P.out[o].t.esize_log2, ch, w);
-          }
+      for (int o = 0; o < 3; ++o) {
+        if ((MULTI || o == 0) && op[o].p) {
+          store16_act<LE1>(op[o].p, op[o].pstride, o_f32[o], P.out[o].act, P.out[o].a1, P.out[o].a2, v);
+          op[o].p += 2 * op[o].pstride;
         }
       }
     };
@@ -369,6 +391,7 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
     }
   }
 }
+
 
 // ------------------------------------------------------------------ kernel
 __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_constant__ GemmParams P) {
@@ -610,17 +633,30 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
     const bool has_add = P.add1.base != nullptr && P.add_kc == 0;   // add_kc: the residual went through the tensor core
     const bool has_film = P.film != nullptr;
     const bool multi = P.n_out != 1 || P.rm_out != nullptr;
-    const int kind = (has_add ? 1 : 0) | (has_film ? 2 : 0) | (multi ? 4 : 0);
+    bool le1 = true;   // every PReLU slope of every output <= 1: two-instruction PReLU
+    for (int o = 0; o < 3; ++o)
+      if (o < P.n_out && ((P.out[o].act >= 1 && !(P.out[o].a1 <= 1.f)) || (P.out[o].act == 2 && !(P.out[o].a2 <= 1.f)))) le1 = false;
+    const int kind = (has_add ? 1 : 0) | (has_film ? 2 : 0) | (multi ? 4 : 0) | (le1 ? 8 : 0);
+#define UV_EPI(A, F, M, L) epilogue_role<A, F, M, L>(P, tmem_base, t_full, t_empty, film_s, warp, lane)
     switch (kind) {
-      case 0: epilogue_role<false, false, false>(P, tmem_base, t_full, t_empty, film_s, warp, lane); break;
-      case 1: epilogue_role<true, false, false>(P, tmem_base, t_full, t_empty, film_s, warp, lane); break;
-      case 2: epilogue_role<false, true, false>(P, tmem_base, t_full, t_empty, film_s, warp, lane); break;
-      case 3: epilogue_role<true, true, false>(P, tmem_base, t_full, t_empty, film_s, warp, lane); break;
-      case 4: epilogue_role<false, false, true>(P, tmem_base, t_full, t_empty, film_s, warp, lane); break;
-      case 5: epilogue_role<true, false, true>(P, tmem_base, t_full, t_empty, film_s, warp, lane); break;
-      case 6: epilogue_role<false, true, true>(P, tmem_base, t_full, t_empty, film_s, warp, lane); break;
-      default: epilogue_role<true, true, true>(P, tmem_base, t_full, t_empty, film_s, warp, lane); break;
+      case 0: UV_EPI(false, false, false, false); break;
+      case 1: UV_EPI(true, false, false, false); break;
+      case 2: UV_EPI(false, true, false, false); break;
+      case 3: UV_EPI(true, true, false, false); break;
+      case 4: UV_EPI(false, false, true, false); break;
+      case 5: UV_EPI(true, false, true, false); break;
+      case 6: UV_EPI(false, true, true, false); break;
+      case 7: UV_EPI(true, true, true, false); break;
+      case 8: UV_EPI(false, false, false, true); break;
+      case 9: UV_EPI(true, false, false, true); break;
+      case 10: UV_EPI(false, true, false, true); break;
+      case 11: UV_EPI(true, true, false, true); break;
+      case 12: UV_EPI(false, false, true, true); break;
+      case 13: UV_EPI(true, false, true, true); break;
+      case 14: UV_EPI(false, true, true, true); break;
+      default: UV_EPI(true, true, true, true); break;
     }
+#undef UV_EPI
   }
 
   tc_fence_before();

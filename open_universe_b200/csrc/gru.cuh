@@ -212,9 +212,10 @@ __global__ void __launch_bounds__(kGruThreads, 1) gru_kernel(const __grid_consta
   char* out_p[3] = {nullptr, nullptr, nullptr};
   long long out_inc[3] = {0, 0, 0};
   bool out_f32[3] = {false, false, false};
-  ActSpec acts[3];
+  int o_act[3];
+  float o_a1[3], o_a2[3];
 #pragma unroll
-  for (int o = 0; o < 3; ++o) acts[o] = act_spec(P.out[o]);
+  for (int o = 0; o < 3; ++o) { o_act[o] = P.out[o].act; o_a1[o] = P.out[o].a1; o_a2[o] = P.out[o].a2; }
   if (gvalid) {
     gi_p = P.gi + ((size_t)gb * P.Lh + t0) * (6 * H) + dir * 3 * H + ju;
     if (has_add) {
@@ -420,7 +421,7 @@ __global__ void __launch_bounds__(kGruThreads, 1) gru_kernel(const __grid_consta
         if (o < n_out) {
           float w[8];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) w[i] = act_apply(v[i], acts[o]);
+          for (int i = 0; i < 8; ++i) w[i] = apply_act(v[i], o_act[o], o_a1[o], o_a2[o]);
           if (out_f32[o]) {
             *reinterpret_cast<float4*>(out_p[o]) = make_float4(w[0], w[1], w[2], w[3]);
             *reinterpret_cast<float4*>(out_p[o] + 16) = make_float4(w[4], w[5], w[6], w[7]);

@@ -264,6 +264,8 @@ static int run_case(const Case& c, int swap_lbo, int num_sms) {
 static void run_perf(int num_sms) {
   struct PC { const char* name; int B, Lv, C, k, add, nout; } pcs[] = {
       {"L0 C32 k5", 64, 64160, 32, 5, 0, 1}, {"L0 C32 k3", 64, 64160, 32, 3, 0, 1}, {"L0 C32 k3 +add 2out", 64, 64160, 32, 3, 1, 2},
+      {"L0 C32 k3 +add 1out", 64, 64160, 32, 3, 1, 1}, {"L0 C32 k3 2out", 64, 64160, 32, 3, 0, 2}, {"L0 C32 k3 3out", 64, 64160, 32, 3, 0, 3},
+      {"L1 C64 k3 +add 1out", 64, 32080, 64, 3, 1, 1}, {"L1 C64 k3 2out", 64, 32080, 64, 3, 0, 2},
       {"L1 C64 k5", 64, 32080, 64, 5, 0, 1}, {"L1 C64 k3", 64, 32080, 64, 3, 0, 1}, {"L1 C64 k3 +add 2out", 64, 32080, 64, 3, 1, 2},
       {"L2 C128 k5", 64, 8020, 128, 5, 0, 1}, {"L2 C128 k3", 64, 8020, 128, 3, 0, 1}, {"L2 C128 k3 +add 2out", 64, 8020, 128, 3, 1, 2},
       {"L3 C256 k5", 64, 2005, 256, 5, 0, 1}, {"L3 C256 k3", 64, 2005, 256, 3, 0, 1},
@@ -286,6 +288,8 @@ static void run_perf(int num_sms) {
     p.m_rows = pc.B * A.Lh; p.Lh_A = A.Lh; p.M_valid = pc.Lv; p.up = 1; p.C_out = pc.C;
     p.has_bias = 1; p.scale = 1.f; p.n_out = pc.nout;
     p.out[0].t = desc_of(O); p.out[1].t = desc_of(O2); p.out[1].act = 1; p.out[1].a1 = 0.25f;
+    HT O3 = make_tensor(pc.B, pc.Lv, pc.C, 1, 2, false);
+    p.out[2].t = desc_of(O3); p.out[2].act = 1; p.out[2].a1 = 0.5f;
     HT AD = make_tensor(pc.B, pc.Lv, pc.C, 1, 2, false);
     if (pc.add) p.add1 = desc_of(AD);
     int* d_err; CK(cudaMalloc(&d_err, 4)); CK(cudaMemset(d_err, 0, 4));
@@ -303,7 +307,7 @@ static void run_perf(int num_sms) {
     double flop = 2.0 * pc.B * pc.Lv * (double)pc.C * pc.C * pc.k;
     double bytes = (double)pc.B * pc.Lv * pc.C * 2 * (1 + pc.nout + pc.add);
     printf("[perf %s] %.3f ms  %.1f TFLOP/s  %.0f GB/s (algorithmic reads + writes)\n", pc.name, ms, flop / ms * 1e-9, bytes / ms * 1e-6);
-    cudaFree(AD.dev); cudaFree(A.dev); cudaFree(O.dev); cudaFree(O2.dev); cudaFree(d_w); cudaFree(d_err);
+    cudaFree(O3.dev); cudaFree(AD.dev); cudaFree(A.dev); cudaFree(O.dev); cudaFree(O2.dev); cudaFree(d_w); cudaFree(d_err);
   }
 }
 
