@@ -131,6 +131,7 @@ static int launch_op(uv_plan* p, const uv_op& op, cudaStream_t s) {
       g.scale = op.scale; g.n_out = op.n_out;
       for (int i = 0; i < 3; ++i) g.out[i] = to_out(p, op.out[i]);
       g.rm_out = aptr<float>(p, op.rm_out); g.rm_ld = op.rm_ld;
+      g.rm_H = op.rm_out >= 0 ? op.H : 0; g.rm_Bp = op.i1;   // GEMM ops with a row-major output feed the GRU (H, batch pitch)
       g.err_flag = p->err_flag;
       CUDA_TRY(gemm_launch(g, p->model->num_sms, s));
       break;
@@ -188,22 +189,31 @@ static int launch_op(uv_plan* p, const uv_op& op, cudaStream_t s) {
       g.whh = wptr<const char>(p, op.p3);
       g.bhh = wptr<const float>(p, op.p4);
       g.B = op.B; g.T = op.T; g.H = op.H; g.Lh = op.Lh_A;
+      g.NB = op.i0; g.Bp = op.i1;
+      if (!gru_config_ok(g.H, g.NB) || g.Bp % g.NB || g.Bp < g.B) return fail(UV_ERR_INVALID, "GRU batch geometry (NB, Bp) invalid");
       g.add1 = to_desc(p, op.add1); g.scale = op.scale; g.n_out = op.n_out;
       for (int i = 0; i < 3; ++i) g.out[i] = to_out(p, op.out[i]);
+      if (g.add1.base && (g.add1.split != 1 || g.add1.esize_log2 != 1)) return fail(UV_ERR_INVALID, "GRU residual must be a plain bf16 tensor");
+      for (int i = 0; i < g.n_out; ++i)
+        if (g.out[i].t.split != 1) return fail(UV_ERR_INVALID, "GRU outputs must be plain tensors");
       g.err_flag = p->err_flag;
+      static const int gru_flags = getenv("UV_GRU_FLAGS") ? atoi(getenv("UV_GRU_FLAGS")) : 1;
+      g.dbg_flags = gru_flags;
       static const bool clk_dbg = getenv("UV_GRU_CLK") != nullptr;   // debug: per-phase clocks of one CTA, printed to stderr
       if (clk_dbg) {
         long long* d = nullptr;
-        CUDA_TRY(cudaMalloc(&d, 16 * sizeof(long long)));
-        CUDA_TRY(cudaMemset(d, 0, 16 * sizeof(long long)));
+        CUDA_TRY(cudaMalloc(&d, 32 * sizeof(long long)));
+        CUDA_TRY(cudaMemset(d, 0, 32 * sizeof(long long)));
         g.clk = d;
         CUDA_TRY(gru_launch(g, s));
-        long long h[16];
+        long long h[32];
         CUDA_TRY(cudaStreamSynchronize(s));
         CUDA_TRY(cudaMemcpy(h, d, sizeof(h), cudaMemcpyDeviceToHost));
         cudaFree(d);
         fprintf(stderr, "[gru clk/step] T=%d:", op.T);
         for (int i = 0; i < 10; ++i) fprintf(stderr, " p%d=%lld", i, h[i] / (op.T > 0 ? op.T : 1));
+        fprintf(stderr, " | publish->slice group landed (MMA thread; last = committed):");
+        for (int i = 16; i < 25; ++i) fprintf(stderr, " %lld", h[i] / (op.T > 1 ? op.T - 1 : 1));
         fprintf(stderr, "\n");
         break;
       }

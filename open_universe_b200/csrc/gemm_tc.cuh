@@ -293,7 +293,11 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
       pa1 = out_ptr(P.add1, b, l_out, chunk_base, inv_split_a1);
       if (a2_on) pa2 = out_ptr(P.add2, b, l_out, chunk_base, inv_split_a2);
     }
-    float* rm_row = (MULTI && P.rm_out && valid) ? P.rm_out + (long long)g * P.rm_ld + n0 : nullptr;
+    float* rm_row = nullptr;
+    if (MULTI && P.rm_out && valid) {
+      if (P.rm_H == 0) rm_row = P.rm_out + (long long)g * P.rm_ld + n0;
+      else rm_row = P.rm_out + ((long long)m * 16 * P.rm_Bp + b) * (3 * (P.rm_H >> 3) + 4);   // (t, b) corner of the GRU layout
+    }
 
     const int stage = it % n_acc;
     mbar_wait(smem_u32(&t_full[stage]), (it / n_acc) & 1, P.err_flag, 6);
@@ -348,6 +352,15 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
       }
       if (MULTI && rm_row) {
         float4* dst = reinterpret_cast<float4*>(rm_row + 16 * cg);
+        if (P.rm_H) {
+          // column n = dir*3H + gate*H + rank*U + u  ->  block (dir, rank), row b, offset gate*U + u (16 columns never straddle: U % 16 == 0)
+          const int H = P.rm_H, U = H >> 3, S = 3 * U + 4;
+          const int n = n0 + 16 * cg;
+          const int dirn = n / (3 * H), rem = n - dirn * 3 * H;
+          const int gate = rem / H, j = rem - gate * H;
+          const int rank = j / U, u = j - rank * U;
+          dst = reinterpret_cast<float4*>(rm_row + (long long)(dirn * 8 + rank) * P.rm_Bp * S + gate * U + u);
+        }
 #pragma unroll
         for (int i = 0; i < 4; ++i) dst[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
       }

@@ -67,6 +67,7 @@ struct GemmParams {
   OutDesc out[3];
   float* rm_out;     // optional f32 row-major output [m_rows][rm_ld], column n_glob
   int rm_ld;
+  int rm_H, rm_Bp;   // rm_H > 0: rm_out is the GRU gate-input layout [t][dir][rank 8][b < rm_Bp][3U + 4] (gru.cuh), H = rm_H
   // ---- pipeline (filled by host)
   int na_stages, nb_stages;
   int a_stage_bytes, b_stage_bytes;

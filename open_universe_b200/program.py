@@ -99,6 +99,24 @@ class Program:
         return self.emit(op, name)
 
 
+def gru_geometry(H, B):
+    """(NB, Bp, S): utterances per GRU cluster, batch pitch and row pitch (floats) of the gate-input
+    buffer [t][dir][rank 8][b < Bp][S = 3U + 4].  Mirrors gru_smem_layout() in csrc/gru.cuh: NB is limited
+    by the gate-thread mapping (U/8 * NB <= 256), the 227 KB of shared memory and, by choice, 32: the
+    recurrence is latency bound and more, smaller clusters shorten every phase of a step."""
+    U = H // 8
+
+    def smem(nb):
+        gh = _ru(3 * U * (nb + 1) * 4, 128)
+        return 3 * U * H * 2 + 2048 + 2 * nb * H * 2 + gh + nb * (3 * U + 4) * 4 + (U // 8) * nb * 144 + 128
+
+    nb = 32   # 32 utterances per cluster: 16 does not shorten a step (the h exchange is latency bound) and needs twice the clusters
+    while nb > 16 and ((U // 8) * nb > 256 or smem(nb) > 227 * 1024):
+        nb -= 16
+    nb = min(nb, _ru(B, 16))
+    return nb, _ru(B, nb), 3 * U + 4
+
+
 def _act(t, slope):
     return (t, 1, slope, 1.0)
 
@@ -235,13 +253,16 @@ def build_program(pm, cfg, B, T, n_steps):
     def gru_layer(name, x_raw, out_list, step=-1, add1=None, scale=1.0):
         """in-proj GEMM -> recurrence (score.py:117 / condition.py:212)."""
         H = L[name + ".hh"]["H"]
+        nb, bp, srow = gru_geometry(H, B)
         gi = pg.tensors.get("gi")
         if gi is None:
-            gi = pg.alloc(lb.P * 6 * H * 4)
+            gi = pg.alloc(Fr * 16 * bp * srow * 4)
             pg.tensors["gi"] = gi
-        pg.gemm(name + ".ih", name + ".ih", x_raw, lb, lb.L, [], step, rm_out=gi)
+        op = pg.gemm(name + ".ih", name + ".ih", x_raw, lb, lb.L, [], step, rm_out=gi)
+        op.H, op.i1 = H, bp           # the epilogue scatters into the GRU's [t][dir][rank][b][3U+4] layout
         op = new_op(_abi.OP_GRU, step)
         op.B, op.T, op.H, op.Lh_A = B, Fr, H, lb.Lh
+        op.i0, op.i1 = nb, bp
         op.p0, op.p3, op.p4 = gi, L[name + ".hh"]["whh_w"], L[name + ".hh"]["bhh_w"]
         if add1 is not None:
             op.add1 = add1

@@ -105,7 +105,10 @@ class Emulator:
         valid = m < op.M_valid
         b_idx, m, acc = b_idx[valid], m[valid], acc[valid]
         if op.rm_out >= 0:
-            rm = self.a_f32(op.rm_out, M * op.rm_ld).view(M, op.rm_ld)
+            # GRU gate-input layout [t][dir][rank 8][b < Bp][3U + 4] (csrc/gru.cuh)
+            H, Bp = op.H, op.i1
+            U, S = H // 8, 3 * (H // 8) + 4
+            rm = self.a_f32(op.rm_out, op.M_valid * 16 * Bp * S).view(op.M_valid, 2, 8, Bp, S)
         # the kernel adds the bias on the tensor core from its packed hi + lo bf16 image
         bias = bias_n[: op.C_out] if bias_n is not None else None
         film = self.a_f32(op.film, 2 * op.C_out) if op.film >= 0 else None
@@ -122,7 +125,9 @@ class Emulator:
             if film is not None:
                 v = film[: op.C_out] * v + film[op.C_out :]
             if op.rm_out >= 0:
-                rm[g[valid], ph * op.C_out : (ph + 1) * op.C_out] = v
+                assert op.up == 1 and op.C_out == 6 * H
+                vv = v.view(-1, 2, 3, 8, U).permute(0, 1, 3, 2, 4).reshape(-1, 2, 8, 3 * U)  # [row, dir, rank, gate*U + u]
+                rm[m, :, :, b_idx, : 3 * U] = vv
             self._write_outs(op, b_idx, l, v)
 
     def op_prep(self, op, io):
@@ -235,20 +240,22 @@ class Emulator:
 
     def op_gru(self, op, round_h=True):
         B, T, H, Lh = op.B, op.T, op.H, op.Lh_A
-        rows = B * Lh
-        gi = self.a_f32(op.p0, rows * 6 * H).view(rows, 6 * H)
+        Bp, U = op.i1, H // 8
+        S = 3 * U + 4
+        gi_blk = self.a_f32(op.p0, T * 16 * Bp * S).view(T, 2, 8, Bp, S)[:, :, :, :B, : 3 * U]  # [t, dir, rank, b, gate*U+u]
+        # -> [b, t, dir*3H + gate*H + rank*U + u]
+        gi_bt = gi_blk.reshape(T, 2, 8, B, 3, U).permute(3, 0, 1, 4, 2, 5).reshape(B, T, 6 * H)
         bits = self.blob[op.p3 : op.p3 + 2 * 3 * H * H * 2].view(np.int16)
         whh = unpack_gru_whh(bits.copy(), H)
         bhh = self.w_f32(op.p4, 6 * H).view(2, 3 * H)
-        ridx = (torch.arange(B) * Lh)[:, None] + torch.arange(T)[None, :]  # [B, T]
         out = torch.zeros(B, T, 2 * H)
         for d in range(2):
             h = torch.zeros(B, H)
-            g_d = gi[:, d * 3 * H : (d + 1) * 3 * H]
+            g_d = gi_bt[:, :, d * 3 * H : (d + 1) * 3 * H]
             for t in (range(T) if d == 0 else range(T - 1, -1, -1)):
                 hb = h.to(torch.bfloat16).float() if round_h else h
                 gh = hb @ whh[d].t() + bhh[d]
-                git = g_d[ridx[:, t]]
+                git = g_d[:, t]
                 r = torch.sigmoid(git[:, :H] + gh[:, :H])
                 z = torch.sigmoid(git[:, H : 2 * H] + gh[:, H : 2 * H])
                 n = torch.tanh(git[:, 2 * H :] + r * gh[:, 2 * H :])
