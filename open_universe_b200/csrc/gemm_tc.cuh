@@ -38,7 +38,8 @@ constexpr int kSubM = 128;          // UMMA M
 constexpr int kTileM = 256;         // rows per CTA tile (two UMMA sub-tiles)
 constexpr int kMaxAStages = 12;
 constexpr int kMaxBStages = 8;
-constexpr int kGemmThreads = 320;   // producer warp, MMA warp, 2 x 4 epilogue warps
+constexpr int kEpiWarps = 8;        // 4 TMEM lane quarters x 2 sub-tiles (16 = two column halves each: measured slower, the multi-output paths spill at 112 registers)
+constexpr int kGemmThreads = 64 + 32 * kEpiWarps;   // producer warp, MMA warp, epilogue warps
 constexpr int kMaxAcc = 4;          // TMEM accumulator stages
 constexpr int kOnesBytes = 2 * kSubM * 16;   // [2 chunks][128 rows][8] bf16
 constexpr int kFilmMaxC = 768;
@@ -69,6 +70,18 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
       "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.b32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// Non-blocking probe (try_wait may suspend the thread for a while when the phase is not complete).
+__device__ __forceinline__ bool mbar_test_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
       "selp.b32 %0, 1, 0, p;\n\t}"
       : "=r"(ok)
       : "r"(bar), "r"(parity)
@@ -176,15 +189,16 @@ __device__ __forceinline__ OutPtr out_ptr(const TensDesc& t, int b, int l, int c
   return o;
 }
 
+// 16 columns -> one output tensor.  a1 = 1 stands for "no activation" (max(v, v) = v), so the common
+// cases are branch free; the second slope is the rare double activation.
 template <bool LE1>
-__device__ __forceinline__ void store16_act(char* p, long long pstride, bool f32, int act, float a1, float a2, const float* v) {
+__device__ __forceinline__ void store16_act(char* p, long long pstride, bool f32, float a1, bool dbl, float a2, const float* v) {
   float w[16];
 #pragma unroll
-  for (int i = 0; i < 16; ++i) {
-    float x = v[i];
-    if (act >= 1) x = prelu_t<LE1>(x, a1);
-    if (act == 2) x = prelu_t<LE1>(x, a2);
-    w[i] = x;
+  for (int i = 0; i < 16; ++i) w[i] = prelu_t<LE1>(v[i], a1);
+  if (dbl) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) w[i] = prelu_t<LE1>(w[i], a2);
   }
   if (!f32) {
 #pragma unroll
@@ -231,15 +245,21 @@ __device__ __forceinline__ void add_f32(const char* p, long long pstride, float*
 }
 
 // Epilogue of one warp: lane = TMEM lane = output row of its 128-row half of every tile.
-// All per-tile address work is done once (no integer divisions, 64-bit pointers advanced by a
-// constant per column group); the column loop is TMEM load -> math -> 16-byte stores.
+// The work is a flat sequence of units (tile, 16-column group) run as a two-buffer software pipeline
+// that crosses tile boundaries: while unit u is processed, the TMEM load of unit u+1 is in flight, also
+// when u+1 is the first group of the next tile (its accumulator barrier is probed without blocking).
+// Per-tile address work is done once (no integer divisions; 64-bit pointers advance by a constant per
+// group) and overlaps that load.
 template <bool ADD, bool FILM, bool MULTI, bool LE1>
 __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem_base, uint64_t* t_full, uint64_t* t_empty,
                                               const float* film_s, int warp, int lane) {
-  const int sub = (warp - 2) >> 2;
+  const int sub = ((warp - 2) >> 2) & 1;
+  const int chalf = (warp - 2) >> 3;            // with 16 epilogue warps: which half of the column groups
   const int quarter = warp & 3;                 // a warp may only touch TMEM lanes 32*(warp%4)..+31
   const int row_in_tile = sub * kSubM + quarter * 32 + lane;
   const int ngroups = P.N_TILE >> 4;
+  const int g_begin = (kEpiWarps == 16 && chalf) ? (ngroups + 1) >> 1 : 0;
+  const int g_end = (kEpiWarps == 16 && !chalf) ? (ngroups + 1) >> 1 : ngroups;
   const uint32_t acc_stride = accum_stride_cols(P.N_TILE);
   const int n_acc = P.n_acc;
   const int ntn = P.n_tiles_n;
@@ -252,156 +272,199 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
   const int n_out = P.n_out;
   const float inv_Lh = 1.f / (float)P.Lh_A;
   const float inv_Cout = 1.f / (float)P.C_out;
-  float inv_split[3];
-  bool o_f32[3];
+  float inv_split[3], o_a1[3];
+  bool o_f32[3], o_dbl[3];
 #pragma unroll
   for (int o = 0; o < 3; ++o) {
     inv_split[o] = 1.f / (float)(P.out[o].t.split > 0 ? P.out[o].t.split : 1);
     o_f32[o] = P.out[o].t.esize_log2 == 2;
+    o_a1[o] = P.out[o].act >= 1 ? P.out[o].a1 : 1.f;
+    o_dbl[o] = P.out[o].act == 2;
   }
   const float inv_split_a1 = 1.f / (float)(P.add1.split > 0 ? P.add1.split : 1);
   const float inv_split_a2 = 1.f / (float)(P.add2.split > 0 ? P.add2.split : 1);
+  const uint32_t t_lane = tmem_base + (uint32_t)sub * acc_stride + ((uint32_t)(quarter * 32) << 16);
+  const uint32_t t_stage = 2u * acc_stride;
+  const uint32_t full0 = smem_u32(t_full), empty0 = smem_u32(t_empty);
 
+  if ((int)blockIdx.x >= total_tiles) return;
+  int tiles_left = (total_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
   int n_tile = blockIdx.x % ntn, m_tile = blockIdx.x / ntn;
   const int dn = gridDim.x % ntn, dm = gridDim.x / ntn;
-  int it = 0;
-  for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-    const int n0 = n_tile * P.N_TILE;
-    int phase = 0, co0 = n0;
+
+  // state of the tile being processed
+  int stage = 0;
+  uint32_t phase = 0;
+  bool valid = false;
+  int n0 = 0, co0 = 0;
+  OutPtr op[3], pa1, pa2;
+  float* rm_row = nullptr;
+#pragma unroll
+  for (int o = 0; o < 3; ++o) { op[o].p = nullptr; op[o].pstride = 0; }
+  pa1.p = pa2.p = nullptr; pa1.pstride = pa2.pstride = 0;
+
+  auto tile_setup = [&]() {
+    n0 = n_tile * P.N_TILE;
+    int ph = 0;
+    co0 = n0;
     if (P.up > 1) {
-      phase = fast_div(n0, P.C_out, inv_Cout);
-      co0 = n0 - phase * P.C_out;
+      ph = fast_div(n0, P.C_out, inv_Cout);
+      co0 = n0 - ph * P.C_out;
     }
     const int g = m_tile * kTileM + row_in_tile;
     const int b = fast_div(g, P.Lh_A, inv_Lh);
     const int m = g - b * P.Lh_A;
-    const bool valid = (g < P.m_rows) && (m < P.M_valid);
-    const int l_out = P.up * m + phase;
+    valid = (g < P.m_rows) && (m < P.M_valid);
+    const int l_out = P.up * m + ph;
     const int chunk_base = co0 >> 3;
-    // next tile of this CTA (static round robin)
-    n_tile += dn; m_tile += dm;
+    n_tile += dn; m_tile += dm;   // next tile of this CTA (static round robin)
     if (n_tile >= ntn) { n_tile -= ntn; ++m_tile; }
-
-    OutPtr op[3], pa1, pa2;
 #pragma unroll
     for (int o = 0; o < 3; ++o) {
-      if (o < n_out && valid && (MULTI || o == 0)) op[o] = out_ptr(P.out[o].t, b, l_out, chunk_base, inv_split[o]);
-      else { op[o].p = nullptr; op[o].pstride = 0; }
+      if (o < n_out && valid && (MULTI || o == 0)) op[o] = out_ptr(P.out[o].t, b, l_out, chunk_base + 2 * g_begin, inv_split[o]);
+      else op[o].p = nullptr;
     }
-    pa1.p = pa2.p = nullptr; pa1.pstride = pa2.pstride = 0;
-    if (ADD && valid) {
-      pa1 = out_ptr(P.add1, b, l_out, chunk_base, inv_split_a1);
-      if (a2_on) pa2 = out_ptr(P.add2, b, l_out, chunk_base, inv_split_a2);
-    }
-    float* rm_row = nullptr;
-    if (MULTI && P.rm_out && valid) {
-      if (P.rm_H == 0) rm_row = P.rm_out + (long long)g * P.rm_ld + n0;
-      else rm_row = P.rm_out + ((long long)m * 16 * P.rm_Bp + b) * (3 * (P.rm_H >> 3) + 4);   // (t, b) corner of the GRU layout
-    }
-
-    const int stage = it % n_acc;
-    mbar_wait(smem_u32(&t_full[stage]), (it / n_acc) & 1, P.err_flag, 6);
-    tc_fence_after();
-    const uint32_t taddr = tmem_base + (uint32_t)(stage * 2 + sub) * acc_stride + ((uint32_t)(quarter * 32) << 16);
-
-    uint32_t r0[16], r1[16];
-    AddRegs ad0, ad1;
-
-    auto add_issue = [&](int cg, AddRegs& ad) {
-      if (!ADD) return;
-      if (a1_bf16 && pa1.p) {
-        const char* q = pa1.p + (long long)(2 * cg) * pa1.pstride;
-        ad.a1[0] = *reinterpret_cast<const uint4*>(q);
-        ad.a1[1] = *reinterpret_cast<const uint4*>(q + pa1.pstride);
+    if (ADD) {
+      pa1.p = pa2.p = nullptr;
+      if (valid) {
+        pa1 = out_ptr(P.add1, b, l_out, chunk_base, inv_split_a1);
+        if (a2_on) pa2 = out_ptr(P.add2, b, l_out, chunk_base, inv_split_a2);
       }
-      if (a2_bf16 && pa2.p) {
-        const char* q = pa2.p + (long long)(2 * cg) * pa2.pstride;
-        ad.a2[0] = *reinterpret_cast<const uint4*>(q);
-        ad.a2[1] = *reinterpret_cast<const uint4*>(q + pa2.pstride);
+    }
+    if (MULTI) {
+      rm_row = nullptr;
+      if (P.rm_out && valid) {
+        if (P.rm_H == 0) rm_row = P.rm_out + (long long)g * P.rm_ld + n0;
+        else rm_row = P.rm_out + ((long long)m * 16 * P.rm_Bp + b) * (3 * (P.rm_H >> 3) + 4);   // (t, b) corner of the GRU layout
       }
+    }
+  };
+
+  struct AddRegs ad0, ad1;
+  auto add_issue = [&](int g16, AddRegs& ad) {
+    if (!ADD) return;
+    if (a1_bf16 && pa1.p) {
+      const char* q = pa1.p + (long long)(2 * g16) * pa1.pstride;
+      ad.a1[0] = *reinterpret_cast<const uint4*>(q);
+      ad.a1[1] = *reinterpret_cast<const uint4*>(q + pa1.pstride);
+    }
+    if (a2_bf16 && pa2.p) {
+      const char* q = pa2.p + (long long)(2 * g16) * pa2.pstride;
+      ad.a2[0] = *reinterpret_cast<const uint4*>(q);
+      ad.a2[1] = *reinterpret_cast<const uint4*>(q + pa2.pstride);
+    }
+  };
+
+  auto process = [&](int g16, const uint32_t* r, const AddRegs& ad) {
+    if (!valid) return;
+    float v[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+    if (ADD) {
+      if (a1_bf16) add_unpack(ad.a1, v);
+      else add_f32(pa1.p + (long long)(2 * g16) * pa1.pstride, pa1.pstride, v);
+      if (a2_on) {
+        if (a2_bf16) add_unpack(ad.a2, v);
+        else add_f32(pa2.p + (long long)(2 * g16) * pa2.pstride, pa2.pstride, v);
+      }
+    }
+    if (do_scale) {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) v[i] *= scale;
+    }
+    if (FILM) {
+      const float4* ga = reinterpret_cast<const float4*>(film_s + co0 + 16 * g16);
+      const float4* be = reinterpret_cast<const float4*>(film_s + P.C_out + co0 + 16 * g16);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float4 gq = ga[i], bq = be[i];
+        v[4 * i] = fmaf(gq.x, v[4 * i], bq.x);
+        v[4 * i + 1] = fmaf(gq.y, v[4 * i + 1], bq.y);
+        v[4 * i + 2] = fmaf(gq.z, v[4 * i + 2], bq.z);
+        v[4 * i + 3] = fmaf(gq.w, v[4 * i + 3], bq.w);
+      }
+    }
+    if (MULTI && rm_row) {
+      float4* dst = reinterpret_cast<float4*>(rm_row + 16 * g16);
+      if (P.rm_H) {
+        // column n = dir*3H + gate*H + rank*U + u  ->  block (dir, rank), row b, offset gate*U + u (16 columns never straddle: U % 16 == 0)
+        const int H = P.rm_H, U = H >> 3, S = 3 * U + 4;
+        const int n = n0 + 16 * g16;
+        const int dirn = n / (3 * H), rem = n - dirn * 3 * H;
+        const int gate = rem / H, j = rem - gate * H;
+        const int rank = j / U, u = j - rank * U;
+        dst = reinterpret_cast<float4*>(rm_row + (long long)(dirn * 8 + rank) * P.rm_Bp * S + gate * U + u);
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) dst[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+    }
+#pragma unroll
+    for (int o = 0; o < 3; ++o) {
+      if ((MULTI || o == 0) && op[o].p) {
+        store16_act<LE1>(op[o].p, op[o].pstride, o_f32[o], o_a1[o], o_dbl[o], P.out[o].a2, v);
+        op[o].p += 2 * op[o].pstride;
+      }
+    }
+  };
+
+  // Two-buffer software pipeline over this warp's 16-column groups of a tile (group g+1 loads while g is
+  // processed).  It crosses the tile boundary when the group count is even: the first group of the next
+  // tile is loaded into r0 while the last group (in r1) is processed, provided that accumulator is
+  // already complete.
+  uint32_t r0[16], r1[16];
+  const bool have = g_begin < g_end;
+  mbar_wait(full0, 0, P.err_flag, 6);
+  tc_fence_after();
+  if (have) tc_ld16_issue(t_lane + 16u * g_begin, r0);
+  for (; tiles_left > 0; --tiles_left) {
+    tile_setup();
+    add_issue(g_begin, ad0);
+    const uint32_t taddr = t_lane + (uint32_t)stage * t_stage;
+    int nstage = stage + 1;
+    uint32_t nphase = phase;
+    if (nstage == n_acc) { nstage = 0; nphase ^= 1u; }
+    const bool more_tiles = tiles_left > 1;
+    bool prefetched = false;
+    auto release = [&]() {   // this warp's part of the accumulator is in registers: the MMA warp may reuse it
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(empty0 + 8u * stage);
     };
-
-    auto process = [&](int cg, const uint32_t* r, const AddRegs& ad) {
-      if (!valid) return;
-      float v[16];
-#pragma unroll
-      for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
-      if (ADD) {
-        if (a1_bf16) add_unpack(ad.a1, v);
-        else add_f32(pa1.p + (long long)(2 * cg) * pa1.pstride, pa1.pstride, v);
-        if (a2_on) {
-          if (a2_bf16) add_unpack(ad.a2, v);
-          else add_f32(pa2.p + (long long)(2 * cg) * pa2.pstride, pa2.pstride, v);
-        }
-      }
-      if (do_scale) {
-#pragma unroll
-        for (int i = 0; i < 16; ++i) v[i] *= scale;
-      }
-      if (FILM) {
-        const float4* ga = reinterpret_cast<const float4*>(film_s + co0 + 16 * cg);
-        const float4* be = reinterpret_cast<const float4*>(film_s + P.C_out + co0 + 16 * cg);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const float4 gq = ga[i], bq = be[i];
-          v[4 * i] = fmaf(gq.x, v[4 * i], bq.x);
-          v[4 * i + 1] = fmaf(gq.y, v[4 * i + 1], bq.y);
-          v[4 * i + 2] = fmaf(gq.z, v[4 * i + 2], bq.z);
-          v[4 * i + 3] = fmaf(gq.w, v[4 * i + 3], bq.w);
-        }
-      }
-      if (MULTI && rm_row) {
-        float4* dst = reinterpret_cast<float4*>(rm_row + 16 * cg);
-        if (P.rm_H) {
-          // column n = dir*3H + gate*H + rank*U + u  ->  block (dir, rank), row b, offset gate*U + u (16 columns never straddle: U % 16 == 0)
-          const int H = P.rm_H, U = H >> 3, S = 3 * U + 4;
-          const int n = n0 + 16 * cg;
-          const int dirn = n / (3 * H), rem = n - dirn * 3 * H;
-          const int gate = rem / H, j = rem - gate * H;
-          const int rank = j / U, u = j - rank * U;
-          dst = reinterpret_cast<float4*>(rm_row + (long long)(dirn * 8 + rank) * P.rm_Bp * S + gate * U + u);
-        }
-#pragma unroll
-        for (int i = 0; i < 4; ++i) dst[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-      }
-#pragma unroll
-      for (int o = 0; o < 3; ++o) {
-        if ((MULTI || o == 0) && op[o].p) {
-          store16_act<LE1>(op[o].p, op[o].pstride, o_f32[o], P.out[o].act, P.out[o].a1, P.out[o].a2, v);
-          op[o].p += 2 * op[o].pstride;
-        }
-      }
-    };
-
-    // software pipeline: TMEM load + residual loads of group cg+1 fly while group cg is processed
-    tc_ld16_issue(taddr, r0);
-    add_issue(0, ad0);
-    for (int cg = 0; cg < ngroups; cg += 2) {
+    if (!have) release();
+    for (int g2 = g_begin; g2 < g_end; g2 += 2) {
       tc_ld_wait();
-      const bool more1 = cg + 1 < ngroups;
+      const bool more1 = g2 + 1 < g_end;
       if (more1) {
-        tc_ld16_issue(taddr + 16 * (cg + 1), r1);
-        add_issue(cg + 1, ad1);
+        tc_ld16_issue(taddr + 16u * (g2 + 1), r1);
+        add_issue(g2 + 1, ad1);
       } else {
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(smem_u32(&t_empty[stage]));
+        release();
       }
-      process(cg, r0, ad0);
+      process(g2, r0, ad0);
       if (more1) {
         tc_ld_wait();
-        const bool more2 = cg + 2 < ngroups;
-        if (more2) {
-          tc_ld16_issue(taddr + 16 * (cg + 2), r0);
-          add_issue(cg + 2, ad0);
+        if (g2 + 2 < g_end) {
+          tc_ld16_issue(taddr + 16u * (g2 + 2), r0);
+          add_issue(g2 + 2, ad0);
         } else {
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(smem_u32(&t_empty[stage]));
+          release();
+          // never block here: this group is still to be processed
+          if (more_tiles && mbar_test_wait(full0 + 8u * nstage, nphase)) {
+            tc_fence_after();
+            tc_ld16_issue(t_lane + (uint32_t)nstage * t_stage + 16u * g_begin, r0);
+            prefetched = true;
+          }
         }
-        process(cg + 1, r1, ad1);
+        process(g2 + 1, r1, ad1);
       }
     }
+    if (more_tiles && !prefetched) {
+      mbar_wait(full0 + 8u * nstage, nphase, P.err_flag, 6);
+      tc_fence_after();
+      if (have) tc_ld16_issue(t_lane + (uint32_t)nstage * t_stage + 16u * g_begin, r0);
+    }
+    stage = nstage;
+    phase = nphase;
   }
 }
 
@@ -433,7 +496,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
   if (threadIdx.x == 0) {
     for (int i = 0; i < kMaxAStages; ++i) { mbar_init(smem_u32(&a_full[i]), 1); mbar_init(smem_u32(&a_empty[i]), 1); }
     for (int i = 0; i < kMaxBStages; ++i) { mbar_init(smem_u32(&b_full[i]), 1); mbar_init(smem_u32(&b_empty[i]), 1); }
-    for (int i = 0; i < kMaxAcc; ++i) { mbar_init(smem_u32(&t_full[i]), 1); mbar_init(smem_u32(&t_empty[i]), 8); }
+    for (int i = 0; i < kMaxAcc; ++i) { mbar_init(smem_u32(&t_full[i]), 1); mbar_init(smem_u32(&t_empty[i]), kEpiWarps); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   // ones tile: K columns 0 and 1 are 1.0 (they meet the hi / lo halves of the bias image), the rest 0
@@ -555,90 +618,102 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
     }
   } else if (warp == 1) {
     // ============================== MMA issuer
+    // One thread; its instruction latency paces small-K layers, so descriptors are split into a constant
+    // high word and a low word (address >> 4 | LBO) that advances by plain 32-bit adds.
     if (elect_one()) {
       const uint32_t idesc = make_idesc(kSubM, P.N_TILE);
       const uint32_t lbo_a = a_slab_chunk_bytes, lbo_b = (uint32_t)P.N_TILE * 16u;
+      const uint32_t desc_hi = (128u >> 4) | (1u << 14);                       // SBO = 128 B, descriptor version 1
+      const uint32_t a_lo0 = (smem_u32(a_ring) >> 4) | ((lbo_a >> 4) << 16);
+      const uint32_t r_lo0 = (smem_u32(a_ring) >> 4) | (((uint32_t)kAddRowsBytes >> 4) << 16);   // residual slabs (no halo)
+      const uint32_t b_lo0 = (smem_u32(b_ring) >> 4) | ((lbo_b >> 4) << 16);
+      const uint32_t i_lo0 = (smem_u32(ident) >> 4) | ((lbo_b >> 4) << 16);
+      const uint32_t a_stage16 = (uint32_t)P.a_stage_bytes >> 4, b_stage16 = (uint32_t)P.b_stage_bytes >> 4;
+      const uint32_t a_kstep = (2u * lbo_a) >> 4, r_kstep = (2u * (uint32_t)kAddRowsBytes) >> 4, b_kstep = (2u * lbo_b) >> 4;
+      const uint32_t b_img16 = b_bytes >> 4;
       const uint64_t ones_desc = make_desc(smem_u32(ones), (uint32_t)kSubM * 16u, 128);
+      const int ksteps = P.KC >> 4;
+      auto dsc = [&](uint32_t lo) { return ((uint64_t)desc_hi << 32) | (uint64_t)lo; };
       if (P.b_resident) {
         mbar_wait(smem_u32(&b_full[0]), 0, P.err_flag, 7);
         tc_fence_after();
       }
-      int ia = 0, ib = 0, it = 0;
-      uint32_t pa = 0, pb = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-        const int as = it % n_acc;
-        mbar_wait(smem_u32(&t_empty[as]), ((it / n_acc) & 1) ^ 1, P.err_flag, 3);
+      int ia = 0, ib = 0, as = 0;
+      uint32_t pa = 0, pb = 0, pt = 1;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        mbar_wait(smem_u32(&t_empty[as]), pt, P.err_flag, 3);
         tc_fence_after();
         const uint32_t d0 = tmem_base + (uint32_t)(as * 2) * acc_stride;
         const uint32_t d1 = d0 + acc_stride;
         uint32_t accumulate = 0;
         if (bias_bytes) {
-          uint32_t bias_addr;
+          uint32_t bias_lo;
           if (P.b_resident) {
-            bias_addr = smem_u32(b_ring) + (uint32_t)n_img * b_bytes;
+            bias_lo = b_lo0 + (uint32_t)n_img * b_img16;
           } else {
             mbar_wait(smem_u32(&b_full[ib]), pb, P.err_flag, 5);
             tc_fence_after();
-            bias_addr = smem_u32(b_ring + (size_t)ib * P.b_stage_bytes);
+            bias_lo = b_lo0 + (uint32_t)ib * b_stage16;
           }
-          const uint64_t bd = make_desc(bias_addr, lbo_b, 128);
-          tc_mma_bf16(d0, ones_desc, bd, idesc, 0);
-          tc_mma_bf16(d1, ones_desc, bd, idesc, 0);
+          tc_mma_bf16(d0, ones_desc, dsc(bias_lo), idesc, 0);
+          tc_mma_bf16(d1, ones_desc, dsc(bias_lo), idesc, 0);
           accumulate = 1;
           if (!P.b_resident) {
             tc_commit(smem_u32(&b_empty[ib]));
             if (++ib == P.nb_stages) { ib = 0; pb ^= 1; }
           }
         }
-        for (int s = 0; s < P.n_src; ++s) {
-          for (int g = 0; g < P.n_groups; ++g) {
-            mbar_wait(smem_u32(&a_full[ia]), pa, P.err_flag, 4);
-            tc_fence_after();
-            const uint32_t a_addr = smem_u32(a_ring + (size_t)ia * P.a_stage_bytes);
-            for (int q = 0; q < n_shift; ++q) {
-              uint32_t b_addr;
-              if (P.b_resident) {
-                b_addr = smem_u32(b_ring) + (uint32_t)((s * P.n_groups + g) * n_shift + q) * b_bytes;
-              } else {
-                mbar_wait(smem_u32(&b_full[ib]), pb, P.err_flag, 5);
-                tc_fence_after();
-                b_addr = smem_u32(b_ring + (size_t)ib * P.b_stage_bytes);
-              }
-              for (int kk = 0; kk < (P.KC >> 4); ++kk) {
-                const uint32_t a_k = a_addr + q * 16 + kk * 2 * a_slab_chunk_bytes;
-                const uint64_t bd = make_desc(b_addr + kk * 2 * lbo_b, lbo_b, 128);
-                tc_mma_bf16(d0, make_desc(a_k, lbo_a, 128), bd, idesc, accumulate);
-                tc_mma_bf16(d1, make_desc(a_k + kSubM * 16, lbo_a, 128), bd, idesc, accumulate);
-                accumulate = 1;
-              }
-              if (!P.b_resident) {
-                tc_commit(smem_u32(&b_empty[ib]));
-                if (++ib == P.nb_stages) { ib = 0; pb ^= 1; }
-              }
+        uint32_t img_lo = b_lo0;   // resident weights: images are consumed in storage order
+        for (int sg = 0; sg < P.n_src * P.n_groups; ++sg) {
+          mbar_wait(smem_u32(&a_full[ia]), pa, P.err_flag, 4);
+          tc_fence_after();
+          const uint32_t a_lo = a_lo0 + (uint32_t)ia * a_stage16;
+          for (int q = 0; q < n_shift; ++q) {
+            uint32_t bl;
+            if (P.b_resident) {
+              bl = img_lo;
+              img_lo += b_img16;
+            } else {
+              mbar_wait(smem_u32(&b_full[ib]), pb, P.err_flag, 5);
+              tc_fence_after();
+              bl = b_lo0 + (uint32_t)ib * b_stage16;
             }
-            tc_commit(smem_u32(&a_empty[ia]));
-            if (++ia == P.na_stages) { ia = 0; pa ^= 1; }
+            uint32_t al = a_lo + (uint32_t)q;   // tap q = slab shifted by q rows of 16 B
+            for (int kk = 0; kk < ksteps; ++kk) {
+              tc_mma_bf16(d0, dsc(al), dsc(bl), idesc, accumulate);
+              tc_mma_bf16(d1, dsc(al + (uint32_t)(kSubM * 16 >> 4)), dsc(bl), idesc, accumulate);
+              accumulate = 1;
+              al += a_kstep;
+              bl += b_kstep;
+            }
+            if (!P.b_resident) {
+              tc_commit(smem_u32(&b_empty[ib]));
+              if (++ib == P.nb_stages) { ib = 0; pb ^= 1; }
+            }
           }
+          tc_commit(smem_u32(&a_empty[ia]));
+          if (++ia == P.na_stages) { ia = 0; pa ^= 1; }
         }
         if (P.add_kc) {
-          const uint32_t img_bytes = (uint32_t)P.N_TILE * P.add_kc * 2u;
+          const uint32_t img16 = ((uint32_t)P.N_TILE * P.add_kc * 2u) >> 4;
           for (int j = 0; j < P.N_TILE / P.add_kc; ++j) {
             mbar_wait(smem_u32(&a_full[ia]), pa, P.err_flag, 4);
             tc_fence_after();
-            const uint32_t a_addr = smem_u32(a_ring + (size_t)ia * P.a_stage_bytes);
-            const uint32_t i_addr = smem_u32(ident) + j * img_bytes;
+            uint32_t al = r_lo0 + (uint32_t)ia * a_stage16;
+            uint32_t bl = i_lo0 + (uint32_t)j * img16;
             for (int kk = 0; kk < (P.add_kc >> 4); ++kk) {
-              const uint32_t a_k = a_addr + kk * 2 * kAddRowsBytes;
-              const uint64_t bd = make_desc(i_addr + kk * 2 * lbo_b, lbo_b, 128);
-              tc_mma_bf16(d0, make_desc(a_k, kAddRowsBytes, 128), bd, idesc, accumulate);
-              tc_mma_bf16(d1, make_desc(a_k + kSubM * 16, kAddRowsBytes, 128), bd, idesc, accumulate);
+              tc_mma_bf16(d0, dsc(al), dsc(bl), idesc, accumulate);
+              tc_mma_bf16(d1, dsc(al + (uint32_t)(kSubM * 16 >> 4)), dsc(bl), idesc, accumulate);
               accumulate = 1;
+              al += r_kstep;
+              bl += b_kstep;
             }
             tc_commit(smem_u32(&a_empty[ia]));
             if (++ia == P.na_stages) { ia = 0; pa ^= 1; }
           }
         }
         tc_commit(smem_u32(&t_full[as]));
+        if (++as == n_acc) { as = 0; pt ^= 1; }
       }
     }
   } else {
