@@ -4,9 +4,10 @@ import ctypes as C
 
 UV_ABI_VERSION = 4
 
-OP_PREP, OP_MEL, OP_MEL_FIN, OP_CONV_IN, OP_GEMM, OP_GRU, OP_CONV_OUT, OP_INIT_X, OP_POST, OP_FILM = range(1, 11)
+OP_PREP, OP_MEL, OP_MEL_FIN, OP_CONV_IN, OP_GEMM, OP_GRU, OP_CONV_OUT, OP_INIT_X, OP_POST, OP_FILM, OP_CONVBLOCK = range(1, 12)
 OP_NAMES = {
     1: "PREP", 2: "MEL", 3: "MEL_FIN", 4: "CONV_IN", 5: "GEMM", 6: "GRU", 7: "CONV_OUT", 8: "INIT_X", 9: "POST", 10: "FILM",
+    11: "CONVBLOCK",
 }
 
 DT_BF16, DT_F32 = 1, 2

@@ -9,6 +9,7 @@
 #include "../../include/universe_b200.h"
 #include "gemm_tc.cuh"
 #include "gru.cuh"
+#include "convblock.cuh"
 #include "small_ops.cuh"
 
 using namespace uv;
@@ -134,6 +135,35 @@ static int launch_op(uv_plan* p, const uv_op& op, cudaStream_t s) {
       g.rm_H = op.rm_out >= 0 ? op.H : 0; g.rm_Bp = op.i1;   // GEMM ops with a row-major output feed the GRU (H, batch pitch)
       g.err_flag = p->err_flag;
       CUDA_TRY(gemm_launch(g, p->model->num_sms, s));
+      break;
+    }
+    case UV_OP_CONVBLOCK: {
+      CbParams c;
+      memset(&c, 0, sizeof(c));
+      if (op.a.split != 1 || op.a.dtype != 1) return fail(UV_ERR_INVALID, "fused ConvBlock input must be a plain bf16 tensor");
+      c.x_base = p->arena + op.a.off; c.x_P = op.a.P; c.x_G = op.a.G;
+      c.C = op.C;
+      c.w[0] = wptr<const char>(p, op.w_w); c.w[1] = wptr<const char>(p, op.p0); c.w[2] = wptr<const char>(p, op.p1);
+      for (int k = 0; k < 3; ++k) c.has_bias[k] = (op.i0 >> k) & 1;
+      c.m_rows = op.m_rows; c.Lh = op.Lh_A; c.M_valid = op.M_valid;
+      c.n_tiles = (op.m_rows + kCbRowsOut - 1) / kCbRowsOut;
+      c.cond = to_desc(p, op.add1); c.scale1 = op.f0;
+      c.film = aptr<const float>(p, op.film);
+      c.slope2 = op.f1; c.slope3 = op.f2;
+      c.h_raw = to_desc(p, op.add2); c.scale3 = op.scale;
+      c.n_out = op.n_out;
+      for (int i = 0; i < 3; ++i) c.out[i] = to_out(p, op.out[i]);
+      memset(&c.cond_out, 0, sizeof(c.cond_out));
+      if (op.i1) {
+        if (op.n_out > 2) return fail(UV_ERR_INVALID, "fused ConvBlock: at most two block outputs next to a stage-1 output");
+        c.cond_out = to_out(p, op.out[2]);
+        memset(&c.out[2], 0, sizeof(c.out[2]));
+      }
+      if ((c.cond.base && (c.cond.split != 1 || c.cond.esize_log2 != 1)) || (c.h_raw.base && (c.h_raw.split != 1 || c.h_raw.esize_log2 != 1)))
+        return fail(UV_ERR_INVALID, "fused ConvBlock: condition / residual must be plain bf16 tensors");
+      if (!cb_plan(c)) return fail(UV_ERR_INVALID, "fused ConvBlock: unsupported channel count");
+      c.err_flag = p->err_flag;
+      CUDA_TRY(convblock_launch(c, p->model->num_sms, s));
       break;
     }
     case UV_OP_PREP:

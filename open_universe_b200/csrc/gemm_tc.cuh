@@ -189,13 +189,17 @@ __device__ __forceinline__ OutPtr out_ptr(const TensDesc& t, int b, int l, int c
   return o;
 }
 
-// 16 columns -> one output tensor.  a1 = 1 stands for "no activation" (max(v, v) = v), so the common
-// cases are branch free; the second slope is the rare double activation.
+// 16 columns -> one output tensor.  a1 = 1 stands for "no activation"; both tests are warp uniform.
 template <bool LE1>
 __device__ __forceinline__ void store16_act(char* p, long long pstride, bool f32, float a1, bool dbl, float a2, const float* v) {
   float w[16];
+  if (a1 != 1.f) {
 #pragma unroll
-  for (int i = 0; i < 16; ++i) w[i] = prelu_t<LE1>(v[i], a1);
+    for (int i = 0; i < 16; ++i) w[i] = prelu_t<LE1>(v[i], a1);
+  } else {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) w[i] = v[i];
+  }
   if (dbl) {
 #pragma unroll
     for (int i = 0; i < 16; ++i) w[i] = prelu_t<LE1>(w[i], a2);

@@ -13,6 +13,7 @@ activation is applied by the producer's epilogue); raw copies are kept only
 where a residual / skip / condition needs them.
 """
 import math
+import os
 
 import numpy as np
 import torch
@@ -36,6 +37,22 @@ class Level:
         self.Lh = _ru(L + 2, 8)
         self.rows = B * self.Lh
         self.P = G + _ru(self.rows, 256) + G   # GEMM tiles are 256 rows (csrc/gemm_tc.cuh kTileM)
+
+
+FUSE_CONVBLOCKS = os.environ.get("UV_FUSE_CONVBLOCKS", "") == "1"   # experimental: one launch per C <= 64 ConvBlock (csrc/convblock.cuh); measured slower than three GEMM launches so far
+
+
+class _PartSink:
+    """Builds GEMM records exactly like Program.gemm() without emitting them (parts of a fused op)."""
+
+    def __init__(self, pg):
+        self.pg = pg
+
+    def gemm(self, *args, **kw):
+        n = len(self.pg.ops)
+        op = self.pg.gemm(*args, **kw)
+        del self.pg.ops[n:], self.pg.names[n:]
+        return op
 
 
 class Program:
@@ -243,12 +260,45 @@ def build_program(pm, cfg, B, T, n_steps):
         outs = [] if only_conv1 else [_act(c1, s2)]
         if cond_out is not None:
             outs.append(_raw(cond_out))
-        pg.gemm(name + ".conv1", name + ".conv1", h_act, lev, lev.L, outs, step, add1=cond,
-                scale=SQRT1_2 if cond is not None else 1.0, film=film)
+        lys = [L[name + f".conv{k}"] for k in (1, 2, 3)]
+        fuse = (
+            FUSE_CONVBLOCKS and not only_conv1 and v_add2 is None and C % 16 == 0 and C <= 64
+            and all(ly["KC"] == C and ly["N_TILE"] == C and ly["N_total"] == C and ly["up"] == 1 and ly["n_src"] == 1 for ly in lys)
+            and (lys[0]["smin"], lys[0]["smax"]) == (-2, 2) and all((ly["smin"], ly["smax"]) == (-1, 1) for ly in lys[1:])
+            and len(v_outs) <= (2 if cond_out is not None else 3)
+            and h_raw.split == 1 and h_raw.dtype == DT_BF16 and (cond is None or (cond.split == 1 and cond.dtype == DT_BF16))
+        )
+        sink = _PartSink(pg) if fuse else pg
+        g1 = sink.gemm(name + ".conv1", name + ".conv1", h_act, lev, lev.L, outs, step, add1=cond,
+                       scale=SQRT1_2 if cond is not None else 1.0, film=film)
         if only_conv1:
             return
-        pg.gemm(name + ".conv2", name + ".conv2", c1, lev, lev.L, [_act(c2, s3)], step)
-        pg.gemm(name + ".conv3", name + ".conv3", c2, lev, lev.L, v_outs, step, add1=h_raw, add2=v_add2, scale=v_scale)
+        g2 = sink.gemm(name + ".conv2", name + ".conv2", c1, lev, lev.L, [_act(c2, s3)], step)
+        g3 = sink.gemm(name + ".conv3", name + ".conv3", c2, lev, lev.L, v_outs, step, add1=h_raw, add2=v_add2, scale=v_scale)
+        if not fuse:
+            return
+        # one launch for the whole block (csrc/convblock.cuh); the three GEMM records stay attached for the
+        # CPU emulator, which runs them one after the other (same arithmetic, same bf16 intermediates)
+        op = new_op(_abi.OP_CONVBLOCK, step)
+        op.a, op.C = h_act, C
+        op.w_w, op.p0, op.p1 = (ly["w_w"] for ly in lys)
+        op.i0 = sum((1 << k) for k, g in enumerate((g1, g2, g3)) if g.bias_w >= 0)
+        op.m_rows, op.Lh_A, op.M_valid = lev.rows, lev.Lh, lev.L
+        if cond is not None:
+            op.add1 = cond
+        op.f0 = g1.scale
+        op.film = film
+        op.f1, op.f2 = s2, s3
+        op.add2 = h_raw
+        op.scale = v_scale
+        op.n_out = len(v_outs)
+        for i, (t, act, a1, a2) in enumerate(v_outs):
+            op.out[i].t, op.out[i].act, op.out[i].a1, op.out[i].a2 = t, act, a1, a2
+        if cond_out is not None:
+            op.i1 = 1
+            op.out[2].t = cond_out
+        op.parts = [g1, g2, g3]
+        pg.emit(op, name + ".block")
 
     def gru_layer(name, x_raw, out_list, step=-1, add1=None, scale=1.0):
         """in-proj GEMM -> recurrence (score.py:117 / condition.py:212)."""

@@ -293,6 +293,9 @@ class Emulator:
             self.op_film(op)
         elif t == _abi.OP_GRU:
             self.op_gru(op)
+        elif t == _abi.OP_CONVBLOCK:
+            for part in op.parts:   # fused on the GPU; here the three convs run one after the other
+                self.op_gemm(part)
         else:
             raise ValueError(t)
 

@@ -31,6 +31,11 @@ def op_outputs(op, pg):
             tens(f"out{i}", op.out[i].t)
         if t == _abi.OP_GEMM and op.rm_out >= 0:
             outs.append(("rm", op.rm_out, op.m_rows * op.rm_ld * 4, torch.float32))
+    elif t == _abi.OP_CONVBLOCK:
+        for i in range(op.n_out):
+            tens(f"out{i}", op.out[i].t)
+        if op.i1:
+            tens("cond", op.out[2].t)
     elif t == _abi.OP_PREP:
         outs += [("sig", op.p0, op.B * op.Lp * 4, torch.float32), ("rms", op.p1, op.B * 4, torch.float32)]
     elif t == _abi.OP_MEL:
