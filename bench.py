@@ -223,8 +223,21 @@ def run_native(args, wl, rank, world, local_rank):
     n_gemm = sum(1 for op in plan.pg.ops if op.type == _abi.OP_GEMM)
     achieved = fl["gemm"] * B / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
     eager_ms = sum(by_kind.values())
+    # measured DRAM bytes per launch of the same kernel (ncu pass over this command, profiles/roofline_traffic.json)
+    traffic, traffic_src = None, None
+    tpath = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    if os.path.exists(tpath):
+        tj = json.load(open(tpath))
+        if tj.get("kernel") == "gemm_tc_kernel":
+            traffic, traffic_src = tj["traffic_bytes_per_launch"], tj.get("source")
     roofline = dict(bound="tensor", kernel="gemm_tc_kernel", achieved=achieved, peak=pk["tensor"], unit="TFLOP/s",
-                    frac=achieved / pk["tensor"], traffic=None, peak_source=pk["src"] + " sustained bf16",
+                    frac=achieved / pk["tensor"], traffic=traffic, traffic_unit="bytes/launch (dram read + write, ncu)",
+                    traffic_source=traffic_src,
+                    hbm_view=(dict(achieved=traffic * n_gemm / (gemm_ms * 1e-3) / 1e9, peak=pk["hbm"], unit="GB/s",
+                                   frac=traffic * n_gemm / (gemm_ms * 1e-3) / 1e9 / pk["hbm"],
+                                   note="same launches seen as HBM traffic: the C <= 64 levels are HBM bound, the rest tensor bound")
+                              if traffic and gemm_ms > 0 else None),
+                    peak_source=pk["src"] + " sustained bf16",
                     launches_per_step=n_gemm, kernel_ms_per_step=gemm_ms, share_of_step=gemm_ms / eager_ms if eager_ms else None,
                     whole_step_tflops=fl["total"] * B * world / (ms * 1e-3) / 1e12)
     line = dict(metric="audio-sec enhanced/sec", value=audio_s / (ms * 1e-3), unit="audio-s/s", n_gpus=world, steps=args.steps,
