@@ -201,12 +201,8 @@ class Universe(torch.nn.Module):
             raise ValueError("open_universe_b200 supports single-channel conditioners (input_channels == 1)")
         if ensemble_stat not in ("mean", "median", "signal_median"):
             raise NotImplementedError()
-        if target is not None or fake_score_snr is not None:
-            raise NotImplementedError("the `target` / `fake_score_snr` sampler test hook is not implemented natively yet")
         if use_aux_signal or warm_start is not None:
             raise NotImplementedError("`use_aux_signal` / `warm_start` (signal decoupling layer) are not implemented natively yet")
-        if ensemble_stat == "signal_median" and ensemble is not None:
-            raise NotImplementedError("ensemble_stat='signal_median' is not implemented yet")
         if self.normalization_norm not in (2, "2"):
             raise NotImplementedError("only normalization_norm == 2 is supported")
         if self.diff_kwargs.get("schedule", "geometric") != "geometric":
@@ -219,8 +215,20 @@ class Universe(torch.nn.Module):
             mix = torch.stack([mix] * ensemble, dim=0).view((-1,) + mix_shape[1:])
 
         B, T = mix.shape[0], mix.shape[-1]
-        plan = self._get_plan(B, T, n_steps)
         dev = self._device()
+        if target is not None:
+            # "perfect score" test hook (reference universe.py:269-298): the networks are not evaluated at all
+            if dev.type != "cuda":
+                raise RuntimeError("open_universe_b200 runs only on a CUDA device")
+            if target.ndim == 1:
+                target = target[None, None, :]
+            elif target.ndim == 2:
+                target = target[:, None, :]
+            if ensemble is not None:
+                target = torch.stack([target] * ensemble, dim=0).view((-1,) + target.shape[1:])
+            x = self._enhance_known_score(mix.to(dev), target.to(dev), n_steps, epsilon, fake_score_snr, rng, keep_rms, noise)
+            return self._finish(x, x_ndim, ensemble, ensemble_stat, mix_shape if ensemble is not None else None)
+        plan = self._get_plan(B, T, n_steps)
         Lp = plan.pg.Lp
         mix_f = mix.reshape(B, T).to(device=dev, dtype=torch.float32).contiguous()
         if noise is None:
@@ -237,18 +245,93 @@ class Universe(torch.nn.Module):
         with torch.cuda.device(dev):
             plan.enhance(mix_f.data_ptr(), noise.data_ptr(), out.data_ptr(), dbg.data_ptr() if dbg is not None else None,
                          coefs, bool(keep_rms), stream)
-        x = out.to(mix.dtype)[:, None, :]
+        x = self._finish(out.to(mix.dtype)[:, None, :], x_ndim, ensemble, ensemble_stat, mix_shape if ensemble is not None else None)
+        if return_steps:
+            return x, dbg
+        return x
 
+    @staticmethod
+    def _finish(x, x_ndim, ensemble, ensemble_stat, mix_shape):
+        """Ensemble statistic and rank restoration (reference universe.py:359-373)."""
         if ensemble is not None:
-            x = x.view((-1,) + mix_shape)
-            x = x.mean(dim=0) if ensemble_stat == "mean" else x.median(dim=0).values
+            x = x.view((-1,) + tuple(mix_shape))
+            if ensemble_stat == "mean":
+                x = x.mean(dim=0)
+            elif ensemble_stat == "median":
+                x = x.median(dim=0).values
+            else:
+                x = signal_median(x)
         if x_ndim == 1:
             x = x[0, 0]
         elif x_ndim == 2:
             x = x[:, 0, :]
-        if return_steps:
-            return x, dbg
         return x
+
+    def _enhance_known_score(self, mix, target, n_steps, epsilon, fake_score_snr, rng, keep_rms, noise):
+        """enhance() with `target` given (reference universe.py:269-298,321-357): the score is the analytic
+        -(x - target) / sigma^2 plus white noise at `fake_score_snr` dB (default 5), so the sampler follows a
+        closed form.  Off the hot path: a handful of elementwise device ops, no network evaluation.
+        `noise`: optional injected list of the n_steps sampler draws (unit variance), as in enhance_debug."""
+        mix_len = mix.shape[-1]
+        mix_rms = mix.square().mean(dim=(-2, -1), keepdim=True).sqrt()
+        mix, pad = self.pad(mix)
+        target, _ = self.pad(target, pad=pad)
+        kw = dict(self.normalization_kwargs or {})
+        level = 10.0 ** (float(kw.get("level_db", 0.0)) / 20.0)
+
+        def norm2(sig):   # utils/norm.py:22-23,47-87 with norm = 2, zero_mean
+            sig = sig - sig.mean(dim=(1, 2), keepdim=True)
+            return sig * (level / sig.std(dim=(1, 2), keepdim=True).clamp(min=1e-5))
+
+        if kw.get("ref", "noisy") == "both":
+            target = norm2(target)
+        else:
+            mean = mix.mean(dim=(1, 2), keepdim=True)
+            gain = level / (mix - mean).std(dim=(1, 2), keepdim=True).clamp(min=1e-5)
+            target = (target - mean) * gain
+        score_snr = 5.0 if fake_score_snr is None else float(fake_score_snr)
+        sig = program.sampler_tables(self.model_config(), n_steps)[0].to(device=mix.device, dtype=mix.dtype)
+        delta_t = 1.0 / (n_steps - 1)
+        gamma = (float(self.diff_kwargs.sigma_max) / float(self.diff_kwargs.sigma_min)) ** -delta_t
+        eta = 1.0 - gamma ** epsilon
+        beta = math.sqrt(1.0 - gamma ** (2.0 * (epsilon - 1.0)))
+
+        def draw(i):
+            if noise is not None:
+                return noise[i].to(mix).reshape(target.shape)
+            return torch.randn(target.shape, dtype=mix.dtype, device=mix.device, generator=rng)
+
+        def score(x, s):
+            true = -(x - target) / s ** 2
+            rms = true.square().mean().sqrt() * 10.0 ** (-score_snr / 20.0)
+            return true + torch.randn(true.shape, dtype=true.dtype, device=true.device, generator=rng) * rms
+
+        x = draw(0) * sig[0]
+        for n in range(n_steps - 1):
+            sc = score(x, sig[n])
+            x = x + sig[n] ** 2 * eta * sc + beta * sig[n + 1] * draw(n + 1)
+        x = x + sig[-1] ** 2 * score(x, sig[-1])
+        x = self.unpad(x, pad)
+        x = torch.nn.functional.pad(x, (0, mix_len - x.shape[-1]))
+        if keep_rms:
+            x = x * (mix_rms / x.square().mean(dim=(-2, -1), keepdim=True).sqrt().clamp(min=1e-5))
+        scale = x.abs().max(dim=-1, keepdim=True).values
+        return torch.where(scale > 1.0, x / scale, x)
+
+
+def signal_median(signal):
+    """Ensemble member that is "the median" for the most samples (reference utils/stats.py:22-66): per sample,
+    the sorted position holding the member whose index is closest to n/2; the member index that this position
+    equals most often over the samples is returned whole.  signal: (ensemble, batch, ...) -> (batch, ...)."""
+    shape = signal.shape
+    flat = signal.flatten(start_dim=2)
+    n = flat.shape[0]
+    order = flat.sort(dim=0).indices
+    pos = (order - n / 2).abs().min(dim=0).indices                     # (batch, samples)
+    counts = torch.nn.functional.one_hot(pos, n).sum(dim=1)            # (batch, n)
+    select = counts.argmax(dim=1)
+    out = flat[select, torch.arange(flat.shape[1], device=flat.device)]
+    return out.reshape(shape[1:])
 
 
 class UniverseGAN(Universe):

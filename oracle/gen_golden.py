@@ -25,6 +25,10 @@ CASES = [
     ("pp16k_opts", "universepp_16k", 1, 2072, dict(n_steps=5, epsilon=1.7, keep_rms=True)),
     ("orig16k", "universe_16k", 2, 3000, {}),
     ("pp24k", "universepp_24k", 2, 3500, {}),
+    # enhance() keyword surface off the default path: known-score test hook (target + practically noiseless fake
+    # score, so the CPU generator of the reference does not matter) and the signal_median ensemble statistic
+    ("pp16k_target", "universepp_16k", 2, 3000, dict(fake_score_snr=200.0, keep_rms=True, with_target=True)),
+    ("pp16k_sigmed", "universepp_16k", 1, 2072, dict(n_steps=4, ensemble=3, ensemble_stat="signal_median")),
 ]
 
 
@@ -41,7 +45,10 @@ def make_inputs(B, T, tot_ds, n_steps, seed=1235):
 def main():
     os.makedirs(OUT, exist_ok=True)
     listing = {}
+    only = set(sys.argv[1:])   # optional: regenerate only the named cases
     for case, name, B, T, kw in CASES:
+        if only and case not in only:
+            continue
         ref, cfg = rh.build_reference_model(name)
         mine = config.instantiate(config.to_attr(cfg))
         testing.seed_weights(mine, seed=7)
@@ -50,10 +57,21 @@ def main():
         assert not unexpected and all(k.startswith("loss_") for k in missing), (missing[:5], unexpected[:5])
         tot_ds = ref.tot_ds
         n_steps = kw.get("n_steps", cfg["diffusion"]["n_steps"])
-        mix, noise = make_inputs(B, T, tot_ds, n_steps)
+        kw = dict(kw)
+        with_target = kw.pop("with_target", False)
+        mix, noise = make_inputs(B * (kw.get("ensemble") or 1), T, tot_ds, n_steps)
+        mix = mix[:B]
+        extra = {}
+        if with_target:
+            gt = torch.Generator().manual_seed(99)
+            extra["target"] = 0.05 * torch.randn(B, T, generator=gt)
+            kw["target"] = extra["target"][:, None, :]   # the reference wants the target in the mixture's 3-D shape
+            kw["rng"] = torch.Generator().manual_seed(5)
         out, steps = rh.run_reference_enhance(ref, mix, [n[:, None, :] for n in noise], **kw)
-        fix = dict(model=name, B=B, T=T, kwargs=kw, seed_weights=7, seed_inputs=1235,
-                   out=out.contiguous(), steps=torch.stack([s[:, 0] for s in steps]).contiguous())
+        kw.pop("target", None), kw.pop("rng", None)
+        fix = dict(model=name, B=B, T=T, kwargs=kw, seed_weights=7, seed_inputs=1235, with_target=with_target, **extra,
+                   out=out.contiguous(),
+                   steps=torch.stack([s[:, 0] for s in steps]).contiguous() if steps else torch.zeros(0))
         torch.save(fix, os.path.join(OUT, f"enhance_{case}.pt"))
         print(case, "out rms", out.pow(2).mean().sqrt().item(), "max", out.abs().max().item(),
               "net rms", [round(s.pow(2).mean().sqrt().item(), 4) for s in steps])
@@ -63,6 +81,8 @@ def main():
                 state_dict=[[k, list(v.shape)] for k, v in rsd.items()],
                 model_parameters=[list(p.shape) for p in ref.model_parameters()],
             )
+    if only:
+        return
     with open(os.path.join(OUT, "state_dict_layout.json"), "w") as f:
         json.dump(listing, f)
     # config files of the three named models, resolved (the reference yaml cannot travel either)

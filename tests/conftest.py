@@ -45,15 +45,16 @@ def build_model(model_name, seed=7):
 def golden_inputs(fix, tot_ds):
     """Rebuilds the inputs of oracle/gen_golden.py::make_inputs."""
     B, T = fix["B"], fix["T"]
+    Be = B * (fix["kwargs"].get("ensemble") or 1)   # the noise covers every ensemble member
     n_steps = fix["kwargs"].get("n_steps", 8)
     seed = fix["seed_inputs"]
     g = torch.Generator().manual_seed(seed)
-    mix = 0.1 * torch.randn(B, T, generator=g) + 0.01
+    mix = 0.1 * torch.randn(Be, T, generator=g) + 0.01
     mix[0] *= 30.0
     Lp = T + (tot_ds - T % tot_ds)
     gn = torch.Generator().manual_seed(seed + 1)
-    noise = torch.stack([torch.randn(B, Lp, generator=gn) for _ in range(n_steps)])
-    return mix, noise
+    noise = torch.stack([torch.randn(Be, Lp, generator=gn) for _ in range(n_steps)])
+    return mix[:B], noise
 
 
 GOLDEN_CASES = ["pp16k", "pp16k_opts", "orig16k", "pp24k"]

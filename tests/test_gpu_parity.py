@@ -82,6 +82,32 @@ def test_enhance_public_api_rng_ranks_and_ensemble():
         model.enhance(mix, use_aux_signal=True)
 
 
+def test_signal_median_ensemble_matches_reference_golden():
+    """ensemble=3, ensemble_stat="signal_median" (universe.py:261-264,359-368; utils/stats.py:22-66)."""
+    fix = load_fixture("pp16k_sigmed")
+    model, _ = _gpu_model(fix["model"], fix["seed_weights"])
+    mix, noise = golden_inputs(fix, model.tot_ds)
+    kw = fix["kwargs"]
+    out = model._enhance_impl(mix.cuda(), kw["n_steps"], None, None, None, None, False, False, kw["ensemble"],
+                              kw["ensemble_stat"], None, noise=noise.cuda(), return_steps=False).cpu()
+    assert out.shape == fix["out"].shape
+    assert uo.rel_l2(out, fix["out"]) < TOL and uo.si_sdr(out, fix["out"]).min() > SISDR_MIN
+
+
+def test_known_score_hook_matches_reference_golden():
+    """target= / fake_score_snr= (universe.py:269-298): analytic score, closed-form sampler trajectory."""
+    fix = load_fixture("pp16k_target")
+    model, _ = _gpu_model(fix["model"], fix["seed_weights"])
+    mix, noise = golden_inputs(fix, model.tot_ds)
+    kw = fix["kwargs"]
+    out = model._enhance_impl(mix.cuda(), None, None, fix["target"].cuda(), kw["fake_score_snr"], None, False, kw["keep_rms"],
+                              None, "median", None, noise=noise.cuda(), return_steps=False).cpu()
+    assert uo.rel_l2(out, fix["out"]) < 1e-4
+    # public call, device generator, default 5 dB score noise: runs, finite, peak-limited
+    o2 = model.enhance(mix.cuda(), target=fix["target"].cuda(), rng=torch.Generator(device="cuda").manual_seed(3))
+    assert o2.shape == mix.shape and torch.isfinite(o2).all() and o2.abs().max() <= 1.0 + 1e-6
+
+
 def test_deterministic_and_batch_independent():
     model, _ = _gpu_model("universepp_16k")
     B, T = 4, 3200
