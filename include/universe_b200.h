@@ -143,6 +143,9 @@ int uv_enhance(uv_plan* p, const float* mix, const float* noise, float* out, flo
 int uv_run_ops(uv_plan* p, int first, int last, const float* mix, const float* noise, float* out,
                float* dbg_net, const uv_step_coef* coef, int keep_rms, void* stream);
 int uv_arena_read(uv_plan* p, size_t off, void* host_dst, size_t nbytes);
+/* Device address of the plan's arena (for zero-copy views of intermediate tensors, e.g. the conditioner's
+ * y_hat consumed by aux_to_wav, reference universe_gan.py:147-151; the caller must not free it).          */
+void* uv_plan_arena_ptr(uv_plan* p);
 int uv_arena_write(uv_plan* p, size_t off, const void* host_src, size_t nbytes);
 
 /* Measurement: runs the program eagerly with a cudaEvent pair around every launch (on `stream`)

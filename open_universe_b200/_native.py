@@ -18,7 +18,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 EXPORTS = [
     "uv_abi_version", "uv_sizeof_op", "uv_last_error", "uv_model_create", "uv_model_destroy", "uv_plan_create",
     "uv_plan_destroy", "uv_plan_arena_bytes", "uv_enhance", "uv_run_ops", "uv_arena_read", "uv_arena_write",
-    "uv_plan_num_launches", "uv_profile_ops",
+    "uv_plan_num_launches", "uv_profile_ops", "uv_plan_arena_ptr",
 ]
 
 
@@ -79,6 +79,8 @@ def lib():
     L.uv_profile_ops.argtypes = [C.c_void_p] + io + [C.POINTER(C.c_float)]
     L.uv_arena_read.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
     L.uv_arena_write.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
+    L.uv_plan_arena_ptr.argtypes = [C.c_void_p]
+    L.uv_plan_arena_ptr.restype = C.c_void_p
     if L.uv_abi_version() != _abi.UV_ABI_VERSION:
         raise RuntimeError(f"ABI version mismatch: library {L.uv_abi_version()}, binding {_abi.UV_ABI_VERSION}")
     if L.uv_sizeof_op() != C.sizeof(_abi.UvOp):
@@ -147,6 +149,20 @@ class NativePlan:
         _check(lib().uv_profile_ops(self.handle, mix_ptr, noise_ptr, out_ptr, dbg_ptr, self._coefs(coefs),
                                     1 if keep_rms else 0, stream_ptr, ms), "uv_profile_ops")
         return list(ms)
+
+    def arena_view(self, off, n_floats, device):
+        """Zero-copy f32 torch view of arena[off : off + 4 n_floats] (the plan keeps owning the memory)."""
+        import torch
+
+        class _Ptr:
+            pass
+
+        h = _Ptr()
+        h.__cuda_array_interface__ = dict(shape=(n_floats,), typestr="<f4", data=(lib().uv_plan_arena_ptr(self.handle) + off, False),
+                                          version=2)
+        t = torch.as_tensor(h, device=device)
+        t._uv_plan = self   # keep the arena alive as long as the view
+        return t
 
     def arena_read(self, off, nbytes):
         buf = C.create_string_buffer(nbytes)

@@ -430,6 +430,8 @@ extern "C" int uv_arena_read(uv_plan* p, size_t off, void* host_dst, size_t nbyt
   return UV_OK;
 }
 
+extern "C" void* uv_plan_arena_ptr(uv_plan* p) { return p ? (void*)p->arena : nullptr; }
+
 extern "C" int uv_arena_write(uv_plan* p, size_t off, const void* host_src, size_t nbytes) {
   if (!p || off + nbytes > p->arena_bytes) return fail(UV_ERR_INVALID, "uv_arena_write: out of range");
   CUDA_TRY(cudaSetDevice(p->model->device));

@@ -165,6 +165,23 @@ class MelAdapterP(nn.Module):
         self.conv_block = ConvBlockP(output_channels, weight_norm=weight_norm)
 
 
+def sinc_hann_kernel(orig, new, zeros=6, rolloff=0.99):
+    """Polyphase windowed-sinc resampling filter bank of torchaudio 2.x `Resample(orig, new)` (defaults
+    lowpass_filter_width 6, rolloff 0.99, sinc_interp_hann), restated from its published definition: phase i of
+    `new`, taps j in [-width, width + orig): t = (j / orig - i / new) * base, base = min(orig, new) * rolloff,
+    h = sinc(pi t) cos^2(pi t / (2 zeros)) base / orig on |t| <= zeros.  Returns (kernel [new, 1, 2 width + orig], width).
+    The reference stores these as buffers of bigvgan's Activation1d (alias_free_act.py:21-22)."""
+    base = min(orig, new) * rolloff
+    width = math.ceil(zeros * orig / base)
+    j = torch.arange(-width, width + orig, dtype=torch.float64)[None, None, :] / orig
+    i = torch.arange(0, -new, -1, dtype=torch.float64)[:, None, None] / new
+    t = ((i + j) * base).clamp(-zeros, zeros)
+    window = torch.cos(t * math.pi / zeros / 2) ** 2
+    t = t * math.pi
+    k = torch.where(t == 0, torch.ones_like(t), torch.sin(t) / t) * window * (base / orig)
+    return k.float(), width
+
+
 class SnakeActP(nn.Module):
     """State of bigvgan AliasFreeSnake inside `signal_decoupling_layer`
     (reference bigvgan/snake.py, alias_free_act.py:8-30): alpha + the two resampling kernels."""
@@ -173,8 +190,8 @@ class SnakeActP(nn.Module):
         super().__init__()
         self.act = nn.Module()
         self.act.alpha = nn.Parameter(torch.zeros(channels))
-        self.upsample = _Buf("kernel", torch.zeros(2, 1, 15))
-        self.downsample = _Buf("kernel", torch.zeros(1, 1, 28))
+        self.upsample = _Buf("kernel", sinc_hann_kernel(1, 2)[0])      # [2, 1, 15]
+        self.downsample = _Buf("kernel", sinc_hann_kernel(2, 1)[0])    # [1, 1, 28]
 
 
 class SignalDecouplingP(nn.Module):

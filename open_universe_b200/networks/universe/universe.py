@@ -117,6 +117,17 @@ class Universe(torch.nn.Module):
     def aux_to_wav(self, y_aux):
         return y_aux
 
+    @staticmethod
+    def _resample(x, kernel, orig, new):
+        """torchaudio `Resample` with its precomputed filter bank (functional._apply_sinc_resample_kernel): pad
+        (width, width + orig), strided conv with the `new` phase filters, interleave the phases, crop."""
+        width = (kernel.shape[-1] - orig) // 2
+        shape = x.shape
+        w = torch.nn.functional.pad(x.reshape(-1, shape[-1]), (width, width + orig))
+        y = torch.nn.functional.conv1d(w[:, None], kernel.to(w), stride=orig)
+        y = y.transpose(1, 2).reshape(w.shape[0], -1)[..., : math.ceil(new * shape[-1] / orig)]
+        return y.reshape(shape[:-1] + y.shape[-1:])
+
     def pad(self, x, pad=None):
         if pad is None:
             pad = self.tot_ds - x.shape[-1] % self.tot_ds
@@ -141,7 +152,7 @@ class Universe(torch.nn.Module):
     def _device(self):
         return next(self.parameters()).device
 
-    def _get_plan(self, B, T, n_steps):
+    def _get_plan(self, B, T, n_steps, aux=False):
         dev = self._device()
         if dev.type != "cuda":
             raise RuntimeError(
@@ -152,9 +163,9 @@ class Universe(torch.nn.Module):
             sd = {k: v.detach().float().cpu() for k, v in self.state_dict().items()}
             self._packed = weights.pack_model(sd, self.model_config())
             self._native_model = _native.NativeModel(self._packed.blob.bytes(), dev.index or 0)
-        key = (B, T, n_steps)
+        key = (B, T, n_steps, aux)
         if key not in self._plans:
-            pg = program.build_program(self._packed, self.model_config(), B, T, n_steps)
+            pg = program.build_program(self._packed, self.model_config(), B, T, n_steps, aux=aux)
             self._plans[key] = _native.NativePlan(self._native_model, pg, use_graph=self.use_cuda_graph)
         return self._plans[key]
 
@@ -201,8 +212,9 @@ class Universe(torch.nn.Module):
             raise ValueError("open_universe_b200 supports single-channel conditioners (input_channels == 1)")
         if ensemble_stat not in ("mean", "median", "signal_median"):
             raise NotImplementedError()
-        if use_aux_signal or warm_start is not None:
-            raise NotImplementedError("`use_aux_signal` / `warm_start` (signal decoupling layer) are not implemented natively yet")
+        aux = bool(use_aux_signal) or warm_start is not None
+        if warm_start is not None and not 0 <= int(warm_start) < n_steps:
+            raise ValueError("warm_start must be a step index in [0, n_steps)")
         if self.normalization_norm not in (2, "2"):
             raise NotImplementedError("only normalization_norm == 2 is supported")
         if self.diff_kwargs.get("schedule", "geometric") != "geometric":
@@ -228,13 +240,15 @@ class Universe(torch.nn.Module):
                 target = torch.stack([target] * ensemble, dim=0).view((-1,) + target.shape[1:])
             x = self._enhance_known_score(mix.to(dev), target.to(dev), n_steps, epsilon, fake_score_snr, rng, keep_rms, noise)
             return self._finish(x, x_ndim, ensemble, ensemble_stat, mix_shape if ensemble is not None else None)
-        plan = self._get_plan(B, T, n_steps)
+        plan = self._get_plan(B, T, n_steps, aux=aux)
         Lp = plan.pg.Lp
         mix_f = mix.reshape(B, T).to(device=dev, dtype=torch.float32).contiguous()
         if noise is None:
             # same draws, same order as the reference (universe.py:39-41,326,338): n_steps tensors of (B,1,Lp)
-            noise = torch.empty((n_steps, B, Lp), dtype=torch.float32, device=dev)
-            for i in range(n_steps):
+            # (use_aux_signal draws nothing, warm_start = n draws for the steps from n on: universe.py:317-331)
+            noise = torch.zeros((n_steps, B, Lp), dtype=torch.float32, device=dev)
+            first = n_steps if use_aux_signal else (int(warm_start) if warm_start is not None else 0)
+            for i in range(first, n_steps):
                 noise[i] = torch.randn((B, 1, Lp), dtype=torch.float32, device=dev, generator=rng)[:, 0, :]
         else:
             noise = noise.to(device=dev, dtype=torch.float32).reshape(n_steps, B, Lp).contiguous()
@@ -242,13 +256,41 @@ class Universe(torch.nn.Module):
         dbg = torch.empty((n_steps, B, Lp), dtype=torch.float32, device=dev) if return_steps else None
         coefs = program.step_coefs(self.model_config(), n_steps, epsilon)
         stream = torch.cuda.current_stream(dev).cuda_stream
+        io = (mix_f.data_ptr(), noise.data_ptr(), out.data_ptr(), dbg.data_ptr() if dbg is not None else None,
+              coefs, bool(keep_rms), stream)
         with torch.cuda.device(dev):
-            plan.enhance(mix_f.data_ptr(), noise.data_ptr(), out.data_ptr(), dbg.data_ptr() if dbg is not None else None,
-                         coefs, bool(keep_rms), stream)
+            if not aux:
+                plan.enhance(*io)
+            else:
+                self._enhance_aux(plan, io, B, Lp, n_steps, noise, use_aux_signal, warm_start)
         x = self._finish(out.to(mix.dtype)[:, None, :], x_ndim, ensemble, ensemble_stat, mix_shape if ensemble is not None else None)
         if return_steps:
             return x, dbg
         return x
+
+    def _enhance_aux(self, plan, io, B, Lp, n_steps, noise, use_aux_signal, warm_start):
+        """use_aux_signal / warm_start (reference universe.py:313-331): front end + conditioner (including the
+        decoder tail that yields y_hat) run natively, `aux_to_wav` maps y_hat to a waveform with a few device-side
+        torch ops (off the hot path), which either is the result (use_aux_signal) or, plus sigma_n z, the state
+        the native sampler resumes from at step n = warm_start.  The draws are consumed like the reference's:
+        noise[warm_start] initialises x, noise[warm_start + 1 ...] are the z of the following steps."""
+        pg = plan.pg
+        plan.run_ops(0, pg.idx_init_x, *io)
+        t = pg.y_hat
+        C = t.nch * 8
+        planes = plan.arena_view(t.off, t.nch * t.P * 8, noise.device).view(t.nch, t.P, 8)
+        rows = planes[:, t.G : t.G + B * t.Lh].reshape(t.nch, B, t.Lh, 8)[:, :, :Lp]        # [chunk][b][l][8]
+        y_hat = rows.permute(1, 0, 3, 2).reshape(B, C, Lp)
+        sig = self.aux_to_wav(y_hat)[:, 0, :]
+        x = plan.arena_view(pg.x, B * Lp, noise.device).view(B, Lp)
+        if use_aux_signal:
+            x.copy_(sig)
+        else:
+            n0 = int(warm_start)
+            sigma = program.sampler_tables(self.model_config(), n_steps)[0]
+            x.copy_(sig + float(sigma[n0]) * noise[n0])
+            plan.run_ops(pg.step_first_op[n0], pg.idx_post, *io)
+        plan.run_ops(pg.idx_post, pg.idx_post + 1, *io)
 
     @staticmethod
     def _finish(x, x_ndim, ensemble, ensemble_stat, mix_shape):
@@ -351,6 +393,24 @@ class UniverseGAN(Universe):
             self.signal_decoupling_layer = SignalDecouplingP(self.n_channels, losses.get("signal_decoupling_act", None))
         else:
             self.signal_decoupling_layer = None
+
+    def aux_to_wav(self, y_aux):
+        """signal_decoupling_layer (reference universe_gan.py:119-128,147-151; blocks.py:209-231): alias-free snake
+        (2x sinc up-sampling, x + sin^2(a x) / a with a = exp(alpha), 2x down-sampling; bigvgan alias_free_act.py:8-30,
+        snake.py:53-64) or PReLU, then Conv1d(C -> 1, k3, same)."""
+        sdl = getattr(self, "signal_decoupling_layer", None)
+        if sdl is None:
+            return y_aux
+        x = y_aux.float()
+        act = getattr(sdl.prelu, "act", None)
+        if act is not None:
+            x = self._resample(x, act.upsample.kernel, 1, 2)
+            a = torch.exp(act.act.alpha.to(x))[None, :, None]
+            x = x + (1.0 / (a + 1e-9)) * torch.sin(x * a) ** 2
+            x = self._resample(x, act.downsample.kernel, 2, 1)
+        elif hasattr(sdl.prelu, "weight"):
+            x = torch.nn.functional.prelu(x, sdl.prelu.weight.to(x))
+        return torch.nn.functional.conv1d(x, sdl.conv.weight.to(x), sdl.conv.bias.to(x), padding="same")
 
     def model_parameters(self):
         params = itertools.chain(self.get_score_model().parameters(), self.condition_model.parameters())

@@ -191,7 +191,9 @@ def step_coefs(cfg, n_steps, epsilon):
     return out
 
 
-def build_program(pm, cfg, B, T, n_steps):
+def build_program(pm, cfg, B, T, n_steps, aux=False):
+    """aux=True also evaluates the tail of the conditioner decoder's last block (y_hat, the input of aux_to_wav:
+    reference condition.py:264-270,362; universe.py:313-331), which the default path never uses."""
     meta = pm.meta
     rates, chans, extra = meta["rates"], meta["chans"], meta["extra"]
     nlev = len(rates)
@@ -398,13 +400,16 @@ def build_program(pm, cfg, B, T, n_steps):
             lev_i -= 1
             lev, C = lv[lev_i], chans[lev_i]
             u_raw, u_act = pg.tens(f"{name}.u", lev, C), pg.tens(f"{name}.ua", lev, C)
-            outs = [_act(u_act, L[name + ".conv1"]["slope"])] + ([] if last else [_raw(u_raw)])
+            outs = [_act(u_act, L[name + ".conv1"]["slope"])] + ([] if (last and not aux) else [_raw(u_raw)])
             pg.gemm(name + ".rc", name + ".rc", y_act, lv[lev_i + 1], lv[lev_i + 1].L, outs)
             y_raw, y_act = u_raw, u_act
         lev, C = lv[lev_i], chans[lev_i]
         cond = pg.tens(f"cond{i}", lev, C)
         conds.append(cond)
-        if last:
+        if last and aux:
+            pg.y_hat = pg.tens("c.y_hat", lev, C, dtype=DT_F32)
+            conv_block("c.", name, lev, C, y_raw, y_act, [_raw(pg.y_hat)], cond_out=cond)
+        elif last:
             # y_hat is unused by enhance() (universe.py:314-316): only conv1 (the condition) is needed
             conv_block("c.", name, lev, C, y_raw, y_act, [], cond_out=cond, only_conv1=True)
         else:
@@ -426,12 +431,15 @@ def build_program(pm, cfg, B, T, n_steps):
     # =========================================================== sampler / score network
     op = new_op(_abi.OP_INIT_X)
     op.B, op.Lp, op.p0, op.f0, op.i0 = B, Lp, pg.x, float(sigma[0]), 0
+    pg.idx_init_x = len(pg.ops)   # ops [0, idx_init_x) = front end + conditioner
     pg.emit(op, "init_x")
+    pg.step_first_op = []
     frows = L["s.film"]["rows"]
     n_blocks = meta["n_blocks"]
     for n in range(n_steps):
         fbase = pg.film + n * R * 4
         h_raw, h_act = pg.tens("s.h0", lv[0], chans[0]), pg.tens("s.h0a", lv[0], chans[0])
+        pg.step_first_op.append(len(pg.ops))
         op = new_op(_abi.OP_CONV_IN, n)
         op.B, op.Lp, op.C, op.p0, op.p3, op.p4 = B, Lp, chans[0], pg.x, L["s.in"]["w_w"], L["s.in"]["bias_w"]
         op.f0 = float(w_in[n])
@@ -496,6 +504,7 @@ def build_program(pm, cfg, B, T, n_steps):
         op.B, op.Lp, op.C, op.p0, op.p3, op.p4, op.i0 = B, Lp, chans[0], pg.x, L["s.out"]["w_w"], L["s.out"]["bias_w"], n
         op.p1 = pg.coef
         pg.emit(op, f"s{n}.out")
+    pg.idx_post = len(pg.ops)
     op = new_op(_abi.OP_POST)
     op.B, op.T, op.Lp, op.i0, op.p0, op.p1, op.p2 = B, T, Lp, pg.pad_left, pg.x, pg.mix_rms, pg.coef + n_steps * 16
     pg.emit(op, "post")

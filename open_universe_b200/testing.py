@@ -50,6 +50,21 @@ def seed_weights(model, seed=0):
     return model
 
 
+def perturb_snake_alpha(model):
+    """seed_weights() leaves the snake's log-alpha of the signal decoupling layer at 0 (its default); the
+    aux-signal fixtures spread it so that a channel mix-up or a missing exp() shows."""
+    sdl = getattr(model, "signal_decoupling_layer", None)
+    if sdl is not None and hasattr(sdl.prelu, "act"):
+        a = sdl.prelu.act.act.alpha
+        with torch.no_grad():
+            a.copy_(torch.linspace(-0.7, 0.9, a.numel()).to(a))
+        if getattr(model, "ema", None) is not None:
+            model.ema.shadow_params = [p.detach().clone() for p in model.model_parameters()]
+        if hasattr(model, "_invalidate"):
+            model._invalidate()
+    return model
+
+
 def synthetic_noisy_speech(B, T, seed=1234, device="cpu"):
     """Broadband 'noisy speech' stand-in: one-pole low-passed noise + white noise."""
     g = torch.Generator().manual_seed(seed)

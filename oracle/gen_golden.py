@@ -29,6 +29,9 @@ CASES = [
     # score, so the CPU generator of the reference does not matter) and the signal_median ensemble statistic
     ("pp16k_target", "universepp_16k", 2, 3000, dict(fake_score_snr=200.0, keep_rms=True, with_target=True)),
     ("pp16k_sigmed", "universepp_16k", 1, 2072, dict(n_steps=4, ensemble=3, ensemble_stat="signal_median")),
+    # signal decoupling layer paths (universe.py:313-331, universe_gan.py:147-151); snake alpha perturbed
+    ("pp16k_aux", "universepp_16k", 2, 3000, dict(use_aux_signal=True, snake_alpha=True)),
+    ("pp16k_warm", "universepp_16k", 2, 3000, dict(warm_start=5, keep_rms=True, snake_alpha=True)),
 ]
 
 
@@ -52,12 +55,14 @@ def main():
         ref, cfg = rh.build_reference_model(name)
         mine = config.instantiate(config.to_attr(cfg))
         testing.seed_weights(mine, seed=7)
+        kw = dict(kw)
+        if kw.pop("snake_alpha", False):
+            testing.perturb_snake_alpha(mine)
         sd = mine.state_dict()
         missing, unexpected = ref.load_state_dict(sd, strict=False)
         assert not unexpected and all(k.startswith("loss_") for k in missing), (missing[:5], unexpected[:5])
         tot_ds = ref.tot_ds
         n_steps = kw.get("n_steps", cfg["diffusion"]["n_steps"])
-        kw = dict(kw)
         with_target = kw.pop("with_target", False)
         mix, noise = make_inputs(B * (kw.get("ensemble") or 1), T, tot_ds, n_steps)
         mix = mix[:B]

@@ -281,10 +281,38 @@ def normalize(mix, level_db):
     return mix * gain
 
 
-def enhance(sd, cfg, mix, noises, n_steps=None, epsilon=None, keep_rms=False, explicit_gru=False, return_steps=False):
-    """Universe.enhance universe.py:231-375 for the default path (target None, no
-    ensemble / aux / warm start) with the noise sequence injected.
-    mix: [B, T]; noises: list of n_steps tensors [B, 1, Lp]. Returns [B, T]."""
+def resample(x, kernel, orig, new):
+    """torchaudio.transforms.Resample.forward with its stored filter bank (the kernels are buffers of the
+    checkpoint: bigvgan/alias_free_act.py:21-22): pad (w, w + orig), conv with stride orig, interleave phases."""
+    width = (kernel.shape[-1] - orig) // 2
+    shape = x.shape
+    w = F.pad(x.reshape(-1, shape[-1]), (width, width + orig))
+    y = F.conv1d(w[:, None], kernel, stride=orig).transpose(1, 2).reshape(w.shape[0], -1)
+    y = y[..., : math.ceil(new * shape[-1] / orig)]
+    return y.reshape(shape[:-1] + y.shape[-1:])
+
+
+def aux_to_wav(sd, y_aux, prefix="signal_decoupling_layer"):
+    """UniverseGAN.aux_to_wav universe_gan.py:147-151 -> PReLU_Conv(C, 1, 3, act_type) blocks.py:209-231 with the
+    alias-free snake of bigvgan/snake.py:53-64,131-160 + alias_free_act.py:24-30 (alpha in log scale)."""
+    if prefix + ".conv.weight" not in sd:
+        return y_aux
+    x = y_aux
+    if prefix + ".prelu.act.act.alpha" in sd:
+        x = resample(x, sd[prefix + ".prelu.act.upsample.kernel"], 1, 2)
+        a = torch.exp(sd[prefix + ".prelu.act.act.alpha"])[None, :, None]
+        x = x + (1.0 / (a + 1e-9)) * torch.sin(x * a) ** 2
+        x = resample(x, sd[prefix + ".prelu.act.downsample.kernel"], 2, 1)
+    elif prefix + ".prelu.weight" in sd:
+        x = F.prelu(x, sd[prefix + ".prelu.weight"])
+    return F.conv1d(x, sd[prefix + ".conv.weight"], sd[prefix + ".conv.bias"], padding="same")
+
+
+def enhance(sd, cfg, mix, noises, n_steps=None, epsilon=None, keep_rms=False, explicit_gru=False, return_steps=False,
+            use_aux_signal=False, warm_start=None):
+    """Universe.enhance universe.py:231-375 (target None, no ensemble) with the noise sequence injected.
+    mix: [B, T]; noises: list of tensors [B, 1, Lp], consumed in the reference's order (n_steps of them on the
+    default path; with warm_start = n the first one initialises x at step n). Returns [B, T]."""
     edm = cfg.get("edm") is not None
     sp = "_edm_model" if edm else "score_model"
     scfg = cfg["score_model"]
@@ -299,7 +327,7 @@ def enhance(sd, cfg, mix, noises, n_steps=None, epsilon=None, keep_rms=False, ex
     sigma, eta, beta = sampler_constants(cfg, n_steps, epsilon)
     n = sigma.shape[0]
     B = mix.shape[0]
-    cond = conditioner(sd, "condition_model", cfg["condition_model"], mix, explicit_gru=explicit_gru)
+    cond, y_hat, _ = conditioner(sd, "condition_model", cfg["condition_model"], mix, explicit_gru=explicit_gru, return_all=True)
 
     def score_fn(x, s):
         sv = s.expand(B)
@@ -315,15 +343,22 @@ def enhance(sd, cfg, mix, noises, n_steps=None, epsilon=None, keep_rms=False, ex
         return (est - x) / s**2, net
 
     steps = []
-    x = noises[0] * sigma[0]
-    for i in range(n - 1):
-        score, net = score_fn(x, sigma[i])
+    noises = list(noises)
+    if use_aux_signal:                       # universe.py:317-319
+        x = aux_to_wav(sd, y_hat)
+    else:
+        n0 = 0 if warm_start is None else int(warm_start)
+        x = noises.pop(0) * sigma[n0]        # universe.py:324-331
+        if warm_start is not None:
+            x = aux_to_wav(sd, y_hat) + x
+        for i in range(n0, n - 1):
+            score, net = score_fn(x, sigma[i])
+            steps.append(net)
+            z = noises.pop(0) * sigma[i + 1]
+            x = x + sigma[i] ** 2 * eta * score + beta * z
+        score, net = score_fn(x, sigma[-1])
         steps.append(net)
-        z = noises[i + 1] * sigma[i + 1]
-        x = x + sigma[i] ** 2 * eta * score + beta * z
-    score, net = score_fn(x, sigma[-1])
-    steps.append(net)
-    x = x + sigma[-1] ** 2 * score
+        x = x + sigma[-1] ** 2 * score
     x = x[..., pad // 2 : -(pad - pad // 2)]
     if keep_rms:
         x_rms = x.square().mean(dim=(-2, -1), keepdim=True).sqrt().clamp(min=1e-5)

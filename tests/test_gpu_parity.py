@@ -8,7 +8,7 @@ import subprocess
 import pytest
 import torch
 
-from conftest import GOLDEN_CASES, ROOT, build_model, golden_inputs, load_fixture
+from conftest import GOLDEN_CASES, ROOT, build_model, golden_inputs, load_fixture  # noqa: F401
 from oracle import universe_oracle as uo
 
 pytestmark = pytest.mark.gpu
@@ -79,7 +79,7 @@ def test_enhance_public_api_rng_ranks_and_ensemble():
     e = model.enhance(mix, rng=rng, ensemble=3, ensemble_stat="median")
     assert e.shape == (2, T) and torch.isfinite(e).all()
     with pytest.raises(NotImplementedError):
-        model.enhance(mix, use_aux_signal=True)
+        model.enhance(mix, ensemble=2, ensemble_stat="mode")
 
 
 def test_signal_median_ensemble_matches_reference_golden():
@@ -92,6 +92,30 @@ def test_signal_median_ensemble_matches_reference_golden():
                               kw["ensemble_stat"], None, noise=noise.cuda(), return_steps=False).cpu()
     assert out.shape == fix["out"].shape
     assert uo.rel_l2(out, fix["out"]) < TOL and uo.si_sdr(out, fix["out"]).min() > SISDR_MIN
+
+
+@pytest.mark.parametrize("case", ["pp16k_aux", "pp16k_warm"])
+def test_aux_signal_and_warm_start_match_reference_golden(case):
+    """use_aux_signal / warm_start (universe.py:313-331): conditioner incl. the decoder tail and the resumed sampler
+    run natively, aux_to_wav in the shell."""
+    from open_universe_b200 import testing
+
+    fix = load_fixture(case)
+    model, _ = build_model(fix["model"], fix["seed_weights"])
+    testing.perturb_snake_alpha(model)
+    model = model.to("cuda").eval()
+    mix, noise = golden_inputs(fix, model.tot_ds)
+    kw = fix["kwargs"]
+    nat = torch.zeros_like(noise)
+    if kw.get("warm_start") is not None:   # the reference consumes its draws from the start of the list
+        n0 = kw["warm_start"]
+        nat[n0:] = noise[: noise.shape[0] - n0]
+    out = model._enhance_impl(mix.cuda(), None, None, None, None, None, bool(kw.get("use_aux_signal")), bool(kw.get("keep_rms")),
+                              None, "median", kw.get("warm_start"), noise=nat.cuda(), return_steps=False).cpu()
+    assert uo.rel_l2(out, fix["out"]) < TOL and uo.si_sdr(out, fix["out"]).min() > SISDR_MIN
+    # public call with a device generator
+    o2 = model.enhance(mix.cuda(), rng=torch.Generator(device="cuda").manual_seed(1), **kw)
+    assert o2.shape == mix.shape and torch.isfinite(o2).all()
 
 
 def test_known_score_hook_matches_reference_golden():
