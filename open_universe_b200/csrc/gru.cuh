@@ -49,7 +49,7 @@ struct GruParams {
 };
 
 struct GruSmem {
-  int w_bytes, h_bytes, gh_stride, gh_bytes, gi_bytes, st_bytes, total;
+  int w_bytes, h_bytes, gh_stride, gh_bytes, gi_bytes, st_bytes, union_bytes, total;
 };
 constexpr int kGruStagePitch = 144;   // bytes per (8 units, utterance) pair in the output staging: 8 steps x 16 B + 16 B skew
 __host__ __device__ inline GruSmem gru_smem_layout(int H, int NB) {
@@ -61,7 +61,11 @@ __host__ __device__ inline GruSmem gru_smem_layout(int H, int NB) {
   s.gh_bytes = ((rows * s.gh_stride * 4) + 127) & ~127;
   s.gi_bytes = NB * (rows + 4) * 4;             // gate inputs of one step [NB][3U + 4] f32 (row pitch 16 B off a bank multiple)
   s.st_bytes = (U / 8) * NB * kGruStagePitch;   // 8 steps of bf16 h per (chunk, utterance) pair (two such buffers)
-  s.total = s.w_bytes + 2 * s.h_bytes + s.gh_bytes + s.gi_bytes + 2 * s.st_bytes + 256;
+  // W is only staged in shared memory until it has been copied into tensor memory: the staging area is then
+  // reused for the per-step buffers (gh, gi, output staging)
+  const int step_bytes = s.gh_bytes + s.gi_bytes + 2 * s.st_bytes;
+  s.union_bytes = s.w_bytes > step_bytes ? s.w_bytes : step_bytes;
+  s.total = 2 * s.h_bytes + s.union_bytes + 256;
   return s;
 }
 
@@ -224,12 +228,12 @@ __global__ void __launch_bounds__(kGruThreads, 1) gru_kernel(const __grid_consta
   extern __shared__ __align__(1024) uint8_t gsm[];
   const int H = P.H, U = H / kGruNC, rows = 3 * U, NB = P.NB;
   const GruSmem L = gru_smem_layout(H, NB);
-  uint8_t* w_s = gsm;
-  uint8_t* h_s = gsm + L.w_bytes;                       // two operand buffers
-  float* gh_s = reinterpret_cast<float*>(h_s + 2 * L.h_bytes);
+  uint8_t* h_s = gsm;                                   // two operand buffers
+  uint8_t* w_s = gsm + 2 * L.h_bytes;                   // W staging (start-up only), then:
+  float* gh_s = reinterpret_cast<float*>(w_s);
   float* gi_s = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(gh_s) + L.gh_bytes);
   uint8_t* st_s = reinterpret_cast<uint8_t*>(gi_s) + L.gi_bytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(st_s + 2 * L.st_bytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(w_s + L.union_bytes);
   uint64_t* h_full = bars;         // [2 buffers][3 groups]: that group's slices of h have landed in buffer i
   uint64_t* mma_done = bars + 16;  // [1]
   uint64_t* w_full = bars + 17;    // [1]
@@ -276,9 +280,6 @@ __global__ void __launch_bounds__(kGruThreads, 1) gru_kernel(const __grid_consta
       const uint32_t n = wb - off < 32768u ? wb - off : 32768u;
       bulk_g2s(smem_u32(w_s + off), src + off, n, smem_u32(w_full));
     }
-    // gate inputs of the first step
-    mbar_expect_tx(smem_u32(gi_full), gi_bytes);
-    bulk_g2s(smem_u32(gi_s), gi_blk0 + (long long)t0 * gi_tstride, gi_bytes, smem_u32(gi_full));
   }
   // h_0 = 0 (both buffers), slack rows of W zero
   for (int i = tid; i < (2 * L.h_bytes) / 16; i += kGruThreads) reinterpret_cast<uint4*>(h_s)[i] = make_uint4(0, 0, 0, 0);
@@ -317,6 +318,12 @@ __global__ void __launch_bounds__(kGruThreads, 1) gru_kernel(const __grid_consta
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  if (tid == 0) {
+    // gate inputs of the first step (their buffer overlays the W staging area, free only now)
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    mbar_expect_tx(smem_u32(gi_full), gi_bytes);
+    bulk_g2s(smem_u32(gi_s), gi_blk0 + (long long)t0 * gi_tstride, gi_bytes, smem_u32(gi_full));
+  }
   cluster_sync_all();   // every CTA's barriers and zeroed buffers exist before any remote access
 
   const bool clk_on = P.clk != nullptr && tid == 0 && rank == 0 && blockIdx.y == 0 && dir == 0;

@@ -125,7 +125,8 @@ def gru_geometry(H, B):
 
     def smem(nb):
         gh = _ru(3 * U * (nb + 1) * 4, 128)
-        return 3 * U * H * 2 + 2048 + 2 * nb * H * 2 + gh + nb * (3 * U + 4) * 4 + (U // 8) * nb * 144 + 128
+        step = gh + nb * (3 * U + 4) * 4 + 2 * (U // 8) * nb * 144       # gh, gi, two output staging buffers
+        return 2 * nb * H * 2 + max(3 * U * H * 2 + 2048, step) + 256   # W staging is overlaid by the step buffers
 
     nb = 32   # 32 utterances per cluster: 16 does not shorten a step (the h exchange is latency bound) and needs twice the clusters
     while nb > 16 and ((U // 8) * nb > 256 or smem(nb) > 227 * 1024):
