@@ -170,11 +170,22 @@ static int launch_op(uv_plan* p, const uv_op& op, cudaStream_t s) {
       prep_kernel<<<op.B, 1024, 0, s>>>(p->io_dev, op.T, op.Lp, op.i0, op.f0, aptr<float>(p, op.p0), aptr<float>(p, op.p1));
       break;
     case UV_OP_MEL: {
+      if (op.T != kMelFT) return fail(UV_ERR_INVALID, "MEL op built for another frame tile than the kernel's");
       const int nft = (op.F + kMelFT - 1) / kMelFT;
-      const size_t sm = ((size_t)(kMelFT - 1) * op.i1 + op.i0 + (size_t)kMelFT * op.i2) * sizeof(float);
-      mel_kernel<<<dim3(nft, op.B), 256, sm, s>>>(aptr<const float>(p, op.p0), op.Lp, op.F, op.i0, op.i1, op.i2, op.H, op.C,
-                                                  op.i3, wptr<const float>(p, op.p3), wptr<const float>(p, op.p4),
-                                                  aptr<float>(p, op.p1), aptr<float>(p, op.p2), nft);
+      const size_t sm = ((size_t)(kMelFT - 1) * op.i1 + op.i0 + 4 + (size_t)kMelPwPitch * op.i2) * sizeof(float);
+      const int threads = (op.i2 + 31) / 32 * 32;   // one thread per frequency bin
+      // (the filterbank stage keeps two chunks of kMelFbRows x n_mels floats in the signal buffer, one band per thread)
+      if (threads > 512 || sm > 200 * 1024 || op.i0 % 4 || op.i1 % 4 || op.C > threads ||
+          2 * kMelFbRows * op.C > (kMelFT - 1) * op.i1 + op.i0)
+        return fail(UV_ERR_INVALID, "MEL front end: n_fft / hop / n_mels unsupported");
+      static bool attr_done = false;
+      if (!attr_done) {
+        CUDA_TRY(cudaFuncSetAttribute(mel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        attr_done = true;
+      }
+      mel_kernel<<<dim3(nft, op.B), threads, sm, s>>>(aptr<const float>(p, op.p0), op.Lp, op.F, op.i0, op.i1, op.i2, op.H, op.C,
+                                                      op.i3, wptr<const float>(p, op.p3), wptr<const float>(p, op.p4),
+                                                      aptr<float>(p, op.p1), aptr<float>(p, op.p2), nft);
       break;
     }
     case UV_OP_MEL_FIN: {

@@ -73,16 +73,21 @@ __global__ void __launch_bounds__(1024) prep_kernel(const IoTable* io, int T, in
 // MelAdapter.compute_mel_spec (condition.py:92-108): explicit (n_fft-hop)/2 padding,
 // Hann-windowed power spectrum (torchaudio MelSpectrogram, center=False, power=2),
 // mel filterbank.  The windowed real-DFT basis [n_fft][2*nbp] and fb come from the
-// checkpoint buffers.  One CTA = 8 frames of one utterance; fp32 throughout.
-constexpr int kMelFT = 8;
-__global__ void __launch_bounds__(256) mel_kernel(const float* __restrict__ sig, int Lp, int F, int n_fft, int hop,
+// checkpoint buffers.  One CTA = 32 frames of one utterance, one thread per frequency bin (block = bins rounded
+// up to a warp); fp32 throughout.  The 1.7 MB basis is streamed from L2 once per CTA, so the frame tile
+// sets the L2 traffic (8 frames per CTA were L2-bandwidth bound at 3.5 TB/s), and one bin per thread avoids a
+// second, mostly idle pass over the bins (321 bins on 256 threads).
+constexpr int kMelFT = 32;
+constexpr int kMelFbRows = 16;            // filterbank rows (bins) per staged chunk
+constexpr int kMelPwPitch = kMelFT + 4;   // power spectrum rows [bin][frame], padded: conflict-free 16-byte accesses
+__global__ void __launch_bounds__(512) mel_kernel(const float* __restrict__ sig, int Lp, int F, int n_fft, int hop,
                                                   int nb, int nbp, int n_mels, int pad_left,
                                                   const float* __restrict__ basis, const float* __restrict__ fb,
                                                   float* __restrict__ melraw, float* __restrict__ energy, int nft) {
   extern __shared__ float smem_f[];
   const int span = (kMelFT - 1) * hop + n_fft;
   float* xs = smem_f;          // [span]
-  float* pw = smem_f + span;   // [kMelFT][nb]
+  float* pw = smem_f + ((span + 3) & ~3);   // [nb][kMelPwPitch]
   __shared__ double sh[96];
   const int b = blockIdx.y, f0 = blockIdx.x * kMelFT;
   const float* x = sig + (size_t)b * Lp;
@@ -97,27 +102,88 @@ __global__ void __launch_bounds__(256) mel_kernel(const float* __restrict__ sig,
     for (int f = 0; f < kMelFT; ++f) re[f] = im[f] = 0.f;
     const float* bc = basis + k;
     const float* bs = basis + nbp + k;
-    for (int n = 0; n < n_fft; ++n) {
-      const float c = bc[(size_t)n * 2 * nbp], s = bs[(size_t)n * 2 * nbp];
+    // four samples per step: one 16-byte broadcast load feeds 8 FMAs (scalar loads left the loop LDS bound);
+    // hop and n are multiples of 4, so the loads stay 16-byte aligned
+    const size_t bst = (size_t)2 * nbp;
+    float c[4], s4[4], cn[4], sn[4];   // basis of this / the next step (one CTA per SM: nothing else hides the L2 latency)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { cn[j] = bc[(size_t)j * bst]; sn[j] = bs[(size_t)j * bst]; }
+    for (int n = 0; n < n_fft; n += 4) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { c[j] = cn[j]; s4[j] = sn[j]; }
+      if (n + 4 < n_fft) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { cn[j] = bc[(size_t)(n + 4 + j) * bst]; sn[j] = bs[(size_t)(n + 4 + j) * bst]; }
+      }
 #pragma unroll
       for (int f = 0; f < kMelFT; ++f) {
-        const float v = xs[f * hop + n];
-        re[f] = fmaf(v, c, re[f]);
-        im[f] = fmaf(v, s, im[f]);
+        const float4 v = *reinterpret_cast<const float4*>(xs + f * hop + n);
+        re[f] = fmaf(v.x, c[0], re[f]); im[f] = fmaf(v.x, s4[0], im[f]);
+        re[f] = fmaf(v.y, c[1], re[f]); im[f] = fmaf(v.y, s4[1], im[f]);
+        re[f] = fmaf(v.z, c[2], re[f]); im[f] = fmaf(v.z, s4[2], im[f]);
+        re[f] = fmaf(v.w, c[3], re[f]); im[f] = fmaf(v.w, s4[3], im[f]);
       }
     }
 #pragma unroll
-    for (int f = 0; f < kMelFT; ++f) pw[f * nb + k] = re[f] * re[f] + im[f] * im[f];
+    for (int f = 0; f < kMelFT; f += 4)
+      *reinterpret_cast<float4*>(pw + (size_t)k * kMelPwPitch + f) =
+          make_float4(re[f] * re[f] + im[f] * im[f], re[f + 1] * re[f + 1] + im[f + 1] * im[f + 1],
+                      re[f + 2] * re[f + 2] + im[f + 2] * im[f + 2], re[f + 3] * re[f + 3] + im[f + 3] * im[f + 3]);
   }
   __syncthreads();
+  // mel filterbank: thread = (mel band m, group g of the tile's frames); per bin one coalesced fb load and
+  // broadcast 16-byte loads of the power row feed 8-32 FMAs (a thread per (frame, band) item with a scalar load
+  // pair per FMA was latency bound and took as long as the DFT)
   double e = 0, d1 = 0, d2 = 0;
-  for (int idx = threadIdx.x; idx < kMelFT * n_mels; idx += blockDim.x) {
-    const int f = idx / n_mels, m = idx - f * n_mels;
-    float acc = 0.f;
-    for (int k = 0; k < nb; ++k) acc = fmaf(pw[f * nb + k], fb[(size_t)k * n_mels + m], acc);
-    if (f0 + f < F) {
-      melraw[((size_t)b * F + f0 + f) * n_mels + m] = acc;
-      e += (double)acc * acc;
+  int ng = blockDim.x / n_mels;
+  ng = ng >= 4 ? 4 : (ng >= 2 ? 2 : 1);
+  const int fpt = kMelFT / ng;   // frames per thread: 8, 16 or 32
+  // fb rows are staged through the (now dead) signal buffer in chunks of kMelFbRows bins, double buffered
+  const int tpg = blockDim.x / ng;                 // threads per frame group
+  const int g = threadIdx.x / tpg, m = threadIdx.x % tpg;
+  const bool active = g < ng && m < n_mels;        // (n_mels <= tpg is checked by the host)
+  float acc[kMelFT];
+#pragma unroll
+  for (int f = 0; f < kMelFT; ++f) acc[f] = 0.f;
+  const int chunk = kMelFbRows * n_mels;
+  float* fbs = xs;                                 // [2][kMelFbRows][n_mels]
+  const int n_chunks = (nb + kMelFbRows - 1) / kMelFbRows;
+  auto load_chunk = [&](int ci, float* dst) {
+    const int k0 = ci * kMelFbRows;
+    const int cnt = (nb - k0 < kMelFbRows ? nb - k0 : kMelFbRows) * n_mels;
+    for (int i = threadIdx.x; i < cnt; i += blockDim.x) dst[i] = fb[(size_t)k0 * n_mels + i];
+  };
+  load_chunk(0, fbs);
+  __syncthreads();
+  for (int ci = 0; ci < n_chunks; ++ci) {
+    float* cur = fbs + (ci & 1) * chunk;
+    if (ci + 1 < n_chunks) load_chunk(ci + 1, fbs + ((ci + 1) & 1) * chunk);
+    if (active) {
+      const int k0 = ci * kMelFbRows;
+      const int kn = nb - k0 < kMelFbRows ? nb - k0 : kMelFbRows;
+      const float* prow = pw + (size_t)k0 * kMelPwPitch + g * fpt;
+      for (int kk = 0; kk < kn; ++kk) {
+        const float w = cur[kk * n_mels + m];
+#pragma unroll
+        for (int f = 0; f < kMelFT; f += 4) {
+          if (f < fpt) {
+            const float4 v = *reinterpret_cast<const float4*>(prow + (size_t)kk * kMelPwPitch + f);
+            acc[f] = fmaf(v.x, w, acc[f]); acc[f + 1] = fmaf(v.y, w, acc[f + 1]);
+            acc[f + 2] = fmaf(v.z, w, acc[f + 2]); acc[f + 3] = fmaf(v.w, w, acc[f + 3]);
+          }
+        }
+      }
+    }
+    __syncthreads();
+  }
+  if (active) {
+#pragma unroll
+    for (int f = 0; f < kMelFT; ++f) {
+      const int fr = f0 + g * fpt + f;
+      if (f < fpt && fr < F) {
+        melraw[((size_t)b * F + fr) * n_mels + m] = acc[f];
+        e += (double)acc[f] * acc[f];
+      }
     }
   }
   block_sum3(e, d1, d2, sh);

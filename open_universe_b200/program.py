@@ -39,6 +39,7 @@ class Level:
         self.P = G + _ru(self.rows, 256) + G   # GEMM tiles are 256 rows (csrc/gemm_tc.cuh kTileM)
 
 
+MEL_FT = 32   # frames per CTA of the mel kernel (csrc/small_ops.cuh kMelFT)
 FUSE_CONVBLOCKS = os.environ.get("UV_FUSE_CONVBLOCKS", "") == "1"   # experimental: one launch per C <= 64 ConvBlock (csrc/convblock.cuh); measured slower than three GEMM launches so far
 
 
@@ -230,7 +231,7 @@ def build_program(pm, cfg, B, T, n_steps, aux=False):
     # ---- PREP (universe.py:219-223,272; utils/norm.py:47-87)
     level = 10.0 ** (float(cfg.get("normalization_kwargs", {}).get("level_db", 0.0)) / 20.0)
     mel = L["c.mel"]
-    nft = (Fr + 7) // 8
+    nft = (Fr + MEL_FT - 1) // MEL_FT
     pg.mel_energy = pg.alloc(B * nft * 4)
     pg.melraw = pg.alloc(B * Fr * mel["n_mels"] * 4)
     op = new_op(_abi.OP_PREP)
@@ -241,7 +242,7 @@ def build_program(pm, cfg, B, T, n_steps, aux=False):
     lb = lv[nlev]
     # mel front-end (condition.py:92-114)
     op = new_op(_abi.OP_MEL)
-    op.B, op.Lp, op.F, op.C = B, Lp, Fr, mel["n_mels"]
+    op.B, op.Lp, op.F, op.C, op.T = B, Lp, Fr, mel["n_mels"], MEL_FT
     op.i0, op.i1, op.i2, op.i3 = mel["n_fft"], mel["hop"], mel["n_bins"], (mel["n_fft"] - mel["hop"]) // 2
     op.H = mel["nbp"]
     op.p0, op.p1, op.p2, op.p3, op.p4 = pg.sig, pg.melraw, pg.mel_energy, mel["basis_w"], mel["fb_w"]

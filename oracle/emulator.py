@@ -156,10 +156,11 @@ class Emulator:
         power = ri[..., :nb] ** 2 + ri[..., nbp : nbp + nb] ** 2
         mel = power @ fb  # [B, F, n_mels]
         self.a_f32(op.p1, B * F_ * n_mels).copy_(mel.reshape(-1))
-        nft = (F_ + 7) // 8
-        e = torch.zeros(B, nft * 8)
+        ft = op.T   # frames per partial energy sum (= per CTA of the kernel)
+        nft = (F_ + ft - 1) // ft
+        e = torch.zeros(B, nft * ft)
         e[:, :F_] = (mel**2).sum(-1)
-        self.a_f32(op.p2, B * nft).copy_(e.view(B, nft, 8).sum(-1).reshape(-1))
+        self.a_f32(op.p2, B * nft).copy_(e.view(B, nft, ft).sum(-1).reshape(-1))
 
     def op_mel_fin(self, op):
         B, F_, n_mels, nft = op.B, op.F, op.C, op.i0

@@ -39,7 +39,7 @@ def op_outputs(op, pg):
     elif t == _abi.OP_PREP:
         outs += [("sig", op.p0, op.B * op.Lp * 4, torch.float32), ("rms", op.p1, op.B * 4, torch.float32)]
     elif t == _abi.OP_MEL:
-        outs += [("mel", op.p1, op.B * op.F * op.C * 4, torch.float32), ("energy", op.p2, op.B * ((op.F + 7) // 8) * 4, torch.float32)]
+        outs += [("mel", op.p1, op.B * op.F * op.C * 4, torch.float32), ("energy", op.p2, op.B * ((op.F + op.T - 1) // op.T) * 4, torch.float32)]
     elif t in (_abi.OP_INIT_X, _abi.OP_CONV_OUT):
         outs.append(("x", op.p0, op.B * op.Lp * 4, torch.float32))
     elif t == _abi.OP_FILM:
