@@ -245,6 +245,7 @@ def run_native(args, wl, rank, world, local_rank):
                 data="synthetic",
                 config=dict(workload=wl["desc"], model=wl["model"], batch_per_gpu=B, clip_samples=T, n_steps=n_steps,
                             weights="random-init (seeded)", sharding=f"utterances x{world}, no collective",
+                            lanes=f"{len(plan.pg.lanes)} utterance lane(s) per GPU (independent halves of the batch on two captured streams)",
                             l2="per-step working set (GBs of activations) >> 126 MB L2; no explicit flush",
                             timing="CUDA events on the launch stream, max over ranks"),
                 clocks=clocks,

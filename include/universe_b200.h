@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define UV_ABI_VERSION 4
+#define UV_ABI_VERSION 5
 
 typedef enum {
   UV_OK = 0,
@@ -105,6 +105,12 @@ typedef struct {
   int32_t i0, i1, i2, i3;
   int64_t p0, p1, p2, p3, p4, p5;
   float f0, f1, f2, f3;
+  /* ---- utterance lanes: a program may process two independent halves of the batch ("lanes", each with its
+   * own tensors); uv_plan_create captures lane 1 on a second stream so that its kernels overlap lane 0's
+   * GRU recurrence.  PREP / INIT_X / CONV_OUT / POST carry i1 = first utterance of their lane and
+   * i2 = utterances of the whole call (the io tensors of uv_enhance always cover all lanes).            */
+  int32_t lane;          /* 0 or 1                                                                */
+  int32_t sync;          /* bit 0: record this lane's event after the op; bit 1: wait for the other lane's event first */
 } uv_op;
 
 typedef struct uv_model uv_model;
@@ -152,6 +158,12 @@ int uv_arena_write(uv_plan* p, size_t off, const void* host_src, size_t nbytes);
  * and returns the device time of each op in ms_per_op[n_ops] (0 for plan-time setup ops).  */
 int uv_profile_ops(uv_plan* p, const float* mix, const float* noise, float* out, float* dbg_net,
                    const uv_step_coef* coef, int keep_rms, void* stream, float* ms_per_op);
+
+/* Measurement: runs the program eagerly the way the graph runs it (lane 0 and lane 1 on two internal streams,
+ * same fork / join / stagger edges) with a cudaEvent pair around every launch, and returns each op's start and
+ * end time in ms relative to the start of the pass: the timeline that shows what overlaps the GRU recurrences. */
+int uv_trace_ops(uv_plan* p, const float* mix, const float* noise, float* out, float* dbg_net,
+                 const uv_step_coef* coef, int keep_rms, float* t_start_ms, float* t_end_ms);
 
 /* Number of kernel launches one uv_enhance() replays (for bench accounting). */
 int uv_plan_num_launches(const uv_plan* p);

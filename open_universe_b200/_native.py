@@ -18,7 +18,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 EXPORTS = [
     "uv_abi_version", "uv_sizeof_op", "uv_last_error", "uv_model_create", "uv_model_destroy", "uv_plan_create",
     "uv_plan_destroy", "uv_plan_arena_bytes", "uv_enhance", "uv_run_ops", "uv_arena_read", "uv_arena_write",
-    "uv_plan_num_launches", "uv_profile_ops", "uv_plan_arena_ptr",
+    "uv_plan_num_launches", "uv_profile_ops", "uv_plan_arena_ptr", "uv_trace_ops",
 ]
 
 
@@ -77,6 +77,7 @@ def lib():
     L.uv_enhance.argtypes = [C.c_void_p] + io
     L.uv_run_ops.argtypes = [C.c_void_p, C.c_int, C.c_int] + io
     L.uv_profile_ops.argtypes = [C.c_void_p] + io + [C.POINTER(C.c_float)]
+    L.uv_trace_ops.argtypes = [C.c_void_p] + io[:-1] + [C.POINTER(C.c_float), C.POINTER(C.c_float)]
     L.uv_arena_read.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
     L.uv_arena_write.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
     L.uv_plan_arena_ptr.argtypes = [C.c_void_p]
@@ -149,6 +150,14 @@ class NativePlan:
         _check(lib().uv_profile_ops(self.handle, mix_ptr, noise_ptr, out_ptr, dbg_ptr, self._coefs(coefs),
                                     1 if keep_rms else 0, stream_ptr, ms), "uv_profile_ops")
         return list(ms)
+
+    def trace_ops(self, mix_ptr, noise_ptr, out_ptr, dbg_ptr, coefs, keep_rms):
+        """(start, end) device times in ms of every op of one eager pass run on the plan's own lane streams."""
+        n = len(self.pg.ops)
+        t0, t1 = (C.c_float * n)(), (C.c_float * n)()
+        _check(lib().uv_trace_ops(self.handle, mix_ptr, noise_ptr, out_ptr, dbg_ptr, self._coefs(coefs),
+                                  1 if keep_rms else 0, t0, t1), "uv_trace_ops")
+        return list(t0), list(t1)
 
     def arena_view(self, off, n_floats, device):
         """Zero-copy f32 torch view of arena[off : off + 4 n_floats] (the plan keeps owning the memory)."""

@@ -42,12 +42,15 @@ struct uv_plan {
   IoTable* io_dev = nullptr;
   IoTable* io_host = nullptr;     // pinned
   char* coef_host = nullptr;      // pinned: uv_step_coef[n_steps] + int keep_rms (+pad)
-  int64_t coef_off = -1;
+  std::vector<int64_t> coef_offs;   // one per utterance lane
   int n_steps = 0;
   int* err_flag = nullptr;
+  int* sched = nullptr;           // [n_ops][2] tile / finished-CTA counters of the GEMM launches (self-rewinding)
   cudaGraph_t graph = nullptr;
   cudaGraphExec_t exec = nullptr;
   cudaStream_t cap_stream = nullptr;
+  cudaStream_t lane_stream = nullptr;   // second capture stream: ops of lane 1
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_lane[2] = {nullptr, nullptr};
   int n_launches = 0;
   bool use_graph = false;
 };
@@ -113,7 +116,8 @@ static int check_tens(const uv_plan* p, const uv_tens& t, const char* what) {
   return UV_OK;
 }
 
-static int launch_op(uv_plan* p, const uv_op& op, cudaStream_t s) {
+static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
+  const uv_op& op = p->ops[op_index];
   switch (op.type) {
     case UV_OP_GEMM: {
       GemmParams g;
@@ -134,6 +138,7 @@ static int launch_op(uv_plan* p, const uv_op& op, cudaStream_t s) {
       g.rm_out = aptr<float>(p, op.rm_out); g.rm_ld = op.rm_ld;
       g.rm_H = op.rm_out >= 0 ? op.H : 0; g.rm_Bp = op.i1;   // GEMM ops with a row-major output feed the GRU (H, batch pitch)
       g.err_flag = p->err_flag;
+      g.sched = p->sched + 2 * op_index;
       CUDA_TRY(gemm_launch(g, p->model->num_sms, s));
       break;
     }
@@ -167,7 +172,7 @@ static int launch_op(uv_plan* p, const uv_op& op, cudaStream_t s) {
       break;
     }
     case UV_OP_PREP:
-      prep_kernel<<<op.B, 1024, 0, s>>>(p->io_dev, op.T, op.Lp, op.i0, op.f0, aptr<float>(p, op.p0), aptr<float>(p, op.p1));
+      prep_kernel<<<op.B, 1024, 0, s>>>(p->io_dev, op.i1, op.T, op.Lp, op.i0, op.f0, aptr<float>(p, op.p0), aptr<float>(p, op.p1));
       break;
     case UV_OP_MEL: {
       if (op.T != kMelFT) return fail(UV_ERR_INVALID, "MEL op built for another frame tile than the kernel's");
@@ -203,19 +208,22 @@ static int launch_op(uv_plan* p, const uv_op& op, cudaStream_t s) {
     }
     case UV_OP_INIT_X: {
       const long long n = (long long)op.B * op.Lp;
-      init_x_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(p->io_dev, n, op.i0, op.f0, aptr<float>(p, op.p0));
+      const int B_total = op.i2 > 0 ? op.i2 : op.B;   // i1 / i2: first utterance of this lane / utterances of the whole call
+      init_x_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(p->io_dev, n, ((long long)op.i0 * B_total + op.i1) * op.Lp, op.f0,
+                                                                aptr<float>(p, op.p0));
       break;
     }
     case UV_OP_CONV_OUT: {
       const long long n = (long long)op.B * op.Lp;
       conv_out_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(to_desc(p, op.a), op.B, op.Lp, op.C, wptr<const float>(p, op.p3),
                                                                   wptr<const float>(p, op.p4), aptr<float>(p, op.p0),
-                                                                  aptr<const StepCoef>(p, op.p1), op.i0, p->io_dev);
+                                                                  aptr<const StepCoef>(p, op.p1), op.i0, p->io_dev, op.i1,
+                                                                  op.i2 > 0 ? op.i2 : op.B);
       break;
     }
     case UV_OP_POST:
       post_kernel<<<op.B, 1024, 0, s>>>(aptr<const float>(p, op.p0), op.T, op.Lp, op.i0, aptr<const float>(p, op.p1),
-                                        aptr<const int>(p, op.p2), p->io_dev);
+                                        aptr<const int>(p, op.p2), p->io_dev, op.i1);
       break;
     case UV_OP_FILM:
       film_kernel<<<op.i0, 512, 2 * op.C * sizeof(float), s>>>(aptr<const float>(p, op.p0), op.i1, op.C, op.H, op.i2,
@@ -291,9 +299,77 @@ static int validate_ops(uv_plan* p) {
 static int enqueue_range(uv_plan* p, int first, int last, cudaStream_t s, bool skip_setup) {
   for (int i = first; i < last; ++i) {
     if (skip_setup && p->ops[i].step == -2) continue;
-    int rc = launch_op(p, p->ops[i], s);
+    int rc = launch_op(p, i, s);
     if (rc) return rc;
   }
+  return UV_OK;
+}
+
+// Graph capture of the whole program.  Ops of the two utterance lanes are independent (each lane owns its
+// tensors): lane 1 is captured on a second stream forked from / joined to the capture stream, so its kernels
+// run next to lane 0's -- in particular next to lane 0's GRU recurrence, which occupies 16 of the 148 SMs for
+// hundreds of dependent steps.  An op flagged sync & 1 records its lane's event after the launch, an op
+// flagged sync & 2 first waits for the other lane's event: the builder uses one such edge to start lane 1
+// behind lane 0, so that the two lanes do not reach their recurrences together.
+static int ensure_lane_objects(uv_plan* p, bool two) {
+  if (!p->cap_stream) CUDA_TRY(cudaStreamCreateWithFlags(&p->cap_stream, cudaStreamNonBlocking));
+  if (two && !p->lane_stream) {
+    CUDA_TRY(cudaStreamCreateWithFlags(&p->lane_stream, cudaStreamNonBlocking));
+    CUDA_TRY(cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming));
+    CUDA_TRY(cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming));
+    for (int l = 0; l < 2; ++l) CUDA_TRY(cudaEventCreateWithFlags(&p->ev_lane[l], cudaEventDisableTiming));
+  }
+  return UV_OK;
+}
+
+static bool has_two_lanes(const uv_plan* p) {
+  for (const uv_op& op : p->ops)
+    if (op.lane == 1) return true;
+  return false;
+}
+
+// Enqueues the program with lane 0 on s0 and lane 1 on s1 (fork at the start, join at the end, cross-lane edges
+// as flagged).  Works both under stream capture and eagerly; `ev` (optional, 2 per op) brackets every launch with
+// timing events on its own stream (uv_trace_ops).
+static int enqueue_lanes(uv_plan* p, cudaStream_t s0, cudaStream_t s1, bool two, cudaEvent_t* ev) {
+  const int n_ops = (int)p->ops.size();
+  bool recorded[2] = {false, false};
+  if (two) {
+    CUDA_TRY(cudaEventRecord(p->ev_fork, s0));
+    CUDA_TRY(cudaStreamWaitEvent(s1, p->ev_fork, 0));
+  }
+  for (int i = 0; i < n_ops; ++i) {
+    const uv_op& op = p->ops[i];
+    if (op.step == -2) continue;
+    const int lane = two && op.lane == 1 ? 1 : 0;
+    cudaStream_t s = lane ? s1 : s0;
+    if (two && (op.sync & 2) && recorded[lane ^ 1]) CUDA_TRY(cudaStreamWaitEvent(s, p->ev_lane[lane ^ 1], 0));
+    if (ev) CUDA_TRY(cudaEventRecord(ev[2 * i], s));
+    int rc = launch_op(p, i, s);
+    if (rc) return rc;
+    if (ev) CUDA_TRY(cudaEventRecord(ev[2 * i + 1], s));
+    if (two && (op.sync & 1)) {
+      CUDA_TRY(cudaEventRecord(p->ev_lane[lane], s));
+      recorded[lane] = true;
+    }
+  }
+  if (two) {
+    CUDA_TRY(cudaEventRecord(p->ev_join, s1));
+    CUDA_TRY(cudaStreamWaitEvent(s0, p->ev_join, 0));
+  }
+  return UV_OK;
+}
+
+static int capture_program(uv_plan* p) {
+  const bool two = has_two_lanes(p);
+  int rc = ensure_lane_objects(p, two);
+  if (rc) return rc;
+  CUDA_TRY(cudaStreamBeginCapture(p->cap_stream, cudaStreamCaptureModeThreadLocal));
+  rc = enqueue_lanes(p, p->cap_stream, p->lane_stream, two, nullptr);
+  cudaError_t e = cudaStreamEndCapture(p->cap_stream, &p->graph);
+  if (rc) return rc;
+  if (e != cudaSuccess) return fail(UV_ERR_CUDA, std::string("graph capture: ") + cudaGetErrorString(e));
+  CUDA_TRY(cudaGraphInstantiate(&p->exec, p->graph, 0));
   return UV_OK;
 }
 
@@ -318,25 +394,23 @@ extern "C" int uv_plan_create(uv_plan** out, uv_model* m, const uv_op* ops, int 
   CUDA_TRY(cudaMallocHost(&p->coef_host, (size_t)n_steps * 16 + 16));
   CUDA_TRY(cudaMalloc(&p->err_flag, sizeof(int)));
   CUDA_TRY(cudaMemset(p->err_flag, 0, sizeof(int)));
+  CUDA_TRY(cudaMalloc(&p->sched, (size_t)n_ops * 2 * sizeof(int)));
+  CUDA_TRY(cudaMemset(p->sched, 0, (size_t)n_ops * 2 * sizeof(int)));
   int rc = validate_ops(p);
   if (rc) { uv_plan_destroy(p); return rc; }
   for (const uv_op& op : p->ops) {
-    if (op.type == UV_OP_CONV_OUT) p->coef_off = op.p1;
+    if (op.type == UV_OP_CONV_OUT) {
+      bool seen = false;
+      for (int64_t o : p->coef_offs) seen = seen || o == op.p1;
+      if (!seen) p->coef_offs.push_back(op.p1);
+    }
     if (op.step != -2) ++p->n_launches;
   }
   // plan-time setup ops (FiLM table)
   for (int i = 0; i < n_ops; ++i)
-    if (p->ops[i].step == -2 && (rc = launch_op(p, p->ops[i], 0))) { uv_plan_destroy(p); return rc; }
+    if (p->ops[i].step == -2 && (rc = launch_op(p, i, 0))) { uv_plan_destroy(p); return rc; }
   CUDA_TRY(cudaDeviceSynchronize());
-  if (p->use_graph) {
-    CUDA_TRY(cudaStreamCreateWithFlags(&p->cap_stream, cudaStreamNonBlocking));
-    CUDA_TRY(cudaStreamBeginCapture(p->cap_stream, cudaStreamCaptureModeThreadLocal));
-    rc = enqueue_range(p, 0, n_ops, p->cap_stream, true);
-    cudaError_t e = cudaStreamEndCapture(p->cap_stream, &p->graph);
-    if (rc) { uv_plan_destroy(p); return rc; }
-    if (e != cudaSuccess) { uv_plan_destroy(p); return fail(UV_ERR_CUDA, std::string("graph capture: ") + cudaGetErrorString(e)); }
-    CUDA_TRY(cudaGraphInstantiate(&p->exec, p->graph, 0));
-  }
+  if (p->use_graph && (rc = capture_program(p))) { uv_plan_destroy(p); return rc; }
   *out = p;
   return UV_OK;
 }
@@ -347,6 +421,12 @@ extern "C" void uv_plan_destroy(uv_plan* p) {
   if (p->exec) cudaGraphExecDestroy(p->exec);
   if (p->graph) cudaGraphDestroy(p->graph);
   if (p->cap_stream) cudaStreamDestroy(p->cap_stream);
+  if (p->lane_stream) cudaStreamDestroy(p->lane_stream);
+  if (p->ev_fork) cudaEventDestroy(p->ev_fork);
+  if (p->ev_join) cudaEventDestroy(p->ev_join);
+  for (int l = 0; l < 2; ++l)
+    if (p->ev_lane[l]) cudaEventDestroy(p->ev_lane[l]);
+  cudaFree(p->sched);
   cudaFree(p->arena);
   cudaFree(p->io_dev);
   cudaFree(p->err_flag);
@@ -365,11 +445,12 @@ static int stage_io(uv_plan* p, const float* mix, const float* noise, float* out
   CUDA_TRY(cudaStreamSynchronize(s));
   p->io_host->mix = mix; p->io_host->noise = noise; p->io_host->out = out; p->io_host->dbg = dbg;
   CUDA_TRY(cudaMemcpyAsync(p->io_dev, p->io_host, sizeof(IoTable), cudaMemcpyHostToDevice, s));
-  if (p->coef_off >= 0) {
+  if (!p->coef_offs.empty()) {
     memcpy(p->coef_host, coef, (size_t)p->n_steps * 16);
     int kr[4] = {keep_rms, 0, 0, 0};
     memcpy(p->coef_host + (size_t)p->n_steps * 16, kr, 16);
-    CUDA_TRY(cudaMemcpyAsync(p->arena + p->coef_off, p->coef_host, (size_t)p->n_steps * 16 + 16, cudaMemcpyHostToDevice, s));
+    for (int64_t off : p->coef_offs)
+      CUDA_TRY(cudaMemcpyAsync(p->arena + off, p->coef_host, (size_t)p->n_steps * 16 + 16, cudaMemcpyHostToDevice, s));
   }
   return UV_OK;
 }
@@ -421,7 +502,7 @@ extern "C" int uv_profile_ops(uv_plan* p, const float* mix, const float* noise, 
   for (int i = 0; i < n; ++i) {
     if (p->ops[i].step == -2) continue;
     CUDA_TRY(cudaEventRecord(ev[2 * i], s));
-    if ((rc = launch_op(p, p->ops[i], s))) return rc;
+    if ((rc = launch_op(p, i, s))) return rc;
     CUDA_TRY(cudaEventRecord(ev[2 * i + 1], s));
   }
   CUDA_TRY(cudaStreamSynchronize(s));
@@ -430,6 +511,34 @@ extern "C" int uv_profile_ops(uv_plan* p, const float* mix, const float* noise, 
     if (p->ops[i].step != -2) CUDA_TRY(cudaEventElapsedTime(&ms_per_op[i], ev[2 * i], ev[2 * i + 1]));
   }
   for (auto& e : ev) cudaEventDestroy(e);
+  return check_err_flag(p);
+}
+
+extern "C" int uv_trace_ops(uv_plan* p, const float* mix, const float* noise, float* out, float* dbg_net,
+                            const uv_step_coef* coef, int keep_rms, float* t_start_ms, float* t_end_ms) {
+  if (!p || !t_start_ms || !t_end_ms) return fail(UV_ERR_INVALID, "uv_trace_ops: null argument");
+  CUDA_TRY(cudaSetDevice(p->model->device));
+  const bool two = has_two_lanes(p);
+  int rc = ensure_lane_objects(p, two);
+  if (rc) return rc;
+  cudaStream_t s0 = p->cap_stream;
+  if ((rc = stage_io(p, mix, noise, out, dbg_net, coef, keep_rms, s0))) return rc;
+  const int n = (int)p->ops.size();
+  std::vector<cudaEvent_t> ev(2 * n);
+  for (auto& e : ev) CUDA_TRY(cudaEventCreate(&e));
+  cudaEvent_t base;
+  CUDA_TRY(cudaEventCreate(&base));
+  CUDA_TRY(cudaEventRecord(base, s0));
+  if ((rc = enqueue_lanes(p, s0, p->lane_stream, two, ev.data()))) return rc;
+  CUDA_TRY(cudaStreamSynchronize(s0));
+  for (int i = 0; i < n; ++i) {
+    t_start_ms[i] = t_end_ms[i] = 0.f;
+    if (p->ops[i].step == -2) continue;
+    CUDA_TRY(cudaEventElapsedTime(&t_start_ms[i], base, ev[2 * i]));
+    CUDA_TRY(cudaEventElapsedTime(&t_end_ms[i], base, ev[2 * i + 1]));
+  }
+  for (auto& e : ev) cudaEventDestroy(e);
+  cudaEventDestroy(base);
   return check_err_flag(p);
 }
 

@@ -27,8 +27,14 @@
 // software-pipelined: the TMEM load and the residual loads of column group g+1 are in
 // flight while group g is processed.  2-4 accumulator stages live in TMEM so the MMAs
 // run ahead of the epilogues.  Layers whose whole weight set fits keep it resident in
-// shared memory and give the rest to a deep A ring.  Persistent grid, static
-// round-robin tile schedule.
+// shared memory and give the rest to a deep A ring.  Persistent grid with a DYNAMIC tile
+// schedule: the producer thread claims tile indices from a global counter (two claims in
+// flight, so the atomic's latency hides behind the current tile's copies) and publishes them
+// through a small shared-memory ring to the MMA issuer and the epilogue warps; -1 ends the
+// kernel.  A CTA that becomes resident late (its SM was busy with another stream's kernel,
+// e.g. the GRU clusters of the other utterance lane) finds the counter exhausted and exits at
+// once instead of holding a statically assigned share of the tiles.  The last CTA to leave
+// resets the counter pair, so the launch is replayable without a memset.
 #pragma once
 #include "uv_common.cuh"
 
@@ -41,6 +47,8 @@ constexpr int kMaxBStages = 8;
 constexpr int kEpiWarps = 8;        // 4 TMEM lane quarters x 2 sub-tiles (16 = two column halves each: measured slower, the multi-output paths spill at 112 registers)
 constexpr int kGemmThreads = 64 + 32 * kEpiWarps;   // producer warp, MMA warp, epilogue warps
 constexpr int kMaxAcc = 4;          // TMEM accumulator stages
+constexpr int kSchedSlots = 32;     // ring of claimed tile indices (producer -> MMA issuer + epilogue warps)
+constexpr int kSchedBytes = kSchedSlots * (4 + 2 * 8);
 constexpr int kOnesBytes = 2 * kSubM * 16;   // [2 chunks][128 rows][8] bf16
 constexpr int kFilmMaxC = 768;
 constexpr int kFilmBytes = 2 * kFilmMaxC * 4;
@@ -256,7 +264,8 @@ __device__ __forceinline__ void add_f32(const char* p, long long pstride, float*
 // group) and overlaps that load.
 template <bool ADD, bool FILM, bool MULTI, bool LE1>
 __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem_base, uint64_t* t_full, uint64_t* t_empty,
-                                              const float* film_s, int warp, int lane) {
+                                              const float* film_s, const int* s_ring, uint64_t* s_full, uint64_t* s_empty,
+                                              int warp, int lane) {
   const int sub = ((warp - 2) >> 2) & 1;
   const int chalf = (warp - 2) >> 3;            // with 16 epilogue warps: which half of the column groups
   const int quarter = warp & 3;                 // a warp may only touch TMEM lanes 32*(warp%4)..+31
@@ -267,7 +276,7 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
   const uint32_t acc_stride = accum_stride_cols(P.N_TILE);
   const int n_acc = P.n_acc;
   const int ntn = P.n_tiles_n;
-  const int total_tiles = P.n_tiles_m * ntn;
+  const float inv_ntn = 1.f / (float)ntn;
   const bool a1_bf16 = ADD && P.add1.esize_log2 == 1;
   const bool a2_on = ADD && P.add2.base != nullptr;
   const bool a2_bf16 = a2_on && P.add2.esize_log2 == 1;
@@ -291,10 +300,24 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
   const uint32_t t_stage = 2u * acc_stride;
   const uint32_t full0 = smem_u32(t_full), empty0 = smem_u32(t_empty);
 
-  if ((int)blockIdx.x >= total_tiles) return;
-  int tiles_left = (total_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
-  int n_tile = blockIdx.x % ntn, m_tile = blockIdx.x / ntn;
-  const int dn = gridDim.x % ntn, dm = gridDim.x / ntn;
+  // claimed-tile ring (filled by the producer thread): every consumer reads every slot once
+  const uint32_t sfull0 = smem_u32(s_full), sempty0 = smem_u32(s_empty);
+  int s_slot = 0;
+  uint32_t s_par = 0;
+  auto sched_take = [&]() {   // slot s_slot is known to be full
+    const int t = s_ring[s_slot];
+    __syncwarp();
+    if (lane == 0) mbar_arrive(sempty0 + 8u * s_slot);
+    if (++s_slot == kSchedSlots) { s_slot = 0; s_par ^= 1u; }
+    return t;
+  };
+  auto sched_next = [&]() {
+    mbar_wait(sfull0 + 8u * s_slot, s_par, P.err_flag, 8);
+    return sched_take();
+  };
+  int cur_tile = sched_next();
+  if (cur_tile < 0) return;
+  int n_tile = 0, m_tile = 0;
 
   // state of the tile being processed
   int stage = 0;
@@ -308,6 +331,11 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
   pa1.p = pa2.p = nullptr; pa1.pstride = pa2.pstride = 0;
 
   auto tile_setup = [&]() {
+    m_tile = cur_tile; n_tile = 0;
+    if (ntn > 1) {
+      m_tile = fast_div(cur_tile, ntn, inv_ntn);
+      n_tile = cur_tile - m_tile * ntn;
+    }
     n0 = n_tile * P.N_TILE;
     int ph = 0;
     co0 = n0;
@@ -321,8 +349,6 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
     valid = (g < P.m_rows) && (m < P.M_valid);
     const int l_out = P.up * m + ph;
     const int chunk_base = co0 >> 3;
-    n_tile += dn; m_tile += dm;   // next tile of this CTA (static round robin)
-    if (n_tile >= ntn) { n_tile -= ntn; ++m_tile; }
 #pragma unroll
     for (int o = 0; o < 3; ++o) {
       if (o < n_out && valid && (MULTI || o == 0)) op[o] = out_ptr(P.out[o].t, b, l_out, chunk_base + 2 * g_begin, inv_split[o]);
@@ -420,14 +446,15 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
   mbar_wait(full0, 0, P.err_flag, 6);
   tc_fence_after();
   if (have) tc_ld16_issue(t_lane + 16u * g_begin, r0);
-  for (; tiles_left > 0; --tiles_left) {
+  for (;;) {
     tile_setup();
     add_issue(g_begin, ad0);
     const uint32_t taddr = t_lane + (uint32_t)stage * t_stage;
     int nstage = stage + 1;
     uint32_t nphase = phase;
     if (nstage == n_acc) { nstage = 0; nphase ^= 1u; }
-    const bool more_tiles = tiles_left > 1;
+    int next_tile = -1;
+    bool next_known = false;
     bool prefetched = false;
     auto release = [&]() {   // this warp's part of the accumulator is in registers: the MMA warp may reuse it
       tc_fence_before();
@@ -453,7 +480,11 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
         } else {
           release();
           // never block here: this group is still to be processed
-          if (more_tiles && mbar_test_wait(full0 + 8u * nstage, nphase)) {
+          if (__all_sync(0xffffffffu, mbar_test_wait(sfull0 + 8u * s_slot, s_par))) {
+            next_tile = sched_take();
+            next_known = true;
+          }
+          if (next_known && next_tile >= 0 && __all_sync(0xffffffffu, mbar_test_wait(full0 + 8u * nstage, nphase))) {
             tc_fence_after();
             tc_ld16_issue(t_lane + (uint32_t)nstage * t_stage + 16u * g_begin, r0);
             prefetched = true;
@@ -462,11 +493,14 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
         process(g2 + 1, r1, ad1);
       }
     }
-    if (more_tiles && !prefetched) {
+    if (!next_known) next_tile = sched_next();
+    if (next_tile < 0) break;
+    if (!prefetched) {
       mbar_wait(full0 + 8u * nstage, nphase, P.err_flag, 6);
       tc_fence_after();
       if (have) tc_ld16_issue(t_lane + (uint32_t)nstage * t_stage + 16u * g_begin, r0);
     }
+    cur_tile = next_tile;
     stage = nstage;
     phase = nphase;
   }
@@ -492,7 +526,10 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
   uint64_t* b_empty = b_full + kMaxBStages;
   uint64_t* t_full = b_empty + kMaxBStages;
   uint64_t* t_empty = t_full + kMaxAcc;
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(t_empty + kMaxAcc);
+  uint64_t* s_full = t_empty + kMaxAcc;
+  uint64_t* s_empty = s_full + kSchedSlots;
+  int* s_ring = reinterpret_cast<int*>(s_empty + kSchedSlots);
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(s_ring + kSchedSlots);
 
   const uint32_t acc_stride = accum_stride_cols(P.N_TILE);
   const int n_acc = P.n_acc;
@@ -501,6 +538,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
     for (int i = 0; i < kMaxAStages; ++i) { mbar_init(smem_u32(&a_full[i]), 1); mbar_init(smem_u32(&a_empty[i]), 1); }
     for (int i = 0; i < kMaxBStages; ++i) { mbar_init(smem_u32(&b_full[i]), 1); mbar_init(smem_u32(&b_empty[i]), 1); }
     for (int i = 0; i < kMaxAcc; ++i) { mbar_init(smem_u32(&t_full[i]), 1); mbar_init(smem_u32(&t_empty[i]), kEpiWarps); }
+    for (int i = 0; i < kSchedSlots; ++i) { mbar_init(smem_u32(&s_full[i]), 1); mbar_init(smem_u32(&s_empty[i]), 1 + kEpiWarps); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   // ones tile: K columns 0 and 1 are 1.0 (they meet the hi / lo halves of the bias image), the rest 0
@@ -562,7 +600,19 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
       }
       int ia = 0, ib = 0;
       uint32_t pa = 0, pb = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      // dynamic schedule: two claims in flight, each published (-1 = no more tiles) before its loads are issued
+      int ss = 0;
+      uint32_t sp = 0;
+      int tile = atomicAdd(P.sched, 1);
+      int tile_nxt = atomicAdd(P.sched, 1);
+      for (;;) {
+        const bool live = tile < total_tiles;
+        mbar_wait(smem_u32(&s_empty[ss]), sp ^ 1, P.err_flag, 9);
+        s_ring[ss] = live ? tile : -1;
+        mbar_arrive(smem_u32(&s_full[ss]));
+        if (++ss == kSchedSlots) { ss = 0; sp ^= 1; }
+        if (!live) break;
+        const int tile_nn = tile_nxt < total_tiles ? atomicAdd(P.sched, 1) : tile_nxt;
         const int n_tile = tile % P.n_tiles_n;
         const int m_tile = tile / P.n_tiles_n;
         const long long row0 = (long long)P.a_G + (long long)m_tile * kTileM + P.smin;
@@ -618,6 +668,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
             if (++ia == P.na_stages) { ia = 0; pa ^= 1; }
           }
         }
+        tile = tile_nxt;
+        tile_nxt = tile_nn;
       }
     }
   } else if (warp == 1) {
@@ -642,9 +694,14 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
         mbar_wait(smem_u32(&b_full[0]), 0, P.err_flag, 7);
         tc_fence_after();
       }
-      int ia = 0, ib = 0, as = 0;
-      uint32_t pa = 0, pb = 0, pt = 1;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      int ia = 0, ib = 0, as = 0, ss = 0;
+      uint32_t pa = 0, pb = 0, pt = 1, sp = 0;
+      for (;;) {
+        mbar_wait(smem_u32(&s_full[ss]), sp, P.err_flag, 8);
+        const int tile = s_ring[ss];
+        mbar_arrive(smem_u32(&s_empty[ss]));
+        if (++ss == kSchedSlots) { ss = 0; sp ^= 1; }
+        if (tile < 0) break;
         mbar_wait(smem_u32(&t_empty[as]), pt, P.err_flag, 3);
         tc_fence_after();
         const uint32_t d0 = tmem_base + (uint32_t)(as * 2) * acc_stride;
@@ -729,7 +786,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
     for (int o = 0; o < 3; ++o)
       if (o < P.n_out && ((P.out[o].act >= 1 && !(P.out[o].a1 <= 1.f)) || (P.out[o].act == 2 && !(P.out[o].a2 <= 1.f)))) le1 = false;
     const int kind = (has_add ? 1 : 0) | (has_film ? 2 : 0) | (multi ? 4 : 0) | (le1 ? 8 : 0);
-#define UV_EPI(A, F, M, L) epilogue_role<A, F, M, L>(P, tmem_base, t_full, t_empty, film_s, warp, lane)
+#define UV_EPI(A, F, M, L) epilogue_role<A, F, M, L>(P, tmem_base, t_full, t_empty, film_s, s_ring, s_full, s_empty, warp, lane)
     switch (kind) {
       case 0: UV_EPI(false, false, false, false); break;
       case 1: UV_EPI(true, false, false, false); break;
@@ -757,12 +814,20 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols) : "memory");
   }
+  // all claims of this CTA are done: the last CTA out rewinds the counter pair for the next launch
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(P.sched + 1, 1) == (int)gridDim.x - 1) {
+      P.sched[0] = 0;
+      P.sched[1] = 0;
+    }
+  }
 }
 
 // ------------------------------------------------------------------ host side
 inline size_t gemm_smem_bytes(const GemmParams& p) {
   return (size_t)kOnesBytes + kFilmBytes + p.ident_bytes + (size_t)p.na_stages * p.a_stage_bytes + (size_t)p.nb_stages * p.b_stage_bytes +
-         (2 * kMaxAStages + 2 * kMaxBStages + 2 * kMaxAcc) * sizeof(uint64_t) + 16;
+         (2 * kMaxAStages + 2 * kMaxBStages + 2 * kMaxAcc) * sizeof(uint64_t) + kSchedBytes + 16;
 }
 
 // Fills the pipeline fields of `p` (stage sizes / counts, resident-weight mode) for the 227 KB smem of an SM.
@@ -792,7 +857,7 @@ inline bool gemm_plan_pipeline(GemmParams& p) {
   p.n_acc = 512 / (2 * stride);
   if (p.n_acc > kMaxAcc) p.n_acc = kMaxAcc;
   if (p.n_acc < 1) return false;
-  const long long fixed = kOnesBytes + kFilmBytes + p.ident_bytes + (2 * kMaxAStages + 2 * kMaxBStages + 2 * kMaxAcc) * 8 + 16 + 1024;
+  const long long fixed = kOnesBytes + kFilmBytes + p.ident_bytes + (2 * kMaxAStages + 2 * kMaxBStages + 2 * kMaxAcc) * 8 + kSchedBytes + 16 + 1024;
   const long long budget = kGemmSmemBudget - fixed;
   const int n_img = p.n_src * p.n_groups * (p.smax - p.smin + 1);
   const long long total_b = (((long long)n_img * b_bytes + bias_bytes) + 127) & ~127LL;
@@ -830,10 +895,14 @@ inline cudaError_t gemm_launch(GemmParams p, int num_sms, cudaStream_t stream) {
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
+  if (!p.sched) return cudaErrorInvalidValue;
   const int total = p.n_tiles_m * p.n_tiles_n;
   int grid = total < num_sms ? total : num_sms;
   if (grid < 1) grid = 1;
-  gemm_tc_kernel<<<grid, kGemmThreads, smem, stream>>>(p);
+  // always the whole shared memory of the SM: one CTA per SM, and never co-resident with a GRU CTA of the other
+  // lane (whose tensor-memory allocation would stall this CTA's tcgen05.alloc for the length of the recurrence)
+  (void)smem;
+  gemm_tc_kernel<<<grid, kGemmThreads, kGemmSmemBudget, stream>>>(p);
   return cudaGetLastError();
 }
 

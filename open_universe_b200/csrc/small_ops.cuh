@@ -44,11 +44,12 @@ __device__ __forceinline__ void block_sum3(double& a, double& b, double& c, doub
 // Universe.pad (universe.py:219-223) + utils.normalize_batch norm=2, zero_mean
 // (utils/norm.py:47-87): statistics over the PADDED signal, unbiased std, clamp 1e-5.
 // Also mix_rms over the unpadded input (universe.py:259).  One CTA per utterance.
-__global__ void __launch_bounds__(1024) prep_kernel(const IoTable* io, int T, int Lp, int pad_left, float level,
+// b_off = first utterance of this lane in the caller's batch (the io tensors cover all lanes).
+__global__ void __launch_bounds__(1024) prep_kernel(const IoTable* io, int b_off, int T, int Lp, int pad_left, float level,
                                                     float* sig, float* mix_rms) {
   __shared__ double sh[96];
   const int b = blockIdx.x;
-  const float* mix = io->mix + (size_t)b * T;
+  const float* mix = io->mix + (size_t)(b_off + b) * T;
   double s = 0, ss = 0, dummy = 0;
   for (int i = threadIdx.x; i < T; i += blockDim.x) {
     const double v = mix[i];
@@ -251,9 +252,9 @@ __global__ void __launch_bounds__(256) conv_in_kernel(const float* __restrict__ 
 }
 
 // ---------------------------------------------------------------- INIT_X   x = sigma_0 * z_0 (universe.py:326)
-__global__ void __launch_bounds__(256) init_x_kernel(const IoTable* io, long long n, int noise_idx, float sigma0, float* x) {
+__global__ void __launch_bounds__(256) init_x_kernel(const IoTable* io, long long n, long long noise_off, float sigma0, float* x) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) x[i] = sigma0 * io->noise[(long long)noise_idx * n + i];
+  if (i < n) x[i] = sigma0 * io->noise[noise_off + i];
 }
 
 // ---------------------------------------------------------------- CONV_OUT
@@ -261,7 +262,8 @@ __global__ void __launch_bounds__(256) init_x_kernel(const IoTable* io, long lon
 // the EDM wrapper and the sampler update (universe.py:197-209, 334-343):  x <- a x + b net + c z.
 __global__ void __launch_bounds__(256) conv_out_kernel(TensDesc a, int B, int Lp, int C, const float* __restrict__ w /*[3][C]*/,
                                                        const float* __restrict__ bias, float* __restrict__ x,
-                                                       const StepCoef* __restrict__ coef, int step, const IoTable* io) {
+                                                       const StepCoef* __restrict__ coef, int step, const IoTable* io,
+                                                       int b_off, int B_total) {
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (long long)B * Lp) return;
   const int b = (int)(idx / Lp), l = (int)(idx - (long long)b * Lp);
@@ -281,16 +283,16 @@ __global__ void __launch_bounds__(256) conv_out_kernel(TensDesc a, int B, int Lp
   }
   const StepCoef cf = coef[step];
   float xn = cf.a * x[idx] + cf.b * acc;
-  if (cf.c != 0.f) xn = fmaf(cf.c, io->noise[(long long)(step + 1) * B * Lp + idx], xn);
+  if (cf.c != 0.f) xn = fmaf(cf.c, io->noise[((long long)(step + 1) * B_total + b_off) * Lp + idx], xn);
   x[idx] = xn;
-  if (io->dbg) io->dbg[(long long)step * B * Lp + idx] = acc;
+  if (io->dbg) io->dbg[((long long)step * B_total + b_off) * Lp + idx] = acc;
 }
 
 // ---------------------------------------------------------------- POST
 // unpad, optional keep_rms, per-utterance peak normalisation (universe.py:349-357). One CTA per utterance.
 __global__ void __launch_bounds__(1024) post_kernel(const float* __restrict__ x, int T, int Lp, int pad_left,
                                                     const float* __restrict__ mix_rms, const int* __restrict__ keep_rms,
-                                                    const IoTable* io) {
+                                                    const IoTable* io, int b_off) {
   __shared__ double sh[96];
   __shared__ float s_max[32];
   const int b = blockIdx.x;
@@ -314,7 +316,7 @@ __global__ void __launch_bounds__(1024) post_kernel(const float* __restrict__ x,
     g = mix_rms[b] / x_rms;
   }
   const float peak = mx * g;
-  float* o = io->out + (size_t)b * T;
+  float* o = io->out + (size_t)(b_off + b) * T;
   for (int i = threadIdx.x; i < T; i += blockDim.x) {
     float v = xr[i] * g;
     if (peak > 1.f) v = v / peak;

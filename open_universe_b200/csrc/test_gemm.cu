@@ -203,8 +203,13 @@ static int run_case(const Case& c, int swap_lbo, int num_sms) {
   p.out[1].t = desc_of(out1); p.out[1].act = 2; p.out[1].a1 = 0.25f; p.out[1].a2 = -0.5f;
   p.rm_out = d_rm; p.rm_ld = N_total;
   p.err_flag = d_err;
+  int* d_sched;
+  CK(cudaMalloc(&d_sched, 8));
+  CK(cudaMemset(d_sched, 0, 8));
+  p.sched = d_sched;
 
   CK(gemm_launch(p, num_sms, 0));
+  CK(gemm_launch(p, num_sms, 0));   // relaunch: the kernel rewinds its own tile counter
   cudaError_t e = cudaDeviceSynchronize();
   int err = 0;
   if (e != cudaSuccess) {
@@ -294,6 +299,8 @@ static void run_perf(int num_sms) {
     if (pc.add) p.add1 = desc_of(AD);
     int* d_err; CK(cudaMalloc(&d_err, 4)); CK(cudaMemset(d_err, 0, 4));
     p.err_flag = d_err;
+    int* d_sched; CK(cudaMalloc(&d_sched, 8)); CK(cudaMemset(d_sched, 0, 8));
+    p.sched = d_sched;
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
     for (int i = 0; i < 3; ++i) CK(gemm_launch(p, num_sms, 0));

@@ -77,6 +77,7 @@ struct GemmParams {
   int b_resident;    // 1: all weight images of the (single) N tile stay in smem for the whole kernel
   int n_acc;         // TMEM accumulator stages (1, 2 or 4), each holding both 128-row halves of a tile
   int* err_flag;     // set on watchdog timeout
+  int* sched;        // [2] zero before the first launch: tile counter, finished-CTA counter (the kernel rewinds both)
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {

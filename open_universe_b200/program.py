@@ -12,6 +12,7 @@ with the consumer's slope (the MMA reads shared memory directly, so the
 activation is applied by the producer's epilogue); raw copies are kept only
 where a residual / skip / condition needs them.
 """
+import copy
 import math
 import os
 
@@ -57,11 +58,12 @@ class _PartSink:
 
 
 class Program:
-    def __init__(self, pm, B, T, n_steps, sigmas, log10_sigmas, in_scales):
+    def __init__(self, pm, B, T, n_steps, sigmas, log10_sigmas, in_scales, arena_base=0, lane=0):
         self.pm = pm
         self.ops = []
         self.names = []
-        self.arena = 0
+        self.arena = arena_base
+        self.lane = lane
         self.tensors = {}
         self.B, self.T, self.n_steps = B, T, n_steps
         self.sigmas, self.log10_sigmas, self.in_scales = sigmas, log10_sigmas, in_scales
@@ -86,8 +88,9 @@ class Program:
         return t
 
     def emit(self, op, name):
+        op.lane = self.lane
         self.ops.append(op)
-        self.names.append(name)
+        self.names.append(name if self.lane == 0 else f"L{self.lane}.{name}")
         return op
 
     # ---- op helpers
@@ -129,7 +132,7 @@ def gru_geometry(H, B):
         step = gh + nb * (3 * U + 4) * 4 + 2 * (U // 8) * nb * 144       # gh, gi, two output staging buffers
         return 2 * nb * H * 2 + max(3 * U * H * 2 + 2048, step) + 256   # W staging is overlaid by the step buffers
 
-    nb = 32   # 32 utterances per cluster: 16 does not shorten a step (the h exchange is latency bound) and needs twice the clusters
+    nb = int(os.environ.get("UV_GRU_NB", "32"))   # utterances per cluster
     while nb > 16 and ((U // 8) * nb > 256 or smem(nb) > 227 * 1024):
         nb -= 16
     nb = min(nb, _ru(B, 16))
@@ -193,9 +196,53 @@ def step_coefs(cfg, n_steps, epsilon):
     return out
 
 
-def build_program(pm, cfg, B, T, n_steps, aux=False):
+LANE_MIN_B = 16   # smallest batch that is split into two utterance lanes
+
+
+def default_lanes(B, aux=False):
+    """Two lanes whenever the batch is large enough: the lanes' kernels overlap each other's GRU recurrence
+    (16 of 148 SMs busy for hundreds of dependent steps) and launch gaps.  UV_LANES=1 forces one lane."""
+    if aux or os.environ.get("UV_LANES", "") == "1":
+        return 1
+    return 2 if B >= LANE_MIN_B else 1
+
+
+def build_program(pm, cfg, B, T, n_steps, aux=False, lanes=None):
+    """Program of one enhance() call.  lanes = 2 splits the utterances into two independent halves whose op
+    lists are concatenated (lane 0 first); each lane owns its tensors, the FiLM table is shared.  The native
+    plan captures lane 1 on a second stream (csrc/capi.cu capture_program).  One cross-lane edge staggers the
+    lanes: lane 1 starts when lane 0 has finished the op named by UV_LANE_STAGGER (default: the conditioner
+    encoder's second rate-change conv, about a third of a score step of lane 0's work), so that their
+    recurrences do not coincide.  The result carries lane 0's attributes plus `lanes` (the per-lane programs)."""
+    if lanes is None:
+        lanes = default_lanes(B, aux)
+    if lanes == 1 or B < 2:
+        return _build_lane(pm, cfg, B, T, n_steps, aux=aux)
+    assert not aux, "aux-signal programs are single-lane (run_ops ranges address one op list)"
+    B0 = (B + 1) // 2
+    pg0 = _build_lane(pm, cfg, B0, T, n_steps, b_off=0, B_total=B)
+    pg1 = _build_lane(pm, cfg, B - B0, T, n_steps, b_off=B0, B_total=B, arena_base=pg0.arena, lane=1, shared=pg0)
+    stagger = os.environ.get("UV_LANE_STAGGER", "c.enc1.rc")
+    if stagger in pg0.names:
+        pg0.ops[pg0.names.index(stagger)].sync |= 1
+        first = next(i for i, op in enumerate(pg1.ops) if op.step != -2)
+        pg1.ops[first].sync |= 2
+    pg = copy.copy(pg0)
+    pg.lanes = [pg0, pg1]
+    pg.lane_ops = [len(pg0.ops), len(pg1.ops)]
+    pg.ops = pg0.ops + pg1.ops
+    pg.names = pg0.names + pg1.names
+    pg.arena = pg1.arena
+    pg.B = B
+    return pg
+
+
+def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_base=0, lane=0, shared=None):
     """aux=True also evaluates the tail of the conditioner decoder's last block (y_hat, the input of aux_to_wav:
-    reference condition.py:264-270,362; universe.py:313-331), which the default path never uses."""
+    reference condition.py:264-270,362; universe.py:313-331), which the default path never uses.
+    b_off / B_total: this lane's first utterance in / the size of the caller's batch (io tensors cover all lanes)."""
+    if B_total is None:
+        B_total = B
     meta = pm.meta
     rates, chans, extra = meta["rates"], meta["chans"], meta["extra"]
     nlev = len(rates)
@@ -203,7 +250,9 @@ def build_program(pm, cfg, B, T, n_steps, aux=False):
     pad = tot_ds - T % tot_ds
     Lp = T + pad
     sigma, log10s, w_in = sampler_tables(cfg, n_steps)
-    pg = Program(pm, B, T, n_steps, sigma, log10s, w_in)
+    pg = Program(pm, B, T, n_steps, sigma, log10s, w_in, arena_base=arena_base, lane=lane)
+    pg.lanes = [pg]
+    pg.b_off, pg.B_total = b_off, B_total
     pg.Lp, pg.pad_left = Lp, pad // 2
     lv = [Level(B, Lp // math.prod(rates[:i])) for i in range(nlev + 1)]
     pg.levels = lv
@@ -216,17 +265,20 @@ def build_program(pm, cfg, B, T, n_steps, aux=False):
     pg.x = pg.alloc(B * Lp * 4)          # sampler state (f32 [B][Lp])
     pg.mix_rms = pg.alloc(B * 4)
     pg.coef = pg.alloc(n_steps * 16 + 16)  # uv_step_coef[n_steps] | keep_rms flag
-    pg.log10s = pg.alloc(n_steps * 4)
     R = L["s.film"]["R"]
-    pg.film = pg.alloc(n_steps * R * 4)
-    pg.init_off = pg.log10s
-    pg.init_blob = np.asarray(log10s.numpy(), dtype=np.float32).tobytes()
+    if shared is None:
+        pg.log10s = pg.alloc(n_steps * 4)
+        pg.film = pg.alloc(n_steps * R * 4)
+        pg.init_off = pg.log10s
+        pg.init_blob = np.asarray(log10s.numpy(), dtype=np.float32).tobytes()
 
-    # ---- plan-time setup: FiLM table (sigma_block.py:50-57,73-78; score.py:109,208)
-    op = new_op(_abi.OP_FILM, -2)
-    op.i0, op.i1, op.i2, op.C, op.H = n_steps, 0 if meta["simple_embed"] else 1, R, meta["noise_cond_dim"], L["s.embed"]["n_rff"]
-    op.p0, op.p1, op.p3, op.p4, op.p5 = pg.log10s, pg.film, L["s.embed"]["w_w"], L["s.film"]["w_w"], L["s.film"]["bias_w"]
-    pg.emit(op, "film_table")
+        # ---- plan-time setup: FiLM table (sigma_block.py:50-57,73-78; score.py:109,208)
+        op = new_op(_abi.OP_FILM, -2)
+        op.i0, op.i1, op.i2, op.C, op.H = n_steps, 0 if meta["simple_embed"] else 1, R, meta["noise_cond_dim"], L["s.embed"]["n_rff"]
+        op.p0, op.p1, op.p3, op.p4, op.p5 = pg.log10s, pg.film, L["s.embed"]["w_w"], L["s.film"]["w_w"], L["s.film"]["bias_w"]
+        pg.emit(op, "film_table")
+    else:
+        pg.log10s, pg.film, pg.init_off, pg.init_blob = shared.log10s, shared.film, shared.init_off, shared.init_blob
 
     # ---- PREP (universe.py:219-223,272; utils/norm.py:47-87)
     level = 10.0 ** (float(cfg.get("normalization_kwargs", {}).get("level_db", 0.0)) / 20.0)
@@ -236,6 +288,7 @@ def build_program(pm, cfg, B, T, n_steps, aux=False):
     pg.melraw = pg.alloc(B * Fr * mel["n_mels"] * 4)
     op = new_op(_abi.OP_PREP)
     op.B, op.T, op.Lp, op.i0, op.f0, op.p0, op.p1 = B, T, Lp, pg.pad_left, level, pg.sig, pg.mix_rms
+    op.i1, op.i2 = b_off, B_total
     pg.emit(op, "prep")
 
     # =========================================================== conditioner
@@ -433,6 +486,7 @@ def build_program(pm, cfg, B, T, n_steps, aux=False):
     # =========================================================== sampler / score network
     op = new_op(_abi.OP_INIT_X)
     op.B, op.Lp, op.p0, op.f0, op.i0 = B, Lp, pg.x, float(sigma[0]), 0
+    op.i1, op.i2 = b_off, B_total
     pg.idx_init_x = len(pg.ops)   # ops [0, idx_init_x) = front end + conditioner
     pg.emit(op, "init_x")
     pg.step_first_op = []
@@ -505,10 +559,12 @@ def build_program(pm, cfg, B, T, n_steps, aux=False):
         op.a = y_act
         op.B, op.Lp, op.C, op.p0, op.p3, op.p4, op.i0 = B, Lp, chans[0], pg.x, L["s.out"]["w_w"], L["s.out"]["bias_w"], n
         op.p1 = pg.coef
+        op.i1, op.i2 = b_off, B_total
         pg.emit(op, f"s{n}.out")
     pg.idx_post = len(pg.ops)
     op = new_op(_abi.OP_POST)
     op.B, op.T, op.Lp, op.i0, op.p0, op.p1, op.p2 = B, T, Lp, pg.pad_left, pg.x, pg.mix_rms, pg.coef + n_steps * 16
+    op.i1, op.i2 = b_off, B_total
     pg.emit(op, "post")
     pg.arena = _ru(pg.arena, 1024)
     return pg

@@ -131,8 +131,8 @@ class Emulator:
             self._write_outs(op, b_idx, l, v)
 
     def op_prep(self, op, io):
-        mix = io["mix"].float()
         B, T, Lp = op.B, op.T, op.Lp
+        mix = io["mix"].float()[op.i1 : op.i1 + B]   # i1 = first utterance of this lane
         x = torch.zeros(B, Lp)
         x[:, op.i0 : op.i0 + T] = mix
         rms = mix.square().mean(dim=1).sqrt()
@@ -184,7 +184,8 @@ class Emulator:
         self._write_outs(op, b_idx, l_idx, v.reshape(B * Lp, C))
 
     def op_init_x(self, op, io):
-        self.a_f32(op.p0, op.B * op.Lp).copy_((io["noise"][op.i0].float() * np.float32(op.f0)).reshape(-1))
+        z = io["noise"][op.i0].float().reshape(-1, op.Lp)[op.i1 : op.i1 + op.B]
+        self.a_f32(op.p0, op.B * op.Lp).copy_((z * np.float32(op.f0)).reshape(-1))
 
     def op_conv_out(self, op, io):
         B, Lp, C = op.B, op.Lp, op.C
@@ -197,10 +198,11 @@ class Emulator:
         x = self.a_f32(op.p0, B * Lp).view(B, Lp)
         xn = ca * x + cb * net
         if cc != 0:
-            xn = xn + cc * io["noise"][op.i0 + 1].float().view(B, Lp)
+            xn = xn + cc * io["noise"][op.i0 + 1].float().reshape(-1, Lp)[op.i1 : op.i1 + B]
         x.copy_(xn)
         if io.get("dbg") is not None:
-            io["dbg"][op.i0] = net.clone()
+            B_total = op.i2 if op.i2 > 0 else B
+            io["dbg"].setdefault(op.i0, torch.zeros(B_total, Lp))[op.i1 : op.i1 + B] = net
 
     def op_post(self, op, io):
         B, T, Lp = op.B, op.T, op.Lp
@@ -210,7 +212,10 @@ class Emulator:
             x_rms = x.square().mean(dim=1).sqrt().clamp(min=1e-5)
             x = x * (rms / x_rms)[:, None]
         scale = x.abs().max(dim=1, keepdim=True).values
-        io["out"] = torch.where(scale > 1.0, x / scale, x)
+        B_total = op.i2 if op.i2 > 0 else B
+        if io.get("out") is None or io["out"].shape[0] != B_total:
+            io["out"] = torch.zeros(B_total, T)
+        io["out"][op.i1 : op.i1 + B] = torch.where(scale > 1.0, x / scale, x)
 
     def op_film(self, op):
         n_steps, kind, R, D, n_rff = op.i0, op.i1, op.i2, op.C, op.H

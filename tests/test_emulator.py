@@ -58,3 +58,31 @@ def test_arena_tensors_do_not_overlap():
     for (a0, a1, an), (b0, b1, bn) in zip(spans, spans[1:]):
         assert a1 <= b0, (an, bn)
     assert spans[-1][1] <= pg.arena
+
+
+def test_two_lane_program_equals_single_lane_programs():
+    """The two-lane program (halves of the batch with their own tensors, io offsets i1 / i2) computes, for each
+    half, bit for bit what a single-lane program of that half computes (the CPU emulator's fp32 matmuls block
+    differently for another batch size, so the comparison is per lane, not against one program of the whole batch)."""
+    model, cfg = build_model("universepp_16k")
+    mcfg = model.model_config()
+    pm = weights.pack_model(model.state_dict(), mcfg)
+    B, T, n_steps = 3, 700, 3
+    g = torch.Generator().manual_seed(5)
+    mix = 0.1 * torch.randn(B, T, generator=g)
+    Lp = T + (model.tot_ds - T % model.tot_ds)
+    noise = torch.stack([torch.randn(B, Lp, generator=g) for _ in range(n_steps)])
+    coefs = program.step_coefs(mcfg, n_steps, 1.3)
+    pg2 = program.build_program(pm, mcfg, B, T, n_steps, lanes=2)
+    assert len(pg2.lanes) == 2 and [l.B for l in pg2.lanes] == [2, 1] and pg2.lanes[1].b_off == 2
+    assert sum(op.lane for op in pg2.ops) == pg2.lane_ops[1]
+    assert sum(1 for op in pg2.ops if op.sync & 1) == 1 and sum(1 for op in pg2.ops if op.sync & 2) == 1
+    assert sum(1 for op in pg2.ops if op.step == -2) == 1          # one shared FiLM table
+    io2 = Emulator(pm, pg2).run(mix, noise, coefs, dbg=True)
+    for b0, b1 in ((0, 2), (2, 3)):
+        pg1 = program.build_program(pm, mcfg, b1 - b0, T, n_steps, lanes=1)
+        io1 = Emulator(pm, pg1).run(mix[b0:b1], noise[:, b0:b1], coefs, dbg=True)
+        assert torch.equal(io1["out"], io2["out"][b0:b1])
+        for i in range(n_steps):
+            assert torch.equal(io1["dbg"][i], io2["dbg"][i][b0:b1])
+    assert program.default_lanes(64) == 2 and program.default_lanes(8) == 1 and program.default_lanes(64, aux=True) == 1
