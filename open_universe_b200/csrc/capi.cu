@@ -172,7 +172,7 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
       break;
     }
     case UV_OP_PREP:
-      prep_kernel<<<op.B, 1024, 0, s>>>(p->io_dev, op.i1, op.T, op.Lp, op.i0, op.f0, aptr<float>(p, op.p0), aptr<float>(p, op.p1));
+      CUDA_TRY(launch_pdl(prep_kernel, dim3(op.B), dim3(1024), 0, s, p->io_dev, op.i1, op.T, op.Lp, op.i0, op.f0, aptr<float>(p, op.p0), aptr<float>(p, op.p1)));
       break;
     case UV_OP_MEL: {
       if (op.T != kMelFT) return fail(UV_ERR_INVALID, "MEL op built for another frame tile than the kernel's");
@@ -188,42 +188,42 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
         CUDA_TRY(cudaFuncSetAttribute(mel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         attr_done = true;
       }
-      mel_kernel<<<dim3(nft, op.B), threads, sm, s>>>(aptr<const float>(p, op.p0), op.Lp, op.F, op.i0, op.i1, op.i2, op.H, op.C,
+      CUDA_TRY(launch_pdl(mel_kernel, dim3(nft, op.B), dim3(threads), sm, s, aptr<const float>(p, op.p0), op.Lp, op.F, op.i0, op.i1, op.i2, op.H, op.C,
                                                       op.i3, wptr<const float>(p, op.p3), wptr<const float>(p, op.p4),
-                                                      aptr<float>(p, op.p1), aptr<float>(p, op.p2), nft);
+                                                      aptr<float>(p, op.p1), aptr<float>(p, op.p2), nft));
       break;
     }
     case UV_OP_MEL_FIN: {
       const int items = op.F * (op.C / 8);
-      mel_fin_kernel<<<dim3((items + 255) / 256, op.B), 256, 0, s>>>(aptr<const float>(p, op.p0), aptr<const float>(p, op.p1),
-                                                                     op.F, op.C, op.i0, to_out(p, op.out[0]));
+      CUDA_TRY(launch_pdl(mel_fin_kernel, dim3((items + 255) / 256, op.B), dim3(256), 0, s, aptr<const float>(p, op.p0), aptr<const float>(p, op.p1),
+                                                                     op.F, op.C, op.i0, to_out(p, op.out[0])));
       break;
     }
     case UV_OP_CONV_IN: {
       const long long n = (long long)op.B * op.Lp;
-      conv_in_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(aptr<const float>(p, op.p0), op.B, op.Lp, op.C, op.f0,
+      CUDA_TRY(launch_pdl(conv_in_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, s, aptr<const float>(p, op.p0), op.B, op.Lp, op.C, op.f0,
                                                                  wptr<const float>(p, op.p3), wptr<const float>(p, op.p4),
-                                                                 op.n_out, to_out(p, op.out[0]), to_out(p, op.out[1]));
+                                                                 op.n_out, to_out(p, op.out[0]), to_out(p, op.out[1])));
       break;
     }
     case UV_OP_INIT_X: {
       const long long n = (long long)op.B * op.Lp;
       const int B_total = op.i2 > 0 ? op.i2 : op.B;   // i1 / i2: first utterance of this lane / utterances of the whole call
-      init_x_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(p->io_dev, n, ((long long)op.i0 * B_total + op.i1) * op.Lp, op.f0,
-                                                                aptr<float>(p, op.p0));
+      CUDA_TRY(launch_pdl(init_x_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, s, p->io_dev, n, ((long long)op.i0 * B_total + op.i1) * op.Lp, op.f0,
+                                                                aptr<float>(p, op.p0)));
       break;
     }
     case UV_OP_CONV_OUT: {
       const long long n = (long long)op.B * op.Lp;
-      conv_out_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(to_desc(p, op.a), op.B, op.Lp, op.C, wptr<const float>(p, op.p3),
+      CUDA_TRY(launch_pdl(conv_out_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, s, to_desc(p, op.a), op.B, op.Lp, op.C, wptr<const float>(p, op.p3),
                                                                   wptr<const float>(p, op.p4), aptr<float>(p, op.p0),
                                                                   aptr<const StepCoef>(p, op.p1), op.i0, p->io_dev, op.i1,
-                                                                  op.i2 > 0 ? op.i2 : op.B);
+                                                                  op.i2 > 0 ? op.i2 : op.B));
       break;
     }
     case UV_OP_POST:
-      post_kernel<<<op.B, 1024, 0, s>>>(aptr<const float>(p, op.p0), op.T, op.Lp, op.i0, aptr<const float>(p, op.p1),
-                                        aptr<const int>(p, op.p2), p->io_dev, op.i1);
+      CUDA_TRY(launch_pdl(post_kernel, dim3(op.B), dim3(1024), 0, s, aptr<const float>(p, op.p0), op.T, op.Lp, op.i0, aptr<const float>(p, op.p1),
+                                        aptr<const int>(p, op.p2), p->io_dev, op.i1));
       break;
     case UV_OP_FILM:
       film_kernel<<<op.i0, 512, 2 * op.C * sizeof(float), s>>>(aptr<const float>(p, op.p0), op.i1, op.C, op.H, op.i2,

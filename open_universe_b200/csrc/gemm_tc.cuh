@@ -120,6 +120,14 @@ __device__ __forceinline__ bool elect_one() {
   asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.b32 %0, 1, 0, p;\n\t}" : "=r"(pred));
   return pred != 0;
 }
+__device__ __forceinline__ unsigned long long gtimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+// phase stamps of one CTA (debug; P.clk == nullptr in production): 0 entry, 1 prologue done, 2 first tile's loads
+// issued, 3 resident weights landed, 4 first A slab landed, 5 first accumulator complete, 6 last tile stored, 7 exit
+#define UV_STAMP(i) do { if (P.clk) P.clk[(size_t)blockIdx.x * 8 + (i)] = gtimer(); } while (0)
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
@@ -317,6 +325,7 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
   };
   int cur_tile = sched_next();
   if (cur_tile < 0) return;
+  pdl_wait();   // residual loads and output stores below touch the predecessors' tensors
   int n_tile = 0, m_tile = 0;
 
   // state of the tile being processed
@@ -445,6 +454,7 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
   const bool have = g_begin < g_end;
   mbar_wait(full0, 0, P.err_flag, 6);
   tc_fence_after();
+  if (warp == 2 && lane == 0) UV_STAMP(5);
   if (have) tc_ld16_issue(t_lane + 16u * g_begin, r0);
   for (;;) {
     tile_setup();
@@ -494,7 +504,10 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
       }
     }
     if (!next_known) next_tile = sched_next();
-    if (next_tile < 0) break;
+    if (next_tile < 0) {
+      if (warp == 2 && lane == 0) UV_STAMP(6);
+      break;
+    }
     if (!prefetched) {
       mbar_wait(full0 + 8u * nstage, nphase, P.err_flag, 6);
       tc_fence_after();
@@ -512,6 +525,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
   extern __shared__ __align__(1024) uint8_t smem[];
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) UV_STAMP(0);
+  pdl_launch_dependents();   // the next kernel's CTAs take over this SM when this CTA exits and start their own prologue
 
   // smem carve-up: ones tile | FiLM table | identity images | A ring | B ring (or resident weight set) | barriers | tmem ptr
   uint8_t* ones = smem;
@@ -574,6 +589,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  if (threadIdx.x == 0) UV_STAMP(1);
 
   const int n_shift = P.smax - P.smin + 1;
   const int rows_a = kTileM + P.smax - P.smin;  // halo'd slab rows
@@ -605,6 +621,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
       uint32_t sp = 0;
       int tile = atomicAdd(P.sched, 1);
       int tile_nxt = atomicAdd(P.sched, 1);
+      pdl_wait();   // weights and the tile counter do not depend on the predecessor; the activations do
       for (;;) {
         const bool live = tile < total_tiles;
         mbar_wait(smem_u32(&s_empty[ss]), sp ^ 1, P.err_flag, 9);
@@ -668,6 +685,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
             if (++ia == P.na_stages) { ia = 0; pa ^= 1; }
           }
         }
+        if (ss == 1 && sp == 0) UV_STAMP(2);
         tile = tile_nxt;
         tile_nxt = tile_nn;
       }
@@ -694,6 +712,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
         mbar_wait(smem_u32(&b_full[0]), 0, P.err_flag, 7);
         tc_fence_after();
       }
+      UV_STAMP(3);
+      bool first_slab = true;
       int ia = 0, ib = 0, as = 0, ss = 0;
       uint32_t pa = 0, pb = 0, pt = 1, sp = 0;
       for (;;) {
@@ -728,6 +748,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
         for (int sg = 0; sg < P.n_src * P.n_groups; ++sg) {
           mbar_wait(smem_u32(&a_full[ia]), pa, P.err_flag, 4);
           tc_fence_after();
+          if (first_slab) { UV_STAMP(4); first_slab = false; }
           const uint32_t a_lo = a_lo0 + (uint32_t)ia * a_stage16;
           for (int q = 0; q < n_shift; ++q) {
             uint32_t bl;
@@ -816,6 +837,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
   }
   // all claims of this CTA are done: the last CTA out rewinds the counter pair for the next launch
   if (threadIdx.x == 0) {
+    UV_STAMP(7);
     __threadfence();
     if (atomicAdd(P.sched + 1, 1) == (int)gridDim.x - 1) {
       P.sched[0] = 0;
@@ -902,8 +924,7 @@ inline cudaError_t gemm_launch(GemmParams p, int num_sms, cudaStream_t stream) {
   // always the whole shared memory of the SM: one CTA per SM, and never co-resident with a GRU CTA of the other
   // lane (whose tensor-memory allocation would stall this CTA's tcgen05.alloc for the length of the recurrence)
   (void)smem;
-  gemm_tc_kernel<<<grid, kGemmThreads, kGemmSmemBudget, stream>>>(p);
-  return cudaGetLastError();
+  return launch_pdl(gemm_tc_kernel, dim3(grid), dim3(kGemmThreads), kGemmSmemBudget, stream, p);
 }
 
 }  // namespace uv

@@ -294,6 +294,10 @@ __global__ void __launch_bounds__(kGruThreads, 1) gru_kernel(const __grid_consta
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  // Everything above (barriers, tensor-memory allocation, the W_hh bulk load) is independent of the predecessor.
+  // No early pdl_launch_dependents() here: the dependents' CTAs would sit on the free SMs for the whole recurrence
+  // and keep the other utterance lane's kernels out.
+  pdl_wait();
   const uint32_t tmem_base = *tmem_ptr_smem;
   if (warp < 4) {
     // W_hh slice: staging image in shared memory ([K chunk][row][8]) -> tensor memory (lane = row,
@@ -580,13 +584,15 @@ inline cudaError_t gru_launch(const GruParams& g, cudaStream_t s) {
   cfg.blockDim = dim3(kGruThreads);
   cfg.dynamicSmemBytes = L.total;
   cfg.stream = s;
-  cudaLaunchAttribute at[1];
+  cudaLaunchAttribute at[2];
   at[0].id = cudaLaunchAttributeClusterDimension;
   at[0].val.clusterDim.x = kGruNC;
   at[0].val.clusterDim.y = 1;
   at[0].val.clusterDim.z = 1;
+  at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = at;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = pdl_enabled() ? 2 : 1;
   return cudaLaunchKernelEx(&cfg, gru_kernel, g);
 }
 

@@ -47,6 +47,8 @@ __device__ __forceinline__ void block_sum3(double& a, double& b, double& c, doub
 // b_off = first utterance of this lane in the caller's batch (the io tensors cover all lanes).
 __global__ void __launch_bounds__(1024) prep_kernel(const IoTable* io, int b_off, int T, int Lp, int pad_left, float level,
                                                     float* sig, float* mix_rms) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ double sh[96];
   const int b = blockIdx.x;
   const float* mix = io->mix + (size_t)(b_off + b) * T;
@@ -85,6 +87,8 @@ __global__ void __launch_bounds__(512) mel_kernel(const float* __restrict__ sig,
                                                   int nb, int nbp, int n_mels, int pad_left,
                                                   const float* __restrict__ basis, const float* __restrict__ fb,
                                                   float* __restrict__ melraw, float* __restrict__ energy, int nft) {
+  pdl_launch_dependents();
+  pdl_wait();
   extern __shared__ float smem_f[];
   const int span = (kMelFT - 1) * hop + n_fft;
   float* xs = smem_f;          // [span]
@@ -194,6 +198,8 @@ __global__ void __launch_bounds__(512) mel_kernel(const float* __restrict__ sig,
 // Global mel normalisation (condition.py:105-106): x / clamp(sqrt(mean_t sum_m x^2), 1e-5) -> bf16 planes.
 __global__ void __launch_bounds__(256) mel_fin_kernel(const float* __restrict__ melraw, const float* __restrict__ energy,
                                                       int F, int n_mels, int nft, OutDesc out) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float s_inv;
   const int b = blockIdx.y;
   if (threadIdx.x == 0) {
@@ -221,6 +227,8 @@ __global__ void __launch_bounds__(256) mel_fin_kernel(const float* __restrict__ 
 __global__ void __launch_bounds__(256) conv_in_kernel(const float* __restrict__ x, int B, int Lp, int C, float in_scale,
                                                       const float* __restrict__ w /*[3][C]*/, const float* __restrict__ bias,
                                                       int n_out, OutDesc o0, OutDesc o1) {
+  pdl_launch_dependents();
+  pdl_wait();
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (long long)B * Lp) return;
   const int b = (int)(idx / Lp), l = (int)(idx - (long long)b * Lp);
@@ -253,6 +261,8 @@ __global__ void __launch_bounds__(256) conv_in_kernel(const float* __restrict__ 
 
 // ---------------------------------------------------------------- INIT_X   x = sigma_0 * z_0 (universe.py:326)
 __global__ void __launch_bounds__(256) init_x_kernel(const IoTable* io, long long n, long long noise_off, float sigma0, float* x) {
+  pdl_launch_dependents();
+  pdl_wait();
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) x[i] = sigma0 * io->noise[noise_off + i];
 }
@@ -264,6 +274,8 @@ __global__ void __launch_bounds__(256) conv_out_kernel(TensDesc a, int B, int Lp
                                                        const float* __restrict__ bias, float* __restrict__ x,
                                                        const StepCoef* __restrict__ coef, int step, const IoTable* io,
                                                        int b_off, int B_total) {
+  pdl_launch_dependents();
+  pdl_wait();
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (long long)B * Lp) return;
   const int b = (int)(idx / Lp), l = (int)(idx - (long long)b * Lp);
@@ -293,6 +305,8 @@ __global__ void __launch_bounds__(256) conv_out_kernel(TensDesc a, int B, int Lp
 __global__ void __launch_bounds__(1024) post_kernel(const float* __restrict__ x, int T, int Lp, int pad_left,
                                                     const float* __restrict__ mix_rms, const int* __restrict__ keep_rms,
                                                     const IoTable* io, int b_off) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ double sh[96];
   __shared__ float s_max[32];
   const int b = blockIdx.x;

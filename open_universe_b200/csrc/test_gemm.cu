@@ -6,6 +6,7 @@
 #include <cstring>
 #include <cmath>
 #include <string>
+#include <algorithm>
 #include <vector>
 
 #include "gemm_tc.cuh"
@@ -266,8 +267,17 @@ static int run_case(const Case& c, int swap_lbo, int num_sms) {
 }
 
 // Throughput of layer-shaped problems (cfg 2 sizes: B=64, 4 s clips).
-static void run_perf(int num_sms) {
-  struct PC { const char* name; int B, Lv, C, k, add, nout; } pcs[] = {
+// phases = true: a few layers at 1/4 and full size with the per-CTA phase stamps of the kernel (where a launch's
+// fixed cost goes); times in us relative to the earliest CTA entry, min / median / max over the CTAs.
+static void run_perf(int num_sms, bool phases = false) {
+  struct PC { const char* name; int B, Lv, C, k, add, nout; };
+  std::vector<PC> pcs;
+  if (phases) pcs = {{"L0 C32 k3 B16", 16, 64160, 32, 3, 0, 1}, {"L0 C32 k3 B64", 64, 64160, 32, 3, 0, 1},
+                     {"L1 C64 k5 B16", 16, 32080, 64, 5, 0, 1}, {"L1 C64 k5 B64", 64, 32080, 64, 5, 0, 1},
+                     {"L2 C128 k3 B16", 16, 8020, 128, 3, 0, 1}, {"L2 C128 k3 B64", 64, 8020, 128, 3, 0, 1},
+                     {"L3 C256 k3 B16", 16, 2005, 256, 3, 0, 1}, {"L3 C256 k3 B64", 64, 2005, 256, 3, 0, 1},
+                     {"L4 C512 k3 B64", 64, 401, 512, 3, 0, 1}};
+  else pcs = {
       {"L0 C32 k5", 64, 64160, 32, 5, 0, 1}, {"L0 C32 k3", 64, 64160, 32, 3, 0, 1}, {"L0 C32 k3 +add 2out", 64, 64160, 32, 3, 1, 2},
       {"L0 C32 k3 +add 1out", 64, 64160, 32, 3, 1, 1}, {"L0 C32 k3 2out", 64, 64160, 32, 3, 0, 2}, {"L0 C32 k3 3out", 64, 64160, 32, 3, 0, 3},
       {"L1 C64 k3 +add 1out", 64, 32080, 64, 3, 1, 1}, {"L1 C64 k3 2out", 64, 32080, 64, 3, 0, 2},
@@ -275,6 +285,8 @@ static void run_perf(int num_sms) {
       {"L2 C128 k5", 64, 8020, 128, 5, 0, 1}, {"L2 C128 k3", 64, 8020, 128, 3, 0, 1}, {"L2 C128 k3 +add 2out", 64, 8020, 128, 3, 1, 2},
       {"L3 C256 k5", 64, 2005, 256, 5, 0, 1}, {"L3 C256 k3", 64, 2005, 256, 3, 0, 1},
       {"L4 C512 k5", 64, 401, 512, 5, 0, 1}, {"L4 C512 k3", 64, 401, 512, 3, 0, 1}};
+  unsigned long long* d_clk = nullptr;
+  if (phases) CK(cudaMalloc(&d_clk, (size_t)num_sms * 8 * 8));
   for (auto& pc : pcs) {
     HT A = make_tensor(pc.B, pc.Lv, pc.C, 1, 2, false);
     CK(cudaMemset(A.dev, 0x3c, A.data.size()));  // small finite bf16 values everywhere
@@ -314,6 +326,32 @@ static void run_perf(int num_sms) {
     double flop = 2.0 * pc.B * pc.Lv * (double)pc.C * pc.C * pc.k;
     double bytes = (double)pc.B * pc.Lv * pc.C * 2 * (1 + pc.nout + pc.add);
     printf("[perf %s] %.3f ms  %.1f TFLOP/s  %.0f GB/s (algorithmic reads + writes)\n", pc.name, ms, flop / ms * 1e-9, bytes / ms * 1e-6);
+    if (phases) {
+      CK(cudaMemset(d_clk, 0, (size_t)num_sms * 64));
+      p.clk = d_clk;
+      CK(cudaEventRecord(e0));
+      CK(gemm_launch(p, num_sms, 0));
+      CK(cudaEventRecord(e1));
+      CK(cudaDeviceSynchronize());
+      CK(cudaEventElapsedTime(&ms, e0, e1));
+      std::vector<unsigned long long> h((size_t)num_sms * 8);
+      CK(cudaMemcpy(h.data(), d_clk, h.size() * 8, cudaMemcpyDeviceToHost));
+      unsigned long long t0 = ~0ull;
+      int nc = 0;
+      for (int c = 0; c < num_sms; ++c)
+        if (h[(size_t)c * 8]) { t0 = std::min(t0, h[(size_t)c * 8]); ++nc; }
+      static const char* nm[8] = {"entry", "prologue done", "1st tile loads issued", "weights landed", "1st A slab landed",
+                                  "1st accumulator done", "last tile stored", "exit"};
+      printf("   single launch %.1f us (events), %d CTAs; phase: min / median / max us after the first CTA entry\n", ms * 1e3, nc);
+      for (int i = 0; i < 8; ++i) {
+        std::vector<double> v;
+        for (int c = 0; c < num_sms; ++c)
+          if (h[(size_t)c * 8 + i]) v.push_back((double)(h[(size_t)c * 8 + i] - t0) * 1e-3);
+        if (v.empty()) continue;
+        std::sort(v.begin(), v.end());
+        printf("   %-22s %8.2f %8.2f %8.2f\n", nm[i], v.front(), v[v.size() / 2], v.back());
+      }
+    }
     cudaFree(O3.dev); cudaFree(AD.dev); cudaFree(A.dev); cudaFree(O.dev); cudaFree(O2.dev); cudaFree(d_w); cudaFree(d_err);
   }
 }
@@ -326,6 +364,7 @@ int main(int argc, char** argv) {
   int swap = argc > 2 ? atoi(argv[2]) : 0;
   if (name == "list") { for (auto& c : kCases) printf("%s\n", c.name); return 0; }
   if (name == "perf") { run_perf(dev_sms); return 0; }
+  if (name == "phases") { run_perf(dev_sms, true); return 0; }
   for (auto& c : kCases)
     if (name == c.name) return run_case(c, swap, dev_sms);
   printf("unknown case %s\n", name.c_str());

@@ -12,6 +12,8 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
+#include <utility>
 
 namespace uv {
 
@@ -78,11 +80,42 @@ struct GemmParams {
   int n_acc;         // TMEM accumulator stages (1, 2 or 4), each holding both 128-row halves of a tile
   int* err_flag;     // set on watchdog timeout
   int* sched;        // [2] zero before the first launch: tile counter, finished-CTA counter (the kernel rewinds both)
+  unsigned long long* clk;   // debug (test_gemm phases): [gridDim.x][8] globaltimer stamps of the CTA's phases, or null
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
+
+// Programmatic dependent launch (every kernel of the per-step chain is launched with the "programmatic stream
+// serialization" attribute): the next kernel's CTAs may become resident and run their prologue (barrier init,
+// tensor-memory allocation, weight loads) as soon as every CTA of this grid has called pdl_launch_dependents();
+// they must call pdl_wait() before touching memory that a predecessor writes.  Without the launch attribute both
+// are no-ops.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+// Host side: <<<>>> with the optional programmatic-serialization attribute.
+#ifdef __CUDACC__
+inline bool pdl_enabled() {
+  static const bool on = !(getenv("UV_PDL") && atoi(getenv("UV_PDL")) == 0);
+  return on;
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
+}
+#endif
 
 __device__ __forceinline__ float prelu1(float v, float a) { return v >= 0.f ? v : a * v; }
 

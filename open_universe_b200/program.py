@@ -222,7 +222,7 @@ def build_program(pm, cfg, B, T, n_steps, aux=False, lanes=None):
     B0 = (B + 1) // 2
     pg0 = _build_lane(pm, cfg, B0, T, n_steps, b_off=0, B_total=B)
     pg1 = _build_lane(pm, cfg, B - B0, T, n_steps, b_off=B0, B_total=B, arena_base=pg0.arena, lane=1, shared=pg0)
-    stagger = os.environ.get("UV_LANE_STAGGER", "c.enc1.rc")
+    stagger = os.environ.get("UV_LANE_STAGGER", "c.enc3.rc")
     if stagger in pg0.names:
         pg0.ops[pg0.names.index(stagger)].sync |= 1
         first = next(i for i, op in enumerate(pg1.ops) if op.step != -2)
