@@ -111,6 +111,10 @@ typedef struct {
    * i2 = utterances of the whole call (the io tensors of uv_enhance always cover all lanes).            */
   int32_t lane;          /* 0 or 1                                                                */
   int32_t sync;          /* bit 0: record this lane's event after the op; bit 1: wait for the other lane's event first */
+  /* ---- UV_OP_GEMM: A stored raw.  a_act = 1: the kernel applies PReLU(a_slope) to A in shared memory, so the
+   * producer of A writes one tensor instead of a raw and an activated copy (blocks.py:209-231: PReLU -> conv). */
+  int32_t a_act;
+  float a_slope;
 } uv_op;
 
 typedef struct uv_model uv_model;

@@ -77,6 +77,8 @@ class UvOp(C.Structure):
         ("f3", C.c_float),
         ("lane", C.c_int32),
         ("sync", C.c_int32),
+        ("a_act", C.c_int32),
+        ("a_slope", C.c_float),
     ]
 
 

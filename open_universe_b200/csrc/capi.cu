@@ -138,6 +138,7 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
       g.rm_out = aptr<float>(p, op.rm_out); g.rm_ld = op.rm_ld;
       g.rm_H = op.rm_out >= 0 ? op.H : 0; g.rm_Bp = op.i1;   // GEMM ops with a row-major output feed the GRU (H, batch pitch)
       g.err_flag = p->err_flag;
+      g.a_act = op.a_act; g.a_slope = op.a_slope;
       g.sched = p->sched + 2 * op_index;
       CUDA_TRY(gemm_launch(g, p->model->num_sms, s));
       break;

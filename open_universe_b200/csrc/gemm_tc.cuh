@@ -27,7 +27,11 @@
 // software-pipelined: the TMEM load and the residual loads of column group g+1 are in
 // flight while group g is processed.  2-4 accumulator stages live in TMEM so the MMAs
 // run ahead of the epilogues.  Layers whose whole weight set fits keep it resident in
-// shared memory and give the rest to a deep A ring.  Persistent grid with a DYNAMIC tile
+// shared memory and give the rest to a deep A ring.  A tensor consumed through a PReLU may be
+// stored RAW (a_act): two transform warps then apply the activation to every A slab in shared
+// memory between its arrival and the MMAs (fp32 math, one bf16 rounding), so the producer of
+// that tensor writes ONE copy instead of a raw and an activated one -- the layers around it are
+// HBM bound.  Persistent grid with a DYNAMIC tile
 // schedule: the producer thread claims tile indices from a global counter (two claims in
 // flight, so the atomic's latency hides behind the current tile's copies) and publishes them
 // through a small shared-memory ring to the MMA issuer and the epilogue warps; -1 ends the
@@ -45,10 +49,11 @@ constexpr int kTileM = 256;         // rows per CTA tile (two UMMA sub-tiles)
 constexpr int kMaxAStages = 12;
 constexpr int kMaxBStages = 8;
 constexpr int kEpiWarps = 8;        // 4 TMEM lane quarters x 2 sub-tiles (16 = two column halves each: measured slower, the multi-output paths spill at 112 registers)
-constexpr int kGemmThreads = 64 + 32 * kEpiWarps;   // producer warp, MMA warp, epilogue warps
+constexpr int kXfWarps = 2;         // A-operand transform warps (PReLU of a raw tensor in shared memory)
+constexpr int kGemmThreads = 64 + 32 * kEpiWarps + 32 * kXfWarps;   // producer warp, MMA warp, epilogue warps, transform warps
 constexpr int kMaxAcc = 4;          // TMEM accumulator stages
 constexpr int kSchedSlots = 32;     // ring of claimed tile indices (producer -> MMA issuer + epilogue warps)
-constexpr int kSchedBytes = kSchedSlots * (4 + 2 * 8);
+constexpr int kSchedBytes = kSchedSlots * (4 + 2 * 8) + kMaxAStages * 8;   // + the a_ready barriers of the transform warps
 constexpr int kOnesBytes = 2 * kSubM * 16;   // [2 chunks][128 rows][8] bf16
 constexpr int kFilmMaxC = 768;
 constexpr int kFilmBytes = 2 * kFilmMaxC * 4;
@@ -175,6 +180,24 @@ template <bool LE1>
 __device__ __forceinline__ float prelu_t(float v, float a) {
   if (LE1) return fmaxf(v, a * v);
   return fmaf(a, fminf(v, 0.f), fmaxf(v, 0.f));
+}
+
+// PReLU of a bf16 pair: the products a x in fp32 (packed multiply), ONE rounding to bf16, then a packed max / min
+// against x itself: for a <= 1, max(x, rn(a x)) is x for x >= 0 and rn(a x) for x < 0 (rounding is monotone and x
+// is a bf16 value); for a > 1 the same holds with min.
+__device__ __forceinline__ uint32_t prelu_bf16x2(uint32_t x, float a, bool le1) {
+  const float lo = __uint_as_float(x << 16), hi = __uint_as_float(x & 0xffff0000u);
+  uint64_t s2, a2, p2;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(s2) : "f"(lo), "f"(hi));
+  asm("mov.b64 %0, {%1, %1};" : "=l"(a2) : "f"(a));
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(p2) : "l"(s2), "l"(a2));
+  float plo, phi;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(plo), "=f"(phi) : "l"(p2));
+  uint32_t p, r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(p) : "f"(phi), "f"(plo));
+  if (le1) asm("max.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(x), "r"(p));
+  else asm("min.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(x), "r"(p));
+  return r;
 }
 
 // floor(g / d) for 0 <= g < 2^24-ish without an integer division (per tile, per thread)
@@ -543,7 +566,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
   uint64_t* t_empty = t_full + kMaxAcc;
   uint64_t* s_full = t_empty + kMaxAcc;
   uint64_t* s_empty = s_full + kSchedSlots;
-  int* s_ring = reinterpret_cast<int*>(s_empty + kSchedSlots);
+  uint64_t* a_ready = s_empty + kSchedSlots;
+  int* s_ring = reinterpret_cast<int*>(a_ready + kMaxAStages);
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(s_ring + kSchedSlots);
 
   const uint32_t acc_stride = accum_stride_cols(P.N_TILE);
@@ -553,7 +577,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
     for (int i = 0; i < kMaxAStages; ++i) { mbar_init(smem_u32(&a_full[i]), 1); mbar_init(smem_u32(&a_empty[i]), 1); }
     for (int i = 0; i < kMaxBStages; ++i) { mbar_init(smem_u32(&b_full[i]), 1); mbar_init(smem_u32(&b_empty[i]), 1); }
     for (int i = 0; i < kMaxAcc; ++i) { mbar_init(smem_u32(&t_full[i]), 1); mbar_init(smem_u32(&t_empty[i]), kEpiWarps); }
-    for (int i = 0; i < kSchedSlots; ++i) { mbar_init(smem_u32(&s_full[i]), 1); mbar_init(smem_u32(&s_empty[i]), 1 + kEpiWarps); }
+    const uint32_t ring_readers = 1 + kEpiWarps + (P.a_act ? kXfWarps : 0);
+    for (int i = 0; i < kSchedSlots; ++i) { mbar_init(smem_u32(&s_full[i]), 1); mbar_init(smem_u32(&s_empty[i]), ring_readers); }
+    for (int i = 0; i < kMaxAStages; ++i) mbar_init(smem_u32(&a_ready[i]), kXfWarps);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   // ones tile: K columns 0 and 1 are 1.0 (they meet the hi / lo halves of the bias image), the rest 0
@@ -714,6 +740,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
       }
       UV_STAMP(3);
       bool first_slab = true;
+      const uint32_t a_wait0 = P.a_act ? smem_u32(a_ready) : smem_u32(a_full);
       int ia = 0, ib = 0, as = 0, ss = 0;
       uint32_t pa = 0, pb = 0, pt = 1, sp = 0;
       for (;;) {
@@ -746,7 +773,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
         }
         uint32_t img_lo = b_lo0;   // resident weights: images are consumed in storage order
         for (int sg = 0; sg < P.n_src * P.n_groups; ++sg) {
-          mbar_wait(smem_u32(&a_full[ia]), pa, P.err_flag, 4);
+          mbar_wait(a_wait0 + 8u * ia, pa, P.err_flag, 4);   // landed (and, for a raw A tensor, activated)
           tc_fence_after();
           if (first_slab) { UV_STAMP(4); first_slab = false; }
           const uint32_t a_lo = a_lo0 + (uint32_t)ia * a_stage16;
@@ -779,7 +806,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
         if (P.add_kc) {
           const uint32_t img16 = ((uint32_t)P.N_TILE * P.add_kc * 2u) >> 4;
           for (int j = 0; j < P.N_TILE / P.add_kc; ++j) {
-            mbar_wait(smem_u32(&a_full[ia]), pa, P.err_flag, 4);
+            mbar_wait(a_wait0 + 8u * ia, pa, P.err_flag, 4);
             tc_fence_after();
             uint32_t al = r_lo0 + (uint32_t)ia * a_stage16;
             uint32_t bl = i_lo0 + (uint32_t)j * img16;
@@ -796,6 +823,54 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
         }
         tc_commit(smem_u32(&t_full[as]));
         if (++as == n_acc) { as = 0; pt ^= 1; }
+      }
+    }
+  } else if (warp >= 2 + kEpiWarps) {
+    // ============================== A-operand transform (only for a raw A tensor)
+    if (P.a_act) {
+      const int w = warp - (2 + kEpiWarps);
+      const float slope = P.a_slope;
+      const bool le1 = slope <= 1.f;
+      const int nvec = (int)(a_bytes >> 4);
+      const int n_conv = P.n_src * P.n_groups;
+      const int n_res = P.add_kc ? P.N_TILE / P.add_kc : 0;   // residual slabs pass through untouched (but are handed on: stage roles rotate)
+      int ia = 0, ss = 0;
+      uint32_t pa = 0, sp = 0;
+      for (;;) {
+        mbar_wait(smem_u32(&s_full[ss]), sp, P.err_flag, 8);
+        const int tile = s_ring[ss];
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&s_empty[ss]));
+        if (++ss == kSchedSlots) { ss = 0; sp ^= 1; }
+        if (tile < 0) break;
+        for (int sl = 0; sl < n_conv + n_res; ++sl) {
+          mbar_wait(smem_u32(&a_full[ia]), pa, P.err_flag, 4);
+          uint4* v = reinterpret_cast<uint4*>(a_ring + (size_t)ia * P.a_stage_bytes);
+          if (sl < n_conv) {
+            // four 16-byte vectors per lane in flight (the loop is shared-memory latency bound otherwise)
+            constexpr int kStep = 32 * kXfWarps;
+            for (int i0 = w * 32 + lane; i0 < nvec; i0 += 4 * kStep) {
+              uint4 u[4];
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                if (i0 + k * kStep < nvec) u[k] = v[i0 + k * kStep];
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                if (i0 + k * kStep < nvec) {
+                  u[k].x = prelu_bf16x2(u[k].x, slope, le1);
+                  u[k].y = prelu_bf16x2(u[k].y, slope, le1);
+                  u[k].z = prelu_bf16x2(u[k].z, slope, le1);
+                  u[k].w = prelu_bf16x2(u[k].w, slope, le1);
+                  v[i0 + k * kStep] = u[k];
+                }
+              }
+            }
+          }
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic stores -> tensor-core reads
+          __syncwarp();
+          if (lane == 0) mbar_arrive(smem_u32(&a_ready[ia]));
+          if (++ia == P.na_stages) { ia = 0; pa ^= 1; }
+        }
       }
     }
   } else {

@@ -123,9 +123,18 @@ static const Case kCases[] = {
     {"upsplit", 2, 300, 128, 1, -1, 1, 64, 64, 4, 64, true, false, true, false, 0.70710678f, 0, false},
     {"add256reg", 2, 300, 256, 1, -1, 1, 64, 256, 1, 128, true, false, true, false, 0.70710678f, 0, false},
     {"rmonly", 2, 130, 64, 1, 0, 0, 64, 256, 1, 128, true, false, false, false, 1.f, -1, true},
+    // raw A tensor, PReLU applied in shared memory by the transform warps (names starting with "xf")
+    {"xf32", 3, 777, 32, 1, -2, 2, 32, 32, 1, 32, true, false, false, false, 1.f, 0, false},
+    {"xf64add", 2, 500, 64, 1, -2, 2, 64, 64, 1, 64, true, true, true, false, 0.70710678f, 2, false},
+    {"xfdown", 2, 100, 64, 4, -1, 1, 64, 128, 1, 128, true, false, false, false, 1.f, 0, false},
+    {"xfbig", 2, 401, 256, 1, -1, 1, 64, 512, 1, 128, true, false, false, false, 1.f, 0, false},
+    {"xfupsplit", 2, 300, 128, 1, -1, 1, 64, 64, 4, 64, true, false, true, false, 0.70710678f, 0, false},
 };
 
 static int run_case(const Case& c, int swap_lbo, int num_sms) {
+  const bool a_act = strncmp(c.name, "xf", 2) == 0;
+  const float a_slope = 0.3f;
+  auto xf = [&](float v) { return a_act ? bf2f(f2bf(v >= 0.f ? v : a_slope * v)) : v; };
   const int n_shift = c.smax - c.smin + 1;
   const int N_total = c.up * c.C_out;
   // A: split tensor with n_src phases; unsplit valid length = M_valid * n_src
@@ -204,12 +213,15 @@ static int run_case(const Case& c, int swap_lbo, int num_sms) {
   p.out[1].t = desc_of(out1); p.out[1].act = 2; p.out[1].a1 = 0.25f; p.out[1].a2 = -0.5f;
   p.rm_out = d_rm; p.rm_ld = N_total;
   p.err_flag = d_err;
+  p.a_act = a_act ? 1 : 0;
+  p.a_slope = a_slope;
   int* d_sched;
   CK(cudaMalloc(&d_sched, 8));
   CK(cudaMemset(d_sched, 0, 8));
   p.sched = d_sched;
 
   CK(gemm_launch(p, num_sms, 0));
+  CK(cudaDeviceSynchronize());      // (one counter pair per op: back-to-back launches of the SAME op must not overlap under PDL)
   CK(gemm_launch(p, num_sms, 0));   // relaunch: the kernel rewinds its own tile counter
   cudaError_t e = cudaDeviceSynchronize();
   int err = 0;
@@ -234,7 +246,7 @@ static int run_case(const Case& c, int swap_lbo, int num_sms) {
         for (int s = 0; s < c.n_src; ++s)
           for (int q = 0; q < n_shift; ++q)
             for (int ci = 0; ci < c.C_in; ++ci)
-              acc += (double)A.get_row(s, b, m + c.smin + q, ci) *
+              acc += (double)xf(A.get_row(s, b, m + c.smin + q, ci)) *
                      W[(((size_t)n * c.n_src + s) * n_shift + q) * c.C_in + ci];
         int phase = n / c.C_out, co = n % c.C_out, l = c.up * m + phase;
         double v = acc;
@@ -284,7 +296,10 @@ static void run_perf(int num_sms, bool phases = false) {
       {"L1 C64 k5", 64, 32080, 64, 5, 0, 1}, {"L1 C64 k3", 64, 32080, 64, 3, 0, 1}, {"L1 C64 k3 +add 2out", 64, 32080, 64, 3, 1, 2},
       {"L2 C128 k5", 64, 8020, 128, 5, 0, 1}, {"L2 C128 k3", 64, 8020, 128, 3, 0, 1}, {"L2 C128 k3 +add 2out", 64, 8020, 128, 3, 1, 2},
       {"L3 C256 k5", 64, 2005, 256, 5, 0, 1}, {"L3 C256 k3", 64, 2005, 256, 3, 0, 1},
-      {"L4 C512 k5", 64, 401, 512, 5, 0, 1}, {"L4 C512 k3", 64, 401, 512, 3, 0, 1}};
+      {"L4 C512 k5", 64, 401, 512, 5, 0, 1}, {"L4 C512 k3", 64, 401, 512, 3, 0, 1},
+      // raw A tensor + in-kernel PReLU ("xf"): against the same layer above
+      {"L0 C32 k5 xf", 64, 64160, 32, 5, 0, 1}, {"L1 C64 k5 xf", 64, 32080, 64, 5, 0, 1}, {"L2 C128 k5 xf", 64, 8020, 128, 5, 0, 1},
+      {"L3 C256 k5 xf", 64, 2005, 256, 5, 0, 1}, {"L4 C512 k5 xf", 64, 401, 512, 5, 0, 1}};
   unsigned long long* d_clk = nullptr;
   if (phases) CK(cudaMalloc(&d_clk, (size_t)num_sms * 8 * 8));
   for (auto& pc : pcs) {
@@ -309,17 +324,19 @@ static void run_perf(int num_sms, bool phases = false) {
     p.out[2].t = desc_of(O3); p.out[2].act = 1; p.out[2].a1 = 0.5f;
     HT AD = make_tensor(pc.B, pc.Lv, pc.C, 1, 2, false);
     if (pc.add) p.add1 = desc_of(AD);
+    if (strstr(pc.name, " xf")) { p.a_act = 1; p.a_slope = 0.25f; }
     int* d_err; CK(cudaMalloc(&d_err, 4)); CK(cudaMemset(d_err, 0, 4));
     p.err_flag = d_err;
-    int* d_sched; CK(cudaMalloc(&d_sched, 8)); CK(cudaMemset(d_sched, 0, 8));
+    int* d_sched; CK(cudaMalloc(&d_sched, 64)); CK(cudaMemset(d_sched, 0, 64));
     p.sched = d_sched;
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
-    for (int i = 0; i < 3; ++i) CK(gemm_launch(p, num_sms, 0));
+    // one counter pair per op in the product; here the same op is relaunched back to back, so rotate pairs
+    for (int i = 0; i < 3; ++i) { p.sched = d_sched + 2 * (i & 7); CK(gemm_launch(p, num_sms, 0)); }
     CK(cudaDeviceSynchronize());
     const int iters = 10;
     CK(cudaEventRecord(e0));
-    for (int i = 0; i < iters; ++i) CK(gemm_launch(p, num_sms, 0));
+    for (int i = 0; i < iters; ++i) { p.sched = d_sched + 2 * (i & 7); CK(gemm_launch(p, num_sms, 0)); }
     CK(cudaEventRecord(e1));
     CK(cudaDeviceSynchronize());
     float ms; CK(cudaEventElapsedTime(&ms, e0, e1)); ms /= iters;

@@ -41,7 +41,16 @@ class Level:
 
 
 MEL_FT = 32   # frames per CTA of the mel kernel (csrc/small_ops.cuh kMelFT)
+# A tensor that is consumed both raw (residual / skip) and through a PReLU (the next conv) is written ONCE, raw; the
+# consuming GEMM activates it in shared memory (csrc/gemm_tc.cuh, a_act).  UV_RAW_A=0 restores the two-copy scheme.
+RAW_A = os.environ.get("UV_RAW_A", "1") != "0" and os.environ.get("UV_FUSE_CONVBLOCKS", "") != "1"
+RAW_A_MAXC = int(os.environ.get("UV_RAW_A_MAXC", "512"))   # channel limit of the scheme (measured on B200: it pays at every level, 46.2 ms per pass against 46.7 with 128 and 48.5 with 32)
 FUSE_CONVBLOCKS = os.environ.get("UV_FUSE_CONVBLOCKS", "") == "1"   # experimental: one launch per C <= 64 ConvBlock (csrc/convblock.cuh); measured slower than three GEMM launches so far
+
+
+def raw_ok(C):
+    """One raw copy + in-kernel activation for a C-channel tensor?  Pays where the layers are HBM bound."""
+    return RAW_A and C <= RAW_A_MAXC
 
 
 class _PartSink:
@@ -95,7 +104,7 @@ class Program:
 
     # ---- op helpers
     def gemm(self, name, layer, a, lev_rows, M_valid, outs, step=-1, add1=None, add2=None, scale=1.0,
-             film=-1, rm_out=-1, bias=True):
+             film=-1, rm_out=-1, bias=True, a_slope=None):
         ly = self.pm.layers[layer]
         op = new_op(_abi.OP_GEMM, step)
         op.a = a
@@ -117,6 +126,8 @@ class Program:
             op.out[i].t, op.out[i].act, op.out[i].a1, op.out[i].a2 = t, act, a1, a2
         op.rm_out = rm_out
         op.rm_ld = ly["N_total"]
+        if a_slope is not None:   # `a` is a raw tensor: PReLU(a_slope) is applied inside the kernel
+            op.a_act, op.a_slope = 1, a_slope
         return self.emit(op, name)
 
 
@@ -310,7 +321,8 @@ def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_
     def conv_block(pfx, name, lev, C, h_raw, h_act, v_outs, step=-1, film=-1, cond=None, cond_out=None,
                    v_add2=None, v_scale=SQRT1_2, only_conv1=False):
         """conv1 -> [+cond]/sqrt2 -> [FiLM] -> conv2 -> conv3 -> (h + c)/sqrt2  (blocks.py:387-403).
-        h_act = PReLU_conv1(h), h_raw = h.  v_outs: outputs of the residual sum."""
+        h_act = PReLU_conv1(h), h_raw = h (h_act = None: only h exists, conv1 activates it in the kernel).
+        v_outs: outputs of the residual sum."""
         c1 = pg.tens(f"{pfx}tmp.c1.{lev.L}.{C}", lev, C)
         c2 = pg.tens(f"{pfx}tmp.c2.{lev.L}.{C}", lev, C)
         s2, s3 = L[name + ".conv2"]["slope"], L[name + ".conv3"]["slope"]
@@ -319,15 +331,16 @@ def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_
             outs.append(_raw(cond_out))
         lys = [L[name + f".conv{k}"] for k in (1, 2, 3)]
         fuse = (
-            FUSE_CONVBLOCKS and not only_conv1 and v_add2 is None and C % 16 == 0 and C <= 64
+            FUSE_CONVBLOCKS and h_act is not None and not only_conv1 and v_add2 is None and C % 16 == 0 and C <= 64
             and all(ly["KC"] == C and ly["N_TILE"] == C and ly["N_total"] == C and ly["up"] == 1 and ly["n_src"] == 1 for ly in lys)
             and (lys[0]["smin"], lys[0]["smax"]) == (-2, 2) and all((ly["smin"], ly["smax"]) == (-1, 1) for ly in lys[1:])
             and len(v_outs) <= (2 if cond_out is not None else 3)
             and h_raw.split == 1 and h_raw.dtype == DT_BF16 and (cond is None or (cond.split == 1 and cond.dtype == DT_BF16))
         )
         sink = _PartSink(pg) if fuse else pg
-        g1 = sink.gemm(name + ".conv1", name + ".conv1", h_act, lev, lev.L, outs, step, add1=cond,
-                       scale=SQRT1_2 if cond is not None else 1.0, film=film)
+        g1 = sink.gemm(name + ".conv1", name + ".conv1", h_act if h_act is not None else h_raw, lev, lev.L, outs, step, add1=cond,
+                       scale=SQRT1_2 if cond is not None else 1.0, film=film,
+                       a_slope=None if h_act is not None else L[name + ".conv1"]["slope"])
         if only_conv1:
             return
         g2 = sink.gemm(name + ".conv2", name + ".conv2", c1, lev, lev.L, [_act(c2, s3)], step)
@@ -386,12 +399,14 @@ def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_
     conv_block("c.", "c.melblk", lb, Cb, mb_raw, mb_act, [_raw(x_mel)])
 
     # input conv (condition.py:360) and encoder (condition.py:189-206)
-    h_raw, h_act = pg.tens("c.h0", lv[0], chans[0]), pg.tens("c.h0a", lv[0], chans[0])
+    raw0 = raw_ok(chans[0])
+    h_raw, h_act = pg.tens("c.h0", lv[0], chans[0]), None if raw0 else pg.tens("c.h0a", lv[0], chans[0])
     op = new_op(_abi.OP_CONV_IN)
     op.B, op.Lp, op.C, op.p0, op.p3, op.p4, op.f0 = B, Lp, chans[0], pg.sig, L["c.in"]["w_w"], L["c.in"]["bias_w"], 1.0
-    op.n_out = 2
+    op.n_out = 1 if raw0 else 2
     op.out[0].t = h_raw
-    op.out[1].t, op.out[1].act, op.out[1].a1, op.out[1].a2 = h_act, 1, L["c.enc0.conv1"]["slope"], 1.0
+    if not raw0:
+        op.out[1].t, op.out[1].act, op.out[1].a1, op.out[1].a2 = h_act, 1, L["c.enc0.conv1"]["slope"], 1.0
     pg.emit(op, "c.in")
     st_inputs = []
     for i in range(nlev):
@@ -404,9 +419,14 @@ def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_
             outs.append(_act(vst, L[f"c.st{i}"]["slope"]))
             st_inputs.append((i, vst))
         conv_block("c.", f"c.enc{i}", lv[i], C, h_raw, h_act, outs)
-        h_raw, h_act = pg.tens(f"c.h{i+1}", lv[i + 1], chans[i + 1]), pg.tens(f"c.h{i+1}a", lv[i + 1], chans[i + 1])
         nxt = f"c.enc{i+1}.conv1" if (i + 1 < nlev or extra) else "c.cb1.conv1"
-        pg.gemm(f"c.enc{i}.rc", f"c.enc{i}.rc", vds, lv[i + 1], lv[i + 1].L, [_raw(h_raw), _act(h_act, L[nxt]["slope"])])
+        h_raw = pg.tens(f"c.h{i+1}", lv[i + 1], chans[i + 1])
+        if raw_ok(chans[i + 1]) and (i + 1 < nlev or extra):
+            h_act = None
+            pg.gemm(f"c.enc{i}.rc", f"c.enc{i}.rc", vds, lv[i + 1], lv[i + 1].L, [_raw(h_raw)])
+        else:
+            h_act = pg.tens(f"c.h{i+1}a", lv[i + 1], chans[i + 1])
+            pg.gemm(f"c.enc{i}.rc", f"c.enc{i}.rc", vds, lv[i + 1], lv[i + 1].L, [_raw(h_raw), _act(h_act, L[nxt]["slope"])])
     # extra 512-channel block (condition.py:159-166): x = its v_out
     if extra:
         x_last = pg.tens("c.x_last", lb, Cb, dtype=DT_F32)
@@ -454,8 +474,12 @@ def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_
         if r is not None:
             lev_i -= 1
             lev, C = lv[lev_i], chans[lev_i]
-            u_raw, u_act = pg.tens(f"{name}.u", lev, C), pg.tens(f"{name}.ua", lev, C)
-            outs = [_act(u_act, L[name + ".conv1"]["slope"])] + ([] if (last and not aux) else [_raw(u_raw)])
+            if raw_ok(C) and not (last and not aux):
+                u_raw, u_act = pg.tens(f"{name}.u", lev, C), None
+                outs = [_raw(u_raw)]
+            else:
+                u_raw, u_act = pg.tens(f"{name}.u", lev, C), pg.tens(f"{name}.ua", lev, C)
+                outs = [_act(u_act, L[name + ".conv1"]["slope"])] + ([] if (last and not aux) else [_raw(u_raw)])
             pg.gemm(name + ".rc", name + ".rc", y_act, lv[lev_i + 1], lv[lev_i + 1].L, outs)
             y_raw, y_act = u_raw, u_act
         lev, C = lv[lev_i], chans[lev_i]
@@ -494,14 +518,15 @@ def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_
     n_blocks = meta["n_blocks"]
     for n in range(n_steps):
         fbase = pg.film + n * R * 4
-        h_raw, h_act = pg.tens("s.h0", lv[0], chans[0]), pg.tens("s.h0a", lv[0], chans[0])
+        h_raw, h_act = pg.tens("s.h0", lv[0], chans[0]), None if raw0 else pg.tens("s.h0a", lv[0], chans[0])
         pg.step_first_op.append(len(pg.ops))
         op = new_op(_abi.OP_CONV_IN, n)
         op.B, op.Lp, op.C, op.p0, op.p3, op.p4 = B, Lp, chans[0], pg.x, L["s.in"]["w_w"], L["s.in"]["bias_w"]
         op.f0 = float(w_in[n])
-        op.n_out = 2
+        op.n_out = 1 if raw0 else 2
         op.out[0].t = h_raw
-        op.out[1].t, op.out[1].act, op.out[1].a1, op.out[1].a2 = h_act, 1, L["s.enc0.conv1"]["slope"], 1.0
+        if not raw0:
+            op.out[1].t, op.out[1].act, op.out[1].a1, op.out[1].a2 = h_act, 1, L["s.enc0.conv1"]["slope"], 1.0
         pg.emit(op, f"s{n}.in")
         skips = []
         for i in range(n_blocks):
@@ -514,17 +539,22 @@ def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_
                 skip = pg.tens(f"s.skip{i}", lev, C)
             skips.append(skip)
             outs = [_raw(skip)]
+            rc_slope = None
             if i < nlev:
-                vds = pg.tens(f"s.enc{i}.vds", lv[i + 1], C, split=rates[i])
-                outs.append(_act(vds, L[f"s.enc{i}.rc"]["slope"]))
+                if raw_ok(C):   # the down conv reads the (phase-split) skip tensor itself and activates it in the kernel
+                    vds, rc_slope = skip, L[f"s.enc{i}.rc"]["slope"]
+                else:
+                    vds = pg.tens(f"s.enc{i}.vds", lv[i + 1], C, split=rates[i])
+                    outs.append(_act(vds, L[f"s.enc{i}.rc"]["slope"]))
             conv_block("s.", f"s.enc{i}", lev, C, h_raw, h_act, outs, step=n, film=fbase + frows[f"enc{i}"] * 4)
             if i < nlev:
                 h_raw = pg.tens(f"s.h{i+1}", lv[i + 1], chans[i + 1])
                 outs = [_raw(h_raw)]
-                if i + 1 < n_blocks:
+                h_act = None
+                if i + 1 < n_blocks and not raw_ok(chans[i + 1]):
                     h_act = pg.tens(f"s.h{i+1}a", lv[i + 1], chans[i + 1])
                     outs.append(_act(h_act, L[f"s.enc{i+1}.conv1"]["slope"]))
-                pg.gemm(f"s.enc{i}.rc", f"s.enc{i}.rc", vds, lv[i + 1], lv[i + 1].L, outs, n)
+                pg.gemm(f"s.enc{i}.rc", f"s.enc{i}.rc", vds, lv[i + 1], lv[i + 1].L, outs, n, a_slope=rc_slope)
         gru_in = skips[-1] if extra else h_raw
         # decoder (score.py:197-211)
         lev_i = nlev
@@ -535,8 +565,8 @@ def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_
             if i == 0:
                 # GRU (score.py:117) fused with the first decoder block's (h + res)/sqrt2 when it has no up conv
                 if r is None:
-                    u_raw, u_act = pg.tens("s.dec0.u", lb, Cb), pg.tens("s.dec0.ua", lb, Cb)
-                    gru_layer("s.gru", gru_in, [_raw(u_raw), _act(u_act, L[name + ".conv1"]["slope"])], step=n,
+                    u_raw, u_act = pg.tens("s.dec0.u", lb, Cb), None if raw_ok(Cb) else pg.tens("s.dec0.ua", lb, Cb)
+                    gru_layer("s.gru", gru_in, [_raw(u_raw)] + ([] if raw_ok(Cb) else [_act(u_act, L[name + ".conv1"]["slope"])]), step=n,
                               add1=res, scale=SQRT1_2)
                 else:
                     y_act = pg.tens("s.gru_out", lb, Cb)
@@ -544,9 +574,9 @@ def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_
             if r is not None:
                 lev_i -= 1
                 lev, C = lv[lev_i], chans[lev_i]
-                u_raw, u_act = pg.tens(f"{name}.u", lev, C), pg.tens(f"{name}.ua", lev, C)
+                u_raw, u_act = pg.tens(f"{name}.u", lev, C), None if raw_ok(C) else pg.tens(f"{name}.ua", lev, C)
                 pg.gemm(name + ".rc", name + ".rc", y_act, lv[lev_i + 1], lv[lev_i + 1].L,
-                        [_raw(u_raw), _act(u_act, L[name + ".conv1"]["slope"])], n, add1=res, scale=SQRT1_2)
+                        [_raw(u_raw)] + ([] if raw_ok(C) else [_act(u_act, L[name + ".conv1"]["slope"])]), n, add1=res, scale=SQRT1_2)
             lev, C = lv[lev_i], chans[lev_i]
             v_act = pg.tens(f"{name}.va", lev, C)
             if i < n_dec - 1:

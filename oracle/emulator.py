@@ -83,6 +83,9 @@ class Emulator:
     # ---------------------------------------------------------------- ops
     def op_gemm(self, op):
         a = self.view(op.a).float()  # [n_src, nch, P, 8]
+        if op.a_act:
+            # raw A tensor: the kernel's transform warps apply PReLU in fp32 and round to bf16 once (csrc/gemm_tc.cuh)
+            a = torch.where(a >= 0, a, np.float32(op.a_slope) * a).to(torch.bfloat16).float()
         n_shift = op.smax - op.smin + 1
         C_in = op.a.nch * 8
         has_bias = op.bias_w >= 0
