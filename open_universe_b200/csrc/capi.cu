@@ -288,7 +288,7 @@ static int validate_ops(uv_plan* p) {
       if ((rc = check_tens(p, op.out[k].t, "out"))) return rc;
     if (op.type == UV_OP_GEMM) {
       if (op.a.off < 0 || op.KC % 16 || op.N_TILE % 16 || op.N_TILE > 256 || op.N_total % op.N_TILE ||
-          (op.a.nch * 8) % op.KC || op.C_out % op.N_TILE || op.smin < -kGuard || op.smax > kGuard || op.a.split != op.n_src)
+          (op.a.nch * 8) % op.KC || (op.C_out % op.N_TILE && (op.up <= 1 || op.N_TILE % op.C_out)) || op.smin < -kGuard || op.smax > kGuard || op.a.split != op.n_src)
         return fail(UV_ERR_INVALID, "malformed GEMM op #" + std::to_string(i));
       if (op.a.P < op.a.G + ((op.m_rows + kTileM - 1) / kTileM) * kTileM + op.smax)
         return fail(UV_ERR_INVALID, "GEMM A plane too short, op #" + std::to_string(i));

@@ -355,7 +355,8 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
   int stage = 0;
   uint32_t phase = 0;
   bool valid = false;
-  int n0 = 0, co0 = 0;
+  int n0 = 0, co0 = 0, t_b = 0, t_l = 0;
+  const int gpp = P.N_TILE > P.C_out ? (P.C_out >> 4) : 0x7fffffff;   // column groups per phase of a multi-phase tile
   OutPtr op[3], pa1, pa2;
   float* rm_row = nullptr;
 #pragma unroll
@@ -380,6 +381,7 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
     const int m = g - b * P.Lh_A;
     valid = (g < P.m_rows) && (m < P.M_valid);
     const int l_out = P.up * m + ph;
+    t_b = b; t_l = l_out;
     const int chunk_base = co0 >> 3;
 #pragma unroll
     for (int o = 0; o < 3; ++o) {
@@ -419,6 +421,13 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
 
   auto process = [&](int g16, const uint32_t* r, const AddRegs& ad) {
     if (!valid) return;
+    if (g16 >= gpp && g16 % gpp == 0) {
+      // next phase of a multi-phase tile (transposed conv): one output row further, channel chunks from 0 again
+      ++t_l;
+#pragma unroll
+      for (int o = 0; o < 3; ++o)
+        if ((MULTI || o == 0) && op[o].p) op[o] = out_ptr(P.out[o].t, t_b, t_l, 0, inv_split[o]);
+    }
     float v[16];
 #pragma unroll
     for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
@@ -693,16 +702,16 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
         }
         if (P.add_kc) {
           // residual operand (same row space, phase plane = output phase): one un-halo'd slab per identity image
-          const int n0 = n_tile * P.N_TILE;
-          const int phase = n0 / P.C_out;
-          const int co0 = n0 - phase * P.C_out;
           const int cpi = P.add_kc >> 3;
           for (int j = 0; j < P.N_TILE / P.add_kc; ++j) {
+            const int col = n_tile * P.N_TILE + j * P.add_kc;   // a tile may span several phases; a slab never does
+            const int phase = col / P.C_out;
+            const int co0 = col - phase * P.C_out;
             mbar_wait(smem_u32(&a_empty[ia]), pa ^ 1, P.err_flag, 1);
             const uint32_t fb = smem_u32(&a_full[ia]);
             mbar_expect_tx(fb, (uint32_t)cpi * kAddRowsBytes);
             const uint32_t dst = smem_u32(a_ring + (size_t)ia * P.a_stage_bytes);
-            const long long plane0 = (long long)phase * P.add1.nchunks + (co0 >> 3) + j * cpi;
+            const long long plane0 = (long long)phase * P.add1.nchunks + (co0 >> 3);
             const long long rowa = (long long)P.add1.G + (long long)m_tile * kTileM;
             for (int jc = 0; jc < cpi; ++jc) {
               const char* src = P.add1.base + (((plane0 + jc) * P.add1.P + rowa) << 4);
@@ -942,12 +951,16 @@ inline bool gemm_plan_pipeline(GemmParams& p) {
   if (p.add1.base && !p.add2.base && p.add1.esize_log2 == 1 && p.add1.Lh == p.Lh_A && p.add1.split == p.up &&
       p.add1.G == p.a_G && p.C_out <= 128 && !p.no_add_mma) {
     for (int kc = 64; kc >= 16; kc -= 16)
-      if (p.N_TILE % kc == 0) { p.add_kc = kc; break; }
+      if (p.N_TILE % kc == 0 && p.C_out % kc == 0) { p.add_kc = kc; break; }
     if (p.add_kc) {
       p.ident_bytes = p.N_TILE * p.N_TILE * 2;
       const int add_bytes = (p.add_kc / 8) * kAddRowsBytes;
       if (add_bytes > p.a_stage_bytes) p.a_stage_bytes = add_bytes;
     }
+  }
+  if (p.N_TILE > p.C_out) {
+    // tile spanning several phases of a transposed conv: whole phases only, adds through the tensor core only
+    if (p.up <= 1 || p.N_TILE % p.C_out || p.C_out % 16 || p.film || p.rm_out || p.add2.base || (p.add1.base && !p.add_kc)) return false;
   }
   p.n_tiles_m = (p.m_rows + kTileM - 1) / kTileM;
   const int stride = (int)accum_stride_cols(p.N_TILE);

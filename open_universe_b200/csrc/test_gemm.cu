@@ -129,6 +129,11 @@ static const Case kCases[] = {
     {"xfdown", 2, 100, 64, 4, -1, 1, 64, 128, 1, 128, true, false, false, false, 1.f, 0, false},
     {"xfbig", 2, 401, 256, 1, -1, 1, 64, 512, 1, 128, true, false, false, false, 1.f, 0, false},
     {"xfupsplit", 2, 300, 128, 1, -1, 1, 64, 64, 4, 64, true, false, true, false, 0.70710678f, 0, false},
+    // transposed convs whose N tile spans two whole phases (N_TILE = 2 C_out)
+    {"mp2upsplit", 3, 300, 64, 1, -1, 1, 64, 32, 2, 64, true, false, true, false, 0.70710678f, 0, false},
+    {"mp4upsplit", 2, 300, 128, 1, -1, 1, 64, 64, 4, 128, true, false, true, false, 0.70710678f, 0, false},
+    {"mp2up", 2, 301, 64, 1, -1, 1, 64, 32, 2, 64, true, false, false, false, 1.f, 2, false},
+    {"xfmp3up", 2, 200, 96, 1, -1, 1, 48, 32, 3, 96, true, false, false, false, 1.f, 0, false},
 };
 
 static int run_case(const Case& c, int swap_lbo, int num_sms) {

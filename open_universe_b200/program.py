@@ -45,6 +45,9 @@ MEL_FT = 32   # frames per CTA of the mel kernel (csrc/small_ops.cuh kMelFT)
 # consuming GEMM activates it in shared memory (csrc/gemm_tc.cuh, a_act).  UV_RAW_A=0 restores the two-copy scheme.
 RAW_A = os.environ.get("UV_RAW_A", "1") != "0" and os.environ.get("UV_FUSE_CONVBLOCKS", "") != "1"
 RAW_A_MAXC = int(os.environ.get("UV_RAW_A_MAXC", "512"))   # channel limit of the scheme (measured on B200: it pays at every level, 46.2 ms per pass against 46.7 with 128 and 48.5 with 32)
+# ... and of its use in front of the encoder's strided down convs (they re-read and re-activate all r phases of A for
+# every N tile, so the transform warps pace the wide levels)
+RAW_A_RC_MAXC = int(os.environ.get("UV_RAW_A_RC_MAXC", "64"))
 FUSE_CONVBLOCKS = os.environ.get("UV_FUSE_CONVBLOCKS", "") == "1"   # experimental: one launch per C <= 64 ConvBlock (csrc/convblock.cuh); measured slower than three GEMM launches so far
 
 
@@ -541,7 +544,7 @@ def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_
             outs = [_raw(skip)]
             rc_slope = None
             if i < nlev:
-                if raw_ok(C):   # the down conv reads the (phase-split) skip tensor itself and activates it in the kernel
+                if raw_ok(C) and C <= RAW_A_RC_MAXC:   # the down conv reads the (phase-split) skip tensor itself and activates it in the kernel
                     vds, rc_slope = skip, L[f"s.enc{i}.rc"]["slope"]
                 else:
                     vds = pg.tens(f"s.enc{i}.vds", lv[i + 1], C, split=rates[i])

@@ -12,6 +12,7 @@ All transformations are exact algebra done once at load time in fp32:
   * GRU recurrent weights into per-CTA K-major UMMA slices (csrc/gru.cuh).
 """
 import math
+import os
 
 import numpy as np
 import torch
@@ -54,6 +55,20 @@ def pick_ntile(c_out):
         if c_out % n == 0:
             return n
     raise ValueError(f"no N tile for C_out={c_out}")
+
+
+MULTI_PHASE = os.environ.get("UV_MULTI_PHASE", "1") != "0"
+
+
+def pick_ntile_up(c_out, up):
+    """N tile of a transposed conv (N = up x C_out columns, phase major).  A tile may span several whole phases:
+    the A slabs are then read once for k phases instead of once per phase and the MMAs are k times wider
+    (csrc/gemm_tc.cuh steps the output row at every phase boundary of a tile)."""
+    n = pick_ntile(c_out)
+    if not MULTI_PHASE or n != c_out:
+        return n
+    k = max(d for d in range(1, up + 1) if up % d == 0 and c_out * d <= 128)
+    return c_out * k
 
 
 def to_bf16_bits(x):
@@ -195,7 +210,7 @@ class PackedModel:
         """resid: the op that uses this layer adds a residual / condition tensor; for C_out <= 128 it goes
         through identity MMAs whose images take N_TILE^2 * 2 bytes of shared memory (csrc/gemm_tc.cuh)."""
         n, s, q, ci = w4.shape
-        n_tile = pick_ntile(c_out)
+        n_tile = pick_ntile_up(c_out, up) if up > 1 else pick_ntile(c_out)
         kc = pick_kc(ci, n, n_tile, s, q, reserve=n_tile * n_tile * 2 if (resid and c_out <= 128) else 0)
         bias_n = bias.float().repeat(n // c_out) if bias is not None else None  # column n -> channel n % C_out
         self.layers[name] = dict(
