@@ -201,6 +201,7 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
       break;
     }
     case UV_OP_CONV_IN: {
+      if (op.C > kEdgeMaxC || op.C % 8) return fail(UV_ERR_INVALID, "input conv: channel count unsupported");
       const long long n = (long long)op.B * op.Lp;
       CUDA_TRY(launch_pdl(conv_in_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, s, aptr<const float>(p, op.p0), op.B, op.Lp, op.C, op.f0,
                                                                  wptr<const float>(p, op.p3), wptr<const float>(p, op.p4),
@@ -215,6 +216,7 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
       break;
     }
     case UV_OP_CONV_OUT: {
+      if (op.C > kEdgeMaxC || op.C % 8) return fail(UV_ERR_INVALID, "output conv: channel count unsupported");
       const long long n = (long long)op.B * op.Lp;
       CUDA_TRY(launch_pdl(conv_out_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, s, to_desc(p, op.a), op.B, op.Lp, op.C, wptr<const float>(p, op.p3),
                                                                   wptr<const float>(p, op.p4), aptr<float>(p, op.p0),

@@ -13,6 +13,8 @@ struct IoTable {
   float* dbg;          // [n_steps][B][Lp] or null
 };
 
+constexpr int kEdgeMaxC = 128;   // channels of the 1 <-> C edge convs (32 / 48 in the reference configs)
+
 struct StepCoef {
   float a, b, c, pad_;
 };
@@ -228,6 +230,11 @@ __global__ void __launch_bounds__(256) conv_in_kernel(const float* __restrict__ 
                                                       const float* __restrict__ w /*[3][C]*/, const float* __restrict__ bias,
                                                       int n_out, OutDesc o0, OutDesc o1) {
   pdl_launch_dependents();
+  // the three taps and the bias of every channel, staged once per block: one 16-byte broadcast load per channel
+  // instead of four global loads per channel and thread (the kernel was load-instruction bound)
+  __shared__ float4 ws[kEdgeMaxC];
+  for (int c = threadIdx.x; c < C; c += blockDim.x) ws[c] = make_float4(w[c], w[C + c], w[2 * C + c], bias[c]);
+  __syncthreads();
   pdl_wait();
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (long long)B * Lp) return;
@@ -241,8 +248,8 @@ __global__ void __launch_bounds__(256) conv_in_kernel(const float* __restrict__ 
     float v[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      const int c = ch * 8 + i;
-      v[i] = fmaf(w[c], xm, fmaf(w[C + c], x0, fmaf(w[2 * C + c], xp, bias[c])));
+      const float4 q = ws[ch * 8 + i];
+      v[i] = fmaf(q.x, xm, fmaf(q.y, x0, fmaf(q.z, xp, q.w)));
     }
     if (n_out > 0) {
       float u[8];
@@ -275,6 +282,9 @@ __global__ void __launch_bounds__(256) conv_out_kernel(TensDesc a, int B, int Lp
                                                        const StepCoef* __restrict__ coef, int step, const IoTable* io,
                                                        int b_off, int B_total) {
   pdl_launch_dependents();
+  __shared__ __align__(16) float ws[3 * kEdgeMaxC];   // [tap][C]: 16-byte broadcast loads instead of one global load per weight
+  for (int i = threadIdx.x; i < 3 * C; i += blockDim.x) ws[i] = w[i];
+  __syncthreads();
   pdl_wait();
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (long long)B * Lp) return;
@@ -289,8 +299,10 @@ __global__ void __launch_bounds__(256) conv_out_kernel(TensDesc a, int B, int Lp
       rk.p += (long long)(k - 1) * 16;
       float v[8];
       load8(rk, 1, ch, v);
-#pragma unroll
-      for (int i = 0; i < 8; ++i) acc = fmaf(v[i], w[k * C + ch * 8 + i], acc);
+      const float4 w0 = *reinterpret_cast<const float4*>(ws + k * C + ch * 8);
+      const float4 w1 = *reinterpret_cast<const float4*>(ws + k * C + ch * 8 + 4);
+      acc = fmaf(v[0], w0.x, acc); acc = fmaf(v[1], w0.y, acc); acc = fmaf(v[2], w0.z, acc); acc = fmaf(v[3], w0.w, acc);
+      acc = fmaf(v[4], w1.x, acc); acc = fmaf(v[5], w1.y, acc); acc = fmaf(v[6], w1.z, acc); acc = fmaf(v[7], w1.w, acc);
     }
   }
   const StepCoef cf = coef[step];
