@@ -181,6 +181,32 @@ def test_full_size_properties_cfg2():
     assert uo.rel_l2(out3.cpu(), out[:2].cpu()) < 1e-6
 
 
+def test_two_lanes_equal_one_lane_and_oracle(monkeypatch):
+    """B >= 16 is compiled as two utterance lanes on two captured streams (odd B: 9 + 8 here).  Same bits as the
+    single-lane program of the whole batch (rows are computed independently of their tile / lane), and both
+    within the gate of the CPU oracle."""
+    model, cfg = _gpu_model("universepp_16k")
+    B, T = 17, 1700
+    g = torch.Generator().manual_seed(11)
+    mix = 0.05 * torch.randn(B, T, generator=g)
+    Lp = T + (model.tot_ds - T % model.tot_ds)
+    noise = torch.randn(8, B, Lp, generator=g)
+    monkeypatch.delenv("UV_LANES", raising=False)
+    out2, st2 = model.enhance_debug(mix.cuda(), noise.cuda(), keep_rms=True)
+    pg = model._plans[(B, T, 8, False)].pg
+    assert [l.B for l in pg.lanes] == [9, 8]
+    monkeypatch.setenv("UV_LANES", "1")
+    model._invalidate()
+    out1, st1 = model.enhance_debug(mix.cuda(), noise.cuda(), keep_rms=True)
+    assert len(model._plans[(B, T, 8, False)].pg.lanes) == 1
+    assert torch.equal(out1, out2) and torch.equal(st1, st2)
+    sd = {k: v.detach().cpu() for k, v in model.state_dict().items()}
+    ref, ref_steps = uo.enhance(sd, cfg.model, mix, [n[:, None, :] for n in noise], keep_rms=True, return_steps=True)
+    for i in range(8):
+        assert uo.rel_l2(st2[i].cpu(), ref_steps[i][:, 0]) < TOL, f"step {i}"
+    assert uo.rel_l2(out2.cpu(), ref) < TOL and uo.si_sdr(out2.cpu(), ref).min() > SISDR_MIN
+
+
 def test_gemm_kernel_unit_cases():
     exe = os.path.join(ROOT, "open_universe_b200", "csrc", "test_gemm")
     if not os.path.exists(exe):
