@@ -149,6 +149,8 @@ def run_native(args, wl, rank, world, local_rank):
     dev = torch.device("cuda", local_rank)
     torch.cuda.set_device(dev)
     if world > 1:
+        # stdout carries exactly one JSON line: keep NCCL's version / info banner out of it
+        os.environ["NCCL_DEBUG"] = os.environ.get("UV_NCCL_DEBUG", "WARN")
         dist.init_process_group("nccl", device_id=dev)
     cfg = load_model_cfg(wl["model"])
     fs = int(cfg.model.fs)
