@@ -1,0 +1,210 @@
+"""Enhance a file or a directory of audio files -- the caller users actually run
+(reference: open_universe/bin/enhance.py:24-192).
+
+Same command line as the reference (`input output --model --hf-token --model-strict --seed --device` plus the
+keywords of `model.enhance`, added by `inference_utils.add_enhance_arguments`), same output layout (the folder
+structure is retained), same per-file arithmetic: a file of C channels is a batch of C utterances
+(enhance.py:187-190), resampled to the model rate and back with `torchaudio.functional.resample`.
+
+What differs is the schedule.  The reference enhances one file at a time (B = #channels, a few thousand eager
+kernel launches each).  Here all utterances are gathered first, grouped into batches of IDENTICAL length (padding
+and the normalisation statistics depend on the length, universe.py:219-223,272, so equal-length batches leave every
+utterance's result unchanged); under `torchrun` the files are dealt whole to the ranks (one process per GPU, no
+collective: the outputs are files), and each batch is one replay of the native CUDA graph.  `--batch-size` bounds the batch.
+
+The noise of a batch is drawn by `enhance()` from the seeded generator in batch order, so results are reproducible
+for a given seed, input set and batch size, but they are not the reference's file-by-file draws.
+
+    python -m open_universe_b200.bin.enhance noisy/ enhanced/ --model exp/universepp/checkpoints/last.ckpt
+    torchrun --nproc-per-node 8 -m open_universe_b200.bin.enhance noisy/ enhanced/ --model ...
+"""
+import argparse
+import os
+import sys
+import time
+from pathlib import Path
+
+import numpy as np
+import torch
+
+from open_universe_b200 import inference_utils, sharding
+
+AUDIO_SUFFIXES = [".wav", ".mp3", ".flac"]   # reference enhance.py:33
+
+
+def handle_help():
+    """Defers --help until the model's own arguments are known (reference enhance.py:36-57)."""
+    help_idx = -1
+    for flag in ("--help", "-h"):
+        if flag in sys.argv:
+            help_idx = sys.argv.index(flag)
+    if "--model" not in sys.argv:
+        return False
+    if help_idx >= 0:
+        sys.argv.pop(help_idx)
+        return True
+    return False
+
+
+def find_files(path):
+    """reference enhance.py:60-74"""
+    path = Path(path)
+    if not path.is_dir():
+        return [path], path.parent, False
+    files = sorted(p for p in path.rglob("*") if p.suffix in AUDIO_SUFFIXES)
+    return files, path, True
+
+
+def load_audio(path):
+    """-> (float32 tensor [channels, samples], fs).  torchaudio.load when its codec backend exists (the reference's
+    call, enhance.py:183), else WAV through scipy (this image has no torchcodec)."""
+    try:
+        import torchaudio
+
+        audio, fs = torchaudio.load(str(path))
+        return audio.float(), int(fs)
+    except (ImportError, RuntimeError, OSError):
+        pass
+    from scipy.io import wavfile
+
+    if Path(path).suffix.lower() != ".wav":
+        raise RuntimeError(f"{path}: no decoder for this format here (torchaudio's codec backend is missing); WAV works")
+    fs, data = wavfile.read(str(path))
+    if data.dtype == np.int16:
+        x = data.astype(np.float32) / 32768.0
+    elif data.dtype == np.int32:
+        x = data.astype(np.float32) / 2147483648.0
+    elif data.dtype == np.uint8:
+        x = (data.astype(np.float32) - 128.0) / 128.0
+    else:
+        x = data.astype(np.float32)
+    x = x[:, None] if x.ndim == 1 else x
+    return torch.from_numpy(np.ascontiguousarray(x.T)), int(fs)
+
+
+def save_audio(path, audio, fs):
+    """audio: float tensor [channels, samples] (reference: torchaudio.save, enhance.py:192)."""
+    try:
+        import torchaudio
+
+        torchaudio.save(str(path), audio, fs)
+        return
+    except (ImportError, RuntimeError, OSError):
+        pass
+    from scipy.io import wavfile
+
+    wavfile.write(str(path), fs, np.ascontiguousarray(audio.numpy().T.astype(np.float32)))
+
+
+def resample(audio, fs, target_fs):
+    """reference enhance.py:77-80"""
+    if fs != target_fs:
+        import torchaudio
+
+        audio = torchaudio.functional.resample(audio, fs, target_fs)
+    return audio
+
+
+def output_path_for(path, rel_path, dir_proc, output):
+    """reference enhance.py:173-181"""
+    output = Path(output)
+    if dir_proc:
+        return output / Path(path).relative_to(rel_path)
+    return output / Path(path).name if output.is_dir() else output
+
+
+def enhance_files(model, files, out_paths, enhance_kwargs, batch_size=64, device=None, rank=0, world=1, progress=False):
+    """Enhances this rank's share of `files` into `out_paths`.  Returns a dict of counters.
+    Files are dealt to ranks whole (largest first, round robin: balanced without any exchange); every channel of a
+    file is one utterance; utterances of identical (resampled) length share a batch."""
+    device = device if device is not None else next(model.parameters()).device
+    t0 = time.perf_counter()
+    order = sorted(range(len(files)), key=lambda i: (-os.path.getsize(files[i]), str(files[i])))
+    mine = [fi for k, fi in enumerate(order) if k % world == rank]
+    utts = []        # (file index, channel, tensor [T] on the device at the model rate)
+    fs_of = {}
+    for fi in mine:
+        audio, fs = load_audio(files[fi])
+        fs_of[fi] = fs
+        a = resample(audio.to(device), fs, model.fs)
+        for c in range(a.shape[0]):
+            utts.append((fi, c, a[c]))
+    batches = sharding.length_buckets([u[2].shape[-1] for u in utts], list(range(len(utts))), batch_size)
+    done = {}
+    n_audio_s = 0.0
+    it = batches
+    if progress:
+        from tqdm import tqdm
+
+        it = tqdm(it)
+    with torch.no_grad():
+        for batch in it:
+            x = torch.stack([utts[i][2] for i in batch])
+            y = model.enhance(x, **enhance_kwargs)
+            for i, yi in zip(batch, y):
+                done[i] = yi
+            n_audio_s += x.numel() / model.fs
+    by_file = {}
+    for i, (fi, c, _) in enumerate(utts):
+        by_file.setdefault(fi, []).append(i)
+    for fi, idx in by_file.items():
+        fs = fs_of[fi]
+        enh = resample(torch.stack([done[i] for i in idx]), model.fs, fs)
+        Path(out_paths[fi]).parent.mkdir(exist_ok=True, parents=True)
+        save_audio(out_paths[fi], enh.cpu(), fs)
+    return dict(files=len(by_file), utterances=len(done), batches=len(batches), audio_seconds=n_audio_s,
+                seconds=time.perf_counter() - t0)
+
+
+def main(argv=None):
+    if argv is not None:
+        sys.argv = [sys.argv[0]] + list(argv)
+    parser = argparse.ArgumentParser(description="Enhance a file or a directory of audio files")
+    parser.add_argument("input", type=Path, help="Path to an audio file or a folder of audio files")
+    parser.add_argument("output", type=Path,
+                        help="Output path for the enhanced files. In the case of a folder, the orignal structure is retained.")
+    parser.add_argument("--model", type=str, default="line-corporation/open-universe:plusplus",
+                        help="A checkpoint path or a model stored in the model zoo")
+    parser.add_argument("--hf-token", type=str, help="Huggingface access token")
+    parser.add_argument("--model-strict", action="store_true", help="Use strict policy to load the model.")
+    parser.add_argument("--seed", type=int, default=1028282, help="Set a deterministic seed to get reproducible results")
+    parser.add_argument("--device", type=str, default="cuda:0", help="cuda:X (there is no CPU path in this implementation)")
+    parser.add_argument("--batch-size", type=int, default=64, help="Utterances of equal length enhanced together")
+    requires_help = handle_help()
+    args, _ = parser.parse_known_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    device = args.device
+    if world > 1:
+        device = f"cuda:{int(os.environ.get('LOCAL_RANK', '0'))}"
+    if not device.startswith("cuda"):
+        raise ValueError(f"open_universe_b200 runs on a CUDA sm_100 device only; provided {device}")
+    if not torch.cuda.is_available():
+        raise RuntimeError("no CUDA device: open_universe_b200 has no CPU fallback")
+
+    model = inference_utils.load_model(args.model, device=device, strict=args.model_strict, hf_token=args.hf_token)
+    rng = torch.Generator(device=device)
+    rng.manual_seed(args.seed + rank)
+    inference_utils.add_enhance_arguments(model, parser)
+    if requires_help:
+        sys.argv.append("--help")
+    args = parser.parse_args()
+    enhance_kwargs = {}
+    for group in parser._action_groups:
+        if group.title == "enhance":
+            enhance_kwargs = {a.dest: getattr(args, a.dest, None) for a in group._group_actions}
+    enhance_kwargs["rng"] = rng
+
+    files, rel_path, dir_proc = find_files(args.input)
+    outs = [output_path_for(p, rel_path, dir_proc, args.output) for p in files]
+    stats = enhance_files(model, files, outs, enhance_kwargs, batch_size=args.batch_size, device=device, rank=rank,
+                          world=world, progress=dir_proc and rank == 0)
+    print(f"[rank {rank}] {stats['files']} files, {stats['utterances']} utterances in {stats['batches']} batches, "
+          f"{stats['audio_seconds']:.1f} s of audio in {stats['seconds']:.2f} s "
+          f"({stats['audio_seconds'] / max(stats['seconds'], 1e-9):.1f} audio-s/s incl. file IO and plan creation)")
+    return stats
+
+
+if __name__ == "__main__":
+    main()

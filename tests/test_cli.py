@@ -1,0 +1,143 @@
+"""The file pipeline around enhance() (open_universe_b200/bin/enhance.py; reference open_universe/bin/enhance.py):
+file discovery, output layout, WAV IO, equal-length batching, per-rank dealing on the CPU with a stand-in model;
+end to end on the GPU against direct model.enhance calls with the same generator."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+import yaml
+from scipy.io import wavfile
+
+from conftest import build_model
+from open_universe_b200 import sharding
+from open_universe_b200.bin import enhance as cli
+
+
+def _write_wavs(root, specs):
+    """specs: list of (relative path, fs, channels, samples, dtype)"""
+    g = np.random.default_rng(0)
+    paths = []
+    for rel, fs, ch, n, dt in specs:
+        p = root / rel
+        p.parent.mkdir(parents=True, exist_ok=True)
+        x = 0.1 * g.standard_normal((n, ch)).astype(np.float32)
+        if dt == "int16":
+            x = np.round(x * 32767).astype(np.int16)
+        wavfile.write(str(p), fs, x[:, 0] if ch == 1 else x)
+        paths.append(p)
+    return paths
+
+
+class _HalfModel(torch.nn.Module):
+    """Stand-in with the attributes the pipeline reads: halves the signal, records the batches it saw."""
+
+    fs = 16000
+
+    def __init__(self):
+        super().__init__()
+        self.w = torch.nn.Parameter(torch.zeros(1))
+        self.batches = []
+
+    def enhance(self, mix, **kw):
+        self.batches.append(tuple(mix.shape))
+        return 0.5 * mix
+
+
+SPECS = [("a.wav", 16000, 1, 4000, "float32"), ("sub/b.wav", 16000, 1, 4000, "int16"), ("sub/c.wav", 16000, 2, 4000, "float32"),
+         ("sub/deep/d.wav", 8000, 1, 3000, "float32"), ("e.wav", 16000, 1, 5000, "float32"), ("notes.txt", 0, 0, 0, "")]
+
+
+def _make_tree(tmp_path):
+    src = tmp_path / "noisy"
+    _write_wavs(src, [s for s in SPECS if s[0].endswith(".wav")])
+    (src / "notes.txt").write_text("not audio")
+    return src
+
+
+def test_find_files_and_output_layout(tmp_path):
+    src = _make_tree(tmp_path)
+    files, rel, is_dir = cli.find_files(src)
+    assert is_dir and rel == src
+    assert sorted(str(p.relative_to(src)) for p in files) == ["a.wav", "e.wav", "sub/b.wav", "sub/c.wav", "sub/deep/d.wav"]
+    out = tmp_path / "enh"
+    assert cli.output_path_for(src / "sub" / "b.wav", rel, True, out) == out / "sub" / "b.wav"   # structure retained
+    f1, rel1, d1 = cli.find_files(src / "a.wav")
+    assert f1 == [src / "a.wav"] and not d1
+    assert cli.output_path_for(f1[0], rel1, False, tmp_path / "x.wav") == tmp_path / "x.wav"
+    (tmp_path / "outdir").mkdir()
+    assert cli.output_path_for(f1[0], rel1, False, tmp_path / "outdir") == tmp_path / "outdir" / "a.wav"
+
+
+def test_wav_io_roundtrip(tmp_path):
+    (p16, pf) = _write_wavs(tmp_path, [("i16.wav", 16000, 2, 100, "int16"), ("f32.wav", 24000, 1, 77, "float32")])
+    a, fs = cli.load_audio(p16)
+    assert a.shape == (2, 100) and fs == 16000 and a.dtype == torch.float32 and a.abs().max() <= 1.0
+    b, fs = cli.load_audio(pf)
+    assert b.shape == (1, 77) and fs == 24000
+    cli.save_audio(tmp_path / "o.wav", b, fs)
+    c, fs2 = cli.load_audio(tmp_path / "o.wav")
+    assert fs2 == fs and torch.equal(b, c)
+
+
+@pytest.mark.parametrize("world", [1, 2])
+def test_enhance_files_batches_equal_lengths_and_deals_whole_files(tmp_path, world):
+    src = _make_tree(tmp_path)
+    files, rel, is_dir = cli.find_files(src)
+    out = tmp_path / "enh"
+    outs = [cli.output_path_for(p, rel, is_dir, out) for p in files]
+    seen, n_files = [], 0
+    for rank in range(world):
+        model = _HalfModel()
+        st = cli.enhance_files(model, files, outs, {}, batch_size=3, device="cpu", rank=rank, world=world)
+        n_files += st["files"]
+        seen += model.batches
+        for B, T in model.batches:
+            assert B <= 3
+    assert n_files == 5
+    # 16 kHz: four utterances of 4000 samples (a, b, both channels of c), one of 5000; the 8 kHz file becomes 6000
+    assert sorted(T for B, T in seen for _ in range(B)) == [4000, 4000, 4000, 4000, 5000, 6000]
+    for p, o in zip(files, outs):
+        x, fs = cli.load_audio(p)
+        y, fs_o = cli.load_audio(o)
+        assert fs_o == fs and y.shape == x.shape                       # original rate and channel count restored
+        if fs == 16000:
+            assert torch.allclose(y, 0.5 * x, atol=1e-6)
+
+
+def test_length_buckets_never_mix_lengths():
+    lengths = [5, 7, 5, 5, 7, 9, 5]
+    batches = sharding.length_buckets(lengths, list(range(7)), 2)
+    assert sorted(i for b in batches for i in b) == list(range(7))
+    for b in batches:
+        assert len(b) <= 2 and len({lengths[i] for i in b}) == 1
+
+
+@pytest.mark.gpu
+def test_cli_end_to_end_equals_direct_enhance_calls(tmp_path):
+    """python -m open_universe_b200.bin.enhance on a small tree == model.enhance on the same equal-length batches,
+    in the same order, with the same generator (the native path itself is parity-tested in test_gpu_parity.py)."""
+    model, cfg = build_model("universepp_16k")
+    d = tmp_path / "exp" / "checkpoints"
+    d.mkdir(parents=True)
+    torch.save({"state_dict": {k: v.clone() for k, v in model.state_dict().items()}}, d / "last.ckpt")
+    (tmp_path / "exp" / ".hydra").mkdir()
+    with open(tmp_path / "exp" / ".hydra" / "config.yaml", "w") as f:
+        yaml.safe_dump(json.loads(json.dumps(cfg)), f)
+    src = tmp_path / "noisy"
+    specs = [("a.wav", 16000, 1, 3000, "float32"), ("s/b.wav", 16000, 1, 3000, "float32"), ("s/c.wav", 16000, 1, 2000, "float32")]
+    _write_wavs(src, specs)
+    out = tmp_path / "enh"
+    st = cli.main([str(src), str(out), "--model", str(d / "last.ckpt"), "--seed", "5", "--n_steps", "4", "--batch-size", "8"])
+    assert st["files"] == 3 and st["batches"] == 2
+    gm = model.to("cuda").eval()
+    rng = torch.Generator(device="cuda").manual_seed(5)
+    files = {rel: cli.load_audio(src / rel)[0].cuda() for rel, *_ in specs}
+    # batches in ascending length; inside a batch: files largest first, then by path (the dealing order)
+    ref_c = gm.enhance(files["s/c.wav"], n_steps=4, rng=rng)
+    ref_ab = gm.enhance(torch.cat([files["a.wav"], files["s/b.wav"]]), n_steps=4, rng=rng)
+    got = {rel: cli.load_audio(out / rel)[0] for rel, *_ in specs}
+    assert torch.allclose(got["s/c.wav"], ref_c.cpu(), atol=1e-6)
+    assert torch.allclose(got["a.wav"], ref_ab[0:1].cpu(), atol=1e-6)
+    assert torch.allclose(got["s/b.wav"], ref_ab[1:2].cpu(), atol=1e-6)
