@@ -210,8 +210,8 @@ class Universe(torch.nn.Module):
             raise ValueError("The input should have at most 3 dimensions")
         if mix.shape[1] != 1:
             raise ValueError("open_universe_b200 supports single-channel conditioners (input_channels == 1)")
-        if ensemble_stat not in ("mean", "median", "signal_median"):
-            raise NotImplementedError()
+        if ensemble is not None and ensemble_stat not in ("mean", "median", "signal_median"):
+            raise NotImplementedError()   # reference universe.py:359-367: only looked at when an ensemble is asked for
         aux = bool(use_aux_signal) or warm_start is not None
         if warm_start is not None and not 0 <= int(warm_start) < n_steps:
             raise ValueError("warm_start must be a step index in [0, n_steps)")
