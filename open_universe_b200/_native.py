@@ -10,7 +10,7 @@ import subprocess
 from . import _abi
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libuniverse_b200.so")
+LIB_PATH = os.environ.get("UV_LIB") or os.path.join(_HERE, "libuniverse_b200.so")   # UV_LIB: A/B runs of two builds
 CSRC = os.path.join(_HERE, "csrc")
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17"]

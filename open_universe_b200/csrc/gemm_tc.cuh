@@ -49,7 +49,10 @@ constexpr int kTileM = 256;         // rows per CTA tile (two UMMA sub-tiles)
 constexpr int kMaxAStages = 12;
 constexpr int kMaxBStages = 8;
 constexpr int kEpiWarps = 8;        // 4 TMEM lane quarters x 2 sub-tiles (16 = two column halves each: measured slower, the multi-output paths spill at 112 registers)
-constexpr int kXfWarps = 2;         // A-operand transform warps (PReLU of a raw tensor in shared memory)
+#ifndef UV_XF_WARPS
+#define UV_XF_WARPS 2   // 4 removes the transform cost at level 1 (k5: 104 vs 125 us) but costs 128 registers + spills everywhere else: 45.3 vs 45.2 ms per pass
+#endif
+constexpr int kXfWarps = UV_XF_WARPS;         // A-operand transform warps (PReLU of a raw tensor in shared memory)
 constexpr int kGemmThreads = 64 + 32 * kEpiWarps + 32 * kXfWarps;   // producer warp, MMA warp, epilogue warps, transform warps
 constexpr int kMaxAcc = 4;          // TMEM accumulator stages
 constexpr int kSchedSlots = 32;     // ring of claimed tile indices (producer -> MMA issuer + epilogue warps)
