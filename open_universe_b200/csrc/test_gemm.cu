@@ -304,16 +304,22 @@ static void run_perf(int num_sms, bool phases = false) {
       {"L4 C512 k5", 64, 401, 512, 5, 0, 1}, {"L4 C512 k3", 64, 401, 512, 3, 0, 1},
       // raw A tensor + in-kernel PReLU ("xf"): against the same layer above
       {"L0 C32 k5 xf", 64, 64160, 32, 5, 0, 1}, {"L1 C64 k5 xf", 64, 32080, 64, 5, 0, 1}, {"L2 C128 k5 xf", 64, 8020, 128, 5, 0, 1},
-      {"L3 C256 k5 xf", 64, 2005, 256, 5, 0, 1}, {"L4 C512 k5 xf", 64, 401, 512, 5, 0, 1}};
+      {"L3 C256 k5 xf", 64, 2005, 256, 5, 0, 1}, {"L4 C512 k5 xf", 64, 401, 512, 5, 0, 1},
+      // the same level-0 / level-1 layers on tensors stored phase-split by 2 ("space to depth": 2 sources x 3 shifts,
+      // N = 2 C columns): what a k5 / k3 "same" conv would cost in that formulation (dense weight images)
+      {"L0 C32 s2d", 64, 64160, 32, 3, 0, 1}, {"L0 C32 s2d xf", 64, 64160, 32, 3, 0, 1}, {"L0 C32 s2d +add", 64, 64160, 32, 3, 1, 1},
+      {"L1 C64 s2d", 64, 32080, 64, 3, 0, 1}, {"L1 C64 s2d xf", 64, 32080, 64, 3, 0, 1}};
   unsigned long long* d_clk = nullptr;
   if (phases) CK(cudaMalloc(&d_clk, (size_t)num_sms * 8 * 8));
   for (auto& pc : pcs) {
-    HT A = make_tensor(pc.B, pc.Lv, pc.C, 1, 2, false);
+    const bool s2d = strstr(pc.name, "s2d") != nullptr;
+    const int sp = s2d ? 2 : 1;
+    HT A = make_tensor(pc.B, pc.Lv, pc.C, sp, 2, false);
     CK(cudaMemset(A.dev, 0x3c, A.data.size()));  // small finite bf16 values everywhere
-    HT O = make_tensor(pc.B, pc.Lv, pc.C, 1, 2, false);
+    HT O = make_tensor(pc.B, pc.Lv, pc.C, sp, 2, false);
     HT O2 = make_tensor(pc.B, pc.Lv, pc.C, 1, 2, false);
-    const int KC = pc.C < 64 ? pc.C : 64, NT = pc.C < 128 ? pc.C : 128;
-    size_t wbytes = (size_t)pc.C * pc.C * pc.k * 2 + (size_t)pc.C * 32;
+    const int KC = pc.C < 64 ? pc.C : 64, NT = s2d ? 2 * pc.C : (pc.C < 128 ? pc.C : 128);
+    size_t wbytes = (size_t)pc.C * pc.C * pc.k * 2 * sp * sp + (size_t)pc.C * 32 * sp;
     char* d_w;
     CK(cudaMalloc(&d_w, wbytes));
     CK(cudaMemset(d_w, 0x3c, wbytes));
@@ -322,12 +328,13 @@ static void run_perf(int num_sms, bool phases = false) {
     p.a_base = A.dev; p.a_nchunks = pc.C / 8; p.a_P = A.P; p.a_G = A.G; p.n_src = 1;
     p.smin = -(pc.k / 2); p.smax = pc.k / 2; p.KC = KC; p.n_groups = pc.C / KC;
     p.w = d_w; p.N_TILE = NT; p.n_tiles_n = pc.C / NT;
-    p.m_rows = pc.B * A.Lh; p.Lh_A = A.Lh; p.M_valid = pc.Lv; p.up = 1; p.C_out = pc.C;
+    p.m_rows = pc.B * A.Lh; p.Lh_A = A.Lh; p.M_valid = pc.Lv / sp; p.up = sp; p.C_out = pc.C;
+    if (s2d) { p.n_src = 2; p.smin = -1; p.smax = 1; p.n_tiles_n = 1; }
     p.has_bias = 1; p.scale = 1.f; p.n_out = pc.nout;
     p.out[0].t = desc_of(O); p.out[1].t = desc_of(O2); p.out[1].act = 1; p.out[1].a1 = 0.25f;
     HT O3 = make_tensor(pc.B, pc.Lv, pc.C, 1, 2, false);
     p.out[2].t = desc_of(O3); p.out[2].act = 1; p.out[2].a1 = 0.5f;
-    HT AD = make_tensor(pc.B, pc.Lv, pc.C, 1, 2, false);
+    HT AD = make_tensor(pc.B, pc.Lv, pc.C, sp, 2, false);
     if (pc.add) p.add1 = desc_of(AD);
     if (strstr(pc.name, " xf")) { p.a_act = 1; p.a_slope = 0.25f; }
     int* d_err; CK(cudaMalloc(&d_err, 4)); CK(cudaMemset(d_err, 0, 4));
