@@ -447,8 +447,9 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
       for (int i = 0; i < 16; ++i) v[i] *= scale;
     }
     if (FILM) {
-      const float4* ga = reinterpret_cast<const float4*>(film_s + co0 + 16 * g16);
-      const float4* be = reinterpret_cast<const float4*>(film_s + P.C_out + co0 + 16 * g16);
+      const int gc = g16 >= gpp ? g16 - (g16 / gpp) * gpp : g16;   // column group within its phase (multi-phase tiles)
+      const float4* ga = reinterpret_cast<const float4*>(film_s + co0 + 16 * gc);
+      const float4* be = reinterpret_cast<const float4*>(film_s + P.C_out + co0 + 16 * gc);
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const float4 gq = ga[i], bq = be[i];
@@ -963,7 +964,7 @@ inline bool gemm_plan_pipeline(GemmParams& p) {
   }
   if (p.N_TILE > p.C_out) {
     // tile spanning several phases of a transposed conv: whole phases only, adds through the tensor core only
-    if (p.up <= 1 || p.N_TILE % p.C_out || p.C_out % 16 || p.film || p.rm_out || p.add2.base || (p.add1.base && !p.add_kc)) return false;
+    if (p.up <= 1 || p.N_TILE % p.C_out || p.C_out % 16 || p.rm_out || p.add2.base || (p.add1.base && !p.add_kc)) return false;
   }
   p.n_tiles_m = (p.m_rows + kTileM - 1) / kTileM;
   const int stride = (int)accum_stride_cols(p.N_TILE);

@@ -289,14 +289,26 @@ __global__ void __launch_bounds__(256) conv_out_kernel(TensDesc a, int B, int Lp
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (long long)B * Lp) return;
   const int b = (int)(idx / Lp), l = (int)(idx - (long long)b * Lp);
-  // rows l-1, l, l+1 of the plain planes tensor; rows -1 and Lp are the zero gap
-  const RowAddr r = row_addr(a, b, l);
+  // rows l-1, l, l+1 of the planes tensor (plain: neighbouring rows, rows -1 and Lp are the zero gap; phase-split:
+  // the neighbours live in other phase planes, samples outside [0, Lp) are skipped)
+  RowAddr rt[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const int lk = l + k - 1;
+    if (a.split > 1) {
+      rt[k] = row_addr(a, b, lk < 0 ? 0 : lk);
+      if (lk < 0 || lk >= Lp) rt[k].p = nullptr;
+    } else {
+      rt[k] = row_addr(a, b, l);
+      rt[k].p += (long long)(k - 1) * 16;
+    }
+  }
   float acc = bias[0];
   for (int ch = 0; ch < (C >> 3); ++ch) {
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
-      RowAddr rk = r;
-      rk.p += (long long)(k - 1) * 16;
+      const RowAddr rk = rt[k];
+      if (rk.p == nullptr) continue;
       float v[8];
       load8(rk, 1, ch, v);
       const float4 w0 = *reinterpret_cast<const float4*>(ws + k * C + ch * 8);

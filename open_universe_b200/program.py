@@ -322,32 +322,41 @@ def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_
     pg.emit(op, "c.mel_fin")
 
     def conv_block(pfx, name, lev, C, h_raw, h_act, v_outs, step=-1, film=-1, cond=None, cond_out=None,
-                   v_add2=None, v_scale=SQRT1_2, only_conv1=False):
+                   v_add2=None, v_scale=SQRT1_2, only_conv1=False, s2d=False):
         """conv1 -> [+cond]/sqrt2 -> [FiLM] -> conv2 -> conv3 -> (h + c)/sqrt2  (blocks.py:387-403).
         h_act = PReLU_conv1(h), h_raw = h (h_act = None: only h exists, conv1 activates it in the kernel).
         v_outs: outputs of the residual sum."""
-        c1 = pg.tens(f"{pfx}tmp.c1.{lev.L}.{C}", lev, C)
-        c2 = pg.tens(f"{pfx}tmp.c2.{lev.L}.{C}", lev, C)
+        sfx = ""
+        if s2d:
+            # every tensor of this block is stored phase-split by 2 in the next level's row space; the convs are the
+            # ".s2d" packings (2 sources x 3 shifts, both output phases of a row in one tile; weights.w4_same_s2d)
+            assert h_act is None and cond_out is None and not only_conv1 and v_add2 is None
+            sfx = ".s2d"
+            c1 = pg.tens(f"{pfx}tmp.c1.s2d.{C}", lev, C, split=2)
+            c2 = pg.tens(f"{pfx}tmp.c2.s2d.{C}", lev, C, split=2)
+        else:
+            c1 = pg.tens(f"{pfx}tmp.c1.{lev.L}.{C}", lev, C)
+            c2 = pg.tens(f"{pfx}tmp.c2.{lev.L}.{C}", lev, C)
         s2, s3 = L[name + ".conv2"]["slope"], L[name + ".conv3"]["slope"]
         outs = [] if only_conv1 else [_act(c1, s2)]
         if cond_out is not None:
             outs.append(_raw(cond_out))
         lys = [L[name + f".conv{k}"] for k in (1, 2, 3)]
         fuse = (
-            FUSE_CONVBLOCKS and h_act is not None and not only_conv1 and v_add2 is None and C % 16 == 0 and C <= 64
+            FUSE_CONVBLOCKS and not s2d and h_act is not None and not only_conv1 and v_add2 is None and C % 16 == 0 and C <= 64
             and all(ly["KC"] == C and ly["N_TILE"] == C and ly["N_total"] == C and ly["up"] == 1 and ly["n_src"] == 1 for ly in lys)
             and (lys[0]["smin"], lys[0]["smax"]) == (-2, 2) and all((ly["smin"], ly["smax"]) == (-1, 1) for ly in lys[1:])
             and len(v_outs) <= (2 if cond_out is not None else 3)
             and h_raw.split == 1 and h_raw.dtype == DT_BF16 and (cond is None or (cond.split == 1 and cond.dtype == DT_BF16))
         )
         sink = _PartSink(pg) if fuse else pg
-        g1 = sink.gemm(name + ".conv1", name + ".conv1", h_act if h_act is not None else h_raw, lev, lev.L, outs, step, add1=cond,
+        g1 = sink.gemm(name + ".conv1", name + ".conv1" + sfx, h_act if h_act is not None else h_raw, lev, lev.L, outs, step, add1=cond,
                        scale=SQRT1_2 if cond is not None else 1.0, film=film,
                        a_slope=None if h_act is not None else L[name + ".conv1"]["slope"])
         if only_conv1:
             return
-        g2 = sink.gemm(name + ".conv2", name + ".conv2", c1, lev, lev.L, [_act(c2, s3)], step)
-        g3 = sink.gemm(name + ".conv3", name + ".conv3", c2, lev, lev.L, v_outs, step, add1=h_raw, add2=v_add2, scale=v_scale)
+        g2 = sink.gemm(name + ".conv2", name + ".conv2" + sfx, c1, lev, lev.L, [_act(c2, s3)], step)
+        g3 = sink.gemm(name + ".conv3", name + ".conv3" + sfx, c2, lev, lev.L, v_outs, step, add1=h_raw, add2=v_add2, scale=v_scale)
         if not fuse:
             return
         # one launch for the whole block (csrc/convblock.cuh); the three GEMM records stay attached for the
@@ -403,6 +412,9 @@ def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_
 
     # input conv (condition.py:360) and encoder (condition.py:189-206)
     raw0 = raw_ok(chans[0])
+    # finest level of the score network phase-split by 2 ("space to depth", weights.w4_same_s2d); UV_S2D=0 disables
+    s2d0 = bool(meta.get("s2d0")) and raw0 and not FUSE_CONVBLOCKS and os.environ.get("UV_S2D", "1") != "0"
+    pg.s2d0 = s2d0
     h_raw, h_act = pg.tens("c.h0", lv[0], chans[0]), None if raw0 else pg.tens("c.h0a", lv[0], chans[0])
     op = new_op(_abi.OP_CONV_IN)
     op.B, op.Lp, op.C, op.p0, op.p3, op.p4, op.f0 = B, Lp, chans[0], pg.sig, L["c.in"]["w_w"], L["c.in"]["bias_w"], 1.0
@@ -506,7 +518,7 @@ def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_
         if r is not None:
             lev_i -= 1
         lev, C = lv[lev_i], chans[lev_i]
-        sc = pg.tens(f"sc{i}", lev, C)
+        sc = pg.tens(f"sc{i}", lv[1], C, split=2) if (s2d0 and lev_i == 0) else pg.tens(f"sc{i}", lev, C)
         pg.gemm(f"s.dec{i}.sc", f"s.dec{i}.sc", conds[i], lev, lev.L, [_raw(sc)])
         scs.append(sc)
 
@@ -521,7 +533,10 @@ def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_
     n_blocks = meta["n_blocks"]
     for n in range(n_steps):
         fbase = pg.film + n * R * 4
-        h_raw, h_act = pg.tens("s.h0", lv[0], chans[0]), None if raw0 else pg.tens("s.h0a", lv[0], chans[0])
+        if s2d0:
+            h_raw, h_act = pg.tens("s.h0", lv[1], chans[0], split=2), None
+        else:
+            h_raw, h_act = pg.tens("s.h0", lv[0], chans[0]), None if raw0 else pg.tens("s.h0a", lv[0], chans[0])
         pg.step_first_op.append(len(pg.ops))
         op = new_op(_abi.OP_CONV_IN, n)
         op.B, op.Lp, op.C, op.p0, op.p3, op.p4 = B, Lp, chans[0], pg.x, L["s.in"]["w_w"], L["s.in"]["bias_w"]
@@ -549,7 +564,10 @@ def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_
                 else:
                     vds = pg.tens(f"s.enc{i}.vds", lv[i + 1], C, split=rates[i])
                     outs.append(_act(vds, L[f"s.enc{i}.rc"]["slope"]))
-            conv_block("s.", f"s.enc{i}", lev, C, h_raw, h_act, outs, step=n, film=fbase + frows[f"enc{i}"] * 4)
+            if s2d0 and i == 0:
+                conv_block("s.", f"s.enc{i}", lv[1], C, h_raw, None, outs, step=n, film=fbase + frows[f"enc{i}"] * 4, s2d=True)
+            else:
+                conv_block("s.", f"s.enc{i}", lev, C, h_raw, h_act, outs, step=n, film=fbase + frows[f"enc{i}"] * 4)
             if i < nlev:
                 h_raw = pg.tens(f"s.h{i+1}", lv[i + 1], chans[i + 1])
                 outs = [_raw(h_raw)]
@@ -577,16 +595,21 @@ def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_
             if r is not None:
                 lev_i -= 1
                 lev, C = lv[lev_i], chans[lev_i]
-                u_raw, u_act = pg.tens(f"{name}.u", lev, C), None if raw_ok(C) else pg.tens(f"{name}.ua", lev, C)
+                if s2d0 and lev_i == 0:
+                    u_raw, u_act = pg.tens(f"{name}.u", lv[1], C, split=2), None   # the up conv writes both phases of a row
+                else:
+                    u_raw, u_act = pg.tens(f"{name}.u", lev, C), None if raw_ok(C) else pg.tens(f"{name}.ua", lev, C)
                 pg.gemm(name + ".rc", name + ".rc", y_act, lv[lev_i + 1], lv[lev_i + 1].L,
                         [_raw(u_raw)] + ([] if raw_ok(C) else [_act(u_act, L[name + ".conv1"]["slope"])]), n, add1=res, scale=SQRT1_2)
             lev, C = lv[lev_i], chans[lev_i]
-            v_act = pg.tens(f"{name}.va", lev, C)
+            blk_s2d = s2d0 and lev_i == 0
+            v_act = pg.tens(f"{name}.va", lv[1], C, split=2) if blk_s2d else pg.tens(f"{name}.va", lev, C)
             if i < n_dec - 1:
                 vo = _act(v_act, L[f"s.dec{i+1}.rc"]["slope"])
             else:
                 vo = (v_act, 2, L["s.out"]["slope_a"], L["s.out"]["slope_b"])  # score.py:290 (two PReLUs)
-            conv_block("s.", name, lev, C, u_raw, u_act, [vo], step=n, film=fbase + frows[f"dec{i}"] * 4, cond=scs[i])
+            conv_block("s.", name, lv[1] if blk_s2d else lev, C, u_raw, u_act, [vo], step=n, film=fbase + frows[f"dec{i}"] * 4,
+                       cond=scs[i], s2d=blk_s2d)
             y_act = v_act
         op = new_op(_abi.OP_CONV_OUT, n)
         op.a = y_act

@@ -103,6 +103,28 @@ def w4_plain(w):
     return w.permute(0, 2, 1)[:, None].contiguous(), -(w.shape[2] // 2)
 
 
+S2D = os.environ.get("UV_S2D", "1") != "0"
+
+
+def w4_same_s2d(w):
+    """'same' conv [Co, Ci, k <= 5] on tensors stored phase-split by 2 ("space to depth"): row m of phase plane ph is
+    sample 2m + ph.  Output column n = ph Co + co (the two output phases of a row), source s = input phase plane,
+    shift q in {-1, 0, 1}: input sample 2(m + q) + s, i.e. tap t = 2q + s - ph of the original kernel (zero where
+    |t| exceeds the kernel).  -> W4 [2 Co, 2, 3, Ci], smin = -1.  A k5 conv is then 2 sources x 3 shifts = 6 K blocks
+    for 2 output samples instead of 5 per sample, and the tensor core re-reads each A slab 3 times, not 5."""
+    co, ci, k = w.shape
+    pad = k // 2
+    assert k % 2 == 1 and k <= 5
+    w4 = torch.zeros(2 * co, 2, 3, ci)
+    for ph in range(2):
+        for s_ in range(2):
+            for qi, q in enumerate((-1, 0, 1)):
+                t = 2 * q + s_ - ph
+                if abs(t) <= pad:
+                    w4[ph * co : (ph + 1) * co, s_, qi, :] = w[:, :, t + pad]
+    return w4, -1
+
+
 def w4_down(w, lp=None):
     """Strided conv (k = stride = r), optionally preceded by the 'same' low-pass lp
     (2r+1 taps): y[m] = sum_tau W'[tau] v[r m + tau - r], W' = W (*) lp (3r taps).
@@ -220,14 +242,20 @@ class PackedModel:
             C_out=c_out, C_in=ci, up=up, slope=slope,
         )
 
-    def add_conv_block(self, sd, prefix, name, rate=None, direction="none"):
-        """ConvBlock parameters (blocks.py:240-329)."""
+    def add_conv_block(self, sd, prefix, name, rate=None, direction="none", s2d=False):
+        """ConvBlock parameters (blocks.py:240-329).  s2d: also pack the three convs for phase-split-by-2 tensors
+        (layers `<name>.convN.s2d`; the program builder picks them for the score network's finest level)."""
         for cn in ("conv1", "conv2", "conv3"):
             p = f"{prefix}.{cn}"
-            w4, smin = w4_plain(eff_weight(sd, p + ".conv"))
+            w = eff_weight(sd, p + ".conv")
+            w4, smin = w4_plain(w)
             resid = cn == "conv3" or (cn == "conv1" and name.startswith("s.dec"))
             self.add_gemm(f"{name}.{cn}", w4, smin, w4.shape[0], bias=sd[p + ".conv.bias"],
                           slope=float(sd[p + ".prelu.weight"]), resid=resid)
+            if s2d:
+                w4s, smin_s = w4_same_s2d(w)
+                self.add_gemm(f"{name}.{cn}.s2d", w4s, smin_s, w.shape[0], up=2, bias=sd[p + ".conv.bias"],
+                              slope=float(sd[p + ".prelu.weight"]), resid=resid)
         if direction in ("down", "up"):
             p = f"{prefix}.rate_change_conv"
             w = eff_weight(sd, p + ".conv")
@@ -281,6 +309,11 @@ def pack_model(sd, cfg):
     if scfg.get("seq_model", "gru") != "gru" or ccfg.get("seq_model", "gru") != "gru":
         raise NotImplementedError("only seq_model == 'gru' is supported")
 
+    # finest level of the score network stored phase-split by 2 (needs an even first rate factor: that level's block
+    # output doubles as the phase-split input of the first down conv, and 2 C columns must fit one N tile)
+    s2d0 = S2D and rates[0] == 2 and 2 * c0 <= 128 and c0 % 16 == 0
+    pm.meta["s2d0"] = s2d0
+
     # ---------------- score network (score.py:214-298)
     pm.add_conv_in(sd, sp + ".input_conv", "s.in")
     film_w, film_b, film_rows = [], [], {}
@@ -297,12 +330,13 @@ def pack_model(sd, cfg):
     for i in range(n_blocks):
         down = i < nlev
         pm.add_conv_block(sd, f"{sp}.encoder.ds_modules.{i}", f"s.enc{i}", rates[i] if down else None,
-                          "down" if down else "none")
+                          "down" if down else "none", s2d=s2d0 and i == 0)
         add_film(f"{sp}.encoder.cond_proj.{i}", f"enc{i}")
     pm.add_gru(sd, sp + ".encoder.gru", "s.gru", 0)
     up_rates = ([None] if extra else []) + rates[::-1]
     for i, r in enumerate(up_rates):
-        pm.add_conv_block(sd, f"{sp}.decoder.up_modules.{i}", f"s.dec{i}", r, "up" if r else "none")
+        pm.add_conv_block(sd, f"{sp}.decoder.up_modules.{i}", f"s.dec{i}", r, "up" if r else "none",
+                          s2d=s2d0 and i == len(up_rates) - 1)
         add_film(f"{sp}.decoder.noise_cond_proj.{i}", f"dec{i}")
         w4, smin = w4_plain(eff_weight(sd, f"{sp}.decoder.signal_cond_proj.{i}"))
         pm.add_gemm(f"s.dec{i}.sc", w4, smin, w4.shape[0], bias=sd[f"{sp}.decoder.signal_cond_proj.{i}.bias"])
