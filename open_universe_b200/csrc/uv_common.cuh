@@ -140,7 +140,10 @@ __device__ __forceinline__ RowAddr row_addr(const TensDesc& t, int b, int l) {
     return r;
   }
   int ph = 0, ll = l;
-  if (t.split > 1) {
+  if (t.split == 2) {   // the space-to-depth tensors of the finest level: no division
+    ll = l >> 1;
+    ph = l & 1;
+  } else if (t.split > 1) {
     ll = l / t.split;
     ph = l - ll * t.split;
   }
