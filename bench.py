@@ -28,6 +28,7 @@ WORKLOADS = {
     # BASELINE.json configs[1] (the configuration the metric is quoted on)
     "cfg2": dict(model="universepp_16k", B=64, T=64000, n_steps=8, desc="UNIVERSE++ 16 kHz, batch 64 x 4 s clips, 8 steps"),
     "cfg3": dict(model="universe_16k", B=64, T=64000, n_steps=8, desc="UNIVERSE original 16 kHz, batch 64 x 4 s, n_steps 8 (config-faithful)"),
+    "cfg3_n50": dict(model="universe_16k", B=64, T=64000, n_steps=50, desc="UNIVERSE original 16 kHz, batch 64 x 4 s, n_steps 50 (paper-faithful)"),
     "cfg4": dict(model="universepp_24k", B=32, T=240000, n_steps=8, desc="UNIVERSE++ 24 kHz, batch 32 x 10 s clips, 8 steps"),
     "cfg5": dict(model="universepp_16k", B=32, T=480000, n_steps=8, desc="UNIVERSE++ 16 kHz, 30 s clips in batches of 32 (utterance-sharded sweep)"),
 }
@@ -173,12 +174,12 @@ def run_native(args, wl, rank, world, local_rank):
             torch.cuda.synchronize(dev)
 
     def step_resident():
-        return model._enhance_impl(mix_dev, None, None, None, None, None, False, False, None, "median", None,
+        return model._enhance_impl(mix_dev, n_steps, None, None, None, None, False, False, None, "median", None,
                                    noise=noise, return_steps=False)
 
     def step_e2e():
         m = mix_host.to(dev, non_blocking=True)          # H2D from pinned memory
-        out = model.enhance(m, rng=gen)                  # public API (draws the noise with torch.randn)
+        out = model.enhance(m, n_steps=n_steps, rng=gen)   # public API (draws the noise with torch.randn)
         out_host.copy_(out)                              # D2H of the result (blocking)
         return out_host
 
