@@ -139,6 +139,7 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
       g.rm_H = op.rm_out >= 0 ? op.H : 0; g.rm_Bp = op.i1;   // GEMM ops with a row-major output feed the GRU (H, batch pitch)
       g.err_flag = p->err_flag;
       g.a_act = op.a_act; g.a_slope = op.a_slope;
+      g.reverse = op.i3 & 1;   // tile order (L2 reuse with the producer of A)
       g.sched = p->sched + 2 * op_index;
       CUDA_TRY(gemm_launch(g, p->model->num_sms, s));
       break;
@@ -205,7 +206,7 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
       const long long n = (long long)op.B * op.Lp;
       CUDA_TRY(launch_pdl(conv_in_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, s, aptr<const float>(p, op.p0), op.B, op.Lp, op.C, op.f0,
                                                                  wptr<const float>(p, op.p3), wptr<const float>(p, op.p4),
-                                                                 op.n_out, to_out(p, op.out[0]), to_out(p, op.out[1])));
+                                                                 op.n_out, to_out(p, op.out[0]), to_out(p, op.out[1]), op.i3 & 1));
       break;
     }
     case UV_OP_INIT_X: {
@@ -221,7 +222,7 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
       CUDA_TRY(launch_pdl(conv_out_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, s, to_desc(p, op.a), op.B, op.Lp, op.C, wptr<const float>(p, op.p3),
                                                                   wptr<const float>(p, op.p4), aptr<float>(p, op.p0),
                                                                   aptr<const StepCoef>(p, op.p1), op.i0, p->io_dev, op.i1,
-                                                                  op.i2 > 0 ? op.i2 : op.B));
+                                                                  op.i2 > 0 ? op.i2 : op.B, op.i3 & 1));
       break;
     }
     case UV_OP_POST:

@@ -664,13 +664,18 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
       for (;;) {
         const bool live = tile < total_tiles;
         mbar_wait(smem_u32(&s_empty[ss]), sp ^ 1, P.err_flag, 9);
-        s_ring[ss] = live ? tile : -1;
+        // reverse: claim k is tile total-1-k.  A kernel's output (263 MB at the finest levels) exceeds the 126 MB L2, so
+        // what is still cached when the next kernel starts is the END of the tensor; a consumer that starts from the
+        // end reads that part from L2 instead of evicting it on its way there (the builder alternates the direction
+        // along each chain of kernels).
+        const int tile_id = P.reverse ? total_tiles - 1 - tile : tile;
+        s_ring[ss] = live ? tile_id : -1;
         mbar_arrive(smem_u32(&s_full[ss]));
         if (++ss == kSchedSlots) { ss = 0; sp ^= 1; }
         if (!live) break;
         const int tile_nn = tile_nxt < total_tiles ? atomicAdd(P.sched, 1) : tile_nxt;
-        const int n_tile = tile % P.n_tiles_n;
-        const int m_tile = tile / P.n_tiles_n;
+        const int n_tile = tile_id % P.n_tiles_n;
+        const int m_tile = tile_id / P.n_tiles_n;
         const long long row0 = (long long)P.a_G + (long long)m_tile * kTileM + P.smin;
         const char* w_tile = P.w + (long long)n_tile * w_ntile_stride;
         if (!P.b_resident && bias_bytes) {

@@ -228,7 +228,7 @@ __global__ void __launch_bounds__(256) mel_fin_kernel(const float* __restrict__ 
 // condition.py:360), writing the raw tensor and the PReLU-activated copy.
 __global__ void __launch_bounds__(256) conv_in_kernel(const float* __restrict__ x, int B, int Lp, int C, float in_scale,
                                                       const float* __restrict__ w /*[3][C]*/, const float* __restrict__ bias,
-                                                      int n_out, OutDesc o0, OutDesc o1) {
+                                                      int n_out, OutDesc o0, OutDesc o1, int reverse) {
   pdl_launch_dependents();
   // the three taps and the bias of every channel, staged once per block: one 16-byte broadcast load per channel
   // instead of four global loads per channel and thread (the kernel was load-instruction bound)
@@ -236,7 +236,9 @@ __global__ void __launch_bounds__(256) conv_in_kernel(const float* __restrict__ 
   for (int c = threadIdx.x; c < C; c += blockDim.x) ws[c] = make_float4(w[c], w[C + c], w[2 * C + c], bias[c]);
   __syncthreads();
   pdl_wait();
-  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  // reverse: blocks walk the signal from its end (the consumer of these tensors starts where this kernel finished)
+  const long long blk = reverse ? (long long)gridDim.x - 1 - blockIdx.x : blockIdx.x;
+  const long long idx = blk * blockDim.x + threadIdx.x;
   if (idx >= (long long)B * Lp) return;
   const int b = (int)(idx / Lp), l = (int)(idx - (long long)b * Lp);
   const float* xr = x + (size_t)b * Lp;
@@ -280,13 +282,14 @@ __global__ void __launch_bounds__(256) init_x_kernel(const IoTable* io, long lon
 __global__ void __launch_bounds__(256) conv_out_kernel(TensDesc a, int B, int Lp, int C, const float* __restrict__ w /*[3][C]*/,
                                                        const float* __restrict__ bias, float* __restrict__ x,
                                                        const StepCoef* __restrict__ coef, int step, const IoTable* io,
-                                                       int b_off, int B_total) {
+                                                       int b_off, int B_total, int reverse) {
   pdl_launch_dependents();
   __shared__ __align__(16) float ws[3 * kEdgeMaxC];   // [tap][C]: 16-byte broadcast loads instead of one global load per weight
   for (int i = threadIdx.x; i < 3 * C; i += blockDim.x) ws[i] = w[i];
   __syncthreads();
   pdl_wait();
-  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long blk = reverse ? (long long)gridDim.x - 1 - blockIdx.x : blockIdx.x;
+  const long long idx = blk * blockDim.x + threadIdx.x;
   if (idx >= (long long)B * Lp) return;
   const int b = (int)(idx / Lp), l = (int)(idx - (long long)b * Lp);
   // rows l-1, l, l+1 of the planes tensor (plain: neighbouring rows, rows -1 and Lp are the zero gap; phase-split:

@@ -44,6 +44,7 @@ MEL_FT = 32   # frames per CTA of the mel kernel (csrc/small_ops.cuh kMelFT)
 # A tensor that is consumed both raw (residual / skip) and through a PReLU (the next conv) is written ONCE, raw; the
 # consuming GEMM activates it in shared memory (csrc/gemm_tc.cuh, a_act).  UV_RAW_A=0 restores the two-copy scheme.
 RAW_A = os.environ.get("UV_RAW_A", "1") != "0" and os.environ.get("UV_FUSE_CONVBLOCKS", "") != "1"
+ALTERNATE = os.environ.get("UV_ALTERNATE", "1") != "0"   # alternate the tile direction along each chain of kernels
 RAW_A_MAXC = int(os.environ.get("UV_RAW_A_MAXC", "512"))   # channel limit of the scheme (measured on B200: it pays at every level, 46.2 ms per pass against 46.7 with 128 and 48.5 with 32)
 # ... and of its use in front of the encoder's strided down convs (they re-read and re-activate all r phases of A for
 # every N tile, so the transform warps pace the wide levels)
@@ -76,6 +77,7 @@ class Program:
         self.names = []
         self.arena = arena_base
         self.lane = lane
+        self.rev = 0
         self.tensors = {}
         self.B, self.T, self.n_steps = B, T, n_steps
         self.sigmas, self.log10_sigmas, self.in_scales = sigmas, log10_sigmas, in_scales
@@ -101,6 +103,11 @@ class Program:
 
     def emit(self, op, name):
         op.lane = self.lane
+        if ALTERNATE and op.step != -2 and op.type in (_abi.OP_GEMM, _abi.OP_CONV_IN, _abi.OP_CONV_OUT):
+            # the kernels of a chain walk their tensors in alternating directions: a consumer starts at the end its
+            # producer just wrote, which is the part of the tensor the L2 still holds (csrc/gemm_tc.cuh, `reverse`)
+            op.i3 = self.rev
+            self.rev ^= 1
         self.ops.append(op)
         self.names.append(name if self.lane == 0 else f"L{self.lane}.{name}")
         return op
