@@ -61,6 +61,8 @@ constexpr int kOnesBytes = 2 * kSubM * 16;   // [2 chunks][128 rows][8] bf16
 constexpr int kFilmMaxC = 768;
 constexpr int kFilmBytes = 2 * kFilmMaxC * 4;
 constexpr int kGemmSmemBudget = 227 * 1024;
+constexpr int kRmPitch = 20;        // floats per row of the GRU-layout staging buffer (16 + 4: conflict-free 16-byte accesses)
+constexpr int kRmScratchBytes = kEpiWarps * 32 * kRmPitch * 4;
 constexpr int kAddRowsBytes = kTileM * 16;   // one 8-channel chunk of a residual slab (no halo)
 
 // TMEM columns per accumulator (power of two >= 32).
@@ -299,7 +301,7 @@ __device__ __forceinline__ void add_f32(const char* p, long long pstride, float*
 template <bool ADD, bool FILM, bool MULTI, bool LE1>
 __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem_base, uint64_t* t_full, uint64_t* t_empty,
                                               const float* film_s, const int* s_ring, uint64_t* s_full, uint64_t* s_empty,
-                                              int warp, int lane) {
+                                              float* rm_scratch, int warp, int lane) {
   const int sub = ((warp - 2) >> 2) & 1;
   const int chalf = (warp - 2) >> 3;            // with 16 epilogue warps: which half of the column groups
   const int quarter = warp & 3;                 // a warp may only touch TMEM lanes 32*(warp%4)..+31
@@ -362,6 +364,12 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
   const int gpp = P.N_TILE > P.C_out ? (P.C_out >> 4) : 0x7fffffff;   // column groups per phase of a multi-phase tile
   OutPtr op[3], pa1, pa2;
   float* rm_row = nullptr;
+  // GRU gate-input layout: a (t, b) row's 16 columns are 64 contiguous bytes, rows are ~400 KB apart.  Stored straight
+  // from the accumulator layout (lane = row) a warp store touches 32 lines for 16 bytes each; staged through shared
+  // memory, four lanes write one row's 64 bytes and a store instruction covers 8 rows (8 lines).
+  const bool rm_x = MULTI && P.rm_xpose;
+  float* rm_ptr[4] = {nullptr, nullptr, nullptr, nullptr};   // rows 8 j + lane / 4 of this warp's 32 rows
+  float* rm_sc = rm_scratch + (warp - 2) * 32 * kRmPitch;
 #pragma unroll
   for (int o = 0; o < 3; ++o) { op[o].p = nullptr; op[o].pstride = 0; }
   pa1.p = pa2.p = nullptr; pa1.pstride = pa2.pstride = 0;
@@ -398,7 +406,16 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
         if (a2_on) pa2 = out_ptr(P.add2, b, l_out, chunk_base, inv_split_a2);
       }
     }
-    if (MULTI) {
+    if (rm_x) {
+      const int S = 3 * (P.rm_H >> 3) + 4;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int gj = g - lane + 8 * j + (lane >> 2);
+        const int bj = fast_div(gj, P.Lh_A, inv_Lh);
+        const int mj = gj - bj * P.Lh_A;
+        rm_ptr[j] = (gj < P.m_rows && mj < P.M_valid) ? P.rm_out + ((long long)mj * 16 * P.rm_Bp + bj) * S : nullptr;
+      }
+    } else if (MULTI) {
       rm_row = nullptr;
       if (P.rm_out && valid) {
         if (P.rm_H == 0) rm_row = P.rm_out + (long long)g * P.rm_ld + n0;
@@ -423,6 +440,26 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
   };
 
   auto process = [&](int g16, const uint32_t* r, const AddRegs& ad) {
+    if (rm_x) {
+      // (no other output, add or FiLM on this path: host-checked)  every lane takes part, rows are masked per store
+      const int H = P.rm_H, U = H >> 3, S = 3 * U + 4;
+      const int n = n0 + 16 * g16;
+      const int dirn = n / (3 * H), rem = n - dirn * 3 * H;
+      const int gate = rem / H, jj = rem - gate * H;
+      const int rank = jj / U, u = jj - rank * U;
+      const long long coloff = (long long)(dirn * 8 + rank) * P.rm_Bp * S + gate * U + u + 4 * (lane & 3);
+      __syncwarp();
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        *reinterpret_cast<uint4*>(rm_sc + lane * kRmPitch + 4 * i) = make_uint4(r[4 * i], r[4 * i + 1], r[4 * i + 2], r[4 * i + 3]);
+      __syncwarp();
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const uint4 x = *reinterpret_cast<const uint4*>(rm_sc + (8 * j + (lane >> 2)) * kRmPitch + 4 * (lane & 3));
+        if (rm_ptr[j]) *reinterpret_cast<uint4*>(rm_ptr[j] + coloff) = x;
+      }
+      return;
+    }
     if (!valid) return;
     if (g16 >= gpp && g16 % gpp == 0) {
       // next phase of a multi-phase tile (transposed conv): one output row further, channel chunks from 0 again
@@ -582,6 +619,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
   uint64_t* a_ready = s_empty + kSchedSlots;
   int* s_ring = reinterpret_cast<int*>(a_ready + kMaxAStages);
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(s_ring + kSchedSlots);
+  float* rm_scratch = reinterpret_cast<float*>(tmem_ptr_smem + 4);   // kRmScratchBytes, only with rm_xpose
 
   const uint32_t acc_stride = accum_stride_cols(P.N_TILE);
   const int n_acc = P.n_acc;
@@ -900,7 +938,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
     for (int o = 0; o < 3; ++o)
       if (o < P.n_out && ((P.out[o].act >= 1 && !(P.out[o].a1 <= 1.f)) || (P.out[o].act == 2 && !(P.out[o].a2 <= 1.f)))) le1 = false;
     const int kind = (has_add ? 1 : 0) | (has_film ? 2 : 0) | (multi ? 4 : 0) | (le1 ? 8 : 0);
-#define UV_EPI(A, F, M, L) epilogue_role<A, F, M, L>(P, tmem_base, t_full, t_empty, film_s, s_ring, s_full, s_empty, warp, lane)
+#define UV_EPI(A, F, M, L) epilogue_role<A, F, M, L>(P, tmem_base, t_full, t_empty, film_s, s_ring, s_full, s_empty, rm_scratch, warp, lane)
     switch (kind) {
       case 0: UV_EPI(false, false, false, false); break;
       case 1: UV_EPI(true, false, false, false); break;
@@ -976,7 +1014,9 @@ inline bool gemm_plan_pipeline(GemmParams& p) {
   p.n_acc = 512 / (2 * stride);
   if (p.n_acc > kMaxAcc) p.n_acc = kMaxAcc;
   if (p.n_acc < 1) return false;
-  const long long fixed = kOnesBytes + kFilmBytes + p.ident_bytes + (2 * kMaxAStages + 2 * kMaxBStages + 2 * kMaxAcc) * 8 + kSchedBytes + 16 + 1024;
+  p.rm_xpose = (p.rm_out && p.rm_H > 0 && p.n_out == 0 && !p.add1.base && !p.add2.base && !p.film && p.scale == 1.f) ? 1 : 0;
+  const long long fixed = kOnesBytes + kFilmBytes + p.ident_bytes + (2 * kMaxAStages + 2 * kMaxBStages + 2 * kMaxAcc) * 8 + kSchedBytes + 16 + 1024 +
+                          (p.rm_xpose ? kRmScratchBytes : 0);
   const long long budget = kGemmSmemBudget - fixed;
   const int n_img = p.n_src * p.n_groups * (p.smax - p.smin + 1);
   const long long total_b = (((long long)n_img * b_bytes + bias_bytes) + 127) & ~127LL;
