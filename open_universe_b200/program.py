@@ -48,7 +48,7 @@ ALTERNATE = os.environ.get("UV_ALTERNATE", "1") != "0"   # alternate the tile di
 RAW_A_MAXC = int(os.environ.get("UV_RAW_A_MAXC", "512"))   # channel limit of the scheme (measured on B200: it pays at every level, 46.2 ms per pass against 46.7 with 128 and 48.5 with 32)
 # ... and of its use in front of the encoder's strided down convs (they re-read and re-activate all r phases of A for
 # every N tile, so the transform warps pace the wide levels)
-RAW_A_RC_MAXC = int(os.environ.get("UV_RAW_A_RC_MAXC", "64"))
+RAW_A_RC_MAXC = int(os.environ.get("UV_RAW_A_RC_MAXC", "128"))
 FUSE_CONVBLOCKS = os.environ.get("UV_FUSE_CONVBLOCKS", "") == "1"   # experimental: one launch per C <= 64 ConvBlock (csrc/convblock.cuh); measured slower than three GEMM launches so far
 
 
