@@ -115,6 +115,9 @@ typedef struct {
    * producer of A writes one tensor instead of a raw and an activated copy (blocks.py:209-231: PReLU -> conv). */
   int32_t a_act;
   float a_slope;
+  /* UV_OP_GEMM / CONV_IN / CONV_OUT: i3 bit 0 = walk the tensor from its end (tiles / blocks in descending order).
+   * The builder alternates it along each chain of kernels so that a consumer starts where its producer finished,
+   * i.e. on the part of the tensor the L2 still holds.                                                          */
 } uv_op;
 
 typedef struct uv_model uv_model;
