@@ -151,7 +151,10 @@ def run_native(args, wl, rank, world, local_rank):
     torch.cuda.set_device(dev)
     if world > 1:
         # stdout carries exactly one JSON line: keep NCCL's version / info banner out of it
-        os.environ["NCCL_DEBUG"] = os.environ.get("UV_NCCL_DEBUG", "WARN")
+        # (VERSION and every level above it print the banner; no NCCL_DEBUG at all prints nothing)
+        os.environ.pop("NCCL_DEBUG", None)
+        if os.environ.get("UV_NCCL_DEBUG"):
+            os.environ["NCCL_DEBUG"] = os.environ["UV_NCCL_DEBUG"]
         dist.init_process_group("nccl", device_id=dev)
     cfg = load_model_cfg(wl["model"])
     fs = int(cfg.model.fs)
