@@ -18,9 +18,12 @@
  *
  * All functions return 0 on success, a negative uv_status otherwise;
  * uv_last_error() gives a human readable message (thread local).
- * No exceptions cross the boundary.  Calls on one handle must be serialised by
- * the caller.  All device work is enqueued on the cudaStream_t passed in
- * (as void*; NULL = legacy default stream).
+ * No exceptions cross the boundary.  Calls on one plan are serialised by the
+ * library (a plan owns one arena and one io table); use one plan per stream /
+ * thread for concurrency.  All device work is enqueued on the cudaStream_t
+ * passed in (as void*; NULL = legacy default stream); uv_enhance() does not wait
+ * for the device: batch k+1 can be queued behind batch k.  Every entry point
+ * selects the handle's device and restores the caller's current device.
  */
 #ifndef UNIVERSE_B200_H_
 #define UNIVERSE_B200_H_
@@ -32,7 +35,7 @@
 extern "C" {
 #endif
 
-#define UV_ABI_VERSION 5
+#define UV_ABI_VERSION 6
 
 typedef enum {
   UV_OK = 0,
@@ -100,7 +103,7 @@ typedef struct {
   uv_out out[3];
   int64_t rm_out;        /* arena: f32 row-major [m_rows][rm_ld]           */
   int32_t rm_ld;
-  /* ---- generic fields used by the small ops (meaning per type, see csrc/ops.cu) */
+  /* ---- generic fields used by the small ops (meaning per type: launch_op() in open_universe_b200/csrc/capi.cu) */
   int32_t B, T, Lp, C, H, F;
   int32_t i0, i1, i2, i3;
   int64_t p0, p1, p2, p3, p4, p5;
@@ -150,6 +153,11 @@ size_t uv_plan_arena_bytes(const uv_plan* p);
  * outputs.  coef: host array of n_steps uv_step_coef. keep_rms as in enhance(). */
 int uv_enhance(uv_plan* p, const float* mix, const float* noise, float* out, float* dbg_net,
                const uv_step_coef* coef, int keep_rms, void* stream);
+
+/* Waits for `stream` and reports what the calls queued so far left behind: UV_ERR_KERNEL if a device-side
+ * watchdog fired (a pipeline barrier that never completed; the code is in uv_last_error()), UV_ERR_CUDA for
+ * a CUDA error, UV_OK otherwise.  uv_enhance() itself checks the flag of the PREVIOUS calls on entry. */
+int uv_plan_status(uv_plan* p, void* stream);
 
 /* Debug / parity: run ops [first, last) eagerly (no graph) on `stream` with the
  * same io pointers, and copy a byte range of the arena back / forth.       */

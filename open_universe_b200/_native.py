@@ -18,7 +18,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 EXPORTS = [
     "uv_abi_version", "uv_sizeof_op", "uv_last_error", "uv_model_create", "uv_model_destroy", "uv_plan_create",
     "uv_plan_destroy", "uv_plan_arena_bytes", "uv_enhance", "uv_run_ops", "uv_arena_read", "uv_arena_write",
-    "uv_plan_num_launches", "uv_profile_ops", "uv_plan_arena_ptr", "uv_trace_ops",
+    "uv_plan_num_launches", "uv_profile_ops", "uv_plan_arena_ptr", "uv_trace_ops", "uv_plan_status",
 ]
 
 
@@ -80,6 +80,7 @@ def lib():
     L.uv_trace_ops.argtypes = [C.c_void_p] + io[:-1] + [C.POINTER(C.c_float), C.POINTER(C.c_float)]
     L.uv_arena_read.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
     L.uv_arena_write.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
+    L.uv_plan_status.argtypes = [C.c_void_p, C.c_void_p]
     L.uv_plan_arena_ptr.argtypes = [C.c_void_p]
     L.uv_plan_arena_ptr.restype = C.c_void_p
     if L.uv_abi_version() != _abi.UV_ABI_VERSION:
@@ -139,6 +140,10 @@ class NativePlan:
     def enhance(self, mix_ptr, noise_ptr, out_ptr, dbg_ptr, coefs, keep_rms, stream_ptr):
         _check(lib().uv_enhance(self.handle, mix_ptr, noise_ptr, out_ptr, dbg_ptr, self._coefs(coefs),
                                 1 if keep_rms else 0, stream_ptr), "uv_enhance")
+
+    def status(self, stream_ptr=None):
+        """Waits for the stream; raises if a device watchdog fired or a CUDA error is pending."""
+        _check(lib().uv_plan_status(self.handle, stream_ptr), "uv_plan_status")
 
     def run_ops(self, first, last, mix_ptr, noise_ptr, out_ptr, dbg_ptr, coefs, keep_rms, stream_ptr):
         _check(lib().uv_run_ops(self.handle, first, last, mix_ptr, noise_ptr, out_ptr, dbg_ptr, self._coefs(coefs),

@@ -3,6 +3,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -13,6 +14,8 @@
 #include "small_ops.cuh"
 
 using namespace uv;
+
+static constexpr int kMelMaxSmem = 200 * 1024;   // dynamic shared memory the mel kernel may ask for (set per device in uv_model_create)
 
 static thread_local std::string g_err;
 static int fail(int code, const std::string& msg) {
@@ -27,6 +30,19 @@ static int fail(int code, const std::string& msg) {
                                    std::to_string(__LINE__) + ")");                              \
   } while (0)
 
+// Entry points select the handle's device and restore the caller's current device on return.
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    if (prev != dev) cudaSetDevice(dev);
+    else prev = -1;
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
 struct uv_model {
   int device = 0;
   char* blob = nullptr;
@@ -40,11 +56,19 @@ struct uv_plan {
   char* arena = nullptr;
   size_t arena_bytes = 0;
   IoTable* io_dev = nullptr;
-  IoTable* io_host = nullptr;     // pinned
-  char* coef_host = nullptr;      // pinned: uv_step_coef[n_steps] + int keep_rms (+pad)
+  // pinned staging of the per-call io table and sampler coefficients: a ring of kStage slots, each guarded by an
+  // event recorded behind its H2D copies, so that a call never waits for the previous call's device work
+  static constexpr int kStage = 4;
+  char* stage_host = nullptr;     // kStage x stage_bytes: IoTable | uv_step_coef[n_steps] | int keep_rms (+pad)
+  size_t stage_bytes = 0, coef_bytes = 0;
+  cudaEvent_t stage_ev[kStage] = {nullptr, nullptr, nullptr, nullptr};
+  bool stage_used[kStage] = {false, false, false, false};
+  int stage_next = 0;
   std::vector<int64_t> coef_offs;   // one per utterance lane
   int n_steps = 0;
-  int* err_flag = nullptr;
+  int* err_host = nullptr;        // mapped pinned host int written by a tripped device watchdog (mbar_wait)
+  int* err_flag = nullptr;        // its device alias
+  std::mutex mu;                  // calls on one plan are serialised (one arena, one io table)
   int* sched = nullptr;           // [n_ops][2] tile / finished-CTA counters of the GEMM launches (self-rewinding)
   cudaGraph_t graph = nullptr;
   cudaGraphExec_t exec = nullptr;
@@ -66,22 +90,31 @@ extern "C" int uv_model_create(uv_model** out, const void* weights, size_t nbyte
   cudaDeviceProp prop;
   CUDA_TRY(cudaGetDeviceProperties(&prop, device));
   if (prop.major != 10) return fail(UV_ERR_NO_DEVICE, "device is not sm_100 (B200): found sm_" + std::to_string(prop.major * 10 + prop.minor));
-  CUDA_TRY(cudaSetDevice(device));
+  DeviceGuard guard(device);
+  // function attributes are per device: every model (= device) sets them, no process-wide "done" flags
+  CUDA_TRY(gemm_set_attributes());
+  CUDA_TRY(convblock_set_attributes());
+  CUDA_TRY(cudaFuncSetAttribute(gru_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  CUDA_TRY(cudaFuncSetAttribute(mel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMelMaxSmem));
+  char* blob = nullptr;
+  CUDA_TRY(cudaMalloc(&blob, nbytes));
+  cudaError_t e = cudaMemcpy(blob, weights, nbytes, cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) {
+    cudaFree(blob);
+    return fail(UV_ERR_CUDA, std::string("weight upload: ") + cudaGetErrorString(e));
+  }
   uv_model* m = new uv_model();
   m->device = device;
   m->nbytes = nbytes;
   m->num_sms = prop.multiProcessorCount;
-  CUDA_TRY(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemBudget));
-  CUDA_TRY(cudaFuncSetAttribute(gru_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-  CUDA_TRY(cudaMalloc(&m->blob, nbytes));
-  CUDA_TRY(cudaMemcpy(m->blob, weights, nbytes, cudaMemcpyHostToDevice));
+  m->blob = blob;
   *out = m;
   return UV_OK;
 }
 
 extern "C" void uv_model_destroy(uv_model* m) {
   if (!m) return;
-  cudaSetDevice(m->device);
+  DeviceGuard guard(m->device);
   cudaFree(m->blob);
   delete m;
 }
@@ -182,14 +215,9 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
       const size_t sm = ((size_t)(kMelFT - 1) * op.i1 + op.i0 + 4 + (size_t)kMelPwPitch * op.i2) * sizeof(float);
       const int threads = (op.i2 + 31) / 32 * 32;   // one thread per frequency bin
       // (the filterbank stage keeps two chunks of kMelFbRows x n_mels floats in the signal buffer, one band per thread)
-      if (threads > 512 || sm > 200 * 1024 || op.i0 % 4 || op.i1 % 4 || op.C > threads ||
+      if (threads > 512 || sm > (size_t)kMelMaxSmem || op.i0 % 4 || op.i1 % 4 || op.C > threads ||
           2 * kMelFbRows * op.C > (kMelFT - 1) * op.i1 + op.i0)
         return fail(UV_ERR_INVALID, "MEL front end: n_fft / hop / n_mels unsupported");
-      static bool attr_done = false;
-      if (!attr_done) {
-        CUDA_TRY(cudaFuncSetAttribute(mel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr_done = true;
-      }
       CUDA_TRY(launch_pdl(mel_kernel, dim3(nft, op.B), dim3(threads), sm, s, aptr<const float>(p, op.p0), op.Lp, op.F, op.i0, op.i1, op.i2, op.H, op.C,
                                                       op.i3, wptr<const float>(p, op.p3), wptr<const float>(p, op.p4),
                                                       aptr<float>(p, op.p1), aptr<float>(p, op.p2), nft));
@@ -377,31 +405,26 @@ static int capture_program(uv_plan* p) {
   return UV_OK;
 }
 
-extern "C" int uv_plan_create(uv_plan** out, uv_model* m, const uv_op* ops, int n_ops, size_t arena_bytes,
-                              const void* init, size_t nbytes_init, size_t init_off, int n_steps, int use_graph) {
-  if (!out || !m || !ops || n_ops <= 0) return fail(UV_ERR_INVALID, "uv_plan_create: null argument");
-  CUDA_TRY(cudaSetDevice(m->device));
-  uv_plan* p = new uv_plan();
-  p->model = m;
-  p->ops.assign(ops, ops + n_ops);
-  p->arena_bytes = arena_bytes;
-  p->n_steps = n_steps;
-  p->use_graph = use_graph != 0;
-  CUDA_TRY(cudaMalloc(&p->arena, arena_bytes));
-  CUDA_TRY(cudaMemset(p->arena, 0, arena_bytes));
+static int plan_build(uv_plan* p, const void* init, size_t nbytes_init, size_t init_off) {
+  const int n_ops = (int)p->ops.size();
+  CUDA_TRY(cudaMalloc(&p->arena, p->arena_bytes));
+  CUDA_TRY(cudaMemset(p->arena, 0, p->arena_bytes));
   if (init && nbytes_init) {
-    if (init_off + nbytes_init > arena_bytes) return fail(UV_ERR_INVALID, "init blob out of arena");
+    if (init_off + nbytes_init > p->arena_bytes) return fail(UV_ERR_INVALID, "init blob out of arena");
     CUDA_TRY(cudaMemcpy(p->arena + init_off, init, nbytes_init, cudaMemcpyHostToDevice));
   }
   CUDA_TRY(cudaMalloc(&p->io_dev, sizeof(IoTable)));
-  CUDA_TRY(cudaMallocHost(&p->io_host, sizeof(IoTable)));
-  CUDA_TRY(cudaMallocHost(&p->coef_host, (size_t)n_steps * 16 + 16));
-  CUDA_TRY(cudaMalloc(&p->err_flag, sizeof(int)));
-  CUDA_TRY(cudaMemset(p->err_flag, 0, sizeof(int)));
+  p->coef_bytes = (size_t)p->n_steps * 16 + 16;
+  p->stage_bytes = (sizeof(IoTable) + p->coef_bytes + 63) & ~(size_t)63;
+  CUDA_TRY(cudaMallocHost(&p->stage_host, p->stage_bytes * uv_plan::kStage));
+  for (int i = 0; i < uv_plan::kStage; ++i) CUDA_TRY(cudaEventCreateWithFlags(&p->stage_ev[i], cudaEventDisableTiming));
+  CUDA_TRY(cudaHostAlloc(&p->err_host, sizeof(int), cudaHostAllocMapped));
+  *p->err_host = 0;
+  CUDA_TRY(cudaHostGetDevicePointer(&p->err_flag, p->err_host, 0));
   CUDA_TRY(cudaMalloc(&p->sched, (size_t)n_ops * 2 * sizeof(int)));
   CUDA_TRY(cudaMemset(p->sched, 0, (size_t)n_ops * 2 * sizeof(int)));
   int rc = validate_ops(p);
-  if (rc) { uv_plan_destroy(p); return rc; }
+  if (rc) return rc;
   for (const uv_op& op : p->ops) {
     if (op.type == UV_OP_CONV_OUT) {
       bool seen = false;
@@ -412,16 +435,35 @@ extern "C" int uv_plan_create(uv_plan** out, uv_model* m, const uv_op* ops, int 
   }
   // plan-time setup ops (FiLM table)
   for (int i = 0; i < n_ops; ++i)
-    if (p->ops[i].step == -2 && (rc = launch_op(p, i, 0))) { uv_plan_destroy(p); return rc; }
+    if (p->ops[i].step == -2 && (rc = launch_op(p, i, 0))) return rc;
   CUDA_TRY(cudaDeviceSynchronize());
-  if (p->use_graph && (rc = capture_program(p))) { uv_plan_destroy(p); return rc; }
+  if (p->use_graph && (rc = capture_program(p))) return rc;
+  return UV_OK;
+}
+
+extern "C" int uv_plan_create(uv_plan** out, uv_model* m, const uv_op* ops, int n_ops, size_t arena_bytes,
+                              const void* init, size_t nbytes_init, size_t init_off, int n_steps, int use_graph) {
+  if (!out || !m || !ops || n_ops <= 0) return fail(UV_ERR_INVALID, "uv_plan_create: null argument");
+  DeviceGuard guard(m->device);
+  uv_plan* p = new uv_plan();
+  p->model = m;
+  p->ops.assign(ops, ops + n_ops);
+  p->arena_bytes = arena_bytes;
+  p->n_steps = n_steps;
+  p->use_graph = use_graph != 0;
+  const int rc = plan_build(p, init, nbytes_init, init_off);
+  if (rc) {   // every early return above lands here: nothing of a half-built plan is leaked
+    const std::string msg = g_err;
+    uv_plan_destroy(p);
+    return fail(rc, msg);
+  }
   *out = p;
   return UV_OK;
 }
 
 extern "C" void uv_plan_destroy(uv_plan* p) {
   if (!p) return;
-  cudaSetDevice(p->model->device);
+  DeviceGuard guard(p->model->device);
   if (p->exec) cudaGraphExecDestroy(p->exec);
   if (p->graph) cudaGraphDestroy(p->graph);
   if (p->cap_stream) cudaStreamDestroy(p->cap_stream);
@@ -430,39 +472,52 @@ extern "C" void uv_plan_destroy(uv_plan* p) {
   if (p->ev_join) cudaEventDestroy(p->ev_join);
   for (int l = 0; l < 2; ++l)
     if (p->ev_lane[l]) cudaEventDestroy(p->ev_lane[l]);
+  for (int i = 0; i < uv_plan::kStage; ++i)
+    if (p->stage_ev[i]) cudaEventDestroy(p->stage_ev[i]);
   cudaFree(p->sched);
   cudaFree(p->arena);
   cudaFree(p->io_dev);
-  cudaFree(p->err_flag);
-  if (p->io_host) cudaFreeHost(p->io_host);
-  if (p->coef_host) cudaFreeHost(p->coef_host);
+  if (p->err_host) cudaFreeHost(p->err_host);
+  if (p->stage_host) cudaFreeHost(p->stage_host);
   delete p;
 }
 
 extern "C" size_t uv_plan_arena_bytes(const uv_plan* p) { return p ? p->arena_bytes : 0; }
 extern "C" int uv_plan_num_launches(const uv_plan* p) { return p ? p->n_launches : 0; }
 
-static int stage_io(uv_plan* p, const float* mix, const float* noise, float* out, float* dbg,
-                    const uv_step_coef* coef, int keep_rms, cudaStream_t s) {
-  if (!mix || !noise || !out || !coef) return fail(UV_ERR_INVALID, "uv_enhance: null pointer");
-  // the previous call's async copies from these pinned buffers must have completed
-  CUDA_TRY(cudaStreamSynchronize(s));
-  p->io_host->mix = mix; p->io_host->noise = noise; p->io_host->out = out; p->io_host->dbg = dbg;
-  CUDA_TRY(cudaMemcpyAsync(p->io_dev, p->io_host, sizeof(IoTable), cudaMemcpyHostToDevice, s));
-  if (!p->coef_offs.empty()) {
-    memcpy(p->coef_host, coef, (size_t)p->n_steps * 16);
-    int kr[4] = {keep_rms, 0, 0, 0};
-    memcpy(p->coef_host + (size_t)p->n_steps * 16, kr, 16);
-    for (int64_t off : p->coef_offs)
-      CUDA_TRY(cudaMemcpyAsync(p->arena + off, p->coef_host, (size_t)p->n_steps * 16 + 16, cudaMemcpyHostToDevice, s));
-  }
+// A tripped device watchdog (mbar_wait -> trap) leaves its code in mapped host memory: visible without any
+// device call, also after the trap has made the context unusable.
+static int check_err_flag(uv_plan* p) {
+  const int flag = *reinterpret_cast<volatile int*>(p->err_host);
+  if (flag) return fail(UV_ERR_KERNEL, "device watchdog fired, code " + std::to_string(flag));
   return UV_OK;
 }
 
-static int check_err_flag(uv_plan* p) {
-  int flag = 0;
-  CUDA_TRY(cudaMemcpy(&flag, p->err_flag, sizeof(int), cudaMemcpyDeviceToHost));
-  if (flag) return fail(UV_ERR_KERNEL, "device watchdog fired, code " + std::to_string(flag));
+// Stages the io table and the sampler coefficients of one call through the next slot of the pinned ring and
+// enqueues their H2D copies on `s`.  The host only waits if that slot's copies of kStage calls ago are still
+// pending, so batch k+1 can be queued behind batch k.
+static int stage_io(uv_plan* p, const float* mix, const float* noise, float* out, float* dbg,
+                    const uv_step_coef* coef, int keep_rms, cudaStream_t s) {
+  if (!mix || !noise || !out || !coef) return fail(UV_ERR_INVALID, "uv_enhance: null pointer");
+  int rc = check_err_flag(p);   // outcome of the previous calls
+  if (rc) return rc;
+  const int slot = p->stage_next;
+  p->stage_next = (slot + 1) % uv_plan::kStage;
+  if (p->stage_used[slot]) CUDA_TRY(cudaEventSynchronize(p->stage_ev[slot]));
+  char* h = p->stage_host + (size_t)slot * p->stage_bytes;
+  IoTable* io = reinterpret_cast<IoTable*>(h);
+  io->mix = mix; io->noise = noise; io->out = out; io->dbg = dbg;
+  CUDA_TRY(cudaMemcpyAsync(p->io_dev, io, sizeof(IoTable), cudaMemcpyHostToDevice, s));
+  if (!p->coef_offs.empty()) {
+    char* c = h + sizeof(IoTable);
+    memcpy(c, coef, (size_t)p->n_steps * 16);
+    int kr[4] = {keep_rms, 0, 0, 0};
+    memcpy(c + (size_t)p->n_steps * 16, kr, 16);
+    for (int64_t off : p->coef_offs)
+      CUDA_TRY(cudaMemcpyAsync(p->arena + off, c, p->coef_bytes, cudaMemcpyHostToDevice, s));
+  }
+  CUDA_TRY(cudaEventRecord(p->stage_ev[slot], s));
+  p->stage_used[slot] = true;
   return UV_OK;
 }
 
@@ -470,14 +525,29 @@ extern "C" int uv_enhance(uv_plan* p, const float* mix, const float* noise, floa
                           const uv_step_coef* coef, int keep_rms, void* stream) {
   if (!p) return fail(UV_ERR_INVALID, "uv_enhance: null plan");
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-  CUDA_TRY(cudaSetDevice(p->model->device));
+  DeviceGuard guard(p->model->device);
+  std::lock_guard<std::mutex> lock(p->mu);
   int rc = stage_io(p, mix, noise, out, dbg_net, coef, keep_rms, s);
   if (rc) return rc;
   if (p->use_graph) {
-    CUDA_TRY(cudaGraphLaunch(p->exec, s));
+    cudaError_t e = cudaGraphLaunch(p->exec, s);
+    if (e != cudaSuccess) {
+      if (check_err_flag(p)) return UV_ERR_KERNEL;   // a sticky error left by a tripped watchdog
+      return fail(UV_ERR_CUDA, std::string("cudaGraphLaunch: ") + cudaGetErrorString(e));
+    }
   } else if ((rc = enqueue_range(p, 0, (int)p->ops.size(), s, true))) {
     return rc;
   }
+  return UV_OK;
+}
+
+extern "C" int uv_plan_status(uv_plan* p, void* stream) {
+  if (!p) return fail(UV_ERR_INVALID, "uv_plan_status: null plan");
+  DeviceGuard guard(p->model->device);
+  cudaError_t e = cudaStreamSynchronize(reinterpret_cast<cudaStream_t>(stream));
+  int rc = check_err_flag(p);
+  if (rc) return rc;
+  if (e != cudaSuccess) return fail(UV_ERR_CUDA, std::string("cudaStreamSynchronize: ") + cudaGetErrorString(e));
   return UV_OK;
 }
 
@@ -485,7 +555,8 @@ extern "C" int uv_run_ops(uv_plan* p, int first, int last, const float* mix, con
                           float* dbg_net, const uv_step_coef* coef, int keep_rms, void* stream) {
   if (!p || first < 0 || last > (int)p->ops.size()) return fail(UV_ERR_INVALID, "uv_run_ops: bad range");
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-  CUDA_TRY(cudaSetDevice(p->model->device));
+  DeviceGuard guard(p->model->device);
+  std::lock_guard<std::mutex> lock(p->mu);
   int rc = stage_io(p, mix, noise, out, dbg_net, coef, keep_rms, s);
   if (rc) return rc;
   if ((rc = enqueue_range(p, first, last, s, false))) return rc;
@@ -497,7 +568,8 @@ extern "C" int uv_profile_ops(uv_plan* p, const float* mix, const float* noise, 
                               const uv_step_coef* coef, int keep_rms, void* stream, float* ms_per_op) {
   if (!p || !ms_per_op) return fail(UV_ERR_INVALID, "uv_profile_ops: null argument");
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-  CUDA_TRY(cudaSetDevice(p->model->device));
+  DeviceGuard guard(p->model->device);
+  std::lock_guard<std::mutex> lock(p->mu);
   int rc = stage_io(p, mix, noise, out, dbg_net, coef, keep_rms, s);
   if (rc) return rc;
   const int n = (int)p->ops.size();
@@ -521,7 +593,8 @@ extern "C" int uv_profile_ops(uv_plan* p, const float* mix, const float* noise, 
 extern "C" int uv_trace_ops(uv_plan* p, const float* mix, const float* noise, float* out, float* dbg_net,
                             const uv_step_coef* coef, int keep_rms, float* t_start_ms, float* t_end_ms) {
   if (!p || !t_start_ms || !t_end_ms) return fail(UV_ERR_INVALID, "uv_trace_ops: null argument");
-  CUDA_TRY(cudaSetDevice(p->model->device));
+  DeviceGuard guard(p->model->device);
+  std::lock_guard<std::mutex> lock(p->mu);
   const bool two = has_two_lanes(p);
   int rc = ensure_lane_objects(p, two);
   if (rc) return rc;
@@ -548,7 +621,7 @@ extern "C" int uv_trace_ops(uv_plan* p, const float* mix, const float* noise, fl
 
 extern "C" int uv_arena_read(uv_plan* p, size_t off, void* host_dst, size_t nbytes) {
   if (!p || off + nbytes > p->arena_bytes) return fail(UV_ERR_INVALID, "uv_arena_read: out of range");
-  CUDA_TRY(cudaSetDevice(p->model->device));
+  DeviceGuard guard(p->model->device);
   CUDA_TRY(cudaDeviceSynchronize());
   CUDA_TRY(cudaMemcpy(host_dst, p->arena + off, nbytes, cudaMemcpyDeviceToHost));
   return UV_OK;
@@ -558,7 +631,7 @@ extern "C" void* uv_plan_arena_ptr(uv_plan* p) { return p ? (void*)p->arena : nu
 
 extern "C" int uv_arena_write(uv_plan* p, size_t off, const void* host_src, size_t nbytes) {
   if (!p || off + nbytes > p->arena_bytes) return fail(UV_ERR_INVALID, "uv_arena_write: out of range");
-  CUDA_TRY(cudaSetDevice(p->model->device));
+  DeviceGuard guard(p->model->device);
   CUDA_TRY(cudaMemcpy(p->arena + off, host_src, nbytes, cudaMemcpyHostToDevice));
   return UV_OK;
 }

@@ -394,15 +394,13 @@ inline bool cb_plan(CbParams& p) {
   return false;
 }
 
+inline cudaError_t convblock_set_attributes() {   // per device (uv_model_create)
+  return cudaFuncSetAttribute(convblock_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+}
+
 inline cudaError_t convblock_launch(CbParams p, int num_sms, cudaStream_t s) {
   if (!cb_plan(p)) return cudaErrorInvalidConfiguration;
   const CbSmem L = cb_smem_layout(p.C, p.has_bias, p.n_bufs);
-  static bool attr_done = false;
-  if (!attr_done) {
-    cudaError_t e = cudaFuncSetAttribute(convblock_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    if (e != cudaSuccess) return e;
-    attr_done = true;
-  }
   const int grid = p.n_tiles < num_sms ? p.n_tiles : num_sms;
   convblock_kernel<<<grid, kCbThreads, L.total, s>>>(p);
   return cudaGetLastError();

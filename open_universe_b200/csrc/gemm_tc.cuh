@@ -111,7 +111,9 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, int* er
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
     if (++spins > (1u << 26)) {
-      if (err_flag) atomicExch(err_flag, code);
+      // err_flag is mapped pinned host memory (capi.cu): a plain store + system fence reaches the host even though
+      // the trap below kills the context
+      if (err_flag) *reinterpret_cast<volatile int*>(err_flag) = code;
       __threadfence_system();
       __trap();
     }
@@ -1045,15 +1047,14 @@ inline bool gemm_plan_pipeline(GemmParams& p) {
   return true;
 }
 
+// Function attributes are per device: call once for every device the kernel is launched on (uv_model_create does).
+inline cudaError_t gemm_set_attributes() {
+  return cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemBudget);
+}
+
 inline cudaError_t gemm_launch(GemmParams p, int num_sms, cudaStream_t stream) {
   if (!gemm_plan_pipeline(p)) return cudaErrorInvalidConfiguration;
   const size_t smem = gemm_smem_bytes(p);
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemBudget);
-    if (e != cudaSuccess) return e;
-    attr_set = true;
-  }
   if (!p.sched) return cudaErrorInvalidValue;
   const int total = p.n_tiles_m * p.n_tiles_n;
   int grid = total < num_sms ? total : num_sms;

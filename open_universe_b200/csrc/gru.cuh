@@ -129,7 +129,7 @@ __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity,
   uint32_t spins = 0;
   while (!mbar_try_wait_cluster(bar, parity)) {
     if (++spins > (1u << 22)) {
-      if (err_flag) atomicExch(err_flag, code);
+      if (err_flag) *reinterpret_cast<volatile int*>(err_flag) = code;
       __threadfence_system();
       __trap();
     }

@@ -386,6 +386,7 @@ static void run_perf(int num_sms, bool phases = false) {
 }
 
 int main(int argc, char** argv) {
+  if (gemm_set_attributes() != cudaSuccess) { fprintf(stderr, "cudaFuncSetAttribute failed (no sm_100 device?)\n"); }
   if (argc < 2) { printf("usage: test_gemm <case|perf|list> [swap]\n"); return 2; }
   int dev_sms = 0;
   CK(cudaDeviceGetAttribute(&dev_sms, cudaDevAttrMultiProcessorCount, 0));

@@ -49,6 +49,8 @@ RAW_A_MAXC = int(os.environ.get("UV_RAW_A_MAXC", "512"))   # channel limit of th
 # ... and of its use in front of the encoder's strided down convs (they re-read and re-activate all r phases of A for
 # every N tile, so the transform warps pace the wide levels)
 RAW_A_RC_MAXC = int(os.environ.get("UV_RAW_A_RC_MAXC", "128"))
+RECYCLE = os.environ.get("UV_RECYCLE", "1") != "0"   # liveness-based reuse of the activation slots of the arena (finalize_arena)
+VBASE = 1 << 44   # planes tensors carry virtual offsets >= VBASE until finalize_arena() places them
 FUSE_CONVBLOCKS = os.environ.get("UV_FUSE_CONVBLOCKS", "") == "1"   # experimental: one launch per C <= 64 ConvBlock (csrc/convblock.cuh); measured slower than three GEMM launches so far
 
 
@@ -76,6 +78,7 @@ class Program:
         self.ops = []
         self.names = []
         self.arena = arena_base
+        self.varena = VBASE      # virtual address space of the planes tensors (placed by finalize_arena)
         self.lane = lane
         self.rev = 0
         self.tensors = {}
@@ -96,7 +99,8 @@ class Program:
             return t
         assert C % 8 == 0
         es = 2 if dtype == DT_BF16 else 4
-        off = self.alloc(split * (C // 8) * lev.P * 8 * es)
+        off = _ru(self.varena, 1024)
+        self.varena = off + split * (C // 8) * lev.P * 8 * es
         t = UvTens(off, dtype, C // 8, split, lev.Lh, lev.P, G)
         self.tensors[name] = t
         return t
@@ -139,6 +143,107 @@ class Program:
         if a_slope is not None:   # `a` is a raw tensor: PReLU(a_slope) is applied inside the kernel
             op.a_act, op.a_slope = 1, a_slope
         return self.emit(op, name)
+
+
+def _op_tensors(op):
+    """Every uv_tens record of an op (and of the parts of a fused op)."""
+    yield op.a
+    yield op.add1
+    yield op.add2
+    for k in range(3):
+        yield op.out[k].t
+    for part in getattr(op, "parts", ()):
+        yield from _op_tensors(part)
+
+
+def _tens_bytes(t):
+    return t.split * t.nch * t.P * 8 * (2 if t.dtype == DT_BF16 else 4)
+
+
+def finalize_arena(pg, recycle=True, persistent=()):
+    """Places the planes tensors of a lane program (virtual offsets >= VBASE) behind its raw buffers.
+
+    recycle=False: one slot per tensor, in allocation order.
+    recycle=True: a slot is shared by tensors whose live ranges do not overlap.  Time = op index over the front end /
+    conditioner and the FIRST sampler step; the later steps name exactly the same tensors in the same order, so the
+    placement of step 0 holds for all of them.  A tensor touched both before and inside the sampler loop (the hoisted
+    condition projections), and every tensor listed in `persistent`, lives to the end.  Slots are only shared inside
+    a class (utterance pitch, plane pitch, element size): the rows between utterances and the guard rows of every
+    plane are never written and serve as the zero padding of the convolutions (csrc/uv_common.cuh), which stays true
+    only if a plane always holds tensors of one row geometry.  The result is checked op by op on the CPU by the
+    emulator tests (same program, same offsets).
+    Sets pg.arena, pg.live {name: (first, last)} and patches every record."""
+    tens = {t.off: (name, t) for name, t in pg.tensors.items() if isinstance(t, UvTens)}
+    assert all(off >= VBASE for off in tens)
+    n_ops = len(pg.ops)
+    first_step = [i for i, op in enumerate(pg.ops) if op.step == 0]
+    t_end = (first_step[-1] + 1) if first_step else n_ops
+    live = {}
+    in_loop, pre_loop = set(), set()
+    for i, op in enumerate(pg.ops):
+        if op.step > 0:
+            continue   # same tensors as step 0 (asserted below)
+        for u in _op_tensors(op):
+            if u.off < 0:
+                continue
+            assert u.off in tens, ("op references an unknown tensor", pg.names[i])
+            lo, hi = live.get(u.off, (i, i))
+            live[u.off] = (min(lo, i), max(hi, i))
+            (in_loop if op.step == 0 else pre_loop).add(u.off)
+    if first_step:
+        n0 = len(first_step)
+        for n in range(1, pg.n_steps):
+            for k, i0 in enumerate(first_step):
+                a, b = pg.ops[i0], pg.ops[pg.step_first_op[n] + k]
+                assert [u.off for u in _op_tensors(a)] == [u.off for u in _op_tensors(b)], (pg.names[i0], "step", n)
+        assert pg.step_first_op[1] - pg.step_first_op[0] == n0 if pg.n_steps > 1 else True
+    keep = {t.off for t in persistent if t is not None}
+    for off in tens:
+        lo, hi = live.get(off, (0, 0))
+        if off in keep or (off in in_loop and off in pre_loop):
+            hi = 1 << 30
+        live[off] = (lo, hi)
+    base = _ru(pg.arena, 1024)
+    place = {}
+    if not recycle:
+        for off in sorted(tens):
+            place[off] = base
+            base = _ru(base + _tens_bytes(tens[off][1]), 1024)
+    else:
+        classes = {}
+        for off, (_, t) in tens.items():
+            classes.setdefault((t.Lh, t.P, t.dtype), []).append(off)
+        for key in sorted(classes):
+            _, P, dtype = key
+            plane = P * 8 * (2 if dtype == DT_BF16 else 4)   # a multiple of 128 bytes (P is a multiple of 8)
+            # interval allocation in units of planes: tensors in order of their first use, first fit among the
+            # planes whose occupant's life has ended
+            busy = []    # (first plane, n planes, last use)
+            n_planes = 0
+            for off in sorted(classes[key], key=lambda o: (live[o][0], -live[o][1], o)):
+                lo, hi = live[off]
+                need = tens[off][1].split * tens[off][1].nch
+                busy = [b for b in busy if b[2] >= lo]   # an output may not share planes with an input of the same op
+                busy.sort()
+                pos = 0
+                for b0, bn, _ in busy:
+                    if pos + need <= b0:
+                        break
+                    pos = max(pos, b0 + bn)
+                busy.append((pos, need, hi))
+                n_planes = max(n_planes, pos + need)
+                place[off] = base + pos * plane
+            base = _ru(base + n_planes * plane, 1024)
+    for op in pg.ops:
+        for u in _op_tensors(op):
+            if u.off >= VBASE:
+                u.off = place[u.off]
+    pg.live = {}
+    for off, (name, t) in tens.items():
+        pg.live[name] = live[off]
+        t.off = place[off]
+    pg.arena = base
+    return pg
 
 
 def gru_geometry(H, B):
@@ -228,7 +333,7 @@ def default_lanes(B, aux=False):
     return 2 if B >= LANE_MIN_B else 1
 
 
-def build_program(pm, cfg, B, T, n_steps, aux=False, lanes=None):
+def build_program(pm, cfg, B, T, n_steps, aux=False, lanes=None, recycle=None):
     """Program of one enhance() call.  lanes = 2 splits the utterances into two independent halves whose op
     lists are concatenated (lane 0 first); each lane owns its tensors, the FiLM table is shared.  The native
     plan captures lane 1 on a second stream (csrc/capi.cu capture_program).  One cross-lane edge staggers the
@@ -237,12 +342,14 @@ def build_program(pm, cfg, B, T, n_steps, aux=False, lanes=None):
     recurrences do not coincide.  The result carries lane 0's attributes plus `lanes` (the per-lane programs)."""
     if lanes is None:
         lanes = default_lanes(B, aux)
+    if recycle is None:
+        recycle = RECYCLE
     if lanes == 1 or B < 2:
-        return _build_lane(pm, cfg, B, T, n_steps, aux=aux)
+        return _build_lane(pm, cfg, B, T, n_steps, aux=aux, recycle=recycle)
     assert not aux, "aux-signal programs are single-lane (run_ops ranges address one op list)"
     B0 = (B + 1) // 2
-    pg0 = _build_lane(pm, cfg, B0, T, n_steps, b_off=0, B_total=B)
-    pg1 = _build_lane(pm, cfg, B - B0, T, n_steps, b_off=B0, B_total=B, arena_base=pg0.arena, lane=1, shared=pg0)
+    pg0 = _build_lane(pm, cfg, B0, T, n_steps, b_off=0, B_total=B, recycle=recycle)
+    pg1 = _build_lane(pm, cfg, B - B0, T, n_steps, b_off=B0, B_total=B, arena_base=pg0.arena, lane=1, shared=pg0, recycle=recycle)
     stagger = os.environ.get("UV_LANE_STAGGER", "c.enc3.rc")
     if stagger in pg0.names:
         pg0.ops[pg0.names.index(stagger)].sync |= 1
@@ -258,7 +365,7 @@ def build_program(pm, cfg, B, T, n_steps, aux=False, lanes=None):
     return pg
 
 
-def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_base=0, lane=0, shared=None):
+def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_base=0, lane=0, shared=None, recycle=True):
     """aux=True also evaluates the tail of the conditioner decoder's last block (y_hat, the input of aux_to_wav:
     reference condition.py:264-270,362; universe.py:313-331), which the default path never uses.
     b_off / B_total: this lane's first utterance in / the size of the caller's batch (io tensors cover all lanes)."""
@@ -339,11 +446,12 @@ def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_
             # ".s2d" packings (2 sources x 3 shifts, both output phases of a row in one tile; weights.w4_same_s2d)
             assert h_act is None and cond_out is None and not only_conv1 and v_add2 is None
             sfx = ".s2d"
-            c1 = pg.tens(f"{pfx}tmp.c1.s2d.{C}", lev, C, split=2)
-            c2 = pg.tens(f"{pfx}tmp.c2.s2d.{C}", lev, C, split=2)
+            c1 = pg.tens(f"{name}.c1", lev, C, split=2)
+            c2 = pg.tens(f"{name}.c2", lev, C, split=2)
         else:
-            c1 = pg.tens(f"{pfx}tmp.c1.{lev.L}.{C}", lev, C)
-            c2 = pg.tens(f"{pfx}tmp.c2.{lev.L}.{C}", lev, C)
+            # (one name per block: finalize_arena() shares the slots of tensors whose lives do not overlap)
+            c1 = pg.tens(f"{name}.c1", lev, C)
+            c2 = pg.tens(f"{name}.c2", lev, C)
         s2, s3 = L[name + ".conv2"]["slope"], L[name + ".conv3"]["slope"]
         outs = [] if only_conv1 else [_act(c1, s2)]
         if cond_out is not None:
@@ -629,6 +737,8 @@ def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_
     op.B, op.T, op.Lp, op.i0, op.p0, op.p1, op.p2 = B, T, Lp, pg.pad_left, pg.x, pg.mix_rms, pg.coef + n_steps * 16
     op.i1, op.i2 = b_off, B_total
     pg.emit(op, "post")
+    # the aux-signal paths read y_hat from the host side after the conditioner has run (universe.py _enhance_aux)
+    finalize_arena(pg, recycle=recycle, persistent=[getattr(pg, "y_hat", None)])
     pg.arena = _ru(pg.arena, 1024)
     return pg
 

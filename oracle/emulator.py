@@ -21,6 +21,41 @@ def _dt(t):
     return torch.bfloat16 if t.dtype == _abi.DT_BF16 else torch.float32
 
 
+def op_outputs(op):
+    """[(label, arena offset, nbytes, torch dtype)] of everything `op` writes into the arena (per-op GPU-vs-emulator
+    comparisons: tests/test_gpu_modules.py, tools/gpu_debug.py)."""
+    outs = []
+    t = op.type
+
+    def tens(label, u):
+        es = 2 if u.dtype == _abi.DT_BF16 else 4
+        outs.append((label, u.off, u.split * u.nch * u.P * 8 * es, torch.bfloat16 if es == 2 else torch.float32))
+
+    if t in (_abi.OP_GEMM, _abi.OP_GRU, _abi.OP_CONV_IN, _abi.OP_MEL_FIN):
+        for i in range(op.n_out):
+            tens(f"out{i}", op.out[i].t)
+        if t == _abi.OP_GEMM and op.rm_out >= 0:
+            if op.H > 0:   # GRU gate-input layout [t][dir][rank 8][b < Bp][3U + 4]
+                outs.append(("rm", op.rm_out, op.M_valid * 16 * op.i1 * (3 * (op.H // 8) + 4) * 4, torch.float32))
+            else:
+                outs.append(("rm", op.rm_out, op.m_rows * op.rm_ld * 4, torch.float32))
+    elif t == _abi.OP_CONVBLOCK:
+        for i in range(op.n_out):
+            tens(f"out{i}", op.out[i].t)
+        if op.i1:
+            tens("cond", op.out[2].t)
+    elif t == _abi.OP_PREP:
+        outs += [("sig", op.p0, op.B * op.Lp * 4, torch.float32), ("rms", op.p1, op.B * 4, torch.float32)]
+    elif t == _abi.OP_MEL:
+        outs += [("mel", op.p1, op.B * op.F * op.C * 4, torch.float32),
+                 ("energy", op.p2, op.B * ((op.F + op.T - 1) // op.T) * 4, torch.float32)]
+    elif t in (_abi.OP_INIT_X, _abi.OP_CONV_OUT):
+        outs.append(("x", op.p0, op.B * op.Lp * 4, torch.float32))
+    elif t == _abi.OP_FILM:
+        outs.append(("film", op.p1, op.i0 * op.i2 * 4, torch.float32))
+    return outs
+
+
 class Emulator:
     def __init__(self, pm, pg):
         self.pm, self.pg = pm, pg

@@ -32,6 +32,9 @@ CASES = [
     # signal decoupling layer paths (universe.py:313-331, universe_gan.py:147-151); snake alpha perturbed
     ("pp16k_aux", "universepp_16k", 2, 3000, dict(use_aux_signal=True, snake_alpha=True)),
     ("pp16k_warm", "universepp_16k", 2, 3000, dict(warm_start=5, keep_rms=True, snake_alpha=True)),
+    # BASELINE config length (4 s clips: 401 bottleneck frames = GRU steps).  To keep the fixture small only the
+    # final waveforms and the network outputs of utterance 1 at steps 0, 3 and 7 are stored (fp32).
+    ("pp16k_4s", "universepp_16k", 2, 64000, dict(keep_steps=[0, 3, 7], keep_row=1)),
 ]
 
 
@@ -64,6 +67,7 @@ def main():
         tot_ds = ref.tot_ds
         n_steps = kw.get("n_steps", cfg["diffusion"]["n_steps"])
         with_target = kw.pop("with_target", False)
+        keep_steps, keep_row = kw.pop("keep_steps", None), kw.pop("keep_row", None)
         mix, noise = make_inputs(B * (kw.get("ensemble") or 1), T, tot_ds, n_steps)
         mix = mix[:B]
         extra = {}
@@ -74,9 +78,12 @@ def main():
             kw["rng"] = torch.Generator().manual_seed(5)
         out, steps = rh.run_reference_enhance(ref, mix, [n[:, None, :] for n in noise], **kw)
         kw.pop("target", None), kw.pop("rng", None)
+        st = torch.stack([s[:, 0] for s in steps]).contiguous() if steps else torch.zeros(0)
+        if keep_steps is not None:
+            st = st[keep_steps][:, keep_row : keep_row + 1].clone()
+            extra.update(keep_steps=keep_steps, keep_row=keep_row)
         fix = dict(model=name, B=B, T=T, kwargs=kw, seed_weights=7, seed_inputs=1235, with_target=with_target, **extra,
-                   out=out.contiguous(),
-                   steps=torch.stack([s[:, 0] for s in steps]).contiguous() if steps else torch.zeros(0))
+                   out=out.contiguous(), steps=st)
         torch.save(fix, os.path.join(OUT, f"enhance_{case}.pt"))
         print(case, "out rms", out.pow(2).mean().sqrt().item(), "max", out.abs().max().item(),
               "net rms", [round(s.pow(2).mean().sqrt().item(), 4) for s in steps])

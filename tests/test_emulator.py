@@ -44,45 +44,45 @@ def test_step_coefs_reduce_to_reference_update():
         assert abs(a * x + b * net + c * z - ref) < 1e-6
 
 
-def test_arena_tensors_do_not_overlap():
-    model, cfg = build_model("universepp_16k")
-    pm = weights.pack_model(model.state_dict(), model.model_config())
-    pg = program.build_program(pm, model.model_config(), 3, 2000, 8)
-    spans = []
+def _spans(pg):
+    out = []
     for name, t in pg.tensors.items():
         if isinstance(t, int):
             continue
-        es = 2 if t.dtype == 1 else 4
-        spans.append((t.off, t.off + t.split * t.nch * t.P * 8 * es, name))
-    spans.sort()
-    for (a0, a1, an), (b0, b1, bn) in zip(spans, spans[1:]):
-        assert a1 <= b0, (an, bn)
-    assert spans[-1][1] <= pg.arena
+        out.append((t.off, t.off + program._tens_bytes(t), name, (t.Lh, t.P, t.dtype)))
+    return sorted(out)
 
 
-def test_two_lane_program_equals_single_lane_programs():
-    """The two-lane program (halves of the batch with their own tensors, io offsets i1 / i2) computes, for each
-    half, bit for bit what a single-lane program of that half computes (the CPU emulator's fp32 matmuls block
-    differently for another batch size, so the comparison is per lane, not against one program of the whole batch)."""
+def test_arena_tensors_do_not_overlap_without_recycling():
     model, cfg = build_model("universepp_16k")
+    pm = weights.pack_model(model.state_dict(), model.model_config())
+    pg = program.build_program(pm, model.model_config(), 3, 2000, 8, recycle=False)
+    spans = _spans(pg)
+    for (a0, a1, an, _), (b0, b1, bn, _) in zip(spans, spans[1:]):
+        assert a1 <= b0, (an, bn)
+    assert spans[-1][1] <= pg.arena and spans[0][0] >= pg.sig
+
+
+@pytest.mark.parametrize("name,B", [("universepp_16k", 3), ("universepp_16k", 17), ("universe_16k", 2), ("universepp_24k", 2)])
+def test_recycled_arena_shares_slots_only_between_dead_tensors_of_one_geometry(name, B):
+    """finalize_arena(): two tensors may overlap in memory only if their live ranges are disjoint (an op's outputs
+    never share planes with its inputs) and they have the same row geometry (the never-written padding rows of a plane
+    stay zero); raw buffers are never shared; the program is smaller than with one slot per tensor."""
+    model, cfg = build_model(name)
     mcfg = model.model_config()
     pm = weights.pack_model(model.state_dict(), mcfg)
-    B, T, n_steps = 3, 700, 3
-    g = torch.Generator().manual_seed(5)
-    mix = 0.1 * torch.randn(B, T, generator=g)
-    Lp = T + (model.tot_ds - T % model.tot_ds)
-    noise = torch.stack([torch.randn(B, Lp, generator=g) for _ in range(n_steps)])
-    coefs = program.step_coefs(mcfg, n_steps, 1.3)
-    pg2 = program.build_program(pm, mcfg, B, T, n_steps, lanes=2)
-    assert len(pg2.lanes) == 2 and [l.B for l in pg2.lanes] == [2, 1] and pg2.lanes[1].b_off == 2
-    assert sum(op.lane for op in pg2.ops) == pg2.lane_ops[1]
-    assert sum(1 for op in pg2.ops if op.sync & 1) == 1 and sum(1 for op in pg2.ops if op.sync & 2) == 1
-    assert sum(1 for op in pg2.ops if op.step == -2) == 1          # one shared FiLM table
-    io2 = Emulator(pm, pg2).run(mix, noise, coefs, dbg=True)
-    for b0, b1 in ((0, 2), (2, 3)):
-        pg1 = program.build_program(pm, mcfg, b1 - b0, T, n_steps, lanes=1)
-        io1 = Emulator(pm, pg1).run(mix[b0:b1], noise[:, b0:b1], coefs, dbg=True)
-        assert torch.equal(io1["out"], io2["out"][b0:b1])
-        for i in range(n_steps):
-            assert torch.equal(io1["dbg"][i], io2["dbg"][i][b0:b1])
-    assert program.default_lanes(64) == 2 and program.default_lanes(8) == 1 and program.default_lanes(64, aux=True) == 1
+    pg = program.build_program(pm, mcfg, B, 2000, 8, recycle=True)
+    plain = program.build_program(pm, mcfg, B, 2000, 8, recycle=False)
+    assert pg.arena < 0.6 * plain.arena
+    for lane in pg.lanes:
+        spans = _spans(lane)
+        assert min(s[0] for s in spans) >= max(lane.x, lane.sig) and max(s[1] for s in spans) <= lane.arena
+        for i, (a0, a1, an, ag) in enumerate(spans):
+            for b0, b1, bn, bg in spans[i + 1:]:
+                if b0 >= a1:
+                    break
+                (alo, ahi), (blo, bhi) = lane.live[an], lane.live[bn]
+                assert ahi < blo or bhi < alo, (an, bn, lane.live[an], lane.live[bn])
+                assert ag == bg, (an, bn)
+    if len(pg.lanes) == 2:   # lanes run concurrently: disjoint arenas
+        assert max(s[1] for s in _spans(pg.lanes[0])) <= min(s[0] for s in _spans(pg.lanes[1]))

@@ -162,25 +162,6 @@ def test_graph_replay_equals_eager_launches():
     assert torch.equal(a, b) and torch.equal(sa, sb)
 
 
-def test_full_size_properties_cfg2():
-    """BASELINE config 2 size (64 x 4 s, 8 steps): finite, peak-normalised, utterance-permutation
-    equivariant (size-independent properties; the oracle would need minutes here)."""
-    model, _ = _gpu_model("universepp_16k")
-    B, T = 64, 64000
-    g = torch.Generator(device="cuda").manual_seed(1)
-    mix = 0.1 * torch.randn(B, T, device="cuda", generator=g)
-    noise = torch.randn(8, B, T + 160, device="cuda", generator=g)
-    out, steps = model.enhance_debug(mix, noise)
-    assert torch.isfinite(out).all() and torch.isfinite(steps).all()
-    assert out.abs().max() <= 1.0 + 1e-6 and out.std() > 1e-4
-    perm = torch.randperm(B, device="cuda", generator=g)
-    out2, _ = model.enhance_debug(mix[perm], noise[:, perm])
-    assert torch.equal(out2, out[perm])
-    # same utterances in a smaller batch: same plan-independent result
-    out3, _ = model.enhance_debug(mix[:2], noise[:, :2])
-    assert uo.rel_l2(out3.cpu(), out[:2].cpu()) < 1e-6
-
-
 def test_two_lanes_equal_one_lane_and_oracle(monkeypatch):
     """B >= 16 is compiled as two utterance lanes on two captured streams (odd B: 9 + 8 here).  Same bits as the
     single-lane program of the whole batch (rows are computed independently of their tile / lane), and both

@@ -14,37 +14,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 from open_universe_b200 import _abi, _native, config, networks, program, testing, weights  # noqa: E402,F401
-from oracle.emulator import Emulator  # noqa: E402
-
-
-def op_outputs(op, pg):
-    """[(label, arena offset, nbytes, torch dtype)] written by `op`."""
-    outs = []
-    t = op.type
-
-    def tens(label, u):
-        es = 2 if u.dtype == _abi.DT_BF16 else 4
-        outs.append((label, u.off, u.split * u.nch * u.P * 8 * es, torch.bfloat16 if es == 2 else torch.float32))
-
-    if t in (_abi.OP_GEMM, _abi.OP_GRU, _abi.OP_CONV_IN, _abi.OP_MEL_FIN):
-        for i in range(op.n_out):
-            tens(f"out{i}", op.out[i].t)
-        if t == _abi.OP_GEMM and op.rm_out >= 0:
-            outs.append(("rm", op.rm_out, op.m_rows * op.rm_ld * 4, torch.float32))
-    elif t == _abi.OP_CONVBLOCK:
-        for i in range(op.n_out):
-            tens(f"out{i}", op.out[i].t)
-        if op.i1:
-            tens("cond", op.out[2].t)
-    elif t == _abi.OP_PREP:
-        outs += [("sig", op.p0, op.B * op.Lp * 4, torch.float32), ("rms", op.p1, op.B * 4, torch.float32)]
-    elif t == _abi.OP_MEL:
-        outs += [("mel", op.p1, op.B * op.F * op.C * 4, torch.float32), ("energy", op.p2, op.B * ((op.F + op.T - 1) // op.T) * 4, torch.float32)]
-    elif t in (_abi.OP_INIT_X, _abi.OP_CONV_OUT):
-        outs.append(("x", op.p0, op.B * op.Lp * 4, torch.float32))
-    elif t == _abi.OP_FILM:
-        outs.append(("film", op.p1, op.i0 * op.i2 * 4, torch.float32))
-    return outs
+from oracle.emulator import Emulator, op_outputs  # noqa: E402
 
 
 def main():
@@ -84,7 +54,7 @@ def main():
         em.run_op(i, io)
         plan.run_ops(i, i + 1, dmix.data_ptr(), dnoise.data_ptr(), dout.data_ptr(), ddbg.data_ptr(), coefs, False, None)
         errs = []
-        for label, off, nbytes, dt in op_outputs(op, pg):
+        for label, off, nbytes, dt in op_outputs(op):
             gbytes = plan.arena_read(off, nbytes)
             gt = torch.frombuffer(bytearray(gbytes), dtype=dt).float()
             et = em.arena[off : off + nbytes].view(dt).float()
