@@ -142,7 +142,9 @@ void uv_model_destroy(uv_model* m);
 
 /* Builds a plan: allocates + zeroes the arena, copies `init` (nbytes_init bytes)
  * to arena offset init_off, runs the ops flagged step == -2 once (plan-time
- * setup such as the FiLM table) and captures the remaining ops in a CUDA graph. */
+ * setup such as the FiLM table) and captures the remaining ops in a CUDA graph.
+ * use_graph: 0 = eager launches, 1 = capture now, 2 = capture lazily (the first uv_enhance() of the plan runs
+ * eagerly, the second captures: a shape that is used once never pays for the capture). */
 int uv_plan_create(uv_plan** out, uv_model* m, const uv_op* ops, int n_ops, size_t arena_bytes,
                    const void* init, size_t nbytes_init, size_t init_off, int n_steps, int use_graph);
 void uv_plan_destroy(uv_plan* p);

@@ -121,6 +121,7 @@ class NativePlan:
     """One (B, T, n_steps) plan: arena + captured CUDA graph."""
 
     def __init__(self, model, pg, use_graph=True):
+        """use_graph: False / 0 eager launches, True / 1 capture at creation, 2 capture at the second enhance()."""
         self.model = model  # keep alive
         self.pg = pg
         self.handle = C.c_void_p()
@@ -128,7 +129,8 @@ class NativePlan:
         arr = (_abi.UvOp * n)(*pg.ops)
         init = C.create_string_buffer(pg.init_blob, len(pg.init_blob))
         _check(lib().uv_plan_create(C.byref(self.handle), model.handle, arr, n, pg.arena, init, len(pg.init_blob),
-                                    pg.init_off, pg.n_steps, 1 if use_graph else 0), "uv_plan_create")
+                                    pg.init_off, pg.n_steps, int(use_graph)), "uv_plan_create")
+        self.arena_bytes = int(pg.arena)
         self.num_launches = lib().uv_plan_num_launches(self.handle)
 
     def _coefs(self, coefs):

@@ -7,7 +7,8 @@ structure is retained), same per-file arithmetic: a file of C channels is a batc
 (enhance.py:187-190), resampled to the model rate and back with `torchaudio.functional.resample`.
 
 What differs is the schedule.  The reference enhances one file at a time (B = #channels, a few thousand eager
-kernel launches each).  Here all utterances are gathered first, grouped into batches of IDENTICAL length (padding
+kernel launches each).  Here the files stream through in windows (decoded ahead by a thread pool, written back by
+writer threads); the utterances of a window are grouped into batches of IDENTICAL length (padding
 and the normalisation statistics depend on the length, universe.py:219-223,272, so equal-length batches leave every
 utterance's result unchanged); under `torchrun` the files are dealt whole to the ranks (one process per GPU, no
 collective: the outputs are files), and each batch is one replay of the native CUDA graph.  `--batch-size` bounds the batch.
@@ -113,47 +114,82 @@ def output_path_for(path, rel_path, dir_proc, output):
     return output / Path(path).name if output.is_dir() else output
 
 
-def enhance_files(model, files, out_paths, enhance_kwargs, batch_size=64, device=None, rank=0, world=1, progress=False):
+def enhance_files(model, files, out_paths, enhance_kwargs, batch_size=64, device=None, rank=0, world=1, progress=False,
+                  window=256, io_threads=4):
     """Enhances this rank's share of `files` into `out_paths`.  Returns a dict of counters.
     Files are dealt to ranks whole (largest first, round robin: balanced without any exchange); every channel of a
-    file is one utterance; utterances of identical (resampled) length share a batch."""
+    file is one utterance; utterances of identical (resampled) length share a batch.
+
+    The files stream through in windows of `window` files: a pool of `io_threads` threads decodes window k + 1 while
+    the device works on window k, and finished files are copied back and written by writer threads, so neither the
+    host nor the device ever holds more than about two windows and file IO overlaps the device work (the reference
+    is strictly serial: load, enhance, save, one file at a time; enhance.py:168-192).  Batches are formed inside a
+    window, in ascending length."""
+    from concurrent.futures import ThreadPoolExecutor
+
     device = device if device is not None else next(model.parameters()).device
     t0 = time.perf_counter()
     order = sorted(range(len(files)), key=lambda i: (-os.path.getsize(files[i]), str(files[i])))
     mine = [fi for k, fi in enumerate(order) if k % world == rank]
-    utts = []        # (file index, channel, tensor [T] on the device at the model rate)
-    fs_of = {}
-    for fi in mine:
-        audio, fs = load_audio(files[fi])
-        fs_of[fi] = fs
-        a = resample(audio.to(device), fs, model.fs)
-        for c in range(a.shape[0]):
-            utts.append((fi, c, a[c]))
-    batches = sharding.length_buckets([u[2].shape[-1] for u in utts], list(range(len(utts))), batch_size)
-    done = {}
-    n_audio_s = 0.0
-    it = batches
+    windows = [mine[k : k + window] for k in range(0, len(mine), window)]
+    loader = ThreadPoolExecutor(max(1, io_threads))
+    prefetch = ThreadPoolExecutor(1)   # runs load_window (which fans out over `loader`) one window ahead
+    writer = ThreadPoolExecutor(2)
+    stats = dict(files=0, utterances=0, batches=0, audio_seconds=0.0)
+
+    def load_window(w):
+        return list(loader.map(lambda fi: (fi,) + tuple(load_audio(files[fi])), w))
+
+    def write_file(path, enh, fs):
+        Path(path).parent.mkdir(exist_ok=True, parents=True)
+        save_audio(path, enh.cpu(), fs)   # the device-to-host copy waits for this file's batches only (stream order)
+
     if progress:
         from tqdm import tqdm
 
-        it = tqdm(it)
+        bar = tqdm(total=len(mine))
+    pending = []
+    nxt = prefetch.submit(load_window, windows[0]) if windows else None
     with torch.no_grad():
-        for batch in it:
-            x = torch.stack([utts[i][2] for i in batch])
-            y = model.enhance(x, **enhance_kwargs)
-            for i, yi in zip(batch, y):
-                done[i] = yi
-            n_audio_s += x.numel() / model.fs
-    by_file = {}
-    for i, (fi, c, _) in enumerate(utts):
-        by_file.setdefault(fi, []).append(i)
-    for fi, idx in by_file.items():
-        fs = fs_of[fi]
-        enh = resample(torch.stack([done[i] for i in idx]), model.fs, fs)
-        Path(out_paths[fi]).parent.mkdir(exist_ok=True, parents=True)
-        save_audio(out_paths[fi], enh.cpu(), fs)
-    return dict(files=len(by_file), utterances=len(done), batches=len(batches), audio_seconds=n_audio_s,
-                seconds=time.perf_counter() - t0)
+        for wi in range(len(windows)):
+            loaded = nxt.result()
+            nxt = prefetch.submit(load_window, windows[wi + 1]) if wi + 1 < len(windows) else None
+            utts = []        # (file index, channel, tensor [T] on the device at the model rate)
+            fs_of = {}
+            for fi, audio, fs in loaded:
+                fs_of[fi] = fs
+                a = resample(audio.to(device, non_blocking=True), fs, model.fs)
+                for c in range(a.shape[0]):
+                    utts.append((fi, c, a[c]))
+            batches = sharding.length_buckets([u[2].shape[-1] for u in utts], list(range(len(utts))), batch_size)
+            done = {}
+            for batch in batches:
+                x = torch.stack([utts[i][2] for i in batch])
+                y = model.enhance(x, **enhance_kwargs)
+                for i, yi in zip(batch, y):
+                    done[i] = yi
+                stats["audio_seconds"] += x.numel() / model.fs
+            by_file = {}
+            for i, (fi, c, _) in enumerate(utts):
+                by_file.setdefault(fi, []).append(i)
+            for fi, idx in by_file.items():
+                enh = resample(torch.stack([done[i] for i in idx]), model.fs, fs_of[fi])
+                pending.append(writer.submit(write_file, out_paths[fi], enh, fs_of[fi]))
+            stats["files"] += len(by_file)
+            stats["utterances"] += len(done)
+            stats["batches"] += len(batches)
+            if progress:
+                bar.update(len(by_file))
+            # bound what is in flight: at most the previous window's files may still be waiting for their writer
+            while len(pending) > 2 * window:
+                pending.pop(0).result()
+    for f in pending:
+        f.result()
+    prefetch.shutdown()
+    loader.shutdown()
+    writer.shutdown()
+    stats["seconds"] = time.perf_counter() - t0
+    return stats
 
 
 def main(argv=None):
@@ -170,6 +206,8 @@ def main(argv=None):
     parser.add_argument("--seed", type=int, default=1028282, help="Set a deterministic seed to get reproducible results")
     parser.add_argument("--device", type=str, default="cuda:0", help="cuda:X (there is no CPU path in this implementation)")
     parser.add_argument("--batch-size", type=int, default=64, help="Utterances of equal length enhanced together")
+    parser.add_argument("--window", type=int, default=256, help="Files decoded ahead and batched together")
+    parser.add_argument("--io-threads", type=int, default=4, help="Decoder threads")
     requires_help = handle_help()
     args, _ = parser.parse_known_args()
 
@@ -199,7 +237,7 @@ def main(argv=None):
     files, rel_path, dir_proc = find_files(args.input)
     outs = [output_path_for(p, rel_path, dir_proc, args.output) for p in files]
     stats = enhance_files(model, files, outs, enhance_kwargs, batch_size=args.batch_size, device=device, rank=rank,
-                          world=world, progress=dir_proc and rank == 0)
+                          world=world, progress=dir_proc and rank == 0, window=args.window, io_threads=args.io_threads)
     print(f"[rank {rank}] {stats['files']} files, {stats['utterances']} utterances in {stats['batches']} batches, "
           f"{stats['audio_seconds']:.1f} s of audio in {stats['seconds']:.2f} s "
           f"({stats['audio_seconds'] / max(stats['seconds'], 1e-9):.1f} audio-s/s incl. file IO and plan creation)")

@@ -77,6 +77,8 @@ struct uv_plan {
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_lane[2] = {nullptr, nullptr};
   int n_launches = 0;
   bool use_graph = false;
+  bool lazy_graph = false;        // use_graph == 2: the first uv_enhance() runs eagerly, the second captures the graph
+  long long n_calls = 0;
 };
 
 extern "C" int uv_abi_version(void) { return UV_ABI_VERSION; }
@@ -437,7 +439,7 @@ static int plan_build(uv_plan* p, const void* init, size_t nbytes_init, size_t i
   for (int i = 0; i < n_ops; ++i)
     if (p->ops[i].step == -2 && (rc = launch_op(p, i, 0))) return rc;
   CUDA_TRY(cudaDeviceSynchronize());
-  if (p->use_graph && (rc = capture_program(p))) return rc;
+  if (p->use_graph && !p->lazy_graph && (rc = capture_program(p))) return rc;
   return UV_OK;
 }
 
@@ -451,6 +453,7 @@ extern "C" int uv_plan_create(uv_plan** out, uv_model* m, const uv_op* ops, int 
   p->arena_bytes = arena_bytes;
   p->n_steps = n_steps;
   p->use_graph = use_graph != 0;
+  p->lazy_graph = use_graph == 2;
   const int rc = plan_build(p, init, nbytes_init, init_off);
   if (rc) {   // every early return above lands here: nothing of a half-built plan is leaked
     const std::string msg = g_err;
@@ -529,6 +532,17 @@ extern "C" int uv_enhance(uv_plan* p, const float* mix, const float* noise, floa
   std::lock_guard<std::mutex> lock(p->mu);
   int rc = stage_io(p, mix, noise, out, dbg_net, coef, keep_rms, s);
   if (rc) return rc;
+  const long long call = p->n_calls++;
+  if (p->use_graph && !p->exec) {
+    // lazy capture: a shape that is used once (a corpus where every file has its own length) never pays for the
+    // capture + instantiation of several hundred kernel nodes; the first call runs the same two-lane schedule eagerly
+    if (call == 0) {
+      const bool two = has_two_lanes(p);
+      if ((rc = ensure_lane_objects(p, two))) return rc;
+      return enqueue_lanes(p, s, p->lane_stream, two, nullptr);
+    }
+    if ((rc = capture_program(p))) return rc;
+  }
   if (p->use_graph) {
     cudaError_t e = cudaGraphLaunch(p->exec, s);
     if (e != cudaSuccess) {

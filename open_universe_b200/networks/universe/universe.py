@@ -6,9 +6,11 @@ They keep the reference's constructor signature, state-dict layout, EMA handling
 into a packed blob + op program (weights.py, program.py) and replays one CUDA graph of
 hand-written sm_100a kernels through the C ABI (_native.py).
 """
+import collections
 import itertools
 import logging
 import math
+import os
 from typing import Optional
 
 import torch
@@ -62,8 +64,13 @@ class Universe(torch.nn.Module):
 
         self._packed = None      # weights.PackedModel
         self._native_model = None
-        self._plans = {}
+        self._plans = collections.OrderedDict()
         self.use_cuda_graph = True
+        # plan cache: least recently used plans are closed (arena, graph) when the cache holds more than
+        # plan_cache_bytes of arenas or plan_cache_max plans (a directory of files of many lengths must not run the
+        # device out of memory); the graph of a plan is captured at its second use
+        self.plan_cache_bytes = int(float(os.environ.get("UV_PLAN_CACHE_GB", "48")) * 2**30)
+        self.plan_cache_max = int(os.environ.get("UV_PLAN_CACHE_MAX", "32"))
 
     # ------------------------------------------------------------------ reference API surface
     def init_losses(self, score_model, condition_model, losses, training):
@@ -143,7 +150,7 @@ class Universe(torch.nn.Module):
     def _invalidate(self):
         for p in getattr(self, "_plans", {}).values():
             p.close()
-        self._plans = {}
+        self._plans = collections.OrderedDict()
         if getattr(self, "_native_model", None) is not None:
             self._native_model.close()
         self._native_model = None
@@ -164,10 +171,21 @@ class Universe(torch.nn.Module):
             self._packed = weights.pack_model(sd, self.model_config())
             self._native_model = _native.NativeModel(self._packed.blob.bytes(), dev.index or 0)
         key = (B, T, n_steps, aux)
-        if key not in self._plans:
-            pg = program.build_program(self._packed, self.model_config(), B, T, n_steps, aux=aux)
-            self._plans[key] = _native.NativePlan(self._native_model, pg, use_graph=self.use_cuda_graph)
-        return self._plans[key]
+        plan = self._plans.get(key)
+        if plan is not None:
+            self._plans.move_to_end(key)
+            return plan
+        pg = program.build_program(self._packed, self.model_config(), B, T, n_steps, aux=aux)
+        # make room first: the new arena must fit next to the ones that stay
+        held = sum(p.arena_bytes for p in self._plans.values())
+        while self._plans and (held + pg.arena > self.plan_cache_bytes or len(self._plans) >= self.plan_cache_max):
+            _, old = self._plans.popitem(last=False)
+            held -= old.arena_bytes
+            old.close()
+        with torch.cuda.device(dev):
+            plan = _native.NativePlan(self._native_model, pg, use_graph=2 if self.use_cuda_graph else 0)
+        self._plans[key] = plan
+        return plan
 
     # ------------------------------------------------------------------ enhance (reference universe.py:231-375)
     def enhance(

@@ -768,11 +768,14 @@ def algorithmic_flops(cfg, Lp, n_steps):
     edge = 2 * 3 * c0 * Lp  # 1 -> C or C -> 1, k = 3
     # score network, one evaluation
     s_gemm = 0
+    sc = 0   # signal_cond_proj 1x1 convs: step invariant, the program evaluates them once (hoisted)
     for i in range(nlev):
         s_gemm += 2 * (block(chans[i], lens[i]) + rc(chans[i], lens[i]))  # encoder + decoder block at this level
-        s_gemm += 2 * chans[i] * chans[i] * lens[i]                      # signal_cond_proj 1x1
+        sc += 2 * chans[i] * chans[i] * lens[i]
     if extra:
-        s_gemm += 2 * block(Cb, Fr) + 2 * Cb * Cb * Fr
+        s_gemm += 2 * block(Cb, Fr)
+        sc += 2 * Cb * Cb * Fr
+    s_gemm += sc
     s_gemm += gru_ih
     score = s_gemm + gru_hh + 2 * edge
     # conditioner
@@ -787,5 +790,7 @@ def algorithmic_flops(cfg, Lp, n_steps):
     c_gemm += 2 * gru_ih
     cond = c_gemm + 2 * gru_hh + edge
     # the hoisted 1x1 projections run once, not per step; algorithmic count keeps the reference's per-step figure
+    # gemm_executed / total_executed: the same count without the n_steps - 1 repeats of the hoisted projections
     return dict(cond=cond, score=score, total=cond + n_steps * score, gemm=c_gemm + n_steps * s_gemm,
-                gru_hh=(2 + n_steps) * gru_hh)
+                gru_hh=(2 + n_steps) * gru_hh, gemm_executed=c_gemm + n_steps * s_gemm - (n_steps - 1) * sc,
+                total_executed=cond + n_steps * score - (n_steps - 1) * sc)

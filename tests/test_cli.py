@@ -141,3 +141,55 @@ def test_cli_end_to_end_equals_direct_enhance_calls(tmp_path):
     assert torch.allclose(got["s/c.wav"], ref_c.cpu(), atol=1e-6)
     assert torch.allclose(got["a.wav"], ref_ab[0:1].cpu(), atol=1e-6)
     assert torch.allclose(got["s/b.wav"], ref_ab[1:2].cpu(), atol=1e-6)
+
+
+def test_windows_stream_every_file_once_with_bounded_batches(tmp_path):
+    """The streaming schedule (windows decoded ahead, writer threads): every file written exactly once, batches never
+    mix lengths or cross a window, results independent of the window size."""
+    src = tmp_path / "noisy"
+    specs = [(f"f{k:03d}.wav", 16000, 1, 2000 + 100 * (k % 7), "float32") for k in range(37)]
+    files = _write_wavs(src, specs)
+    for window in (5, 64):
+        outs = [tmp_path / f"out{window}" / p.name for p in files]
+        model = _HalfModel()
+        st = cli.enhance_files(model, files, outs, {}, batch_size=4, device="cpu", window=window, io_threads=3)
+        assert st["files"] == 37 and st["utterances"] == 37
+        assert all(B <= 4 for B, T in model.batches)
+        assert sum(B for B, T in model.batches) == 37
+        for p, o in zip(files, outs):
+            assert torch.allclose(cli.load_audio(o)[0], 0.5 * cli.load_audio(p)[0], atol=1e-6)
+
+
+@pytest.mark.gpu
+def test_cli_300_files_of_300_distinct_lengths(tmp_path):
+    """A corpus where every file has its own length (the reference loops file by file, enhance.py:168-192): one plan
+    per length goes through the bounded plan cache without running out of memory, and every output equals the direct
+    one-by-one model.enhance call with the same generator state."""
+    model, cfg = build_model("universepp_16k")
+    d = tmp_path / "exp" / "checkpoints"
+    d.mkdir(parents=True)
+    torch.save({"state_dict": {k: v.clone() for k, v in model.state_dict().items()}}, d / "last.ckpt")
+    (tmp_path / "exp" / ".hydra").mkdir()
+    with open(tmp_path / "exp" / ".hydra" / "config.yaml", "w") as f:
+        yaml.safe_dump(json.loads(json.dumps(cfg)), f)
+    src = tmp_path / "noisy"
+    specs = [(f"d{k % 5}/f{k:03d}.wav", 16000, 1, 1600 + 53 * k, "float32") for k in range(300)]
+    files = _write_wavs(src, specs)
+    out = tmp_path / "enh"
+    st = cli.main([str(src), str(out), "--model", str(d / "last.ckpt"), "--seed", "9", "--n_steps", "2", "--batch-size", "8",
+                   "--window", "64"])
+    assert st["files"] == 300 and st["batches"] == 300
+    gm = model.to("cuda").eval()
+    rng = torch.Generator(device="cuda").manual_seed(9)
+    found, _, _ = cli.find_files(src)
+    order = sorted(range(len(found)), key=lambda i: (-os.path.getsize(found[i]), str(found[i])))
+    worst = 0.0
+    for w0 in range(0, 300, 64):
+        win = order[w0 : w0 + 64]
+        for fi in sorted(win, key=lambda i: os.path.getsize(found[i])):   # batches of a window in ascending length
+            x = cli.load_audio(found[fi])[0].cuda()
+            ref = gm.enhance(x, n_steps=2, rng=rng).cpu()
+            got = cli.load_audio(out / found[fi].relative_to(src))[0]
+            worst = max(worst, (got - ref).abs().max().item())
+    assert len(gm._plans) <= gm.plan_cache_max
+    assert worst < 1e-6, worst

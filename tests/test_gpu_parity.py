@@ -155,11 +155,37 @@ def test_graph_replay_equals_eager_launches():
     g = torch.Generator().manual_seed(9)
     mix = 0.05 * torch.randn(2, 2500, generator=g).cuda()
     noise = torch.randn(8, 2, 2560, generator=g).cuda()
-    a, sa = model.enhance_debug(mix, noise)
+    a0, sa0 = model.enhance_debug(mix, noise)   # first use of a plan: eager launches (the graph is captured lazily)
+    a, sa = model.enhance_debug(mix, noise)     # second use: captured + replayed
+    a2, sa2 = model.enhance_debug(mix, noise)   # replay
+    assert torch.equal(a0, a) and torch.equal(sa0, sa) and torch.equal(a2, a) and torch.equal(sa2, sa)
     model._invalidate()
     model.use_cuda_graph = False
     b, sb = model.enhance_debug(mix, noise)
     assert torch.equal(a, b) and torch.equal(sa, sb)
+
+
+def test_plan_cache_is_bounded_and_evicted_shapes_reproduce():
+    """Many distinct lengths (every file of a real corpus has its own): the cache keeps at most plan_cache_max plans /
+    plan_cache_bytes of arenas, closes the least recently used ones, and a shape that was evicted gives the same
+    bits when it comes back."""
+    model, _ = _gpu_model("universepp_16k")
+    model.plan_cache_max = 4
+    g = torch.Generator().manual_seed(21)
+    first = {}
+    lengths = [1600 + 37 * k for k in range(12)]
+    for T in lengths + lengths[:3]:
+        mix = 0.05 * torch.randn(1, T, generator=torch.Generator().manual_seed(T)).cuda()
+        noise = torch.randn(8, 1, T + (160 - T % 160), generator=torch.Generator().manual_seed(T + 1)).cuda()
+        out, _ = model.enhance_debug(mix, noise)
+        assert len(model._plans) <= 4
+        if T in first:
+            assert torch.equal(out, first[T])
+        first[T] = out
+    model.plan_cache_bytes = 1   # a budget below one arena: only the plan in use survives
+    model.enhance_debug(mix, noise)
+    model.enhance_debug(0.05 * torch.randn(1, 1600, generator=g).cuda(), torch.randn(8, 1, 1760, generator=g).cuda())
+    assert len(model._plans) == 1
 
 
 def test_two_lanes_equal_one_lane_and_oracle(monkeypatch):

@@ -110,3 +110,17 @@ def test_enhance_fails_loudly_without_gpu_and_validates_input():
         model.enhance(torch.zeros(1, 1600))
     with pytest.raises(RuntimeError):
         model.get_score_model()(None, None, None)
+
+
+def test_reference_import_paths_resolve_to_this_package():
+    """`from open_universe import inference_utils` (reference README.md:27-49) and the `_target_` paths of the model
+    configs resolve through the alias package to the very same module objects."""
+    import open_universe
+    import open_universe_b200
+    from open_universe import inference_utils
+    from open_universe.networks.universe import Universe, UniverseGAN
+
+    assert inference_utils is open_universe_b200.inference_utils
+    assert UniverseGAN is open_universe_b200.networks.universe.UniverseGAN and Universe is open_universe_b200.networks.universe.Universe
+    assert hasattr(inference_utils, "load_model") and hasattr(inference_utils, "add_enhance_arguments")
+    assert open_universe.networks is open_universe_b200.networks

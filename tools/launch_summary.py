@@ -4,13 +4,17 @@ per-launch DRAM traffic of the dominant kernel for bench.py's roofline.traffic f
 Usage: python tools/launch_summary.py gpurun_out/launches.csv [--json profiles/roofline_traffic.json]"""
 import collections
 import csv
+import gzip
 import json
+import os
 import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 
 def main():
     path = sys.argv[1]
-    rows = list(csv.reader(open(path)))
+    rows = list(csv.reader(gzip.open(path, "rt") if path.endswith(".gz") else open(path)))
     hi = [i for i, r in enumerate(rows) if r and r[0] == "ID"][0]
     hdr, data = rows[hi], rows[hi + 1:]
     ci = {h: i for i, h in enumerate(hdr)}
@@ -40,7 +44,9 @@ def main():
     if "--json" in sys.argv:
         out = sys.argv[sys.argv.index("--json") + 1]
         a = agg[top]
-        json.dump({"kernel": top.split("::")[-1], "launches": cnt[top],
+        import bench   # the build the pass was taken on: bench.py quotes the figure only for the same sources
+
+        json.dump({"kernel": top.split("::")[-1], "launches": cnt[top], "build": bench.source_hash(),
                    "traffic_bytes_per_launch": (a["dram__bytes_read.sum"] + a["dram__bytes_write.sum"]) / cnt[top],
                    "share_of_kernel_time_under_ncu": a["ns"] / tot, "source": path}, open(out, "w"), indent=1)
 
