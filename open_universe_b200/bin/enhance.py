@@ -115,7 +115,7 @@ def output_path_for(path, rel_path, dir_proc, output):
 
 
 def enhance_files(model, files, out_paths, enhance_kwargs, batch_size=64, device=None, rank=0, world=1, progress=False,
-                  window=256, io_threads=4):
+                  window=None, io_threads=4):
     """Enhances this rank's share of `files` into `out_paths`.  Returns a dict of counters.
     Files are dealt to ranks whole (largest first, round robin: balanced without any exchange); every channel of a
     file is one utterance; utterances of identical (resampled) length share a batch.
@@ -128,13 +128,15 @@ def enhance_files(model, files, out_paths, enhance_kwargs, batch_size=64, device
     from concurrent.futures import ThreadPoolExecutor
 
     device = device if device is not None else next(model.parameters()).device
+    if window is None:
+        window = max(64, batch_size)   # small enough that decoding window k + 1 overlaps the device work on window k
     t0 = time.perf_counter()
     order = sorted(range(len(files)), key=lambda i: (-os.path.getsize(files[i]), str(files[i])))
     mine = [fi for k, fi in enumerate(order) if k % world == rank]
     windows = [mine[k : k + window] for k in range(0, len(mine), window)]
     loader = ThreadPoolExecutor(max(1, io_threads))
     prefetch = ThreadPoolExecutor(1)   # runs load_window (which fans out over `loader`) one window ahead
-    writer = ThreadPoolExecutor(2)
+    writer = ThreadPoolExecutor(max(2, io_threads))
     stats = dict(files=0, utterances=0, batches=0, audio_seconds=0.0)
 
     def load_window(w):
@@ -206,7 +208,7 @@ def main(argv=None):
     parser.add_argument("--seed", type=int, default=1028282, help="Set a deterministic seed to get reproducible results")
     parser.add_argument("--device", type=str, default="cuda:0", help="cuda:X (there is no CPU path in this implementation)")
     parser.add_argument("--batch-size", type=int, default=64, help="Utterances of equal length enhanced together")
-    parser.add_argument("--window", type=int, default=256, help="Files decoded ahead and batched together")
+    parser.add_argument("--window", type=int, default=None, help="Files decoded ahead and batched together (default: max(64, batch size))")
     parser.add_argument("--io-threads", type=int, default=4, help="Decoder threads")
     requires_help = handle_help()
     args, _ = parser.parse_known_args()

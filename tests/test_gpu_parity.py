@@ -183,8 +183,7 @@ def test_plan_cache_is_bounded_and_evicted_shapes_reproduce():
             assert torch.equal(out, first[T])
         first[T] = out
     model.plan_cache_bytes = 1   # a budget below one arena: only the plan in use survives
-    model.enhance_debug(mix, noise)
-    model.enhance_debug(0.05 * torch.randn(1, 1600, generator=g).cuda(), torch.randn(8, 1, 1760, generator=g).cuda())
+    model.enhance_debug(0.05 * torch.randn(1, 2500, generator=g).cuda(), torch.randn(8, 1, 2560, generator=g).cuda())
     assert len(model._plans) == 1
 
 
