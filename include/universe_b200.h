@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define UV_ABI_VERSION 6
+#define UV_ABI_VERSION 7
 
 typedef enum {
   UV_OK = 0,
@@ -184,6 +184,29 @@ int uv_trace_ops(uv_plan* p, const float* mix, const float* noise, float* out, f
 
 /* Number of kernel launches one uv_enhance() replays (for bench accounting). */
 int uv_plan_num_launches(const uv_plan* p);
+
+/* ---- allocation-free entry point -------------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).
+ *
+ * The conditioner's mel front end (MelAdapter.compute_mel_spec: power mel spectrogram, then division by
+ * sqrt(mean_t sum_m S^2)) on a padded, normalised signal, with the scratch the two kernels exchange (raw mel
+ * bands + partial energy sums: (B * F * n_mels + B * ceil(F / 32)) floats, F = Lp / hop) in a file-scope static
+ * device array of UV_STATIC_SCRATCH_BYTES.  Every GPU that loads the library holds that array until exit.
+ * The call allocates nothing (no cudaMalloc / cudaFree / allocating library routine); a problem whose scratch
+ * exceeds the array is rejected with UV_ERR_INVALID.  Nothing in the array has to start at zero (both regions are
+ * rewritten in full by every call), but ALL calls on a device share it: calls that overlap on the GPU (different
+ * streams, or a second call before the first has finished on another stream) race; serialise them.
+ * sig: device f32 [B][Lp] (Lp a multiple of hop), mel_out: device f32 [B][n_mels][Lp / hop]; weights come from
+ * the model blob (offsets as in the packed layer "c.mel").                                                  */
+#define UV_STATIC_SCRATCH_BYTES (16u << 20)
+typedef struct {
+  int32_t n_fft, hop, n_bins, nbp; /* window length, hop, n_fft / 2 + 1, bins padded to a multiple of 32 */
+  int32_t n_mels, pad_;
+  int64_t basis_w;                 /* model blob: f32 [n_fft][2 * nbp] windowed DFT basis (cos | sin)   */
+  int64_t fb_w;                    /* model blob: f32 [n_bins][n_mels] mel filterbank                   */
+} uv_mel_desc;
+int uv_mel_spec_static(uv_model* m, const uv_mel_desc* d, const float* sig, int B, int Lp, float* mel_out, void* stream);
 
 #ifdef __cplusplus
 }

@@ -2,7 +2,7 @@
 lives in `_native.py`)."""
 import ctypes as C
 
-UV_ABI_VERSION = 6
+UV_ABI_VERSION = 7
 
 OP_PREP, OP_MEL, OP_MEL_FIN, OP_CONV_IN, OP_GEMM, OP_GRU, OP_CONV_OUT, OP_INIT_X, OP_POST, OP_FILM, OP_CONVBLOCK = range(1, 12)
 OP_NAMES = {
@@ -80,6 +80,14 @@ class UvOp(C.Structure):
         ("a_act", C.c_int32),
         ("a_slope", C.c_float),
     ]
+
+
+class UvMelDesc(C.Structure):
+    _fields_ = [("n_fft", C.c_int32), ("hop", C.c_int32), ("n_bins", C.c_int32), ("nbp", C.c_int32), ("n_mels", C.c_int32),
+                ("pad_", C.c_int32), ("basis_w", C.c_int64), ("fb_w", C.c_int64)]
+
+
+UV_STATIC_SCRATCH_BYTES = 16 << 20
 
 
 class UvStepCoef(C.Structure):

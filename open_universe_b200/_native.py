@@ -19,6 +19,7 @@ EXPORTS = [
     "uv_abi_version", "uv_sizeof_op", "uv_last_error", "uv_model_create", "uv_model_destroy", "uv_plan_create",
     "uv_plan_destroy", "uv_plan_arena_bytes", "uv_enhance", "uv_run_ops", "uv_arena_read", "uv_arena_write",
     "uv_plan_num_launches", "uv_profile_ops", "uv_plan_arena_ptr", "uv_trace_ops", "uv_plan_status",
+    "uv_mel_spec_static",
 ]
 
 
@@ -81,6 +82,7 @@ def lib():
     L.uv_arena_read.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
     L.uv_arena_write.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
     L.uv_plan_status.argtypes = [C.c_void_p, C.c_void_p]
+    L.uv_mel_spec_static.argtypes = [C.c_void_p, C.POINTER(_abi.UvMelDesc), C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
     L.uv_plan_arena_ptr.argtypes = [C.c_void_p]
     L.uv_plan_arena_ptr.restype = C.c_void_p
     if L.uv_abi_version() != _abi.UV_ABI_VERSION:
@@ -104,6 +106,13 @@ class NativeModel:
         self.device_index = device_index
         buf = C.create_string_buffer(blob_bytes, len(blob_bytes))
         _check(lib().uv_model_create(C.byref(self.handle), buf, len(blob_bytes), device_index), "uv_model_create")
+
+    def mel_spec_static(self, mel_layer, sig_ptr, B, Lp, out_ptr, stream_ptr=None):
+        """Allocation-free mel front end (uv_mel_spec_static); `mel_layer` = the packed layer record "c.mel".
+        Returns the status code (0 = ok) instead of raising, so that callers can test the rejection path."""
+        d = _abi.UvMelDesc(mel_layer["n_fft"], mel_layer["hop"], mel_layer["n_bins"], mel_layer["nbp"], mel_layer["n_mels"], 0,
+                           mel_layer["basis_w"], mel_layer["fb_w"])
+        return lib().uv_mel_spec_static(self.handle, C.byref(d), sig_ptr, B, Lp, out_ptr, stream_ptr)
 
     def close(self):
         if self.handle:

@@ -649,3 +649,82 @@ extern "C" int uv_arena_write(uv_plan* p, size_t off, const void* host_src, size
   CUDA_TRY(cudaMemcpy(p->arena + off, host_src, nbytes, cudaMemcpyHostToDevice));
   return UV_OK;
 }
+
+// ------------------------------------------------------------------ allocation-free mel front end
+// uv_mel_spec_static (include/universe_b200.h): the mel front end of the conditioner for callers that cannot
+// allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the
+// reference.  The scratch the two kernels exchange (raw mel bands,
+// partial energy sums) lives in a file-scope device array of UV_STATIC_SCRATCH_BYTES that every GPU which loads
+// the library holds until exit.  In host code `g_static_scratch` is only a stand-in for the symbol: the device
+// address is fetched with cudaGetSymbolAddress once per device, with that device current, and handed to the kernels.
+static __device__ __align__(256) float g_static_scratch[UV_STATIC_SCRATCH_BYTES / sizeof(float)];
+
+static std::mutex g_static_mu;
+static float* g_static_ptr[64] = {nullptr};   // per device
+
+static int static_scratch_ptr(int device, float** out) {
+  if (device < 0 || device >= 64) return fail(UV_ERR_INVALID, "uv_mel_spec_static: device index out of range");
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (!g_static_ptr[device]) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);   // the current device is `device` (DeviceGuard of the caller)
+    if (e != cudaSuccess || !p)
+      return fail(UV_ERR_CUDA, std::string("cudaGetSymbolAddress(g_static_scratch): ") + cudaGetErrorString(e));
+    g_static_ptr[device] = static_cast<float*>(p);
+  }
+  *out = g_static_ptr[device];
+  return UV_OK;
+}
+
+// Variant of mel_fin_kernel: same normalisation (condition.py:105-106), plain f32 output [B][n_mels][F] instead of
+// bf16 planes.  One thread per (band, frame), frame fastest: coalesced stores.
+__global__ void __launch_bounds__(256) mel_fin_plain_kernel(const float* __restrict__ melraw, const float* __restrict__ energy,
+                                                            int F, int n_mels, int nft, float* __restrict__ out) {
+  __shared__ float s_inv;
+  const int b = blockIdx.y;
+  if (threadIdx.x == 0) {
+    float e = 0.f;
+    for (int i = 0; i < nft; ++i) e += energy[(size_t)b * nft + i];
+    s_inv = 1.f / fmaxf(sqrtf(e / (float)F), 1e-5f);
+  }
+  __syncthreads();
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= F * n_mels) return;
+  const int m = idx / F, f = idx - m * F;
+  out[((size_t)b * n_mels + m) * F + f] = melraw[((size_t)b * F + f) * n_mels + m] * s_inv;
+}
+
+extern "C" int uv_mel_spec_static(uv_model* m, const uv_mel_desc* d, const float* sig, int B, int Lp, float* mel_out,
+                                  void* stream) {
+  if (!m || !d || !sig || !mel_out) return fail(UV_ERR_INVALID, "uv_mel_spec_static: null argument");
+  if (B <= 0 || Lp <= 0 || d->hop <= 0 || Lp % d->hop) return fail(UV_ERR_INVALID, "uv_mel_spec_static: Lp must be a positive multiple of hop");
+  const int F = Lp / d->hop;
+  const int nft = (F + kMelFT - 1) / kMelFT;
+  const int threads = (d->n_bins + 31) / 32 * 32;
+  const size_t sm = ((size_t)(kMelFT - 1) * d->hop + d->n_fft + 4 + (size_t)kMelPwPitch * d->n_bins) * sizeof(float);
+  if (threads > 512 || sm > (size_t)kMelMaxSmem || d->n_fft % 4 || d->hop % 4 || d->n_mels > threads || d->n_mels <= 0 ||
+      d->nbp < d->n_bins || 2 * kMelFbRows * d->n_mels > (kMelFT - 1) * d->hop + d->n_fft)
+    return fail(UV_ERR_INVALID, "uv_mel_spec_static: n_fft / hop / n_mels unsupported");
+  const size_t need = ((size_t)B * F * d->n_mels + (size_t)B * nft) * sizeof(float);
+  if (need > (size_t)UV_STATIC_SCRATCH_BYTES)
+    return fail(UV_ERR_INVALID, "uv_mel_spec_static: B x frames x n_mels needs " + std::to_string(need) +
+                                    " bytes of scratch, the static array holds " + std::to_string((size_t)UV_STATIC_SCRATCH_BYTES));
+  const size_t basis_bytes = (size_t)d->n_fft * 2 * d->nbp * 4, fb_bytes = (size_t)d->n_bins * d->n_mels * 4;
+  if (d->basis_w < 0 || d->fb_w < 0 || (size_t)d->basis_w + basis_bytes > m->nbytes || (size_t)d->fb_w + fb_bytes > m->nbytes)
+    return fail(UV_ERR_INVALID, "uv_mel_spec_static: weight offsets outside the model blob");
+  DeviceGuard guard(m->device);
+  float* scratch = nullptr;
+  int rc = static_scratch_ptr(m->device, &scratch);
+  if (rc) return rc;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  float* melraw = scratch;                                  // [B][F][n_mels], fully rewritten by every call
+  float* energy = scratch + (size_t)B * F * d->n_mels;      // [B][nft], fully rewritten by every call
+  mel_kernel<<<dim3(nft, B), dim3(threads), sm, s>>>(sig, Lp, F, d->n_fft, d->hop, d->n_bins, d->nbp, d->n_mels,
+                                                     (d->n_fft - d->hop) / 2,
+                                                     reinterpret_cast<const float*>(m->blob + d->basis_w),
+                                                     reinterpret_cast<const float*>(m->blob + d->fb_w), melraw, energy, nft);
+  CUDA_TRY(cudaGetLastError());
+  mel_fin_plain_kernel<<<dim3((F * d->n_mels + 255) / 256, B), dim3(256), 0, s>>>(melraw, energy, F, d->n_mels, nft, mel_out);
+  CUDA_TRY(cudaGetLastError());
+  return UV_OK;
+}
