@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define UV_ABI_VERSION 7
+#define UV_ABI_VERSION 8
 
 typedef enum {
   UV_OK = 0,
@@ -77,11 +77,12 @@ typedef enum {
   UV_OP_INIT_X = 8,   /* x = sigma_0 * z_0               (universe.py:326)                            */
   UV_OP_POST = 9,     /* crop, keep_rms, peak normalise  (universe.py:349-357)                        */
   UV_OP_FILM = 10,    /* noise-level embedding + FiLM table (sigma_block.py, score.py:109,208)        */
-  UV_OP_CONVBLOCK = 11 /* fused conv1 -> conv2 -> conv3 + residual of a ConvBlock with C <= 64 (blocks.py:387-403):
-                        * a = h_act, w_w / p0 / p1 = the three convs' weight images (i0 bit s = conv s has a bias),
-                        * add1 = condition (f0 = scale after the add), film, f1 / f2 = PReLU slopes in front of
-                        * conv2 / conv3, add2 = h (residual), scale, out[0..n_out) = block outputs,
-                        * i1 = 1: out[2] is the stage-1 output (the decoder's conditioning signal)            */
+  UV_OP_CONVBLOCK = 11 /* fused ConvBlock of a 64-column level (C = 64, or C = 32 stored phase-split by 2): PReLU -> conv1 ->
+                        * [+cond] * f0 -> [FiLM] -> PReLU -> conv2 -> PReLU -> conv3 -> (. + x) * scale  (blocks.py:387-403).
+                        * a = x (raw), a_slope = slope in front of conv1, w_w / p0 / p1 = the three convs' packed weights
+                        * (i0 bit s: conv s has a bias; i1 byte s: n_src | n_shift << 4 of conv s), add1 = condition,
+                        * film (C = its channel count), f1 / f2 = slopes in front of conv2 / conv3, out[0..n_out) = block
+                        * outputs, i2 = 1: out[2] is the stage-1 output (the conditioner's conditioning signal)          */
 } uv_op_type;
 
 /* One record per kernel launch.  Offsets named *_w index the model's weight

@@ -2,7 +2,7 @@
 lives in `_native.py`)."""
 import ctypes as C
 
-UV_ABI_VERSION = 7
+UV_ABI_VERSION = 8
 
 OP_PREP, OP_MEL, OP_MEL_FIN, OP_CONV_IN, OP_GEMM, OP_GRU, OP_CONV_OUT, OP_INIT_X, OP_POST, OP_FILM, OP_CONVBLOCK = range(1, 12)
 OP_NAMES = {

@@ -10,7 +10,7 @@
 #include "../../include/universe_b200.h"
 #include "gemm_tc.cuh"
 #include "gru.cuh"
-#include "convblock.cuh"
+#include "convblock_pair.cuh"
 #include "small_ops.cuh"
 
 using namespace uv;
@@ -95,7 +95,7 @@ extern "C" int uv_model_create(uv_model** out, const void* weights, size_t nbyte
   DeviceGuard guard(device);
   // function attributes are per device: every model (= device) sets them, no process-wide "done" flags
   CUDA_TRY(gemm_set_attributes());
-  CUDA_TRY(convblock_set_attributes());
+  CUDA_TRY(convblock_pair_set_attributes());
   CUDA_TRY(cudaFuncSetAttribute(gru_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   CUDA_TRY(cudaFuncSetAttribute(mel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMelMaxSmem));
   char* blob = nullptr;
@@ -180,32 +180,45 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
       break;
     }
     case UV_OP_CONVBLOCK: {
+      // every tensor of the block as 8 chunk planes of 64 "channels": a plain 64-channel tensor, or 32 channels stored
+      // phase-split by 2 in this row space (the space-to-depth form of the finest level)
+      auto as64 = [](TensDesc d) {
+        if (d.base && d.split == 2 && d.nchunks == 4) { d.split = 1; d.nchunks = 8; }
+        return d;
+      };
       CbParams c;
       memset(&c, 0, sizeof(c));
-      if (op.a.split != 1 || op.a.dtype != 1) return fail(UV_ERR_INVALID, "fused ConvBlock input must be a plain bf16 tensor");
-      c.x_base = p->arena + op.a.off; c.x_P = op.a.P; c.x_G = op.a.G;
-      c.C = op.C;
+      const TensDesc x = as64(to_desc(p, op.a));
+      if (!x.base || x.split != 1 || x.nchunks != kCbPlanes || x.esize_log2 != 1 || !op.a_act)
+        return fail(UV_ERR_INVALID, "fused ConvBlock: input must be a raw 64-column bf16 tensor");
+      c.x_base = x.base; c.x_P = x.P; c.x_G = x.G;
+      c.a_slope = op.a_slope;
       c.w[0] = wptr<const char>(p, op.w_w); c.w[1] = wptr<const char>(p, op.p0); c.w[2] = wptr<const char>(p, op.p1);
-      for (int k = 0; k < 3; ++k) c.has_bias[k] = (op.i0 >> k) & 1;
+      for (int k = 0; k < 3; ++k) {
+        c.has_bias[k] = (op.i0 >> k) & 1;
+        c.n_src[k] = (op.i1 >> (8 * k)) & 15;
+        c.n_shift[k] = (op.i1 >> (8 * k + 4)) & 15;
+      }
       c.m_rows = op.m_rows; c.Lh = op.Lh_A; c.M_valid = op.M_valid;
-      c.n_tiles = (op.m_rows + kCbRowsOut - 1) / kCbRowsOut;
-      c.cond = to_desc(p, op.add1); c.scale1 = op.f0;
-      c.film = aptr<const float>(p, op.film);
-      c.slope2 = op.f1; c.slope3 = op.f2;
-      c.h_raw = to_desc(p, op.add2); c.scale3 = op.scale;
+      c.cond = as64(to_desc(p, op.add1)); c.scale1 = op.f0;
+      if (c.cond.base && (c.cond.split != 1 || c.cond.nchunks != kCbPlanes || c.cond.esize_log2 != 1 || c.cond.Lh != x.Lh))
+        return fail(UV_ERR_INVALID, "fused ConvBlock: condition must be a 64-column bf16 tensor of the block's geometry");
+      c.film = aptr<const float>(p, op.film); c.film_C = op.C;
+      c.slope2 = op.f1; c.slope3 = op.f2; c.scale3 = op.scale;
       c.n_out = op.n_out;
-      for (int i = 0; i < 3; ++i) c.out[i] = to_out(p, op.out[i]);
-      memset(&c.cond_out, 0, sizeof(c.cond_out));
-      if (op.i1) {
+      for (int i = 0; i < 3; ++i) { c.out[i] = to_out(p, op.out[i]); c.out[i].t = as64(c.out[i].t); }
+      if (op.i2) {
         if (op.n_out > 2) return fail(UV_ERR_INVALID, "fused ConvBlock: at most two block outputs next to a stage-1 output");
-        c.cond_out = to_out(p, op.out[2]);
+        c.cond_out = c.out[2];
         memset(&c.out[2], 0, sizeof(c.out[2]));
       }
-      if ((c.cond.base && (c.cond.split != 1 || c.cond.esize_log2 != 1)) || (c.h_raw.base && (c.h_raw.split != 1 || c.h_raw.esize_log2 != 1)))
-        return fail(UV_ERR_INVALID, "fused ConvBlock: condition / residual must be plain bf16 tensors");
-      if (!cb_plan(c)) return fail(UV_ERR_INVALID, "fused ConvBlock: unsupported channel count");
+      for (int i = 0; i < 3; ++i)
+        if (c.out[i].t.base && c.out[i].t.nchunks != kCbPlanes) return fail(UV_ERR_INVALID, "fused ConvBlock: outputs must have 64 columns");
+      c.reverse = op.i3 & 1;
       c.err_flag = p->err_flag;
-      CUDA_TRY(convblock_launch(c, p->model->num_sms, s));
+      c.sched = p->sched + 2 * op_index;
+      if (!cb_params_ok(c)) return fail(UV_ERR_INVALID, "fused ConvBlock: unsupported stage geometry");
+      CUDA_TRY(convblock_pair_launch(c, p->model->num_sms, s));
       break;
     }
     case UV_OP_PREP:
@@ -323,7 +336,8 @@ static int validate_ops(uv_plan* p) {
       if (op.a.off < 0 || op.KC % 16 || op.N_TILE % 16 || op.N_TILE > 256 || op.N_total % op.N_TILE ||
           (op.a.nch * 8) % op.KC || (op.C_out % op.N_TILE && (op.up <= 1 || op.N_TILE % op.C_out)) || op.smin < -kGuard || op.smax > kGuard || op.a.split != op.n_src)
         return fail(UV_ERR_INVALID, "malformed GEMM op #" + std::to_string(i));
-      if (op.a.P < op.a.G + ((op.m_rows + kTileM - 1) / kTileM) * kTileM + op.smax)
+      const int tile_rows = kTileM * gemm_msub(op.N_TILE);
+      if (op.a.P < op.a.G + ((op.m_rows + tile_rows - 1) / tile_rows) * tile_rows + op.smax)
         return fail(UV_ERR_INVALID, "GEMM A plane too short, op #" + std::to_string(i));
     }
   }

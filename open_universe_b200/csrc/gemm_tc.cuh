@@ -44,11 +44,11 @@
 
 namespace uv {
 
-constexpr int kSubM = 128;          // UMMA M
-constexpr int kTileM = 256;         // rows per CTA tile (two UMMA sub-tiles)
-constexpr int kMaxAStages = 12;
-constexpr int kMaxBStages = 8;
-constexpr int kEpiWarps = 8;        // 4 TMEM lane quarters x 2 sub-tiles (16 = two column halves each: measured slower, the multi-output paths spill at 112 registers)
+constexpr int kSubM = 128;          // rows of a tile owned by one CTA of the pair (= its TMEM lanes)
+constexpr int kTileM = 256;         // rows per tile = UMMA M of the SM pair (tcgen05 cta_group::2)
+constexpr int kMaxAStages = 16;
+constexpr int kMaxBStages = 12;
+constexpr int kEpiWarps = 8;        // per CTA: 4 TMEM lane quarters x 2 halves of the tile's column groups
 #ifndef UV_XF_WARPS
 #define UV_XF_WARPS 2   // 4 removes the transform cost at level 1 (k5: 104 vs 125 us) but costs 128 registers + spills everywhere else: 45.3 vs 45.2 ms per pass
 #endif
@@ -56,14 +56,15 @@ constexpr int kXfWarps = UV_XF_WARPS;         // A-operand transform warps (PReL
 constexpr int kGemmThreads = 64 + 32 * kEpiWarps + 32 * kXfWarps;   // producer warp, MMA warp, epilogue warps, transform warps
 constexpr int kMaxAcc = 4;          // TMEM accumulator stages
 constexpr int kSchedSlots = 32;     // ring of claimed tile indices (producer -> MMA issuer + epilogue warps)
-constexpr int kSchedBytes = kSchedSlots * (4 + 2 * 8) + kMaxAStages * 8;   // + the a_ready barriers of the transform warps
+constexpr int kSchedBytes = kSchedSlots * (4 + 2 * 8);
+constexpr int kPairCtas = 2;        // CTAs per cluster: one tcgen05 CTA pair
 constexpr int kOnesBytes = 2 * kSubM * 16;   // [2 chunks][128 rows][8] bf16
 constexpr int kFilmMaxC = 768;
 constexpr int kFilmBytes = 2 * kFilmMaxC * 4;
 constexpr int kGemmSmemBudget = 227 * 1024;
 constexpr int kRmPitch = 20;        // floats per row of the GRU-layout staging buffer (16 + 4: conflict-free 16-byte accesses)
 constexpr int kRmScratchBytes = kEpiWarps * 32 * kRmPitch * 4;
-constexpr int kAddRowsBytes = kTileM * 16;   // one 8-channel chunk of a residual slab (no halo)
+constexpr int kAddRowsBytes = kSubM * 16;    // one 8-channel chunk of a residual slab (no halo), this CTA's rows
 
 // TMEM columns per accumulator (power of two >= 32).
 __host__ __device__ inline uint32_t accum_stride_cols(int n_tile) {
@@ -119,6 +120,71 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, int* er
     }
   }
 }
+// ---- CTA-pair plumbing.  Remote arrives and the waits on barriers that receive them use the DEFAULT (cta-scope)
+// semantics, like every cluster barrier of CUTLASS: what they order lives in shared / tensor memory and is moved by
+// the async proxy or fenced by tcgen05.fence / fence.proxy.async before the arrive.  Cluster-scope release / acquire
+// compile to MEMBAR.ALL.GPU + CGAERRBAR / CCTL.IVALL on every arrive / wait, which made the epilogue warps wait for
+// all their outstanding global stores at every tile (level-0 convs 3.5x slower, measured).  The one datum that crosses
+// CTAs through a generic store -- the claimed tile index -- is sent with st.async, whose completion is part of the
+// receiving barrier's transaction count.
+__device__ __forceinline__ uint32_t cta_rank_in_cluster() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t map_shared_rank(uint32_t saddr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+  return r;
+}
+// arrive on a barrier given by its shared::cluster address (own or peer CTA)
+__device__ __forceinline__ void mbar_arrive_cl(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// 4-byte store into the peer's shared memory that completes 4 bytes of the transaction count of the peer's barrier
+// (armed by mbar_expect_tx_cl): the value is visible to whoever observes that barrier phase complete.
+__device__ __forceinline__ void mbar_expect_tx_cl(uint32_t cluster_bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cluster.b64 _, [%0], %1;" ::"r"(cluster_bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void st_async_u32(uint32_t cluster_addr, uint32_t v, uint32_t cluster_bar) {
+  asm volatile("st.async.shared::cluster.mbarrier::complete_tx::bytes.u32 [%0], %1, [%2];" ::"r"(cluster_addr), "r"(v), "r"(cluster_bar)
+               : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait_cl(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.b32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ bool mbar_test_wait_cl(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.b32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait_cl(uint32_t bar, uint32_t parity, int* err_flag, int code) {
+  uint32_t spins = 0;
+  while (!mbar_try_wait_cl(bar, parity)) {
+    if (++spins > (1u << 26)) {
+      if (err_flag) *reinterpret_cast<volatile int*>(err_flag) = code;
+      __threadfence_system();
+      __trap();
+    }
+  }
+}
+__device__ __forceinline__ void cluster_barrier() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
 __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
   asm volatile(
       "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
@@ -154,6 +220,22 @@ __device__ __forceinline__ void tc_mma_bf16(uint32_t d_tmem, uint64_t adesc, uin
       "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
+}
+// The SM pair: M = 256 (128 rows per CTA), each CTA supplies N / 2 columns of B, issued by the leader CTA only;
+// the descriptors name the same shared-memory offsets in both CTAs.
+__device__ __forceinline__ void tc_mma2_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// Arrives, once all earlier MMAs of the pair have completed, on the barrier at this offset in BOTH CTAs of the pair.
+__device__ __forceinline__ void tc_commit2(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+               "h"((uint16_t)3)
+               : "memory");
 }
 // 32 lanes x 16 consecutive fp32 columns -> 16 registers; completes at tc_ld_wait().
 __device__ __forceinline__ void tc_ld16_issue(uint32_t taddr, uint32_t* r) {
@@ -294,7 +376,8 @@ __device__ __forceinline__ void add_f32(const char* p, long long pstride, float*
   }
 }
 
-// Epilogue of one warp: lane = TMEM lane = output row of its 128-row half of every tile.
+// Epilogue of one warp: lane = TMEM lane = output row among this CTA's 128 rows of every tile (rows 128 rank ...);
+// two warps share a lane quarter and take one half of the tile's 16-column groups each.
 // The work is a flat sequence of units (tile, 16-column group) run as a two-buffer software pipeline
 // that crosses tile boundaries: while unit u is processed, the TMEM load of unit u+1 is in flight, also
 // when u+1 is the first group of the next tile (its accumulator barrier is probed without blocking).
@@ -303,14 +386,19 @@ __device__ __forceinline__ void add_f32(const char* p, long long pstride, float*
 template <bool ADD, bool FILM, bool MULTI, bool LE1>
 __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem_base, uint64_t* t_full, uint64_t* t_empty,
                                               const float* film_s, const int* s_ring, uint64_t* s_full, uint64_t* s_empty,
-                                              float* rm_scratch, int warp, int lane) {
-  const int sub = ((warp - 2) >> 2) & 1;
-  const int chalf = (warp - 2) >> 3;            // with 16 epilogue warps: which half of the column groups
+                                              float* rm_scratch, int warp, int lane, uint32_t rank) {
+  // msub = 1: the two warps of a lane quarter split the tile's column groups; msub = 2 (narrow tiles): they take one
+  // 128-row sub-tile of this CTA's 256 rows each
+  const int msub = P.msub;
+  const int wh = (warp - 2) >> 2;               // 0 / 1: which of the two warps of this lane quarter
+  const int sub = msub == 2 ? wh : 0;
+  const int chalf = msub == 2 ? 0 : wh;
   const int quarter = warp & 3;                 // a warp may only touch TMEM lanes 32*(warp%4)..+31
-  const int row_in_tile = sub * kSubM + quarter * 32 + lane;
+  const int tile_rows = kTileM * msub;
+  const int row_in_tile = (int)rank * kSubM * msub + sub * kSubM + quarter * 32 + lane;
   const int ngroups = P.N_TILE >> 4;
-  const int g_begin = (kEpiWarps == 16 && chalf) ? (ngroups + 1) >> 1 : 0;
-  const int g_end = (kEpiWarps == 16 && !chalf) ? (ngroups + 1) >> 1 : ngroups;
+  const int g_begin = chalf ? (ngroups + 1) >> 1 : 0;
+  const int g_end = (msub == 2 || chalf) ? ngroups : (ngroups + 1) >> 1;
   const uint32_t acc_stride = accum_stride_cols(P.N_TILE);
   const int n_acc = P.n_acc;
   const int ntn = P.n_tiles_n;
@@ -335,22 +423,24 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
   const float inv_split_a1 = 1.f / (float)(P.add1.split > 0 ? P.add1.split : 1);
   const float inv_split_a2 = 1.f / (float)(P.add2.split > 0 ? P.add2.split : 1);
   const uint32_t t_lane = tmem_base + (uint32_t)sub * acc_stride + ((uint32_t)(quarter * 32) << 16);
-  const uint32_t t_stage = 2u * acc_stride;
-  const uint32_t full0 = smem_u32(t_full), empty0 = smem_u32(t_empty);
+  const uint32_t t_stage = (uint32_t)msub * acc_stride;
+  const uint32_t full0 = smem_u32(t_full);
+  const uint32_t empty_cl0 = map_shared_rank(smem_u32(t_empty), 0);   // the MMA issuer (leader CTA) waits for both CTAs' epilogues
 
   // claimed-tile ring (filled by the producer thread): every consumer reads every slot once
-  const uint32_t sfull0 = smem_u32(s_full), sempty0 = smem_u32(s_empty);
+  const uint32_t sfull0 = smem_u32(s_full);
+  const uint32_t sempty_cl0 = map_shared_rank(smem_u32(s_empty), 0);   // the scheduler lives in the leader CTA
   int s_slot = 0;
   uint32_t s_par = 0;
   auto sched_take = [&]() {   // slot s_slot is known to be full
-    const int t = s_ring[s_slot];
+    const int t = *reinterpret_cast<const volatile int*>(s_ring + s_slot);
     __syncwarp();
-    if (lane == 0) mbar_arrive(sempty0 + 8u * s_slot);
+    if (lane == 0) mbar_arrive_cl(sempty_cl0 + 8u * s_slot);
     if (++s_slot == kSchedSlots) { s_slot = 0; s_par ^= 1u; }
     return t;
   };
   auto sched_next = [&]() {
-    mbar_wait(sfull0 + 8u * s_slot, s_par, P.err_flag, 8);
+    mbar_wait_cl(sfull0 + 8u * s_slot, s_par, P.err_flag, 8);
     return sched_take();
   };
   int cur_tile = sched_next();
@@ -389,16 +479,19 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
       ph = fast_div(n0, P.C_out, inv_Cout);
       co0 = n0 - ph * P.C_out;
     }
-    const int g = m_tile * kTileM + row_in_tile;
+    const int g = m_tile * tile_rows + row_in_tile;
     const int b = fast_div(g, P.Lh_A, inv_Lh);
     const int m = g - b * P.Lh_A;
     valid = (g < P.m_rows) && (m < P.M_valid);
-    const int l_out = P.up * m + ph;
+    // first column group of this warp: in a multi-phase tile it may lie in a later phase (= a later output row)
+    int ph_b = 0, gin = g_begin;
+    if (g_begin >= gpp) { ph_b = g_begin / gpp; gin = g_begin - ph_b * gpp; }
+    const int l_out = P.up * m + ph + ph_b;
     t_b = b; t_l = l_out;
     const int chunk_base = co0 >> 3;
 #pragma unroll
     for (int o = 0; o < 3; ++o) {
-      if (o < n_out && valid && (MULTI || o == 0)) op[o] = out_ptr(P.out[o].t, b, l_out, chunk_base + 2 * g_begin, inv_split[o]);
+      if (o < n_out && valid && (MULTI || o == 0)) op[o] = out_ptr(P.out[o].t, b, l_out, chunk_base + 2 * gin, inv_split[o]);
       else op[o].p = nullptr;
     }
     if (ADD) {
@@ -463,7 +556,7 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
       return;
     }
     if (!valid) return;
-    if (g16 >= gpp && g16 % gpp == 0) {
+    if (g16 != g_begin && g16 >= gpp && g16 % gpp == 0) {
       // next phase of a multi-phase tile (transposed conv): one output row further, channel chunks from 0 again
       ++t_l;
 #pragma unroll
@@ -544,7 +637,7 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
     auto release = [&]() {   // this warp's part of the accumulator is in registers: the MMA warp may reuse it
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(empty0 + 8u * stage);
+      if (lane == 0) mbar_arrive_cl(empty_cl0 + 8u * stage);
     };
     if (!have) release();
     for (int g2 = g_begin; g2 < g_end; g2 += 2) {
@@ -565,7 +658,7 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
         } else {
           release();
           // never block here: this group is still to be processed
-          if (__all_sync(0xffffffffu, mbar_test_wait(sfull0 + 8u * s_slot, s_par))) {
+          if (__all_sync(0xffffffffu, mbar_test_wait_cl(sfull0 + 8u * s_slot, s_par))) {
             next_tile = sched_take();
             next_known = true;
           }
@@ -596,11 +689,22 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
 
 
 // ------------------------------------------------------------------ kernel
+// Launched as clusters of two CTAs (one tcgen05 CTA pair on two SMs of a TPC).  A tile is 256 rows x N_TILE columns:
+// CTA `rank` holds rows [128 rank, 128 rank + 128) of every A slab and columns [N_TILE/2 rank, ...) of every weight
+// image in its own shared memory and its rows of the accumulator in its own tensor memory; the leader (rank 0)
+// issues ONE M = 256 tcgen05.mma.cta_group::2 per K step for the pair.  Measured on B200 (tools/mma_bench.cu): a
+// 1-SM M128 MMA costs ~97 clk whatever N <= 128 is (66 % of the tensor peak at N = 128, 17-33 % at N = 32-64), the
+// pair's M256 MMA costs 64 clk at N = 128 and 128 clk at N = 256 (100 %), 51 clk at N = 64.
+// Division of labour in a pair: both CTAs load, transform and drain their own halves; tile claims, MMA issue and all
+// "stage consumed" / "accumulator complete" signals (multicast tcgen05.commit) come from the leader; the peer's
+// warp 1 relays "my half of this stage has landed" to the leader's barriers.
 __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_constant__ GemmParams P) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  if (threadIdx.x == 0) UV_STAMP(0);
+  const uint32_t rank = cta_rank_in_cluster();
+  const bool leader = rank == 0;
+  if (threadIdx.x == 0 && leader) UV_STAMP(0);
   pdl_launch_dependents();   // the next kernel's CTAs take over this SM when this CTA exits and start their own prologue
 
   // smem carve-up: ones tile | FiLM table | identity images | A ring | B ring (or resident weight set) | barriers | tmem ptr
@@ -623,16 +727,26 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(s_ring + kSchedSlots);
   float* rm_scratch = reinterpret_cast<float*>(tmem_ptr_smem + 4);   // kRmScratchBytes, only with rm_xpose
 
+  const int n_half = P.N_TILE >> 1;                // weight / identity columns held by this CTA
   const uint32_t acc_stride = accum_stride_cols(P.N_TILE);
   const int n_acc = P.n_acc;
-  const uint32_t tmem_cols = (uint32_t)n_acc * 2u * acc_stride;
+  const int msub = P.msub;                         // 128-row sub-tiles per CTA (2 for narrow tiles)
+  const uint32_t tmem_cols = (uint32_t)n_acc * msub * acc_stride;
+  const uint32_t xf = P.a_act ? (uint32_t)kXfWarps : 0u;
   if (threadIdx.x == 0) {
-    for (int i = 0; i < kMaxAStages; ++i) { mbar_init(smem_u32(&a_full[i]), 1); mbar_init(smem_u32(&a_empty[i]), 1); }
-    for (int i = 0; i < kMaxBStages; ++i) { mbar_init(smem_u32(&b_full[i]), 1); mbar_init(smem_u32(&b_empty[i]), 1); }
-    for (int i = 0; i < kMaxAcc; ++i) { mbar_init(smem_u32(&t_full[i]), 1); mbar_init(smem_u32(&t_empty[i]), kEpiWarps); }
-    const uint32_t ring_readers = 1 + kEpiWarps + (P.a_act ? kXfWarps : 0);
+    // arrival counts: the leader's "full" barriers also take the peer's relay arrive; the leader's "empty" barriers
+    // of the accumulators and of the tile ring take the readers of both CTAs
+    const uint32_t pr = leader ? 1u : 0u;
+    for (int i = 0; i < kMaxAStages; ++i) {
+      mbar_init(smem_u32(&a_full[i]), 1 + (P.a_act ? 0u : pr));
+      mbar_init(smem_u32(&a_ready[i]), kXfWarps + pr);
+      mbar_init(smem_u32(&a_empty[i]), 1);
+    }
+    for (int i = 0; i < kMaxBStages; ++i) { mbar_init(smem_u32(&b_full[i]), 1 + pr); mbar_init(smem_u32(&b_empty[i]), 1); }
+    for (int i = 0; i < kMaxAcc; ++i) { mbar_init(smem_u32(&t_full[i]), 1); mbar_init(smem_u32(&t_empty[i]), 2 * kEpiWarps); }
+    // ring readers: leader = MMA issuer + epilogue + transform warps, peer = producer + relay + epilogue + transform warps
+    const uint32_t ring_readers = (1 + kEpiWarps + xf) + (2 + kEpiWarps + xf);
     for (int i = 0; i < kSchedSlots; ++i) { mbar_init(smem_u32(&s_full[i]), 1); mbar_init(smem_u32(&s_empty[i]), ring_readers); }
-    for (int i = 0; i < kMaxAStages; ++i) mbar_init(smem_u32(&a_ready[i]), kXfWarps);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   // ones tile: K columns 0 and 1 are 1.0 (they meet the hi / lo halves of the bias image), the rest 0
@@ -645,12 +759,13 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
     for (int i = threadIdx.x; i < 2 * P.C_out; i += kGemmThreads) film_s[i] = P.film[i];
   }
   if (P.add_kc) {
-    // identity images [N_TILE / add_kc][add_kc / 8][N_TILE][8]: image j maps residual channel j*add_kc + k to column j*add_kc + k
-    const int per_img = (P.add_kc >> 3) * P.N_TILE;
+    // this CTA's half of the identity images [N_TILE / add_kc][add_kc / 8][n_half][8]: image j maps residual channel
+    // j*add_kc + k to column j*add_kc + k; local column n stands for column rank*n_half + n
+    const int per_img = (P.add_kc >> 3) * n_half;
     const int n_ent = (P.N_TILE / P.add_kc) * per_img;
     for (int i = threadIdx.x; i < n_ent; i += kGemmThreads) {
       const int j = i / per_img, rem = i - j * per_img;
-      const int c = rem / P.N_TILE, n = rem - c * P.N_TILE;
+      const int c = rem / n_half, n = rem - c * n_half + (int)rank * n_half;
       const int e = n - j * P.add_kc - 8 * c;   // K element of this 16-byte entry that is 1.0
       uint32_t w[4] = {0u, 0u, 0u, 0u};
       if (e >= 0 && e < 8) w[e >> 1] = (e & 1) ? 0x3F800000u : 0x00003F80u;
@@ -658,66 +773,89 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
     }
   }
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  cluster_barrier();   // both CTAs' barriers exist before any remote arrive / multicast commit
   if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr_smem)),
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr_smem)),
                  "r"(tmem_cols)
                  : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
   }
   tc_fence_before();
   __syncthreads();
+  cluster_barrier();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
-  if (threadIdx.x == 0) UV_STAMP(1);
+  if (threadIdx.x == 0 && leader) UV_STAMP(1);
 
   const int n_shift = P.smax - P.smin + 1;
-  const int rows_a = kTileM + P.smax - P.smin;  // halo'd slab rows
+  const int cta_rows = kSubM * msub;            // rows of a tile held by this CTA (contiguous)
+  const int rows_a = cta_rows + P.smax - P.smin;   // halo'd slab rows of this CTA
+  const uint32_t add_rows_bytes = (uint32_t)cta_rows * 16u;   // one 8-channel chunk of a residual slab (no halo)
   const int kc_chunks = P.KC >> 3;
   const int total_tiles = P.n_tiles_m * P.n_tiles_n;
   const uint32_t a_slab_chunk_bytes = (uint32_t)rows_a * 16u;
   const uint32_t a_bytes = a_slab_chunk_bytes * kc_chunks;
-  const uint32_t b_bytes = (uint32_t)P.N_TILE * P.KC * 2u;
-  const uint32_t bias_bytes = P.has_bias ? (uint32_t)P.N_TILE * 32u : 0u;
+  const uint32_t b_bytes = (uint32_t)n_half * P.KC * 2u;            // this CTA's half of a weight image
+  const uint32_t bias_bytes = P.has_bias ? (uint32_t)n_half * 32u : 0u;
   const int n_img = P.n_src * P.n_groups * n_shift;  // weight images per N tile
-  const long long w_ntile_stride = (long long)n_img * b_bytes + bias_bytes;
+  const long long w_half_stride = (long long)n_img * b_bytes + bias_bytes;   // packed per (N tile, half): images, bias image
+  const int n_conv = P.n_src * P.n_groups;
+  const int n_res = P.add_kc ? P.N_TILE / P.add_kc : 0;
 
   if (warp == 0) {
-    // ============================== producer
+    // ============================== producer (both CTAs: own rows of A, own columns of the weights)
     if (elect_one()) {
       if (P.b_resident) {
         const uint32_t fbb = smem_u32(&b_full[0]);
-        const uint32_t total = (uint32_t)w_ntile_stride;
+        const uint32_t total = (uint32_t)w_half_stride;
+        const char* wsrc = P.w + (long long)rank * w_half_stride;
         mbar_expect_tx(fbb, total);
         for (uint32_t off = 0; off < total; off += 32768u) {
           const uint32_t n = total - off < 32768u ? total - off : 32768u;
-          bulk_g2s(smem_u32(b_ring + off), P.w + off, n, fbb);
+          bulk_g2s(smem_u32(b_ring + off), wsrc + off, n, fbb);
         }
       }
       int ia = 0, ib = 0;
       uint32_t pa = 0, pb = 0;
-      // dynamic schedule: two claims in flight, each published (-1 = no more tiles) before its loads are issued
       int ss = 0;
       uint32_t sp = 0;
-      int tile = atomicAdd(P.sched, 1);
-      int tile_nxt = atomicAdd(P.sched, 1);
+      // leader: dynamic schedule, two claims in flight, each published to BOTH CTAs' rings (-1 = no more tiles) before
+      // its loads are issued.  peer: takes the tile indices from its ring like every other reader.
+      int tile = 0, tile_nxt = 0;
+      const uint32_t ring_peer = map_shared_rank(smem_u32(s_ring), 1), sfull_peer = map_shared_rank(smem_u32(s_full), 1);
+      const uint32_t sempty_cl0 = map_shared_rank(smem_u32(s_empty), 0);
+      if (leader) {
+        tile = atomicAdd(P.sched, 1);
+        tile_nxt = atomicAdd(P.sched, 1);
+      }
       pdl_wait();   // weights and the tile counter do not depend on the predecessor; the activations do
       for (;;) {
-        const bool live = tile < total_tiles;
-        mbar_wait(smem_u32(&s_empty[ss]), sp ^ 1, P.err_flag, 9);
-        // reverse: claim k is tile total-1-k.  A kernel's output (263 MB at the finest levels) exceeds the 126 MB L2, so
-        // what is still cached when the next kernel starts is the END of the tensor; a consumer that starts from the
-        // end reads that part from L2 instead of evicting it on its way there (the builder alternates the direction
-        // along each chain of kernels).
-        const int tile_id = P.reverse ? total_tiles - 1 - tile : tile;
-        s_ring[ss] = live ? tile_id : -1;
-        mbar_arrive(smem_u32(&s_full[ss]));
+        int tile_id;
+        if (leader) {
+          const bool live = tile < total_tiles;
+          mbar_wait_cl(smem_u32(&s_empty[ss]), sp ^ 1, P.err_flag, 9);
+          // reverse: claim k is tile total-1-k.  A kernel's output (263 MB at the finest levels) exceeds the 126 MB L2, so
+          // what is still cached when the next kernel starts is the END of the tensor; a consumer that starts from the
+          // end reads that part from L2 instead of evicting it on its way there (the builder alternates the direction
+          // along each chain of kernels).
+          tile_id = live ? (P.reverse ? total_tiles - 1 - tile : tile) : -1;
+          s_ring[ss] = tile_id;
+          mbar_arrive(smem_u32(&s_full[ss]));
+          mbar_expect_tx_cl(sfull_peer + 8u * ss, 4u);
+          st_async_u32(ring_peer + 4u * ss, (uint32_t)tile_id, sfull_peer + 8u * ss);
+        } else {
+          mbar_wait_cl(smem_u32(&s_full[ss]), sp, P.err_flag, 8);
+          tile_id = *reinterpret_cast<const volatile int*>(s_ring + ss);
+          mbar_arrive_cl(sempty_cl0 + 8u * ss);
+        }
         if (++ss == kSchedSlots) { ss = 0; sp ^= 1; }
-        if (!live) break;
-        const int tile_nn = tile_nxt < total_tiles ? atomicAdd(P.sched, 1) : tile_nxt;
+        if (tile_id < 0) break;
+        int tile_nn = tile_nxt;
+        if (leader && tile_nxt < total_tiles) tile_nn = atomicAdd(P.sched, 1);
         const int n_tile = tile_id % P.n_tiles_n;
         const int m_tile = tile_id / P.n_tiles_n;
-        const long long row0 = (long long)P.a_G + (long long)m_tile * kTileM + P.smin;
-        const char* w_tile = P.w + (long long)n_tile * w_ntile_stride;
+        const long long row0 = (long long)P.a_G + ((long long)m_tile * kPairCtas + rank) * cta_rows + P.smin;
+        const char* w_tile = P.w + (long long)(2 * n_tile + (int)rank) * w_half_stride;
         if (!P.b_resident && bias_bytes) {
           mbar_wait(smem_u32(&b_empty[ib]), pb ^ 1, P.err_flag, 2);
           const uint32_t fbb = smem_u32(&b_full[ib]);
@@ -752,156 +890,195 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
         if (P.add_kc) {
           // residual operand (same row space, phase plane = output phase): one un-halo'd slab per identity image
           const int cpi = P.add_kc >> 3;
-          for (int j = 0; j < P.N_TILE / P.add_kc; ++j) {
+          for (int j = 0; j < n_res; ++j) {
             const int col = n_tile * P.N_TILE + j * P.add_kc;   // a tile may span several phases; a slab never does
             const int phase = col / P.C_out;
             const int co0 = col - phase * P.C_out;
             mbar_wait(smem_u32(&a_empty[ia]), pa ^ 1, P.err_flag, 1);
             const uint32_t fb = smem_u32(&a_full[ia]);
-            mbar_expect_tx(fb, (uint32_t)cpi * kAddRowsBytes);
+            mbar_expect_tx(fb, (uint32_t)cpi * add_rows_bytes);
             const uint32_t dst = smem_u32(a_ring + (size_t)ia * P.a_stage_bytes);
             const long long plane0 = (long long)phase * P.add1.nchunks + (co0 >> 3);
-            const long long rowa = (long long)P.add1.G + (long long)m_tile * kTileM;
+            const long long rowa = (long long)P.add1.G + ((long long)m_tile * kPairCtas + rank) * cta_rows;
             for (int jc = 0; jc < cpi; ++jc) {
               const char* src = P.add1.base + (((plane0 + jc) * P.add1.P + rowa) << 4);
-              bulk_g2s(dst + jc * kAddRowsBytes, src, kAddRowsBytes, fb);
+              bulk_g2s(dst + jc * add_rows_bytes, src, add_rows_bytes, fb);
             }
             if (++ia == P.na_stages) { ia = 0; pa ^= 1; }
           }
         }
-        if (ss == 1 && sp == 0) UV_STAMP(2);
+        if (leader && ss == 1 && sp == 0) UV_STAMP(2);
         tile = tile_nxt;
         tile_nxt = tile_nn;
       }
     }
   } else if (warp == 1) {
-    // ============================== MMA issuer
-    // One thread; its instruction latency paces small-K layers, so descriptors are split into a constant
-    // high word and a low word (address >> 4 | LBO) that advances by plain 32-bit adds.
-    if (elect_one()) {
-      const uint32_t idesc = make_idesc(kSubM, P.N_TILE);
-      const uint32_t lbo_a = a_slab_chunk_bytes, lbo_b = (uint32_t)P.N_TILE * 16u;
-      const uint32_t desc_hi = (128u >> 4) | (1u << 14);                       // SBO = 128 B, descriptor version 1
-      const uint32_t a_lo0 = (smem_u32(a_ring) >> 4) | ((lbo_a >> 4) << 16);
-      const uint32_t r_lo0 = (smem_u32(a_ring) >> 4) | (((uint32_t)kAddRowsBytes >> 4) << 16);   // residual slabs (no halo)
-      const uint32_t b_lo0 = (smem_u32(b_ring) >> 4) | ((lbo_b >> 4) << 16);
-      const uint32_t i_lo0 = (smem_u32(ident) >> 4) | ((lbo_b >> 4) << 16);
-      const uint32_t a_stage16 = (uint32_t)P.a_stage_bytes >> 4, b_stage16 = (uint32_t)P.b_stage_bytes >> 4;
-      const uint32_t a_kstep = (2u * lbo_a) >> 4, r_kstep = (2u * (uint32_t)kAddRowsBytes) >> 4, b_kstep = (2u * lbo_b) >> 4;
-      const uint32_t b_img16 = b_bytes >> 4;
-      const uint64_t ones_desc = make_desc(smem_u32(ones), (uint32_t)kSubM * 16u, 128);
-      const int ksteps = P.KC >> 4;
-      auto dsc = [&](uint32_t lo) { return ((uint64_t)desc_hi << 32) | (uint64_t)lo; };
-      if (P.b_resident) {
-        mbar_wait(smem_u32(&b_full[0]), 0, P.err_flag, 7);
-        tc_fence_after();
-      }
-      UV_STAMP(3);
-      bool first_slab = true;
-      const uint32_t a_wait0 = P.a_act ? smem_u32(a_ready) : smem_u32(a_full);
-      int ia = 0, ib = 0, as = 0, ss = 0;
-      uint32_t pa = 0, pb = 0, pt = 1, sp = 0;
-      for (;;) {
-        mbar_wait(smem_u32(&s_full[ss]), sp, P.err_flag, 8);
-        const int tile = s_ring[ss];
-        mbar_arrive(smem_u32(&s_empty[ss]));
-        if (++ss == kSchedSlots) { ss = 0; sp ^= 1; }
-        if (tile < 0) break;
-        mbar_wait(smem_u32(&t_empty[as]), pt, P.err_flag, 3);
-        tc_fence_after();
-        const uint32_t d0 = tmem_base + (uint32_t)(as * 2) * acc_stride;
-        const uint32_t d1 = d0 + acc_stride;
-        uint32_t accumulate = 0;
-        if (bias_bytes) {
-          uint32_t bias_lo;
-          if (P.b_resident) {
-            bias_lo = b_lo0 + (uint32_t)n_img * b_img16;
-          } else {
-            mbar_wait(smem_u32(&b_full[ib]), pb, P.err_flag, 5);
-            tc_fence_after();
-            bias_lo = b_lo0 + (uint32_t)ib * b_stage16;
-          }
-          tc_mma_bf16(d0, ones_desc, dsc(bias_lo), idesc, 0);
-          tc_mma_bf16(d1, ones_desc, dsc(bias_lo), idesc, 0);
-          accumulate = 1;
-          if (!P.b_resident) {
-            tc_commit(smem_u32(&b_empty[ib]));
-            if (++ib == P.nb_stages) { ib = 0; pb ^= 1; }
-          }
-        }
-        uint32_t img_lo = b_lo0;   // resident weights: images are consumed in storage order
-        for (int sg = 0; sg < P.n_src * P.n_groups; ++sg) {
-          mbar_wait(a_wait0 + 8u * ia, pa, P.err_flag, 4);   // landed (and, for a raw A tensor, activated)
+    if (leader) {
+      // ============================== MMA issuer (leader CTA)
+      // One thread; its instruction latency paces small-K layers, so descriptors are split into a constant
+      // high word and a low word (address >> 4 | LBO) that advances by plain 32-bit adds.
+      if (elect_one()) {
+        const uint32_t idesc = make_idesc(kTileM, P.N_TILE);
+        const uint32_t lbo_a = a_slab_chunk_bytes, lbo_b = (uint32_t)n_half * 16u;
+        const uint32_t desc_hi = (128u >> 4) | (1u << 14);                       // SBO = 128 B, descriptor version 1
+        const uint32_t a_lo0 = (smem_u32(a_ring) >> 4) | ((lbo_a >> 4) << 16);
+        const uint32_t r_lo0 = (smem_u32(a_ring) >> 4) | ((add_rows_bytes >> 4) << 16);   // residual slabs (no halo)
+        const uint32_t b_lo0 = (smem_u32(b_ring) >> 4) | ((lbo_b >> 4) << 16);
+        const uint32_t i_lo0 = (smem_u32(ident) >> 4) | ((lbo_b >> 4) << 16);
+        const uint32_t a_stage16 = (uint32_t)P.a_stage_bytes >> 4, b_stage16 = (uint32_t)P.b_stage_bytes >> 4;
+        const uint32_t a_kstep = (2u * lbo_a) >> 4, r_kstep = (2u * add_rows_bytes) >> 4, b_kstep = (2u * lbo_b) >> 4;
+        const uint32_t sub16 = (uint32_t)(kSubM * 16) >> 4;   // second sub-tile: 128 rows further down the slab
+        const bool two = msub == 2;
+        const uint32_t b_img16 = b_bytes >> 4;
+        const uint64_t ones_desc = make_desc(smem_u32(ones), (uint32_t)kSubM * 16u, 128);
+        const int ksteps = P.KC >> 4;
+        auto dsc = [&](uint32_t lo) { return ((uint64_t)desc_hi << 32) | (uint64_t)lo; };
+        if (P.b_resident) {
+          mbar_wait_cl(smem_u32(&b_full[0]), 0, P.err_flag, 7);
           tc_fence_after();
-          if (first_slab) { UV_STAMP(4); first_slab = false; }
-          const uint32_t a_lo = a_lo0 + (uint32_t)ia * a_stage16;
-          for (int q = 0; q < n_shift; ++q) {
-            uint32_t bl;
+        }
+        UV_STAMP(3);
+        bool first_slab = true;
+        const uint32_t a_wait0 = P.a_act ? smem_u32(a_ready) : smem_u32(a_full);
+        const uint32_t sempty0 = smem_u32(s_empty);
+        int ia = 0, ib = 0, as = 0, ss = 0;
+        uint32_t pa = 0, pb = 0, pt = 1, sp = 0;
+        for (;;) {
+          mbar_wait(smem_u32(&s_full[ss]), sp, P.err_flag, 8);
+          const int tile = s_ring[ss];
+          mbar_arrive(sempty0 + 8u * ss);
+          if (++ss == kSchedSlots) { ss = 0; sp ^= 1; }
+          if (tile < 0) break;
+          mbar_wait_cl(smem_u32(&t_empty[as]), pt, P.err_flag, 3);   // both CTAs' epilogues have drained this accumulator
+          tc_fence_after();
+          const uint32_t d0 = tmem_base + (uint32_t)(as * msub) * acc_stride;
+          const uint32_t d1 = d0 + acc_stride;
+          uint32_t accumulate = 0;
+          if (bias_bytes) {
+            uint32_t bias_lo;
             if (P.b_resident) {
-              bl = img_lo;
-              img_lo += b_img16;
+              bias_lo = b_lo0 + (uint32_t)n_img * b_img16;
             } else {
-              mbar_wait(smem_u32(&b_full[ib]), pb, P.err_flag, 5);
+              mbar_wait_cl(smem_u32(&b_full[ib]), pb, P.err_flag, 5);
               tc_fence_after();
-              bl = b_lo0 + (uint32_t)ib * b_stage16;
+              bias_lo = b_lo0 + (uint32_t)ib * b_stage16;
             }
-            uint32_t al = a_lo + (uint32_t)q;   // tap q = slab shifted by q rows of 16 B
-            for (int kk = 0; kk < ksteps; ++kk) {
-              tc_mma_bf16(d0, dsc(al), dsc(bl), idesc, accumulate);
-              tc_mma_bf16(d1, dsc(al + (uint32_t)(kSubM * 16 >> 4)), dsc(bl), idesc, accumulate);
-              accumulate = 1;
-              al += a_kstep;
-              bl += b_kstep;
-            }
+            tc_mma2_bf16(d0, ones_desc, dsc(bias_lo), idesc, 0);
+            if (two) tc_mma2_bf16(d1, ones_desc, dsc(bias_lo), idesc, 0);
+            accumulate = 1;
             if (!P.b_resident) {
-              tc_commit(smem_u32(&b_empty[ib]));
+              tc_commit2(smem_u32(&b_empty[ib]));
               if (++ib == P.nb_stages) { ib = 0; pb ^= 1; }
             }
           }
-          tc_commit(smem_u32(&a_empty[ia]));
-          if (++ia == P.na_stages) { ia = 0; pa ^= 1; }
-        }
-        if (P.add_kc) {
-          const uint32_t img16 = ((uint32_t)P.N_TILE * P.add_kc * 2u) >> 4;
-          for (int j = 0; j < P.N_TILE / P.add_kc; ++j) {
-            mbar_wait(a_wait0 + 8u * ia, pa, P.err_flag, 4);
+          uint32_t img_lo = b_lo0;   // resident weights: images are consumed in storage order
+          for (int sg = 0; sg < n_conv; ++sg) {
+            mbar_wait_cl(a_wait0 + 8u * ia, pa, P.err_flag, 4);   // landed (and, for a raw A tensor, activated) in both CTAs
             tc_fence_after();
-            uint32_t al = r_lo0 + (uint32_t)ia * a_stage16;
-            uint32_t bl = i_lo0 + (uint32_t)j * img16;
-            for (int kk = 0; kk < (P.add_kc >> 4); ++kk) {
-              tc_mma_bf16(d0, dsc(al), dsc(bl), idesc, accumulate);
-              tc_mma_bf16(d1, dsc(al + (uint32_t)(kSubM * 16 >> 4)), dsc(bl), idesc, accumulate);
-              accumulate = 1;
-              al += r_kstep;
-              bl += b_kstep;
+            if (first_slab) { UV_STAMP(4); first_slab = false; }
+            const uint32_t a_lo = a_lo0 + (uint32_t)ia * a_stage16;
+            for (int q = 0; q < n_shift; ++q) {
+              uint32_t bl;
+              if (P.b_resident) {
+                bl = img_lo;
+                img_lo += b_img16;
+              } else {
+                mbar_wait_cl(smem_u32(&b_full[ib]), pb, P.err_flag, 5);
+                tc_fence_after();
+                bl = b_lo0 + (uint32_t)ib * b_stage16;
+              }
+              uint32_t al = a_lo + (uint32_t)q;   // tap q = slab shifted by q rows of 16 B
+              for (int kk = 0; kk < ksteps; ++kk) {
+                tc_mma2_bf16(d0, dsc(al), dsc(bl), idesc, accumulate);
+                if (two) tc_mma2_bf16(d1, dsc(al + sub16), dsc(bl), idesc, accumulate);
+                accumulate = 1;
+                al += a_kstep;
+                bl += b_kstep;
+              }
+              if (!P.b_resident) {
+                tc_commit2(smem_u32(&b_empty[ib]));
+                if (++ib == P.nb_stages) { ib = 0; pb ^= 1; }
+              }
             }
-            tc_commit(smem_u32(&a_empty[ia]));
+            tc_commit2(smem_u32(&a_empty[ia]));
             if (++ia == P.na_stages) { ia = 0; pa ^= 1; }
           }
+          if (P.add_kc) {
+            const uint32_t img16 = ((uint32_t)n_half * P.add_kc * 2u) >> 4;
+            for (int j = 0; j < n_res; ++j) {
+              mbar_wait_cl(a_wait0 + 8u * ia, pa, P.err_flag, 4);
+              tc_fence_after();
+              uint32_t al = r_lo0 + (uint32_t)ia * a_stage16;
+              uint32_t bl = i_lo0 + (uint32_t)j * img16;
+              for (int kk = 0; kk < (P.add_kc >> 4); ++kk) {
+                tc_mma2_bf16(d0, dsc(al), dsc(bl), idesc, accumulate);
+                if (two) tc_mma2_bf16(d1, dsc(al + sub16), dsc(bl), idesc, accumulate);
+                accumulate = 1;
+                al += r_kstep;
+                bl += b_kstep;
+              }
+              tc_commit2(smem_u32(&a_empty[ia]));
+              if (++ia == P.na_stages) { ia = 0; pa ^= 1; }
+            }
+          }
+          tc_commit2(smem_u32(&t_full[as]));
+          if (++as == n_acc) { as = 0; pt ^= 1; }
         }
-        tc_commit(smem_u32(&t_full[as]));
-        if (++as == n_acc) { as = 0; pt ^= 1; }
+      }
+    } else {
+      // ============================== relay (peer CTA): walks the stages in the issuer's order and tells the leader's
+      // barriers when this CTA's half of a stage has landed (and, for a raw A tensor, has been activated)
+      if (elect_one()) {
+        const uint32_t a_loc0 = P.a_act ? smem_u32(a_ready) : smem_u32(a_full);
+        const uint32_t a_rem0 = map_shared_rank(a_loc0, 0);
+        const uint32_t b_loc0 = smem_u32(b_full), b_rem0 = map_shared_rank(b_loc0, 0);
+        const uint32_t sempty_cl0 = map_shared_rank(smem_u32(s_empty), 0);
+        if (P.b_resident) {
+          mbar_wait(b_loc0, 0, P.err_flag, 7);
+          mbar_arrive_cl(b_rem0);
+        }
+        int ia = 0, ib = 0, ss = 0;
+        uint32_t pa = 0, pb = 0, sp = 0;
+        auto relay_b = [&]() {
+          mbar_wait(b_loc0 + 8u * ib, pb, P.err_flag, 5);
+          mbar_arrive_cl(b_rem0 + 8u * ib);
+          if (++ib == P.nb_stages) { ib = 0; pb ^= 1; }
+        };
+        for (;;) {
+          mbar_wait_cl(smem_u32(&s_full[ss]), sp, P.err_flag, 8);
+          const int tile = *reinterpret_cast<const volatile int*>(s_ring + ss);
+          mbar_arrive_cl(sempty_cl0 + 8u * ss);
+          if (++ss == kSchedSlots) { ss = 0; sp ^= 1; }
+          if (tile < 0) break;
+          if (!P.b_resident && bias_bytes) relay_b();
+          for (int sl = 0; sl < n_conv + n_res; ++sl) {
+            mbar_wait(a_loc0 + 8u * ia, pa, P.err_flag, 4);
+            mbar_arrive_cl(a_rem0 + 8u * ia);
+            if (++ia == P.na_stages) { ia = 0; pa ^= 1; }
+            if (!P.b_resident && sl < n_conv)
+              for (int q = 0; q < n_shift; ++q) relay_b();
+          }
+        }
       }
     }
   } else if (warp >= 2 + kEpiWarps) {
-    // ============================== A-operand transform (only for a raw A tensor)
+    // ============================== A-operand transform (only for a raw A tensor): every CTA activates its own slabs
     if (P.a_act) {
       const int w = warp - (2 + kEpiWarps);
       const float slope = P.a_slope;
       const bool le1 = slope <= 1.f;
       const int nvec = (int)(a_bytes >> 4);
-      const int n_conv = P.n_src * P.n_groups;
-      const int n_res = P.add_kc ? P.N_TILE / P.add_kc : 0;   // residual slabs pass through untouched (but are handed on: stage roles rotate)
+      const uint32_t sempty_cl0 = map_shared_rank(smem_u32(s_empty), 0);
       int ia = 0, ss = 0;
       uint32_t pa = 0, sp = 0;
       for (;;) {
-        mbar_wait(smem_u32(&s_full[ss]), sp, P.err_flag, 8);
-        const int tile = s_ring[ss];
+        mbar_wait_cl(smem_u32(&s_full[ss]), sp, P.err_flag, 8);
+        const int tile = *reinterpret_cast<const volatile int*>(s_ring + ss);
         __syncwarp();
-        if (lane == 0) mbar_arrive(smem_u32(&s_empty[ss]));
+        if (lane == 0) mbar_arrive_cl(sempty_cl0 + 8u * ss);
         if (++ss == kSchedSlots) { ss = 0; sp ^= 1; }
         if (tile < 0) break;
-        for (int sl = 0; sl < n_conv + n_res; ++sl) {
+        for (int sl = 0; sl < n_conv + n_res; ++sl) {   // residual slabs pass through untouched (but are handed on: stage roles rotate)
           mbar_wait(smem_u32(&a_full[ia]), pa, P.err_flag, 4);
           uint4* v = reinterpret_cast<uint4*>(a_ring + (size_t)ia * P.a_stage_bytes);
           if (sl < n_conv) {
@@ -940,7 +1117,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
     for (int o = 0; o < 3; ++o)
       if (o < P.n_out && ((P.out[o].act >= 1 && !(P.out[o].a1 <= 1.f)) || (P.out[o].act == 2 && !(P.out[o].a2 <= 1.f)))) le1 = false;
     const int kind = (has_add ? 1 : 0) | (has_film ? 2 : 0) | (multi ? 4 : 0) | (le1 ? 8 : 0);
-#define UV_EPI(A, F, M, L) epilogue_role<A, F, M, L>(P, tmem_base, t_full, t_empty, film_s, s_ring, s_full, s_empty, rm_scratch, warp, lane)
+#define UV_EPI(A, F, M, L) epilogue_role<A, F, M, L>(P, tmem_base, t_full, t_empty, film_s, s_ring, s_full, s_empty, rm_scratch, warp, lane, rank)
     switch (kind) {
       case 0: UV_EPI(false, false, false, false); break;
       case 1: UV_EPI(true, false, false, false); break;
@@ -964,15 +1141,16 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
 
   tc_fence_before();
   __syncthreads();
+  cluster_barrier();   // neither CTA leaves (or frees tensor memory) while the other can still signal / be signalled
   if (warp == 1) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols) : "memory");
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols) : "memory");
   }
-  // all claims of this CTA are done: the last CTA out rewinds the counter pair for the next launch
-  if (threadIdx.x == 0) {
+  // all claims of this pair are done: the last pair to leave rewinds the counter pair for the next launch
+  if (threadIdx.x == 0 && leader) {
     UV_STAMP(7);
     __threadfence();
-    if (atomicAdd(P.sched + 1, 1) == (int)gridDim.x - 1) {
+    if (atomicAdd(P.sched + 1, 1) == (int)(gridDim.x >> 1) - 1) {
       P.sched[0] = 0;
       P.sched[1] = 0;
     }
@@ -982,16 +1160,31 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
 // ------------------------------------------------------------------ host side
 inline size_t gemm_smem_bytes(const GemmParams& p) {
   return (size_t)kOnesBytes + kFilmBytes + p.ident_bytes + (size_t)p.na_stages * p.a_stage_bytes + (size_t)p.nb_stages * p.b_stage_bytes +
-         (2 * kMaxAStages + 2 * kMaxBStages + 2 * kMaxAcc) * sizeof(uint64_t) + kSchedBytes + 16;
+         (3 * kMaxAStages + 2 * kMaxBStages + 2 * kMaxAcc) * sizeof(uint64_t) + kSchedBytes + 16;
 }
 
+// 128-row sub-tiles per CTA of the pair: a tile is 256 * gemm_msub(N_TILE) rows (planes are padded to 512 rows).
+#ifndef UV_MSUB_MAXN
+#define UV_MSUB_MAXN 128
+#endif
+inline int gemm_msub(int n_tile) { return n_tile <= UV_MSUB_MAXN ? 2 : 1; }
+constexpr int kMaxTileRows = 2 * kTileM;
+
 // Fills the pipeline fields of `p` (stage sizes / counts, resident-weight mode) for the 227 KB smem of an SM.
+// All sizes are per CTA of the pair: 128 (+ halo) rows of A, N_TILE / 2 columns of the weights.
 // Returns false if the layer cannot be scheduled.
 inline bool gemm_plan_pipeline(GemmParams& p) {
-  const int rows_a = kTileM + p.smax - p.smin;
+  if (p.N_TILE % 16 || p.N_TILE > 256 || p.N_TILE < 16) return false;
+  const int n_half = p.N_TILE / 2;
+  // N tiles up to UV_MSUB_MAXN columns: 256 contiguous rows per CTA (two sub-tiles, two MMAs per K step), so the
+  // per-tile costs of every role (claims, barrier round trips, address set-up) are paid half as often; measured with
+  // 128 rows per CTA the HBM-bound levels 0 / 1 ran 2x slower than with 256 (test_gemm perf), and on the whole model
+  // 64 / 128 as the limit gave 52.4 / 47.0 ms per eager pass (tools/ab_msub.sh).
+  p.msub = gemm_msub(p.N_TILE);
+  const int rows_a = kSubM * p.msub + p.smax - p.smin;
   const int a_bytes = (p.KC / 8) * rows_a * 16;
-  const int b_bytes = p.N_TILE * p.KC * 2;
-  const int bias_bytes = p.has_bias ? p.N_TILE * 32 : 0;
+  const int b_bytes = n_half * p.KC * 2;
+  const int bias_bytes = p.has_bias ? n_half * 32 : 0;
   p.a_stage_bytes = (a_bytes + 127) & ~127;
   // Residual through the tensor core (identity MMA): a bf16 add1 laid out in the GEMM's own row space
   // (phase-split like the output of an up conv), memory-bound layers only (C_out <= 128).
@@ -1002,8 +1195,8 @@ inline bool gemm_plan_pipeline(GemmParams& p) {
     for (int kc = 64; kc >= 16; kc -= 16)
       if (p.N_TILE % kc == 0 && p.C_out % kc == 0) { p.add_kc = kc; break; }
     if (p.add_kc) {
-      p.ident_bytes = p.N_TILE * p.N_TILE * 2;
-      const int add_bytes = (p.add_kc / 8) * kAddRowsBytes;
+      p.ident_bytes = p.N_TILE * n_half * 2;
+      const int add_bytes = (p.add_kc / 8) * kAddRowsBytes * p.msub;
       if (add_bytes > p.a_stage_bytes) p.a_stage_bytes = add_bytes;
     }
   }
@@ -1011,13 +1204,13 @@ inline bool gemm_plan_pipeline(GemmParams& p) {
     // tile spanning several phases of a transposed conv: whole phases only, adds through the tensor core only
     if (p.up <= 1 || p.N_TILE % p.C_out || p.C_out % 16 || p.rm_out || p.add2.base || (p.add1.base && !p.add_kc)) return false;
   }
-  p.n_tiles_m = (p.m_rows + kTileM - 1) / kTileM;
-  const int stride = (int)accum_stride_cols(p.N_TILE);
-  p.n_acc = 512 / (2 * stride);
+  p.n_tiles_m = (p.m_rows + kTileM * p.msub - 1) / (kTileM * p.msub);
+  const int stride = (int)accum_stride_cols(p.N_TILE) * p.msub;
+  p.n_acc = 512 / stride;
   if (p.n_acc > kMaxAcc) p.n_acc = kMaxAcc;
   if (p.n_acc < 1) return false;
   p.rm_xpose = (p.rm_out && p.rm_H > 0 && p.n_out == 0 && !p.add1.base && !p.add2.base && !p.film && p.scale == 1.f) ? 1 : 0;
-  const long long fixed = kOnesBytes + kFilmBytes + p.ident_bytes + (2 * kMaxAStages + 2 * kMaxBStages + 2 * kMaxAcc) * 8 + kSchedBytes + 16 + 1024 +
+  const long long fixed = kOnesBytes + kFilmBytes + p.ident_bytes + (3 * kMaxAStages + 2 * kMaxBStages + 2 * kMaxAcc) * 8 + kSchedBytes + 16 + 1024 +
                           (p.rm_xpose ? kRmScratchBytes : 0);
   const long long budget = kGemmSmemBudget - fixed;
   const int n_img = p.n_src * p.n_groups * (p.smax - p.smin + 1);
@@ -1039,7 +1232,7 @@ inline bool gemm_plan_pipeline(GemmParams& p) {
     bool grew = false;
     for (int k = 0; k < 2; ++k)
       if (nb < kMaxBStages && (long long)na * p.a_stage_bytes + (long long)(nb + 1) * p.b_stage_bytes <= budget) { ++nb; grew = true; }
-    if (na < 4 && (long long)(na + 1) * p.a_stage_bytes + (long long)nb * p.b_stage_bytes <= budget) { ++na; grew = true; }
+    if (na < 6 && (long long)(na + 1) * p.a_stage_bytes + (long long)nb * p.b_stage_bytes <= budget) { ++na; grew = true; }
     if (!grew) break;
   }
   p.na_stages = na;
@@ -1054,15 +1247,29 @@ inline cudaError_t gemm_set_attributes() {
 
 inline cudaError_t gemm_launch(GemmParams p, int num_sms, cudaStream_t stream) {
   if (!gemm_plan_pipeline(p)) return cudaErrorInvalidConfiguration;
-  const size_t smem = gemm_smem_bytes(p);
+  if (gemm_smem_bytes(p) + (p.rm_xpose ? kRmScratchBytes : 0) > (size_t)kGemmSmemBudget) return cudaErrorInvalidConfiguration;
   if (!p.sched) return cudaErrorInvalidValue;
   const int total = p.n_tiles_m * p.n_tiles_n;
-  int grid = total < num_sms ? total : num_sms;
-  if (grid < 1) grid = 1;
+  int pairs = num_sms / kPairCtas;
+  if (total < pairs) pairs = total;
+  if (pairs < 1) pairs = 1;
   // always the whole shared memory of the SM: one CTA per SM, and never co-resident with a GRU CTA of the other
   // lane (whose tensor-memory allocation would stall this CTA's tcgen05.alloc for the length of the recurrence)
-  (void)smem;
-  return launch_pdl(gemm_tc_kernel, dim3(grid), dim3(kGemmThreads), kGemmSmemBudget, stream, p);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(pairs * kPairCtas);
+  cfg.blockDim = dim3(kGemmThreads);
+  cfg.dynamicSmemBytes = kGemmSmemBudget;
+  cfg.stream = stream;
+  cudaLaunchAttribute at[2];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = kPairCtas;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = 1;
+  at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl_enabled() ? 2 : 1;
+  return cudaLaunchKernelEx(&cfg, gemm_tc_kernel, p);
 }
 
 }  // namespace uv

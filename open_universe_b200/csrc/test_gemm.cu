@@ -73,7 +73,7 @@ static HT make_tensor(int B, int L, int C, int split, int esz, bool randomize) {
   t.B = B; t.L = L; t.C = C; t.split = split; t.esz = esz; t.G = kGuard;
   int rows = (L + split - 1) / split;
   t.Lh = ((rows + 2 + 7) / 8) * 8;
-  t.P = t.G + ((B * t.Lh + kTileM - 1) / kTileM) * kTileM + t.G;
+  t.P = t.G + ((B * t.Lh + kMaxTileRows - 1) / kMaxTileRows) * kMaxTileRows + t.G;
   t.data.assign((size_t)split * (C / 8) * t.P * 8 * esz, 0);
   if (randomize)
     for (int b = 0; b < B; ++b)
@@ -134,6 +134,12 @@ static const Case kCases[] = {
     {"mp4upsplit", 2, 300, 128, 1, -1, 1, 64, 64, 4, 128, true, false, true, false, 0.70710678f, 0, false},
     {"mp2up", 2, 301, 64, 1, -1, 1, 64, 32, 2, 64, true, false, false, false, 1.f, 2, false},
     {"xfmp3up", 2, 200, 96, 1, -1, 1, 48, 32, 3, 96, true, false, false, false, 1.f, 0, false},
+    // N tiles of 256 columns (two accumulator stages of the SM pair)
+    {"n256", 3, 401, 256, 1, -1, 1, 64, 512, 1, 256, true, false, false, false, 1.f, 0, false},
+    {"n256add", 2, 300, 256, 1, -2, 2, 64, 256, 1, 256, true, true, true, false, 0.70710678f, 2, false},
+    {"n256upsplit", 2, 100, 128, 1, -1, 1, 64, 64, 4, 256, true, false, true, false, 0.70710678f, 0, false},
+    {"rm256", 2, 130, 64, 1, 0, 0, 64, 512, 1, 256, true, false, false, false, 1.f, -1, true},
+    {"tiny", 1, 10, 32, 1, -1, 1, 32, 32, 1, 32, true, false, false, false, 1.f, 0, false},
 };
 
 static int run_case(const Case& c, int swap_lbo, int num_sms) {
@@ -152,32 +158,36 @@ static int run_case(const Case& c, int swap_lbo, int num_sms) {
   std::vector<float> bias(c.C_out), film(2 * c.C_out);
   for (auto& v : bias) v = frand() * 0.5f;
   for (auto& v : film) v = frand();
-  const size_t n_img_elems = (size_t)c.n_src * n_groups * n_shift * c.N_TILE * c.KC;
-  const size_t bias_elems = c.bias ? (size_t)c.N_TILE * 16 : 0;
-  const size_t nt_stride = n_img_elems + bias_elems;
-  std::vector<uint16_t> img(nt_stride * n_tiles_n, 0);
-  for (int nt = 0; nt < n_tiles_n; ++nt) {
-    for (int s = 0; s < c.n_src; ++s)
-      for (int g = 0; g < n_groups; ++g)
-        for (int q = 0; q < n_shift; ++q) {
-          size_t base = nt * nt_stride + (((size_t)s * n_groups + g) * n_shift + q) * (size_t)c.N_TILE * c.KC;
-          for (int j = 0; j < kcc; ++j)
-            for (int n = 0; n < c.N_TILE; ++n)
-              for (int e = 0; e < 8; ++e) {
-                int ci = g * c.KC + j * 8 + e;
-                int ng = nt * c.N_TILE + n;
-                img[base + ((size_t)j * c.N_TILE + n) * 8 + e] =
-                    f2bf(W[(((size_t)ng * c.n_src + s) * n_shift + q) * c.C_in + ci]);
-              }
+  // packed per (N tile, half of its columns): the CTA of rank h of a pair holds columns [h N_TILE/2, (h+1) N_TILE/2)
+  const int NH = c.N_TILE / 2;
+  const size_t n_img_elems = (size_t)c.n_src * n_groups * n_shift * NH * c.KC;
+  const size_t bias_elems = c.bias ? (size_t)NH * 16 : 0;
+  const size_t nt_stride = n_img_elems + bias_elems;   // per half
+  std::vector<uint16_t> img(nt_stride * 2 * n_tiles_n, 0);
+  for (int nt = 0; nt < n_tiles_n; ++nt)
+    for (int h = 0; h < 2; ++h) {
+      const size_t hb = (size_t)(2 * nt + h) * nt_stride;
+      for (int s = 0; s < c.n_src; ++s)
+        for (int g = 0; g < n_groups; ++g)
+          for (int q = 0; q < n_shift; ++q) {
+            size_t base = hb + (((size_t)s * n_groups + g) * n_shift + q) * (size_t)NH * c.KC;
+            for (int j = 0; j < kcc; ++j)
+              for (int n = 0; n < NH; ++n)
+                for (int e = 0; e < 8; ++e) {
+                  int ci = g * c.KC + j * 8 + e;
+                  int ng = nt * c.N_TILE + h * NH + n;
+                  img[base + ((size_t)j * NH + n) * 8 + e] =
+                      f2bf(W[(((size_t)ng * c.n_src + s) * n_shift + q) * c.C_in + ci]);
+                }
+          }
+      if (c.bias)
+        for (int n = 0; n < NH; ++n) {
+          const float bv = bias[(nt * c.N_TILE + h * NH + n) % c.C_out];
+          const uint16_t hi = f2bf(bv);
+          img[hb + n_img_elems + (size_t)n * 8 + 0] = hi;
+          img[hb + n_img_elems + (size_t)n * 8 + 1] = f2bf(bv - bf2f(hi));
         }
-    if (c.bias)
-      for (int n = 0; n < c.N_TILE; ++n) {
-        const float bv = bias[(nt * c.N_TILE + n) % c.C_out];
-        const uint16_t hi = f2bf(bv);
-        img[nt * nt_stride + n_img_elems + (size_t)n * 8 + 0] = hi;
-        img[nt * nt_stride + n_img_elems + (size_t)n * 8 + 1] = f2bf(bv - bf2f(hi));
-      }
-  }
+    }
   char* d_w;
   CK(cudaMalloc(&d_w, img.size() * 2));
   CK(cudaMemcpy(d_w, img.data(), img.size() * 2, cudaMemcpyHostToDevice));
@@ -318,7 +328,8 @@ static void run_perf(int num_sms, bool phases = false) {
     CK(cudaMemset(A.dev, 0x3c, A.data.size()));  // small finite bf16 values everywhere
     HT O = make_tensor(pc.B, pc.Lv, pc.C, sp, 2, false);
     HT O2 = make_tensor(pc.B, pc.Lv, pc.C, 1, 2, false);
-    const int KC = pc.C < 64 ? pc.C : 64, NT = s2d ? 2 * pc.C : (pc.C < 128 ? pc.C : 128);
+    const int ntmax = getenv("UV_PERF_NT") ? atoi(getenv("UV_PERF_NT")) : 256;
+    const int KC = pc.C < 64 ? pc.C : 64, NT = s2d ? 2 * pc.C : (pc.C < ntmax ? pc.C : ntmax);
     size_t wbytes = (size_t)pc.C * pc.C * pc.k * 2 * sp * sp + (size_t)pc.C * 32 * sp;
     char* d_w;
     CK(cudaMalloc(&d_w, wbytes));

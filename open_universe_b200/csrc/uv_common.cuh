@@ -77,7 +77,8 @@ struct GemmParams {
   int ident_bytes;   // smem bytes of the identity images
   int no_add_mma;    // test hook: keep add1 on the register path
   int b_resident;    // 1: all weight images of the (single) N tile stay in smem for the whole kernel
-  int n_acc;         // TMEM accumulator stages (1, 2 or 4), each holding both 128-row halves of a tile
+  int n_acc;         // TMEM accumulator stages (1, 2 or 4)
+  int msub;          // host: 128-row sub-tiles per CTA of the pair (2 for narrow N tiles: a tile is then 512 rows)
   int rm_xpose;      // host: rm_out in the GRU layout is stored through the shared-memory transpose (gemm_tc.cuh)
   int reverse;       // 1: tiles are taken from the last row tile down (see gemm_tc.cuh: L2 reuse between consecutive kernels)
   int a_act;         // 1: A is stored RAW; PReLU(a_slope) is applied to every slab in shared memory before the MMAs read it

@@ -37,21 +37,22 @@ class Level:
         self.L = L
         self.Lh = _ru(L + 2, 8)
         self.rows = B * self.Lh
-        self.P = G + _ru(self.rows, 256) + G   # GEMM tiles are 256 rows (csrc/gemm_tc.cuh kTileM)
+        self.P = G + _ru(self.rows, 512) + G   # GEMM tiles are 256 or 512 rows (csrc/gemm_tc.cuh kMaxTileRows)
 
 
 MEL_FT = 32   # frames per CTA of the mel kernel (csrc/small_ops.cuh kMelFT)
 # A tensor that is consumed both raw (residual / skip) and through a PReLU (the next conv) is written ONCE, raw; the
 # consuming GEMM activates it in shared memory (csrc/gemm_tc.cuh, a_act).  UV_RAW_A=0 restores the two-copy scheme.
-RAW_A = os.environ.get("UV_RAW_A", "1") != "0" and os.environ.get("UV_FUSE_CONVBLOCKS", "") != "1"
+RAW_A = os.environ.get("UV_RAW_A", "1") != "0"
 ALTERNATE = os.environ.get("UV_ALTERNATE", "1") != "0"   # alternate the tile direction along each chain of kernels
 RAW_A_MAXC = int(os.environ.get("UV_RAW_A_MAXC", "512"))   # channel limit of the scheme (measured on B200: it pays at every level, 46.2 ms per pass against 46.7 with 128 and 48.5 with 32)
 # ... and of its use in front of the encoder's strided down convs (they re-read and re-activate all r phases of A for
 # every N tile, so the transform warps pace the wide levels)
 RAW_A_RC_MAXC = int(os.environ.get("UV_RAW_A_RC_MAXC", "128"))
+# one launch per ConvBlock of the 64-column levels (csrc/convblock_pair.cuh): C = 64, or C = 32 in space-to-depth form
+FUSE_CONVBLOCKS = os.environ.get("UV_FUSE_CONVBLOCKS", "1") != "0"
 RECYCLE = os.environ.get("UV_RECYCLE", "1") != "0"   # liveness-based reuse of the activation slots of the arena (finalize_arena)
 VBASE = 1 << 44   # planes tensors carry virtual offsets >= VBASE until finalize_arena() places them
-FUSE_CONVBLOCKS = os.environ.get("UV_FUSE_CONVBLOCKS", "") == "1"   # experimental: one launch per C <= 64 ConvBlock (csrc/convblock.cuh); measured slower than three GEMM launches so far
 
 
 def raw_ok(C):
@@ -60,7 +61,7 @@ def raw_ok(C):
 
 
 class _PartSink:
-    """Builds GEMM records exactly like Program.gemm() without emitting them (parts of a fused op)."""
+    """Builds GEMM records exactly like Program.gemm() without emitting them (the parts of a fused op)."""
 
     def __init__(self, pg):
         self.pg = pg
@@ -107,7 +108,7 @@ class Program:
 
     def emit(self, op, name):
         op.lane = self.lane
-        if ALTERNATE and op.step != -2 and op.type in (_abi.OP_GEMM, _abi.OP_CONV_IN, _abi.OP_CONV_OUT):
+        if ALTERNATE and op.step != -2 and op.type in (_abi.OP_GEMM, _abi.OP_CONV_IN, _abi.OP_CONV_OUT, _abi.OP_CONVBLOCK):
             # the kernels of a chain walk their tensors in alternating directions: a consumer starts at the end its
             # producer just wrote, which is the part of the tensor the L2 still holds (csrc/gemm_tc.cuh, `reverse`)
             op.i3 = self.rev
@@ -146,13 +147,13 @@ class Program:
 
 
 def _op_tensors(op):
-    """Every uv_tens record of an op (and of the parts of a fused op)."""
+    """Every uv_tens record of an op."""
     yield op.a
     yield op.add1
     yield op.add2
     for k in range(3):
         yield op.out[k].t
-    for part in getattr(op, "parts", ()):
+    for part in getattr(op, "parts", ()):   # the GEMM records of a fused ConvBlock (run by the CPU emulator)
         yield from _op_tensors(part)
 
 
@@ -456,13 +457,14 @@ def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_
         outs = [] if only_conv1 else [_act(c1, s2)]
         if cond_out is not None:
             outs.append(_raw(cond_out))
-        lys = [L[name + f".conv{k}"] for k in (1, 2, 3)]
+        lys = [L[name + f".conv{k}" + sfx] for k in (1, 2, 3)]
         fuse = (
-            FUSE_CONVBLOCKS and not s2d and h_act is not None and not only_conv1 and v_add2 is None and C % 16 == 0 and C <= 64
-            and all(ly["KC"] == C and ly["N_TILE"] == C and ly["N_total"] == C and ly["up"] == 1 and ly["n_src"] == 1 for ly in lys)
-            and (lys[0]["smin"], lys[0]["smax"]) == (-2, 2) and all((ly["smin"], ly["smax"]) == (-1, 1) for ly in lys[1:])
-            and len(v_outs) <= (2 if cond_out is not None else 3)
-            and h_raw.split == 1 and h_raw.dtype == DT_BF16 and (cond is None or (cond.split == 1 and cond.dtype == DT_BF16))
+            FUSE_CONVBLOCKS and h_act is None and not only_conv1 and v_add2 is None and C * (2 if s2d else 1) == 64
+            and all(ly["N_TILE"] == 64 and ly["N_total"] == 64 and ly["KC"] * ly["n_src"] == 64 and ly["smin"] == -ly["smax"] for ly in lys)
+            and len(v_outs) + (1 if cond_out is not None else 0) <= 3 and (cond_out is None or len(v_outs) <= 2)
+            and h_raw.dtype == DT_BF16 and (cond is None or (cond.dtype == DT_BF16 and (cond.nch, cond.split, cond.Lh, cond.P) == (h_raw.nch, h_raw.split, h_raw.Lh, h_raw.P)))
+            and all(t.dtype == DT_BF16 and (t.nch == 8 or (s2d and t.nch == 4 and t.split == 2)) for t, *_ in v_outs)
+            and (cond_out is None or (cond_out.dtype == DT_BF16 and cond_out.nch == 8))
         )
         sink = _PartSink(pg) if fuse else pg
         g1 = sink.gemm(name + ".conv1", name + ".conv1" + sfx, h_act if h_act is not None else h_raw, lev, lev.L, outs, step, add1=cond,
@@ -474,25 +476,26 @@ def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_
         g3 = sink.gemm(name + ".conv3", name + ".conv3" + sfx, c2, lev, lev.L, v_outs, step, add1=h_raw, add2=v_add2, scale=v_scale)
         if not fuse:
             return
-        # one launch for the whole block (csrc/convblock.cuh); the three GEMM records stay attached for the
-        # CPU emulator, which runs them one after the other (same arithmetic, same bf16 intermediates)
+        # one launch for the whole block (csrc/convblock_pair.cuh); the three GEMM records stay attached for the CPU
+        # emulator, which runs them one after the other (same arithmetic, same bf16 intermediates c1 / c2)
         op = new_op(_abi.OP_CONVBLOCK, step)
-        op.a, op.C = h_act, C
+        op.a = h_raw
+        op.a_act, op.a_slope = 1, L[name + ".conv1"]["slope"]
         op.w_w, op.p0, op.p1 = (ly["w_w"] for ly in lys)
         op.i0 = sum((1 << k) for k, g in enumerate((g1, g2, g3)) if g.bias_w >= 0)
+        op.i1 = sum(((ly["n_src"] | ((ly["smax"] - ly["smin"] + 1) << 4)) << (8 * k)) for k, ly in enumerate(lys))
         op.m_rows, op.Lh_A, op.M_valid = lev.rows, lev.Lh, lev.L
         if cond is not None:
             op.add1 = cond
         op.f0 = g1.scale
-        op.film = film
+        op.film, op.C = film, C
         op.f1, op.f2 = s2, s3
-        op.add2 = h_raw
         op.scale = v_scale
         op.n_out = len(v_outs)
         for i, (t, act, a1, a2) in enumerate(v_outs):
             op.out[i].t, op.out[i].act, op.out[i].a1, op.out[i].a2 = t, act, a1, a2
         if cond_out is not None:
-            op.i1 = 1
+            op.i2 = 1
             op.out[2].t = cond_out
         op.parts = [g1, g2, g3]
         pg.emit(op, name + ".block")
@@ -528,7 +531,7 @@ def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_
     # input conv (condition.py:360) and encoder (condition.py:189-206)
     raw0 = raw_ok(chans[0])
     # finest level of the score network phase-split by 2 ("space to depth", weights.w4_same_s2d); UV_S2D=0 disables
-    s2d0 = bool(meta.get("s2d0")) and raw0 and not FUSE_CONVBLOCKS and os.environ.get("UV_S2D", "1") != "0"
+    s2d0 = bool(meta.get("s2d0")) and raw0 and os.environ.get("UV_S2D", "1") != "0"
     pg.s2d0 = s2d0
     h_raw, h_act = pg.tens("c.h0", lv[0], chans[0]), None if raw0 else pg.tens("c.h0a", lv[0], chans[0])
     op = new_op(_abi.OP_CONV_IN)

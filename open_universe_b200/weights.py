@@ -7,8 +7,9 @@ All transformations are exact algebra done once at load time in fp32:
     folded into the strided / transposed rate-change convolutions,
   * re-expression of every dense layer as a multi-tap GEMM
         D[row, n] = sum_{src s, shift q, c}  A_s[row + q, c] * W4[n, s, q, c]
-    and packing of W4 into bf16 tile images [n_tile][s][group][q][KC/8][N_TILE][8]
-    (the no-swizzle K-major UMMA layout consumed by csrc/gemm_tc.cuh),
+    and packing of W4 into bf16 images [n_tile][half 2][s][group][q][KC/8][N_TILE/2][8]
+    (the no-swizzle K-major UMMA layout consumed by csrc/gemm_tc.cuh; the GEMM kernel runs on SM pairs,
+    tcgen05 cta_group::2, and the CTA of rank h holds columns [h N_TILE/2, (h+1) N_TILE/2) of every image),
   * GRU recurrent weights into per-CTA K-major UMMA slices (csrc/gru.cuh).
 """
 import math
@@ -26,8 +27,13 @@ def eff_weight(sd, prefix):
     return sd[prefix + ".weight"].float()
 
 
-TILE_M = 256          # csrc/gemm_tc.cuh kTileM
-SMEM_BUDGET = 227 * 1024 - (4096 + 6144 + 384 + 16 + 1024)  # gemm_plan_pipeline(): 227 KB minus the fixed regions
+TILE_M = 256          # csrc/gemm_tc.cuh kTileM: rows of a tile of the SM pair
+SUB_M = 128           # ... of which every CTA of the pair holds 128 (kSubM)
+SMEM_BUDGET = 227 * 1024 - (4096 + 6144 + 640 + 640 + 16 + 1024)  # gemm_plan_pipeline(): 227 KB minus the fixed regions
+# widest N tile.  256 columns run the pair's MMA at the same rate as 128 (tools/mma_bench.cu) and halve the A re-reads,
+# but leave two (msub = 1) accumulator stages and halve the tile count of the short level-3 / 4 launches; measured on the
+# whole model (tools/ab_msub.sh, eager pass, one lane): 128 / 256 = 46.97 / 47.50 ms with 256-row CTA tiles for N <= 128
+NTILE_MAX = int(os.environ.get("UV_NTILE_MAX", "128"))
 
 
 def _kc_options(c_in):
@@ -41,17 +47,19 @@ def pick_kc(c_in, n_total=None, n_tile=None, n_src=1, n_shift=1, reserve=0):
     room for three A stages next to it (mirrors gemm_plan_pipeline in csrc/gemm_tc.cuh)."""
     opts = _kc_options(c_in)
     if n_total is not None and n_total == n_tile:
-        total_b = n_total * n_src * n_shift * c_in * 2 + n_tile * 32
-        for kc in opts:
-            a_stage = (kc // 8) * (TILE_M + n_shift - 1) * 16
+        total_b = (n_total * n_src * n_shift * c_in * 2 + n_tile * 32) // 2   # per CTA: half of the columns
+        # (a weight set that leaves no room for a deep ring of full-width A slabs is streamed instead: with 200 KB of
+        # resident weights the 256-channel layers fell back to KC = 16 and ran 40 % slower)
+        for kc in (opts if total_b <= 120 * 1024 else []):
+            a_stage = (kc // 8) * (SUB_M + n_shift - 1) * 16
             if total_b + 3 * a_stage + 256 + reserve <= SMEM_BUDGET:
                 return kc
     return opts[0]
 
 
 def pick_ntile(c_out):
-    """Largest multiple of 16 that divides C_out and leaves two TMEM accumulator stages (<= 128)."""
-    for n in range(min(128, c_out), 15, -16):
+    """Largest multiple of 16 that divides C_out and leaves two TMEM accumulator stages (<= 256 columns)."""
+    for n in range(min(NTILE_MAX, c_out), 15, -16):
         if c_out % n == 0:
             return n
     raise ValueError(f"no N tile for C_out={c_out}")
@@ -67,7 +75,7 @@ def pick_ntile_up(c_out, up):
     n = pick_ntile(c_out)
     if not MULTI_PHASE or n != c_out:
         return n
-    k = max(d for d in range(1, up + 1) if up % d == 0 and c_out * d <= 128)
+    k = max(d for d in range(1, up + 1) if up % d == 0 and c_out * d <= NTILE_MAX)
     return c_out * k
 
 
@@ -154,11 +162,12 @@ def w4_up(w, lp=None):
 
 
 def pack_w4(w4, kc, n_tile, bias_n=None):
-    """[N, S, Q, Ci] fp32 -> per N tile: bf16 images [S][Ci/kc][Q][kc/8][n_tile][8] followed (bias_n
+    """(n_tile here is the PACKING tile: half an N tile of the kernel, see add_gemm.)
+    [N, S, Q, Ci] fp32 -> per N tile: bf16 images [S][Ci/kc][Q][kc/8][n_tile][8] followed (bias_n
     given: fp32 [N]) by the bias image [2][n_tile][8] whose K columns 0 / 1 carry the hi / lo bf16
     halves of the bias (it meets the kernel's constant ones tile, csrc/gemm_tc.cuh)."""
     n, s, q, ci = w4.shape
-    assert n % n_tile == 0 and ci % kc == 0 and kc % 16 == 0 and n_tile % 16 == 0
+    assert n % n_tile == 0 and ci % kc == 0 and kc % 16 == 0 and n_tile % 8 == 0
     x = w4.view(n // n_tile, n_tile, s, q, ci // kc, kc // 8, 8)
     x = x.permute(0, 2, 4, 3, 5, 1, 6).reshape(n // n_tile, -1)  # nt, (s, g, q, j, n, e)
     if bias_n is not None:
@@ -233,10 +242,10 @@ class PackedModel:
         through identity MMAs whose images take N_TILE^2 * 2 bytes of shared memory (csrc/gemm_tc.cuh)."""
         n, s, q, ci = w4.shape
         n_tile = pick_ntile_up(c_out, up) if up > 1 else pick_ntile(c_out)
-        kc = pick_kc(ci, n, n_tile, s, q, reserve=n_tile * n_tile * 2 if (resid and c_out <= 128) else 0)
+        kc = pick_kc(ci, n, n_tile, s, q, reserve=n_tile * n_tile if (resid and c_out <= 128) else 0)
         bias_n = bias.float().repeat(n // c_out) if bias is not None else None  # column n -> channel n % C_out
         self.layers[name] = dict(
-            w_w=self.blob.add(pack_w4(w4, kc, n_tile, bias_n)),
+            w_w=self.blob.add(pack_w4(w4, kc, n_tile // 2, bias_n)),   # per (N tile, half): images, then the bias image
             bias_w=self.blob.add_f32(bias) if bias is not None else -1,
             n_src=s, smin=smin, smax=smin + q - 1, KC=kc, N_TILE=n_tile, N_total=n,
             C_out=c_out, C_in=ci, up=up, slope=slope,

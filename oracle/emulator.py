@@ -42,7 +42,7 @@ def op_outputs(op):
     elif t == _abi.OP_CONVBLOCK:
         for i in range(op.n_out):
             tens(f"out{i}", op.out[i].t)
-        if op.i1:
+        if op.i2:
             tens("cond", op.out[2].t)
     elif t == _abi.OP_PREP:
         outs += [("sig", op.p0, op.B * op.Lp * 4, torch.float32), ("rms", op.p1, op.B * 4, torch.float32)]
@@ -128,7 +128,7 @@ class Emulator:
         if key not in self._wcache:
             nb = op.N_total * op.n_src * n_shift * C_in * 2 + (op.N_total * 32 if has_bias else 0)
             bits = self.blob[op.w_w : op.w_w + nb].view(np.int16)
-            res = unpack_w4(bits, op.N_total, op.n_src, n_shift, C_in, op.KC, op.N_TILE, has_bias)
+            res = unpack_w4(bits, op.N_total, op.n_src, n_shift, C_in, op.KC, op.N_TILE // 2, has_bias)   # packed per half N tile
             self._wcache[key] = res if has_bias else (res, None)
         w4, bias_n = self._wcache[key]
         M = op.m_rows

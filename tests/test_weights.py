@@ -81,7 +81,7 @@ def test_tile_choices():
         assert c % kc == 0 and kc % 16 == 0
     for c in (32, 48, 64, 96, 128, 192, 256, 384, 512, 768, 1536, 2304):
         n = weights.pick_ntile(c)
-        assert c % n == 0 and n % 16 == 0 and n <= 128
+        assert c % n == 0 and n % 16 == 0 and n <= 256
 
 
 def test_binomial_taps_closed_form():
