@@ -215,9 +215,31 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
       for (int i = 0; i < 3; ++i)
         if (c.out[i].t.base && c.out[i].t.nchunks != kCbPlanes) return fail(UV_ERR_INVALID, "fused ConvBlock: outputs must have 64 columns");
       c.reverse = op.i3 & 1;
+      {
+        static const bool bulk_on = !(getenv("UV_CB_BULK") && atoi(getenv("UV_CB_BULK")) == 0);
+        const TensDesc& o = c.out[0].t;
+        c.bulk_out = (bulk_on && c.n_out == 1 && o.base && o.split == 1 && o.nchunks == kCbPlanes && o.esize_log2 == 1 && o.Lh == x.Lh) ? 1 : 0;
+      }
       c.err_flag = p->err_flag;
       c.sched = p->sched + 2 * op_index;
       if (!cb_params_ok(c)) return fail(UV_ERR_INVALID, "fused ConvBlock: unsupported stage geometry");
+      static const bool cb_clk = getenv("UV_CB_CLK") != nullptr;   // debug: where pair 0's MMA thread / epilogue warp spend their clocks
+      if (cb_clk) {
+        long long* d = nullptr;
+        CUDA_TRY(cudaMalloc(&d, 16 * sizeof(long long)));
+        CUDA_TRY(cudaMemset(d, 0, 16 * sizeof(long long)));
+        c.clk = d;
+        CUDA_TRY(convblock_pair_launch(c, p->model->num_sms, s));
+        CUDA_TRY(cudaStreamSynchronize(s));
+        long long h[16];
+        CUDA_TRY(cudaMemcpy(h, d, sizeof(h), cudaMemcpyDeviceToHost));
+        cudaFree(d);
+        const double it = h[3] > 0 ? (double)h[3] : 1.0;
+        fprintf(stderr, "[cb clk] items %lld (stage launches of pair 0): MMA thread per item: wait epi %.0f, wait xa %.0f, issue+commit %.0f, ring %.0f | "
+                        "epilogue warp per item: wait mma %.0f, work s1 %.0f s2 %.0f s3 %.0f (per tile), ring %.0f\n",
+                h[3], h[0] / it, h[1] / it, h[2] / it, h[4] / it, h[8] / it, 3 * h[9] / it, 3 * h[10] / it, 3 * h[11] / it, h[12] / it);
+        break;
+      }
       CUDA_TRY(convblock_pair_launch(c, p->model->num_sms, s));
       break;
     }

@@ -34,7 +34,10 @@ constexpr int kCbRowsOut = 252;      // output rows per CTA and tile
 constexpr int kCbCtaRows = 256;      // accumulator rows per CTA (two sub-tiles)
 constexpr int kCbBufRows = 264;      // buffer rows (256 + halo, padded)
 constexpr int kCbLoadRows = 260;
-constexpr int kCbSlots = 2;
+constexpr int kCbSlots = 2;          // tiles in flight per CTA: working buffer + accumulator pair each
+constexpr int kCbXBufs = 3;          // raw x slabs: the loads run one tile ahead of the slots
+constexpr int kCbXfWarps = 4;        // warps applying PReLU(x) (the GEMM kernel has 2: its register budget is tighter)
+constexpr int kCbThreads = 64 + 32 * kEpiWarps + 32 * kCbXfWarps;
 constexpr uint32_t kCbPlaneBytes = kCbBufRows * 16;
 constexpr uint32_t kCbBufBytes = kCbPlanes * kCbPlaneBytes;     // 33 792
 constexpr int kCbIdentBytes = kCbN * (kCbN / 2) * 2;            // one identity image (add_kc = 64), this CTA's half
@@ -57,8 +60,11 @@ struct CbParams {
   int n_out;
   OutDesc out[3];
   int reverse;
+  int bulk_out;         // host: the single output is a plain tensor of the block's geometry: stage 3 stages its rows in the
+                        // tile's (by then consumed) raw slab and one thread writes them with bulk shared -> global copies
   int* err_flag;
   int* sched;
+  long long* clk;       // debug (UV_CB_CLK=1): [16] clock sums of pair 0's leader: MMA thread 0-5, epilogue warp 2 8-13
 };
 
 struct CbSmem {
@@ -80,18 +86,19 @@ __host__ __device__ inline CbSmem cb_smem_layout(const CbParams& p) {
     off += (L.w_bytes[s] + 127u) & ~127u;
   }
   L.bufs_off = (off + 1023u) & ~1023u;
-  L.bars_off = L.bufs_off + 2u * kCbSlots * kCbBufBytes;   // per slot: raw x, working buffer
+  L.bars_off = L.bufs_off + (uint32_t)(kCbXBufs + kCbSlots) * kCbBufBytes;   // raw x slabs, then the working buffers
   L.total = L.bars_off + 1024;
   return L;
 }
 
 // barriers (same offsets in both CTAs)
 struct CbBars {
-  uint64_t x_full[kCbSlots], x_free[kCbSlots], xa_ready[kCbSlots], mma_done[kCbSlots], epi_done[kCbSlots];
+  uint64_t x_full[kCbXBufs], x_free[kCbXBufs], w_free[kCbSlots], xa_ready[kCbSlots], mma_done[kCbSlots], epi_done[kCbSlots];
   uint64_t w_full;
   uint64_t s_full[kSchedSlots], s_empty[kSchedSlots];
   int s_ring[kSchedSlots];
   uint32_t tmem_ptr;
+  int st_cnt[kCbSlots];   // bulk_out: epilogue warps that have staged their rows of the slot's tile
 };
 static_assert(sizeof(CbBars) <= 1024, "barrier block");
 
@@ -160,6 +167,38 @@ __device__ __forceinline__ void cb_stage_epilogue(const CbParams& P, uint32_t ta
       }
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic stores -> tensor-core reads
+  } else if (P.bulk_out) {
+    // stage 3, staged: the finished rows go to a shared-memory buffer (the caller passes the tile's raw slab; zeros on
+    // padding rows: those rows of the output tensor are zero and stay zero), like c1 / c2; cb_store_rows() writes them out
+    const float a1 = P.out[0].act >= 1 ? P.out[0].a1 : 1.f, a2 = P.out[0].a2;
+    const bool dbl = P.out[0].act == 2;
+    uint8_t* dst = wbuf + (size_t)i * 16;
+#pragma unroll
+    for (int cg = 0; cg < kCbN / 16; ++cg) {
+      tc_ld_wait();
+      if (cg + 1 < kCbN / 16) tc_ld16_issue(taddr + 16u * (cg + 1), r[(cg + 1) & 1]);
+      float v[16];
+#pragma unroll
+      for (int k = 0; k < 16; ++k) v[k] = __uint_as_float(r[cg & 1][k]) * P.scale3;
+      if (a1 != 1.f) {
+#pragma unroll
+        for (int k = 0; k < 16; ++k) v[k] = prelu_t<LE1>(v[k], a1);
+      }
+      if (dbl) {
+#pragma unroll
+        for (int k = 0; k < 16; ++k) v[k] = prelu_t<LE1>(v[k], a2);
+      }
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        uint4 u;
+        __nv_bfloat162* q = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) q[k] = __floats2bfloat162_rn(v[8 * h + 2 * k], v[8 * h + 2 * k + 1]);
+        if (!valid) u = make_uint4(0, 0, 0, 0);
+        *reinterpret_cast<uint4*>(dst + (size_t)(2 * cg + h) * kCbPlaneBytes) = u;
+      }
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic stores -> bulk-copy reads
   } else {
     const bool out_row = valid && i < kCbRowsOut;
     OutPtr op[3];
@@ -189,6 +228,25 @@ __device__ __forceinline__ void cb_stage_epilogue(const CbParams& P, uint32_t ta
   }
 }
 
+// bulk_out: rows [0, 252) of the staging buffer -> the output tensor (one bulk copy per chunk plane); returns when
+// the copies have READ shared memory, i.e. the buffer may be overwritten.  One thread.
+__device__ __forceinline__ void cb_store_rows(const CbParams& P, const uint8_t* wbuf, long long r0) {
+  long long nrows = (long long)P.m_rows - r0;
+  if (nrows > kCbRowsOut) nrows = kCbRowsOut;
+  if (nrows > 0) {
+    const TensDesc& t = P.out[0].t;
+    const uint32_t bytes = (uint32_t)nrows * 16u;
+    char* dst = t.base + (((long long)t.G + r0) << 4);
+    const long long pstride = (long long)t.P << 4;
+    for (int c = 0; c < kCbPlanes; ++c)
+      asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst + c * pstride),
+                   "r"(smem_u32(wbuf + (size_t)c * kCbPlaneBytes)), "r"(bytes)
+                   : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+  }
+}
+
 // Row of the condition tensor that stage 1 adds, fetched before the wait for the accumulator (8 x 16 bytes per row).
 __device__ __forceinline__ void cb_prefetch_cond(const CbParams& P, long long g, float inv_Lh, uint4* pre) {
 #pragma unroll
@@ -202,7 +260,7 @@ __device__ __forceinline__ void cb_prefetch_cond(const CbParams& P, long long g,
   for (int c = 0; c < kCbPlanes; ++c) pre[c] = *reinterpret_cast<const uint4*>(p + c * stride);
 }
 
-__global__ void __launch_bounds__(kGemmThreads, 1) convblock_pair_kernel(const __grid_constant__ CbParams P) {
+__global__ void __launch_bounds__(kCbThreads, 1) convblock_pair_kernel(const __grid_constant__ CbParams P) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = cta_rank_in_cluster();
@@ -213,22 +271,26 @@ __global__ void __launch_bounds__(kGemmThreads, 1) convblock_pair_kernel(const _
   float* film_s = reinterpret_cast<float*>(smem + L.film_off);
   uint8_t* ident = smem + L.ident_off;
   CbBars* B = reinterpret_cast<CbBars*>(smem + L.bars_off);
-  auto xbuf = [&](int s) { return smem + L.bufs_off + (size_t)(2 * s) * kCbBufBytes; };
-  auto wbuf = [&](int s) { return smem + L.bufs_off + (size_t)(2 * s + 1) * kCbBufBytes; };
+  auto xbuf = [&](int x) { return smem + L.bufs_off + (size_t)x * kCbBufBytes; };
+  auto wbuf = [&](int s) { return smem + L.bufs_off + (size_t)(kCbXBufs + s) * kCbBufBytes; };
   constexpr int n_half = kCbN / 2;
   constexpr uint32_t tmem_cols = kCbSlots * 2 * kCbN;   // per slot: two sub-tile accumulators of 64 columns
 
   if (threadIdx.x == 0) {
     const uint32_t pr = leader ? 1u : 0u;
+    for (int x = 0; x < kCbXBufs; ++x) {
+      mbar_init(smem_u32(&B->x_full[x]), 1);
+      mbar_init(smem_u32(&B->x_free[x]), 1);
+    }
     for (int s = 0; s < kCbSlots; ++s) {
-      mbar_init(smem_u32(&B->x_full[s]), 1);
-      mbar_init(smem_u32(&B->x_free[s]), 1);
-      mbar_init(smem_u32(&B->xa_ready[s]), kXfWarps + pr);   // leader: + the peer's relay
+      mbar_init(smem_u32(&B->w_free[s]), 1);
+      mbar_init(smem_u32(&B->xa_ready[s]), kCbXfWarps + pr);   // leader: + the peer's relay
       mbar_init(smem_u32(&B->mma_done[s]), 1);
       mbar_init(smem_u32(&B->epi_done[s]), 2 * kEpiWarps);   // (leader's is used) both CTAs' epilogue warps
     }
     mbar_init(smem_u32(&B->w_full), 1 + pr);
-    const uint32_t ring_readers = (1 + kEpiWarps + kXfWarps) + (2 + kEpiWarps + kXfWarps);
+    B->st_cnt[0] = B->st_cnt[1] = 0;
+    const uint32_t ring_readers = (1 + kEpiWarps + kCbXfWarps) + (2 + kEpiWarps + kCbXfWarps);
     for (int i = 0; i < kSchedSlots; ++i) { mbar_init(smem_u32(&B->s_full[i]), 1); mbar_init(smem_u32(&B->s_empty[i]), ring_readers); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -238,10 +300,10 @@ __global__ void __launch_bounds__(kGemmThreads, 1) convblock_pair_kernel(const _
     reinterpret_cast<uint4*>(ones)[threadIdx.x] = u;
   }
   if (P.film)
-    for (int k = threadIdx.x; k < 2 * kCbN; k += kGemmThreads)
+    for (int k = threadIdx.x; k < 2 * kCbN; k += kCbThreads)
       film_s[k] = P.film[(k < kCbN ? 0 : P.film_C) + (k % kCbN) % P.film_C];
   {  // identity image [8 chunks][n_half][8]: residual channel k -> column k; local column n stands for rank * n_half + n
-    for (int i = threadIdx.x; i < kCbPlanes * n_half; i += kGemmThreads) {
+    for (int i = threadIdx.x; i < kCbPlanes * n_half; i += kCbThreads) {
       const int c = i / n_half, n = i - c * n_half + (int)rank * n_half;
       const int e = n - 8 * c;
       uint32_t w[4] = {0u, 0u, 0u, 0u};
@@ -250,7 +312,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) convblock_pair_kernel(const _
     }
   }
   // slack rows of the buffers are read by the taps of discarded accumulator rows: keep them finite
-  for (uint32_t k = threadIdx.x; k < 2u * kCbSlots * kCbBufBytes / 16; k += kGemmThreads)
+  for (uint32_t k = threadIdx.x; k < (uint32_t)(kCbXBufs + kCbSlots) * kCbBufBytes / 16; k += kCbThreads)
     reinterpret_cast<uint4*>(smem + L.bufs_off)[k] = make_uint4(0, 0, 0, 0);
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   cluster_barrier();
@@ -289,7 +351,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) convblock_pair_kernel(const _
         tile_nxt = atomicAdd(P.sched, 1);
       }
       pdl_wait();
-      uint32_t pf[kCbSlots] = {0, 0};
+      uint32_t pf[kCbXBufs] = {0, 0, 0};
+      int xb = 0;
       for (int k = 0;; ++k) {
         int tile_id;
         if (leader) {
@@ -309,23 +372,23 @@ __global__ void __launch_bounds__(kGemmThreads, 1) convblock_pair_kernel(const _
         if (tile_id < 0) break;
         int tile_nn = tile_nxt;
         if (leader && tile_nxt < P.n_tiles) tile_nn = atomicAdd(P.sched, 1);
-        const int s = k & (kCbSlots - 1);
-        if (k >= kCbSlots) {   // the slot's previous tile has been consumed (stage-3 MMAs complete)
-          mbar_wait(smem_u32(&B->x_free[s]), pf[s], P.err_flag, 10);
-          pf[s] ^= 1;
+        if (k >= kCbXBufs) {   // the tile that used this slab three tiles ago has been consumed (its stage-3 MMAs are complete)
+          mbar_wait(smem_u32(&B->x_free[xb]), pf[xb], P.err_flag, 10);
+          pf[xb] ^= 1;
         }
         const long long row = (long long)P.x_G + tile_r0(tile_id) - H;
         long long nrows = (long long)P.x_P - row;     // never read past the plane (rows past m_rows are masked)
         if (nrows > kCbLoadRows) nrows = kCbLoadRows;
-        const uint32_t fb = smem_u32(&B->x_full[s]);
+        const uint32_t fb = smem_u32(&B->x_full[xb]);
         if (nrows <= 0) {
           mbar_arrive(fb);   // this CTA's part of the last tile lies wholly past the plane: every row is masked
         } else {
           const uint32_t bytes = (uint32_t)nrows * 16u;
           mbar_expect_tx(fb, bytes * kCbPlanes);
-          const uint32_t dst = smem_u32(xbuf(s));
+          const uint32_t dst = smem_u32(xbuf(xb));
           for (int c = 0; c < kCbPlanes; ++c) bulk_g2s(dst + c * kCbPlaneBytes, P.x_base + (((long long)c * P.x_P + row) << 4), bytes, fb);
         }
+        if (++xb == kCbXBufs) xb = 0;
         tile = tile_nxt;
         tile_nxt = tile_nn;
       }
@@ -354,11 +417,17 @@ __global__ void __launch_bounds__(kGemmThreads, 1) convblock_pair_kernel(const _
         tc_fence_after();
         uint32_t px[kCbSlots] = {0, 0}, pe[kCbSlots] = {0, 0};
         bool used[kCbSlots] = {false, false};
+        const bool ck = P.clk != nullptr && blockIdx.x == 0;
+        long long c_wait_epi = 0, c_wait_xa = 0, c_issue = 0, c_items = 0, t_prev = ck ? clock64() : 0, c_ring = 0;
+        int xb0 = 0;   // x slab of the round's first tile (the second one uses the next)
         for (;;) {
           int tl[kCbSlots];
           tl[0] = next_tile();
           if (tl[0] < 0) break;
           tl[1] = next_tile();
+          if (ck) { const long long t = clock64(); c_ring += t - t_prev; t_prev = t; }
+          const int xbs[kCbSlots] = {xb0, xb0 + 1 == kCbXBufs ? 0 : xb0 + 1};
+          xb0 = (xb0 + 2) % kCbXBufs;
 #pragma unroll
           for (int st = 0; st < 3; ++st) {
             for (int s = 0; s < kCbSlots; ++s) {
@@ -367,11 +436,13 @@ __global__ void __launch_bounds__(kGemmThreads, 1) convblock_pair_kernel(const _
                 mbar_wait(smem_u32(&B->epi_done[s]), pe[s], P.err_flag, 14);
                 pe[s] ^= 1;
               }
+              if (ck) { const long long t = clock64(); c_wait_epi += t - t_prev; t_prev = t; }
               used[s] = true;
               if (st == 0) {   // PReLU(x) is in the working buffer of both CTAs
                 mbar_wait(smem_u32(&B->xa_ready[s]), px[s], P.err_flag, 13);
                 px[s] ^= 1;
               }
+              if (ck) { const long long t = clock64(); c_wait_xa += t - t_prev; t_prev = t; }
               tc_fence_after();
               const uint32_t d0 = tmem_base + (uint32_t)(s * 2) * kCbN, d1 = d0 + kCbN;
               const uint32_t a_lo0 = (smem_u32(wbuf(s)) >> 4) | ((lbo_a >> 4) << 16);
@@ -401,7 +472,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) convblock_pair_kernel(const _
               }
               if (st == 2) {
                 // residual: out row i = flat R0 + i = raw slab row i + H, through the identity image
-                uint32_t al = ((smem_u32(xbuf(s)) >> 4) | ((lbo_a >> 4) << 16)) + (uint32_t)H;
+                uint32_t al = ((smem_u32(xbuf(xbs[s])) >> 4) | ((lbo_a >> 4) << 16)) + (uint32_t)H;
                 uint32_t bl = (smem_u32(ident) >> 4) | ((lbo_b >> 4) << 16);
                 for (int kk = 0; kk < (kCbN >> 4); ++kk) {
                   tc_mma2_bf16(d0, dsc(al), dsc(bl), idesc, 1);
@@ -411,11 +482,17 @@ __global__ void __launch_bounds__(kGemmThreads, 1) convblock_pair_kernel(const _
                 }
               }
               tc_commit2(smem_u32(&B->mma_done[s]));
-              if (st == 2) tc_commit2(smem_u32(&B->x_free[s]));
+              if (st == 2) {   // the tile's working buffer and raw slab may be refilled
+                tc_commit2(smem_u32(&B->w_free[s]));
+                if (!P.bulk_out) tc_commit2(smem_u32(&B->x_free[xbs[s]]));   // (bulk_out: the slab then stages the output rows and
+                                                                             // is freed by the thread that stores them)
+              }
+              if (ck) { const long long t = clock64(); c_issue += t - t_prev; t_prev = t; ++c_items; }
             }
           }
           if (tl[1] < 0) break;
         }
+        if (ck) { P.clk[0] = c_wait_epi; P.clk[1] = c_wait_xa; P.clk[2] = c_issue; P.clk[3] = c_items; P.clk[4] = c_ring; }
       } else {
         // ============================== relay: this CTA's weights / activated slabs are in place
         mbar_wait(smem_u32(&B->w_full), 0, P.err_flag, 11);
@@ -436,7 +513,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) convblock_pair_kernel(const _
     const int w = warp - (2 + kEpiWarps);
     const bool le1 = P.a_slope <= 1.f;
     int ss = 0;
-    uint32_t sp = 0, pxf[kCbSlots] = {0, 0};
+    uint32_t sp = 0, pxf[kCbXBufs] = {0, 0, 0}, pwf[kCbSlots] = {0, 0};
+    int xb = 0;
     for (int k = 0;; ++k) {
       mbar_wait(smem_u32(&B->s_full[ss]), sp, P.err_flag, 8);
       const int tile = *reinterpret_cast<const volatile int*>(B->s_ring + ss);
@@ -445,11 +523,16 @@ __global__ void __launch_bounds__(kGemmThreads, 1) convblock_pair_kernel(const _
       if (++ss == kSchedSlots) { ss = 0; sp ^= 1; }
       if (tile < 0) break;
       const int s = k & (kCbSlots - 1);
-      mbar_wait(smem_u32(&B->x_full[s]), pxf[s], P.err_flag, 12);
-      pxf[s] ^= 1;
-      const uint4* src = reinterpret_cast<const uint4*>(xbuf(s));
+      mbar_wait(smem_u32(&B->x_full[xb]), pxf[xb], P.err_flag, 12);
+      pxf[xb] ^= 1;
+      if (k >= kCbSlots) {   // the slot's previous tile no longer reads the working buffer
+        mbar_wait(smem_u32(&B->w_free[s]), pwf[s], P.err_flag, 15);
+        pwf[s] ^= 1;
+      }
+      const uint4* src = reinterpret_cast<const uint4*>(xbuf(xb));
       uint4* dst = reinterpret_cast<uint4*>(wbuf(s));
-      constexpr int kStep = 32 * kXfWarps;
+      if (++xb == kCbXBufs) xb = 0;
+      constexpr int kStep = 32 * kCbXfWarps;
       constexpr int nvec = kCbPlanes * kCbBufRows;
       for (int i0 = w * 32 + lane; i0 < nvec; i0 += 4 * kStep) {
         uint4 u[4];
@@ -491,12 +574,18 @@ __global__ void __launch_bounds__(kGemmThreads, 1) convblock_pair_kernel(const _
       return t;
     };
     bool first = true;
+    const bool ck = P.clk != nullptr && blockIdx.x == 0 && warp == 2 && lane == 0;
+    long long c_wait = 0, c_work[3] = {0, 0, 0}, c_ring = 0, t_prev = ck ? clock64() : 0;
+    int xb0 = 0;   // x slab of the round's first tile, as in the MMA issuer
     for (;;) {
       int tl[kCbSlots];
       tl[0] = next_tile();
       if (tl[0] < 0) break;
       tl[1] = next_tile();
-      if (first) { pdl_wait(); first = false; }   // condition loads / output stores touch the predecessors' tensors
+      const int xbs[kCbSlots] = {xb0, xb0 + 1 == kCbXBufs ? 0 : xb0 + 1};
+      xb0 = (xb0 + 2) % kCbXBufs;
+      if (first) { pdl_wait(); first = false; }
+      if (ck) { const long long t = clock64(); c_ring += t - t_prev; t_prev = t; }   // condition loads / output stores touch the predecessors' tensors
 #pragma unroll
       for (int st = 0; st < 3; ++st) {
         for (int s = 0; s < kCbSlots; ++s) {
@@ -508,9 +597,12 @@ __global__ void __launch_bounds__(kGemmThreads, 1) convblock_pair_kernel(const _
           if (st == 0) cb_prefetch_cond(P, g, inv_Lh, pre);
           mbar_wait(smem_u32(&B->mma_done[s]), pm[s], P.err_flag, 12);
           pm[s] ^= 1;
+          if (ck) { const long long t = clock64(); c_wait += t - t_prev; t_prev = t; }
           tc_fence_after();
           const uint32_t taddr = tmem_base + (uint32_t)(s * 2 + sub) * kCbN + ((uint32_t)(quarter * 32) << 16);
-          uint8_t* wb = wbuf(s);
+          // stages 1 / 2 write the working buffer; a staged stage 3 writes the tile's raw slab (its last reader, the
+          // residual MMA, has completed)
+          uint8_t* wb = st == 2 && P.bulk_out ? xbuf(xbs[s]) : wbuf(s);
           if (le1) {
             if (st == 0) cb_stage_epilogue<0, true>(P, taddr, wb, film_s, i, g, inv_Lh, H - h[0], pre);
             else if (st == 1) cb_stage_epilogue<1, true>(P, taddr, wb, film_s, i, g, inv_Lh, 0, pre);
@@ -523,10 +615,24 @@ __global__ void __launch_bounds__(kGemmThreads, 1) convblock_pair_kernel(const _
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive_cl(epi_cl0 + 8u * s);
+          if (st == 2 && P.bulk_out && lane == 0) {
+            // the last warp to have staged its rows writes the tile out and hands the slab back to the loads
+            __threadfence_block();
+            if (atomicAdd(&B->st_cnt[s], 1) == kEpiWarps - 1) {
+              B->st_cnt[s] = 0;
+              __threadfence_block();
+              asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+              cb_store_rows(P, wb, r0);
+              mbar_arrive(smem_u32(&B->x_free[xbs[s]]));
+            }
+          }
+          __syncwarp();
+          if (ck) { const long long t = clock64(); c_work[st] += t - t_prev; t_prev = t; }
         }
       }
       if (tl[1] < 0) break;
     }
+    if (ck) { P.clk[8] = c_wait; P.clk[9] = c_work[0]; P.clk[10] = c_work[1]; P.clk[11] = c_work[2]; P.clk[12] = c_ring; }
   }
 
   tc_fence_before();
@@ -568,7 +674,7 @@ inline cudaError_t convblock_pair_launch(CbParams p, int num_sms, cudaStream_t s
   if (pairs < 1) pairs = 1;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(pairs * kPairCtas);
-  cfg.blockDim = dim3(kGemmThreads);
+  cfg.blockDim = dim3(kCbThreads);
   cfg.dynamicSmemBytes = 227 * 1024;   // the whole SM, like the GEMM kernel (never co-resident with a GRU CTA)
   cfg.stream = stream;
   cudaLaunchAttribute at[2];
