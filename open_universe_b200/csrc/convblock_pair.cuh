@@ -534,20 +534,20 @@ __global__ void __launch_bounds__(kCbThreads, 1) convblock_pair_kernel(const __g
       if (++xb == kCbXBufs) xb = 0;
       constexpr int kStep = 32 * kCbXfWarps;
       constexpr int nvec = kCbPlanes * kCbBufRows;
-      for (int i0 = w * 32 + lane; i0 < nvec; i0 += 4 * kStep) {
-        uint4 u[4];
+      constexpr int kPer = (nvec + kStep - 1) / kStep;   // 17 vectors per thread, every load in flight before the first
+      const int i0 = w * 32 + lane;                      // store: the pass is latency bound (the MMAs keep shared memory busy)
+      uint4 u[kPer];
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-          if (i0 + j * kStep < nvec) u[j] = src[i0 + j * kStep];
+      for (int j = 0; j < kPer; ++j)
+        if (i0 + j * kStep < nvec) u[j] = src[i0 + j * kStep];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          if (i0 + j * kStep < nvec) {
-            u[j].x = prelu_bf16x2(u[j].x, P.a_slope, le1);
-            u[j].y = prelu_bf16x2(u[j].y, P.a_slope, le1);
-            u[j].z = prelu_bf16x2(u[j].z, P.a_slope, le1);
-            u[j].w = prelu_bf16x2(u[j].w, P.a_slope, le1);
-            dst[i0 + j * kStep] = u[j];
-          }
+      for (int j = 0; j < kPer; ++j) {
+        if (i0 + j * kStep < nvec) {
+          u[j].x = prelu_bf16x2(u[j].x, P.a_slope, le1);
+          u[j].y = prelu_bf16x2(u[j].y, P.a_slope, le1);
+          u[j].z = prelu_bf16x2(u[j].z, P.a_slope, le1);
+          u[j].w = prelu_bf16x2(u[j].w, P.a_slope, le1);
+          dst[i0 + j * kStep] = u[j];
         }
       }
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -556,9 +556,7 @@ __global__ void __launch_bounds__(kCbThreads, 1) convblock_pair_kernel(const __g
     }
   } else {
     // ============================== stage epilogues
-    bool le1 = P.slope2 <= 1.f && P.slope3 <= 1.f;
-    for (int o = 0; o < 3; ++o)
-      if (o < P.n_out && ((P.out[o].act >= 1 && !(P.out[o].a1 <= 1.f)) || (P.out[o].act == 2 && !(P.out[o].a2 <= 1.f)))) le1 = false;
+    // (every PReLU slope of the block is <= 1: cb_params_ok; PReLU(v) = max(v, a v))
     const int sub = (warp - 2) >> 2, quarter = warp & 3;
     const int i = sub * kSubM + quarter * 32 + lane;
     const float inv_Lh = 1.f / (float)P.Lh;
@@ -603,15 +601,9 @@ __global__ void __launch_bounds__(kCbThreads, 1) convblock_pair_kernel(const __g
           // stages 1 / 2 write the working buffer; a staged stage 3 writes the tile's raw slab (its last reader, the
           // residual MMA, has completed)
           uint8_t* wb = st == 2 && P.bulk_out ? xbuf(xbs[s]) : wbuf(s);
-          if (le1) {
-            if (st == 0) cb_stage_epilogue<0, true>(P, taddr, wb, film_s, i, g, inv_Lh, H - h[0], pre);
-            else if (st == 1) cb_stage_epilogue<1, true>(P, taddr, wb, film_s, i, g, inv_Lh, 0, pre);
-            else cb_stage_epilogue<2, true>(P, taddr, wb, film_s, i, g, inv_Lh, 0, pre);
-          } else {
-            if (st == 0) cb_stage_epilogue<0, false>(P, taddr, wb, film_s, i, g, inv_Lh, H - h[0], pre);
-            else if (st == 1) cb_stage_epilogue<1, false>(P, taddr, wb, film_s, i, g, inv_Lh, 0, pre);
-            else cb_stage_epilogue<2, false>(P, taddr, wb, film_s, i, g, inv_Lh, 0, pre);
-          }
+          if (st == 0) cb_stage_epilogue<0, true>(P, taddr, wb, film_s, i, g, inv_Lh, H - h[0], pre);
+          else if (st == 1) cb_stage_epilogue<1, true>(P, taddr, wb, film_s, i, g, inv_Lh, 0, pre);
+          else cb_stage_epilogue<2, true>(P, taddr, wb, film_s, i, g, inv_Lh, 0, pre);
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive_cl(epi_cl0 + 8u * s);
@@ -659,6 +651,10 @@ inline bool cb_params_ok(const CbParams& p) {
   }
   if (H > 4 || p.x_G < H || kCbCtaRows - kCbRowsOut < 2 * ((p.n_shift[1] - 1) / 2 + (p.n_shift[2] - 1) / 2)) return false;
   if (p.film && (p.film_C <= 0 || kCbN % p.film_C)) return false;
+  // the epilogues compute PReLU(v) as max(v, a v): slopes <= 1 only (the host compiler keeps other blocks unfused)
+  if (!(p.slope2 <= 1.f) || !(p.slope3 <= 1.f)) return false;
+  for (int o = 0; o < p.n_out && o < 3; ++o)
+    if ((p.out[o].act >= 1 && !(p.out[o].a1 <= 1.f)) || (p.out[o].act == 2 && !(p.out[o].a2 <= 1.f))) return false;
   return cb_smem_layout(p).total <= 227 * 1024;
 }
 

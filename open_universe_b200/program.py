@@ -465,6 +465,8 @@ def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_
             and h_raw.dtype == DT_BF16 and (cond is None or (cond.dtype == DT_BF16 and (cond.nch, cond.split, cond.Lh, cond.P) == (h_raw.nch, h_raw.split, h_raw.Lh, h_raw.P)))
             and all(t.dtype == DT_BF16 and (t.nch == 8 or (s2d and t.nch == 4 and t.split == 2)) for t, *_ in v_outs)
             and (cond_out is None or (cond_out.dtype == DT_BF16 and cond_out.nch == 8))
+            # the fused epilogues compute PReLU(v) as max(v, a v)
+            and s2 <= 1.0 and s3 <= 1.0 and all((act < 1 or a1 <= 1.0) and (act < 2 or a2 <= 1.0) for _, act, a1, a2 in v_outs)
         )
         sink = _PartSink(pg) if fuse else pg
         g1 = sink.gemm(name + ".conv1", name + ".conv1" + sfx, h_act if h_act is not None else h_raw, lev, lev.L, outs, step, add1=cond,
