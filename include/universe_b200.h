@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define UV_ABI_VERSION 8
+#define UV_ABI_VERSION 9
 
 typedef enum {
   UV_OK = 0,
@@ -77,12 +77,17 @@ typedef enum {
   UV_OP_INIT_X = 8,   /* x = sigma_0 * z_0               (universe.py:326)                            */
   UV_OP_POST = 9,     /* crop, keep_rms, peak normalise  (universe.py:349-357)                        */
   UV_OP_FILM = 10,    /* noise-level embedding + FiLM table (sigma_block.py, score.py:109,208)        */
-  UV_OP_CONVBLOCK = 11 /* fused ConvBlock of a 64-column level (C = 64, or C = 32 stored phase-split by 2): PReLU -> conv1 ->
+  UV_OP_CONVBLOCK = 11, /* fused ConvBlock of a 64-column level (C = 64, or C = 32 stored phase-split by 2): PReLU -> conv1 ->
                         * [+cond] * f0 -> [FiLM] -> PReLU -> conv2 -> PReLU -> conv3 -> (. + x) * scale  (blocks.py:387-403).
                         * a = x (raw), a_slope = slope in front of conv1, w_w / p0 / p1 = the three convs' packed weights
                         * (i0 bit s: conv s has a bias; i1 byte s: n_src | n_shift << 4 of conv s), add1 = condition,
                         * film (C = its channel count), f1 / f2 = slopes in front of conv2 / conv3, out[0..n_out) = block
                         * outputs, i2 = 1: out[2] is the stage-1 output (the conditioner's conditioning signal)          */
+  UV_OP_AUX = 12       /* aux_to_wav fused with the state initialisation of use_aux_signal / warm_start (universe_gan.py:
+                        * 119-128,147-151; bigvgan/alias_free_act.py:8-30, snake.py:53-64; universe.py:317-331):
+                        * a = y_hat (bf16 planes, C channels), p0 = x [B][Lp], p3 = weights f32 (alpha or slope [C] |
+                        * up kernel [2][H] | down kernel [F] | conv [C][3] | bias), i3 = 0 snake / 1 PReLU, f0 = sigma_n
+                        * (0: x = aux_to_wav(y_hat)), i0 = n (the draw added: x += sigma_n z_n), i1 / i2 as INIT_X   */
 } uv_op_type;
 
 /* One record per kernel launch.  Offsets named *_w index the model's weight
@@ -153,9 +158,16 @@ size_t uv_plan_arena_bytes(const uv_plan* p);
 
 /* One enhance() pass.  Device pointers: mix [B][T] f32, noise [n_steps][B][Lp]
  * f32, out [B][T] f32, dbg_net (optional) [n_steps][B][Lp] f32 per-step network
- * outputs.  coef: host array of n_steps uv_step_coef. keep_rms as in enhance(). */
+ * outputs.  coef: host array of n_steps uv_step_coef. keep_rms as in enhance().
+ * noise = the sampler's draws in the reference's order (randn, universe.py:39-41, called :326,338): parity mode,
+ * the caller draws them with torch's generator.  noise == NULL (after uv_set_noise_seed): throughput mode, the
+ * kernels draw z[step][utterance][sample] themselves (Philox4x32-10 keyed by the seed, Box-Muller; a pure function
+ * of (seed, step, utterance, sample), restated on the CPU in oracle/philox.py): same distribution, another stream. */
 int uv_enhance(uv_plan* p, const float* mix, const float* noise, float* out, float* dbg_net,
                const uv_step_coef* coef, int keep_rms, void* stream);
+
+/* Key of the in-kernel draws of the following calls made with noise == NULL (uv_enhance, uv_run_ops, ...). */
+int uv_set_noise_seed(uv_plan* p, unsigned long long seed);
 
 /* Waits for `stream` and reports what the calls queued so far left behind: UV_ERR_KERNEL if a device-side
  * watchdog fired (a pipeline barrier that never completed; the code is in uv_last_error()), UV_ERR_CUDA for
@@ -182,6 +194,13 @@ int uv_profile_ops(uv_plan* p, const float* mix, const float* noise, float* out,
  * end time in ms relative to the start of the pass: the timeline that shows what overlaps the GRU recurrences. */
 int uv_trace_ops(uv_plan* p, const float* mix, const float* noise, float* out, float* dbg_net,
                  const uv_step_coef* coef, int keep_rms, float* t_start_ms, float* t_end_ms);
+
+/* Ensemble statistic "signal_median" (reference utils/stats.py:22-66, used by universe.py:359-367): signal
+ * [n_members][batch][samples] f32 -> out [batch][samples]: the member whose index equals the sorted position that
+ * most often holds the member closest to n_members / 2.  Device pointers; scratch = batch * 32 ints (the call
+ * clears it); n_members <= 32; allocates nothing. */
+int uv_signal_median(const float* signal, int n_members, int batch, long long samples, float* out, int* scratch,
+                     void* stream);
 
 /* Number of kernel launches one uv_enhance() replays (for bench accounting). */
 int uv_plan_num_launches(const uv_plan* p);

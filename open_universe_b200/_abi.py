@@ -2,12 +2,12 @@
 lives in `_native.py`)."""
 import ctypes as C
 
-UV_ABI_VERSION = 8
+UV_ABI_VERSION = 9
 
-OP_PREP, OP_MEL, OP_MEL_FIN, OP_CONV_IN, OP_GEMM, OP_GRU, OP_CONV_OUT, OP_INIT_X, OP_POST, OP_FILM, OP_CONVBLOCK = range(1, 12)
+OP_PREP, OP_MEL, OP_MEL_FIN, OP_CONV_IN, OP_GEMM, OP_GRU, OP_CONV_OUT, OP_INIT_X, OP_POST, OP_FILM, OP_CONVBLOCK, OP_AUX = range(1, 13)
 OP_NAMES = {
     1: "PREP", 2: "MEL", 3: "MEL_FIN", 4: "CONV_IN", 5: "GEMM", 6: "GRU", 7: "CONV_OUT", 8: "INIT_X", 9: "POST", 10: "FILM",
-    11: "CONVBLOCK",
+    11: "CONVBLOCK", 12: "AUX",
 }
 
 DT_BF16, DT_F32 = 1, 2

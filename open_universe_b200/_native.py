@@ -19,7 +19,7 @@ EXPORTS = [
     "uv_abi_version", "uv_sizeof_op", "uv_last_error", "uv_model_create", "uv_model_destroy", "uv_plan_create",
     "uv_plan_destroy", "uv_plan_arena_bytes", "uv_enhance", "uv_run_ops", "uv_arena_read", "uv_arena_write",
     "uv_plan_num_launches", "uv_profile_ops", "uv_plan_arena_ptr", "uv_trace_ops", "uv_plan_status",
-    "uv_mel_spec_static",
+    "uv_mel_spec_static", "uv_set_noise_seed", "uv_signal_median",
 ]
 
 
@@ -83,6 +83,8 @@ def lib():
     L.uv_arena_write.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
     L.uv_plan_status.argtypes = [C.c_void_p, C.c_void_p]
     L.uv_mel_spec_static.argtypes = [C.c_void_p, C.POINTER(_abi.UvMelDesc), C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+    L.uv_set_noise_seed.argtypes = [C.c_void_p, C.c_ulonglong]
+    L.uv_signal_median.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_longlong, C.c_void_p, C.c_void_p, C.c_void_p]
     L.uv_plan_arena_ptr.argtypes = [C.c_void_p]
     L.uv_plan_arena_ptr.restype = C.c_void_p
     if L.uv_abi_version() != _abi.UV_ABI_VERSION:
@@ -152,6 +154,10 @@ class NativePlan:
         _check(lib().uv_enhance(self.handle, mix_ptr, noise_ptr, out_ptr, dbg_ptr, self._coefs(coefs),
                                 1 if keep_rms else 0, stream_ptr), "uv_enhance")
 
+    def set_noise_seed(self, seed):
+        """Key of the in-kernel sampler draws of the following calls that pass noise_ptr = None."""
+        _check(lib().uv_set_noise_seed(self.handle, int(seed) & 0xFFFFFFFFFFFFFFFF), "uv_set_noise_seed")
+
     def status(self, stream_ptr=None):
         """Waits for the stream; raises if a device watchdog fired or a CUDA error is pending."""
         _check(lib().uv_plan_status(self.handle, stream_ptr), "uv_plan_status")
@@ -204,3 +210,22 @@ class NativePlan:
             self.close()
         except Exception:
             pass
+
+
+def signal_median(signal):
+    """Ensemble statistic on the device (uv_signal_median; reference utils/stats.py:22-66).
+    signal: CUDA float tensor (ensemble, batch, ...) -> (batch, ...)."""
+    import torch
+
+    if not signal.is_cuda:
+        raise RuntimeError("open_universe_b200 runs only on a CUDA device")
+    shape = signal.shape
+    E, B = int(shape[0]), int(shape[1])
+    flat = signal.reshape(E, B, -1).to(torch.float32).contiguous()
+    S = int(flat.shape[2])
+    out = torch.empty((B, S), dtype=torch.float32, device=signal.device)
+    scratch = torch.empty((B, 32), dtype=torch.int32, device=signal.device)
+    with torch.cuda.device(signal.device):
+        _check(lib().uv_signal_median(flat.data_ptr(), E, B, S, out.data_ptr(), scratch.data_ptr(),
+                                      torch.cuda.current_stream(signal.device).cuda_stream), "uv_signal_median")
+    return out.reshape(shape[1:]).to(signal.dtype)

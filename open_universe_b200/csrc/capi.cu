@@ -12,6 +12,7 @@
 #include "gru.cuh"
 #include "convblock_pair.cuh"
 #include "small_ops.cuh"
+#include "aux_ops.cuh"
 
 using namespace uv;
 
@@ -79,6 +80,8 @@ struct uv_plan {
   bool use_graph = false;
   bool lazy_graph = false;        // use_graph == 2: the first uv_enhance() runs eagerly, the second captures the graph
   long long n_calls = 0;
+  unsigned long long noise_seed = 0;   // uv_set_noise_seed: key of the in-kernel draws of calls made with noise == NULL
+  bool seeded = false;
 };
 
 extern "C" int uv_abi_version(void) { return UV_ABI_VERSION; }
@@ -96,6 +99,7 @@ extern "C" int uv_model_create(uv_model** out, const void* weights, size_t nbyte
   // function attributes are per device: every model (= device) sets them, no process-wide "done" flags
   CUDA_TRY(gemm_set_attributes());
   CUDA_TRY(convblock_pair_set_attributes());
+  CUDA_TRY(cudaFuncSetAttribute(aux_to_wav_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   CUDA_TRY(cudaFuncSetAttribute(gru_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   CUDA_TRY(cudaFuncSetAttribute(mel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMelMaxSmem));
   char* blob = nullptr;
@@ -277,7 +281,7 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
     case UV_OP_INIT_X: {
       const long long n = (long long)op.B * op.Lp;
       const int B_total = op.i2 > 0 ? op.i2 : op.B;   // i1 / i2: first utterance of this lane / utterances of the whole call
-      CUDA_TRY(launch_pdl(init_x_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, s, p->io_dev, n, ((long long)op.i0 * B_total + op.i1) * op.Lp, op.f0,
+      CUDA_TRY(launch_pdl(init_x_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, s, p->io_dev, n, op.i0, op.i1, B_total, op.Lp, op.f0,
                                                                 aptr<float>(p, op.p0)));
       break;
     }
@@ -288,6 +292,25 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
                                                                   wptr<const float>(p, op.p4), aptr<float>(p, op.p0),
                                                                   aptr<const StepCoef>(p, op.p1), op.i0, p->io_dev, op.i1,
                                                                   op.i2 > 0 ? op.i2 : op.B, op.i3 & 1));
+      break;
+    }
+    case UV_OP_AUX: {
+      AuxParams a;
+      a.a = to_desc(p, op.a);
+      a.B = op.B; a.Lp = op.Lp; a.C = op.C;
+      a.mode = op.i3; a.KU = op.H; a.KD = op.F;
+      a.wts = wptr<const float>(p, op.p3);
+      a.x = aptr<float>(p, op.p0);
+      a.sigma = op.f0; a.step = op.i0;
+      a.b_off = op.i1; a.B_total = op.i2 > 0 ? op.i2 : op.B;
+      a.io = p->io_dev;
+      const size_t smem = aux_smem_bytes(a.C, a.KU, a.KD);
+      if (a.C % 8 || a.C > kEdgeMaxC || a.a.split > 1 || a.mode < 0 || a.mode > 1 || a.KU > kAuxMaxKU || a.KD > kAuxMaxKD ||
+          (a.mode == 0 && (a.KU < 1 || a.KD < 2)) || smem > 200 * 1024)
+        return fail(UV_ERR_INVALID, "aux_to_wav: unsupported geometry");
+      const int tiles = (a.Lp + kAuxTile - 1) / kAuxTile;
+      aux_to_wav_kernel<<<dim3((unsigned)(a.B * tiles)), 256, smem, s>>>(a);
+      CUDA_TRY(cudaGetLastError());
       break;
     }
     case UV_OP_POST:
@@ -537,7 +560,8 @@ static int check_err_flag(uv_plan* p) {
 // pending, so batch k+1 can be queued behind batch k.
 static int stage_io(uv_plan* p, const float* mix, const float* noise, float* out, float* dbg,
                     const uv_step_coef* coef, int keep_rms, cudaStream_t s) {
-  if (!mix || !noise || !out || !coef) return fail(UV_ERR_INVALID, "uv_enhance: null pointer");
+  if (!mix || !out || !coef) return fail(UV_ERR_INVALID, "uv_enhance: null pointer");
+  if (!noise && !p->seeded) return fail(UV_ERR_INVALID, "uv_enhance: noise == NULL needs uv_set_noise_seed() first");
   int rc = check_err_flag(p);   // outcome of the previous calls
   if (rc) return rc;
   const int slot = p->stage_next;
@@ -546,6 +570,7 @@ static int stage_io(uv_plan* p, const float* mix, const float* noise, float* out
   char* h = p->stage_host + (size_t)slot * p->stage_bytes;
   IoTable* io = reinterpret_cast<IoTable*>(h);
   io->mix = mix; io->noise = noise; io->out = out; io->dbg = dbg;
+  io->seed = p->noise_seed; io->pad_ = 0;
   CUDA_TRY(cudaMemcpyAsync(p->io_dev, io, sizeof(IoTable), cudaMemcpyHostToDevice, s));
   if (!p->coef_offs.empty()) {
     char* c = h + sizeof(IoTable);
@@ -588,6 +613,28 @@ extern "C" int uv_enhance(uv_plan* p, const float* mix, const float* noise, floa
   } else if ((rc = enqueue_range(p, 0, (int)p->ops.size(), s, true))) {
     return rc;
   }
+  return UV_OK;
+}
+
+extern "C" int uv_set_noise_seed(uv_plan* p, unsigned long long seed) {
+  if (!p) return fail(UV_ERR_INVALID, "uv_set_noise_seed: null plan");
+  std::lock_guard<std::mutex> lock(p->mu);
+  p->noise_seed = seed;
+  p->seeded = true;
+  return UV_OK;
+}
+
+extern "C" int uv_signal_median(const float* signal, int n_members, int batch, long long samples, float* out, int* scratch, void* stream) {
+  if (!signal || !out || !scratch) return fail(UV_ERR_INVALID, "uv_signal_median: null pointer");
+  if (n_members < 1 || n_members > kMedMaxE || batch < 1 || batch > 65535 || samples < 1)
+    return fail(UV_ERR_INVALID, "uv_signal_median: 1..32 members, 1..65535 rows");
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  CUDA_TRY(cudaMemsetAsync(scratch, 0, (size_t)batch * kMedMaxE * sizeof(int), s));
+  long long nb = (samples + 255) / 256;
+  if (nb > 1184) nb = 1184;   // 8 CTAs per SM
+  signal_median_votes_kernel<<<dim3((unsigned)nb, (unsigned)batch), 256, 0, s>>>(signal, n_members, batch, samples, scratch);
+  signal_median_gather_kernel<<<dim3((unsigned)nb, (unsigned)batch), 256, 0, s>>>(signal, n_members, batch, samples, scratch, out);
+  CUDA_TRY(cudaGetLastError());
   return UV_OK;
 }
 

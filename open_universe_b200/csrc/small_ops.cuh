@@ -8,10 +8,46 @@ namespace uv {
 
 struct IoTable {
   const float* mix;    // [B][T]
-  const float* noise;  // [n_steps][B][Lp]
+  const float* noise;  // [n_steps][B][Lp]; null = the sampler draws are generated in the kernels (unit_normal below)
   float* out;          // [B][T]
   float* dbg;          // [n_steps][B][Lp] or null
+  unsigned long long seed;   // key of the in-kernel draws (uv_set_noise_seed)
+  unsigned long long pad_;
 };
+
+// ---------------------------------------------------------------- in-kernel sampler noise ("throughput mode")
+// z[step][utterance][sample] ~ N(0, 1), a pure function of (seed, step, utterance, sample): Philox4x32-10 keyed by the
+// seed on the counter (sample / 4, utterance, step, tag), four normals per block by Box-Muller.  Independent of the
+// launch geometry, of the lane split and of which rank owns the utterance.  Stands for the reference's
+// torch.randn draws (universe.py:39-41) when the caller does not need torch's own stream; oracle/philox.py is the
+// CPU restatement the GPU test checks it against.
+__device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t* out) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+    c0 = hi1 ^ c1 ^ k0;
+    c1 = lo1;
+    c2 = hi0 ^ c3 ^ k1;
+    c3 = lo0;
+    k0 += 0x9E3779B9u;
+    k1 += 0xBB67AE85u;
+  }
+  out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+constexpr uint32_t kNoiseTag = 0x554E4956u;   // "UNIV"
+__device__ __forceinline__ float unit_normal(unsigned long long seed, int step, int utt, int l) {
+  uint32_t r[4];
+  philox4x32_10((uint32_t)l >> 2, (uint32_t)utt, (uint32_t)step, kNoiseTag, (uint32_t)seed, (uint32_t)(seed >> 32), r);
+  const int pair = (l >> 1) & 1;
+  // 24-bit uniforms in (0, 1): (r >> 8) + 0.5 scaled by 2^-24
+  const float u1 = ((float)(r[2 * pair] >> 8) + 0.5f) * 5.9604644775390625e-8f;
+  const float u2 = ((float)(r[2 * pair + 1] >> 8) + 0.5f) * 5.9604644775390625e-8f;
+  const float rad = sqrtf(-2.f * logf(u1));
+  float sn, cs;
+  sincospif(2.f * u2, &sn, &cs);
+  return rad * ((l & 1) ? sn : cs);
+}
 
 constexpr int kEdgeMaxC = 128;   // channels of the 1 <-> C edge convs (32 / 48 in the reference configs)
 
@@ -269,11 +305,20 @@ __global__ void __launch_bounds__(256) conv_in_kernel(const float* __restrict__ 
 }
 
 // ---------------------------------------------------------------- INIT_X   x = sigma_0 * z_0 (universe.py:326)
-__global__ void __launch_bounds__(256) init_x_kernel(const IoTable* io, long long n, long long noise_off, float sigma0, float* x) {
+__global__ void __launch_bounds__(256) init_x_kernel(const IoTable* io, long long n, int step, int b_off, int B_total, int Lp, float sigma0,
+                                                     float* x) {
   pdl_launch_dependents();
   pdl_wait();
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) x[i] = sigma0 * io->noise[noise_off + i];
+  if (i >= n) return;
+  float z;
+  if (io->noise) {
+    z = io->noise[((long long)step * B_total + b_off) * Lp + i];
+  } else {
+    const int b = (int)(i / Lp);
+    z = unit_normal(io->seed, step, b_off + b, (int)(i - (long long)b * Lp));
+  }
+  x[i] = sigma0 * z;
 }
 
 // ---------------------------------------------------------------- CONV_OUT
@@ -322,7 +367,10 @@ __global__ void __launch_bounds__(256) conv_out_kernel(TensDesc a, int B, int Lp
   }
   const StepCoef cf = coef[step];
   float xn = cf.a * x[idx] + cf.b * acc;
-  if (cf.c != 0.f) xn = fmaf(cf.c, io->noise[((long long)(step + 1) * B_total + b_off) * Lp + idx], xn);
+  if (cf.c != 0.f) {
+    const float z = io->noise ? io->noise[((long long)(step + 1) * B_total + b_off) * Lp + idx] : unit_normal(io->seed, step + 1, b_off + b, l);
+    xn = fmaf(cf.c, z, xn);
+  }
   x[idx] = xn;
   if (io->dbg) io->dbg[((long long)step * B_total + b_off) * Lp + idx] = acc;
 }

@@ -201,9 +201,14 @@ class Universe(torch.nn.Module):
         ensemble: Optional[int] = None,
         ensemble_stat: Optional[str] = "median",
         warm_start: Optional[int] = None,
+        noise_seed: Optional[int] = None,
     ) -> torch.Tensor:
+        """Reference signature (universe.py:231-245) plus one trailing keyword of this port: noise_seed = None draws
+        the sampler noise with torch.randn(generator=rng) exactly like the reference (same draws, same order);
+        noise_seed = k lets the kernels draw it themselves (Philox keyed by k: same distribution, another stream, no
+        [n_steps, B, Lp] noise tensor; `rng` is then unused)."""
         out = self._enhance_impl(mix, n_steps, epsilon, target, fake_score_snr, rng, use_aux_signal, keep_rms,
-                                 ensemble, ensemble_stat, warm_start, noise=None, return_steps=False)
+                                 ensemble, ensemble_stat, warm_start, noise=None, return_steps=False, noise_seed=noise_seed)
         return out
 
     def enhance_debug(self, mix, noise, n_steps=None, epsilon=None, keep_rms=False):
@@ -213,7 +218,7 @@ class Universe(torch.nn.Module):
                                   noise=noise, return_steps=True)
 
     def _enhance_impl(self, mix, n_steps, epsilon, target, fake_score_snr, rng, use_aux_signal, keep_rms, ensemble,
-                      ensemble_stat, warm_start, noise, return_steps):
+                      ensemble_stat, warm_start, noise, return_steps, noise_seed=None):
         if epsilon is None:
             epsilon = self.diff_kwargs.epsilon
         if n_steps is None:
@@ -261,7 +266,10 @@ class Universe(torch.nn.Module):
         plan = self._get_plan(B, T, n_steps, aux=aux)
         Lp = plan.pg.Lp
         mix_f = mix.reshape(B, T).to(device=dev, dtype=torch.float32).contiguous()
-        if noise is None:
+        seeded = noise is None and noise_seed is not None
+        if seeded:
+            plan.set_noise_seed(noise_seed)   # the kernels draw z[step][utterance][sample] themselves
+        elif noise is None:
             # same draws, same order as the reference (universe.py:39-41,326,338): n_steps tensors of (B,1,Lp)
             # (use_aux_signal draws nothing, warm_start = n draws for the steps from n on: universe.py:317-331)
             noise = torch.zeros((n_steps, B, Lp), dtype=torch.float32, device=dev)
@@ -274,7 +282,7 @@ class Universe(torch.nn.Module):
         dbg = torch.empty((n_steps, B, Lp), dtype=torch.float32, device=dev) if return_steps else None
         coefs = program.step_coefs(self.model_config(), n_steps, epsilon)
         stream = torch.cuda.current_stream(dev).cuda_stream
-        io = (mix_f.data_ptr(), noise.data_ptr(), out.data_ptr(), dbg.data_ptr() if dbg is not None else None,
+        io = (mix_f.data_ptr(), None if seeded else noise.data_ptr(), out.data_ptr(), dbg.data_ptr() if dbg is not None else None,
               coefs, bool(keep_rms), stream)
         with torch.cuda.device(dev):
             if not aux:
@@ -294,6 +302,19 @@ class Universe(torch.nn.Module):
         noise[warm_start] initialises x, noise[warm_start + 1 ...] are the z of the following steps."""
         pg = plan.pg
         plan.run_ops(0, pg.idx_init_x, *io)
+        if getattr(pg, "idx_aux", None) is not None:
+            # native: one AUX launch = aux_to_wav(y_hat) [+ sigma_n z_n] into the sampler state (csrc/aux_ops.cuh)
+            if use_aux_signal:
+                plan.run_ops(pg.idx_aux, pg.idx_aux + 1, *io)
+            else:
+                n0 = int(warm_start)
+                plan.run_ops(pg.idx_aux + 1 + n0, pg.idx_aux + 2 + n0, *io)
+                plan.run_ops(pg.step_first_op[n0], pg.idx_post, *io)
+            plan.run_ops(pg.idx_post, pg.idx_post + 1, *io)
+            return
+        # a model without the signal_decoupling_layer (aux_to_wav is the identity on a 1-channel y_hat): host-side ops
+        if noise is None:
+            raise NotImplementedError("noise_seed with use_aux_signal / warm_start needs the signal_decoupling_layer")
         t = pg.y_hat
         C = t.nch * 8
         planes = plan.arena_view(t.off, t.nch * t.P * 8, noise.device).view(t.nch, t.P, 8)
@@ -319,6 +340,8 @@ class Universe(torch.nn.Module):
                 x = x.mean(dim=0)
             elif ensemble_stat == "median":
                 x = x.median(dim=0).values
+            elif x.is_cuda:
+                x = _native.signal_median(x)   # uv_signal_median: two launches, no sort of the whole ensemble
             else:
                 x = signal_median(x)
         if x_ndim == 1:

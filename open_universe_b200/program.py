@@ -742,7 +742,20 @@ def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_
     op.B, op.T, op.Lp, op.i0, op.p0, op.p1, op.p2 = B, T, Lp, pg.pad_left, pg.x, pg.mix_rms, pg.coef + n_steps * 16
     op.i1, op.i2 = b_off, B_total
     pg.emit(op, "post")
-    # the aux-signal paths read y_hat from the host side after the conditioner has run (universe.py _enhance_aux)
+    # use_aux_signal / warm_start (universe.py:313-331): one AUX record per way of starting, run one at a time by
+    # Universe._enhance_aux through uv_run_ops: [idx_aux] x = aux_to_wav(y_hat), [idx_aux + 1 + n] x = aux_to_wav(y_hat)
+    # + sigma_n z_n (the sampler then resumes at step n).  A model without the decoupling layer keeps the host path.
+    if aux and "s.aux" in L and getattr(pg, "y_hat", None) is not None and L["s.aux"]["C"] == pg.y_hat.nch * 8:
+        pg.idx_aux = len(pg.ops)
+        for k in range(n_steps + 1):
+            op = new_op(_abi.OP_AUX, -3)
+            op.a = pg.y_hat
+            op.B, op.Lp, op.C, op.p0, op.p3 = B, Lp, L["s.aux"]["C"], pg.x, L["s.aux"]["w_w"]
+            op.i3, op.H, op.F = L["s.aux"]["mode"], L["s.aux"]["KU"], L["s.aux"]["KD"]
+            op.i0, op.f0 = (k - 1, float(sigma[k - 1])) if k > 0 else (0, 0.0)
+            op.i1, op.i2 = b_off, B_total
+            pg.emit(op, "aux" if k == 0 else f"aux.warm{k - 1}")
+    # the aux-signal paths read y_hat after the conditioner has run (universe.py _enhance_aux)
     finalize_arena(pg, recycle=recycle, persistent=[getattr(pg, "y_hat", None)])
     pg.arena = _ru(pg.arena, 1024)
     return pg

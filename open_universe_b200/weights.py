@@ -365,6 +365,24 @@ def pack_model(sd, cfg):
     pm.layers["s.out"] = dict(w_w=pm.blob.add_f32(wo[0].t().contiguous()), bias_w=pm.blob.add_f32(sd[sp + ".output_conv.conv.bias"]),
                               slope_a=float(sd[sp + ".prelu.weight"]), slope_b=float(sd[sp + ".output_conv.prelu.weight"]))
 
+    # ---------------- signal_decoupling_layer (universe_gan.py:119-128): weights of the AUX op (csrc/aux_ops.cuh)
+    ap = "signal_decoupling_layer"
+    if ap + ".conv.bias" in sd:
+        wa = eff_weight(sd, ap + ".conv")   # [1, C, 3]
+        Ca = wa.shape[1]
+        if ap + ".prelu.act.act.alpha" in sd:
+            kup = sd[ap + ".prelu.act.upsample.kernel"].float()[:, 0, :]     # [2][KU]: the two output phases
+            kdn = sd[ap + ".prelu.act.downsample.kernel"].float()[0, 0, :]   # [KD]
+            head, mode = sd[ap + ".prelu.act.act.alpha"].float().reshape(-1), 0
+        elif ap + ".prelu.weight" in sd:
+            kup, kdn = torch.zeros(2, 0), torch.zeros(0)
+            head, mode = sd[ap + ".prelu.weight"].float().reshape(-1).expand(Ca).contiguous(), 1
+        else:
+            head = None
+        if head is not None and kup.shape[0] == 2 and wa.shape[2] == 3:
+            blob = torch.cat([head, kup.reshape(-1), kdn, wa[0].reshape(-1), sd[ap + ".conv.bias"].float().reshape(-1)])
+            pm.layers["s.aux"] = dict(w_w=pm.blob.add_f32(blob), mode=mode, KU=int(kup.shape[1]), KD=int(kdn.numel()), C=int(Ca))
+
     # ---------------- conditioner (condition.py:273-377)
     pm.add_conv_in(sd, cp + ".input_conv", "c.in")
     tot_ds = math.prod(rates)

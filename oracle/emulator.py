@@ -49,7 +49,7 @@ def op_outputs(op):
     elif t == _abi.OP_MEL:
         outs += [("mel", op.p1, op.B * op.F * op.C * 4, torch.float32),
                  ("energy", op.p2, op.B * ((op.F + op.T - 1) // op.T) * 4, torch.float32)]
-    elif t in (_abi.OP_INIT_X, _abi.OP_CONV_OUT):
+    elif t in (_abi.OP_INIT_X, _abi.OP_CONV_OUT, _abi.OP_AUX):
         outs.append(("x", op.p0, op.B * op.Lp * 4, torch.float32))
     elif t == _abi.OP_FILM:
         outs.append(("film", op.p1, op.i0 * op.i2 * 4, torch.float32))
@@ -225,6 +225,29 @@ class Emulator:
         z = io["noise"][op.i0].float().reshape(-1, op.Lp)[op.i1 : op.i1 + op.B]
         self.a_f32(op.p0, op.B * op.Lp).copy_((z * np.float32(op.f0)).reshape(-1))
 
+    def op_aux(self, op, io):
+        """aux_to_wav (universe_gan.py:147-151) + x = sig [+ sigma_n z_n] (universe.py:317-331), in the packed
+        weights' terms: alpha | up kernel [2][KU] | down kernel [KD] | conv [C][3] | bias."""
+        from oracle import universe_oracle as uo
+
+        B, Lp, C, KU, KD = op.B, op.Lp, op.C, op.H, op.F
+        y = self.read_tensor(op.a, B, Lp)  # [B, C, Lp]
+        w = self.w_f32(op.p3, C + 2 * KU + KD + 3 * C + 1)
+        head, kup, kdn = w[:C], w[C : C + 2 * KU].view(2, 1, KU), w[C + 2 * KU : C + 2 * KU + KD].view(1, 1, KD)
+        cw, bias = w[C + 2 * KU + KD : C + 2 * KU + KD + 3 * C].view(1, C, 3), w[-1:]
+        if op.i3 == 0:
+            y = uo.resample(y, kup, 1, 2)
+            a = torch.exp(head)[None, :, None]
+            y = y + (1.0 / (a + 1e-9)) * torch.sin(y * a) ** 2
+            y = uo.resample(y, kdn, 2, 1)
+        else:
+            y = torch.where(y >= 0, y, head[None, :, None] * y)
+        sig = torch.nn.functional.conv1d(y, cw, bias, padding="same")[:, 0, :]
+        if op.f0 != 0.0:
+            z = io["noise"][op.i0].float().reshape(-1, Lp)[op.i1 : op.i1 + B]
+            sig = sig + np.float32(op.f0) * z
+        self.a_f32(op.p0, B * Lp).copy_(sig.reshape(-1))
+
     def op_conv_out(self, op, io):
         B, Lp, C = op.B, op.Lp, op.C
         a = self.read_tensor(op.a, B, Lp)  # [B, C, Lp]
@@ -337,6 +360,8 @@ class Emulator:
             self.op_film(op)
         elif t == _abi.OP_GRU:
             self.op_gru(op)
+        elif t == _abi.OP_AUX:
+            self.op_aux(op, io)
         elif t == _abi.OP_CONVBLOCK:
             for part in op.parts:   # fused on the GPU; here the three convs run one after the other
                 self.op_gemm(part)

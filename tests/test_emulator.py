@@ -86,3 +86,39 @@ def test_recycled_arena_shares_slots_only_between_dead_tensors_of_one_geometry(n
                 assert ag == bg, (an, bn)
     if len(pg.lanes) == 2:   # lanes run concurrently: disjoint arenas
         assert max(s[1] for s in _spans(pg.lanes[0])) <= min(s[0] for s in _spans(pg.lanes[1]))
+
+
+@pytest.mark.parametrize("case", ["pp16k_aux", "pp16k_warm"])
+def test_aux_program_emulation_matches_reference(case):
+    """use_aux_signal / warm_start as the native path runs them: front end + conditioner, ONE AUX record
+    (aux_to_wav + state initialisation, csrc/aux_ops.cuh), the resumed sampler steps, POST -- against the
+    reference's golden outputs (universe.py:313-331, universe_gan.py:147-151)."""
+    from open_universe_b200 import testing
+
+    fix = load_fixture(case)
+    model, cfg = build_model(fix["model"], fix["seed_weights"])
+    testing.perturb_snake_alpha(model)
+    mcfg = model.model_config()
+    kw = fix["kwargs"]
+    n_steps = kw.get("n_steps", int(cfg.model.diffusion.n_steps))
+    pm = weights.pack_model({k: v.detach().float() for k, v in model.state_dict().items()}, mcfg)
+    assert pm.layers["s.aux"]["mode"] == 0 and pm.layers["s.aux"]["KU"] == 15 and pm.layers["s.aux"]["KD"] == 28
+    pg = program.build_program(pm, mcfg, fix["B"], fix["T"], n_steps, aux=True)
+    assert pg.names[pg.idx_aux] == "aux" and len(pg.ops) == pg.idx_aux + n_steps + 1
+    mix, noise = golden_inputs(fix, model.tot_ds)
+    nat = torch.zeros_like(noise)
+    n0 = kw.get("warm_start")
+    if n0 is not None:   # the reference consumes its draws from the start of the list
+        nat[n0:] = noise[: noise.shape[0] - n0]
+    coefs = program.step_coefs(mcfg, n_steps, kw.get("epsilon", float(cfg.model.diffusion.epsilon)))
+    emu = Emulator(pm, pg)
+    io = emu.run(mix, nat, coefs, keep_rms=kw.get("keep_rms", False), first=0, last=pg.idx_init_x)
+    if n0 is None:
+        emu.run_op(pg.idx_aux, io)
+    else:
+        emu.run_op(pg.idx_aux + 1 + n0, io)
+        for i in range(pg.step_first_op[n0], pg.idx_post):
+            emu.run_op(i, io)
+    emu.run_op(pg.idx_post, io)
+    assert uo.rel_l2(io["out"], fix["out"]) < 1e-2
+    assert uo.si_sdr(io["out"], fix["out"]).min() > 40.0

@@ -97,7 +97,7 @@ def test_signal_median_ensemble_matches_reference_golden():
 @pytest.mark.parametrize("case", ["pp16k_aux", "pp16k_warm"])
 def test_aux_signal_and_warm_start_match_reference_golden(case):
     """use_aux_signal / warm_start (universe.py:313-331): conditioner incl. the decoder tail and the resumed sampler
-    run natively, aux_to_wav in the shell."""
+    run natively, aux_to_wav + the state initialisation as one AUX launch (csrc/aux_ops.cuh)."""
     from open_universe_b200 import testing
 
     fix = load_fixture(case)
