@@ -124,10 +124,23 @@ typedef struct {
    * producer of A writes one tensor instead of a raw and an activated copy (blocks.py:209-231: PReLU -> conv). */
   int32_t a_act;
   float a_slope;
+  /* ---- variable-length calls (uv_set_row_tables): arena offset of this op's per-utterance table, < 0 = every
+   * utterance has the plan's geometry.  GEMM / CONVBLOCK: int32 [B] valid rows of each utterance in the op's row
+   * space (replaces M_valid); every other op: uv_row_geo [B].                                                    */
+  int64_t rows;
   /* UV_OP_GEMM / CONV_IN / CONV_OUT: i3 bit 0 = walk the tensor from its end (tiles / blocks in descending order).
    * The builder alternates it along each chain of kernels so that a consumer starts where its producer finished,
    * i.e. on the part of the tensor the L2 still holds.                                                          */
 } uv_op;
+
+/* Geometry of one utterance of a variable-length call: the reference enhances file by file (bin/enhance.py:168-192),
+ * each file with its own padding (universe.py:219-223), normalisation statistics, mel frames and GRU length. */
+typedef struct {
+  int32_t T;        /* valid samples of the row                      */
+  int32_t pad_left; /* (tot_ds - T % tot_ds) / 2                     */
+  int32_t Lp;       /* T + tot_ds - T % tot_ds (<= the plan's Lp)    */
+  int32_t F;        /* Lp / tot_ds: mel frames = GRU steps           */
+} uv_row_geo;
 
 typedef struct uv_model uv_model;
 typedef struct uv_plan uv_plan;
@@ -165,6 +178,15 @@ size_t uv_plan_arena_bytes(const uv_plan* p);
  * of (seed, step, utterance, sample), restated on the CPU in oracle/philox.py): same distribution, another stream. */
 int uv_enhance(uv_plan* p, const float* mix, const float* noise, float* out, float* dbg_net,
                const uv_step_coef* coef, int keep_rms, void* stream);
+
+/* Variable-length batches: the rows of the next calls have their own lengths.  `tables` (host, nbytes) is the block
+ * of per-utterance tables the ops' `rows` offsets point into, to be placed at arena_off; [clear_off, clear_off +
+ * clear_bytes) = the activation planes, cleared once in front of the next call (rows past an utterance's end are the
+ * zero padding of the convolutions and are never written).  Both happen on the stream of the next uv_enhance /
+ * uv_run_ops; call again only when the lengths change.  The host side (open_universe_b200/program.py row_tables())
+ * builds the block. */
+int uv_set_row_tables(uv_plan* p, const void* tables, size_t nbytes, size_t arena_off, size_t clear_off,
+                      size_t clear_bytes);
 
 /* Key of the in-kernel draws of the following calls made with noise == NULL (uv_enhance, uv_run_ops, ...). */
 int uv_set_noise_seed(uv_plan* p, unsigned long long seed);

@@ -79,6 +79,7 @@ class UvOp(C.Structure):
         ("sync", C.c_int32),
         ("a_act", C.c_int32),
         ("a_slope", C.c_float),
+        ("rows", C.c_int64),
     ]
 
 
@@ -109,6 +110,7 @@ def new_op(type_, step=-1):
         op.out[i].t = no_tens()
     op.w_w = op.bias_w = op.film = op.rm_out = -1
     op.p0 = op.p1 = op.p2 = op.p3 = op.p4 = op.p5 = -1
+    op.rows = -1
     op.scale = 1.0
     op.up = 1
     op.n_src = 1

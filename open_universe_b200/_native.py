@@ -19,7 +19,7 @@ EXPORTS = [
     "uv_abi_version", "uv_sizeof_op", "uv_last_error", "uv_model_create", "uv_model_destroy", "uv_plan_create",
     "uv_plan_destroy", "uv_plan_arena_bytes", "uv_enhance", "uv_run_ops", "uv_arena_read", "uv_arena_write",
     "uv_plan_num_launches", "uv_profile_ops", "uv_plan_arena_ptr", "uv_trace_ops", "uv_plan_status",
-    "uv_mel_spec_static", "uv_set_noise_seed", "uv_signal_median",
+    "uv_mel_spec_static", "uv_set_noise_seed", "uv_signal_median", "uv_set_row_tables",
 ]
 
 
@@ -84,6 +84,7 @@ def lib():
     L.uv_plan_status.argtypes = [C.c_void_p, C.c_void_p]
     L.uv_mel_spec_static.argtypes = [C.c_void_p, C.POINTER(_abi.UvMelDesc), C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
     L.uv_set_noise_seed.argtypes = [C.c_void_p, C.c_ulonglong]
+    L.uv_set_row_tables.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t]
     L.uv_signal_median.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_longlong, C.c_void_p, C.c_void_p, C.c_void_p]
     L.uv_plan_arena_ptr.argtypes = [C.c_void_p]
     L.uv_plan_arena_ptr.restype = C.c_void_p
@@ -143,6 +144,22 @@ class NativePlan:
                                     pg.init_off, pg.n_steps, int(use_graph)), "uv_plan_create")
         self.arena_bytes = int(pg.arena)
         self.num_launches = lib().uv_plan_num_launches(self.handle)
+        self._lengths = None   # the plan starts with the tables of a full-length batch (program._finish_init)
+
+    def set_lengths(self, lengths):
+        """Per-row valid lengths of the following calls (None: every row is T long): a row then behaves like a file of
+        that length enhanced on its own (uv_set_row_tables).  A no-op while the lengths do not change."""
+        from . import program
+
+        key = None if lengths is None else tuple(int(v) for v in lengths)
+        if key is not None and all(v == self.pg.T for v in key):
+            key = None
+        if key == self._lengths:
+            return
+        blob, off, lo, n = program.row_tables(self.pg, key)
+        buf = C.create_string_buffer(blob, len(blob))
+        _check(lib().uv_set_row_tables(self.handle, buf, len(blob), off, lo, n), "uv_set_row_tables")
+        self._lengths = key
 
     def _coefs(self, coefs):
         arr = (_abi.UvStepCoef * len(coefs))()

@@ -8,9 +8,10 @@ structure is retained), same per-file arithmetic: a file of C channels is a batc
 
 What differs is the schedule.  The reference enhances one file at a time (B = #channels, a few thousand eager
 kernel launches each).  Here the files stream through in windows (decoded ahead by a thread pool, written back by
-writer threads); the utterances of a window are grouped into batches of IDENTICAL length (padding
-and the normalisation statistics depend on the length, universe.py:219-223,272, so equal-length batches leave every
-utterance's result unchanged); under `torchrun` the files are dealt whole to the ranks (one process per GPU, no
+writer threads); the utterances of a window are grouped into batches of SIMILAR length and enhanced with
+`model.enhance(x, lengths=...)`: every row keeps the padding, normalisation statistics, mel frames and GRU length of
+its own file (universe.py:219-223,272), so a batch leaves every utterance's result what the file-by-file loop gives
+(`--equal-length-batches` restores batches of identical length only); under `torchrun` the files are dealt whole to the ranks (one process per GPU, no
 collective: the outputs are files), and each batch is one replay of the native CUDA graph.  `--batch-size` bounds the batch.
 
 The noise of a batch is drawn by `enhance()` from the seeded generator in batch order, so results are reproducible
@@ -115,10 +116,10 @@ def output_path_for(path, rel_path, dir_proc, output):
 
 
 def enhance_files(model, files, out_paths, enhance_kwargs, batch_size=64, device=None, rank=0, world=1, progress=False,
-                  window=None, io_threads=4):
+                  window=None, io_threads=4, ragged=True):
     """Enhances this rank's share of `files` into `out_paths`.  Returns a dict of counters.
     Files are dealt to ranks whole (largest first, round robin: balanced without any exchange); every channel of a
-    file is one utterance; utterances of identical (resampled) length share a batch.
+    file is one utterance; utterances of similar (ragged=False: identical) resampled length share a batch.
 
     The files stream through in windows of `window` files: a pool of `io_threads` threads decodes window k + 1 while
     the device works on window k, and finished files are copied back and written by writer threads, so neither the
@@ -163,14 +164,23 @@ def enhance_files(model, files, out_paths, enhance_kwargs, batch_size=64, device
                 a = resample(audio.to(device, non_blocking=True), fs, model.fs)
                 for c in range(a.shape[0]):
                     utts.append((fi, c, a[c]))
-            batches = sharding.length_buckets([u[2].shape[-1] for u in utts], list(range(len(utts))), batch_size)
+            lens = [u[2].shape[-1] for u in utts]
+            if ragged:
+                batches = sharding.ragged_batches(lens, list(range(len(utts))), batch_size)
+            else:
+                batches = [(b, lens[b[0]]) for b in sharding.length_buckets(lens, list(range(len(utts))), batch_size)]
             done = {}
-            for batch in batches:
-                x = torch.stack([utts[i][2] for i in batch])
-                y = model.enhance(x, **enhance_kwargs)
-                for i, yi in zip(batch, y):
-                    done[i] = yi
-                stats["audio_seconds"] += x.numel() / model.fs
+            for batch, T in batches:
+                if all(lens[i] == T for i in batch):
+                    y = model.enhance(torch.stack([utts[i][2] for i in batch]), **enhance_kwargs)
+                else:   # rows of different lengths: each keeps its own geometry (csrc RowGeo)
+                    x = torch.zeros((len(batch), T), dtype=utts[batch[0]][2].dtype, device=device)
+                    for k, i in enumerate(batch):
+                        x[k, : lens[i]] = utts[i][2]
+                    y = model.enhance(x, lengths=[lens[i] for i in batch], **enhance_kwargs)
+                for k, i in enumerate(batch):
+                    done[i] = y[k, : lens[i]]
+                stats["audio_seconds"] += sum(lens[i] for i in batch) / model.fs
             by_file = {}
             for i, (fi, c, _) in enumerate(utts):
                 by_file.setdefault(fi, []).append(i)
@@ -208,6 +218,7 @@ def main(argv=None):
     parser.add_argument("--seed", type=int, default=1028282, help="Set a deterministic seed to get reproducible results")
     parser.add_argument("--device", type=str, default="cuda:0", help="cuda:X (there is no CPU path in this implementation)")
     parser.add_argument("--batch-size", type=int, default=64, help="Utterances of equal length enhanced together")
+    parser.add_argument("--equal-length-batches", action="store_true", help="Only batch utterances of identical length")
     parser.add_argument("--window", type=int, default=None, help="Files decoded ahead and batched together (default: max(64, batch size))")
     parser.add_argument("--io-threads", type=int, default=4, help="Decoder threads")
     requires_help = handle_help()
@@ -239,7 +250,8 @@ def main(argv=None):
     files, rel_path, dir_proc = find_files(args.input)
     outs = [output_path_for(p, rel_path, dir_proc, args.output) for p in files]
     stats = enhance_files(model, files, outs, enhance_kwargs, batch_size=args.batch_size, device=device, rank=rank,
-                          world=world, progress=dir_proc and rank == 0, window=args.window, io_threads=args.io_threads)
+                          world=world, progress=dir_proc and rank == 0, window=args.window, io_threads=args.io_threads,
+                          ragged=not args.equal_length_batches)
     print(f"[rank {rank}] {stats['files']} files, {stats['utterances']} utterances in {stats['batches']} batches, "
           f"{stats['audio_seconds']:.1f} s of audio in {stats['seconds']:.2f} s "
           f"({stats['audio_seconds'] / max(stats['seconds'], 1e-9):.1f} audio-s/s incl. file IO and plan creation)")

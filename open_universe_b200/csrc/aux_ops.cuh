@@ -29,6 +29,7 @@ struct AuxParams {
   int step;              // noise step n (warm_start)
   int b_off, B_total;
   const IoTable* io;
+  const RowGeo* rows;    // per-utterance lengths (null: every row is Lp long)
 };
 
 __host__ __device__ inline size_t aux_smem_bytes(int C, int KU, int KD) {
@@ -50,6 +51,7 @@ __global__ void __launch_bounds__(256) aux_to_wav_kernel(const AuxParams P) {
   float* ds = ss + (size_t)C * ns; // [C][nd]
   const int tiles = (P.Lp + kAuxTile - 1) / kAuxTile;
   const int b = blockIdx.x / tiles, l0 = (blockIdx.x - b * tiles) * kAuxTile;
+  const int Lpb = P.rows ? P.rows[b].Lp : P.Lp;   // the utterance's own length: nothing exists past it
   const float* alpha = P.wts;
   const float* kup = alpha + C;
   const float* kdn = kup + 2 * KU;
@@ -65,7 +67,7 @@ __global__ void __launch_bounds__(256) aux_to_wav_kernel(const AuxParams P) {
       const int ch = e / nx, i = e - ch * nx;
       const int l = x_lo + i;
       float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      if (l >= 0 && l < P.Lp) load8(row_addr(P.a, b, l), P.a.esize_log2, ch, v);
+      if (l >= 0 && l < Lpb) load8(row_addr(P.a, b, l), P.a.esize_log2, ch, v);
 #pragma unroll
       for (int k = 0; k < 8; ++k) xs[(size_t)(ch * 8 + k) * nx + i] = v[k];
     }
@@ -75,7 +77,7 @@ __global__ void __launch_bounds__(256) aux_to_wav_kernel(const AuxParams P) {
       const int c = e / ns, k = e - c * ns;
       const int n = s_lo + k;
       float sv = 0.f;
-      if (n >= 0 && n < 2 * P.Lp) {
+      if (n >= 0 && n < 2 * Lpb) {
         const int i = n >> 1, ph = n & 1;
         const float* xr = xs + (size_t)c * nx + (i - wu - x_lo);
         const float* kr = kup + ph * KU;
@@ -93,7 +95,7 @@ __global__ void __launch_bounds__(256) aux_to_wav_kernel(const AuxParams P) {
       const int c = e / nd, k = e - c * nd;
       const int j = j_lo + k;
       float dv = 0.f;
-      if (j >= 0 && j < P.Lp) {
+      if (j >= 0 && j < Lpb) {
         const float* sr = ss + (size_t)c * ns + 2 * k;   // s index 2 j - wd + t = s_lo + 2 k + t
         for (int t = 0; t < KD; ++t) dv = fmaf(kdn[t], sr[t], dv);
       }
@@ -105,7 +107,7 @@ __global__ void __launch_bounds__(256) aux_to_wav_kernel(const AuxParams P) {
       const int ch = e / nd, k = e - ch * nd;
       const int l = j_lo + k;
       float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      if (l >= 0 && l < P.Lp) load8(row_addr(P.a, b, l), P.a.esize_log2, ch, v);
+      if (l >= 0 && l < Lpb) load8(row_addr(P.a, b, l), P.a.esize_log2, ch, v);
 #pragma unroll
       for (int q = 0; q < 8; ++q) {
         const float sl = alpha[ch * 8 + q];
@@ -118,6 +120,7 @@ __global__ void __launch_bounds__(256) aux_to_wav_kernel(const AuxParams P) {
   for (int k = threadIdx.x; k < kAuxTile; k += blockDim.x) {
     const int l = l0 + k;
     if (l >= P.Lp) break;
+    if (l >= Lpb) { P.x[(size_t)b * P.Lp + l] = 0.f; continue; }
     float acc = bias[0];
     for (int c = 0; c < C; ++c) {
       const float* dr = ds + (size_t)c * nd + k;   // d[l - 1], d[l], d[l + 1]

@@ -80,6 +80,12 @@ struct uv_plan {
   bool use_graph = false;
   bool lazy_graph = false;        // use_graph == 2: the first uv_enhance() runs eagerly, the second captures the graph
   long long n_calls = 0;
+  // uv_set_row_tables: per-utterance geometry of variable-length calls, staged like the sampler coefficients
+  std::vector<char> row_blob;
+  size_t row_off = 0, clear_off = 0, clear_bytes = 0;
+  bool row_dirty = false;         // copy the tables (and clear the activation planes) in front of the next call
+  char* row_host = nullptr;       // pinned ring: kStage x row_cap
+  size_t row_cap = 0;
   unsigned long long noise_seed = 0;   // uv_set_noise_seed: key of the in-kernel draws of calls made with noise == NULL
   bool seeded = false;
 };
@@ -147,6 +153,8 @@ static T* wptr(const uv_plan* p, int64_t off) { return off < 0 ? nullptr : reint
 template <typename T>
 static T* aptr(const uv_plan* p, int64_t off) { return off < 0 ? nullptr : reinterpret_cast<T*>(p->arena + off); }
 
+static const RowGeo* rowgeo(const uv_plan* p, const uv_op& op) { return aptr<const RowGeo>(p, op.rows); }
+
 static int check_tens(const uv_plan* p, const uv_tens& t, const char* what) {
   if (t.off < 0) return UV_OK;
   const size_t es = t.dtype == 1 ? 2 : 4;
@@ -176,6 +184,7 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
       for (int i = 0; i < 3; ++i) g.out[i] = to_out(p, op.out[i]);
       g.rm_out = aptr<float>(p, op.rm_out); g.rm_ld = op.rm_ld;
       g.rm_H = op.rm_out >= 0 ? op.H : 0; g.rm_Bp = op.i1;   // GEMM ops with a row-major output feed the GRU (H, batch pitch)
+      g.mv = op.rows >= 0 ? aptr<const int>(p, op.rows) : nullptr;
       g.err_flag = p->err_flag;
       g.a_act = op.a_act; g.a_slope = op.a_slope;
       g.reverse = op.i3 & 1;   // tile order (L2 reuse with the producer of A)
@@ -224,6 +233,7 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
         const TensDesc& o = c.out[0].t;
         c.bulk_out = (bulk_on && c.n_out == 1 && o.base && o.split == 1 && o.nchunks == kCbPlanes && o.esize_log2 == 1 && o.Lh == x.Lh) ? 1 : 0;
       }
+      c.mv = op.rows >= 0 ? aptr<const int>(p, op.rows) : nullptr;
       c.err_flag = p->err_flag;
       c.sched = p->sched + 2 * op_index;
       if (!cb_params_ok(c)) return fail(UV_ERR_INVALID, "fused ConvBlock: unsupported stage geometry");
@@ -248,7 +258,7 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
       break;
     }
     case UV_OP_PREP:
-      CUDA_TRY(launch_pdl(prep_kernel, dim3(op.B), dim3(1024), 0, s, p->io_dev, op.i1, op.T, op.Lp, op.i0, op.f0, aptr<float>(p, op.p0), aptr<float>(p, op.p1)));
+      CUDA_TRY(launch_pdl(prep_kernel, dim3(op.B), dim3(1024), 0, s, p->io_dev, op.i1, op.T, op.Lp, op.i0, op.f0, aptr<float>(p, op.p0), aptr<float>(p, op.p1), rowgeo(p, op)));
       break;
     case UV_OP_MEL: {
       if (op.T != kMelFT) return fail(UV_ERR_INVALID, "MEL op built for another frame tile than the kernel's");
@@ -261,13 +271,13 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
         return fail(UV_ERR_INVALID, "MEL front end: n_fft / hop / n_mels unsupported");
       CUDA_TRY(launch_pdl(mel_kernel, dim3(nft, op.B), dim3(threads), sm, s, aptr<const float>(p, op.p0), op.Lp, op.F, op.i0, op.i1, op.i2, op.H, op.C,
                                                       op.i3, wptr<const float>(p, op.p3), wptr<const float>(p, op.p4),
-                                                      aptr<float>(p, op.p1), aptr<float>(p, op.p2), nft));
+                                                      aptr<float>(p, op.p1), aptr<float>(p, op.p2), nft, rowgeo(p, op)));
       break;
     }
     case UV_OP_MEL_FIN: {
       const int items = op.F * (op.C / 8);
       CUDA_TRY(launch_pdl(mel_fin_kernel, dim3((items + 255) / 256, op.B), dim3(256), 0, s, aptr<const float>(p, op.p0), aptr<const float>(p, op.p1),
-                                                                     op.F, op.C, op.i0, to_out(p, op.out[0])));
+                                                                     op.F, op.C, op.i0, to_out(p, op.out[0]), rowgeo(p, op)));
       break;
     }
     case UV_OP_CONV_IN: {
@@ -275,14 +285,14 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
       const long long n = (long long)op.B * op.Lp;
       CUDA_TRY(launch_pdl(conv_in_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, s, aptr<const float>(p, op.p0), op.B, op.Lp, op.C, op.f0,
                                                                  wptr<const float>(p, op.p3), wptr<const float>(p, op.p4),
-                                                                 op.n_out, to_out(p, op.out[0]), to_out(p, op.out[1]), op.i3 & 1));
+                                                                 op.n_out, to_out(p, op.out[0]), to_out(p, op.out[1]), op.i3 & 1, rowgeo(p, op)));
       break;
     }
     case UV_OP_INIT_X: {
       const long long n = (long long)op.B * op.Lp;
       const int B_total = op.i2 > 0 ? op.i2 : op.B;   // i1 / i2: first utterance of this lane / utterances of the whole call
       CUDA_TRY(launch_pdl(init_x_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, s, p->io_dev, n, op.i0, op.i1, B_total, op.Lp, op.f0,
-                                                                aptr<float>(p, op.p0)));
+                                                                aptr<float>(p, op.p0), rowgeo(p, op)));
       break;
     }
     case UV_OP_CONV_OUT: {
@@ -291,7 +301,7 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
       CUDA_TRY(launch_pdl(conv_out_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, s, to_desc(p, op.a), op.B, op.Lp, op.C, wptr<const float>(p, op.p3),
                                                                   wptr<const float>(p, op.p4), aptr<float>(p, op.p0),
                                                                   aptr<const StepCoef>(p, op.p1), op.i0, p->io_dev, op.i1,
-                                                                  op.i2 > 0 ? op.i2 : op.B, op.i3 & 1));
+                                                                  op.i2 > 0 ? op.i2 : op.B, op.i3 & 1, rowgeo(p, op)));
       break;
     }
     case UV_OP_AUX: {
@@ -304,6 +314,7 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
       a.sigma = op.f0; a.step = op.i0;
       a.b_off = op.i1; a.B_total = op.i2 > 0 ? op.i2 : op.B;
       a.io = p->io_dev;
+      a.rows = rowgeo(p, op);
       const size_t smem = aux_smem_bytes(a.C, a.KU, a.KD);
       if (a.C % 8 || a.C > kEdgeMaxC || a.a.split > 1 || a.mode < 0 || a.mode > 1 || a.KU > kAuxMaxKU || a.KD > kAuxMaxKD ||
           (a.mode == 0 && (a.KU < 1 || a.KD < 2)) || smem > 200 * 1024)
@@ -315,7 +326,7 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
     }
     case UV_OP_POST:
       CUDA_TRY(launch_pdl(post_kernel, dim3(op.B), dim3(1024), 0, s, aptr<const float>(p, op.p0), op.T, op.Lp, op.i0, aptr<const float>(p, op.p1),
-                                        aptr<const int>(p, op.p2), p->io_dev, op.i1));
+                                        aptr<const int>(p, op.p2), p->io_dev, op.i1, rowgeo(p, op)));
       break;
     case UV_OP_FILM:
       film_kernel<<<op.i0, 512, 2 * op.C * sizeof(float), s>>>(aptr<const float>(p, op.p0), op.i1, op.C, op.H, op.i2,
@@ -337,6 +348,7 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
       if (g.add1.base && (g.add1.split != 1 || g.add1.esize_log2 != 1)) return fail(UV_ERR_INVALID, "GRU residual must be a plain bf16 tensor");
       for (int i = 0; i < g.n_out; ++i)
         if (g.out[i].t.split != 1) return fail(UV_ERR_INVALID, "GRU outputs must be plain tensors");
+      g.rows = op.rows >= 0 ? aptr<const RowGeo>(p, op.rows) : nullptr;
       g.err_flag = p->err_flag;
       static const int gru_flags = getenv("UV_GRU_FLAGS") ? atoi(getenv("UV_GRU_FLAGS")) : 1;
       g.dbg_flags = gru_flags;
@@ -541,6 +553,7 @@ extern "C" void uv_plan_destroy(uv_plan* p) {
   cudaFree(p->io_dev);
   if (p->err_host) cudaFreeHost(p->err_host);
   if (p->stage_host) cudaFreeHost(p->stage_host);
+  if (p->row_host) cudaFreeHost(p->row_host);
   delete p;
 }
 
@@ -572,6 +585,15 @@ static int stage_io(uv_plan* p, const float* mix, const float* noise, float* out
   io->mix = mix; io->noise = noise; io->out = out; io->dbg = dbg;
   io->seed = p->noise_seed; io->pad_ = 0;
   CUDA_TRY(cudaMemcpyAsync(p->io_dev, io, sizeof(IoTable), cudaMemcpyHostToDevice, s));
+  if (p->row_dirty) {
+    // new row lengths: rows past an utterance's end are never written by the kernels (they are the zero padding of
+    // the convolutions), so what a longer utterance of an earlier call left there has to go first
+    if (p->clear_bytes) CUDA_TRY(cudaMemsetAsync(p->arena + p->clear_off, 0, p->clear_bytes, s));
+    char* rh = p->row_host + (size_t)slot * p->row_cap;
+    memcpy(rh, p->row_blob.data(), p->row_blob.size());
+    CUDA_TRY(cudaMemcpyAsync(p->arena + p->row_off, rh, p->row_blob.size(), cudaMemcpyHostToDevice, s));
+    p->row_dirty = false;
+  }
   if (!p->coef_offs.empty()) {
     char* c = h + sizeof(IoTable);
     memcpy(c, coef, (size_t)p->n_steps * 16);
@@ -613,6 +635,30 @@ extern "C" int uv_enhance(uv_plan* p, const float* mix, const float* noise, floa
   } else if ((rc = enqueue_range(p, 0, (int)p->ops.size(), s, true))) {
     return rc;
   }
+  return UV_OK;
+}
+
+extern "C" int uv_set_row_tables(uv_plan* p, const void* tables, size_t nbytes, size_t arena_off, size_t clear_off, size_t clear_bytes) {
+  if (!p || !tables || nbytes == 0) return fail(UV_ERR_INVALID, "uv_set_row_tables: null argument");
+  if (arena_off + nbytes > p->arena_bytes || (arena_off & 15) || clear_off + clear_bytes > p->arena_bytes)
+    return fail(UV_ERR_INVALID, "uv_set_row_tables: range outside the arena");
+  if (arena_off < clear_off + clear_bytes && clear_off < arena_off + nbytes)
+    return fail(UV_ERR_INVALID, "uv_set_row_tables: the tables lie inside the cleared range");
+  DeviceGuard guard(p->model->device);
+  std::lock_guard<std::mutex> lock(p->mu);
+  if (nbytes > p->row_cap) {   // (first call, or a larger table: outside the steady state)
+    if (p->row_host) {
+      for (int i = 0; i < uv_plan::kStage; ++i)
+        if (p->stage_used[i]) CUDA_TRY(cudaEventSynchronize(p->stage_ev[i]));
+      cudaFreeHost(p->row_host);
+      p->row_host = nullptr;
+    }
+    p->row_cap = (nbytes + 4095) & ~(size_t)4095;
+    CUDA_TRY(cudaMallocHost(&p->row_host, p->row_cap * uv_plan::kStage));
+  }
+  p->row_blob.assign(static_cast<const char*>(tables), static_cast<const char*>(tables) + nbytes);
+  p->row_off = arena_off; p->clear_off = clear_off; p->clear_bytes = clear_bytes;
+  p->row_dirty = true;
   return UV_OK;
 }
 
@@ -805,7 +851,7 @@ extern "C" int uv_mel_spec_static(uv_model* m, const uv_mel_desc* d, const float
   mel_kernel<<<dim3(nft, B), dim3(threads), sm, s>>>(sig, Lp, F, d->n_fft, d->hop, d->n_bins, d->nbp, d->n_mels,
                                                      (d->n_fft - d->hop) / 2,
                                                      reinterpret_cast<const float*>(m->blob + d->basis_w),
-                                                     reinterpret_cast<const float*>(m->blob + d->fb_w), melraw, energy, nft);
+                                                     reinterpret_cast<const float*>(m->blob + d->fb_w), melraw, energy, nft, nullptr);
   CUDA_TRY(cudaGetLastError());
   mel_fin_plain_kernel<<<dim3((F * d->n_mels + 255) / 256, B), dim3(256), 0, s>>>(melraw, energy, F, d->n_mels, nft, mel_out);
   CUDA_TRY(cudaGetLastError());

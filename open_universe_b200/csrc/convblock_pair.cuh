@@ -50,6 +50,7 @@ struct CbParams {
   int has_bias[3];
   int n_src[3], n_shift[3];   // K sources (phase planes of the input: kc = 64 / n_src channels each) and taps per stage
   int m_rows, Lh, M_valid, n_tiles;
+  const int* mv;        // optional per-utterance valid rows (variable-length calls), else M_valid
   TensDesc cond;        // optional bf16 tensor (same geometry as x) added to conv1's output
   float scale1;         // applied after the condition add
   const float* film;    // optional [2 film_C] gamma | beta; channel of column n = n % film_C
@@ -68,7 +69,7 @@ struct CbParams {
 };
 
 struct CbSmem {
-  uint32_t film_off, ident_off, w_off[3], w_bytes[3], bufs_off, bars_off, total;
+  uint32_t film_off, mv_off, ident_off, w_off[3], w_bytes[3], bufs_off, bars_off, total;
 };
 __host__ __device__ inline uint32_t cb_stage_bytes(int n_src, int n_shift, int has_bias) {
   return (uint32_t)(n_src * n_shift) * (uint32_t)((kCbN / 2) * (kCbN / n_src) * 2) + (has_bias ? (kCbN / 2) * 32u : 0u);
@@ -78,6 +79,8 @@ __host__ __device__ inline CbSmem cb_smem_layout(const CbParams& p) {
   uint32_t off = kOnesBytes;
   L.film_off = off;
   off += 2 * kCbN * 4;
+  L.mv_off = off;       // per-utterance valid rows of a variable-length call (first kMvEntries utterances)
+  off += kMvBytes;
   L.ident_off = off;
   off += kCbIdentBytes;
   for (int s = 0; s < 3; ++s) {
@@ -104,15 +107,20 @@ static_assert(sizeof(CbBars) <= 1024, "barrier block");
 
 // One stage epilogue of one warp on one tile: TMEM -> registers -> stage math -> working buffer (stages 0 / 1) or
 // global outputs (stage 2).  lane = accumulator row.
+// valid rows of utterance b
+__device__ __forceinline__ int cb_valid_rows(const CbParams& P, const int* mv_s, int b) {
+  return P.mv ? (b < kMvEntries ? mv_s[b] : P.mv[b]) : P.M_valid;
+}
+
 template <int ST, bool LE1>
-__device__ __forceinline__ void cb_stage_epilogue(const CbParams& P, uint32_t taddr, uint8_t* wbuf, const float* film_s,
+__device__ __forceinline__ void cb_stage_epilogue(const CbParams& P, uint32_t taddr, uint8_t* wbuf, const float* film_s, const int* mv_s,
                                                   int i, long long g, float inv_Lh, int own_lo, const uint4* pre) {
   bool valid = g >= 0 && g < P.m_rows;
   int b = 0, m = 0;
   if (valid) {
     b = fast_div((int)g, P.Lh, inv_Lh);
     m = (int)g - b * P.Lh;
-    valid = m < P.M_valid;
+    valid = m < cb_valid_rows(P, mv_s, b);
   }
   uint32_t r[2][16];
   tc_ld16_issue(taddr, r[0]);
@@ -248,12 +256,12 @@ __device__ __forceinline__ void cb_store_rows(const CbParams& P, const uint8_t* 
 }
 
 // Row of the condition tensor that stage 1 adds, fetched before the wait for the accumulator (8 x 16 bytes per row).
-__device__ __forceinline__ void cb_prefetch_cond(const CbParams& P, long long g, float inv_Lh, uint4* pre) {
+__device__ __forceinline__ void cb_prefetch_cond(const CbParams& P, const int* mv_s, long long g, float inv_Lh, uint4* pre) {
 #pragma unroll
   for (int c = 0; c < kCbPlanes; ++c) pre[c] = make_uint4(0, 0, 0, 0);
   if (P.cond.base == nullptr || g < 0 || g >= P.m_rows) return;
   const int b = fast_div((int)g, P.Lh, inv_Lh);
-  if ((int)g - b * P.Lh >= P.M_valid) return;
+  if ((int)g - b * P.Lh >= cb_valid_rows(P, mv_s, b)) return;
   const char* p = P.cond.base + ((long long)P.cond.G + g) * 16;
   const long long stride = (long long)P.cond.P * 16;
 #pragma unroll
@@ -269,6 +277,7 @@ __global__ void __launch_bounds__(kCbThreads, 1) convblock_pair_kernel(const __g
   const CbSmem L = cb_smem_layout(P);
   uint8_t* ones = smem;
   float* film_s = reinterpret_cast<float*>(smem + L.film_off);
+  int* mv_s = reinterpret_cast<int*>(smem + L.mv_off);
   uint8_t* ident = smem + L.ident_off;
   CbBars* B = reinterpret_cast<CbBars*>(smem + L.bars_off);
   auto xbuf = [&](int x) { return smem + L.bufs_off + (size_t)x * kCbBufBytes; };
@@ -302,6 +311,10 @@ __global__ void __launch_bounds__(kCbThreads, 1) convblock_pair_kernel(const __g
   if (P.film)
     for (int k = threadIdx.x; k < 2 * kCbN; k += kCbThreads)
       film_s[k] = P.film[(k < kCbN ? 0 : P.film_C) + (k % kCbN) % P.film_C];
+  if (P.mv) {   // (host-written in front of the call: safe before pdl_wait)
+    const int n_utt = (P.m_rows + P.Lh - 1) / P.Lh;
+    for (int k = threadIdx.x; k < n_utt && k < kMvEntries; k += kCbThreads) mv_s[k] = P.mv[k];
+  }
   {  // identity image [8 chunks][n_half][8]: residual channel k -> column k; local column n stands for rank * n_half + n
     for (int i = threadIdx.x; i < kCbPlanes * n_half; i += kCbThreads) {
       const int c = i / n_half, n = i - c * n_half + (int)rank * n_half;
@@ -592,7 +605,7 @@ __global__ void __launch_bounds__(kCbThreads, 1) convblock_pair_kernel(const __g
           // flat row of accumulator row i at this stage
           const long long g = r0 - H + (st >= 0 ? h[0] : 0) + (st >= 1 ? h[1] : 0) + (st >= 2 ? h[2] : 0) + i;
           uint4 pre[kCbPlanes];
-          if (st == 0) cb_prefetch_cond(P, g, inv_Lh, pre);
+          if (st == 0) cb_prefetch_cond(P, mv_s, g, inv_Lh, pre);
           mbar_wait(smem_u32(&B->mma_done[s]), pm[s], P.err_flag, 12);
           pm[s] ^= 1;
           if (ck) { const long long t = clock64(); c_wait += t - t_prev; t_prev = t; }
@@ -601,9 +614,9 @@ __global__ void __launch_bounds__(kCbThreads, 1) convblock_pair_kernel(const __g
           // stages 1 / 2 write the working buffer; a staged stage 3 writes the tile's raw slab (its last reader, the
           // residual MMA, has completed)
           uint8_t* wb = st == 2 && P.bulk_out ? xbuf(xbs[s]) : wbuf(s);
-          if (st == 0) cb_stage_epilogue<0, true>(P, taddr, wb, film_s, i, g, inv_Lh, H - h[0], pre);
-          else if (st == 1) cb_stage_epilogue<1, true>(P, taddr, wb, film_s, i, g, inv_Lh, 0, pre);
-          else cb_stage_epilogue<2, true>(P, taddr, wb, film_s, i, g, inv_Lh, 0, pre);
+          if (st == 0) cb_stage_epilogue<0, true>(P, taddr, wb, film_s, mv_s, i, g, inv_Lh, H - h[0], pre);
+          else if (st == 1) cb_stage_epilogue<1, true>(P, taddr, wb, film_s, mv_s, i, g, inv_Lh, 0, pre);
+          else cb_stage_epilogue<2, true>(P, taddr, wb, film_s, mv_s, i, g, inv_Lh, 0, pre);
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive_cl(epi_cl0 + 8u * s);

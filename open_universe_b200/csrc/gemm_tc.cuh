@@ -64,6 +64,8 @@ constexpr int kFilmBytes = 2 * kFilmMaxC * 4;
 constexpr int kGemmSmemBudget = 227 * 1024;
 constexpr int kRmPitch = 20;        // floats per row of the GRU-layout staging buffer (16 + 4: conflict-free 16-byte accesses)
 constexpr int kRmScratchBytes = kEpiWarps * 32 * kRmPitch * 4;
+constexpr int kMvEntries = 128;              // per-utterance valid-row table kept in shared memory (variable-length calls)
+constexpr int kMvBytes = kMvEntries * 4;
 constexpr int kAddRowsBytes = kSubM * 16;    // one 8-channel chunk of a residual slab (no halo), this CTA's rows
 
 // TMEM columns per accumulator (power of two >= 32).
@@ -386,7 +388,7 @@ __device__ __forceinline__ void add_f32(const char* p, long long pstride, float*
 template <bool ADD, bool FILM, bool MULTI, bool LE1>
 __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem_base, uint64_t* t_full, uint64_t* t_empty,
                                               const float* film_s, const int* s_ring, uint64_t* s_full, uint64_t* s_empty,
-                                              float* rm_scratch, int warp, int lane, uint32_t rank) {
+                                              float* rm_scratch, const int* mv_s, int warp, int lane, uint32_t rank) {
   // msub = 1: the two warps of a lane quarter split the tile's column groups; msub = 2 (narrow tiles): they take one
   // 128-row sub-tile of this CTA's 256 rows each
   const int msub = P.msub;
@@ -482,7 +484,8 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
     const int g = m_tile * tile_rows + row_in_tile;
     const int b = fast_div(g, P.Lh_A, inv_Lh);
     const int m = g - b * P.Lh_A;
-    valid = (g < P.m_rows) && (m < P.M_valid);
+    // valid rows of utterance b: the table of a variable-length call (first kMvEntries in shared memory), else M_valid
+    valid = (g < P.m_rows) && (m < (P.mv ? (b < kMvEntries ? mv_s[b] : P.mv[b]) : P.M_valid));
     // first column group of this warp: in a multi-phase tile it may lie in a later phase (= a later output row)
     int ph_b = 0, gin = g_begin;
     if (g_begin >= gpp) { ph_b = g_begin / gpp; gin = g_begin - ph_b * gpp; }
@@ -508,7 +511,7 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& P, uint32_t tmem
         const int gj = g - lane + 8 * j + (lane >> 2);
         const int bj = fast_div(gj, P.Lh_A, inv_Lh);
         const int mj = gj - bj * P.Lh_A;
-        rm_ptr[j] = (gj < P.m_rows && mj < P.M_valid) ? P.rm_out + ((long long)mj * 16 * P.rm_Bp + bj) * S : nullptr;
+        rm_ptr[j] = (gj < P.m_rows && mj < (P.mv ? (bj < kMvEntries ? mv_s[bj] : P.mv[bj]) : P.M_valid)) ? P.rm_out + ((long long)mj * 16 * P.rm_Bp + bj) * S : nullptr;
       }
     } else if (MULTI) {
       rm_row = nullptr;
@@ -725,7 +728,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
   uint64_t* a_ready = s_empty + kSchedSlots;
   int* s_ring = reinterpret_cast<int*>(a_ready + kMaxAStages);
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(s_ring + kSchedSlots);
-  float* rm_scratch = reinterpret_cast<float*>(tmem_ptr_smem + 4);   // kRmScratchBytes, only with rm_xpose
+  int* mv_s = reinterpret_cast<int*>(tmem_ptr_smem + 4);             // kMvBytes: P.mv[0 .. kMvEntries)
+  float* rm_scratch = reinterpret_cast<float*>(mv_s + kMvEntries);   // kRmScratchBytes, only with rm_xpose
 
   const int n_half = P.N_TILE >> 1;                // weight / identity columns held by this CTA
   const uint32_t acc_stride = accum_stride_cols(P.N_TILE);
@@ -757,6 +761,10 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
   }
   if (P.film) {
     for (int i = threadIdx.x; i < 2 * P.C_out; i += kGemmThreads) film_s[i] = P.film[i];
+  }
+  if (P.mv) {   // (written by the host in front of the call, not by a predecessor kernel: safe before pdl_wait)
+    const int n_utt = (P.m_rows + P.Lh_A - 1) / P.Lh_A;
+    for (int i = threadIdx.x; i < n_utt && i < kMvEntries; i += kGemmThreads) mv_s[i] = P.mv[i];
   }
   if (P.add_kc) {
     // this CTA's half of the identity images [N_TILE / add_kc][add_kc / 8][n_half][8]: image j maps residual channel
@@ -1117,7 +1125,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
     for (int o = 0; o < 3; ++o)
       if (o < P.n_out && ((P.out[o].act >= 1 && !(P.out[o].a1 <= 1.f)) || (P.out[o].act == 2 && !(P.out[o].a2 <= 1.f)))) le1 = false;
     const int kind = (has_add ? 1 : 0) | (has_film ? 2 : 0) | (multi ? 4 : 0) | (le1 ? 8 : 0);
-#define UV_EPI(A, F, M, L) epilogue_role<A, F, M, L>(P, tmem_base, t_full, t_empty, film_s, s_ring, s_full, s_empty, rm_scratch, warp, lane, rank)
+#define UV_EPI(A, F, M, L) epilogue_role<A, F, M, L>(P, tmem_base, t_full, t_empty, film_s, s_ring, s_full, s_empty, rm_scratch, mv_s, warp, lane, rank)
     switch (kind) {
       case 0: UV_EPI(false, false, false, false); break;
       case 1: UV_EPI(true, false, false, false); break;
@@ -1160,7 +1168,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
 // ------------------------------------------------------------------ host side
 inline size_t gemm_smem_bytes(const GemmParams& p) {
   return (size_t)kOnesBytes + kFilmBytes + p.ident_bytes + (size_t)p.na_stages * p.a_stage_bytes + (size_t)p.nb_stages * p.b_stage_bytes +
-         (3 * kMaxAStages + 2 * kMaxBStages + 2 * kMaxAcc) * sizeof(uint64_t) + kSchedBytes + 16;
+         (3 * kMaxAStages + 2 * kMaxBStages + 2 * kMaxAcc) * sizeof(uint64_t) + kSchedBytes + 16 + kMvBytes;
 }
 
 // 128-row sub-tiles per CTA of the pair: a tile is 256 * gemm_msub(N_TILE) rows (planes are padded to 512 rows).
@@ -1210,7 +1218,7 @@ inline bool gemm_plan_pipeline(GemmParams& p) {
   if (p.n_acc > kMaxAcc) p.n_acc = kMaxAcc;
   if (p.n_acc < 1) return false;
   p.rm_xpose = (p.rm_out && p.rm_H > 0 && p.n_out == 0 && !p.add1.base && !p.add2.base && !p.film && p.scale == 1.f) ? 1 : 0;
-  const long long fixed = kOnesBytes + kFilmBytes + p.ident_bytes + (3 * kMaxAStages + 2 * kMaxBStages + 2 * kMaxAcc) * 8 + kSchedBytes + 16 + 1024 +
+  const long long fixed = kOnesBytes + kFilmBytes + p.ident_bytes + (3 * kMaxAStages + 2 * kMaxBStages + 2 * kMaxAcc) * 8 + kSchedBytes + 16 + kMvBytes + 1024 +
                           (p.rm_xpose ? kRmScratchBytes : 0);
   const long long budget = kGemmSmemBudget - fixed;
   const int n_img = p.n_src * p.n_groups * (p.smax - p.smin + 1);

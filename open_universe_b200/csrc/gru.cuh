@@ -46,6 +46,8 @@ struct GruParams {
   int* err_flag;
   long long* clk;           // optional [16] phase-time accumulators (debug, UV_GRU_CLK=1)
   int dbg_flags;            // UV_GRU_FLAGS: spare debug switches (unused)
+  const RowGeo* rows;       // per-utterance lengths (null: every utterance has T steps): an utterance of F < T frames
+                            // is a sequence of F steps (forward: t = 0 .. F-1, backward: F-1 .. 0), the rest is zero
 };
 
 struct GruSmem {
@@ -364,6 +366,7 @@ __global__ void __launch_bounds__(kGruThreads, 1) gru_kernel(const __grid_consta
     const bool gate_thread = tid < n_pairs;
     const int gn = tid / cpu, gc = tid - gn * cpu;
     const bool gvalid = gate_thread && (b0 + gn) < P.B;
+    const int t_len = (gvalid && P.rows) ? P.rows[b0 + gn].F : T;
     const int ju = (int)rank * U + gc * 8;             // first hidden unit of this thread
     const int q4 = warp & 3;
     const int c_split = ((NB / 16 + 1) / 2) * 16;
@@ -513,7 +516,9 @@ __global__ void __launch_bounds__(kGruThreads, 1) gru_kernel(const __grid_consta
           const float r = fast_sigmoid(gif[i] + gr[i * L.gh_stride]);
           const float z = fast_sigmoid(gif[8 + i] + gz[i * L.gh_stride]);
           const float n = fast_tanh(gif[16 + i] + r * gq[i * L.gh_stride]);
-          hn[i] = gvalid ? (1.f - z) * n + z * hprev[i] : 0.f;
+          // (steps past the utterance's own length: the state is zero -- the backward direction enters its last frame
+          // with h = 0, as in the reference -- and so are the outputs)
+          hn[i] = (gvalid && t < t_len) ? (1.f - z) * n + z * hprev[i] : 0.f;
           hprev[i] = hn[i];
         }
         uint4 hv;

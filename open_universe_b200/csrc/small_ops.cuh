@@ -84,29 +84,31 @@ __device__ __forceinline__ void block_sum3(double& a, double& b, double& c, doub
 // Also mix_rms over the unpadded input (universe.py:259).  One CTA per utterance.
 // b_off = first utterance of this lane in the caller's batch (the io tensors cover all lanes).
 __global__ void __launch_bounds__(1024) prep_kernel(const IoTable* io, int b_off, int T, int Lp, int pad_left, float level,
-                                                    float* sig, float* mix_rms) {
+                                                    float* sig, float* mix_rms, const RowGeo* __restrict__ rows) {
   pdl_launch_dependents();
   pdl_wait();
   __shared__ double sh[96];
   const int b = blockIdx.x;
-  const float* mix = io->mix + (size_t)(b_off + b) * T;
+  const float* mix = io->mix + (size_t)(b_off + b) * T;   // (T = row pitch of the caller's tensor)
+  int Tb = T, Lpb = Lp;
+  if (rows) { const RowGeo r = rows[b]; Tb = r.T; pad_left = r.pad_left; Lpb = r.Lp; }
   double s = 0, ss = 0, dummy = 0;
-  for (int i = threadIdx.x; i < T; i += blockDim.x) {
+  for (int i = threadIdx.x; i < Tb; i += blockDim.x) {
     const double v = mix[i];
     s += v; ss += v * v;
   }
   block_sum3(s, ss, dummy, sh);
-  const double mean = s / Lp;
-  double var = (ss - (double)Lp * mean * mean) / (double)(Lp - 1);
+  const double mean = s / Lpb;
+  double var = (ss - (double)Lpb * mean * mean) / (double)(Lpb - 1);
   if (var < 0) var = 0;
   const float meanf = (float)mean;
   const float gain = level / fmaxf((float)sqrt(var), 1e-5f);
-  if (threadIdx.x == 0) mix_rms[b] = (float)sqrt(ss / T);
+  if (threadIdx.x == 0) mix_rms[b] = (float)sqrt(ss / Tb);
   float* o = sig + (size_t)b * Lp;
   for (int i = threadIdx.x; i < Lp; i += blockDim.x) {
     const int j = i - pad_left;
-    const float v = (j >= 0 && j < T) ? mix[j] : 0.f;
-    o[i] = (v - meanf) * gain;
+    const float v = (j >= 0 && j < Tb) ? mix[j] : 0.f;
+    o[i] = i < Lpb ? (v - meanf) * gain : 0.f;   // nothing exists past the row's own padded length
   }
 }
 
@@ -124,7 +126,8 @@ constexpr int kMelPwPitch = kMelFT + 4;   // power spectrum rows [bin][frame], p
 __global__ void __launch_bounds__(512) mel_kernel(const float* __restrict__ sig, int Lp, int F, int n_fft, int hop,
                                                   int nb, int nbp, int n_mels, int pad_left,
                                                   const float* __restrict__ basis, const float* __restrict__ fb,
-                                                  float* __restrict__ melraw, float* __restrict__ energy, int nft) {
+                                                  float* __restrict__ melraw, float* __restrict__ energy, int nft,
+                                                  const RowGeo* __restrict__ rows) {
   pdl_launch_dependents();
   pdl_wait();
   extern __shared__ float smem_f[];
@@ -133,6 +136,7 @@ __global__ void __launch_bounds__(512) mel_kernel(const float* __restrict__ sig,
   float* pw = smem_f + ((span + 3) & ~3);   // [nb][kMelPwPitch]
   __shared__ double sh[96];
   const int b = blockIdx.y, f0 = blockIdx.x * kMelFT;
+  const int Fb = rows ? rows[b].F : F;
   const float* x = sig + (size_t)b * Lp;
   for (int i = threadIdx.x; i < span; i += blockDim.x) {
     const int j = f0 * hop + i - pad_left;
@@ -224,8 +228,9 @@ __global__ void __launch_bounds__(512) mel_kernel(const float* __restrict__ sig,
     for (int f = 0; f < kMelFT; ++f) {
       const int fr = f0 + g * fpt + f;
       if (f < fpt && fr < F) {
-        melraw[((size_t)b * F + fr) * n_mels + m] = acc[f];
-        e += (double)acc[f] * acc[f];
+        const float a = fr < Fb ? acc[f] : 0.f;   // frames past the row's own length do not exist
+        melraw[((size_t)b * F + fr) * n_mels + m] = a;
+        e += (double)a * a;
       }
     }
   }
@@ -235,15 +240,16 @@ __global__ void __launch_bounds__(512) mel_kernel(const float* __restrict__ sig,
 
 // Global mel normalisation (condition.py:105-106): x / clamp(sqrt(mean_t sum_m x^2), 1e-5) -> bf16 planes.
 __global__ void __launch_bounds__(256) mel_fin_kernel(const float* __restrict__ melraw, const float* __restrict__ energy,
-                                                      int F, int n_mels, int nft, OutDesc out) {
+                                                      int F, int n_mels, int nft, OutDesc out, const RowGeo* __restrict__ rows) {
   pdl_launch_dependents();
   pdl_wait();
   __shared__ float s_inv;
   const int b = blockIdx.y;
+  const int Fb = rows ? rows[b].F : F;
   if (threadIdx.x == 0) {
     float e = 0.f;
     for (int i = 0; i < nft; ++i) e += energy[(size_t)b * nft + i];
-    s_inv = 1.f / fmaxf(sqrtf(e / (float)F), 1e-5f);
+    s_inv = 1.f / fmaxf(sqrtf(e / (float)Fb), 1e-5f);
   }
   __syncthreads();
   const float inv = s_inv;
@@ -251,6 +257,7 @@ __global__ void __launch_bounds__(256) mel_fin_kernel(const float* __restrict__ 
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;  // (frame, chunk), frame fastest
   if (idx >= F * nch) return;
   const int ch = idx / F, f = idx - ch * F;
+  if (f >= Fb) return;   // (rows past the utterance's length stay zero)
   const float* src = melraw + ((size_t)b * F + f) * n_mels + ch * 8;
   float v[8];
 #pragma unroll
@@ -264,7 +271,7 @@ __global__ void __launch_bounds__(256) mel_fin_kernel(const float* __restrict__ 
 // condition.py:360), writing the raw tensor and the PReLU-activated copy.
 __global__ void __launch_bounds__(256) conv_in_kernel(const float* __restrict__ x, int B, int Lp, int C, float in_scale,
                                                       const float* __restrict__ w /*[3][C]*/, const float* __restrict__ bias,
-                                                      int n_out, OutDesc o0, OutDesc o1, int reverse) {
+                                                      int n_out, OutDesc o0, OutDesc o1, int reverse, const RowGeo* __restrict__ rows) {
   pdl_launch_dependents();
   // the three taps and the bias of every channel, staged once per block: one 16-byte broadcast load per channel
   // instead of four global loads per channel and thread (the kernel was load-instruction bound)
@@ -277,10 +284,12 @@ __global__ void __launch_bounds__(256) conv_in_kernel(const float* __restrict__ 
   const long long idx = blk * blockDim.x + threadIdx.x;
   if (idx >= (long long)B * Lp) return;
   const int b = (int)(idx / Lp), l = (int)(idx - (long long)b * Lp);
+  const int Lpb = rows ? rows[b].Lp : Lp;
   const float* xr = x + (size_t)b * Lp;
   const float xm = (l > 0 ? xr[l - 1] : 0.f) * in_scale;
   const float x0 = xr[l] * in_scale;
   const float xp = (l + 1 < Lp ? xr[l + 1] : 0.f) * in_scale;
+  if (l >= Lpb) return;   // rows past the utterance's own length stay zero (x is zero there as well)
   RowAddr r0 = row_addr(o0.t, b, l), r1 = row_addr(o1.t, b, l);
   for (int ch = 0; ch < (C >> 3); ++ch) {
     float v[8];
@@ -306,18 +315,14 @@ __global__ void __launch_bounds__(256) conv_in_kernel(const float* __restrict__ 
 
 // ---------------------------------------------------------------- INIT_X   x = sigma_0 * z_0 (universe.py:326)
 __global__ void __launch_bounds__(256) init_x_kernel(const IoTable* io, long long n, int step, int b_off, int B_total, int Lp, float sigma0,
-                                                     float* x) {
+                                                     float* x, const RowGeo* __restrict__ rows) {
   pdl_launch_dependents();
   pdl_wait();
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  float z;
-  if (io->noise) {
-    z = io->noise[((long long)step * B_total + b_off) * Lp + i];
-  } else {
-    const int b = (int)(i / Lp);
-    z = unit_normal(io->seed, step, b_off + b, (int)(i - (long long)b * Lp));
-  }
+  const int b = (int)(i / Lp), l = (int)(i - (long long)b * Lp);
+  if (rows && l >= rows[b].Lp) { x[i] = 0.f; return; }
+  const float z = io->noise ? io->noise[((long long)step * B_total + b_off) * Lp + i] : unit_normal(io->seed, step, b_off + b, l);
   x[i] = sigma0 * z;
 }
 
@@ -327,7 +332,7 @@ __global__ void __launch_bounds__(256) init_x_kernel(const IoTable* io, long lon
 __global__ void __launch_bounds__(256) conv_out_kernel(TensDesc a, int B, int Lp, int C, const float* __restrict__ w /*[3][C]*/,
                                                        const float* __restrict__ bias, float* __restrict__ x,
                                                        const StepCoef* __restrict__ coef, int step, const IoTable* io,
-                                                       int b_off, int B_total, int reverse) {
+                                                       int b_off, int B_total, int reverse, const RowGeo* __restrict__ rows) {
   pdl_launch_dependents();
   __shared__ __align__(16) float ws[3 * kEdgeMaxC];   // [tap][C]: 16-byte broadcast loads instead of one global load per weight
   for (int i = threadIdx.x; i < 3 * C; i += blockDim.x) ws[i] = w[i];
@@ -337,6 +342,7 @@ __global__ void __launch_bounds__(256) conv_out_kernel(TensDesc a, int B, int Lp
   const long long idx = blk * blockDim.x + threadIdx.x;
   if (idx >= (long long)B * Lp) return;
   const int b = (int)(idx / Lp), l = (int)(idx - (long long)b * Lp);
+  const int Lpb = rows ? rows[b].Lp : Lp;   // (used only after the loads below have been issued)
   // rows l-1, l, l+1 of the planes tensor (plain: neighbouring rows, rows -1 and Lp are the zero gap; phase-split:
   // the neighbours live in other phase planes, samples outside [0, Lp) are skipped)
   RowAddr rt[3];
@@ -366,6 +372,11 @@ __global__ void __launch_bounds__(256) conv_out_kernel(TensDesc a, int B, int Lp
     }
   }
   const StepCoef cf = coef[step];
+  if (l >= Lpb) {   // past the utterance's own length: the state stays zero (the rows read above are zero padding)
+    x[idx] = 0.f;
+    if (io->dbg) io->dbg[((long long)step * B_total + b_off) * Lp + idx] = 0.f;
+    return;
+  }
   float xn = cf.a * x[idx] + cf.b * acc;
   if (cf.c != 0.f) {
     const float z = io->noise ? io->noise[((long long)(step + 1) * B_total + b_off) * Lp + idx] : unit_normal(io->seed, step + 1, b_off + b, l);
@@ -379,12 +390,14 @@ __global__ void __launch_bounds__(256) conv_out_kernel(TensDesc a, int B, int Lp
 // unpad, optional keep_rms, per-utterance peak normalisation (universe.py:349-357). One CTA per utterance.
 __global__ void __launch_bounds__(1024) post_kernel(const float* __restrict__ x, int T, int Lp, int pad_left,
                                                     const float* __restrict__ mix_rms, const int* __restrict__ keep_rms,
-                                                    const IoTable* io, int b_off) {
+                                                    const IoTable* io, int b_off, const RowGeo* __restrict__ rows) {
   pdl_launch_dependents();
   pdl_wait();
   __shared__ double sh[96];
   __shared__ float s_max[32];
   const int b = blockIdx.x;
+  const int Tp = T;   // row pitch of the caller's output tensor
+  if (rows) { T = rows[b].T; pad_left = rows[b].pad_left; }
   const float* xr = x + (size_t)b * Lp + pad_left;
   double ss = 0, d1 = 0, d2 = 0;
   float mx = 0.f;
@@ -405,9 +418,9 @@ __global__ void __launch_bounds__(1024) post_kernel(const float* __restrict__ x,
     g = mix_rms[b] / x_rms;
   }
   const float peak = mx * g;
-  float* o = io->out + (size_t)(b_off + b) * T;
-  for (int i = threadIdx.x; i < T; i += blockDim.x) {
-    float v = xr[i] * g;
+  float* o = io->out + (size_t)(b_off + b) * Tp;
+  for (int i = threadIdx.x; i < Tp; i += blockDim.x) {
+    float v = i < T ? xr[i] * g : 0.f;
     if (peak > 1.f) v = v / peak;
     o[i] = v;
   }

@@ -37,6 +37,17 @@ struct OutDesc {
   int pad_;
 };
 
+// Per-utterance geometry of a call whose rows have different lengths (uv_set_row_tables): the reference enhances file
+// by file (bin/enhance.py:168-192), each with its own padding (universe.py:219-223), statistics, mel frames and GRU
+// length; a batch row b of a variable-length call behaves exactly like that file alone.  An op's `rows` table holds
+// one record per utterance of its lane; absent = every row has the plan's geometry.
+struct RowGeo {
+  int T;         // valid samples of the input row
+  int pad_left;  // (tot_ds - T % tot_ds) / 2
+  int Lp;        // padded length, a multiple of tot_ds (<= the plan's Lp)
+  int F;         // frames: Lp / tot_ds
+};
+
 struct GemmParams {
   // ---- A operand: bf16 planes tensor, sources = its phases
   const char* a_base;
@@ -83,6 +94,7 @@ struct GemmParams {
   int reverse;       // 1: tiles are taken from the last row tile down (see gemm_tc.cuh: L2 reuse between consecutive kernels)
   int a_act;         // 1: A is stored RAW; PReLU(a_slope) is applied to every slab in shared memory before the MMAs read it
   float a_slope;
+  const int* mv;     // optional per-utterance valid rows (replaces M_valid for that utterance: variable-length calls)
   int* err_flag;     // set on watchdog timeout
   int* sched;        // [2] zero before the first launch: tile counter, finished-CTA counter (the kernel rewinds both)
   unsigned long long* clk;   // debug (test_gemm phases): [gridDim.x][8] globaltimer stamps of the CTA's phases, or null

@@ -202,23 +202,30 @@ class Universe(torch.nn.Module):
         ensemble_stat: Optional[str] = "median",
         warm_start: Optional[int] = None,
         noise_seed: Optional[int] = None,
+        lengths=None,
     ) -> torch.Tensor:
-        """Reference signature (universe.py:231-245) plus one trailing keyword of this port: noise_seed = None draws
-        the sampler noise with torch.randn(generator=rng) exactly like the reference (same draws, same order);
-        noise_seed = k lets the kernels draw it themselves (Philox keyed by k: same distribution, another stream, no
-        [n_steps, B, Lp] noise tensor; `rng` is then unused)."""
+        """Reference signature (universe.py:231-245) plus two trailing keywords of this port.
+        noise_seed = None draws the sampler noise with torch.randn(generator=rng) exactly like the reference (same
+        draws, same order); noise_seed = k lets the kernels draw it themselves (Philox keyed by k: same distribution,
+        another stream, no [n_steps, B, Lp] noise tensor; `rng` is then unused).
+        lengths = [T_0, ..., T_{B-1}]: row b of `mix` holds T_b valid samples (right-padded with anything) and is
+        enhanced exactly like a file of that length on its own -- its own padding, normalisation statistics, mel
+        frames and GRU length -- which is how the reference's file loop (bin/enhance.py:168-192) treats a corpus
+        whose files all differ in length.  Row b of the result is valid up to T_b and zero after it.  In parity
+        mode row b consumes the first Lp_b values of its rows of the [B, 1, Lp] draws."""
         out = self._enhance_impl(mix, n_steps, epsilon, target, fake_score_snr, rng, use_aux_signal, keep_rms,
-                                 ensemble, ensemble_stat, warm_start, noise=None, return_steps=False, noise_seed=noise_seed)
+                                 ensemble, ensemble_stat, warm_start, noise=None, return_steps=False, noise_seed=noise_seed,
+                                 lengths=lengths)
         return out
 
-    def enhance_debug(self, mix, noise, n_steps=None, epsilon=None, keep_rms=False):
+    def enhance_debug(self, mix, noise, n_steps=None, epsilon=None, keep_rms=False, lengths=None):
         """Parity entry point: runs enhance() with an injected noise sequence `noise`
         ([n_steps, B, Lp] on the model device) and also returns the per-step network outputs."""
         return self._enhance_impl(mix, n_steps, epsilon, None, None, None, False, keep_rms, None, "median", None,
-                                  noise=noise, return_steps=True)
+                                  noise=noise, return_steps=True, lengths=lengths)
 
     def _enhance_impl(self, mix, n_steps, epsilon, target, fake_score_snr, rng, use_aux_signal, keep_rms, ensemble,
-                      ensemble_stat, warm_start, noise, return_steps, noise_seed=None):
+                      ensemble_stat, warm_start, noise, return_steps, noise_seed=None, lengths=None):
         if epsilon is None:
             epsilon = self.diff_kwargs.epsilon
         if n_steps is None:
@@ -245,9 +252,17 @@ class Universe(torch.nn.Module):
         if n_steps < 2:
             raise ValueError("n_steps must be at least 2")
 
+        if lengths is not None:
+            lengths = [int(v) for v in lengths]
+            if len(lengths) != mix.shape[0]:
+                raise ValueError("lengths: one value per row of mix")
+            if target is not None:
+                raise NotImplementedError("lengths with the known-score test hook")
         if ensemble is not None:
             mix_shape = mix.shape
             mix = torch.stack([mix] * ensemble, dim=0).view((-1,) + mix_shape[1:])
+            if lengths is not None:
+                lengths = lengths * ensemble
 
         B, T = mix.shape[0], mix.shape[-1]
         dev = self._device()
@@ -264,6 +279,7 @@ class Universe(torch.nn.Module):
             x = self._enhance_known_score(mix.to(dev), target.to(dev), n_steps, epsilon, fake_score_snr, rng, keep_rms, noise)
             return self._finish(x, x_ndim, ensemble, ensemble_stat, mix_shape if ensemble is not None else None)
         plan = self._get_plan(B, T, n_steps, aux=aux)
+        plan.set_lengths(lengths)   # (None: back to full-length rows)
         Lp = plan.pg.Lp
         mix_f = mix.reshape(B, T).to(device=dev, dtype=torch.float32).contiguous()
         seeded = noise is None and noise_seed is not None

@@ -51,6 +51,8 @@ RAW_A_MAXC = int(os.environ.get("UV_RAW_A_MAXC", "512"))   # channel limit of th
 RAW_A_RC_MAXC = int(os.environ.get("UV_RAW_A_RC_MAXC", "128"))
 # one launch per ConvBlock of the 64-column levels (csrc/convblock_pair.cuh): C = 64, or C = 32 in space-to-depth form
 FUSE_CONVBLOCKS = os.environ.get("UV_FUSE_CONVBLOCKS", "1") != "0"
+ROW_TABLES_ON = os.environ.get("UV_ROW_TABLES", "1") != "0"   # debug: 0 builds programs without per-utterance tables (no enhance(lengths=))
+ROW_TABLES = 8   # distinct row spaces (samples, the U-Net levels, frames) a program may have
 RECYCLE = os.environ.get("UV_RECYCLE", "1") != "0"   # liveness-based reuse of the activation slots of the arena (finalize_arena)
 VBASE = 1 << 44   # planes tensors carry virtual offsets >= VBASE until finalize_arena() places them
 
@@ -106,8 +108,28 @@ class Program:
         self.tensors[name] = t
         return t
 
+    # ---- per-utterance tables of variable-length calls (row_tables() below fills them; csrc uv_set_row_tables)
+    def rows_geo(self):
+        """uv_row_geo records of this lane's utterances."""
+        return self.rowtab + self.b_off * 16
+
+    def rows_mv(self, M_valid):
+        """int32 table of this lane's utterances: valid rows in a row space of M_valid rows per full-length utterance."""
+        assert M_valid > 0 and self.Lp % M_valid == 0, (self.Lp, M_valid)
+        ratio = self.Lp // M_valid
+        if ratio not in self.row_ratios:
+            self.row_ratios.append(ratio)
+            assert len(self.row_ratios) <= ROW_TABLES
+        k = self.row_ratios.index(ratio)
+        return self.rowtab + self.B_total * 16 + (k * self.B_total + self.b_off) * 4
+
     def emit(self, op, name):
         op.lane = self.lane
+        if getattr(self, "rowtab", None) is not None and ROW_TABLES_ON:
+            if op.type in (_abi.OP_GEMM, _abi.OP_CONVBLOCK):
+                op.rows = self.rows_mv(op.M_valid)
+            elif op.type != _abi.OP_FILM:
+                op.rows = self.rows_geo()
         if ALTERNATE and op.step != -2 and op.type in (_abi.OP_GEMM, _abi.OP_CONV_IN, _abi.OP_CONV_OUT, _abi.OP_CONVBLOCK):
             # the kernels of a chain walk their tensors in alternating directions: a consumer starts at the end its
             # producer just wrote, which is the part of the tensor the L2 still holds (csrc/gemm_tc.cuh, `reverse`)
@@ -205,6 +227,7 @@ def finalize_arena(pg, recycle=True, persistent=()):
             hi = 1 << 30
         live[off] = (lo, hi)
     base = _ru(pg.arena, 1024)
+    pg.planes_lo = base
     place = {}
     if not recycle:
         for off in sorted(tens):
@@ -244,7 +267,36 @@ def finalize_arena(pg, recycle=True, persistent=()):
         pg.live[name] = live[off]
         t.off = place[off]
     pg.arena = base
+    pg.planes_hi = base
     return pg
+
+
+def row_tables(pg, lengths=None):
+    """Host block of the per-utterance tables of a call (uv_set_row_tables) -> (bytes, arena offset, clear offset,
+    clear bytes).  lengths[b] = valid samples of row b of the caller's [B, T] tensor (None: every row is T long).
+    Each row gets the geometry the reference gives a file of that length on its own: pad = tot_ds - T_b % tot_ds
+    (a full block when T_b is a multiple: universe.py:219-223), Lp_b = T_b + pad, F_b = Lp_b / tot_ds frames, and
+    Lp_b / ratio valid rows in every row space of the program.  The cleared range covers the activation planes of
+    all lanes (and the raw buffers of the later lanes in between, which every call rewrites)."""
+    lanes = getattr(pg, "lanes", None) or [pg]
+    p0 = lanes[0]
+    Bt, T, td = p0.B_total, p0.T, p0.tot_ds
+    if lengths is None:
+        lengths = [T] * Bt
+    lengths = [int(v) for v in lengths]
+    if len(lengths) != Bt or min(lengths) < 1 or max(lengths) > T:
+        raise ValueError(f"lengths: need {Bt} values in [1, {T}]")
+    geo = np.zeros((Bt, 4), np.int32)
+    for b, tb in enumerate(lengths):
+        pad = td - tb % td
+        geo[b] = (tb, pad // 2, tb + pad, (tb + pad) // td)
+    mv = np.zeros((ROW_TABLES, Bt), np.int32)
+    for k, ratio in enumerate(p0.row_ratios):
+        assert (geo[:, 2] % ratio == 0).all()
+        mv[k] = geo[:, 2] // ratio
+    lo, hi = min(l.planes_lo for l in lanes), max(l.planes_hi for l in lanes)
+    assert p0.rowtab + geo.nbytes + mv.nbytes <= lo
+    return geo.tobytes() + mv.tobytes(), p0.rowtab, lo, hi - lo
 
 
 def gru_geometry(H, B):
@@ -346,7 +398,7 @@ def build_program(pm, cfg, B, T, n_steps, aux=False, lanes=None, recycle=None):
     if recycle is None:
         recycle = RECYCLE
     if lanes == 1 or B < 2:
-        return _build_lane(pm, cfg, B, T, n_steps, aux=aux, recycle=recycle)
+        return _finish_init(_build_lane(pm, cfg, B, T, n_steps, aux=aux, recycle=recycle))
     assert not aux, "aux-signal programs are single-lane (run_ops ranges address one op list)"
     B0 = (B + 1) // 2
     pg0 = _build_lane(pm, cfg, B0, T, n_steps, b_off=0, B_total=B, recycle=recycle)
@@ -363,6 +415,15 @@ def build_program(pm, cfg, B, T, n_steps, aux=False, lanes=None, recycle=None):
     pg.names = pg0.names + pg1.names
     pg.arena = pg1.arena
     pg.B = B
+    return _finish_init(pg)
+
+
+def _finish_init(pg):
+    """Init blob of the plan: the row tables of a full-length batch, then (at its own offset) log10 sigma."""
+    p0 = (getattr(pg, "lanes", None) or [pg])[0]
+    tables = row_tables(pg)[0]
+    pg.init_blob = tables + bytes(p0.log10s - p0.rowtab - len(tables)) + p0.log10s_blob
+    pg.init_off = p0.rowtab
     return pg
 
 
@@ -382,7 +443,7 @@ def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_
     pg = Program(pm, B, T, n_steps, sigma, log10s, w_in, arena_base=arena_base, lane=lane)
     pg.lanes = [pg]
     pg.b_off, pg.B_total = b_off, B_total
-    pg.Lp, pg.pad_left = Lp, pad // 2
+    pg.Lp, pg.pad_left, pg.tot_ds = Lp, pad // 2, tot_ds
     lv = [Level(B, Lp // math.prod(rates[:i])) for i in range(nlev + 1)]
     pg.levels = lv
     Fr = lv[nlev].L  # bottleneck frames
@@ -396,10 +457,15 @@ def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_
     pg.coef = pg.alloc(n_steps * 16 + 16)  # uv_step_coef[n_steps] | keep_rms flag
     R = L["s.film"]["R"]
     if shared is None:
+        # per-utterance geometry of the whole call: uv_row_geo [B_total] | int32 [ROW_TABLES][B_total] (row_tables());
+        # the plan is created with the tables of a full-length batch (init blob = tables | log10 sigma, _finish_init)
+        pg.rowtab = pg.alloc(B_total * 16 + ROW_TABLES * B_total * 4, align=1024)
+        pg.row_ratios = []
         pg.log10s = pg.alloc(n_steps * 4)
         pg.film = pg.alloc(n_steps * R * 4)
-        pg.init_off = pg.log10s
-        pg.init_blob = np.asarray(log10s.numpy(), dtype=np.float32).tobytes()
+        pg.init_off = pg.rowtab
+        pg.log10s_blob = np.asarray(log10s.numpy(), dtype=np.float32).tobytes()
+        pg.init_blob = b""
 
         # ---- plan-time setup: FiLM table (sigma_block.py:50-57,73-78; score.py:109,208)
         op = new_op(_abi.OP_FILM, -2)
@@ -408,6 +474,7 @@ def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_
         pg.emit(op, "film_table")
     else:
         pg.log10s, pg.film, pg.init_off, pg.init_blob = shared.log10s, shared.film, shared.init_off, shared.init_blob
+        pg.rowtab, pg.row_ratios = shared.rowtab, shared.row_ratios
 
     # ---- PREP (universe.py:219-223,272; utils/norm.py:47-87)
     level = 10.0 ** (float(cfg.get("normalization_kwargs", {}).get("level_db", 0.0)) / 20.0)

@@ -29,6 +29,28 @@ def length_buckets(lengths, indices, batch_size):
     return batches
 
 
+def ragged_batches(lengths, indices, batch_size, quantum=8000, max_waste=0.25):
+    """Batches of utterances of DIFFERENT lengths for enhance(lengths=...): the kernels give every row its own
+    padding / statistics / frames (csrc RowGeo), so mixing lengths does not change results; what it costs is the
+    work spent on the rows' tails.  Utterances are taken in order of length; a batch is closed when it is full or
+    when its shortest member would waste more than `max_waste` of the batch length.  Returns (indices, T) pairs with
+    T = the longest member rounded up to `quantum` samples (so that a corpus maps to a few plan shapes)."""
+    order = sorted(indices, key=lambda i: (int(lengths[i]), i), reverse=True)
+    batches, cur = [], []
+    for i in order:
+        if cur and (len(cur) >= batch_size or int(lengths[i]) < (1.0 - max_waste) * int(lengths[cur[0]])):
+            batches.append(cur)
+            cur = []
+        cur.append(i)
+    if cur:
+        batches.append(cur)
+    out = []
+    for b in batches:
+        longest = int(lengths[b[0]])
+        out.append((b, -(-longest // quantum) * quantum))
+    return out
+
+
 def enhance_sharded(enhance_fn, clips, batch_size, rank=0, world=1, group=None, **kwargs):
     """clips: list of 1-D tensors. Returns the list of enhanced clips (original order) on rank 0,
     None elsewhere.  `enhance_fn(batch [B, T], **kwargs) -> [B, T]` is normally `model.enhance`."""

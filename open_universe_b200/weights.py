@@ -29,7 +29,7 @@ def eff_weight(sd, prefix):
 
 TILE_M = 256          # csrc/gemm_tc.cuh kTileM: rows of a tile of the SM pair
 SUB_M = 128           # ... of which every CTA of the pair holds 128 (kSubM)
-SMEM_BUDGET = 227 * 1024 - (4096 + 6144 + 640 + 640 + 16 + 1024)  # gemm_plan_pipeline(): 227 KB minus the fixed regions
+SMEM_BUDGET = 227 * 1024 - (4096 + 6144 + 640 + 640 + 16 + 512 + 1024)  # gemm_plan_pipeline(): 227 KB minus the fixed regions
 # widest N tile.  256 columns run the pair's MMA at the same rate as 128 (tools/mma_bench.cu) and halve the A re-reads,
 # but leave two (msub = 1) accumulator stages and halve the tile count of the short level-3 / 4 launches; measured on the
 # whole model (tools/ab_msub.sh, eager pass, one lane): 128 / 256 = 46.97 / 47.50 ms with 256-row CTA tiles for N <= 128

@@ -42,6 +42,7 @@ class _HalfModel(torch.nn.Module):
 
     def enhance(self, mix, **kw):
         self.batches.append(tuple(mix.shape))
+        self.lengths = getattr(self, "lengths", []) + [kw.get("lengths")]
         return 0.5 * mix
 
 
@@ -90,7 +91,7 @@ def test_enhance_files_batches_equal_lengths_and_deals_whole_files(tmp_path, wor
     seen, n_files = [], 0
     for rank in range(world):
         model = _HalfModel()
-        st = cli.enhance_files(model, files, outs, {}, batch_size=3, device="cpu", rank=rank, world=world)
+        st = cli.enhance_files(model, files, outs, {}, batch_size=3, device="cpu", rank=rank, world=world, ragged=False)
         n_files += st["files"]
         seen += model.batches
         for B, T in model.batches:
@@ -104,6 +105,32 @@ def test_enhance_files_batches_equal_lengths_and_deals_whole_files(tmp_path, wor
         assert fs_o == fs and y.shape == x.shape                       # original rate and channel count restored
         if fs == 16000:
             assert torch.allclose(y, 0.5 * x, atol=1e-6)
+
+
+def test_enhance_files_ragged_batches_carry_row_lengths(tmp_path):
+    """Default schedule: utterances of similar length share a batch, every row with its own length (enhance(lengths=))."""
+    src = tmp_path / "noisy"
+    specs = [(f"f{k:02d}.wav", 16000, 1, 9000 + 37 * k, "float32") for k in range(20)] + [("short.wav", 16000, 1, 900, "float32")]
+    files = _write_wavs(src, specs)
+    outs = [tmp_path / "out" / p.name for p in files]
+    model = _HalfModel()
+    st = cli.enhance_files(model, files, outs, {}, batch_size=8, device="cpu")
+    assert st["files"] == 21 and st["utterances"] == 21 and st["batches"] == 4          # 8 + 8 + 4 similar ones, the short one alone
+    for (B, T), lens in zip(model.batches, model.lengths):
+        assert B <= 8 and T % 8000 == 0 or lens is None
+        if lens is not None:
+            assert len(lens) == B and max(lens) <= T and min(lens) >= 0.75 * max(lens)
+    for p, o in zip(files, outs):
+        assert torch.allclose(cli.load_audio(o)[0], 0.5 * cli.load_audio(p)[0], atol=1e-6)
+
+
+def test_ragged_batches_bound_the_wasted_tail():
+    lengths = [16000, 15000, 9000, 8900, 8800, 2000, 16000, 100]
+    batches = sharding.ragged_batches(lengths, list(range(8)), 3, quantum=4000, max_waste=0.25)
+    assert sorted(i for b, _ in batches for i in b) == list(range(8))
+    for b, T in batches:
+        ls = [lengths[i] for i in b]
+        assert len(b) <= 3 and T % 4000 == 0 and T >= max(ls) and T - max(ls) < 4000 and min(ls) >= 0.75 * max(ls)
 
 
 def test_length_buckets_never_mix_lengths():
@@ -129,7 +156,8 @@ def test_cli_end_to_end_equals_direct_enhance_calls(tmp_path):
     specs = [("a.wav", 16000, 1, 3000, "float32"), ("s/b.wav", 16000, 1, 3000, "float32"), ("s/c.wav", 16000, 1, 2000, "float32")]
     _write_wavs(src, specs)
     out = tmp_path / "enh"
-    st = cli.main([str(src), str(out), "--model", str(d / "last.ckpt"), "--seed", "5", "--n_steps", "4", "--batch-size", "8"])
+    st = cli.main([str(src), str(out), "--model", str(d / "last.ckpt"), "--seed", "5", "--n_steps", "4", "--batch-size", "8",
+                   "--equal-length-batches"])
     assert st["files"] == 3 and st["batches"] == 2
     gm = model.to("cuda").eval()
     rng = torch.Generator(device="cuda").manual_seed(5)
@@ -152,7 +180,7 @@ def test_windows_stream_every_file_once_with_bounded_batches(tmp_path):
     for window in (5, 64):
         outs = [tmp_path / f"out{window}" / p.name for p in files]
         model = _HalfModel()
-        st = cli.enhance_files(model, files, outs, {}, batch_size=4, device="cpu", window=window, io_threads=3)
+        st = cli.enhance_files(model, files, outs, {}, batch_size=4, device="cpu", window=window, io_threads=3, ragged=False)
         assert st["files"] == 37 and st["utterances"] == 37
         assert all(B <= 4 for B, T in model.batches)
         assert sum(B for B, T in model.batches) == 37
@@ -177,7 +205,7 @@ def test_cli_300_files_of_300_distinct_lengths(tmp_path):
     files = _write_wavs(src, specs)
     out = tmp_path / "enh"
     st = cli.main([str(src), str(out), "--model", str(d / "last.ckpt"), "--seed", "9", "--n_steps", "2", "--batch-size", "8",
-                   "--window", "64"])
+                   "--window", "64", "--equal-length-batches"])
     assert st["files"] == 300 and st["batches"] == 300
     gm = model.to("cuda").eval()
     rng = torch.Generator(device="cuda").manual_seed(9)
@@ -192,4 +220,42 @@ def test_cli_300_files_of_300_distinct_lengths(tmp_path):
             got = cli.load_audio(out / found[fi].relative_to(src))[0]
             worst = max(worst, (got - ref).abs().max().item())
     assert len(gm._plans) <= gm.plan_cache_max
+    assert worst < 1e-6, worst
+
+
+@pytest.mark.gpu
+def test_cli_ragged_corpus_equals_direct_ragged_calls(tmp_path):
+    """The default schedule on a corpus where every file has its own length: a handful of batches instead of one per
+    file, each output equal to model.enhance(x, lengths=...) on the same batch with the same generator state (the
+    per-row geometry itself is tested against file-by-file runs in test_gpu_ragged.py)."""
+    model, cfg = build_model("universepp_16k")
+    d = tmp_path / "exp" / "checkpoints"
+    d.mkdir(parents=True)
+    torch.save({"state_dict": {k: v.clone() for k, v in model.state_dict().items()}}, d / "last.ckpt")
+    (tmp_path / "exp" / ".hydra").mkdir()
+    with open(tmp_path / "exp" / ".hydra" / "config.yaml", "w") as f:
+        yaml.safe_dump(json.loads(json.dumps(cfg)), f)
+    src = tmp_path / "noisy"
+    specs = [(f"f{k:03d}.wav", 16000, 1, 6000 + 61 * k, "float32") for k in range(40)]
+    files = _write_wavs(src, specs)
+    out = tmp_path / "enh"
+    st = cli.main([str(src), str(out), "--model", str(d / "last.ckpt"), "--seed", "9", "--n_steps", "2", "--batch-size", "16",
+                   "--window", "64"])
+    assert st["files"] == 40 and st["batches"] <= 4
+    gm = model.to("cuda").eval()
+    rng = torch.Generator(device="cuda").manual_seed(9)
+    found, _, _ = cli.find_files(src)
+    order = sorted(range(len(found)), key=lambda i: (-os.path.getsize(found[i]), str(found[i])))
+    audio = [cli.load_audio(found[fi])[0][0] for fi in order]          # utterances in the window's order
+    lens = [a.shape[-1] for a in audio]
+    worst = 0.0
+    for batch, T in sharding.ragged_batches(lens, list(range(40)), 16):
+        x = torch.zeros(len(batch), T)
+        for k, i in enumerate(batch):
+            x[k, : lens[i]] = audio[i]
+        ref = gm.enhance(x.cuda(), n_steps=2, rng=rng, lengths=[lens[i] for i in batch]).cpu()
+        for k, i in enumerate(batch):
+            got = cli.load_audio(out / found[order[i]].relative_to(src))[0][0]
+            worst = max(worst, (got - ref[k, : lens[i]]).abs().max().item())
+            assert ref[k, lens[i]:].abs().max() == 0 if lens[i] < T else True
     assert worst < 1e-6, worst
