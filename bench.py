@@ -188,11 +188,11 @@ def gpu_eager_baseline(wl, dev, n_clips, repeats=3):
         torch.backends.cudnn.allow_tf32 = tf32
         torch.backends.cuda.matmul.allow_tf32 = tf32
         best = None
-        with torch.no_grad():
+        with torch.no_grad(), torch.device(dev):   # (factory calls inside the port -- arange, linspace, nn.GRU -- land on the GPU)
             for _ in range(repeats + 1):
                 torch.cuda.synchronize(dev)
                 t0 = time.perf_counter()
-                uo.enhance(sd, cfg.model, mix, noises, n_steps=wl["n_steps"])
+                uo.enhance(sd, cfg.model, mix, list(noises), n_steps=wl["n_steps"])
                 torch.cuda.synchronize(dev)
                 dt = time.perf_counter() - t0
                 best = dt if best is None else min(best, dt)
@@ -348,7 +348,15 @@ def run_native(args, wl, rank, world, local_rank):
     n_gemm = sum(1 for op in ops if op.type == _abi.OP_GEMM)
     gemm_share = by_kind_busy.get("GEMM", 0.0) / trace_total
     gemm_ms = gemm_share * ms                                  # <= ms_per_step by construction
-    achieved = fl["gemm_executed"] * B / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
+    # the ConvBlocks of the 64-column levels run in their own fused kernel (csrc/convblock_pair.cuh): their FLOPs and
+    # bytes are accounted to that kernel, not to gemm_tc_kernel.  Per launch, reference formulation: 2 C C (5 + 3 + 3)
+    # per sample; bytes = the tensors the launch has to move once (x, condition, outputs; bf16)
+    fused = [op for op in ops if op.type == _abi.OP_CONVBLOCK and op.step != -2]
+    fused_flops = sum(2.0 * op.C * op.C * 11 * (op.M_valid * 64 // op.C) * (op.m_rows // op.Lh_A) for op in fused)
+    fused_bytes = sum(128.0 * op.M_valid * (op.m_rows // op.Lh_A) * (1 + op.n_out + (1 if op.add1.off >= 0 else 0) + (1 if op.i2 else 0))
+                      for op in fused)
+    gemm_flops = fl["gemm_executed"] * B - fused_flops
+    achieved = gemm_flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
     # measured DRAM bytes per launch of the same kernel: an ncu pass over this command (tools/launch_summary.py),
     # quoted only if it was taken on this very build
     traffic, traffic_src, traffic_note = None, None, None
@@ -368,11 +376,21 @@ def run_native(args, wl, rank, world, local_rank):
                     launches_per_step=n_gemm, kernel_ms_per_step=gemm_ms, share_of_step=gemm_share,
                     accounting=("kernel_ms_per_step = union of the kernel's launch intervals over both utterance lanes in the "
                                 "two-stream schedule (uv_trace_ops, CUDA events) / traced pass x graph-timed ms_per_step; "
-                                "achieved = algorithmic GEMM FLOPs actually executed (reference formulation, hoisted 1x1 "
-                                "condition projections counted once) / that time"),
-                    flops_per_clip=dict(gemm_executed=fl["gemm_executed"], gemm_reference=fl["gemm"], total_reference=fl["total"]),
+                                "achieved = algorithmic FLOPs of the layers this kernel executes (reference formulation, hoisted "
+                                "1x1 condition projections counted once, the fused ConvBlocks of the 64-column levels excluded: "
+                                "see roofline.fused_convblock) / that time"),
+                    flops_per_clip=dict(gemm_executed=fl["gemm_executed"], gemm_reference=fl["gemm"], total_reference=fl["total"],
+                                        in_gemm_kernel=gemm_flops / B, in_fused_convblocks=fused_flops / B),
                     whole_step_tflops=whole, whole_step_frac=whole / pk["tensor"],
                     whole_step_note="every dense FLOP of the pass in the reference's formulation / the whole timed step")
+    cb_ms = by_kind_busy.get("CONVBLOCK", 0.0) / trace_total * ms
+    if fused and cb_ms > 0:
+        gbs = fused_bytes / (cb_ms * 1e-3) / 1e9
+        roofline["fused_convblock"] = dict(kernel="convblock_pair_kernel", bound="hbm", achieved=gbs, peak=pk["hbm"], unit="GB/s",
+                                           frac=gbs / pk["hbm"], launches_per_step=len(fused), kernel_ms_per_step=cb_ms,
+                                           algorithmic_bytes_per_step=fused_bytes, tflops=fused_flops / (cb_ms * 1e-3) / 1e12,
+                                           note="bytes = x + condition + outputs of every launch, once (bf16); the kernel keeps "
+                                                "c1 / c2 in shared memory; its MMAs (N = 64) are shared-memory bound (DESIGN.md)")
     if traffic and gemm_ms > 0:
         gbs = traffic * n_gemm / (gemm_ms * 1e-3) / 1e9
         roofline["hbm_view"] = dict(achieved=gbs, peak=pk["hbm"], unit="GB/s", frac=gbs / pk["hbm"],

@@ -136,7 +136,7 @@ def gru(sd, prefix, x, num_layers, explicit=False):
             x = torch.cat(outs, dim=-1)
     else:
         C = x.shape[-1]
-        m = torch.nn.GRU(C, C // 2, num_layers=num_layers, bidirectional=True, batch_first=True)
+        m = torch.nn.GRU(C, C // 2, num_layers=num_layers, bidirectional=True, batch_first=True).to(x.device)
         m.load_state_dict({k[len(prefix) + 1 :]: v for k, v in sd.items() if k.startswith(prefix + ".")})
         with torch.no_grad():
             x, _ = m(x)
