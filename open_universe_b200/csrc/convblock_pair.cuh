@@ -366,9 +366,28 @@ __global__ void __launch_bounds__(kCbThreads, 1) convblock_pair_kernel(const __g
       pdl_wait();
       uint32_t pf[kCbXBufs] = {0, 0, 0};
       int xb = 0;
+      // variable-length calls: a tile whose output rows all lie past their utterances' ends is dropped by the leader
+      // (nothing to compute: those rows are zero padding and stay zero)
+      auto tile_has_rows = [&](int claim) {
+        const int t = P.reverse ? P.n_tiles - 1 - claim : claim;
+        const long long g0 = (long long)t * kPairCtas * kCbRowsOut;
+        long long g1 = g0 + kPairCtas * kCbRowsOut;
+        if (g1 > P.m_rows) g1 = P.m_rows;
+        for (int b = (int)(g0 / P.Lh); (long long)b * P.Lh < g1; ++b) {
+          const long long m_lo = g0 - (long long)b * P.Lh;
+          if ((m_lo < 0 ? 0 : m_lo) < cb_valid_rows(P, mv_s, b)) return true;
+        }
+        return false;
+      };
       for (int k = 0;; ++k) {
         int tile_id;
         if (leader) {
+          if (P.mv) {
+            while (tile < P.n_tiles && !tile_has_rows(tile)) {
+              tile = tile_nxt;
+              if (tile_nxt < P.n_tiles) tile_nxt = atomicAdd(P.sched, 1);
+            }
+          }
           const bool live = tile < P.n_tiles;
           mbar_wait(smem_u32(&B->s_empty[ss]), sp ^ 1, P.err_flag, 9);
           tile_id = live ? (P.reverse ? P.n_tiles - 1 - tile : tile) : -1;

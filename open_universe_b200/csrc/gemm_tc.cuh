@@ -837,9 +837,28 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
         tile_nxt = atomicAdd(P.sched, 1);
       }
       pdl_wait();   // weights and the tile counter do not depend on the predecessor; the activations do
+      // variable-length calls: a tile whose rows all lie past their utterances' ends has nothing to compute or store
+      // (those rows are zero padding and stay zero): the leader drops its claim and takes the next one
+      auto tile_has_rows = [&](int claim) {
+        const int t = P.reverse ? total_tiles - 1 - claim : claim;
+        const int g0 = (t / P.n_tiles_n) * kPairCtas * cta_rows;
+        int g1 = g0 + kPairCtas * cta_rows;
+        if (g1 > P.m_rows) g1 = P.m_rows;
+        for (int b = g0 / P.Lh_A; (long long)b * P.Lh_A < g1; ++b) {
+          const int m_lo = g0 - b * P.Lh_A;   // first row of the tile inside utterance b (<= 0: the tile starts before it)
+          if ((m_lo < 0 ? 0 : m_lo) < (b < kMvEntries ? mv_s[b] : P.mv[b])) return true;
+        }
+        return false;
+      };
       for (;;) {
         int tile_id;
         if (leader) {
+          if (P.mv) {
+            while (tile < total_tiles && !tile_has_rows(tile)) {
+              tile = tile_nxt;
+              if (tile_nxt < total_tiles) tile_nxt = atomicAdd(P.sched, 1);
+            }
+          }
           const bool live = tile < total_tiles;
           mbar_wait_cl(smem_u32(&s_empty[ss]), sp ^ 1, P.err_flag, 9);
           // reverse: claim k is tile total-1-k.  A kernel's output (263 MB at the finest levels) exceeds the 126 MB L2, so

@@ -293,6 +293,8 @@ class PackedModel:
 
     def add_conv_in(self, sd, prefix, name):
         w = eff_weight(sd, prefix)  # [C, 1, 3]
+        if w.shape[1] != 1 or w.shape[2] != 3:
+            raise NotImplementedError(f"{prefix}: the 1 -> C edge conv kernel handles fb_kernel_size == 3, input_channels == 1 (got {tuple(w.shape)})")
         self.layers[name] = dict(w_w=self.blob.add_f32(w[:, 0, :].t().contiguous()),
                                  bias_w=self.blob.add_f32(sd[prefix + ".bias"]), C=w.shape[0])
 
@@ -362,6 +364,8 @@ def pack_model(sd, cfg):
                       sd[f"{sp}.sigma_block.layer{i}.lin.bias"].float().reshape(-1)]
         pm.layers["s.embed"] = dict(w_w=pm.blob.add_f32(torch.cat(parts)), n_rff=int(sd[sp + ".sigma_block.freq"].numel()))
     wo = eff_weight(sd, sp + ".output_conv.conv")  # [1, C, 3]
+    if wo.shape[0] != 1 or wo.shape[2] != 3:
+        raise NotImplementedError(f"output_conv: the C -> 1 edge conv kernel handles fb_kernel_size == 3, output_channels == 1 (got {tuple(wo.shape)})")
     pm.layers["s.out"] = dict(w_w=pm.blob.add_f32(wo[0].t().contiguous()), bias_w=pm.blob.add_f32(sd[sp + ".output_conv.conv.bias"]),
                               slope_a=float(sd[sp + ".prelu.weight"]), slope_b=float(sd[sp + ".output_conv.prelu.weight"]))
 

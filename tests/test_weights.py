@@ -98,3 +98,17 @@ def test_dft_basis_matches_rfft():
     ri = x @ basis
     ref = torch.fft.rfft(x * win)
     assert torch.allclose(ri[:, :nb], ref.real, atol=1e-4) and torch.allclose(ri[:, nbp : nbp + nb], -ref.imag, atol=1e-4)
+
+
+def test_unsupported_edge_conv_kernel_size_is_rejected():
+    """conv_in / conv_out kernels are 3-tap: any other fb_kernel_size must fail at pack time, not run wrong."""
+    import pytest
+    from conftest import build_model
+    from open_universe_b200 import weights
+
+    model, cfg = build_model("universepp_16k")
+    sd = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    key = next(k for k in sd if k.endswith("condition_model.input_conv.weight_v") or k.endswith("condition_model.input_conv.weight"))
+    sd[key] = torch.zeros(sd[key].shape[0], 1, 5)
+    with pytest.raises(NotImplementedError):
+        weights.pack_model(sd, model.model_config())
