@@ -274,6 +274,8 @@ __global__ void __launch_bounds__(kCbThreads, 1) convblock_pair_kernel(const __g
   const uint32_t rank = cta_rank_in_cluster();
   const bool leader = rank == 0;
   pdl_launch_dependents();
+  int claim0 = 0;   // the pair's first two tile claims: one atomic, issued before the prologue (as in gemm_tc.cuh)
+  if (threadIdx.x == 0 && leader) claim0 = atomicAdd(P.sched, 2);
   const CbSmem L = cb_smem_layout(P);
   uint8_t* ones = smem;
   float* film_s = reinterpret_cast<float*>(smem + L.film_off);
@@ -348,6 +350,7 @@ __global__ void __launch_bounds__(kCbThreads, 1) convblock_pair_kernel(const __g
 
   if (warp == 0) {
     // ============================== loads
+    claim0 = __shfl_sync(0xffffffffu, claim0, 0);
     if (elect_one()) {
       {  // resident weights of the three stages (this CTA's half of the columns)
         uint32_t tot = 0;
@@ -360,8 +363,8 @@ __global__ void __launch_bounds__(kCbThreads, 1) convblock_pair_kernel(const __g
       int tile = 0, tile_nxt = 0;
       const uint32_t ring_peer = map_shared_rank(smem_u32(B->s_ring), 1), sfull_peer = map_shared_rank(smem_u32(B->s_full), 1);
       if (leader) {
-        tile = atomicAdd(P.sched, 1);
-        tile_nxt = atomicAdd(P.sched, 1);
+        tile = claim0;
+        tile_nxt = claim0 + 1;
       }
       pdl_wait();
       uint32_t pf[kCbXBufs] = {0, 0, 0};
