@@ -287,36 +287,44 @@ __global__ void __launch_bounds__(kCbThreads, 1) convblock_pair_kernel(const __g
   constexpr int n_half = kCbN / 2;
   constexpr uint32_t tmem_cols = kCbSlots * 2 * kCbN;   // per slot: two sub-tile accumulators of 64 columns
 
-  if (threadIdx.x == 0) {
+  {
+    // barrier set-up spread over threads (as in gemm_tc.cuh)
     const uint32_t pr = leader ? 1u : 0u;
-    for (int x = 0; x < kCbXBufs; ++x) {
+    const int t = threadIdx.x;
+    if (t < kSchedSlots) {
+      const uint32_t ring_readers = (1 + kEpiWarps + kCbXfWarps) + (2 + kEpiWarps + kCbXfWarps);
+      mbar_init(smem_u32(&B->s_full[t]), 1);
+      mbar_init(smem_u32(&B->s_empty[t]), ring_readers);
+    } else if (t < kSchedSlots + kCbXBufs) {
+      const int x = t - kSchedSlots;
       mbar_init(smem_u32(&B->x_full[x]), 1);
       mbar_init(smem_u32(&B->x_free[x]), 1);
-    }
-    for (int s = 0; s < kCbSlots; ++s) {
+    } else if (t < kSchedSlots + kCbXBufs + kCbSlots) {
+      const int s = t - kSchedSlots - kCbXBufs;
       mbar_init(smem_u32(&B->w_free[s]), 1);
       mbar_init(smem_u32(&B->xa_ready[s]), kCbXfWarps + pr);   // leader: + the peer's relay
       mbar_init(smem_u32(&B->mma_done[s]), 1);
       mbar_init(smem_u32(&B->epi_done[s]), 2 * kEpiWarps);   // (leader's is used) both CTAs' epilogue warps
+      B->st_cnt[s] = 0;
+    } else if (t == kSchedSlots + kCbXBufs + kCbSlots) {
+      mbar_init(smem_u32(&B->w_full), 1 + pr);
     }
-    mbar_init(smem_u32(&B->w_full), 1 + pr);
-    B->st_cnt[0] = B->st_cnt[1] = 0;
-    const uint32_t ring_readers = (1 + kEpiWarps + kCbXfWarps) + (2 + kEpiWarps + kCbXfWarps);
-    for (int i = 0; i < kSchedSlots; ++i) { mbar_init(smem_u32(&B->s_full[i]), 1); mbar_init(smem_u32(&B->s_empty[i]), ring_readers); }
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    if (t <= kSchedSlots + kCbXBufs + kCbSlots) asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (threadIdx.x < 256) {   // ones tile: K columns 0 / 1 meet the hi / lo halves of a bias image
     uint4 u = make_uint4(0u, 0u, 0u, 0u);
     if (threadIdx.x < kSubM) u.x = 0x3F803F80u;
     reinterpret_cast<uint4*>(ones)[threadIdx.x] = u;
   }
-  if (P.film)
-    for (int k = threadIdx.x; k < 2 * kCbN; k += kCbThreads)
-      film_s[k] = P.film[(k < kCbN ? 0 : P.film_C) + (k % kCbN) % P.film_C];
-  if (P.mv) {   // (host-written in front of the call: safe before pdl_wait)
-    const int n_utt = (P.m_rows + P.Lh - 1) / P.Lh;
-    for (int k = threadIdx.x; k < n_utt && k < kMvEntries; k += kCbThreads) mv_s[k] = P.mv[k];
-  }
+  // FiLM table / per-utterance valid rows: loaded to registers here, stored behind the cluster barrier below so that
+  // the load latency overlaps it (both are written in front of the call, not by a predecessor: safe before pdl_wait)
+  static_assert(2 * kCbN <= kCbThreads && kMvEntries <= kCbThreads, "one entry per thread");
+  float film_r = 0.f;
+  int mv_r = 0;
+  const bool film_on = P.film != nullptr && threadIdx.x < 2 * kCbN;
+  const bool mv_on = P.mv != nullptr && (int)threadIdx.x < kMvEntries && (long long)threadIdx.x * P.Lh < P.m_rows;
+  if (film_on) { const int k = threadIdx.x; film_r = P.film[(k < kCbN ? 0 : P.film_C) + (k % kCbN) % P.film_C]; }
+  if (mv_on) mv_r = P.mv[threadIdx.x];
   {  // identity image [8 chunks][n_half][8]: residual channel k -> column k; local column n stands for rank * n_half + n
     for (int i = threadIdx.x; i < kCbPlanes * n_half; i += kCbThreads) {
       const int c = i / n_half, n = i - c * n_half + (int)rank * n_half;
@@ -336,6 +344,8 @@ __global__ void __launch_bounds__(kCbThreads, 1) convblock_pair_kernel(const __g
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
   }
+  if (film_on) film_s[threadIdx.x] = film_r;
+  if (mv_on) mv_s[threadIdx.x] = mv_r;
   tc_fence_before();
   __syncthreads();
   cluster_barrier();

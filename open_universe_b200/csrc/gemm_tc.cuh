@@ -741,21 +741,29 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
   const int msub = P.msub;                         // 128-row sub-tiles per CTA (2 for narrow tiles)
   const uint32_t tmem_cols = (uint32_t)n_acc * msub * acc_stride;
   const uint32_t xf = P.a_act ? (uint32_t)kXfWarps : 0u;
-  if (threadIdx.x == 0) {
+  {
+    // barrier set-up, one barrier group per thread (144 inits by one thread were ~1 us of every launch's prologue).
     // arrival counts: the leader's "full" barriers also take the peer's relay arrive; the leader's "empty" barriers
     // of the accumulators and of the tile ring take the readers of both CTAs
     const uint32_t pr = leader ? 1u : 0u;
-    for (int i = 0; i < kMaxAStages; ++i) {
+    int i = threadIdx.x;
+    if (i < kMaxAStages) {
       mbar_init(smem_u32(&a_full[i]), 1 + (P.a_act ? 0u : pr));
       mbar_init(smem_u32(&a_ready[i]), kXfWarps + pr);
       mbar_init(smem_u32(&a_empty[i]), 1);
+    } else if ((i -= kMaxAStages) < kMaxBStages) {
+      mbar_init(smem_u32(&b_full[i]), 1 + pr);
+      mbar_init(smem_u32(&b_empty[i]), 1);
+    } else if ((i -= kMaxBStages) < kMaxAcc) {
+      mbar_init(smem_u32(&t_full[i]), 1);
+      mbar_init(smem_u32(&t_empty[i]), 2 * kEpiWarps);
+    } else if ((i -= kMaxAcc) < kSchedSlots) {
+      // ring readers: leader = MMA issuer + epilogue + transform warps, peer = producer + relay + epilogue + transform warps
+      const uint32_t ring_readers = (1 + kEpiWarps + xf) + (2 + kEpiWarps + xf);
+      mbar_init(smem_u32(&s_full[i]), 1);
+      mbar_init(smem_u32(&s_empty[i]), ring_readers);
     }
-    for (int i = 0; i < kMaxBStages; ++i) { mbar_init(smem_u32(&b_full[i]), 1 + pr); mbar_init(smem_u32(&b_empty[i]), 1); }
-    for (int i = 0; i < kMaxAcc; ++i) { mbar_init(smem_u32(&t_full[i]), 1); mbar_init(smem_u32(&t_empty[i]), 2 * kEpiWarps); }
-    // ring readers: leader = MMA issuer + epilogue + transform warps, peer = producer + relay + epilogue + transform warps
-    const uint32_t ring_readers = (1 + kEpiWarps + xf) + (2 + kEpiWarps + xf);
-    for (int i = 0; i < kSchedSlots; ++i) { mbar_init(smem_u32(&s_full[i]), 1); mbar_init(smem_u32(&s_empty[i]), ring_readers); }
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    if (threadIdx.x < kMaxAStages + kMaxBStages + kMaxAcc + kSchedSlots) asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   // ones tile: K columns 0 and 1 are 1.0 (they meet the hi / lo halves of the bias image), the rest 0
   if (threadIdx.x < 256) {
@@ -763,13 +771,22 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
     if (threadIdx.x < kSubM) u.x = 0x3F803F80u;
     reinterpret_cast<uint4*>(ones)[threadIdx.x] = u;
   }
+  // FiLM table and per-utterance valid rows: loaded into registers here, stored to shared memory behind the cluster
+  // barrier / tensor-memory allocation below, so the global-load latency (~0.7 us) overlaps them instead of preceding
+  // them.  (Both are written in front of the call -- plan-time FiLM kernel, host tables --, not by a predecessor
+  // kernel: safe before pdl_wait.)
+  constexpr int kFilmPerThread = (kFilmBytes / 4 + kGemmThreads - 1) / kGemmThreads;
+  float film_r[kFilmPerThread];
+  int mv_r = 0;
+  const bool mv_on = P.mv != nullptr && (int)threadIdx.x < kMvEntries && (int)threadIdx.x * P.Lh_A < P.m_rows;
   if (P.film) {
-    for (int i = threadIdx.x; i < 2 * P.C_out; i += kGemmThreads) film_s[i] = P.film[i];
+#pragma unroll
+    for (int j = 0; j < kFilmPerThread; ++j) {
+      const int i = threadIdx.x + j * kGemmThreads;
+      film_r[j] = i < 2 * P.C_out ? P.film[i] : 0.f;
+    }
   }
-  if (P.mv) {   // (written by the host in front of the call, not by a predecessor kernel: safe before pdl_wait)
-    const int n_utt = (P.m_rows + P.Lh_A - 1) / P.Lh_A;
-    for (int i = threadIdx.x; i < n_utt && i < kMvEntries; i += kGemmThreads) mv_s[i] = P.mv[i];
-  }
+  if (mv_on) mv_r = P.mv[threadIdx.x];
   if (P.add_kc) {
     // this CTA's half of the identity images [N_TILE / add_kc][add_kc / 8][n_half][8]: image j maps residual channel
     // j*add_kc + k to column j*add_kc + k; local column n stands for column rank*n_half + n
@@ -792,6 +809,14 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
   }
+  if (P.film) {
+#pragma unroll
+    for (int j = 0; j < kFilmPerThread; ++j) {
+      const int i = threadIdx.x + j * kGemmThreads;
+      if (i < 2 * P.C_out) film_s[i] = film_r[j];
+    }
+  }
+  if (mv_on) mv_s[threadIdx.x] = mv_r;
   tc_fence_before();
   __syncthreads();
   cluster_barrier();
