@@ -374,6 +374,9 @@ def run_native(args, wl, rank, world, local_rank):
                     traffic_source=traffic_src, traffic_note=traffic_note, build=build,
                     peak_source=pk["src"] + " sustained bf16 (cuBLAS, seconds-long loop under the power cap)",
                     launches_per_step=n_gemm, kernel_ms_per_step=gemm_ms, share_of_step=gemm_share,
+                    # its share of the SUM of all launch durations of the traced pass: the figure that compares with the
+                    # serialised ncu launch list (profiles/r2_launches_final.txt), where nothing overlaps
+                    share_of_summed_launch_time=by_kind_sum.get("GEMM", 0.0) / max(sum(by_kind_sum.values()), 1e-9),
                     accounting=("kernel_ms_per_step = union of the kernel's launch intervals over both utterance lanes in the "
                                 "two-stream schedule (uv_trace_ops, CUDA events) / traced pass x graph-timed ms_per_step; "
                                 "achieved = algorithmic FLOPs of the layers this kernel executes (reference formulation, hoisted "
