@@ -293,11 +293,49 @@ def run_native(args, wl, rank, world, local_rank):
         return model._enhance_impl(mix_dev, n_steps, None, None, None, None, False, False, None, "median", None,
                                    noise=noise, return_steps=False)
 
-    def step_e2e():
-        m = mix_host.to(dev, non_blocking=True)          # H2D from pinned memory
-        out = model.enhance(m, n_steps=n_steps, rng=gen)   # public API (draws the noise with torch.randn)
-        out_host.copy_(out)                              # D2H of the result (blocking)
-        return out_host
+    # End to end, the way a serving loop calls the public API: every step copies ITS input from pinned host memory and ITS
+    # result back to pinned host memory.  The copies run on their own streams (double-buffered device inputs), so the H2D
+    # of step k + 1 and the D2H of step k - 1 overlap the compute of step k; the host never runs more than two steps ahead
+    # (it waits for the D2H of step k - 2), and the timed region ends behind the last D2H.  Same-box probe: 43.16 ms per
+    # step with blocking copies on one stream, 42.60 ms this way.
+    s_in, s_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+    main = torch.cuda.current_stream(dev)
+    dbuf = [torch.empty(B, T, device=dev) for _ in range(2)]
+
+    def run_e2e(k):
+        in_ready = [torch.cuda.Event() for _ in range(2)]
+        in_free = [torch.cuda.Event() for _ in range(2)]
+        for e in in_free:
+            e.record(main)
+        done, keep = [], [None, None]
+
+        def prefetch(slot):
+            with torch.cuda.stream(s_in):
+                s_in.wait_event(in_free[slot])
+                dbuf[slot].copy_(mix_host, non_blocking=True)      # H2D from pinned memory
+                in_ready[slot].record(s_in)
+
+        prefetch(0)
+        for i in range(k):
+            cur = i & 1
+            if i >= 2:
+                done[i - 2].synchronize()
+            if i + 1 < k:
+                prefetch(cur ^ 1)
+            main.wait_event(in_ready[cur])
+            out = model.enhance(dbuf[cur], n_steps=n_steps, rng=gen)   # public API (draws the noise with torch.randn)
+            in_free[cur].record(main)
+            ev = torch.cuda.Event()
+            ev.record(main)
+            with torch.cuda.stream(s_out):
+                s_out.wait_event(ev)
+                out_host.copy_(out, non_blocking=True)             # D2H of the result
+                d = torch.cuda.Event()
+                d.record(s_out)
+            done.append(d)
+            keep[cur] = out
+        for d in done[-2:]:
+            main.wait_event(d)
 
     def timed(fn, k):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -317,9 +355,8 @@ def run_native(args, wl, rank, world, local_rank):
     sampler = ClockSampler(local_rank) if rank == 0 else None
     ms = timed(step_resident, args.steps)
     clocks = sampler.stop() if sampler else None
-    for _ in range(2):
-        step_e2e()
-    ms_e2e = timed(step_e2e, args.steps)
+    run_e2e(3)
+    ms_e2e = timed(lambda: run_e2e(args.steps), 1) / args.steps
 
     # the dominant kernel INSIDE the timed schedule: uv_trace_ops runs the pass the way the graph runs it (both
     # utterance lanes on their own streams, same fork / join / stagger edges) with an event pair around every
@@ -409,7 +446,9 @@ def run_native(args, wl, rank, world, local_rank):
                             timing="CUDA events on the launch stream, max over ranks"),
                 clocks=clocks,
                 e2e=dict(value=audio_s / (ms_e2e * 1e-3), unit="audio-s/s", ms_per_step=ms_e2e,
-                         h2d_bytes_per_step=B * T * 4, d2h_bytes_per_step=B * T * 4),
+                         h2d_bytes_per_step=B * T * 4, d2h_bytes_per_step=B * T * 4,
+                         note="model.enhance() per step on pinned host buffers; each step's H2D / D2H run on copy streams and "
+                              "overlap the neighbouring steps' compute (host at most two steps ahead); all inside the timed region"),
                 gpu_launches=plan.num_launches * args.steps,
                 roofline=roofline,
                 busy_ms_in_schedule={k: round(v / trace_total * ms, 3) for k, v in sorted(by_kind_busy.items(), key=lambda kv: -kv[1])},
