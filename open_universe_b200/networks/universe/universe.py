@@ -288,10 +288,10 @@ class Universe(torch.nn.Module):
         elif noise is None:
             # same draws, same order as the reference (universe.py:39-41,326,338): n_steps tensors of (B,1,Lp)
             # (use_aux_signal draws nothing, warm_start = n draws for the steps from n on: universe.py:317-331)
-            noise = torch.zeros((n_steps, B, Lp), dtype=torch.float32, device=dev)
             first = n_steps if use_aux_signal else (int(warm_start) if warm_start is not None else 0)
-            for i in range(first, n_steps):
-                noise[i] = torch.randn((B, 1, Lp), dtype=torch.float32, device=dev, generator=rng)[:, 0, :]
+            noise = (torch.empty if first == 0 else torch.zeros)((n_steps, B, Lp), dtype=torch.float32, device=dev)
+            for i in range(first, n_steps):   # drawn in place: randn(out=) is empty(...).normal_(), the same draws
+                torch.randn((B, 1, Lp), dtype=torch.float32, device=dev, generator=rng, out=noise[i].view(B, 1, Lp))
         else:
             noise = noise.to(device=dev, dtype=torch.float32).reshape(n_steps, B, Lp).contiguous()
         out = torch.empty((B, T), dtype=torch.float32, device=dev)
