@@ -263,10 +263,11 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
     case UV_OP_MEL: {
       if (op.T != kMelFT) return fail(UV_ERR_INVALID, "MEL op built for another frame tile than the kernel's");
       const int nft = (op.F + kMelFT - 1) / kMelFT;
-      const size_t sm = ((size_t)(kMelFT - 1) * op.i1 + op.i0 + 4 + (size_t)kMelPwPitch * op.i2) * sizeof(float);
+      const size_t sm = mel_smem_bytes(op.i0, op.i1);
       const int threads = (op.i2 + 31) / 32 * 32;   // one thread per frequency bin
-      // (the filterbank stage keeps two chunks of kMelFbRows x n_mels floats in the signal buffer, one band per thread)
-      if (threads > 512 || sm > (size_t)kMelMaxSmem || op.i0 % 4 || op.i1 % 4 || op.C > threads ||
+      // (the filterbank stage keeps two chunks of kMelFbRows x n_mels floats in the signal buffer, one band per thread;
+      // the folded DFT needs n_fft / 2 to be a multiple of 4 and all n_fft / 2 + 1 bins)
+      if (threads > 512 || sm > (size_t)kMelMaxSmem || op.i0 % 8 || op.i1 % 4 || op.C > threads || op.i2 != op.i0 / 2 + 1 ||
           2 * kMelFbRows * op.C > (kMelFT - 1) * op.i1 + op.i0)
         return fail(UV_ERR_INVALID, "MEL front end: n_fft / hop / n_mels unsupported");
       CUDA_TRY(launch_pdl(mel_kernel, dim3(nft, op.B), dim3(threads), sm, s, aptr<const float>(p, op.p0), op.Lp, op.F, op.i0, op.i1, op.i2, op.H, op.C,
@@ -830,8 +831,9 @@ extern "C" int uv_mel_spec_static(uv_model* m, const uv_mel_desc* d, const float
   const int F = Lp / d->hop;
   const int nft = (F + kMelFT - 1) / kMelFT;
   const int threads = (d->n_bins + 31) / 32 * 32;
-  const size_t sm = ((size_t)(kMelFT - 1) * d->hop + d->n_fft + 4 + (size_t)kMelPwPitch * d->n_bins) * sizeof(float);
-  if (threads > 512 || sm > (size_t)kMelMaxSmem || d->n_fft % 4 || d->hop % 4 || d->n_mels > threads || d->n_mels <= 0 ||
+  const size_t sm = mel_smem_bytes(d->n_fft, d->hop);
+  if (threads > 512 || sm > (size_t)kMelMaxSmem || d->n_fft % 8 || d->hop % 4 || d->n_mels > threads || d->n_mels <= 0 ||
+      d->n_bins != d->n_fft / 2 + 1 ||
       d->nbp < d->n_bins || 2 * kMelFbRows * d->n_mels > (kMelFT - 1) * d->hop + d->n_fft)
     return fail(UV_ERR_INVALID, "uv_mel_spec_static: n_fft / hop / n_mels unsupported");
   const size_t need = ((size_t)B * F * d->n_mels + (size_t)B * nft) * sizeof(float);

@@ -123,6 +123,15 @@ __global__ void __launch_bounds__(1024) prep_kernel(const IoTable* io, int b_off
 constexpr int kMelFT = 32;
 constexpr int kMelFbRows = 16;            // filterbank rows (bins) per staged chunk
 constexpr int kMelPwPitch = kMelFT + 4;   // power spectrum rows [bin][frame], padded: conflict-free 16-byte accesses
+// Folded DFT: the window is symmetric about n_fft / 2 (Hann; checked by the host when the basis is packed), so
+//   re[k] = sum_{n=0}^{N/2} (x[n] + x[N-n]) C[n][k],   im[k] = sum_{n=1}^{N/2-1} (x[n] - x[N-n]) S[n][k]
+// (n = 0 and n = N/2 unpaired): the folded frames a = x[n] + x[N-n], b = x[n] - x[N-n] are built once per CTA in shared
+// memory and the multiply-adds per bin are halved.  Only basis rows 0 .. N/2 are read.
+__host__ __device__ inline int mel_fold_pitch(int n_fft) { return n_fft / 2 + 4; }   // floats per folded frame (n = 0 .. N/2, padded)
+__host__ __device__ inline size_t mel_smem_bytes(int n_fft, int hop) {
+  const int span = (kMelFT - 1) * hop + n_fft;
+  return ((size_t)((span + 3) & ~3) + 2 * (size_t)kMelFT * mel_fold_pitch(n_fft)) * sizeof(float);   // (the power rows overlay the folded frames)
+}
 __global__ void __launch_bounds__(512) mel_kernel(const float* __restrict__ sig, int Lp, int F, int n_fft, int hop,
                                                   int nb, int nbp, int n_mels, int pad_left,
                                                   const float* __restrict__ basis, const float* __restrict__ fb,
@@ -132,8 +141,11 @@ __global__ void __launch_bounds__(512) mel_kernel(const float* __restrict__ sig,
   pdl_wait();
   extern __shared__ float smem_f[];
   const int span = (kMelFT - 1) * hop + n_fft;
-  float* xs = smem_f;          // [span]
-  float* pw = smem_f + ((span + 3) & ~3);   // [nb][kMelPwPitch]
+  const int nh = n_fft >> 1, fp = mel_fold_pitch(n_fft);
+  float* xs = smem_f;                           // [span] (later: filterbank staging)
+  float* fa = smem_f + ((span + 3) & ~3);       // [kMelFT][fp]  x[n] + x[N - n]
+  float* fd = fa + (size_t)kMelFT * fp;         // [kMelFT][fp]  x[n] - x[N - n]
+  float* pw = fa;                               // [nb][kMelPwPitch]: overlays the folded frames once the DFT is done
   __shared__ double sh[96];
   const int b = blockIdx.y, f0 = blockIdx.x * kMelFT;
   const int Fb = rows ? rows[b].F : F;
@@ -143,34 +155,57 @@ __global__ void __launch_bounds__(512) mel_kernel(const float* __restrict__ sig,
     xs[i] = (j >= 0 && j < Lp) ? x[j] : 0.f;
   }
   __syncthreads();
-  for (int k = threadIdx.x; k < nb; k += blockDim.x) {
-    float re[kMelFT], im[kMelFT];
+  for (int e = threadIdx.x; e < kMelFT * fp; e += blockDim.x) {
+    const int f = e / fp, n = e - f * fp;
+    const float* xf = xs + f * hop;
+    float va = 0.f, vd = 0.f;
+    if (n == 0 || n == nh) {
+      va = xf[n];
+    } else if (n < nh) {
+      va = xf[n] + xf[n_fft - n];
+      vd = xf[n] - xf[n_fft - n];
+    }
+    fa[e] = va;
+    fd[e] = vd;
+  }
+  __syncthreads();
+  const int k = threadIdx.x;           // one frequency bin per thread (the host launches >= nb threads)
+  const bool bin_on = k < nb;
+  float re[kMelFT], im[kMelFT];
 #pragma unroll
-    for (int f = 0; f < kMelFT; ++f) re[f] = im[f] = 0.f;
+  for (int f = 0; f < kMelFT; ++f) re[f] = im[f] = 0.f;
+  if (bin_on) {
     const float* bc = basis + k;
     const float* bs = basis + nbp + k;
-    // four samples per step: one 16-byte broadcast load feeds 8 FMAs (scalar loads left the loop LDS bound);
-    // hop and n are multiples of 4, so the loads stay 16-byte aligned
+    // four samples per step: 16-byte broadcast loads of the folded frames feed 8 FMAs per frame; n_fft / 2 is a
+    // multiple of 4, so the loads stay 16-byte aligned
     const size_t bst = (size_t)2 * nbp;
     float c[4], s4[4], cn[4], sn[4];   // basis of this / the next step (one CTA per SM: nothing else hides the L2 latency)
 #pragma unroll
     for (int j = 0; j < 4; ++j) { cn[j] = bc[(size_t)j * bst]; sn[j] = bs[(size_t)j * bst]; }
-    for (int n = 0; n < n_fft; n += 4) {
+    for (int n = 0; n < nh; n += 4) {
 #pragma unroll
       for (int j = 0; j < 4; ++j) { c[j] = cn[j]; s4[j] = sn[j]; }
-      if (n + 4 < n_fft) {
+      if (n + 4 < nh) {
 #pragma unroll
         for (int j = 0; j < 4; ++j) { cn[j] = bc[(size_t)(n + 4 + j) * bst]; sn[j] = bs[(size_t)(n + 4 + j) * bst]; }
       }
 #pragma unroll
       for (int f = 0; f < kMelFT; ++f) {
-        const float4 v = *reinterpret_cast<const float4*>(xs + f * hop + n);
-        re[f] = fmaf(v.x, c[0], re[f]); im[f] = fmaf(v.x, s4[0], im[f]);
-        re[f] = fmaf(v.y, c[1], re[f]); im[f] = fmaf(v.y, s4[1], im[f]);
-        re[f] = fmaf(v.z, c[2], re[f]); im[f] = fmaf(v.z, s4[2], im[f]);
-        re[f] = fmaf(v.w, c[3], re[f]); im[f] = fmaf(v.w, s4[3], im[f]);
+        const float4 va = *reinterpret_cast<const float4*>(fa + f * fp + n);
+        const float4 vd = *reinterpret_cast<const float4*>(fd + f * fp + n);
+        re[f] = fmaf(va.x, c[0], re[f]); im[f] = fmaf(vd.x, s4[0], im[f]);
+        re[f] = fmaf(va.y, c[1], re[f]); im[f] = fmaf(vd.y, s4[1], im[f]);
+        re[f] = fmaf(va.z, c[2], re[f]); im[f] = fmaf(vd.z, s4[2], im[f]);
+        re[f] = fmaf(va.w, c[3], re[f]); im[f] = fmaf(vd.w, s4[3], im[f]);
       }
     }
+    const float cm = bc[(size_t)nh * bst];   // the unpaired middle sample (its sine term is zero)
+#pragma unroll
+    for (int f = 0; f < kMelFT; ++f) re[f] = fmaf(fa[f * fp + nh], cm, re[f]);
+  }
+  __syncthreads();   // every bin has read the folded frames: the power rows may overwrite them
+  if (bin_on) {
 #pragma unroll
     for (int f = 0; f < kMelFT; f += 4)
       *reinterpret_cast<float4*>(pw + (size_t)k * kMelPwPitch + f) =

@@ -221,6 +221,11 @@ def dft_basis(window, n_fft):
     """Windowed real-DFT basis f32 [n_fft][2 * nbp]: cos | sin, nbp = bins padded to 32."""
     nb = n_fft // 2 + 1
     nbp = (nb + 31) // 32 * 32
+    # the mel kernel folds the DFT about n_fft / 2 (csrc/small_ops.cuh): that needs w[n] == w[n_fft - n], which the
+    # reference's periodic Hann window satisfies (torchaudio MelSpectrogram default, condition.py:69-90)
+    wd = window.double()
+    if n_fft % 8 or (wd[1:] - wd[1:].flip(0)).abs().max() > 1e-6 * wd.abs().max():
+        raise NotImplementedError("mel front end: the window must be symmetric about n_fft / 2 and n_fft a multiple of 8")
     n = torch.arange(n_fft, dtype=torch.float64)[:, None]
     k = torch.arange(nb, dtype=torch.float64)[None, :]
     ang = 2.0 * math.pi * ((n * k) % n_fft) / n_fft
