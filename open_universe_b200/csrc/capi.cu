@@ -1,5 +1,6 @@
 // C ABI (include/universe_b200.h): model = device weight blob, plan = op program +
 // arena + CUDA graph.  Translates uv_op records into kernel launches.
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -264,7 +265,7 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
       if (op.T != kMelFT) return fail(UV_ERR_INVALID, "MEL op built for another frame tile than the kernel's");
       const int nft = (op.F + kMelFT - 1) / kMelFT;
       const size_t sm = mel_smem_bytes(op.i0, op.i1);
-      const int threads = (op.i2 + 31) / 32 * 32;   // one thread per frequency bin
+      const int threads = std::max(2 * (((op.i2 + 1) / 2 + 31) / 32 * 32), (op.C + 31) / 32 * 32);   // (half of the frames, two bins) per thread; >= one thread per mel band
       // (the filterbank stage keeps two chunks of kMelFbRows x n_mels floats in the signal buffer, one band per thread;
       // the folded DFT needs n_fft / 2 to be a multiple of 4 and all n_fft / 2 + 1 bins)
       if (threads > 512 || sm > (size_t)kMelMaxSmem || op.i0 % 8 || op.i1 % 4 || op.C > threads || op.i2 != op.i0 / 2 + 1 ||
@@ -830,7 +831,7 @@ extern "C" int uv_mel_spec_static(uv_model* m, const uv_mel_desc* d, const float
   if (B <= 0 || Lp <= 0 || d->hop <= 0 || Lp % d->hop) return fail(UV_ERR_INVALID, "uv_mel_spec_static: Lp must be a positive multiple of hop");
   const int F = Lp / d->hop;
   const int nft = (F + kMelFT - 1) / kMelFT;
-  const int threads = (d->n_bins + 31) / 32 * 32;
+  const int threads = std::max(2 * (((d->n_bins + 1) / 2 + 31) / 32 * 32), (d->n_mels + 31) / 32 * 32);
   const size_t sm = mel_smem_bytes(d->n_fft, d->hop);
   if (threads > 512 || sm > (size_t)kMelMaxSmem || d->n_fft % 8 || d->hop % 4 || d->n_mels > threads || d->n_mels <= 0 ||
       d->n_bins != d->n_fft / 2 + 1 ||

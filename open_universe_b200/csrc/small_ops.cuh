@@ -169,48 +169,74 @@ __global__ void __launch_bounds__(512) mel_kernel(const float* __restrict__ sig,
     fd[e] = vd;
   }
   __syncthreads();
-  const int k = threadIdx.x;           // one frequency bin per thread (the host launches >= nb threads)
-  const bool bin_on = k < nb;
-  float re[kMelFT], im[kMelFT];
+  // Thread = (half h of the tile's frames, two adjacent frequency bins): blockDim = 2 x (threads covering ceil(nb / 2)
+  // bin pairs).  A 16-byte load of a folded frame is a broadcast that costs the shared-memory pipe as much as a full
+  // 512-byte access, so what counts is FMAs per load: 16 here (2 bins x 4 samples x re / im per pair of loads) against
+  // 8 with one bin x 32 frames per thread, in the same 64 accumulator registers.
+  constexpr int kHalf = kMelFT / 2;
+  const int nth = blockDim.x >> 1;
+  const int h = threadIdx.x >= nth ? 1 : 0;
+  const int k0 = 2 * (threadIdx.x - h * nth);
+  const bool bin_on = k0 < nb;             // (bin k0 + 1 may be the padding column nb: its basis entries are zero)
+  float re0[kHalf], im0[kHalf], re1[kHalf], im1[kHalf];
 #pragma unroll
-  for (int f = 0; f < kMelFT; ++f) re[f] = im[f] = 0.f;
+  for (int f = 0; f < kHalf; ++f) re0[f] = im0[f] = re1[f] = im1[f] = 0.f;
   if (bin_on) {
-    const float* bc = basis + k;
-    const float* bs = basis + nbp + k;
-    // four samples per step: 16-byte broadcast loads of the folded frames feed 8 FMAs per frame; n_fft / 2 is a
-    // multiple of 4, so the loads stay 16-byte aligned
     const size_t bst = (size_t)2 * nbp;
-    float c[4], s4[4], cn[4], sn[4];   // basis of this / the next step (one CTA per SM: nothing else hides the L2 latency)
+    const float* bc = basis + k0;          // cos | sin halves of a basis row; two adjacent bins = one 8-byte load
+    const float* bs = basis + nbp + k0;
+    const float* fah = fa + (size_t)h * kHalf * fp;
+    const float* fdh = fd + (size_t)h * kHalf * fp;
+    float2 c[4], s4[4], cn[4], sn[4];      // basis of this / the next step (nothing else hides the L2 latency)
 #pragma unroll
-    for (int j = 0; j < 4; ++j) { cn[j] = bc[(size_t)j * bst]; sn[j] = bs[(size_t)j * bst]; }
+    for (int j = 0; j < 4; ++j) {
+      cn[j] = *reinterpret_cast<const float2*>(bc + (size_t)j * bst);
+      sn[j] = *reinterpret_cast<const float2*>(bs + (size_t)j * bst);
+    }
     for (int n = 0; n < nh; n += 4) {
 #pragma unroll
       for (int j = 0; j < 4; ++j) { c[j] = cn[j]; s4[j] = sn[j]; }
       if (n + 4 < nh) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) { cn[j] = bc[(size_t)(n + 4 + j) * bst]; sn[j] = bs[(size_t)(n + 4 + j) * bst]; }
+        for (int j = 0; j < 4; ++j) {
+          cn[j] = *reinterpret_cast<const float2*>(bc + (size_t)(n + 4 + j) * bst);
+          sn[j] = *reinterpret_cast<const float2*>(bs + (size_t)(n + 4 + j) * bst);
+        }
       }
 #pragma unroll
-      for (int f = 0; f < kMelFT; ++f) {
-        const float4 va = *reinterpret_cast<const float4*>(fa + f * fp + n);
-        const float4 vd = *reinterpret_cast<const float4*>(fd + f * fp + n);
-        re[f] = fmaf(va.x, c[0], re[f]); im[f] = fmaf(vd.x, s4[0], im[f]);
-        re[f] = fmaf(va.y, c[1], re[f]); im[f] = fmaf(vd.y, s4[1], im[f]);
-        re[f] = fmaf(va.z, c[2], re[f]); im[f] = fmaf(vd.z, s4[2], im[f]);
-        re[f] = fmaf(va.w, c[3], re[f]); im[f] = fmaf(vd.w, s4[3], im[f]);
+      for (int f = 0; f < kHalf; ++f) {
+        const float4 va = *reinterpret_cast<const float4*>(fah + f * fp + n);
+        const float4 vd = *reinterpret_cast<const float4*>(fdh + f * fp + n);
+        re0[f] = fmaf(va.x, c[0].x, re0[f]); re1[f] = fmaf(va.x, c[0].y, re1[f]);
+        im0[f] = fmaf(vd.x, s4[0].x, im0[f]); im1[f] = fmaf(vd.x, s4[0].y, im1[f]);
+        re0[f] = fmaf(va.y, c[1].x, re0[f]); re1[f] = fmaf(va.y, c[1].y, re1[f]);
+        im0[f] = fmaf(vd.y, s4[1].x, im0[f]); im1[f] = fmaf(vd.y, s4[1].y, im1[f]);
+        re0[f] = fmaf(va.z, c[2].x, re0[f]); re1[f] = fmaf(va.z, c[2].y, re1[f]);
+        im0[f] = fmaf(vd.z, s4[2].x, im0[f]); im1[f] = fmaf(vd.z, s4[2].y, im1[f]);
+        re0[f] = fmaf(va.w, c[3].x, re0[f]); re1[f] = fmaf(va.w, c[3].y, re1[f]);
+        im0[f] = fmaf(vd.w, s4[3].x, im0[f]); im1[f] = fmaf(vd.w, s4[3].y, im1[f]);
       }
     }
-    const float cm = bc[(size_t)nh * bst];   // the unpaired middle sample (its sine term is zero)
+    const float2 cm = *reinterpret_cast<const float2*>(bc + (size_t)nh * bst);   // the unpaired middle sample (its sine term is zero)
 #pragma unroll
-    for (int f = 0; f < kMelFT; ++f) re[f] = fmaf(fa[f * fp + nh], cm, re[f]);
+    for (int f = 0; f < kHalf; ++f) {
+      const float xm = fah[f * fp + nh];
+      re0[f] = fmaf(xm, cm.x, re0[f]);
+      re1[f] = fmaf(xm, cm.y, re1[f]);
+    }
   }
-  __syncthreads();   // every bin has read the folded frames: the power rows may overwrite them
+  __syncthreads();   // every thread has read the folded frames: the power rows may overwrite them
   if (bin_on) {
 #pragma unroll
-    for (int f = 0; f < kMelFT; f += 4)
-      *reinterpret_cast<float4*>(pw + (size_t)k * kMelPwPitch + f) =
-          make_float4(re[f] * re[f] + im[f] * im[f], re[f + 1] * re[f + 1] + im[f + 1] * im[f + 1],
-                      re[f + 2] * re[f + 2] + im[f + 2] * im[f + 2], re[f + 3] * re[f + 3] + im[f + 3] * im[f + 3]);
+    for (int f = 0; f < kHalf; f += 4) {
+      *reinterpret_cast<float4*>(pw + (size_t)k0 * kMelPwPitch + h * kHalf + f) =
+          make_float4(re0[f] * re0[f] + im0[f] * im0[f], re0[f + 1] * re0[f + 1] + im0[f + 1] * im0[f + 1],
+                      re0[f + 2] * re0[f + 2] + im0[f + 2] * im0[f + 2], re0[f + 3] * re0[f + 3] + im0[f + 3] * im0[f + 3]);
+      if (k0 + 1 < nb)
+        *reinterpret_cast<float4*>(pw + (size_t)(k0 + 1) * kMelPwPitch + h * kHalf + f) =
+            make_float4(re1[f] * re1[f] + im1[f] * im1[f], re1[f + 1] * re1[f + 1] + im1[f + 1] * im1[f + 1],
+                        re1[f + 2] * re1[f + 2] + im1[f + 2] * im1[f + 2], re1[f + 3] * re1[f + 3] + im1[f + 3] * im1[f + 3]);
+    }
   }
   __syncthreads();
   // mel filterbank: thread = (mel band m, group g of the tile's frames); per bin one coalesced fb load and
