@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define UV_ABI_VERSION 9
+#define UV_ABI_VERSION 10
 
 typedef enum {
   UV_OK = 0,
@@ -128,6 +128,13 @@ typedef struct {
    * utterance has the plan's geometry.  GEMM / CONVBLOCK: int32 [B] valid rows of each utterance in the op's row
    * space (replaces M_valid); every other op: uv_row_geo [B].                                                    */
   int64_t rows;
+  /* ---- fp32 parity tier (north_star: rel-L2 <= 1e-4 with fp32 operands; the reference's own arithmetic is fp32,
+   * bin/enhance.py:83-192 sets no precision flag).  The precision of a plan is a property of its program: every
+   * planes tensor has dtype 2 (f32), a UV_OP_GEMM whose A is f32 names in p5 the fp32 image of the same multi-tap GEMM
+   * (f32 [n_src][n_shift][C_in][N_total]; bias_w = f32 [C_out]) and writes an optional row-major output
+   * [m_rows][rm_ld] (H = 0), a UV_OP_GRU with p5 >= 0 (f32 W_hh [dir][k < H][gate 3][u < H]) reads row-major gate inputs
+   * [b Lh + t][6H] at p0; both run as fp32 FMA kernels (csrc/hp_ops.cuh).  UV_OP_CONVBLOCK is not used by such programs.
+   * The host compiler builds them with build_program(..., precision="fp32") (Universe.precision = "fp32").        */
   /* UV_OP_GEMM / CONV_IN / CONV_OUT: i3 bit 0 = walk the tensor from its end (tiles / blocks in descending order).
    * The builder alternates it along each chain of kernels so that a consumer starts where its producer finished,
    * i.e. on the part of the tensor the L2 still holds.                                                          */

@@ -2,7 +2,7 @@
 lives in `_native.py`)."""
 import ctypes as C
 
-UV_ABI_VERSION = 9
+UV_ABI_VERSION = 10
 
 OP_PREP, OP_MEL, OP_MEL_FIN, OP_CONV_IN, OP_GEMM, OP_GRU, OP_CONV_OUT, OP_INIT_X, OP_POST, OP_FILM, OP_CONVBLOCK, OP_AUX = range(1, 13)
 OP_NAMES = {

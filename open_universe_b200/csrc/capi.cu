@@ -14,6 +14,7 @@
 #include "convblock_pair.cuh"
 #include "small_ops.cuh"
 #include "aux_ops.cuh"
+#include "hp_ops.cuh"
 
 using namespace uv;
 
@@ -168,6 +169,31 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
   const uv_op& op = p->ops[op_index];
   switch (op.type) {
     case UV_OP_GEMM: {
+      if (op.a.dtype == 2) {
+        // fp32 parity tier (csrc/hp_ops.cuh): f32 planes in, the fp32 image of the same multi-tap GEMM at p5
+        if (op.p5 < 0) return fail(UV_ERR_INVALID, "GEMM on f32 planes needs the fp32 weight image (p5; pack_model(hp=True))");
+        if (op.rm_out >= 0 && op.H > 0) return fail(UV_ERR_INVALID, "fp32 GEMM: row-major outputs only (H == 0)");
+        HpGemmParams h;
+        memset(&h, 0, sizeof(h));
+        h.a_base = reinterpret_cast<const float*>(p->arena + op.a.off);
+        h.a_nch = op.a.nch; h.a_P = op.a.P; h.a_G = op.a.G;
+        h.n_src = op.n_src; h.smin = op.smin; h.n_shift = op.smax - op.smin + 1;
+        h.w = wptr<const float>(p, op.p5);
+        h.bias = wptr<const float>(p, op.bias_w);
+        h.N_total = op.N_total; h.C_out = op.C_out; h.up = op.up;
+        h.m_rows = op.m_rows; h.Lh_A = op.Lh_A; h.M_valid = op.M_valid;
+        h.mv = op.rows >= 0 ? aptr<const int>(p, op.rows) : nullptr;
+        h.film = aptr<const float>(p, op.film);
+        h.add1 = to_desc(p, op.add1); h.add2 = to_desc(p, op.add2);
+        h.scale = op.scale; h.n_out = op.n_out;
+        for (int i = 0; i < 3; ++i) h.out[i] = to_out(p, op.out[i]);
+        h.rm_out = aptr<float>(p, op.rm_out); h.rm_ld = op.rm_ld;
+        h.a_act = op.a_act; h.a_slope = op.a_slope;
+        if (h.N_total % 8 || h.C_out % 8 || h.a_P < h.a_G + ((h.m_rows + kHpBM - 1) / kHpBM) * kHpBM + op.smax)
+          return fail(UV_ERR_INVALID, "fp32 GEMM: geometry unsupported");
+        CUDA_TRY(gemm_hp_launch(h, s));
+        break;
+      }
       GemmParams g;
       memset(&g, 0, sizeof(g));
       g.a_base = p->arena + op.a.off;
@@ -336,6 +362,24 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
                                                                wptr<const float>(p, op.p5), aptr<float>(p, op.p1));
       break;
     case UV_OP_GRU: {
+      if (op.p5 >= 0) {
+        // fp32 parity tier: f32 recurrence on row-major gate inputs (csrc/hp_ops.cuh)
+        if (op.H > 384 || op.H % 32) return fail(UV_ERR_INVALID, "fp32 GRU: hidden size unsupported (needs H % 32 == 0, H <= 384)");
+        HpGruParams h;
+        memset(&h, 0, sizeof(h));
+        h.gi = aptr<const float>(p, op.p0);
+        h.whh = wptr<const float>(p, op.p5);
+        h.bhh = wptr<const float>(p, op.p4);
+        h.B = op.B; h.T = op.T; h.H = op.H; h.Lh = op.Lh_A;
+        h.add1 = to_desc(p, op.add1); h.scale = op.scale; h.n_out = op.n_out;
+        for (int i = 0; i < 3; ++i) h.out[i] = to_out(p, op.out[i]);
+        if (h.add1.base && h.add1.split != 1) return fail(UV_ERR_INVALID, "GRU residual must be a plain tensor");
+        for (int i = 0; i < h.n_out; ++i)
+          if (h.out[i].t.split != 1) return fail(UV_ERR_INVALID, "GRU outputs must be plain tensors");
+        h.rows = op.rows >= 0 ? aptr<const RowGeo>(p, op.rows) : nullptr;
+        CUDA_TRY(gru_hp_launch(h, s));
+        break;
+      }
       if (op.H > kGruMaxH || op.H % (8 * kGruNC)) return fail(UV_ERR_INVALID, "GRU hidden size unsupported (needs H % 64 == 0, H <= 384)");
       GruParams g;
       memset(&g, 0, sizeof(g));

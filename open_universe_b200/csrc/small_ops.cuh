@@ -415,7 +415,7 @@ __global__ void __launch_bounds__(256) conv_out_kernel(TensDesc a, int B, int Lp
       if (lk < 0 || lk >= Lp) rt[k].p = nullptr;
     } else {
       rt[k] = row_addr(a, b, l);
-      rt[k].p += (long long)(k - 1) * 16;
+      rt[k].p += (long long)(k - 1) * (8 << a.esize_log2);
     }
   }
   float acc = bias[0];
@@ -425,7 +425,7 @@ __global__ void __launch_bounds__(256) conv_out_kernel(TensDesc a, int B, int Lp
       const RowAddr rk = rt[k];
       if (rk.p == nullptr) continue;
       float v[8];
-      load8(rk, 1, ch, v);
+      load8(rk, a.esize_log2, ch, v);
       const float4 w0 = *reinterpret_cast<const float4*>(ws + k * C + ch * 8);
       const float4 w1 = *reinterpret_cast<const float4*>(ws + k * C + ch * 8 + 4);
       acc = fmaf(v[0], w0.x, acc); acc = fmaf(v[1], w0.y, acc); acc = fmaf(v[2], w0.z, acc); acc = fmaf(v[3], w0.w, acc);

@@ -71,6 +71,9 @@ class Universe(torch.nn.Module):
         # device out of memory); the graph of a plan is captured at its second use
         self.plan_cache_bytes = int(float(os.environ.get("UV_PLAN_CACHE_GB", "48")) * 2**30)
         self.plan_cache_max = int(os.environ.get("UV_PLAN_CACHE_MAX", "32"))
+        # "bf16" (default): bf16 operands, fp32 accumulation on the tensor cores (north_star gate rel-L2 <= 1e-2);
+        # "fp32": the parity tier (rel-L2 <= 1e-4): f32 activations and weights, fp32 FMA kernels (csrc/hp_ops.cuh)
+        self.precision = os.environ.get("UV_PRECISION", "bf16")
 
     # ------------------------------------------------------------------ reference API surface
     def init_losses(self, score_model, condition_model, losses, training):
@@ -166,16 +169,21 @@ class Universe(torch.nn.Module):
                 "open_universe_b200 runs only on a CUDA sm_100 (B200) device; the model is on "
                 f"'{dev}'. There is no CPU / PyTorch fallback: move it with model.to('cuda')."
             )
+        if self.precision not in program.PRECISIONS:
+            raise ValueError(f"precision must be one of {program.PRECISIONS}, got {self.precision!r}")
+        hp = self.precision == "fp32"
+        if self._packed is not None and hp and not self._packed.hp:
+            self._invalidate()   # the blob on the device lacks the fp32 weight images: pack again with them
         if self._packed is None:
             sd = {k: v.detach().float().cpu() for k, v in self.state_dict().items()}
-            self._packed = weights.pack_model(sd, self.model_config())
+            self._packed = weights.pack_model(sd, self.model_config(), hp=hp)
             self._native_model = _native.NativeModel(self._packed.blob.bytes(), dev.index or 0)
-        key = (B, T, n_steps, aux)
+        key = (B, T, n_steps, aux) + (("fp32",) if hp else ())
         plan = self._plans.get(key)
         if plan is not None:
             self._plans.move_to_end(key)
             return plan
-        pg = program.build_program(self._packed, self.model_config(), B, T, n_steps, aux=aux)
+        pg = program.build_program(self._packed, self.model_config(), B, T, n_steps, aux=aux, precision=self.precision)
         # make room first: the new arena must fit next to the ones that stay
         held = sum(p.arena_bytes for p in self._plans.values())
         while self._plans and (held + pg.arena > self.plan_cache_bytes or len(self._plans) >= self.plan_cache_max):

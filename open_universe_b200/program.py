@@ -76,8 +76,9 @@ class _PartSink:
 
 
 class Program:
-    def __init__(self, pm, B, T, n_steps, sigmas, log10_sigmas, in_scales, arena_base=0, lane=0):
+    def __init__(self, pm, B, T, n_steps, sigmas, log10_sigmas, in_scales, arena_base=0, lane=0, hp=False):
         self.pm = pm
+        self.hp = hp             # fp32 parity tier: every planes tensor is f32, dense ops carry the fp32 weight images
         self.ops = []
         self.names = []
         self.arena = arena_base
@@ -96,6 +97,8 @@ class Program:
 
     def tens(self, name, lev, C, split=1, dtype=DT_BF16):
         """Allocates (or returns) the planes tensor `name` whose row space is `lev`."""
+        if self.hp:
+            dtype = DT_F32
         if name in self.tensors:
             t = self.tensors[name]
             assert (t.nch, t.split, t.Lh, t.P, t.dtype) == (C // 8, split, lev.Lh, lev.P, dtype), name
@@ -165,6 +168,8 @@ class Program:
         op.rm_ld = ly["N_total"]
         if a_slope is not None:   # `a` is a raw tensor: PReLU(a_slope) is applied inside the kernel
             op.a_act, op.a_slope = 1, a_slope
+        if self.hp:               # fp32 tier: f32 [S][Q][C_in][N_total] image of the same GEMM (csrc/hp_ops.cuh)
+            op.p5 = ly["w_hp"]
         return self.emit(op, name)
 
 
@@ -386,23 +391,33 @@ def default_lanes(B, aux=False):
     return 2 if B >= LANE_MIN_B else 1
 
 
-def build_program(pm, cfg, B, T, n_steps, aux=False, lanes=None, recycle=None):
-    """Program of one enhance() call.  lanes = 2 splits the utterances into two independent halves whose op
+PRECISIONS = ("bf16", "fp32")
+
+
+def build_program(pm, cfg, B, T, n_steps, aux=False, lanes=None, recycle=None, precision="bf16"):
+    """Program of one enhance() call.  precision = "fp32": the parity tier of north_star (rel-L2 <= 1e-4): same
+    topology, every activation stored in f32 planes, dense layers and recurrences run by the fp32 kernels of
+    csrc/hp_ops.cuh from the fp32 weight images (pm packed with hp=True), no fused ConvBlocks.  lanes = 2 splits the utterances into two independent halves whose op
     lists are concatenated (lane 0 first); each lane owns its tensors, the FiLM table is shared.  The native
     plan captures lane 1 on a second stream (csrc/capi.cu capture_program).  One cross-lane edge staggers the
     lanes: lane 1 starts when lane 0 has finished the op named by UV_LANE_STAGGER (default: the conditioner
     encoder's second rate-change conv, about a third of a score step of lane 0's work), so that their
     recurrences do not coincide.  The result carries lane 0's attributes plus `lanes` (the per-lane programs)."""
+    if precision not in PRECISIONS:
+        raise ValueError(f"precision must be one of {PRECISIONS}")
+    hp = precision == "fp32"
+    if hp and not pm.hp:
+        raise ValueError("precision='fp32' needs a model packed with pack_model(..., hp=True)")
     if lanes is None:
         lanes = default_lanes(B, aux)
     if recycle is None:
         recycle = RECYCLE
     if lanes == 1 or B < 2:
-        return _finish_init(_build_lane(pm, cfg, B, T, n_steps, aux=aux, recycle=recycle))
+        return _finish_init(_build_lane(pm, cfg, B, T, n_steps, aux=aux, recycle=recycle, hp=hp))
     assert not aux, "aux-signal programs are single-lane (run_ops ranges address one op list)"
     B0 = (B + 1) // 2
-    pg0 = _build_lane(pm, cfg, B0, T, n_steps, b_off=0, B_total=B, recycle=recycle)
-    pg1 = _build_lane(pm, cfg, B - B0, T, n_steps, b_off=B0, B_total=B, arena_base=pg0.arena, lane=1, shared=pg0, recycle=recycle)
+    pg0 = _build_lane(pm, cfg, B0, T, n_steps, b_off=0, B_total=B, recycle=recycle, hp=hp)
+    pg1 = _build_lane(pm, cfg, B - B0, T, n_steps, b_off=B0, B_total=B, arena_base=pg0.arena, lane=1, shared=pg0, recycle=recycle, hp=hp)
     stagger = os.environ.get("UV_LANE_STAGGER", "c.enc3.rc")
     if stagger in pg0.names:
         pg0.ops[pg0.names.index(stagger)].sync |= 1
@@ -427,7 +442,7 @@ def _finish_init(pg):
     return pg
 
 
-def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_base=0, lane=0, shared=None, recycle=True):
+def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_base=0, lane=0, shared=None, recycle=True, hp=False):
     """aux=True also evaluates the tail of the conditioner decoder's last block (y_hat, the input of aux_to_wav:
     reference condition.py:264-270,362; universe.py:313-331), which the default path never uses.
     b_off / B_total: this lane's first utterance in / the size of the caller's batch (io tensors cover all lanes)."""
@@ -440,7 +455,7 @@ def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_
     pad = tot_ds - T % tot_ds
     Lp = T + pad
     sigma, log10s, w_in = sampler_tables(cfg, n_steps)
-    pg = Program(pm, B, T, n_steps, sigma, log10s, w_in, arena_base=arena_base, lane=lane)
+    pg = Program(pm, B, T, n_steps, sigma, log10s, w_in, arena_base=arena_base, lane=lane, hp=hp)
     pg.lanes = [pg]
     pg.b_off, pg.B_total = b_off, B_total
     pg.Lp, pg.pad_left, pg.tot_ds = Lp, pad // 2, tot_ds
@@ -575,14 +590,18 @@ def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_
         nb, bp, srow = gru_geometry(H, B)
         gi = pg.tensors.get("gi")
         if gi is None:
-            gi = pg.alloc(Fr * 16 * bp * srow * 4)
+            # fp32 tier: plain row-major gate inputs [b Lh + t][6H] (csrc/hp_ops.cuh gru_hp_kernel)
+            gi = pg.alloc(lb.rows * 6 * H * 4 if hp else Fr * 16 * bp * srow * 4)
             pg.tensors["gi"] = gi
         op = pg.gemm(name + ".ih", name + ".ih", x_raw, lb, lb.L, [], step, rm_out=gi)
-        op.H, op.i1 = H, bp           # the epilogue scatters into the GRU's [t][dir][rank][b][3U+4] layout
+        if not hp:
+            op.H, op.i1 = H, bp           # the epilogue scatters into the GRU's [t][dir][rank][b][3U+4] layout
         op = new_op(_abi.OP_GRU, step)
         op.B, op.T, op.H, op.Lh_A = B, Fr, H, lb.Lh
         op.i0, op.i1 = nb, bp
         op.p0, op.p3, op.p4 = gi, L[name + ".hh"]["whh_w"], L[name + ".hh"]["bhh_w"]
+        if hp:
+            op.p5 = L[name + ".hh"]["whh_hp"]   # f32 [dir][k][gate][u]: selects the fp32 recurrence kernel
         if add1 is not None:
             op.add1 = add1
         op.scale = scale

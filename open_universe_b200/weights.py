@@ -237,10 +237,14 @@ def dft_basis(window, n_fft):
 
 
 class PackedModel:
-    def __init__(self):
+    def __init__(self, hp=False):
         self.blob = Blob()
         self.layers = {}
         self.meta = {}
+        # hp: also keep every dense layer's fp32 image for the fp32 parity tier (precision="fp32": rel-L2 <= 1e-4,
+        # csrc/hp_ops.cuh): `w_hp` = f32 [S][Q][C_in][N_total] of the same multi-tap GEMM, `whh_hp` = f32
+        # [dir][k < H][gate 3][u < H] of the GRU recurrence.  Doubles the blob, so only on request.
+        self.hp = hp
 
     def add_gemm(self, name, w4, smin, c_out, up=1, bias=None, slope=None, resid=False):
         """resid: the op that uses this layer adds a residual / condition tensor; for C_out <= 128 it goes
@@ -255,6 +259,8 @@ class PackedModel:
             n_src=s, smin=smin, smax=smin + q - 1, KC=kc, N_TILE=n_tile, N_total=n,
             C_out=c_out, C_in=ci, up=up, slope=slope,
         )
+        if self.hp:
+            self.layers[name]["w_hp"] = self.blob.add_f32(w4.permute(1, 2, 3, 0).contiguous())
 
     def add_conv_block(self, sd, prefix, name, rate=None, direction="none", s2d=False):
         """ConvBlock parameters (blocks.py:240-329).  s2d: also pack the three convs for phase-split-by-2 tensors
@@ -295,6 +301,9 @@ class PackedModel:
             bhh_w=self.blob.add_f32(torch.cat([sd[f"{prefix}.bias_hh_l{layer}{s}"].float() for s in sufs])),
             H=whh[0].shape[1],
         )
+        if self.hp:
+            h = whh[0].shape[1]
+            self.layers[f"{name}.hh"]["whh_hp"] = self.blob.add_f32(torch.stack([w.view(3, h, h).permute(2, 0, 1) for w in whh]).contiguous())
 
     def add_conv_in(self, sd, prefix, name):
         w = eff_weight(sd, prefix)  # [C, 1, 3]
@@ -304,10 +313,11 @@ class PackedModel:
                                  bias_w=self.blob.add_f32(sd[prefix + ".bias"]), C=w.shape[0])
 
 
-def pack_model(sd, cfg):
-    """sd: reference-layout state dict (tensors on CPU); cfg: resolved `model` config node."""
+def pack_model(sd, cfg, hp=False):
+    """sd: reference-layout state dict (tensors on CPU); cfg: resolved `model` config node.
+    hp: also pack the fp32 weight images of the fp32 parity tier (PackedModel.hp)."""
     sd = {k: v.detach().cpu() for k, v in sd.items()}
-    pm = PackedModel()
+    pm = PackedModel(hp=hp)
     scfg, ccfg = cfg["score_model"], cfg["condition_model"]
     edm = cfg.get("edm") is not None
     sp, cp = ("_edm_model" if edm else "score_model"), "condition_model"

@@ -118,14 +118,21 @@ class Emulator:
     # ---------------------------------------------------------------- ops
     def op_gemm(self, op):
         a = self.view(op.a).float()  # [n_src, nch, P, 8]
+        hp = op.p5 >= 0   # fp32 tier (csrc/hp_ops.cuh gemm_hp_kernel): f32 planes, f32 weight image [S][Q][C_in][N], no rounding
         if op.a_act:
             # raw A tensor: the kernel's transform warps apply PReLU in fp32 and round to bf16 once (csrc/gemm_tc.cuh)
-            a = torch.where(a >= 0, a, np.float32(op.a_slope) * a).to(torch.bfloat16).float()
+            a = torch.where(a >= 0, a, np.float32(op.a_slope) * a)
+            if not hp:
+                a = a.to(torch.bfloat16).float()
         n_shift = op.smax - op.smin + 1
         C_in = op.a.nch * 8
         has_bias = op.bias_w >= 0
-        key = (op.w_w, op.N_total, op.n_src, n_shift, C_in, has_bias)
-        if key not in self._wcache:
+        key = (op.w_w, op.N_total, op.n_src, n_shift, C_in, has_bias, hp)
+        if key not in self._wcache and hp:
+            w = self.w_f32(op.p5, op.n_src * n_shift * C_in * op.N_total).view(op.n_src, n_shift, C_in, op.N_total)
+            bias = self.w_f32(op.bias_w, op.C_out).repeat(op.N_total // op.C_out) if has_bias else None
+            self._wcache[key] = (w.permute(3, 0, 1, 2).contiguous(), bias)
+        elif key not in self._wcache:
             nb = op.N_total * op.n_src * n_shift * C_in * 2 + (op.N_total * 32 if has_bias else 0)
             bits = self.blob[op.w_w : op.w_w + nb].view(np.int16)
             res = unpack_w4(bits, op.N_total, op.n_src, n_shift, C_in, op.KC, op.N_TILE // 2, has_bias)   # packed per half N tile
@@ -142,7 +149,10 @@ class Emulator:
         b_idx, m = g // op.Lh_A, g % op.Lh_A
         valid = m < op.M_valid
         b_idx, m, acc = b_idx[valid], m[valid], acc[valid]
-        if op.rm_out >= 0:
+        g_rows = g[valid]
+        if op.rm_out >= 0 and op.H == 0:
+            rm_plain = self.a_f32(op.rm_out, op.m_rows * op.rm_ld).view(op.m_rows, op.rm_ld)   # row-major [b Lh + t][N]
+        elif op.rm_out >= 0:
             # GRU gate-input layout [t][dir][rank 8][b < Bp][3U + 4] (csrc/gru.cuh)
             H, Bp = op.H, op.i1
             U, S = H // 8, 3 * (H // 8) + 4
@@ -162,7 +172,9 @@ class Emulator:
             v *= np.float32(op.scale)
             if film is not None:
                 v = film[: op.C_out] * v + film[op.C_out :]
-            if op.rm_out >= 0:
+            if op.rm_out >= 0 and op.H == 0:
+                rm_plain[g_rows, ph * op.C_out : (ph + 1) * op.C_out] = v
+            elif op.rm_out >= 0:
                 assert op.up == 1 and op.C_out == 6 * H
                 vv = v.view(-1, 2, 3, 8, U).permute(0, 1, 3, 2, 4).reshape(-1, 2, 8, 3 * U)  # [row, dir, rank, gate*U + u]
                 rm[m, :, :, b_idx, : 3 * U] = vv
@@ -309,11 +321,17 @@ class Emulator:
         B, T, H, Lh = op.B, op.T, op.H, op.Lh_A
         Bp, U = op.i1, H // 8
         S = 3 * U + 4
-        gi_blk = self.a_f32(op.p0, T * 16 * Bp * S).view(T, 2, 8, Bp, S)[:, :, :, :B, : 3 * U]  # [t, dir, rank, b, gate*U+u]
-        # -> [b, t, dir*3H + gate*H + rank*U + u]
-        gi_bt = gi_blk.reshape(T, 2, 8, B, 3, U).permute(3, 0, 1, 4, 2, 5).reshape(B, T, 6 * H)
-        bits = self.blob[op.p3 : op.p3 + 2 * 3 * H * H * 2].view(np.int16)
-        whh = unpack_gru_whh(bits.copy(), H)
+        if op.p5 >= 0:
+            # fp32 tier (csrc/hp_ops.cuh gru_hp_kernel): gate inputs row-major [b Lh + t][6H], f32 weights [dir][k][gate][u]
+            round_h = False
+            gi_bt = self.a_f32(op.p0, B * Lh * 6 * H).view(B, Lh, 6 * H)[:, :T]
+            whh = self.w_f32(op.p5, 2 * H * 3 * H).view(2, H, 3, H).permute(0, 2, 3, 1).reshape(2, 3 * H, H)
+        else:
+            gi_blk = self.a_f32(op.p0, T * 16 * Bp * S).view(T, 2, 8, Bp, S)[:, :, :, :B, : 3 * U]  # [t, dir, rank, b, gate*U+u]
+            # -> [b, t, dir*3H + gate*H + rank*U + u]
+            gi_bt = gi_blk.reshape(T, 2, 8, B, 3, U).permute(3, 0, 1, 4, 2, 5).reshape(B, T, 6 * H)
+            bits = self.blob[op.p3 : op.p3 + 2 * 3 * H * H * 2].view(np.int16)
+            whh = unpack_gru_whh(bits.copy(), H)
         bhh = self.w_f32(op.p4, 6 * H).view(2, 3 * H)
         out = torch.zeros(B, T, 2 * H)
         for d in range(2):

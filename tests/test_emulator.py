@@ -122,3 +122,27 @@ def test_aux_program_emulation_matches_reference(case):
     emu.run_op(pg.idx_post, io)
     assert uo.rel_l2(io["out"], fix["out"]) < 1e-2
     assert uo.si_sdr(io["out"], fix["out"]).min() > 40.0
+
+
+@pytest.mark.parametrize("case", GOLDEN_CASES)
+def test_fp32_program_emulation_matches_reference(case):
+    """precision="fp32" (the rel-L2 <= 1e-4 tier of north_star): the same compiler emits f32 planes and names the fp32
+    weight images; executed op by op on the CPU it reproduces the reference's golden outputs to fp32 round-off."""
+    fix = load_fixture(case)
+    model, cfg = build_model(fix["model"], fix["seed_weights"])
+    mcfg = model.model_config()
+    kw = fix["kwargs"]
+    n_steps = kw.get("n_steps", int(cfg.model.diffusion.n_steps))
+    pm = weights.pack_model(model.state_dict(), mcfg, hp=True)
+    with pytest.raises(ValueError):
+        program.build_program(weights.PackedModel(), mcfg, fix["B"], fix["T"], n_steps, precision="fp32")
+    pg = program.build_program(pm, mcfg, fix["B"], fix["T"], n_steps, precision="fp32")
+    from open_universe_b200 import _abi
+    assert all(op.type != _abi.OP_CONVBLOCK for op in pg.ops)
+    assert all(t.dtype == _abi.DT_F32 for t in pg.tensors.values() if not isinstance(t, int))
+    mix, noise = golden_inputs(fix, model.tot_ds)
+    coefs = program.step_coefs(mcfg, n_steps, kw.get("epsilon", float(cfg.model.diffusion.epsilon)))
+    io = Emulator(pm, pg).run(mix, noise, coefs, keep_rms=kw.get("keep_rms", False), dbg=True)
+    assert uo.rel_l2(io["out"], fix["out"]) < 1e-5
+    for i in range(n_steps):
+        assert uo.rel_l2(io["dbg"][i], fix["steps"][i]) < 1e-5, i
