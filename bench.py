@@ -273,6 +273,8 @@ def run_native(args, wl, rank, world, local_rank):
         nccl_log = nccl_log_setup(rank)
         dist.init_process_group("nccl", device_id=dev)
     cfg, model = setup_native(wl, dev)
+    model.precision = args.precision
+    hp = args.precision == "fp32"
     fs = int(cfg.model.fs)
     B, T, n_steps = wl["B"], wl["T"], wl["n_steps"]
     mix_host = testing.synthetic_noisy_speech(B, T, seed=1234 + rank).pin_memory()
@@ -401,12 +403,14 @@ def run_native(args, wl, rank, world, local_rank):
     build = source_hash()
     if os.path.exists(tpath):
         tj = json.load(open(tpath))
-        if tj.get("kernel") == "gemm_tc_kernel" and tj.get("build") == build:
+        if hp:
+            traffic_note = "no ncu pass of the fp32 tier's kernel"
+        elif tj.get("kernel") == "gemm_tc_kernel" and tj.get("build") == build:
             traffic, traffic_src = tj["traffic_bytes_per_launch"], tj.get("source")
         else:
             traffic_note = f"profiles/roofline_traffic.json is from build {tj.get('build')}, this is {build}: not quoted"
     whole = fl["total"] * B * world / (ms * 1e-3) / 1e12
-    roofline = dict(bound="tensor", kernel="gemm_tc_kernel", achieved=achieved, peak=pk["tensor"], unit="TFLOP/s",
+    roofline = dict(bound="tensor", kernel="gemm_hp_tc_kernel" if hp else "gemm_tc_kernel", achieved=achieved, peak=pk["tensor"], unit="TFLOP/s",
                     frac=achieved / pk["tensor"], traffic=traffic, traffic_unit="bytes/launch (dram read + write, ncu)",
                     traffic_source=traffic_src, traffic_note=traffic_note, build=build,
                     peak_source=pk["src"] + " sustained bf16 (cuBLAS, seconds-long loop under the power cap)",
@@ -423,6 +427,9 @@ def run_native(args, wl, rank, world, local_rank):
                                         in_gemm_kernel=gemm_flops / B, in_fused_convblocks=fused_flops / B),
                     whole_step_tflops=whole, whole_step_frac=whole / pk["tensor"],
                     whole_step_note="every dense FLOP of the pass in the reference's formulation / the whole timed step")
+    if hp:
+        roofline["note"] = ("fp32 parity tier: every product is 3 bf16 MMAs (x_hi w_hi + x_hi w_lo + x_lo w_hi), so the ceiling of "
+                            "`achieved` (useful FLOPs) is peak / 3; activations are f32 planes (twice the bytes of the bf16 tier)")
     cb_ms = by_kind_busy.get("CONVBLOCK", 0.0) / trace_total * ms
     if fused and cb_ms > 0:
         gbs = fused_bytes / (cb_ms * 1e-3) / 1e9
@@ -436,7 +443,8 @@ def run_native(args, wl, rank, world, local_rank):
         roofline["hbm_view"] = dict(achieved=gbs, peak=pk["hbm"], unit="GB/s", frac=gbs / pk["hbm"],
                                     note="same launches seen as HBM traffic: the C <= 64 levels are HBM bound")
     line = dict(metric="audio-sec enhanced/sec", value=audio_s / (ms * 1e-3), unit="audio-s/s", n_gpus=world, steps=args.steps,
-                warmup=args.warmup, ms_per_step=ms, higher_is_better=True, scaling="weak", vs_baseline=None, dtype="bf16",
+                warmup=args.warmup, ms_per_step=ms, higher_is_better=True, scaling="weak", vs_baseline=None,
+                dtype="fp32 (split-bf16 x3 on the tensor cores, fp32 accumulate; rel-L2 <= 1e-4 tier)" if hp else "bf16",
                 data="synthetic",
                 config=dict(workload=wl["desc"], model=wl["model"], batch_per_gpu=B, clip_samples=T, n_steps=n_steps,
                             weights="random-init (seeded)", sharding=f"utterances x{world}, no collective",
@@ -591,6 +599,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"],
+                    help="fp32: the rel-L2 <= 1e-4 parity tier (f32 activations, split-bf16 tensor-core GEMMs); default bf16 = the headline")
     ap.add_argument("--clips", type=int, default=None, help="cfg5_sweep: size of the clip set (default 4096)")
     ap.add_argument("--ref-clips", type=int, default=4, help="--impl reference: clips per CPU step")
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -133,7 +133,9 @@ typedef struct {
    * planes tensor has dtype 2 (f32), a UV_OP_GEMM whose A is f32 names in p5 the fp32 image of the same multi-tap GEMM
    * (f32 [n_src][n_shift][C_in][N_total]; bias_w = f32 [C_out]) and writes an optional row-major output
    * [m_rows][rm_ld] (H = 0), a UV_OP_GRU with p5 >= 0 (f32 W_hh [dir][k < H][gate 3][u < H]) reads row-major gate inputs
-   * [b Lh + t][6H] at p0; both run as fp32 FMA kernels (csrc/hp_ops.cuh).  UV_OP_CONVBLOCK is not used by such programs.
+   * [b Lh + t][6H] at p0 (csrc/hp_ops.cuh).  The GEMM runs on the tensor cores as a 3-term split-bf16 product (p4 = images
+   * [N tile][src][K group][shift][hi | lo][i0 / 8][i2][8] bf16, i0 = K group, i2 = N tile; ~1e-5 per layer) or, with
+   * UV_HP_SIMT=1 / when p4 < 0, as an fp32 FMA kernel from p5; the recurrence is an fp32 FMA kernel.  UV_OP_CONVBLOCK is not used by such programs.
    * The host compiler builds them with build_program(..., precision="fp32") (Universe.precision = "fp32").        */
   /* UV_OP_GEMM / CONV_IN / CONV_OUT: i3 bit 0 = walk the tensor from its end (tiles / blocks in descending order).
    * The builder alternates it along each chain of kernels so that a consumer starts where its producer finished,

@@ -107,6 +107,7 @@ extern "C" int uv_model_create(uv_model** out, const void* weights, size_t nbyte
   // function attributes are per device: every model (= device) sets them, no process-wide "done" flags
   CUDA_TRY(gemm_set_attributes());
   CUDA_TRY(convblock_pair_set_attributes());
+  CUDA_TRY(gemm_hp_tc_set_attributes());
   CUDA_TRY(cudaFuncSetAttribute(aux_to_wav_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   CUDA_TRY(cudaFuncSetAttribute(gru_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   CUDA_TRY(cudaFuncSetAttribute(mel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMelMaxSmem));
@@ -191,7 +192,12 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
         h.a_act = op.a_act; h.a_slope = op.a_slope;
         if (h.N_total % 8 || h.C_out % 8 || h.a_P < h.a_G + ((h.m_rows + kHpBM - 1) / kHpBM) * kHpBM + op.smax)
           return fail(UV_ERR_INVALID, "fp32 GEMM: geometry unsupported");
-        CUDA_TRY(gemm_hp_launch(h, s));
+        // default: split-bf16 ("bf16x3") on the tensor cores; UV_HP_SIMT=1: the fp32 FMA kernel (same results to ~1e-5)
+        static const bool hp_simt = getenv("UV_HP_SIMT") && atoi(getenv("UV_HP_SIMT")) != 0;
+        h.w_tc = wptr<const char>(p, op.p4); h.KC = op.i0; h.N_TILE = op.i2;
+        h.err_flag = p->err_flag;
+        if (!hp_simt && gemm_hp_tc_ok(h)) CUDA_TRY(gemm_hp_tc_launch(h, s));
+        else CUDA_TRY(gemm_hp_launch(h, s));
         break;
       }
       GemmParams g;

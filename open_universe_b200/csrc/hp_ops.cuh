@@ -14,7 +14,7 @@
 // Everything else of the program (front end, edge convs, FiLM table, sampler, post-processing) already computes in
 // fp32 and reads / writes planes of either element type.
 #pragma once
-#include "uv_common.cuh"
+#include "gemm_tc.cuh"   // PTX glue (mbarriers, bulk copies, tcgen05 wrappers, descriptors)
 
 namespace uv {
 
@@ -40,7 +40,70 @@ struct HpGemmParams {
   int rm_ld;
   int a_act;             // PReLU(a_slope) on A as it is staged
   float a_slope;
+  // ---- tensor-core variant (gemm_hp_tc_kernel): split-bf16 weight images, per N tile and (source, K group, shift):
+  //      [hi | lo][KC/8][N_TILE][8] bf16 (K-major, no swizzle), W = hi + lo to 16 mantissa bits
+  const char* w_tc;
+  int KC, N_TILE;
+  int* err_flag;         // watchdog of the pipeline barriers
 };
+
+// Epilogue of one (row, 8-column chunk) -- order of gemm_tc.cuh / oracle/emulator.py: bias, residuals, scale, FiLM,
+// row-major copy, PReLU outputs.  The 8 columns are one channel chunk of one output phase.
+struct HpEpiCols {
+  int nt, ph, chunk;
+  float bias[8], gam[8], bet[8];
+};
+__device__ __forceinline__ void hp_epi_cols(const HpGemmParams& P, int nt, HpEpiCols& e) {
+  e.nt = nt;
+  e.ph = nt / P.C_out;
+  const int c0 = nt - e.ph * P.C_out;
+  e.chunk = c0 >> 3;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    e.bias[j] = P.bias ? P.bias[c0 + j] : 0.f;
+    e.gam[j] = P.film ? P.film[c0 + j] : 1.f;
+    e.bet[j] = P.film ? P.film[P.C_out + c0 + j] : 0.f;
+  }
+}
+__device__ __forceinline__ void hp_epi_row(const HpGemmParams& P, const HpEpiCols& e, int g, const float* acc) {
+  if (g >= P.m_rows) return;
+  const int b = g / P.Lh_A, m = g - b * P.Lh_A;
+  if (m >= (P.mv ? P.mv[b] : P.M_valid)) return;
+  const int l = P.up * m + e.ph;
+  float v[8], t8[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) v[j] = acc[j] + e.bias[j];
+  if (P.add1.base) {
+    load8(row_addr(P.add1, b, l), P.add1.esize_log2, e.chunk, t8);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] += t8[j];
+  }
+  if (P.add2.base) {
+    load8(row_addr(P.add2, b, l), P.add2.esize_log2, e.chunk, t8);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] += t8[j];
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) v[j] *= P.scale;
+  if (P.film) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = fmaf(e.gam[j], v[j], e.bet[j]);
+  }
+  if (P.rm_out) {
+    float* r = P.rm_out + (size_t)g * P.rm_ld + e.nt;
+    *reinterpret_cast<float4*>(r) = make_float4(v[0], v[1], v[2], v[3]);
+    *reinterpret_cast<float4*>(r + 4) = make_float4(v[4], v[5], v[6], v[7]);
+  }
+#pragma unroll
+  for (int o = 0; o < 3; ++o) {
+    if (o < P.n_out) {
+      float u[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) u[j] = apply_act(v[j], P.out[o].act, P.out[o].a1, P.out[o].a2);
+      store8(row_addr(P.out[o].t, b, l), P.out[o].t.esize_log2, e.chunk, u);
+    }
+  }
+}
 
 __global__ void __launch_bounds__(256, 2) gemm_hp_kernel(const HpGemmParams P) {
   __shared__ __align__(16) float As[2][8][kHpAPitch];
@@ -110,63 +173,205 @@ __global__ void __launch_bounds__(256, 2) gemm_hp_kernel(const HpGemmParams P) {
     __syncthreads();
   }
 
-  // ---- epilogue (order of gemm_tc.cuh / oracle/emulator.py: bias, residuals, scale, FiLM, outputs)
+  // ---- epilogue
   const int nt = n0 + 8 * tx;
   if (nt >= P.N_total) return;
-  const int ph = nt / P.C_out, c0 = nt - ph * P.C_out, chunk = c0 >> 3;
-  float bias[8], gam[8], bet[8];
+  HpEpiCols ec;
+  hp_epi_cols(P, nt, ec);
 #pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    bias[j] = P.bias ? P.bias[c0 + j] : 0.f;
-    gam[j] = P.film ? P.film[c0 + j] : 1.f;
-    bet[j] = P.film ? P.film[P.C_out + c0 + j] : 0.f;
-  }
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int g = g0 + 4 * ty + i;
-    if (g >= P.m_rows) continue;
-    const int b = g / P.Lh_A, m = g - b * P.Lh_A;
-    if (m >= (P.mv ? P.mv[b] : P.M_valid)) continue;
-    const int l = P.up * m + ph;
-    float v[8], t8[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) v[j] = acc[i][j] + bias[j];
-    if (P.add1.base) {
-      load8(row_addr(P.add1, b, l), P.add1.esize_log2, chunk, t8);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) v[j] += t8[j];
-    }
-    if (P.add2.base) {
-      load8(row_addr(P.add2, b, l), P.add2.esize_log2, chunk, t8);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) v[j] += t8[j];
-    }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) v[j] *= P.scale;
-    if (P.film) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) v[j] = fmaf(gam[j], v[j], bet[j]);
-    }
-    if (P.rm_out) {
-      float* r = P.rm_out + (size_t)g * P.rm_ld + nt;
-      *reinterpret_cast<float4*>(r) = make_float4(v[0], v[1], v[2], v[3]);
-      *reinterpret_cast<float4*>(r + 4) = make_float4(v[4], v[5], v[6], v[7]);
-    }
-#pragma unroll
-    for (int o = 0; o < 3; ++o) {
-      if (o < P.n_out) {
-        float u[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) u[j] = apply_act(v[j], P.out[o].act, P.out[o].a1, P.out[o].a2);
-        store8(row_addr(P.out[o].t, b, l), P.out[o].t.esize_log2, chunk, u);
-      }
-    }
-  }
+  for (int i = 0; i < 4; ++i) hp_epi_row(P, ec, g0 + 4 * ty + i, acc[i]);
 }
 
 inline cudaError_t gemm_hp_launch(const HpGemmParams& P, cudaStream_t s) {
   dim3 grid((P.m_rows + kHpBM - 1) / kHpBM, (P.N_total + kHpBN - 1) / kHpBN);
   gemm_hp_kernel<<<grid, 256, 0, s>>>(P);
+  return cudaGetLastError();
+}
+
+
+// ---------------------------------------------------------------- dense layers on the tensor cores, fp32-accurate
+// 3-term split-bf16 ("bf16x3"): x = x_hi + x_lo, w = w_hi + w_lo (each half a bf16: 16 mantissa bits together),
+//   x w ~= x_hi w_hi + x_hi w_lo + x_lo w_hi      (the dropped x_lo w_lo term is 2^-16 relative)
+// Every product of two bf16 values is exact in fp32 and the tensor core accumulates in fp32 (TMEM), so a layer comes
+// out at ~1e-5 relative error: a tenth of the tier's gate and 30x below what tf32 operands (10 mantissa bits) give.
+// One CTA = one 128-row x N_TILE tile:
+//   warps 0-3  producers: read the f32 A slab of one (source, K group) -- 128 + n_shift - 1 rows, so that a conv tap is
+//              a 16-byte shift of the descriptor's start address --, apply PReLU, split and store the hi / lo bf16
+//              images in the no-swizzle K-major core-matrix layout (two slab stages); afterwards the epilogue:
+//              tcgen05.ld of the thread's row, same fused epilogue as gemm_hp_kernel;
+//   warp 4     one thread: bulk copies of the weight items (hi | lo) into a 4-stage ring and all tcgen05.mma
+//              (cta_group::1, M = 128, N = N_TILE, K = 16), 3 MMAs per K step, commits release the stages.
+constexpr int kHtBStages = 4;
+constexpr int kHtThreads = 160;
+
+__host__ __device__ inline int ht_slab_rows(int n_shift) { return (kHpBM + n_shift - 1 + 7) & ~7; }
+__host__ __device__ inline size_t ht_smem_bytes(int KC, int N_TILE, int n_shift) {
+  return 2 * (size_t)(2 * (KC / 8) * ht_slab_rows(n_shift) * 16) + kHtBStages * (size_t)(2 * KC * N_TILE * 2) + 256 + 128;
+}
+
+__device__ __forceinline__ void split_bf16x8(const float* x, uint4& hi, uint4& lo) {
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&hi);
+  __nv_bfloat162* l = reinterpret_cast<__nv_bfloat162*>(&lo);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const __nv_bfloat162 hh = __floats2bfloat162_rn(x[2 * i], x[2 * i + 1]);
+    const float2 hf = __bfloat1622float2(hh);
+    h[i] = hh;
+    l[i] = __floats2bfloat162_rn(x[2 * i] - hf.x, x[2 * i + 1] - hf.y);
+  }
+}
+
+__global__ void __launch_bounds__(kHtThreads) gemm_hp_tc_kernel(const __grid_constant__ HpGemmParams P) {
+  extern __shared__ unsigned char ht_smem_raw[];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int Q = P.n_shift, KC = P.KC, NT = P.N_TILE, KJ = KC >> 3;
+  const int G = (P.a_nch * 8) / KC;
+  const int n_slabs = P.n_src * G;
+  const int n_items = n_slabs * Q;
+  const int slab_rows = ht_slab_rows(Q);
+  const uint32_t a_half = (uint32_t)(KJ * slab_rows * 16), a_stage = 2 * a_half;
+  const uint32_t b_half = (uint32_t)(KC * NT * 2), b_stage = 2 * b_half;
+  unsigned char* sm = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(ht_smem_raw) + 127) & ~(uintptr_t)127);
+  unsigned char* a_s = sm;
+  unsigned char* b_s = sm + 2 * a_stage;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(b_s + kHtBStages * b_stage);
+  uint64_t* a_full = bars;            // [2] 4 arrivals (one per producer warp)
+  uint64_t* a_free = bars + 2;        // [2] tcgen05.commit
+  uint64_t* b_full = bars + 4;        // [kHtBStages] bulk-copy transaction bytes
+  uint64_t* b_free = bars + 8;        // [kHtBStages] tcgen05.commit
+  uint64_t* acc_full = bars + 12;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 13);
+  uint32_t tmem_cols = 32;
+  while ((int)tmem_cols < NT) tmem_cols <<= 1;
+
+  if (tid == 0) {
+    for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(&a_full[i]), 4); mbar_init(smem_u32(&a_free[i]), 1); }
+    for (int i = 0; i < kHtBStages; ++i) { mbar_init(smem_u32(&b_full[i]), 1); mbar_init(smem_u32(&b_free[i]), 1); }
+    mbar_init(smem_u32(acc_full), 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 4) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr_smem)), "r"(tmem_cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+  const int g0 = blockIdx.x * kHpBM;
+  const int n0 = blockIdx.y * NT;
+
+  if (warp < 4) {
+    // ============================== producers: f32 slab -> PReLU -> hi / lo bf16 images
+    for (int i = 0; i < n_slabs; ++i) {
+      const int st = i & 1;
+      mbar_wait(smem_u32(&a_free[st]), (uint32_t)(((i >> 1) & 1) ^ 1), P.err_flag, 41);
+      const int s = i / G, g = i - s * G;
+      unsigned char* hi = a_s + (size_t)st * a_stage;
+      unsigned char* lo = hi + a_half;
+      const float* plane0 = P.a_base + ((size_t)(s * P.a_nch + g * KJ) * P.a_P + P.a_G + P.smin + g0) * 8;
+      for (int r = tid; r < kHpBM + Q - 1; r += 128) {   // (the slab's pitch is rounded up; only the rows the taps reach are filled)
+        for (int j = 0; j < KJ; ++j) {
+          const float* src = plane0 + ((size_t)j * P.a_P + r) * 8;
+          const float4 x0 = *reinterpret_cast<const float4*>(src);
+          const float4 x1 = *reinterpret_cast<const float4*>(src + 4);
+          float x[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+          if (P.a_act) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) x[e] = prelu1(x[e], P.a_slope);
+          }
+          uint4 h4, l4;
+          split_bf16x8(x, h4, l4);
+          *reinterpret_cast<uint4*>(hi + ((size_t)j * slab_rows + r) * 16) = h4;
+          *reinterpret_cast<uint4*>(lo + ((size_t)j * slab_rows + r) * 16) = l4;
+        }
+      }
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic stores -> tensor-core reads
+      __syncwarp();
+      if (lane == 0) mbar_arrive(smem_u32(&a_full[st]));
+    }
+    // ============================== epilogue: thread = row (TMEM lane), 16 columns per tcgen05.ld
+    mbar_wait(smem_u32(acc_full), 0, P.err_flag, 43);
+    tc_fence_after();
+    const int g = g0 + warp * 32 + lane;
+    for (int c = 0; c < NT; c += 16) {
+      uint32_t r[16];
+      tc_ld16_issue(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c, r);
+      tc_ld_wait();
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        HpEpiCols ec;
+        hp_epi_cols(P, n0 + c + 8 * h, ec);
+        float v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[8 * h + e]);
+        hp_epi_row(P, ec, g, v);
+      }
+    }
+    tc_fence_before();
+  } else if (lane == 0) {
+    // ============================== weight copies + MMA issue (one thread)
+    const unsigned char* wsrc = reinterpret_cast<const unsigned char*>(P.w_tc) + (size_t)blockIdx.y * n_items * b_stage;
+    for (int m = 0; m < kHtBStages && m < n_items; ++m) {
+      mbar_expect_tx(smem_u32(&b_full[m]), b_stage);
+      bulk_g2s(smem_u32(b_s + (size_t)m * b_stage), wsrc + (size_t)m * b_stage, b_stage, smem_u32(&b_full[m]));
+    }
+    const uint32_t idesc = make_idesc(kHpBM, NT);
+    const uint32_t lbo_a = (uint32_t)slab_rows * 16u, lbo_b = (uint32_t)NT * 16u;
+    int n = 0;
+    for (int i = 0; i < n_slabs; ++i) {
+      const int st = i & 1;
+      mbar_wait(smem_u32(&a_full[st]), (uint32_t)((i >> 1) & 1), P.err_flag, 44);
+      tc_fence_after();
+      const uint32_t a_hi = smem_u32(a_s + (size_t)st * a_stage), a_lo = a_hi + a_half;
+      for (int q = 0; q < Q; ++q, ++n) {
+        const int bs = n % kHtBStages;
+        mbar_wait(smem_u32(&b_full[bs]), (uint32_t)((n / kHtBStages) & 1), P.err_flag, 45);
+        tc_fence_after();
+        const uint32_t b_hi = smem_u32(b_s + (size_t)bs * b_stage), b_lo = b_hi + b_half;
+        for (int kk = 0; kk < (KC >> 4); ++kk) {
+          const uint32_t ao = (uint32_t)(2 * kk) * lbo_a + (uint32_t)q * 16u;   // tap q = slab shifted by q rows of 16 B
+          const uint32_t bo = (uint32_t)(2 * kk) * lbo_b;
+          const uint64_t ad_hi = make_desc(a_hi + ao, lbo_a, 128), ad_lo = make_desc(a_lo + ao, lbo_a, 128);
+          const uint64_t bd_hi = make_desc(b_hi + bo, lbo_b, 128), bd_lo = make_desc(b_lo + bo, lbo_b, 128);
+          tc_mma_bf16(tmem_base, ad_lo, bd_hi, idesc, (n | kk) != 0 ? 1u : 0u);   // small terms first
+          tc_mma_bf16(tmem_base, ad_hi, bd_lo, idesc, 1u);
+          tc_mma_bf16(tmem_base, ad_hi, bd_hi, idesc, 1u);
+        }
+        tc_commit(smem_u32(&b_free[bs]));
+        // refill the stage of the PREVIOUS item (its MMAs finish while this item's run)
+        const int m = n - 1 + kHtBStages;
+        if (n >= 1 && m < n_items) {
+          const int ms = m % kHtBStages;
+          mbar_wait(smem_u32(&b_free[ms]), (uint32_t)(((m / kHtBStages) & 1) ^ 1), P.err_flag, 46);
+          mbar_expect_tx(smem_u32(&b_full[ms]), b_stage);
+          bulk_g2s(smem_u32(b_s + (size_t)ms * b_stage), wsrc + (size_t)m * b_stage, b_stage, smem_u32(&b_full[ms]));
+        }
+      }
+      tc_commit(smem_u32(&a_free[st]));
+    }
+    tc_commit(smem_u32(acc_full));
+  }
+  __syncthreads();
+  if (warp == 4) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols) : "memory");
+  }
+}
+
+inline cudaError_t gemm_hp_tc_set_attributes() {
+  return cudaFuncSetAttribute(gemm_hp_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+}
+
+inline bool gemm_hp_tc_ok(const HpGemmParams& P) {
+  const int C_in = P.a_nch * 8;
+  return P.w_tc && P.KC >= 16 && P.KC % 16 == 0 && C_in % P.KC == 0 && P.N_TILE >= 16 && P.N_TILE % 16 == 0 && P.N_TILE <= 256 &&
+         P.N_total % P.N_TILE == 0 && P.n_shift >= 1 && P.n_shift <= 17 && ht_smem_bytes(P.KC, P.N_TILE, P.n_shift) <= 200 * 1024;
+}
+
+inline cudaError_t gemm_hp_tc_launch(const HpGemmParams& P, cudaStream_t s) {
+  dim3 grid((P.m_rows + kHpBM - 1) / kHpBM, P.N_total / P.N_TILE);
+  gemm_hp_tc_kernel<<<grid, kHtThreads, ht_smem_bytes(P.KC, P.N_TILE, P.n_shift), s>>>(P);
   return cudaGetLastError();
 }
 

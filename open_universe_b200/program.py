@@ -170,6 +170,7 @@ class Program:
             op.a_act, op.a_slope = 1, a_slope
         if self.hp:               # fp32 tier: f32 [S][Q][C_in][N_total] image of the same GEMM (csrc/hp_ops.cuh)
             op.p5 = ly["w_hp"]
+            op.p4, op.i0, op.i2 = ly["w_tc"], ly["tc_KC"], ly["tc_NT"]   # split-bf16 images, K group, N tile (tensor-core variant)
         return self.emit(op, name)
 
 

@@ -180,6 +180,19 @@ def pack_w4(w4, kc, n_tile, bias_n=None):
     return to_bf16_bits(x)
 
 
+def pack_w4_split(w4, kc, n_tile):
+    """[N, S, Q, Ci] fp32 -> the "bf16x3" images of the fp32 tier's tensor-core GEMM: w = hi + lo with hi = bf16(w),
+    lo = bf16(w - hi) (16 mantissa bits together), per N tile and (source, K group, shift) one item
+    [hi | lo][kc/8][n_tile][8] bf16 in the no-swizzle K-major UMMA layout (one bulk copy per item)."""
+    n, s, q, ci = w4.shape
+    assert n % n_tile == 0 and ci % kc == 0 and kc % 16 == 0 and n_tile % 16 == 0
+    hi = w4.to(torch.bfloat16).float()
+    lo = (w4 - hi).to(torch.bfloat16).float()
+    x = torch.stack([hi, lo]).view(2, n // n_tile, n_tile, s, q, ci // kc, kc // 8, 8)   # h, nt, n, s, q, g, j, e
+    x = x.permute(1, 3, 5, 4, 0, 6, 2, 7).contiguous()                                       # nt, s, g, q, h, j, n, e
+    return to_bf16_bits(x.reshape(-1))
+
+
 def unpack_w4(bits, n, s, q, ci, kc, n_tile, has_bias=False):
     """Inverse of pack_w4 (used by the CPU emulator): -> fp32 [N, S, Q, Ci] (and the bias [N] the
     tensor core sees, hi + lo, when has_bias)."""
@@ -261,6 +274,9 @@ class PackedModel:
         )
         if self.hp:
             self.layers[name]["w_hp"] = self.blob.add_f32(w4.permute(1, 2, 3, 0).contiguous())
+            # tensor-core variant of the fp32 tier (csrc/hp_ops.cuh gemm_hp_tc_kernel): split-bf16 images
+            tc_kc = 32 if ci % 32 == 0 else 16
+            self.layers[name].update(w_tc=self.blob.add(pack_w4_split(w4, tc_kc, n_tile)), tc_KC=tc_kc, tc_NT=n_tile)
 
     def add_conv_block(self, sd, prefix, name, rate=None, direction="none", s2d=False):
         """ConvBlock parameters (blocks.py:240-329).  s2d: also pack the three convs for phase-split-by-2 tensors

@@ -54,7 +54,8 @@ def test_fp32_every_op_matches_emulator():
             err = (gt - et).norm().item() / max(et.norm().item(), 1e-12)
             kind = _abi.OP_NAMES[op.type]
             worst[kind] = max(worst.get(kind, 0.0), err)
-            if not (err < 2e-5) or not torch.isfinite(gt).all():
+            # dense layers: split-bf16 products on the tensor cores (16 mantissa bits per operand), fp32 everywhere else
+            if not (err < (5e-5 if op.type == _abi.OP_GEMM else 2e-5)) or not torch.isfinite(gt).all():
                 bad.append((i, name, label, err))
     e_out = uo.rel_l2(dout.cpu(), eio["out"])
     print("fp32 tier: worst rel-L2 per op kind vs emulator:", {k: f"{v:.1e}" for k, v in worst.items()}, f"final out {e_out:.2e}")

@@ -112,3 +112,18 @@ def test_unsupported_edge_conv_kernel_size_is_rejected():
     sd[key] = torch.zeros(sd[key].shape[0], 1, 5)
     with pytest.raises(NotImplementedError):
         weights.pack_model(sd, model.model_config())
+
+
+def test_split_bf16_images_of_the_fp32_tier():
+    """pack_w4_split: item (N tile, source, K group, shift) = [hi | lo][kc/8][n_tile][8]; hi + lo reproduces the fp32
+    weight to 2^-16 relative (the "bf16x3" operands of csrc/hp_ops.cuh gemm_hp_tc_kernel)."""
+    import numpy as np
+    torch.manual_seed(0)
+    n, s, q, ci, kc, nt = 96, 2, 3, 64, 32, 48
+    w4 = torch.randn(n, s, q, ci)
+    bits = weights.pack_w4_split(w4, kc, nt)
+    x = torch.from_numpy(np.ascontiguousarray(bits)).view(torch.bfloat16).float()
+    x = x.view(n // nt, s, ci // kc, q, 2, kc // 8, nt, 8)
+    rec = (x[:, :, :, :, 0] + x[:, :, :, :, 1]).permute(0, 5, 1, 3, 2, 4, 6).reshape(n, s, q, ci)   # nt, n, s, q, g, j, e
+    assert (rec - w4).abs().max() <= 2.0 ** -16 * w4.abs().max()
+    assert torch.equal(x[:, :, :, :, 0].permute(0, 5, 1, 3, 2, 4, 6).reshape(n, s, q, ci), w4.to(torch.bfloat16).float())
