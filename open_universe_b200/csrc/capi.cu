@@ -108,6 +108,7 @@ extern "C" int uv_model_create(uv_model** out, const void* weights, size_t nbyte
   CUDA_TRY(gemm_set_attributes());
   CUDA_TRY(convblock_pair_set_attributes());
   CUDA_TRY(gemm_hp_tc_set_attributes());
+  CUDA_TRY(gru_hp_set_attributes());
   CUDA_TRY(cudaFuncSetAttribute(aux_to_wav_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   CUDA_TRY(cudaFuncSetAttribute(gru_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   CUDA_TRY(cudaFuncSetAttribute(mel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMelMaxSmem));
@@ -383,6 +384,8 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
         for (int i = 0; i < h.n_out; ++i)
           if (h.out[i].t.split != 1) return fail(UV_ERR_INVALID, "GRU outputs must be plain tensors");
         h.rows = op.rows >= 0 ? aptr<const RowGeo>(p, op.rows) : nullptr;
+        h.err_flag = p->err_flag;
+        if (h.H % hp_gru_kch(h.H) || hp_gru_smem(h.H) > 200 * 1024) return fail(UV_ERR_INVALID, "fp32 GRU: hidden size unsupported");
         CUDA_TRY(gru_hp_launch(h, s));
         break;
       }

@@ -221,10 +221,11 @@ __device__ __forceinline__ void split_bf16x8(const float* x, uint4& hi, uint4& l
   }
 }
 
-__global__ void __launch_bounds__(kHtThreads) gemm_hp_tc_kernel(const __grid_constant__ HpGemmParams P) {
+template <int KJ>   // channel chunks per K group (KC = 8 KJ)
+__global__ void __launch_bounds__(kHtThreads, 2) gemm_hp_tc_kernel(const __grid_constant__ HpGemmParams P) {
   extern __shared__ unsigned char ht_smem_raw[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int Q = P.n_shift, KC = P.KC, NT = P.N_TILE, KJ = KC >> 3;
+  const int Q = P.n_shift, KC = 8 * KJ, NT = P.N_TILE;
   const int G = (P.a_nch * 8) / KC;
   const int n_slabs = P.n_src * G;
   const int n_items = n_slabs * Q;
@@ -270,12 +271,28 @@ __global__ void __launch_bounds__(kHtThreads) gemm_hp_tc_kernel(const __grid_con
       unsigned char* hi = a_s + (size_t)st * a_stage;
       unsigned char* lo = hi + a_half;
       const float* plane0 = P.a_base + ((size_t)(s * P.a_nch + g * KJ) * P.a_P + P.a_G + P.smin + g0) * 8;
-      for (int r = tid; r < kHpBM + Q - 1; r += 128) {   // (the slab's pitch is rounded up; only the rows the taps reach are filled)
+      // thread = row; the Q - 1 halo rows go to the first threads, whose loads are issued together with those of their
+      // first row (all loads of a slab in flight at once: the producers are latency bound)
+      const bool two = tid < Q - 1;
+      float4 x0[2 * KJ], x1[2 * KJ];
+#pragma unroll
+      for (int j = 0; j < KJ; ++j) {
+        const float* src = plane0 + ((size_t)j * P.a_P + tid) * 8;
+        x0[2 * j] = *reinterpret_cast<const float4*>(src);
+        x0[2 * j + 1] = *reinterpret_cast<const float4*>(src + 4);
+      }
+      if (two) {
+#pragma unroll
         for (int j = 0; j < KJ; ++j) {
-          const float* src = plane0 + ((size_t)j * P.a_P + r) * 8;
-          const float4 x0 = *reinterpret_cast<const float4*>(src);
-          const float4 x1 = *reinterpret_cast<const float4*>(src + 4);
-          float x[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+          const float* src = plane0 + ((size_t)j * P.a_P + tid + kHpBM) * 8;
+          x1[2 * j] = *reinterpret_cast<const float4*>(src);
+          x1[2 * j + 1] = *reinterpret_cast<const float4*>(src + 4);
+        }
+      }
+      auto put = [&](const float4* xx, int r) {
+#pragma unroll
+        for (int j = 0; j < KJ; ++j) {
+          float x[8] = {xx[2 * j].x, xx[2 * j].y, xx[2 * j].z, xx[2 * j].w, xx[2 * j + 1].x, xx[2 * j + 1].y, xx[2 * j + 1].z, xx[2 * j + 1].w};
           if (P.a_act) {
 #pragma unroll
             for (int e = 0; e < 8; ++e) x[e] = prelu1(x[e], P.a_slope);
@@ -285,7 +302,9 @@ __global__ void __launch_bounds__(kHtThreads) gemm_hp_tc_kernel(const __grid_con
           *reinterpret_cast<uint4*>(hi + ((size_t)j * slab_rows + r) * 16) = h4;
           *reinterpret_cast<uint4*>(lo + ((size_t)j * slab_rows + r) * 16) = l4;
         }
-      }
+      };
+      put(x0, tid);
+      if (two) put(x1, tid + kHpBM);
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic stores -> tensor-core reads
       __syncwarp();
       if (lane == 0) mbar_arrive(smem_u32(&a_full[st]));
@@ -360,23 +379,26 @@ __global__ void __launch_bounds__(kHtThreads) gemm_hp_tc_kernel(const __grid_con
 }
 
 inline cudaError_t gemm_hp_tc_set_attributes() {
-  return cudaFuncSetAttribute(gemm_hp_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  cudaError_t e = cudaFuncSetAttribute(gemm_hp_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(gemm_hp_tc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
 }
 
 inline bool gemm_hp_tc_ok(const HpGemmParams& P) {
   const int C_in = P.a_nch * 8;
-  return P.w_tc && P.KC >= 16 && P.KC % 16 == 0 && C_in % P.KC == 0 && P.N_TILE >= 16 && P.N_TILE % 16 == 0 && P.N_TILE <= 256 &&
+  return P.w_tc && (P.KC == 16 || P.KC == 32) && C_in % P.KC == 0 && P.N_TILE >= 16 && P.N_TILE % 16 == 0 && P.N_TILE <= 256 &&
          P.N_total % P.N_TILE == 0 && P.n_shift >= 1 && P.n_shift <= 17 && ht_smem_bytes(P.KC, P.N_TILE, P.n_shift) <= 200 * 1024;
 }
 
 inline cudaError_t gemm_hp_tc_launch(const HpGemmParams& P, cudaStream_t s) {
   dim3 grid((P.m_rows + kHpBM - 1) / kHpBM, P.N_total / P.N_TILE);
-  gemm_hp_tc_kernel<<<grid, kHtThreads, ht_smem_bytes(P.KC, P.N_TILE, P.n_shift), s>>>(P);
+  if (P.KC == 32) gemm_hp_tc_kernel<4><<<grid, kHtThreads, ht_smem_bytes(P.KC, P.N_TILE, P.n_shift), s>>>(P);
+  else gemm_hp_tc_kernel<2><<<grid, kHtThreads, ht_smem_bytes(P.KC, P.N_TILE, P.n_shift), s>>>(P);
   return cudaGetLastError();
 }
 
 // ---------------------------------------------------------------- GRU recurrence
-constexpr int kHpGruNB = 8;   // utterances per CTA
+constexpr int kHpGruNB = 4;   // utterances per CTA
 
 struct HpGruParams {
   const float* gi;     // f32 row-major [b Lh + t][6H]: x W_ih^T + b_ih, columns dir * 3H + gate * H + u
@@ -388,6 +410,7 @@ struct HpGruParams {
   int n_out;
   OutDesc out[3];
   const RowGeo* rows;  // per-utterance frame counts (null: T for all)
+  int* err_flag;
 };
 
 __device__ __forceinline__ char* elem_addr(const TensDesc& t, int b, int l, int c) {
@@ -395,19 +418,60 @@ __device__ __forceinline__ char* elem_addr(const TensDesc& t, int b, int l, int 
   return t.base + (((row * 8) + (c & 7)) << t.esize_log2);
 }
 
-// grid (ceil(B / 8), 2 directions), H threads: thread u owns hidden unit u of 8 utterances; the state lives in shared
-// memory as h[k][utterance] (two buffers), W_hh streams from L2 with coalesced loads (gate rows of consecutive units).
-__global__ void __launch_bounds__(384) gru_hp_kernel(const HpGruParams P) {
-  extern __shared__ __align__(16) float hs[];   // [2][H][8]
-  const int H = P.H, u = threadIdx.x, d = blockIdx.y;
+// K rows of W_hh per ring stage and ring depth: 48 KB (H <= 256) or 36 KB (H = 384) per stage, 144 KB in flight
+__host__ __device__ inline int hp_gru_kch(int H) { return H <= 256 ? 16 : 8; }
+__host__ __device__ inline int hp_gru_stages(int H) { return H <= 256 ? 3 : 4; }
+__host__ __device__ inline size_t hp_gru_smem(int H) {
+  return (size_t)hp_gru_stages(H) * hp_gru_kch(H) * 3 * H * 4 + 2 * (size_t)H * kHpGruNB * 4 + 128;
+}
+
+// grid (ceil(B / 4), 2 directions); H compute threads + one producer warp.  Thread u owns hidden unit u of 4
+// utterances (state in shared memory as h[k][utterance], two buffers).  The recurrence needs all of W_hh (3H x H
+// f32: 0.75 - 1.7 MB per direction) at every step: one thread streams it from L2 through a shared-memory ring with bulk
+// copies ([k][gate][u] rows, so consecutive threads read consecutive words), which keeps ~100 KB in flight per SM --
+// with plain loads the kernel was latency bound (35 us per step; 4-5 us this way, FMA / shared-memory bound).
+__global__ void __launch_bounds__(416) gru_hp_kernel(const __grid_constant__ HpGruParams P) {
+  extern __shared__ __align__(128) unsigned char gru_hp_smem[];
+  const int H = P.H, tid = threadIdx.x, lane = tid & 31, d = blockIdx.y;
+  const int KCH = hp_gru_kch(H), NS = hp_gru_stages(H);
+  const int n_chunks = H / KCH;
+  const uint32_t stage_bytes = (uint32_t)(KCH * 3 * H * 4);
+  float* ring = reinterpret_cast<float*>(gru_hp_smem);
+  float* hs = ring + (size_t)NS * KCH * 3 * H;                       // [2][H][4]
+  uint64_t* full = reinterpret_cast<uint64_t*>(hs + 2 * H * kHpGruNB);   // [NS] | empty [NS]
+  uint64_t* empty = full + NS;
   const int b0 = blockIdx.x * kHpGruNB;
   const float* W = P.whh + (size_t)d * H * 3 * H;
+  if (tid == 0) {
+    for (int i = 0; i < NS; ++i) { mbar_init(smem_u32(&full[i]), 1); mbar_init(smem_u32(&empty[i]), (uint32_t)(H >> 5)); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  for (int i = tid; i < 2 * H * kHpGruNB; i += blockDim.x) hs[i] = 0.f;
+  __syncthreads();
+  const long long total = (long long)P.T * n_chunks;
+  if (tid >= H) {
+    // ============================== producer: W_hh chunks, over and over (one per T x n_chunks)
+    if (lane == 0) {
+      int st = 0, chunk = 0;
+      uint32_t par = 1;
+      for (long long it = 0; it < total; ++it) {
+        mbar_wait(smem_u32(&empty[st]), par, P.err_flag, 51);
+        mbar_expect_tx(smem_u32(&full[st]), stage_bytes);
+        bulk_g2s(smem_u32(ring + (size_t)st * KCH * 3 * H), W + (size_t)chunk * KCH * 3 * H, stage_bytes, smem_u32(&full[st]));
+        if (++st == NS) { st = 0; par ^= 1; }
+        if (++chunk == n_chunks) chunk = 0;
+      }
+    }
+    return;
+  }
+  // ============================== compute threads
+  const int u = tid;
   const float br = P.bhh[d * 3 * H + u], bz = P.bhh[d * 3 * H + H + u], bn = P.bhh[d * 3 * H + 2 * H + u];
   int Tb[kHpGruNB];
 #pragma unroll
   for (int b = 0; b < kHpGruNB; ++b) Tb[b] = (b0 + b < P.B) ? (P.rows ? P.rows[b0 + b].F : P.T) : 0;
-  for (int i = u; i < 2 * H * kHpGruNB; i += H) hs[i] = 0.f;
-  __syncthreads();
+  int st = 0;
+  uint32_t par = 0;
   for (int step = 0; step < P.T; ++step) {
     const int t = d == 0 ? step : P.T - 1 - step;
     const float* hc = hs + (step & 1) * H * kHpGruNB;
@@ -425,18 +489,25 @@ __global__ void __launch_bounds__(384) gru_hp_kernel(const HpGruParams P) {
     float ar[kHpGruNB], az[kHpGruNB], an[kHpGruNB];
 #pragma unroll
     for (int b = 0; b < kHpGruNB; ++b) { ar[b] = br; az[b] = bz; an[b] = bn; }
-#pragma unroll 4
-    for (int k = 0; k < H; ++k) {
-      const float wr = W[(size_t)k * 3 * H + u], wz = W[(size_t)k * 3 * H + H + u], wn = W[(size_t)k * 3 * H + 2 * H + u];
-      const float4 h0 = *reinterpret_cast<const float4*>(hc + k * kHpGruNB);
-      const float4 h1 = *reinterpret_cast<const float4*>(hc + k * kHpGruNB + 4);
-      const float hv[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+    for (int c = 0; c < n_chunks; ++c) {
+      mbar_wait(smem_u32(&full[st]), par, P.err_flag, 52);
+      const float* ws = ring + (size_t)st * KCH * 3 * H + u;
+      const float* hk = hc + (size_t)c * KCH * kHpGruNB;
+#pragma unroll 8
+      for (int kk = 0; kk < KCH; ++kk) {
+        const float wr = ws[kk * 3 * H], wz = ws[kk * 3 * H + H], wn = ws[kk * 3 * H + 2 * H];
+        const float4 h4 = *reinterpret_cast<const float4*>(hk + kk * kHpGruNB);
+        const float hv[4] = {h4.x, h4.y, h4.z, h4.w};
 #pragma unroll
-      for (int b = 0; b < kHpGruNB; ++b) {
-        ar[b] = fmaf(wr, hv[b], ar[b]);
-        az[b] = fmaf(wz, hv[b], az[b]);
-        an[b] = fmaf(wn, hv[b], an[b]);
+        for (int b = 0; b < kHpGruNB; ++b) {
+          ar[b] = fmaf(wr, hv[b], ar[b]);
+          az[b] = fmaf(wz, hv[b], az[b]);
+          an[b] = fmaf(wn, hv[b], an[b]);
+        }
       }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(smem_u32(&empty[st]));
+      if (++st == NS) { st = 0; par ^= 1; }
     }
 #pragma unroll
     for (int b = 0; b < kHpGruNB; ++b) {
@@ -466,13 +537,17 @@ __global__ void __launch_bounds__(384) gru_hp_kernel(const HpGruParams P) {
       }
       hn[u * kHpGruNB + b] = hnew;
     }
-    __syncthreads();
+    asm volatile("bar.sync 1, %0;" ::"r"(H) : "memory");   // the compute threads only (the producer runs ahead)
   }
+}
+
+inline cudaError_t gru_hp_set_attributes() {
+  return cudaFuncSetAttribute(gru_hp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
 }
 
 inline cudaError_t gru_hp_launch(const HpGruParams& P, cudaStream_t s) {
   dim3 grid((P.B + kHpGruNB - 1) / kHpGruNB, 2);
-  gru_hp_kernel<<<grid, P.H, 2 * P.H * kHpGruNB * sizeof(float), s>>>(P);
+  gru_hp_kernel<<<grid, P.H + 32, hp_gru_smem(P.H), s>>>(P);
   return cudaGetLastError();
 }
 
