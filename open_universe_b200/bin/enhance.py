@@ -57,16 +57,25 @@ def find_files(path):
     return files, path, True
 
 
+# torchaudio's file IO needs a codec backend (torchcodec), absent from this image: the first failed attempt is
+# remembered, because a failing torchaudio.load / save costs ~0.5 ms per file (7x the WAV read itself; measured: the
+# decode of a 64-file window took longer than its batch on the device).  None = untried, True = works, False = skip.
+_TORCHAUDIO_IO = {"load": None, "save": None}
+
+
 def load_audio(path):
     """-> (float32 tensor [channels, samples], fs).  torchaudio.load when its codec backend exists (the reference's
     call, enhance.py:183), else WAV through scipy (this image has no torchcodec)."""
-    try:
-        import torchaudio
+    if _TORCHAUDIO_IO["load"] is not False:
+        try:
+            import torchaudio
 
-        audio, fs = torchaudio.load(str(path))
-        return audio.float(), int(fs)
-    except (ImportError, RuntimeError, OSError):
-        pass
+            audio, fs = torchaudio.load(str(path))
+            _TORCHAUDIO_IO["load"] = True
+            return audio.float(), int(fs)
+        except (ImportError, RuntimeError, OSError):
+            if _TORCHAUDIO_IO["load"] is None:
+                _TORCHAUDIO_IO["load"] = False
     from scipy.io import wavfile
 
     if Path(path).suffix.lower() != ".wav":
@@ -79,23 +88,28 @@ def load_audio(path):
     elif data.dtype == np.uint8:
         x = (data.astype(np.float32) - 128.0) / 128.0
     else:
-        x = data.astype(np.float32)
-    x = x[:, None] if x.ndim == 1 else x
+        x = data.astype(np.float32, copy=False)   # float32 files: no copy
+    if x.ndim == 1:
+        return torch.from_numpy(x)[None], int(fs)
     return torch.from_numpy(np.ascontiguousarray(x.T)), int(fs)
 
 
 def save_audio(path, audio, fs):
     """audio: float tensor [channels, samples] (reference: torchaudio.save, enhance.py:192)."""
-    try:
-        import torchaudio
+    if _TORCHAUDIO_IO["save"] is not False:
+        try:
+            import torchaudio
 
-        torchaudio.save(str(path), audio, fs)
-        return
-    except (ImportError, RuntimeError, OSError):
-        pass
+            torchaudio.save(str(path), audio, fs)
+            _TORCHAUDIO_IO["save"] = True
+            return
+        except (ImportError, RuntimeError, OSError):
+            if _TORCHAUDIO_IO["save"] is None:
+                _TORCHAUDIO_IO["save"] = False
     from scipy.io import wavfile
 
-    wavfile.write(str(path), fs, np.ascontiguousarray(audio.numpy().T.astype(np.float32)))
+    a = audio.numpy().astype(np.float32, copy=False)
+    wavfile.write(str(path), fs, a[0] if a.shape[0] == 1 else np.ascontiguousarray(a.T))
 
 
 def resample(audio, fs, target_fs):
@@ -140,8 +154,39 @@ def enhance_files(model, files, out_paths, enhance_kwargs, batch_size=64, device
     writer = ThreadPoolExecutor(max(2, io_threads))
     stats = dict(files=0, utterances=0, batches=0, audio_seconds=0.0)
 
-    def load_window(w):
-        return list(loader.map(lambda fi: (fi,) + tuple(load_audio(files[fi])), w))
+    use_cuda = torch.device(device).type == "cuda"
+    copy_stream = torch.cuda.Stream(device) if use_cuda else None
+    stage = {}   # slot -> (pinned host buffer, event behind its last upload)
+
+    def load_window(wi):
+        """Decodes window wi and uploads it: -> ([(file index, audio on the device [C, n], fs)], (flat device buffer,
+        event) or None).  On a CUDA device the whole window goes up as ONE copy from a pinned staging buffer on a copy
+        stream (this runs in the prefetch thread, a window ahead): a per-file `.to(device)` from pageable memory is
+        synchronous -- it made the main thread wait for the device to finish the previous window before it could
+        prepare the next one."""
+        loaded = list(loader.map(lambda fi: (fi,) + tuple(load_audio(files[fi])), windows[wi]))
+        if not use_cuda:
+            return [(fi, a.to(device), fs) for fi, a, fs in loaded], None
+        total = sum(a.numel() for _, a, _ in loaded)
+        slot = wi % 3
+        buf, ev = stage.get(slot, (None, None))
+        if ev is not None:
+            ev.synchronize()
+        if buf is None or buf.numel() < total:
+            buf = torch.empty(max(total, 1), dtype=torch.float32).pin_memory()
+        off, spans = 0, []
+        for fi, a, fs in loaded:
+            n = a.numel()
+            buf[off : off + n].copy_(a.reshape(-1))
+            spans.append((fi, fs, off, tuple(a.shape)))
+            off += n
+        with torch.cuda.device(device), torch.cuda.stream(copy_stream):
+            dev = torch.empty(max(total, 1), dtype=torch.float32, device=device)
+            dev[:total].copy_(buf[:total], non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(copy_stream)
+        stage[slot] = (buf, ev)
+        return [(fi, dev[o : o + shape[0] * shape[1]].view(shape), fs) for fi, fs, o, shape in spans], (dev, ev)
 
     def write_file(path, enh, fs):
         Path(path).parent.mkdir(exist_ok=True, parents=True)
@@ -152,16 +197,19 @@ def enhance_files(model, files, out_paths, enhance_kwargs, batch_size=64, device
 
         bar = tqdm(total=len(mine))
     pending = []
-    nxt = prefetch.submit(load_window, windows[0]) if windows else None
+    nxt = prefetch.submit(load_window, 0) if windows else None
     with torch.no_grad():
         for wi in range(len(windows)):
-            loaded = nxt.result()
-            nxt = prefetch.submit(load_window, windows[wi + 1]) if wi + 1 < len(windows) else None
+            loaded, h2d = nxt.result()
+            nxt = prefetch.submit(load_window, wi + 1) if wi + 1 < len(windows) else None
+            if h2d is not None:   # the upload ran on the copy stream: order it in front of this stream's work
+                torch.cuda.current_stream(device).wait_event(h2d[1])
+                h2d[0].record_stream(torch.cuda.current_stream(device))
             utts = []        # (file index, channel, tensor [T] on the device at the model rate)
             fs_of = {}
             for fi, audio, fs in loaded:
                 fs_of[fi] = fs
-                a = resample(audio.to(device, non_blocking=True), fs, model.fs)
+                a = resample(audio, fs, model.fs)
                 for c in range(a.shape[0]):
                     utts.append((fi, c, a[c]))
             lens = [u[2].shape[-1] for u in utts]
