@@ -259,6 +259,27 @@ typedef struct {
 } uv_mel_desc;
 int uv_mel_spec_static(uv_model* m, const uv_mel_desc* d, const float* sig, int B, int Lp, float* mel_out, void* stream);
 
+/* ---- batch WAV IO of the file pipeline (host side; replaces the per-file torchaudio.load / torchaudio.save of
+ * open_universe/bin/enhance.py:183,192 for RIFF/WAVE files).  A window of files is decoded / encoded by `threads` host
+ * threads without the interpreter lock, into / out of ONE caller-owned float32 staging buffer (pinned, so that the
+ * window crosses PCIe as a single copy).  File i occupies [offs[i], offs[i] + channels * frames) floats, planar
+ * [channels][frames], scaled like torchaudio.load: int16 / 2^15, int32 / 2^31, (uint8 - 128) / 128, float32 as is.
+ * uv_wav_probe fills info[i] (frames = -1: not a PCM 8/16/32-bit or float32 RIFF/WAVE file -- the caller falls back
+ * to its own decoder for that file); all three return the number of files that failed (status[i] != 0), < 0 on a
+ * bad argument.  uv_wav_write writes IEEE-float WAV files (what torchaudio.save writes for a float tensor).     */
+typedef struct {
+  int32_t channels, fs;
+  int32_t format;   /* 1 = integer PCM, 3 = IEEE float */
+  int32_t bits;
+  int64_t frames;   /* < 0: unsupported / unreadable */
+  int64_t data_off; /* byte offset of the samples in the file */
+} uv_wav_info;
+int uv_wav_probe(const char* const* paths, int n, uv_wav_info* info, int threads);
+int uv_wav_read(const char* const* paths, int n, const uv_wav_info* info, const int64_t* offs, float* dst, int threads,
+                int32_t* status);
+int uv_wav_write(const char* const* paths, int n, const int32_t* channels, const int64_t* frames, const int32_t* fs,
+                 const int64_t* offs, const float* src, int threads, int32_t* status);
+
 #ifdef __cplusplus
 }
 #endif

@@ -88,6 +88,11 @@ class UvMelDesc(C.Structure):
                 ("pad_", C.c_int32), ("basis_w", C.c_int64), ("fb_w", C.c_int64)]
 
 
+class UvWavInfo(C.Structure):
+    _fields_ = [("channels", C.c_int32), ("fs", C.c_int32), ("format", C.c_int32), ("bits", C.c_int32),
+                ("frames", C.c_int64), ("data_off", C.c_int64)]
+
+
 UV_STATIC_SCRATCH_BYTES = 16 << 20
 
 

@@ -20,6 +20,7 @@ EXPORTS = [
     "uv_plan_destroy", "uv_plan_arena_bytes", "uv_enhance", "uv_run_ops", "uv_arena_read", "uv_arena_write",
     "uv_plan_num_launches", "uv_profile_ops", "uv_plan_arena_ptr", "uv_trace_ops", "uv_plan_status",
     "uv_mel_spec_static", "uv_set_noise_seed", "uv_signal_median", "uv_set_row_tables",
+    "uv_wav_probe", "uv_wav_read", "uv_wav_write",
 ]
 
 
@@ -86,6 +87,11 @@ def lib():
     L.uv_set_noise_seed.argtypes = [C.c_void_p, C.c_ulonglong]
     L.uv_set_row_tables.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t]
     L.uv_signal_median.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_longlong, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.uv_wav_probe.argtypes = [C.POINTER(C.c_char_p), C.c_int, C.POINTER(_abi.UvWavInfo), C.c_int]
+    L.uv_wav_read.argtypes = [C.POINTER(C.c_char_p), C.c_int, C.POINTER(_abi.UvWavInfo), C.POINTER(C.c_int64), C.c_void_p, C.c_int,
+                              C.POINTER(C.c_int32)]
+    L.uv_wav_write.argtypes = [C.POINTER(C.c_char_p), C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_int64), C.POINTER(C.c_int32),
+                               C.POINTER(C.c_int64), C.c_void_p, C.c_int, C.POINTER(C.c_int32)]
     L.uv_plan_arena_ptr.argtypes = [C.c_void_p]
     L.uv_plan_arena_ptr.restype = C.c_void_p
     if L.uv_abi_version() != _abi.UV_ABI_VERSION:
@@ -246,3 +252,49 @@ def signal_median(signal):
         _check(lib().uv_signal_median(flat.data_ptr(), E, B, S, out.data_ptr(), scratch.data_ptr(),
                                       torch.cuda.current_stream(signal.device).cuda_stream), "uv_signal_median")
     return out.reshape(shape[1:]).to(signal.dtype)
+
+
+# ---------------------------------------------------------------- batch WAV IO (uv_wav_probe / uv_wav_read / uv_wav_write)
+def _c_paths(paths):
+    arr = (C.c_char_p * len(paths))()
+    arr[:] = [os.fsencode(str(p)) for p in paths]
+    return arr
+
+
+def wav_probe(paths, threads=4):
+    """-> list of (channels, frames, fs) per file, None where the native reader does not decode the file."""
+    n = len(paths)
+    info = (_abi.UvWavInfo * max(n, 1))()
+    rc = lib().uv_wav_probe(_c_paths(paths), n, info, threads)
+    if rc < 0:
+        raise RuntimeError("uv_wav_probe: bad argument")
+    return info, [(i.channels, i.frames, i.fs) if i.frames >= 0 else None for i in info[:n]]
+
+
+def wav_read(paths, info, offsets, dst, threads=4):
+    """Decodes the probed files into the float32 CPU tensor `dst` (file i at offsets[i], planar [channels][frames]).
+    -> list of booleans (decoded?)."""
+    n = len(paths)
+    offs = (C.c_int64 * max(n, 1))(*offsets)
+    status = (C.c_int32 * max(n, 1))()
+    assert dst.dtype.itemsize == 4 and dst.is_contiguous() and not dst.is_cuda
+    rc = lib().uv_wav_read(_c_paths(paths), n, info, offs, dst.data_ptr(), threads, status)
+    if rc < 0:
+        raise RuntimeError("uv_wav_read: bad argument")
+    return [status[i] == 0 for i in range(n)]
+
+
+def wav_write(paths, shapes, rates, offsets, src, threads=4):
+    """Writes float32 WAV files from the float32 CPU tensor `src` (file i = shapes[i] = (channels, frames) at
+    offsets[i]).  -> list of booleans (written?)."""
+    n = len(paths)
+    ch = (C.c_int32 * max(n, 1))(*[s[0] for s in shapes])
+    fr = (C.c_int64 * max(n, 1))(*[s[1] for s in shapes])
+    fs = (C.c_int32 * max(n, 1))(*rates)
+    offs = (C.c_int64 * max(n, 1))(*offsets)
+    status = (C.c_int32 * max(n, 1))()
+    assert src.dtype.itemsize == 4 and src.is_contiguous() and not src.is_cuda
+    rc = lib().uv_wav_write(_c_paths(paths), n, ch, fr, fs, offs, src.data_ptr(), threads, status)
+    if rc < 0:
+        raise RuntimeError("uv_wav_write: bad argument")
+    return [status[i] == 0 for i in range(n)]

@@ -29,7 +29,7 @@ from pathlib import Path
 import numpy as np
 import torch
 
-from open_universe_b200 import inference_utils, sharding
+from open_universe_b200 import _native, inference_utils, sharding
 
 AUDIO_SUFFIXES = [".wav", ".mp3", ".flac"]   # reference enhance.py:33
 
@@ -156,41 +156,76 @@ def enhance_files(model, files, out_paths, enhance_kwargs, batch_size=64, device
 
     use_cuda = torch.device(device).type == "cuda"
     copy_stream = torch.cuda.Stream(device) if use_cuda else None
+    down_stream = torch.cuda.Stream(device) if use_cuda else None
     stage = {}   # slot -> (pinned host buffer, event behind its last upload)
+    out_stage = {}   # slot -> (pinned host buffer, future of the writer that reads it)
+    native_io = os.path.exists(_native.LIB_PATH) and os.environ.get("UV_NATIVE_WAV", "1") != "0"
 
     def load_window(wi):
         """Decodes window wi and uploads it: -> ([(file index, audio on the device [C, n], fs)], (flat device buffer,
-        event) or None).  On a CUDA device the whole window goes up as ONE copy from a pinned staging buffer on a copy
-        stream (this runs in the prefetch thread, a window ahead): a per-file `.to(device)` from pageable memory is
-        synchronous -- it made the main thread wait for the device to finish the previous window before it could
-        prepare the next one."""
-        loaded = list(loader.map(lambda fi: (fi,) + tuple(load_audio(files[fi])), windows[wi]))
-        if not use_cuda:
-            return [(fi, a.to(device), fs) for fi, a, fs in loaded], None
-        total = sum(a.numel() for _, a, _ in loaded)
+        event) or None).  WAV files are decoded by the native batch reader (csrc/wav_io.cuh: host threads, no
+        interpreter lock) straight into the window's staging buffer; other formats go through load_audio.  On a CUDA
+        device the buffer is pinned and the whole window goes up as ONE copy on a copy stream (this runs in the
+        prefetch thread, a window ahead): a per-file `.to(device)` from pageable memory is synchronous -- it made the
+        main thread wait for the device to finish the previous window before it could prepare the next one."""
+        w = windows[wi]
+        paths = [files[fi] for fi in w]
+        meta = [None] * len(w)
+        info = None
+        if native_io:
+            wavs = [k for k, p in enumerate(paths) if Path(p).suffix.lower() == ".wav"]
+            if wavs:
+                info, probed = _native.wav_probe([paths[k] for k in wavs], io_threads)
+                for j, k in enumerate(wavs):
+                    meta[k] = probed[j]
+        other = {k: load_audio(paths[k]) for k in range(len(w)) if meta[k] is None}
+        shapes = [(meta[k][0], meta[k][1]) if meta[k] is not None else tuple(other[k][0].shape) for k in range(len(w))]
+        rates = [meta[k][2] if meta[k] is not None else other[k][1] for k in range(len(w))]
+        offs = [0]
+        for c, n in shapes:
+            offs.append(offs[-1] + c * n)
+        total = offs[-1]
         slot = wi % 3
         buf, ev = stage.get(slot, (None, None))
         if ev is not None:
             ev.synchronize()
         if buf is None or buf.numel() < total:
-            buf = torch.empty(max(total, 1), dtype=torch.float32).pin_memory()
-        off, spans = 0, []
-        for fi, a, fs in loaded:
-            n = a.numel()
-            buf[off : off + n].copy_(a.reshape(-1))
-            spans.append((fi, fs, off, tuple(a.shape)))
-            off += n
+            buf = torch.empty(max(total, 1), dtype=torch.float32)
+            if use_cuda:
+                buf = buf.pin_memory()
+        if info is not None:
+            ok = _native.wav_read([paths[k] for k in wavs], info, [offs[k] for k in wavs], buf, io_threads)
+            for j, k in enumerate(wavs):
+                if meta[k] is not None and not ok[j]:
+                    raise RuntimeError(f"{paths[k]}: read error")
+        for k, (a, _) in other.items():
+            buf[offs[k] : offs[k + 1]].copy_(a.reshape(-1))
+        if not use_cuda:
+            stage[slot] = (None, None)   # the views below alias the buffer: a fresh one per window
+            return [(fi, buf[offs[k] : offs[k + 1]].view(shapes[k]), rates[k]) for k, fi in enumerate(w)], None
         with torch.cuda.device(device), torch.cuda.stream(copy_stream):
             dev = torch.empty(max(total, 1), dtype=torch.float32, device=device)
             dev[:total].copy_(buf[:total], non_blocking=True)
             ev = torch.cuda.Event()
             ev.record(copy_stream)
         stage[slot] = (buf, ev)
-        return [(fi, dev[o : o + shape[0] * shape[1]].view(shape), fs) for fi, fs, o, shape in spans], (dev, ev)
+        return [(fi, dev[offs[k] : offs[k + 1]].view(shapes[k]), rates[k]) for k, fi in enumerate(w)], (dev, ev)
 
-    def write_file(path, enh, fs):
-        Path(path).parent.mkdir(exist_ok=True, parents=True)
-        save_audio(path, enh.cpu(), fs)   # the device-to-host copy waits for this file's batches only (stream order)
+    def write_window(items, flat, ev):
+        """items: [(path, (channels, frames), fs, offset)] into the flat host tensor `flat` (valid once ev is done)."""
+        if ev is not None:
+            ev.synchronize()
+        for d in {Path(p).parent for p, _, _, _ in items}:
+            d.mkdir(exist_ok=True, parents=True)
+        wavs = [it for it in items if native_io and Path(it[0]).suffix.lower() == ".wav"]
+        if wavs:
+            ok = _native.wav_write([it[0] for it in wavs], [it[1] for it in wavs], [it[2] for it in wavs], [it[3] for it in wavs],
+                                   flat, io_threads)
+            if not all(ok):
+                raise RuntimeError(f"{wavs[ok.index(False)][0]}: write error")
+        for path, shape, fs, off in items:
+            if not (native_io and Path(path).suffix.lower() == ".wav"):
+                save_audio(path, flat[off : off + shape[0] * shape[1]].view(shape).clone(), fs)
 
     if progress:
         from tqdm import tqdm
@@ -232,16 +267,46 @@ def enhance_files(model, files, out_paths, enhance_kwargs, batch_size=64, device
             by_file = {}
             for i, (fi, c, _) in enumerate(utts):
                 by_file.setdefault(fi, []).append(i)
-            for fi, idx in by_file.items():
-                enh = resample(torch.stack([done[i] for i in idx]), model.fs, fs_of[fi])
-                pending.append(writer.submit(write_file, out_paths[fi], enh, fs_of[fi]))
+            # the window's results go down as ONE copy into a pinned buffer on a copy stream; a writer thread encodes
+            # the files from it (native batch writer for WAV) once the copy has landed
+            enh = {fi: resample(torch.stack([done[i] for i in idx]), model.fs, fs_of[fi]) for fi, idx in by_file.items()}
+            items, off = [], 0
+            for fi, e in enh.items():
+                items.append((str(out_paths[fi]), tuple(e.shape), fs_of[fi], off))
+                off += e.numel()
+            if items:
+                flat_dev = torch.cat([e.reshape(-1).float() for e in enh.values()])
+                slot = wi % 3
+                hbuf, fut = out_stage.get(slot, (None, None))
+                if fut is not None:
+                    fut.result()
+                if hbuf is None or hbuf.numel() < off:
+                    hbuf = torch.empty(max(off, 1), dtype=torch.float32)
+                    if use_cuda:
+                        hbuf = hbuf.pin_memory()
+                ev = None
+                if use_cuda:
+                    main = torch.cuda.current_stream(device)
+                    ready = torch.cuda.Event()
+                    ready.record(main)
+                    with torch.cuda.stream(down_stream):
+                        down_stream.wait_event(ready)
+                        hbuf[:off].copy_(flat_dev, non_blocking=True)
+                        ev = torch.cuda.Event()
+                        ev.record(down_stream)
+                    flat_dev.record_stream(down_stream)
+                else:
+                    hbuf[:off].copy_(flat_dev)
+                fut = writer.submit(write_window, items, hbuf, ev)
+                out_stage[slot] = (hbuf, fut)
+                pending.append(fut)
             stats["files"] += len(by_file)
             stats["utterances"] += len(done)
             stats["batches"] += len(batches)
             if progress:
                 bar.update(len(by_file))
-            # bound what is in flight: at most the previous window's files may still be waiting for their writer
-            while len(pending) > 2 * window:
+            # bound what is in flight: at most the previous windows may still be waiting for their writer
+            while len(pending) > 2:
                 pending.pop(0).result()
     for f in pending:
         f.result()

@@ -15,6 +15,7 @@
 #include "small_ops.cuh"
 #include "aux_ops.cuh"
 #include "hp_ops.cuh"
+#include "wav_io.cuh"
 
 using namespace uv;
 

@@ -259,3 +259,62 @@ def test_cli_ragged_corpus_equals_direct_ragged_calls(tmp_path):
             worst = max(worst, (got - ref[k, : lens[i]]).abs().max().item())
             assert ref[k, lens[i]:].abs().max() == 0 if lens[i] < T else True
     assert worst < 1e-6, worst
+
+
+def test_native_batch_wav_io_matches_the_python_path(tmp_path):
+    """uv_wav_probe / uv_wav_read / uv_wav_write (csrc/wav_io.cuh) against scipy + load_audio: int16 / int32 / uint8 /
+    float32, mono and stereo, odd chunk sizes; unsupported files are reported, not mangled."""
+    import numpy as np
+    from scipy.io import wavfile
+
+    from open_universe_b200 import _native
+    from open_universe_b200.bin import enhance as cli
+
+    g = np.random.default_rng(0)
+    specs = [("f32m", np.float32, 1, 4001), ("f32s", np.float32, 2, 3000), ("i16m", np.int16, 1, 70001), ("i16s", np.int16, 2, 5),
+             ("i32m", np.int32, 1, 777), ("u8s", np.uint8, 3, 1234)]
+    paths = []
+    for name, dt, ch, n in specs:
+        x = g.uniform(-0.9, 0.9, size=(n, ch))
+        if dt == np.int16:
+            d = (x * 32767).astype(np.int16)
+        elif dt == np.int32:
+            d = (x * 2147483647).astype(np.int32)
+        elif dt == np.uint8:
+            d = (x * 127 + 128).astype(np.uint8)
+        else:
+            d = x.astype(np.float32)
+        p = tmp_path / f"{name}.wav"
+        wavfile.write(str(p), 16000 + 1000 * ch, d[:, 0] if ch == 1 else d)
+        paths.append(p)
+    bad = tmp_path / "bad.wav"
+    bad.write_bytes(b"RIFFxxxxWAVEjunk")
+    f64 = tmp_path / "f64.wav"
+    wavfile.write(str(f64), 8000, g.uniform(-1, 1, 100))   # float64: not decoded natively
+    info, probed = _native.wav_probe(paths + [bad, f64], 3)
+    assert probed[-1] is None and probed[-2] is None
+    assert [p[:2] for p in probed[:-2]] == [(ch, n) for _, _, ch, n in specs]
+    offs = [0]
+    for ch, n, _ in probed[:-2]:
+        offs.append(offs[-1] + ch * n)
+    buf = torch.full((offs[-1] + 7,), 9.0)
+    ok = _native.wav_read(paths + [bad, f64], info, offs[:-1] + [offs[-1], offs[-1]], buf, 3)
+    assert ok[: len(specs)] == [True] * len(specs) and ok[-2:] == [False, False]
+    assert (buf[offs[-1]:] == 9.0).all()
+    cli._TORCHAUDIO_IO["load"] = None
+    for k, p in enumerate(paths):
+        ref, fs = cli.load_audio(p)
+        got = buf[offs[k] : offs[k + 1]].view(ref.shape)
+        assert fs == probed[k][2] and torch.equal(got, ref), p
+    # write: planar [C][n] out of one flat buffer -> files scipy reads back bit-exactly
+    outs = [tmp_path / "o" / f"{name}.wav" for name, *_ in specs]
+    (tmp_path / "o").mkdir()
+    shapes = [(ch, n) for _, _, ch, n in specs]
+    okw = _native.wav_write(outs, shapes, [p[2] for p in probed[:-2]], offs[:-1], buf, 2)
+    assert all(okw)
+    for k, o in enumerate(outs):
+        fs, d = wavfile.read(str(o))
+        assert d.dtype == np.float32 and fs == probed[k][2]
+        d = d[:, None] if d.ndim == 1 else d
+        assert np.array_equal(d.T, buf[offs[k] : offs[k + 1]].view(shapes[k]).numpy())
+    assert _native.wav_write([tmp_path / "nodir" / "x.wav"], [(1, 4)], [8000], [0], buf, 1) == [False]
