@@ -222,7 +222,7 @@ __device__ __forceinline__ void split_bf16x8(const float* x, uint4& hi, uint4& l
 }
 
 template <int KJ>   // channel chunks per K group (KC = 8 KJ)
-__global__ void __launch_bounds__(kHtThreads, 3) gemm_hp_tc_kernel(const __grid_constant__ HpGemmParams P) {
+__global__ void __launch_bounds__(kHtThreads, 2) gemm_hp_tc_kernel(const __grid_constant__ HpGemmParams P) {
   extern __shared__ unsigned char ht_smem_raw[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int Q = P.n_shift, KC = 8 * KJ, NT = P.N_TILE;
@@ -398,7 +398,7 @@ inline cudaError_t gemm_hp_tc_launch(const HpGemmParams& P, cudaStream_t s) {
 }
 
 // ---------------------------------------------------------------- GRU recurrence
-constexpr int kHpGruNB = 8;   // utterances per CTA (the W_hh stream of a step is amortised over them; measured: 4 per CTA ran at the same 12.7 us per step with twice the CTAs)
+constexpr int kHpGruNB = 4;   // utterances per CTA (measured on cfg 2: 92 ms of GRU time per pass with 4, 132 ms with 8)
 
 struct HpGruParams {
   const float* gi;     // f32 row-major [b Lh + t][6H]: x W_ih^T + b_ih, columns dir * 3H + gate * H + u
@@ -425,7 +425,7 @@ __host__ __device__ inline size_t hp_gru_smem(int H) {
   return (size_t)hp_gru_stages(H) * hp_gru_kch(H) * 3 * H * 4 + 2 * (size_t)H * kHpGruNB * 4 + 128;
 }
 
-// grid (ceil(B / 8), 2 directions); H compute threads + one producer warp.  Thread u owns hidden unit u of 8
+// grid (ceil(B / 4), 2 directions); H compute threads + one producer warp.  Thread u owns hidden unit u of 4
 // utterances (state in shared memory as h[k][utterance], two buffers).  The recurrence needs all of W_hh (3H x H
 // f32: 0.75 - 1.7 MB per direction) at every step: one thread streams it from L2 through a shared-memory ring with bulk
 // copies ([k][gate][u] rows, so consecutive threads read consecutive words), which keeps ~100 KB in flight per SM --
@@ -437,7 +437,7 @@ __global__ void __launch_bounds__(416) gru_hp_kernel(const __grid_constant__ HpG
   const int n_chunks = H / KCH;
   const uint32_t stage_bytes = (uint32_t)(KCH * 3 * H * 4);
   float* ring = reinterpret_cast<float*>(gru_hp_smem);
-  float* hs = ring + (size_t)NS * KCH * 3 * H;                       // [2][H][8]
+  float* hs = ring + (size_t)NS * KCH * 3 * H;                       // [2][H][4]
   uint64_t* full = reinterpret_cast<uint64_t*>(hs + 2 * H * kHpGruNB);   // [NS] | empty [NS]
   uint64_t* empty = full + NS;
   const int b0 = blockIdx.x * kHpGruNB;
@@ -497,8 +497,7 @@ __global__ void __launch_bounds__(416) gru_hp_kernel(const __grid_constant__ HpG
       for (int kk = 0; kk < KCH; ++kk) {
         const float wr = ws[kk * 3 * H], wz = ws[kk * 3 * H + H], wn = ws[kk * 3 * H + 2 * H];
         const float4 h4 = *reinterpret_cast<const float4*>(hk + kk * kHpGruNB);
-        const float4 h5 = *reinterpret_cast<const float4*>(hk + kk * kHpGruNB + 4);
-        const float hv[8] = {h4.x, h4.y, h4.z, h4.w, h5.x, h5.y, h5.z, h5.w};
+        const float hv[4] = {h4.x, h4.y, h4.z, h4.w};
 #pragma unroll
         for (int b = 0; b < kHpGruNB; ++b) {
           ar[b] = fmaf(wr, hv[b], ar[b]);
