@@ -10,7 +10,7 @@ import torch
 import yaml
 from scipy.io import wavfile
 
-from conftest import build_model
+from conftest import GOLDEN, build_model
 from open_universe_b200 import sharding
 from open_universe_b200.bin import enhance as cli
 
@@ -318,3 +318,93 @@ def test_native_batch_wav_io_matches_the_python_path(tmp_path):
         d = d[:, None] if d.ndim == 1 else d
         assert np.array_equal(d.T, buf[offs[k] : offs[k + 1]].view(shapes[k]).numpy())
     assert _native.wav_write([tmp_path / "nodir" / "x.wav"], [(1, 4)], [8000], [0], buf, 1) == [False]
+
+
+# ---------------------------------------------------------------- the reference's own file flow (oracle/gen_golden_cli.py)
+def _flow_fixture():
+    return torch.load(os.path.join(GOLDEN, "cli_flow.pt"), weights_only=False)
+
+
+def test_oracle_reproduces_the_reference_file_flow():
+    """load -> resample -> enhance -> resample of the REAL reference on three files (mono / stereo / 22.05 kHz),
+    recorded by oracle/gen_golden_cli.py, against the CPU oracle run through the same steps (bin/enhance.py:77-80,183-190)."""
+    from open_universe_b200.bin import enhance as cli
+    from oracle import universe_oracle as uo
+
+    fix = _flow_fixture()
+    model, cfg = build_model(fix["model"], fix["seed_weights"])
+    sd = {k: v.detach().cpu() for k, v in model.state_dict().items()}
+    for f in fix["files"]:
+        x = cli.resample(f["audio"], f["fs"], model.fs)
+        assert x.shape[-1] == f["model_rate_len"]
+        enh = uo.enhance(sd, cfg.model, x, [z[:, None, :] for z in f["noise"]])
+        out = cli.resample(enh, model.fs, f["fs"])
+        assert out.shape == f["out"].shape
+        assert uo.rel_l2(out, f["out"]) < 1e-5, f["name"]
+
+
+class _ReplayModel:
+    """Stand-in handed to enhance_files: forwards to the native model with the fixture's draws, matched to the rows of
+    whatever batch the schedule forms (the CLI draws its own noise per batch; the fixture's draws are per file)."""
+
+    def __init__(self, model, rows):
+        self.model, self.rows, self.fs, self.calls = model, rows, model.fs, 0
+
+    def parameters(self):
+        return self.model.parameters()
+
+    def enhance(self, x, lengths=None, **kw):
+        B, T = x.shape
+        lengths = list(lengths) if lengths is not None else [T] * B
+        td = self.model.tot_ds
+        Lp = T + (td - T % td)
+        n_steps = self.rows[0][1].shape[0]
+        noise = torch.zeros(n_steps, B, Lp)
+        for b in range(B):
+            head = x[b, :16].cpu()
+            k = min(range(len(self.rows)), key=lambda i: (self.rows[i][0][:16] - head).abs().sum().item())
+            z = self.rows[k][1]
+            assert z.shape[-1] == lengths[b] + (td - lengths[b] % td)
+            noise[:, b, : z.shape[-1]] = z
+        self.calls += 1
+        out, _ = self.model.enhance_debug(x, noise.to(x.device), lengths=None if all(v == T for v in lengths) else lengths)
+        return out
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("precision,tol", [("bf16", 1e-2), ("fp32", 1e-4)])
+def test_cli_reproduces_the_reference_file_flow(tmp_path, precision, tol):
+    """The three files of the reference-flow fixture as WAV files through enhance_files (native WAV IO, one ragged batch
+    with per-row lengths, resampling in and out) against what the reference's file-by-file loop produced."""
+    import numpy as np
+    from scipy.io import wavfile
+
+    from open_universe_b200.bin import enhance as cli
+    from oracle import universe_oracle as uo
+
+    fix = _flow_fixture()
+    model, cfg = build_model(fix["model"], fix["seed_weights"])
+    model = model.to("cuda").eval()
+    model.precision = precision
+    src, dst = tmp_path / "in", tmp_path / "out"
+    rows = []
+    for f in fix["files"]:
+        p = src / f["name"]
+        p.parent.mkdir(parents=True, exist_ok=True)
+        a = f["audio"].numpy().astype(np.float32)
+        wavfile.write(str(p), f["fs"], a[0] if a.shape[0] == 1 else np.ascontiguousarray(a.T))
+        x = cli.resample(f["audio"], f["fs"], model.fs)
+        for c in range(x.shape[0]):
+            rows.append((x[c], f["noise"][:, c]))
+    files, rel, is_dir = cli.find_files(src)
+    outs = [cli.output_path_for(p, rel, is_dir, dst) for p in files]
+    proxy = _ReplayModel(model, rows)
+    st = cli.enhance_files(proxy, files, outs, {}, batch_size=8, device="cuda:0")
+    assert st["files"] == 3 and st["utterances"] == 4 and proxy.calls == st["batches"]
+    for f in fix["files"]:
+        fs, d = wavfile.read(str(dst / f["name"]))
+        got = torch.from_numpy(np.ascontiguousarray((d[:, None] if d.ndim == 1 else d).T))
+        assert fs == f["fs"] and got.shape == f["out"].shape
+        err, sdr = uo.rel_l2(got, f["out"]), uo.si_sdr(got, f["out"]).min().item()
+        print(f"{precision} CLI vs reference file flow, {f['name']}: rel-L2 {err:.2e}, SI-SDR {sdr:.1f} dB")
+        assert err < tol and sdr > 40.0, f["name"]

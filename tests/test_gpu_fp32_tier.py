@@ -137,3 +137,24 @@ def test_precision_switch_keeps_both_tiers():
     model.precision = "tf64"
     with pytest.raises(ValueError):
         model.enhance_debug(mix, noise)
+
+
+def test_fp32_config_length_24k_matches_cpu_oracle():
+    """BASELINE configs[3] length at reduced batch: UNIVERSE++ 24 kHz, 1 x 10 s = 1001 GRU steps of the H = 384
+    recurrence, 48-channel levels (16-channel K groups of the split GEMM)."""
+    model, cfg = _gpu_model("universepp_24k")
+    B, T = 1, 240000
+    g = torch.Generator().manual_seed(T + B)
+    mix = 0.05 * torch.randn(B, T, generator=g) + 0.003
+    Lp = T + (model.tot_ds - T % model.tot_ds)
+    noise = torch.randn(8, B, Lp, generator=g)
+    out, steps = model.enhance_debug(mix.cuda(), noise.cuda())
+    out, steps = out.cpu(), steps.cpu()
+    model._invalidate()
+    torch.cuda.empty_cache()
+    sd = {k: v.detach().cpu() for k, v in model.state_dict().items()}
+    ref, ref_steps = uo.enhance(sd, cfg.model, mix, [n[:, None, :] for n in noise], return_steps=True)
+    e_steps = max(uo.rel_l2(steps[i], ref_steps[i][:, 0]) for i in range(8))
+    e_out, sisdr = uo.rel_l2(out, ref), uo.si_sdr(out, ref).min().item()
+    print(f"fp32 tier, 24 kHz 1 x 10 s (1001 GRU steps): worst per-step rel-L2 {e_steps:.2e}, final {e_out:.2e}, SI-SDR {sisdr:.1f} dB")
+    assert e_steps < TOL and e_out < TOL and sisdr > SISDR_MIN
