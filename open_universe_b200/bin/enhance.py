@@ -334,6 +334,8 @@ def main(argv=None):
     parser.add_argument("--equal-length-batches", action="store_true", help="Only batch utterances of identical length")
     parser.add_argument("--window", type=int, default=None, help="Files decoded ahead and batched together (default: max(64, batch size))")
     parser.add_argument("--io-threads", type=int, default=4, help="Decoder threads")
+    parser.add_argument("--precision", type=str, default=None, choices=["bf16", "fp32"],
+                        help="bf16 (default): tensor-core tier, rel-L2 <= 1e-2 against the reference; fp32: parity tier, <= 1e-4, ~4.5x slower")
     requires_help = handle_help()
     args, _ = parser.parse_known_args()
 
@@ -348,6 +350,8 @@ def main(argv=None):
         raise RuntimeError("no CUDA device: open_universe_b200 has no CPU fallback")
 
     model = inference_utils.load_model(args.model, device=device, strict=args.model_strict, hf_token=args.hf_token)
+    if args.precision is not None:
+        model.precision = args.precision
     rng = torch.Generator(device=device)
     rng.manual_seed(args.seed + rank)
     inference_utils.add_enhance_arguments(model, parser)

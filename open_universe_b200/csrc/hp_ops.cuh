@@ -232,7 +232,7 @@ __global__ void __launch_bounds__(kHtThreads, 2) gemm_hp_tc_kernel(const __grid_
   const int slab_rows = ht_slab_rows(Q);
   const uint32_t a_half = (uint32_t)(KJ * slab_rows * 16), a_stage = 2 * a_half;
   const uint32_t b_half = (uint32_t)(KC * NT * 2), b_stage = 2 * b_half;
-  unsigned char* sm = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(ht_smem_raw) + 127) & ~(uintptr_t)127);
+  unsigned char* sm = ht_smem_raw + ((128u - (smem_u32(ht_smem_raw) & 127u)) & 127u);   // (an offset, not an integer cast: the stores below stay STS)
   unsigned char* a_s = sm;
   unsigned char* b_s = sm + 2 * a_stage;
   uint64_t* bars = reinterpret_cast<uint64_t*>(b_s + kHtBStages * b_stage);
