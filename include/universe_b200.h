@@ -83,11 +83,18 @@ typedef enum {
                         * (i0 bit s: conv s has a bias; i1 byte s: n_src | n_shift << 4 of conv s), add1 = condition,
                         * film (C = its channel count), f1 / f2 = slopes in front of conv2 / conv3, out[0..n_out) = block
                         * outputs, i2 = 1: out[2] is the stage-1 output (the conditioner's conditioning signal)          */
-  UV_OP_AUX = 12       /* aux_to_wav fused with the state initialisation of use_aux_signal / warm_start (universe_gan.py:
+  UV_OP_AUX = 12,      /* aux_to_wav fused with the state initialisation of use_aux_signal / warm_start (universe_gan.py:
                         * 119-128,147-151; bigvgan/alias_free_act.py:8-30, snake.py:53-64; universe.py:317-331):
                         * a = y_hat (bf16 planes, C channels), p0 = x [B][Lp], p3 = weights f32 (alpha or slope [C] |
                         * up kernel [2][H] | down kernel [F] | conv [C][3] | bias), i3 = 0 snake / 1 PReLU, f0 = sigma_n
                         * (0: x = aux_to_wav(y_hat)), i0 = n (the draw added: x += sigma_n z_n), i1 / i2 as INIT_X   */
+  UV_OP_SIGP = 13,     /* padded signal p0 f32 [B][Lp] -> out[0]: f32 planes tensor in rows of C = hop / 2 samples, phase-split by 2
+                        * (row m of phase s = samples [(2m + s) C, (2m + s + 1) C)), F frames: the A operand of the framed DFT of
+                        * the mel front end run as ONE multi-tap GEMM on the tensor cores (condition.py:92-108; a UV_OP_GEMM on
+                        * f32 planes with a row-major output, see the fp32 notes below) */
+  UV_OP_MEL_POW = 14   /* p0 = that GEMM's output f32 [b Lh_A + f][i2] (cos bins at column 0, sin bins at column i1, i0 bins)
+                        * -> power spectrum -> mel filterbank p4 (f32 [i0][C]) -> p1 / p2 as UV_OP_MEL (raw mel bands, partial
+                        * energy sums per T frames) */
 } uv_op_type;
 
 /* One record per kernel launch.  Offsets named *_w index the model's weight

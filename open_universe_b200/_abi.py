@@ -4,10 +4,10 @@ import ctypes as C
 
 UV_ABI_VERSION = 10
 
-OP_PREP, OP_MEL, OP_MEL_FIN, OP_CONV_IN, OP_GEMM, OP_GRU, OP_CONV_OUT, OP_INIT_X, OP_POST, OP_FILM, OP_CONVBLOCK, OP_AUX = range(1, 13)
+OP_PREP, OP_MEL, OP_MEL_FIN, OP_CONV_IN, OP_GEMM, OP_GRU, OP_CONV_OUT, OP_INIT_X, OP_POST, OP_FILM, OP_CONVBLOCK, OP_AUX, OP_SIGP, OP_MEL_POW = range(1, 15)
 OP_NAMES = {
     1: "PREP", 2: "MEL", 3: "MEL_FIN", 4: "CONV_IN", 5: "GEMM", 6: "GRU", 7: "CONV_OUT", 8: "INIT_X", 9: "POST", 10: "FILM",
-    11: "CONVBLOCK", 12: "AUX",
+    11: "CONVBLOCK", 12: "AUX", 13: "SIGP", 14: "MEL_POW",
 }
 
 DT_BF16, DT_F32 = 1, 2

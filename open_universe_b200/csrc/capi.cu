@@ -113,6 +113,7 @@ extern "C" int uv_model_create(uv_model** out, const void* weights, size_t nbyte
   CUDA_TRY(cudaFuncSetAttribute(aux_to_wav_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   CUDA_TRY(cudaFuncSetAttribute(gru_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   CUDA_TRY(cudaFuncSetAttribute(mel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMelMaxSmem));
+  CUDA_TRY(cudaFuncSetAttribute(mel_pow_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMelMaxSmem));
   char* blob = nullptr;
   CUDA_TRY(cudaMalloc(&blob, nbytes));
   cudaError_t e = cudaMemcpy(blob, weights, nbytes, cudaMemcpyHostToDevice);
@@ -308,6 +309,26 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
       CUDA_TRY(launch_pdl(mel_kernel, dim3(nft, op.B), dim3(threads), sm, s, aptr<const float>(p, op.p0), op.Lp, op.F, op.i0, op.i1, op.i2, op.H, op.C,
                                                       op.i3, wptr<const float>(p, op.p3), wptr<const float>(p, op.p4),
                                                       aptr<float>(p, op.p1), aptr<float>(p, op.p2), nft, rowgeo(p, op)));
+      break;
+    }
+    case UV_OP_SIGP: {
+      const OutDesc o = to_out(p, op.out[0]);
+      if (op.C % 8 || !o.t.base || o.t.split != 2 || o.t.nchunks * 8 < op.C || op.Lp < 2 * op.F * op.C)
+        return fail(UV_ERR_INVALID, "SIGP: needs half-hop rows of a multiple of 8 samples and a phase-split-by-2 output");
+      const int items = 2 * op.F * (op.C / 8);
+      CUDA_TRY(launch_pdl(sig_planes_kernel, dim3((items + 255) / 256, op.B), dim3(256), 0, s, aptr<const float>(p, op.p0), op.Lp, op.F, op.C, o,
+                          rowgeo(p, op)));
+      break;
+    }
+    case UV_OP_MEL_POW: {
+      if (op.T != kMelFT) return fail(UV_ERR_INVALID, "MEL_POW op built for another frame tile than the kernel's");
+      const int nft = (op.F + kMelFT - 1) / kMelFT;
+      const int threads = std::max(2 * (((op.i0 + 1) / 2 + 31) / 32 * 32), (op.C + 31) / 32 * 32);   // as the MEL op (same filterbank stage)
+      const size_t sm = mel_pow_smem_bytes(op.i0, op.C);
+      if (threads > 512 || sm > (size_t)kMelMaxSmem || op.C > threads || op.i1 < op.i0 || op.i2 < op.i1 + op.i0)
+        return fail(UV_ERR_INVALID, "MEL_POW: bins / bands unsupported");
+      CUDA_TRY(launch_pdl(mel_pow_kernel, dim3(nft, op.B), dim3(threads), sm, s, aptr<const float>(p, op.p0), op.i2, op.Lh_A, op.F, op.i0, op.i1, op.C,
+                          wptr<const float>(p, op.p4), aptr<float>(p, op.p1), aptr<float>(p, op.p2), nft, rowgeo(p, op)));
       break;
     }
     case UV_OP_MEL_FIN: {

@@ -299,6 +299,107 @@ __global__ void __launch_bounds__(512) mel_kernel(const float* __restrict__ sig,
   if (threadIdx.x == 0) energy[(size_t)b * nft + blockIdx.x] = (float)e;
 }
 
+// ---------------------------------------------------------------- mel front end around the tensor-core DFT
+// The framed DFT is one multi-tap GEMM (weights.w4_dft, run by gemm_hp_tc_kernel: split-bf16 products, fp32
+// accumulation) on the padded signal stored as f32 planes in rows of hop / 2 samples, phase-split by 2; its output is
+// f32 row-major [b Lh + f][ld] with the cos bins at column 0 and the sin bins at column nbq.
+// SIGP: sig [B][Lp] -> that planes tensor (thread = one 8-sample piece; reads are contiguous, writes 32-byte pieces).
+__global__ void __launch_bounds__(256) sig_planes_kernel(const float* __restrict__ sig, int Lp, int F, int half, OutDesc out,
+                                                         const RowGeo* __restrict__ rows) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int b = blockIdx.y, nch = half >> 3;
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;   // (half-hop h, chunk), chunk fastest = signal order
+  if (idx >= 2 * F * nch) return;
+  const int h = idx / nch, ch = idx - h * nch;
+  if (rows && h >= 2 * rows[b].F) return;   // past the row's own frames: the planes stay zero (as the signal is)
+  const float* src = sig + (size_t)b * Lp + (size_t)idx * 8;
+  const float4 a = *reinterpret_cast<const float4*>(src), c = *reinterpret_cast<const float4*>(src + 4);
+  const float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
+  store8(row_addr(out.t, b, h), out.t.esize_log2, ch, v);
+}
+
+// MEL_POW: power spectrum re^2 + im^2 of 32 frames -> shared memory [bin][frame] -> mel filterbank (the second half of
+// mel_kernel, same thread mapping) -> melraw [B][F][n_mels] and the partial energy sums mel_fin_kernel reduces.
+__host__ __device__ inline size_t mel_pow_smem_bytes(int nb, int n_mels) {
+  return ((size_t)nb * kMelPwPitch + 2 * (size_t)kMelFbRows * n_mels) * sizeof(float);
+}
+__global__ void __launch_bounds__(512) mel_pow_kernel(const float* __restrict__ D, int ld, int Lh, int F, int nb, int nbq,
+                                                      int n_mels, const float* __restrict__ fb, float* __restrict__ melraw,
+                                                      float* __restrict__ energy, int nft, const RowGeo* __restrict__ rows) {
+  pdl_launch_dependents();
+  pdl_wait();
+  extern __shared__ float smem_f[];
+  float* pw = smem_f;                                   // [nb][kMelPwPitch]
+  float* fbs = smem_f + (size_t)nb * kMelPwPitch;        // [2][kMelFbRows][n_mels]
+  __shared__ double sh[96];
+  const int b = blockIdx.y, f0 = blockIdx.x * kMelFT;
+  const int Fb = rows ? rows[b].F : F;
+  for (int e = threadIdx.x; e < kMelFT * nb; e += blockDim.x) {
+    const int f = e / nb, k = e - f * nb;
+    float p = 0.f;
+    if (f0 + f < Fb) {   // (rows of frames past the utterance's length are never written by the GEMM)
+      const float* row = D + ((size_t)b * Lh + f0 + f) * ld;
+      const float re = row[k], im = row[nbq + k];
+      p = re * re + im * im;
+    }
+    pw[(size_t)k * kMelPwPitch + f] = p;
+  }
+  double e = 0, d1 = 0, d2 = 0;
+  int ng = blockDim.x / n_mels;
+  ng = ng >= 4 ? 4 : (ng >= 2 ? 2 : 1);
+  const int fpt = kMelFT / ng;   // frames per thread: 8, 16 or 32
+  const int tpg = blockDim.x / ng;                 // threads per frame group
+  const int g = threadIdx.x / tpg, m = threadIdx.x % tpg;
+  const bool active = g < ng && m < n_mels;        // (n_mels <= tpg is checked by the host)
+  float acc[kMelFT];
+#pragma unroll
+  for (int f = 0; f < kMelFT; ++f) acc[f] = 0.f;
+  const int chunk = kMelFbRows * n_mels;
+  const int n_chunks = (nb + kMelFbRows - 1) / kMelFbRows;
+  auto load_chunk = [&](int ci, float* dst) {
+    const int k0 = ci * kMelFbRows;
+    const int cnt = (nb - k0 < kMelFbRows ? nb - k0 : kMelFbRows) * n_mels;
+    for (int i = threadIdx.x; i < cnt; i += blockDim.x) dst[i] = fb[(size_t)k0 * n_mels + i];
+  };
+  load_chunk(0, fbs);
+  __syncthreads();
+  for (int ci = 0; ci < n_chunks; ++ci) {
+    float* cur = fbs + (ci & 1) * chunk;
+    if (ci + 1 < n_chunks) load_chunk(ci + 1, fbs + ((ci + 1) & 1) * chunk);
+    if (active) {
+      const int k0 = ci * kMelFbRows;
+      const int kn = nb - k0 < kMelFbRows ? nb - k0 : kMelFbRows;
+      const float* prow = pw + (size_t)k0 * kMelPwPitch + g * fpt;
+      for (int kk = 0; kk < kn; ++kk) {
+        const float w = cur[kk * n_mels + m];
+#pragma unroll
+        for (int f = 0; f < kMelFT; f += 4) {
+          if (f < fpt) {
+            const float4 v = *reinterpret_cast<const float4*>(prow + (size_t)kk * kMelPwPitch + f);
+            acc[f] = fmaf(v.x, w, acc[f]); acc[f + 1] = fmaf(v.y, w, acc[f + 1]);
+            acc[f + 2] = fmaf(v.z, w, acc[f + 2]); acc[f + 3] = fmaf(v.w, w, acc[f + 3]);
+          }
+        }
+      }
+    }
+    __syncthreads();
+  }
+  if (active) {
+#pragma unroll
+    for (int f = 0; f < kMelFT; ++f) {
+      const int fr = f0 + g * fpt + f;
+      if (f < fpt && fr < F) {
+        const float a = fr < Fb ? acc[f] : 0.f;   // frames past the row's own length do not exist
+        melraw[((size_t)b * F + fr) * n_mels + m] = a;
+        e += (double)a * a;
+      }
+    }
+  }
+  block_sum3(e, d1, d2, sh);
+  if (threadIdx.x == 0) energy[(size_t)b * nft + blockIdx.x] = (float)e;
+}
+
 // Global mel normalisation (condition.py:105-106): x / clamp(sqrt(mean_t sum_m x^2), 1e-5) -> bf16 planes.
 __global__ void __launch_bounds__(256) mel_fin_kernel(const float* __restrict__ melraw, const float* __restrict__ energy,
                                                       int F, int n_mels, int nft, OutDesc out, const RowGeo* __restrict__ rows) {

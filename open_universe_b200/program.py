@@ -41,6 +41,9 @@ class Level:
 
 
 MEL_FT = 32   # frames per CTA of the mel kernel (csrc/small_ops.cuh kMelFT)
+# The framed DFT of the mel front end as a tensor-core GEMM (split-bf16, csrc/hp_ops.cuh) between two small kernels
+# (signal -> f32 planes in half-hop rows; power + mel filterbank) instead of the one CUDA-core kernel (UV_MEL_TC=0)
+MEL_TC = os.environ.get("UV_MEL_TC", "1") != "0"
 # A tensor that is consumed both raw (residual / skip) and through a PReLU (the next conv) is written ONCE, raw; the
 # consuming GEMM activates it in shared memory (csrc/gemm_tc.cuh, a_act).  UV_RAW_A=0 restores the two-copy scheme.
 RAW_A = os.environ.get("UV_RAW_A", "1") != "0"
@@ -168,7 +171,7 @@ class Program:
         op.rm_ld = ly["N_total"]
         if a_slope is not None:   # `a` is a raw tensor: PReLU(a_slope) is applied inside the kernel
             op.a_act, op.a_slope = 1, a_slope
-        if self.hp:               # fp32 tier: f32 [S][Q][C_in][N_total] image of the same GEMM (csrc/hp_ops.cuh)
+        if a.dtype == DT_F32:     # fp32 operands: f32 [S][Q][C_in][N_total] image of the same GEMM (csrc/hp_ops.cuh)
             op.p5 = ly["w_hp"]
             op.p4, op.i0, op.i2 = ly["w_tc"], ly["tc_KC"], ly["tc_NT"]   # split-bf16 images, K group, N tile (tensor-core variant)
         return self.emit(op, name)
@@ -395,7 +398,7 @@ def default_lanes(B, aux=False):
 PRECISIONS = ("bf16", "fp32")
 
 
-def build_program(pm, cfg, B, T, n_steps, aux=False, lanes=None, recycle=None, precision="bf16"):
+def build_program(pm, cfg, B, T, n_steps, aux=False, lanes=None, recycle=None, precision="bf16", mel_tc=None):
     """Program of one enhance() call.  precision = "fp32": the parity tier of north_star (rel-L2 <= 1e-4): same
     topology, every activation stored in f32 planes, dense layers and recurrences run by the fp32 kernels of
     csrc/hp_ops.cuh from the fp32 weight images (pm packed with hp=True), no fused ConvBlocks.  lanes = 2 splits the utterances into two independent halves whose op
@@ -414,11 +417,12 @@ def build_program(pm, cfg, B, T, n_steps, aux=False, lanes=None, recycle=None, p
     if recycle is None:
         recycle = RECYCLE
     if lanes == 1 or B < 2:
-        return _finish_init(_build_lane(pm, cfg, B, T, n_steps, aux=aux, recycle=recycle, hp=hp))
+        return _finish_init(_build_lane(pm, cfg, B, T, n_steps, aux=aux, recycle=recycle, hp=hp, mel_tc=mel_tc))
     assert not aux, "aux-signal programs are single-lane (run_ops ranges address one op list)"
     B0 = (B + 1) // 2
-    pg0 = _build_lane(pm, cfg, B0, T, n_steps, b_off=0, B_total=B, recycle=recycle, hp=hp)
-    pg1 = _build_lane(pm, cfg, B - B0, T, n_steps, b_off=B0, B_total=B, arena_base=pg0.arena, lane=1, shared=pg0, recycle=recycle, hp=hp)
+    pg0 = _build_lane(pm, cfg, B0, T, n_steps, b_off=0, B_total=B, recycle=recycle, hp=hp, mel_tc=mel_tc)
+    pg1 = _build_lane(pm, cfg, B - B0, T, n_steps, b_off=B0, B_total=B, arena_base=pg0.arena, lane=1, shared=pg0, recycle=recycle, hp=hp,
+                      mel_tc=mel_tc)
     stagger = os.environ.get("UV_LANE_STAGGER", "c.enc3.rc")
     if stagger in pg0.names:
         pg0.ops[pg0.names.index(stagger)].sync |= 1
@@ -443,7 +447,8 @@ def _finish_init(pg):
     return pg
 
 
-def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_base=0, lane=0, shared=None, recycle=True, hp=False):
+def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_base=0, lane=0, shared=None, recycle=True, hp=False,
+                mel_tc=None):
     """aux=True also evaluates the tail of the conditioner decoder's last block (y_hat, the input of aux_to_wav:
     reference condition.py:264-270,362; universe.py:313-331), which the default path never uses.
     b_off / B_total: this lane's first utterance in / the size of the caller's batch (io tensors cover all lanes)."""
@@ -506,12 +511,31 @@ def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_
     # =========================================================== conditioner
     lb = lv[nlev]
     # mel front-end (condition.py:92-114)
-    op = new_op(_abi.OP_MEL)
-    op.B, op.Lp, op.F, op.C, op.T = B, Lp, Fr, mel["n_mels"], MEL_FT
-    op.i0, op.i1, op.i2, op.i3 = mel["n_fft"], mel["hop"], mel["n_bins"], (mel["n_fft"] - mel["hop"]) // 2
-    op.H = mel["nbp"]
-    op.p0, op.p1, op.p2, op.p3, op.p4 = pg.sig, pg.melraw, pg.mel_energy, mel["basis_w"], mel["fb_w"]
-    pg.emit(op, "c.mel")
+    use_tc = (MEL_TC if mel_tc is None else mel_tc) and "c.mel.dft" in L
+    if use_tc:
+        # signal -> f32 planes in rows of hop / 2 samples (phase-split by 2) -> framed DFT as ONE multi-tap GEMM on the
+        # tensor cores (weights.w4_dft) -> power spectrum + mel filterbank
+        dl = L["c.mel.dft"]
+        sigp = pg.tens("c.sigp", lb, mel["dft_cpad"], split=2, dtype=DT_F32)
+        op = new_op(_abi.OP_SIGP)
+        op.B, op.Lp, op.F, op.C, op.p0 = B, Lp, Fr, mel["half"], pg.sig
+        op.n_out = 1
+        op.out[0].t = sigp
+        pg.emit(op, "c.sigp")
+        pg.dft = pg.alloc(lb.rows * dl["N_total"] * 4)   # f32 row-major [b Lh + f][cos bins | sin bins]
+        pg.gemm("c.mel.dft", "c.mel.dft", sigp, lb, lb.L, [], rm_out=pg.dft, bias=False)
+        op = new_op(_abi.OP_MEL_POW)
+        op.B, op.F, op.C, op.T, op.Lh_A = B, Fr, mel["n_mels"], MEL_FT, lb.Lh
+        op.i0, op.i1, op.i2 = mel["n_bins"], mel["dft_nbq"], dl["N_total"]
+        op.p0, op.p1, op.p2, op.p4 = pg.dft, pg.melraw, pg.mel_energy, mel["fb_w"]
+        pg.emit(op, "c.mel.pow")
+    else:
+        op = new_op(_abi.OP_MEL)
+        op.B, op.Lp, op.F, op.C, op.T = B, Lp, Fr, mel["n_mels"], MEL_FT
+        op.i0, op.i1, op.i2, op.i3 = mel["n_fft"], mel["hop"], mel["n_bins"], (mel["n_fft"] - mel["hop"]) // 2
+        op.H = mel["nbp"]
+        op.p0, op.p1, op.p2, op.p3, op.p4 = pg.sig, pg.melraw, pg.mel_energy, mel["basis_w"], mel["fb_w"]
+        pg.emit(op, "c.mel")
     t_mel = pg.tens("c.mel", lb, mel["n_mels"])
     op = new_op(_abi.OP_MEL_FIN)
     op.B, op.F, op.C, op.i0, op.p0, op.p1 = B, Fr, mel["n_mels"], nft, pg.melraw, pg.mel_energy

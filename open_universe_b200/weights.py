@@ -249,6 +249,33 @@ def dft_basis(window, n_fft):
     return basis.float(), nb, nbp
 
 
+def w4_dft(basis, nb, nbp, n_fft, hop):
+    """The framed, windowed real DFT of the mel front end (condition.py:92-108) as a multi-tap GEMM on the padded signal
+    stored in rows of hop / 2 samples, phase-split by 2 (row m of phase s = samples [(2m + s) half, (2m + s + 1) half)):
+    frame f starts (n_fft - hop) / 2 samples in front of f hop, i.e. at half-hop 2f - (n_fft / hop - 1), and spans
+    2 n_fft / hop half-hops; half-hop 2(f + q) + s is source s at row shift q.  Columns: cos bins [0, nb) then, from
+    column nbq (bins padded to 64), sin bins.  -> (W4 [2 nbq, 2, n_shift, c_pad], smin, c_pad, nbq); rows / channels of
+    the padding are zero.  Run by the split-bf16 tensor-core GEMM of csrc/hp_ops.cuh (1e-5, far below the bf16
+    rounding of the mel planes)."""
+    half = hop // 2
+    assert hop % 2 == 0 and half % 8 == 0 and n_fft % half == 0 and ((n_fft - hop) // 2) % half == 0
+    c_pad = (half + 15) // 16 * 16
+    nbq = (nb + 63) // 64 * 64
+    j0 = -(((n_fft - hop) // 2) // half)
+    taps = []
+    for j in range(n_fft // half):
+        hh = j0 + j
+        s = hh % 2
+        taps.append((j, s, (hh - s) // 2))
+    smin, smax = min(q for _, _, q in taps), max(q for _, _, q in taps)
+    w4 = torch.zeros(2 * nbq, 2, smax - smin + 1, c_pad)
+    for j, s, q in taps:
+        rows = basis[j * half : (j + 1) * half]          # [half, 2 nbp]
+        w4[:nb, s, q - smin, :half] = rows[:, :nb].t()
+        w4[nbq : nbq + nb, s, q - smin, :half] = rows[:, nbp : nbp + nb].t()
+    return w4, smin, c_pad, nbq
+
+
 class PackedModel:
     def __init__(self, hp=False):
         self.blob = Blob()
@@ -426,6 +453,14 @@ def pack_model(sd, cfg, hp=False):
     fb = sd[cp + ".input_mel.mel_spec.mel_scale.fb"].float()
     pm.layers["c.mel"] = dict(basis_w=pm.blob.add_f32(basis), fb_w=pm.blob.add_f32(fb), n_fft=n_fft, hop=tot_ds,
                               n_bins=nb, nbp=nbp, n_mels=fb.shape[1])
+    # the same DFT as a tensor-core GEMM (csrc/hp_ops.cuh gemm_hp_tc_kernel; program.py MEL_TC): always with its fp32 /
+    # split-bf16 images, whatever the tier of the rest of the model
+    if tot_ds % 16 == 0:
+        w4d, smin_d, c_pad, nbq = w4_dft(basis, nb, nbp, n_fft, tot_ds)
+        was_hp, pm.hp = pm.hp, True
+        pm.add_gemm("c.mel.dft", w4d, smin_d, w4d.shape[0])
+        pm.hp = was_hp
+        pm.layers["c.mel"].update(dft_cpad=c_pad, dft_nbq=nbq, half=tot_ds // 2)
     w4, smin = w4_plain(eff_weight(sd, cp + ".input_mel.conv"))
     pm.add_gemm("c.mel.conv", w4, smin, w4.shape[0], bias=sd[cp + ".input_mel.conv.bias"])
     pm.add_conv_block(sd, cp + ".input_mel.conv_block", "c.melblk")

@@ -46,7 +46,9 @@ def op_outputs(op):
             tens("cond", op.out[2].t)
     elif t == _abi.OP_PREP:
         outs += [("sig", op.p0, op.B * op.Lp * 4, torch.float32), ("rms", op.p1, op.B * 4, torch.float32)]
-    elif t == _abi.OP_MEL:
+    elif t == _abi.OP_SIGP:
+        tens("out0", op.out[0].t)
+    elif t in (_abi.OP_MEL, _abi.OP_MEL_POW):
         outs += [("mel", op.p1, op.B * op.F * op.C * 4, torch.float32),
                  ("energy", op.p2, op.B * ((op.F + op.T - 1) // op.T) * 4, torch.float32)]
     elif t in (_abi.OP_INIT_X, _abi.OP_CONV_OUT, _abi.OP_AUX):
@@ -212,6 +214,32 @@ class Emulator:
         e[:, :F_] = (mel**2).sum(-1)
         self.a_f32(op.p2, B * nft).copy_(e.view(B, nft, ft).sum(-1).reshape(-1))
 
+    def op_sigp(self, op):
+        """padded signal [B][Lp] -> f32 planes in rows of C = hop / 2 samples, phase-split by 2 (csrc sig_planes_kernel)."""
+        B, Lp, F_, half = op.B, op.Lp, op.F, op.C
+        sig = self.a_f32(op.p0, B * Lp).view(B, Lp)
+        t = op.out[0].t
+        vals = torch.zeros(B * 2 * F_, t.nch * 8)
+        vals[:, :half] = sig[:, : 2 * F_ * half].reshape(B * 2 * F_, half)
+        b_idx = torch.arange(B).repeat_interleave(2 * F_)
+        l_idx = torch.arange(2 * F_).repeat(B)
+        self._scatter(t, b_idx, l_idx, vals)
+
+    def op_mel_pow(self, op):
+        """DFT rows [b Lh + f][cos | sin] -> power spectrum -> mel filterbank (csrc mel_pow_kernel); outputs as op_mel."""
+        B, F_, n_mels, Lh = op.B, op.F, op.C, op.Lh_A
+        nb, nbq, ld = op.i0, op.i1, op.i2
+        d = self.a_f32(op.p0, B * Lh * ld).view(B, Lh, ld)[:, :F_]
+        power = d[..., :nb] ** 2 + d[..., nbq : nbq + nb] ** 2
+        fb = self.w_f32(op.p4, nb * n_mels).view(nb, n_mels)
+        mel = power @ fb
+        self.a_f32(op.p1, B * F_ * n_mels).copy_(mel.reshape(-1))
+        ft = op.T
+        nft = (F_ + ft - 1) // ft
+        e = torch.zeros(B, nft * ft)
+        e[:, :F_] = (mel**2).sum(-1)
+        self.a_f32(op.p2, B * nft).copy_(e.view(B, nft, ft).sum(-1).reshape(-1))
+
     def op_mel_fin(self, op):
         B, F_, n_mels, nft = op.B, op.F, op.C, op.i0
         mel = self.a_f32(op.p0, B * F_ * n_mels).view(B, F_, n_mels)
@@ -366,6 +394,10 @@ class Emulator:
             self.op_mel(op)
         elif t == _abi.OP_MEL_FIN:
             self.op_mel_fin(op)
+        elif t == _abi.OP_SIGP:
+            self.op_sigp(op)
+        elif t == _abi.OP_MEL_POW:
+            self.op_mel_pow(op)
         elif t == _abi.OP_CONV_IN:
             self.op_conv_in(op)
         elif t == _abi.OP_INIT_X:

@@ -127,3 +127,31 @@ def test_split_bf16_images_of_the_fp32_tier():
     rec = (x[:, :, :, :, 0] + x[:, :, :, :, 1]).permute(0, 5, 1, 3, 2, 4, 6).reshape(n, s, q, ci)   # nt, n, s, q, g, j, e
     assert (rec - w4).abs().max() <= 2.0 ** -16 * w4.abs().max()
     assert torch.equal(x[:, :, :, :, 0].permute(0, 5, 1, 3, 2, 4, 6).reshape(n, s, q, ci), w4.to(torch.bfloat16).float())
+
+
+def test_dft_as_multi_tap_gemm_matches_framed_dft():
+    """weights.w4_dft: frames @ windowed basis == the multi-tap GEMM on the signal in half-hop rows, phase-split by 2
+    (reference condition.py:92-108: (n_fft - hop) / 2 zero padding in front, hop-spaced frames)."""
+    torch.manual_seed(1)
+    for hop, ov in ((160, 4), (240, 4)):
+        n_fft = ov * hop
+        basis, nb, nbp = weights.dft_basis(torch.hann_window(n_fft, periodic=True), n_fft)
+        w4, smin, c_pad, nbq = weights.w4_dft(basis, nb, nbp, n_fft, hop)
+        F = 9
+        sig = torch.randn(F * hop)
+        padl = (n_fft - hop) // 2
+        xp = torch.zeros((F - 1) * hop + n_fft)
+        xp[padl : padl + F * hop] = sig[: xp.numel() - padl]
+        ref = xp.unfold(0, n_fft, hop) @ basis                      # [F, 2 nbp]
+        half = hop // 2
+        rows = torch.zeros(2, F + 8, c_pad)                          # phase planes with 4 zero rows on either side
+        hh = sig.view(2 * F, half)
+        rows[0, 4 : 4 + F, :half] = hh[0::2]
+        rows[1, 4 : 4 + F, :half] = hh[1::2]
+        acc = torch.zeros(F, w4.shape[0])
+        for s in range(2):
+            for qi in range(w4.shape[2]):
+                q = smin + qi
+                acc += rows[s, 4 + q : 4 + q + F] @ w4[:, s, qi, :].t()
+        assert torch.allclose(acc[:, :nb], ref[:, :nb], atol=2e-4) and torch.allclose(acc[:, nbq : nbq + nb], ref[:, nbp : nbp + nb], atol=2e-4)
+        assert acc[:, nb:nbq].abs().max() == 0
