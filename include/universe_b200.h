@@ -93,7 +93,7 @@ typedef enum {
                         * the mel front end run as ONE multi-tap GEMM on the tensor cores (condition.py:92-108; a UV_OP_GEMM on
                         * f32 planes with a row-major output, see the fp32 notes below) */
   UV_OP_MEL_POW = 14   /* p0 = that GEMM's output f32 [b Lh_A + f][i2] (cos bins at column 0, sin bins at column i1, i0 bins)
-                        * -> power spectrum -> mel filterbank p4 (f32 [i0][C]) -> p1 / p2 as UV_OP_MEL (raw mel bands, partial
+                        * -> power spectrum -> mel filterbank p4 (f32 [i0][C]; p5 = int32 [C][2]: the bins [lo, hi) of each band) -> p1 / p2 as UV_OP_MEL (raw mel bands, partial
                         * energy sums per T frames) */
 } uv_op_type;
 

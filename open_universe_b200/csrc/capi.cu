@@ -324,11 +324,11 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
       if (op.T != kMelFT) return fail(UV_ERR_INVALID, "MEL_POW op built for another frame tile than the kernel's");
       const int nft = (op.F + kMelFT - 1) / kMelFT;
       const int threads = std::max(2 * (((op.i0 + 1) / 2 + 31) / 32 * 32), (op.C + 31) / 32 * 32);   // as the MEL op (same filterbank stage)
-      const size_t sm = mel_pow_smem_bytes(op.i0, op.C);
-      if (threads > 512 || sm > (size_t)kMelMaxSmem || op.C > threads || op.i1 < op.i0 || op.i2 < op.i1 + op.i0)
+      const size_t sm = mel_pow_smem_bytes(op.i0);
+      if (threads > 512 || sm > (size_t)kMelMaxSmem || op.C > threads || op.i1 < op.i0 || op.i2 < op.i1 + op.i0 || op.p4 < 0 || op.p5 < 0)
         return fail(UV_ERR_INVALID, "MEL_POW: bins / bands unsupported");
       CUDA_TRY(launch_pdl(mel_pow_kernel, dim3(nft, op.B), dim3(threads), sm, s, aptr<const float>(p, op.p0), op.i2, op.Lh_A, op.F, op.i0, op.i1, op.C,
-                          wptr<const float>(p, op.p4), aptr<float>(p, op.p1), aptr<float>(p, op.p2), nft, rowgeo(p, op)));
+                          wptr<const float>(p, op.p4), wptr<const int2>(p, op.p5), aptr<float>(p, op.p1), aptr<float>(p, op.p2), nft, rowgeo(p, op)));
       break;
     }
     case UV_OP_MEL_FIN: {

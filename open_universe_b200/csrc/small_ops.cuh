@@ -319,19 +319,19 @@ __global__ void __launch_bounds__(256) sig_planes_kernel(const float* __restrict
   store8(row_addr(out.t, b, h), out.t.esize_log2, ch, v);
 }
 
-// MEL_POW: power spectrum re^2 + im^2 of 32 frames -> shared memory [bin][frame] -> mel filterbank (the second half of
-// mel_kernel, same thread mapping) -> melraw [B][F][n_mels] and the partial energy sums mel_fin_kernel reduces.
-__host__ __device__ inline size_t mel_pow_smem_bytes(int nb, int n_mels) {
-  return ((size_t)nb * kMelPwPitch + 2 * (size_t)kMelFbRows * n_mels) * sizeof(float);
-}
+// MEL_POW: power spectrum re^2 + im^2 of 32 frames -> shared memory [bin][frame] -> mel filterbank -> melraw [B][F][n_mels]
+// and the partial energy sums mel_fin_kernel reduces.  Thread = (mel band m, group g of the tile's frames); a band only
+// walks the bins [lo, hi) its filter is non-zero on (rng, from the host: triangular filters see a few dozen of the
+// n_fft / 2 + 1 bins), reading its weights straight from the (cached) filterbank.
+__host__ __device__ inline size_t mel_pow_smem_bytes(int nb) { return (size_t)nb * kMelPwPitch * sizeof(float); }
 __global__ void __launch_bounds__(512) mel_pow_kernel(const float* __restrict__ D, int ld, int Lh, int F, int nb, int nbq,
-                                                      int n_mels, const float* __restrict__ fb, float* __restrict__ melraw,
-                                                      float* __restrict__ energy, int nft, const RowGeo* __restrict__ rows) {
+                                                      int n_mels, const float* __restrict__ fb, const int2* __restrict__ rng,
+                                                      float* __restrict__ melraw, float* __restrict__ energy, int nft,
+                                                      const RowGeo* __restrict__ rows) {
   pdl_launch_dependents();
   pdl_wait();
   extern __shared__ float smem_f[];
   float* pw = smem_f;                                   // [nb][kMelPwPitch]
-  float* fbs = smem_f + (size_t)nb * kMelPwPitch;        // [2][kMelFbRows][n_mels]
   __shared__ double sh[96];
   const int b = blockIdx.y, f0 = blockIdx.x * kMelFT;
   const int Fb = rows ? rows[b].F : F;
@@ -345,6 +345,7 @@ __global__ void __launch_bounds__(512) mel_pow_kernel(const float* __restrict__ 
     }
     pw[(size_t)k * kMelPwPitch + f] = p;
   }
+  __syncthreads();
   double e = 0, d1 = 0, d2 = 0;
   int ng = blockDim.x / n_mels;
   ng = ng >= 4 ? 4 : (ng >= 2 ? 2 : 1);
@@ -352,40 +353,23 @@ __global__ void __launch_bounds__(512) mel_pow_kernel(const float* __restrict__ 
   const int tpg = blockDim.x / ng;                 // threads per frame group
   const int g = threadIdx.x / tpg, m = threadIdx.x % tpg;
   const bool active = g < ng && m < n_mels;        // (n_mels <= tpg is checked by the host)
-  float acc[kMelFT];
+  if (active) {
+    float acc[kMelFT];
 #pragma unroll
-  for (int f = 0; f < kMelFT; ++f) acc[f] = 0.f;
-  const int chunk = kMelFbRows * n_mels;
-  const int n_chunks = (nb + kMelFbRows - 1) / kMelFbRows;
-  auto load_chunk = [&](int ci, float* dst) {
-    const int k0 = ci * kMelFbRows;
-    const int cnt = (nb - k0 < kMelFbRows ? nb - k0 : kMelFbRows) * n_mels;
-    for (int i = threadIdx.x; i < cnt; i += blockDim.x) dst[i] = fb[(size_t)k0 * n_mels + i];
-  };
-  load_chunk(0, fbs);
-  __syncthreads();
-  for (int ci = 0; ci < n_chunks; ++ci) {
-    float* cur = fbs + (ci & 1) * chunk;
-    if (ci + 1 < n_chunks) load_chunk(ci + 1, fbs + ((ci + 1) & 1) * chunk);
-    if (active) {
-      const int k0 = ci * kMelFbRows;
-      const int kn = nb - k0 < kMelFbRows ? nb - k0 : kMelFbRows;
-      const float* prow = pw + (size_t)k0 * kMelPwPitch + g * fpt;
-      for (int kk = 0; kk < kn; ++kk) {
-        const float w = cur[kk * n_mels + m];
+    for (int f = 0; f < kMelFT; ++f) acc[f] = 0.f;
+    const int2 r = rng[m];
+    const float* prow = pw + g * fpt;
+    for (int k = r.x; k < r.y; ++k) {
+      const float w = fb[(size_t)k * n_mels + m];
 #pragma unroll
-        for (int f = 0; f < kMelFT; f += 4) {
-          if (f < fpt) {
-            const float4 v = *reinterpret_cast<const float4*>(prow + (size_t)kk * kMelPwPitch + f);
-            acc[f] = fmaf(v.x, w, acc[f]); acc[f + 1] = fmaf(v.y, w, acc[f + 1]);
-            acc[f + 2] = fmaf(v.z, w, acc[f + 2]); acc[f + 3] = fmaf(v.w, w, acc[f + 3]);
-          }
+      for (int f = 0; f < kMelFT; f += 4) {
+        if (f < fpt) {
+          const float4 v = *reinterpret_cast<const float4*>(prow + (size_t)k * kMelPwPitch + f);
+          acc[f] = fmaf(v.x, w, acc[f]); acc[f + 1] = fmaf(v.y, w, acc[f + 1]);
+          acc[f + 2] = fmaf(v.z, w, acc[f + 2]); acc[f + 3] = fmaf(v.w, w, acc[f + 3]);
         }
       }
     }
-    __syncthreads();
-  }
-  if (active) {
 #pragma unroll
     for (int f = 0; f < kMelFT; ++f) {
       const int fr = f0 + g * fpt + f;

@@ -527,7 +527,7 @@ def _build_lane(pm, cfg, B, T, n_steps, aux=False, b_off=0, B_total=None, arena_
         op = new_op(_abi.OP_MEL_POW)
         op.B, op.F, op.C, op.T, op.Lh_A = B, Fr, mel["n_mels"], MEL_FT, lb.Lh
         op.i0, op.i1, op.i2 = mel["n_bins"], mel["dft_nbq"], dl["N_total"]
-        op.p0, op.p1, op.p2, op.p4 = pg.dft, pg.melraw, pg.mel_energy, mel["fb_w"]
+        op.p0, op.p1, op.p2, op.p4, op.p5 = pg.dft, pg.melraw, pg.mel_energy, mel["fb_w"], mel["fb_rng_w"]
         pg.emit(op, "c.mel.pow")
     else:
         op = new_op(_abi.OP_MEL)

@@ -460,7 +460,13 @@ def pack_model(sd, cfg, hp=False):
         was_hp, pm.hp = pm.hp, True
         pm.add_gemm("c.mel.dft", w4d, smin_d, w4d.shape[0])
         pm.hp = was_hp
-        pm.layers["c.mel"].update(dft_cpad=c_pad, dft_nbq=nbq, half=tot_ds // 2)
+        # bins [lo, hi) that feed each mel band (triangular filters: a band sees a few dozen bins, not all n_fft / 2 + 1)
+        nzr = []
+        for m in range(fb.shape[1]):
+            nz = torch.nonzero(fb[:, m]).reshape(-1)
+            nzr.append((int(nz.min()), int(nz.max()) + 1) if nz.numel() else (0, 0))
+        rng_w = pm.blob.add(np.asarray(nzr, dtype=np.int32))
+        pm.layers["c.mel"].update(dft_cpad=c_pad, dft_nbq=nbq, half=tot_ds // 2, fb_rng_w=rng_w)
     w4, smin = w4_plain(eff_weight(sd, cp + ".input_mel.conv"))
     pm.add_gemm("c.mel.conv", w4, smin, w4.shape[0], bias=sd[cp + ".input_mel.conv.bias"])
     pm.add_conv_block(sd, cp + ".input_mel.conv_block", "c.melblk")
