@@ -339,8 +339,8 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
     }
     case UV_OP_CONV_IN: {
       if (op.C > kEdgeMaxC || op.C % 8) return fail(UV_ERR_INVALID, "input conv: channel count unsupported");
-      const long long n = (long long)op.B * op.Lp;
-      CUDA_TRY(launch_pdl(conv_in_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, s, aptr<const float>(p, op.p0), op.B, op.Lp, op.C, op.f0,
+      if (op.B > 65535) return fail(UV_ERR_INVALID, "input conv: more than 65535 utterances per lane");
+      CUDA_TRY(launch_pdl(conv_in_kernel, dim3((unsigned)((op.Lp + 255) / 256), (unsigned)op.B), dim3(256), 0, s, aptr<const float>(p, op.p0), op.B, op.Lp, op.C, op.f0,
                                                                  wptr<const float>(p, op.p3), wptr<const float>(p, op.p4),
                                                                  op.n_out, to_out(p, op.out[0]), to_out(p, op.out[1]), op.i3 & 1, rowgeo(p, op)));
       break;
@@ -354,8 +354,10 @@ static int launch_op(uv_plan* p, int op_index, cudaStream_t s) {
     }
     case UV_OP_CONV_OUT: {
       if (op.C > kEdgeMaxC || op.C % 8) return fail(UV_ERR_INVALID, "output conv: channel count unsupported");
-      const long long n = (long long)op.B * op.Lp;
-      CUDA_TRY(launch_pdl(conv_out_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, s, to_desc(p, op.a), op.B, op.Lp, op.C, wptr<const float>(p, op.p3),
+      if (op.B > 65535) return fail(UV_ERR_INVALID, "output conv: more than 65535 utterances per lane");
+      // (a phase-split-by-2 input is walked in sample pairs: half the threads)
+      const int per_row = (op.a.split == 2 && !(op.Lp & 1)) ? op.Lp / 2 : op.Lp;
+      CUDA_TRY(launch_pdl(conv_out_kernel, dim3((unsigned)((per_row + 255) / 256), (unsigned)op.B), dim3(256), 0, s, to_desc(p, op.a), op.B, op.Lp, op.C, wptr<const float>(p, op.p3),
                                                                   wptr<const float>(p, op.p4), aptr<float>(p, op.p0),
                                                                   aptr<const StepCoef>(p, op.p1), op.i0, p->io_dev, op.i1,
                                                                   op.i2 > 0 ? op.i2 : op.B, op.i3 & 1, rowgeo(p, op)));

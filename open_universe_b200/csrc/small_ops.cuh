@@ -414,30 +414,61 @@ __global__ void __launch_bounds__(256) mel_fin_kernel(const float* __restrict__ 
 
 // ---------------------------------------------------------------- CONV_IN
 // 1 -> C, k=3, "same" input convolution on an f32 signal (score.py:285 on w_in*x,
-// condition.py:360), writing the raw tensor and the PReLU-activated copy.
+// condition.py:360), writing the raw tensor and / or PReLU-activated copies.
+// Both edge convs were instruction bound (ncu: sm 77 % / 60 %, dram 33 % / 31 %: ~550 / ~640 instructions per sample):
+// the grid is 2-D (block row = utterance: no 64-bit division per thread), activations that are not asked for are not
+// computed (a uniform branch instead of per-element selects), plane pointers advance by additions.
+__device__ __forceinline__ void store8_act(char* p, int esize_log2, int act, float a1, float a2, const float* v) {
+  float u[8];
+  if (act == 0) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) u[i] = v[i];
+  } else if (act == 1) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) u[i] = prelu1(v[i], a1);
+  } else {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) u[i] = prelu1(prelu1(v[i], a1), a2);
+  }
+  if (esize_log2 == 1) {
+    uint4 q;
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&q);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(u[2 * i], u[2 * i + 1]);
+    *reinterpret_cast<uint4*>(p) = q;
+  } else {
+    *reinterpret_cast<float4*>(p) = make_float4(u[0], u[1], u[2], u[3]);
+    *reinterpret_cast<float4*>(p + 16) = make_float4(u[4], u[5], u[6], u[7]);
+  }
+}
+
 __global__ void __launch_bounds__(256) conv_in_kernel(const float* __restrict__ x, int B, int Lp, int C, float in_scale,
                                                       const float* __restrict__ w /*[3][C]*/, const float* __restrict__ bias,
                                                       int n_out, OutDesc o0, OutDesc o1, int reverse, const RowGeo* __restrict__ rows) {
   pdl_launch_dependents();
   // the three taps and the bias of every channel, staged once per block: one 16-byte broadcast load per channel
-  // instead of four global loads per channel and thread (the kernel was load-instruction bound)
+  // instead of four global loads per channel and thread
   __shared__ float4 ws[kEdgeMaxC];
   for (int c = threadIdx.x; c < C; c += blockDim.x) ws[c] = make_float4(w[c], w[C + c], w[2 * C + c], bias[c]);
   __syncthreads();
   pdl_wait();
-  // reverse: blocks walk the signal from its end (the consumer of these tensors starts where this kernel finished)
-  const long long blk = reverse ? (long long)gridDim.x - 1 - blockIdx.x : blockIdx.x;
-  const long long idx = blk * blockDim.x + threadIdx.x;
-  if (idx >= (long long)B * Lp) return;
-  const int b = (int)(idx / Lp), l = (int)(idx - (long long)b * Lp);
+  // grid (blocks per utterance, utterances); reverse: blocks walk the signal from its end (the consumer of these
+  // tensors starts where this kernel finished)
+  const int bx = reverse ? (int)(gridDim.x - 1 - blockIdx.x) : (int)blockIdx.x;
+  const int b = reverse ? (int)(gridDim.y - 1 - blockIdx.y) : (int)blockIdx.y;
+  const int l = bx * (int)blockDim.x + (int)threadIdx.x;
+  if (l >= Lp) return;
   const int Lpb = rows ? rows[b].Lp : Lp;
   const float* xr = x + (size_t)b * Lp;
   const float xm = (l > 0 ? xr[l - 1] : 0.f) * in_scale;
   const float x0 = xr[l] * in_scale;
   const float xp = (l + 1 < Lp ? xr[l + 1] : 0.f) * in_scale;
   if (l >= Lpb) return;   // rows past the utterance's own length stay zero (x is zero there as well)
-  RowAddr r0 = row_addr(o0.t, b, l), r1 = row_addr(o1.t, b, l);
-  for (int ch = 0; ch < (C >> 3); ++ch) {
+  const RowAddr r0 = row_addr(o0.t, b, l), r1 = row_addr(o1.t, b, l);
+  char* p0 = r0.p;
+  char* p1 = r1.p;
+  const int nch = C >> 3;
+  for (int ch = 0; ch < nch; ++ch) {
     float v[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
@@ -445,16 +476,12 @@ __global__ void __launch_bounds__(256) conv_in_kernel(const float* __restrict__ 
       v[i] = fmaf(q.x, xm, fmaf(q.y, x0, fmaf(q.z, xp, q.w)));
     }
     if (n_out > 0) {
-      float u[8];
-#pragma unroll
-      for (int i = 0; i < 8; ++i) u[i] = apply_act(v[i], o0.act, o0.a1, o0.a2);
-      store8(r0, o0.t.esize_log2, ch, u);
+      store8_act(p0, o0.t.esize_log2, o0.act, o0.a1, o0.a2, v);
+      p0 += r0.pstride;
     }
     if (n_out > 1) {
-      float u[8];
-#pragma unroll
-      for (int i = 0; i < 8; ++i) u[i] = apply_act(v[i], o1.act, o1.a1, o1.a2);
-      store8(r1, o1.t.esize_log2, ch, u);
+      store8_act(p1, o1.t.esize_log2, o1.act, o1.a1, o1.a2, v);
+      p1 += r1.pstride;
     }
   }
 }
@@ -475,6 +502,54 @@ __global__ void __launch_bounds__(256) init_x_kernel(const IoTable* io, long lon
 // ---------------------------------------------------------------- CONV_OUT
 // output_conv (C -> 1, k=3; score.py:290) on the already doubly-activated planes, fused with
 // the EDM wrapper and the sampler update (universe.py:197-209, 334-343):  x <- a x + b net + c z.
+template <bool BF16>
+__device__ __forceinline__ void unpack8(const char* p, float* v) {
+  if (BF16) {
+    const uint4 u = *reinterpret_cast<const uint4*>(p);
+    const uint32_t q[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {   // bf16 -> f32 is a 16-bit shift
+      v[2 * i] = __uint_as_float(q[i] << 16);
+      v[2 * i + 1] = __uint_as_float(q[i] & 0xFFFF0000u);
+    }
+  } else {
+    const float4 a = *reinterpret_cast<const float4*>(p), c = *reinterpret_cast<const float4*>(p + 16);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = c.x; v[5] = c.y; v[6] = c.z; v[7] = c.w;
+  }
+}
+__device__ __forceinline__ float fma8(const float* v, const float* wk, float acc) {
+  const float4 w0 = *reinterpret_cast<const float4*>(wk), w1 = *reinterpret_cast<const float4*>(wk + 4);
+  acc = fmaf(v[0], w0.x, acc); acc = fmaf(v[1], w0.y, acc); acc = fmaf(v[2], w0.z, acc); acc = fmaf(v[3], w0.w, acc);
+  acc = fmaf(v[4], w1.x, acc); acc = fmaf(v[5], w1.y, acc); acc = fmaf(v[6], w1.z, acc); acc = fmaf(v[7], w1.w, acc);
+  return acc;
+}
+
+// Phase-split-by-2 input (the space-to-depth form of the finest level): thread = row m of the two phase planes =
+// samples 2m and 2m + 1, whose taps are P1[m-1], P0[m], P1[m] and P0[m], P1[m], P0[m+1]: four coalesced 16-byte
+// loads per chunk feed two samples (a thread per sample needs six, alternating between the planes).  Rows -1 and
+// Lp / 2 are the never-written zero rows of the layout.  Per sample the sum runs chunk by chunk, tap by tap, channel
+// by channel, exactly like the general path below.
+template <bool BF16>
+__device__ __forceinline__ void conv_out_pair(const TensDesc& a, int b, int m, int C, const float* ws, float& acc0, float& acc1) {
+  const long long es8 = 8ll << a.esize_log2;
+  const long long pstride = (long long)a.P * es8;
+  const char* p0 = a.base + ((long long)a.G + (long long)b * a.Lh + m) * es8;   // phase 0, chunk 0, row m
+  const char* p1 = p0 + (long long)a.nchunks * pstride;                          // phase 1
+  const int nch = C >> 3;
+  for (int ch = 0; ch < nch; ++ch) {
+    float va[8], vb[8], vc[8], vd[8];
+    unpack8<BF16>(p1 - es8, va);   // sample 2m - 1
+    unpack8<BF16>(p0, vb);         // 2m
+    unpack8<BF16>(p1, vc);         // 2m + 1
+    unpack8<BF16>(p0 + es8, vd);   // 2m + 2
+    const float* w0 = ws + ch * 8;
+    acc0 = fma8(va, w0, acc0); acc0 = fma8(vb, w0 + C, acc0); acc0 = fma8(vc, w0 + 2 * C, acc0);
+    acc1 = fma8(vb, w0, acc1); acc1 = fma8(vc, w0 + C, acc1); acc1 = fma8(vd, w0 + 2 * C, acc1);
+    p0 += pstride;
+    p1 += pstride;
+  }
+}
+
 __global__ void __launch_bounds__(256) conv_out_kernel(TensDesc a, int B, int Lp, int C, const float* __restrict__ w /*[3][C]*/,
                                                        const float* __restrict__ bias, float* __restrict__ x,
                                                        const StepCoef* __restrict__ coef, int step, const IoTable* io,
@@ -484,11 +559,42 @@ __global__ void __launch_bounds__(256) conv_out_kernel(TensDesc a, int B, int Lp
   for (int i = threadIdx.x; i < 3 * C; i += blockDim.x) ws[i] = w[i];
   __syncthreads();
   pdl_wait();
-  const long long blk = reverse ? (long long)gridDim.x - 1 - blockIdx.x : blockIdx.x;
-  const long long idx = blk * blockDim.x + threadIdx.x;
-  if (idx >= (long long)B * Lp) return;
-  const int b = (int)(idx / Lp), l = (int)(idx - (long long)b * Lp);
-  const int Lpb = rows ? rows[b].Lp : Lp;   // (used only after the loads below have been issued)
+  // grid (blocks per utterance, utterances): no 64-bit division per thread
+  const int bx = reverse ? (int)(gridDim.x - 1 - blockIdx.x) : (int)blockIdx.x;
+  const int b = reverse ? (int)(gridDim.y - 1 - blockIdx.y) : (int)blockIdx.y;
+  const int Lpb = rows ? rows[b].Lp : Lp;
+  const StepCoef cf = coef[step];
+  const long long nbase = ((long long)step * B_total + b_off) * Lp;   // this lane's rows of step `step` in noise / dbg
+  if (a.split == 2 && !(Lp & 1)) {
+    const int m = bx * (int)blockDim.x + (int)threadIdx.x;
+    const int l = 2 * m;
+    if (l >= Lp) return;
+    float acc0 = bias[0], acc1 = acc0;
+    if (a.esize_log2 == 1) conv_out_pair<true>(a, b, m, C, ws, acc0, acc1);
+    else conv_out_pair<false>(a, b, m, C, ws, acc0, acc1);
+    const long long idx = (long long)b * Lp + l;
+    float2* xp = reinterpret_cast<float2*>(x + idx);
+    if (l >= Lpb) {   // past the utterance's own length (even, like Lp): the state stays zero
+      *xp = make_float2(0.f, 0.f);
+      if (io->dbg) { io->dbg[nbase + idx] = 0.f; io->dbg[nbase + idx + 1] = 0.f; }   // (caller memory: no alignment assumed)
+      return;
+    }
+    const float2 xo = *xp;
+    float2 xn = make_float2(cf.a * xo.x + cf.b * acc0, cf.a * xo.y + cf.b * acc1);
+    if (cf.c != 0.f) {
+      float2 z;
+      if (io->noise) z = make_float2(io->noise[nbase + (long long)B_total * Lp + idx], io->noise[nbase + (long long)B_total * Lp + idx + 1]);
+      else z = make_float2(unit_normal(io->seed, step + 1, b_off + b, l), unit_normal(io->seed, step + 1, b_off + b, l + 1));
+      xn.x = fmaf(cf.c, z.x, xn.x);
+      xn.y = fmaf(cf.c, z.y, xn.y);
+    }
+    *xp = xn;
+    if (io->dbg) { io->dbg[nbase + idx] = acc0; io->dbg[nbase + idx + 1] = acc1; }
+    return;
+  }
+  const int l = bx * (int)blockDim.x + (int)threadIdx.x;
+  if (l >= Lp) return;
+  const long long idx = (long long)b * Lp + l;
   // rows l-1, l, l+1 of the planes tensor (plain: neighbouring rows, rows -1 and Lp are the zero gap; phase-split:
   // the neighbours live in other phase planes, samples outside [0, Lp) are skipped)
   RowAddr rt[3];
@@ -511,25 +617,21 @@ __global__ void __launch_bounds__(256) conv_out_kernel(TensDesc a, int B, int Lp
       if (rk.p == nullptr) continue;
       float v[8];
       load8(rk, a.esize_log2, ch, v);
-      const float4 w0 = *reinterpret_cast<const float4*>(ws + k * C + ch * 8);
-      const float4 w1 = *reinterpret_cast<const float4*>(ws + k * C + ch * 8 + 4);
-      acc = fmaf(v[0], w0.x, acc); acc = fmaf(v[1], w0.y, acc); acc = fmaf(v[2], w0.z, acc); acc = fmaf(v[3], w0.w, acc);
-      acc = fmaf(v[4], w1.x, acc); acc = fmaf(v[5], w1.y, acc); acc = fmaf(v[6], w1.z, acc); acc = fmaf(v[7], w1.w, acc);
+      acc = fma8(v, ws + k * C + ch * 8, acc);
     }
   }
-  const StepCoef cf = coef[step];
   if (l >= Lpb) {   // past the utterance's own length: the state stays zero (the rows read above are zero padding)
     x[idx] = 0.f;
-    if (io->dbg) io->dbg[((long long)step * B_total + b_off) * Lp + idx] = 0.f;
+    if (io->dbg) io->dbg[nbase + idx] = 0.f;
     return;
   }
   float xn = cf.a * x[idx] + cf.b * acc;
   if (cf.c != 0.f) {
-    const float z = io->noise ? io->noise[((long long)(step + 1) * B_total + b_off) * Lp + idx] : unit_normal(io->seed, step + 1, b_off + b, l);
+    const float z = io->noise ? io->noise[nbase + (long long)B_total * Lp + idx] : unit_normal(io->seed, step + 1, b_off + b, l);
     xn = fmaf(cf.c, z, xn);
   }
   x[idx] = xn;
-  if (io->dbg) io->dbg[((long long)step * B_total + b_off) * Lp + idx] = acc;
+  if (io->dbg) io->dbg[nbase + idx] = acc;
 }
 
 // ---------------------------------------------------------------- POST
